@@ -1,0 +1,416 @@
+"""ctypes binding of the C ABI declared in include/ag2.h.
+
+This is plumbing for tests/, bench.py and the multi-GPU host (sharded.py): it
+marshals numpy arrays into the `ag2_*` entry points of libag2.so and nothing
+else.  The same `Api` class binds the CPU oracle (prefix ``ag2o_``) for the
+parity tests — the oracle itself is never loaded from this package
+(see oracle/binding.py).
+
+There is no CPU fallback: `load()` raises if libag2.so has not been built, and
+`Context()` raises `Ag2Error(AG2_E_NO_DEVICE)` when no CUDA device is usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libag2.so")
+
+AG2_OK = 0
+AG2_E_INVALID, AG2_E_NO_DEVICE, AG2_E_CUDA, AG2_E_EMPTY_CLOUD = -1, -2, -3, -4
+AG2_E_NO_SAMPLES, AG2_E_NO_WEIGHTS, AG2_E_STATE, AG2_E_IO, AG2_E_CAPACITY, AG2_E_NOMEM = -5, -6, -7, -8, -9, -10
+MODE_NONE, MODE_PREDICTION, MODE_GEOMETRIC = 0, 1, 2
+LIST_HYPOTHESES, LIST_PRUNED, LIST_ANTIPODAL, LIST_SELECTED = 0, 1, 2, 3
+IMAGE_BYTES = 60 * 60 * 3
+
+
+class Params(C.Structure):
+    """ag2_params (include/ag2.h) == HandSearch::Parameters + GraspDetector members."""
+
+    _fields_ = [
+        ("nn_radius_taubin", C.c_double),
+        ("nn_radius_hands", C.c_double),
+        ("num_orientations", C.c_int32),
+        ("num_threads", C.c_int32),
+        ("num_samples", C.c_int32),
+        ("reserved0", C.c_int32),
+        ("finger_width", C.c_double),
+        ("hand_outer_diameter", C.c_double),
+        ("hand_depth", C.c_double),
+        ("hand_height", C.c_double),
+        ("init_bite", C.c_double),
+        ("cam_tf_left", C.c_double * 16),
+        ("cam_tf_right", C.c_double * 16),
+        ("workspace", C.c_double * 6),
+        ("antipodal_mode", C.c_int32),
+        ("filter_half_grasps", C.c_int32),
+        ("prune", C.c_int32),
+        ("num_selected", C.c_int32),
+        ("min_score_diff", C.c_double),
+        ("min_aperture", C.c_double),
+        ("max_aperture", C.c_double),
+        ("normals_radius", C.c_double),
+        ("rng_seed", C.c_uint64),
+    ]
+
+    def copy(self) -> "Params":
+        p = Params()
+        C.memmove(C.byref(p), C.byref(self), C.sizeof(Params))
+        return p
+
+
+HYPOTHESIS_DTYPE = np.dtype(
+    [
+        ("surface", "<f8", 3),
+        ("bottom", "<f8", 3),
+        ("top", "<f8", 3),
+        ("axis", "<f8", 3),
+        ("approach", "<f8", 3),
+        ("binormal", "<f8", 3),
+        ("width", "<f8"),
+        ("score", "<f8"),
+        ("sample_id", "<i4"),
+        ("orientation_id", "<i4"),
+        ("half_antipodal", "u1"),
+        ("full_antipodal", "u1"),
+        ("finger_slot", "u1"),
+        ("depth_step", "u1"),
+        ("num_in_box", "<i4"),
+        ("hand_top", "<f8"),
+        ("hand_bottom", "<f8"),
+    ],
+    align=True,
+)
+assert HYPOTHESIS_DTYPE.itemsize == 192
+
+SWEEP_DTYPE = np.dtype(
+    [
+        ("fingers", "<u4"),
+        ("hand", "<u2"),
+        ("slot", "i1"),
+        ("depth_step", "i1"),
+        ("num_in_box", "<i4"),
+        ("antipodal", "u1"),
+        ("emitted", "u1"),
+        ("reserved", "<u2"),
+    ],
+    align=True,
+)
+assert SWEEP_DTYPE.itemsize == 16
+
+FRAME_DTYPE = np.dtype(
+    [
+        ("sample", "<f8", 3),
+        ("normal", "<f8", 3),
+        ("binormal", "<f8", 3),
+        ("curvature_axis", "<f8", 3),
+        ("valid", "<i4"),
+        ("majority_cam", "<i4"),
+        ("num_neighbors", "<i4"),
+        ("reserved", "<i4"),
+    ],
+    align=True,
+)
+assert FRAME_DTYPE.itemsize == 112
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("num_points", C.c_int64),
+        ("num_samples", C.c_int64),
+        ("num_frames", C.c_int64),
+        ("num_hypotheses", C.c_int64),
+        ("num_pruned", C.c_int64),
+        ("num_antipodal", C.c_int64),
+        ("num_selected", C.c_int64),
+        ("sum_neighbors_hands", C.c_int64),
+        ("sum_cropped", C.c_int64),
+        ("sum_in_box", C.c_int64),
+        ("sum_neighbors_normals", C.c_int64),
+        ("gpu_launches", C.c_int64),
+        ("ms_phase", C.c_double * 8),
+    ]
+
+    def as_dict(self) -> dict:
+        d = {k: int(getattr(self, k)) for k, _ in self._fields_[:-1]}
+        d["ms_phase"] = dict(
+            zip(["grid", "normals", "frames", "hands", "prune", "render", "lenet", "select"], list(self.ms_phase))
+        )
+        return d
+
+
+class Ag2Error(RuntimeError):
+    def __init__(self, code: int, what: str, detail: str = ""):
+        self.code = code
+        super().__init__(f"{what} failed: {code}" + (f" ({detail})" if detail else ""))
+
+
+LENET_SHAPES = [
+    ("conv1_w", (20, 3, 5, 5)),
+    ("conv1_b", (20,)),
+    ("conv2_w", (50, 20, 5, 5)),
+    ("conv2_b", (50,)),
+    ("ip1_w", (500, 7200)),
+    ("ip1_b", (500,)),
+    ("ip2_w", (2, 500)),
+    ("ip2_b", (2,)),
+]
+
+
+def _fptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class Api:
+    """Binds one shared library exporting the ag2.h surface under `prefix`."""
+
+    def __init__(self, path: str, prefix: str = "ag2_"):
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                f"{path} not found: build it first (python -c 'import __graft_entry__ as g; g.build()'). "
+                "There is no CPU fallback for the CUDA path."
+            )
+        self.path = path
+        self.prefix = prefix
+        self.lib = C.CDLL(path, mode=C.RTLD_GLOBAL if prefix == "ag2_" else C.RTLD_LOCAL)
+
+    def fn(self, name: str):
+        f = getattr(self.lib, self.prefix + name)
+        f.restype = C.c_int
+        return f
+
+    def has(self, name: str) -> bool:
+        return hasattr(self.lib, self.prefix + name)
+
+
+_api: Optional[Api] = None
+
+
+def load() -> Api:
+    """Loads libag2.so (the CUDA library).  Raises if it is missing."""
+    global _api
+    if _api is None:
+        _api = Api(LIB_PATH, "ag2_")
+    return _api
+
+
+def default_params() -> Params:
+    p = Params()
+    rc = load().fn("default_params")(C.byref(p))
+    if rc:
+        raise Ag2Error(rc, "ag2_default_params")
+    return p
+
+
+class Context:
+    """One ag2_ctx (or ag2o_ctx): one GPU, one in-flight detect call."""
+
+    def __init__(self, params: Params, device: int = 0, api: Optional[Api] = None):
+        self.api = api or load()
+        self.is_oracle = self.api.prefix != "ag2_"
+        self._h = C.c_void_p()
+        self.params = params.copy()
+        if self.is_oracle:
+            rc = self.api.fn("create")(C.byref(self.params), C.byref(self._h))
+        else:
+            rc = self.api.fn("create")(C.byref(self.params), C.c_int(device), C.byref(self._h))
+        if rc:
+            raise Ag2Error(rc, self.api.prefix + "create")
+        self.n_points = 0
+        self.n_samples = 0
+
+    # -- plumbing
+    def _call(self, name: str, *args):
+        rc = self.api.fn(name)(self._h, *args)
+        if rc:
+            detail = ""
+            if not self.is_oracle and self.api.has("last_error"):
+                f = self.api.lib.ag2_last_error
+                f.restype = C.c_char_p
+                detail = (f(self._h) or b"").decode()
+            raise Ag2Error(rc, self.api.prefix + name, detail)
+
+    def close(self):
+        if self._h:
+            self.api.fn("destroy")(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- parameters / weights
+    def set_params(self, params: Params):
+        self.params = params.copy()
+        self._call("set_params", C.byref(self.params))
+
+    def set_lenet_weights(self, weights: dict):
+        arrs = []
+        for name, shape in LENET_SHAPES:
+            a = np.ascontiguousarray(weights[name], dtype=np.float32)
+            assert a.shape == shape, (name, a.shape, shape)
+            arrs.append(a)
+        self._keep = arrs
+        self._call("set_lenet_weights", *[_fptr(a) for a in arrs])
+
+    def init_lenet_xavier(self, seed: int):
+        self._call("init_lenet_xavier", C.c_uint64(seed))
+
+    def load_lenet_caffemodel(self, path: str):
+        self._call("load_lenet_caffemodel", C.c_char_p(path.encode()))
+
+    def get_lenet_weights(self) -> dict:
+        out = {n: np.zeros(s, dtype=np.float32) for n, s in LENET_SHAPES}
+        self._call("get_lenet_weights", *[_fptr(out[n]) for n, _ in LENET_SHAPES])
+        return out
+
+    # -- inputs
+    def set_cloud(self, xyz: np.ndarray, cam_mask: Optional[np.ndarray] = None, num_cams: int = 1,
+                  normals: Optional[np.ndarray] = None):
+        xyz = np.asarray(xyz)
+        assert xyz.dtype == np.float32 and xyz.ndim == 2 and xyz.shape[1] >= 3
+        if not xyz.flags.c_contiguous:
+            xyz = np.ascontiguousarray(xyz)
+        n = xyz.shape[0]
+        stride = xyz.strides[0]
+        cam = None if cam_mask is None else np.ascontiguousarray(cam_mask, dtype=np.uint8)
+        nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32)
+        if cam is not None:
+            assert cam.shape == (n,)
+        if nrm is not None:
+            assert nrm.shape == (n, 3)
+        self._cloud_keep = (xyz, cam, nrm)
+        self._call("set_cloud", _fptr(xyz), C.c_size_t(stride), C.c_size_t(n), _fptr(cam), C.c_int(num_cams),
+                   _fptr(nrm))
+        self.n_points = n
+
+    def set_cloud_device(self, d_xyz: int, n: int, d_cam_mask: int, num_cams: int, d_normals: int = 0):
+        self._call("set_cloud_device", C.c_void_p(d_xyz), C.c_size_t(n), C.c_void_p(d_cam_mask or None),
+                   C.c_int(num_cams), C.c_void_p(d_normals or None))
+        self.n_points = n
+
+    def set_sample_indices(self, idx):
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        self._call("set_sample_indices", _fptr(idx), C.c_size_t(idx.size))
+        self.n_samples = idx.size
+
+    def set_sample_points(self, xyz):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        self._call("set_sample_points", _fptr(xyz), C.c_size_t(xyz.shape[0]))
+        self.n_samples = xyz.shape[0]
+
+    def set_sample_id_offset(self, first: int):
+        self._call("set_sample_id_offset", C.c_int64(first))
+
+    # -- stages
+    def compute_normals(self):
+        self._call("compute_normals")
+
+    def generate_hypotheses(self):
+        self._call("generate_hypotheses")
+
+    def prune(self):
+        self._call("prune")
+
+    def render_images(self, fetch: bool = True) -> Optional[np.ndarray]:
+        if not fetch:
+            self._call("render_images", None)
+            return None
+        # the count is known after prune
+        n = self.num(LIST_PRUNED)
+        out = np.zeros((n, 60, 60, 3), dtype=np.uint8)
+        self._call("render_images", _fptr(out))
+        return out
+
+    def classify(self):
+        self._call("classify")
+
+    def select(self):
+        self._call("select")
+
+    def detect(self):
+        self._call("detect")
+
+    def synchronize(self):
+        if not self.is_oracle:
+            self._call("synchronize")
+
+    # -- outputs
+    def num(self, which: int) -> int:
+        n = C.c_size_t()
+        self._call("num_hypotheses", C.c_int(which), C.byref(n))
+        return int(n.value)
+
+    def hypotheses(self, which: int = LIST_HYPOTHESES) -> np.ndarray:
+        n = self.num(which)
+        out = np.zeros(max(n, 1), dtype=HYPOTHESIS_DTYPE)
+        got = C.c_size_t()
+        self._call("get_hypotheses", C.c_int(which), _fptr(out), C.c_size_t(out.size), C.byref(got))
+        return out[: int(got.value)]
+
+    def stats(self) -> dict:
+        s = Stats()
+        self._call("get_stats", C.byref(s))
+        return s.as_dict()
+
+    def normals(self) -> np.ndarray:
+        out = np.zeros((self.n_points, 3), dtype=np.float32)
+        self._call("get_normals", _fptr(out))
+        return out
+
+    def frames(self) -> np.ndarray:
+        out = np.zeros(max(self.n_samples, 1), dtype=FRAME_DTYPE)
+        self._call("get_frames", _fptr(out), C.c_size_t(out.size))
+        return out[: self.n_samples]
+
+    def sweep_records(self) -> np.ndarray:
+        R = self.params.num_orientations
+        out = np.zeros(max(self.n_samples * R, 1), dtype=SWEEP_DTYPE)
+        self._call("get_sweep_records", _fptr(out), C.c_size_t(out.size))
+        return out[: self.n_samples * R].reshape(self.n_samples, R)
+
+    def radius_search(self, q, radius: float, brute: bool = False):
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        cap = max(self.n_points, 1)
+        idx = np.zeros(cap, dtype=np.int32)
+        d2 = np.zeros(cap, dtype=np.float32)
+        n = C.c_size_t()
+        if self.is_oracle:
+            self._call("radius_search", _fptr(q), C.c_double(radius), C.c_int(int(brute)), _fptr(idx), _fptr(d2),
+                       C.c_size_t(cap), C.byref(n))
+        else:
+            self._call("radius_search", _fptr(q), C.c_double(radius), _fptr(idx), _fptr(d2), C.c_size_t(cap),
+                       C.byref(n))
+        k = int(n.value)
+        return idx[:k].copy(), d2[:k].copy()
+
+    def in_box(self, which: int, h: int) -> np.ndarray:
+        cap = max(self.n_points, 1)
+        idx = np.zeros(cap, dtype=np.int32)
+        n = C.c_size_t()
+        self._call("get_in_box", C.c_int(which), C.c_size_t(h), _fptr(idx), C.c_size_t(cap), C.byref(n))
+        return idx[: int(n.value)].copy()
+
+    def logits(self) -> np.ndarray:
+        n = self.num(LIST_PRUNED)
+        out = np.zeros((max(n, 1), 2), dtype=np.float32)
+        self._call("get_logits", _fptr(out), C.c_size_t(out.shape[0]))
+        return out[:n]
+
+    def classify_images(self, images: np.ndarray) -> np.ndarray:
+        images = np.ascontiguousarray(images, dtype=np.uint8).reshape(-1, 60, 60, 3)
+        out = np.zeros((images.shape[0], 2), dtype=np.float32)
+        self._call("classify_images", _fptr(images), C.c_size_t(images.shape[0]), _fptr(out))
+        return out

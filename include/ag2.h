@@ -1,0 +1,264 @@
+/*
+ * ag2.h — C ABI of the B200-native grasp-hypothesis hot path (libag2.so).
+ *
+ * This is the drop-in boundary for ONE path of gwding/agile_grasp2: everything
+ * GraspDetector::detectGraspPoses does between receiving a CloudCamera and
+ * returning scored GraspHypothesis records (reference grasp_detector.cpp:84-282):
+ *   neighbour search -> normals -> local frames -> hand search -> antipodal test
+ *   -> prune -> grasp images -> LeNet -> score/select.
+ *
+ * The reference has no FFI of its own; its boundary is a C++ class surface
+ * (hand_search.h:93-133, learning.h:75-81, caffe_classifier.h:55-66,
+ * grasp_detector.h:72-126).  Every entry point below names the reference
+ * interface it replaces.  include/agile_grasp2/ holds header-only C++ shims with the
+ * reference's class names that forward to these functions.
+ *
+ * Conventions: extern "C", plain pointers and sizes, no torch/Eigen/PCL types.
+ * Every function returns an int status: AG2_OK (0) or a negative AG2_E_* code;
+ * ag2_strerror() names it.  One ctx == one GPU == one in-flight call; calls on a
+ * ctx must be serialised by the caller (the reference's HandSearch is not
+ * re-entrant either: it keeps cloud_normals_ as member state, hand_search.h:172).
+ * The caller owns every host buffer it passes in or receives; the ctx owns all
+ * device memory, streams and pinned staging.  There is NO CPU fallback: if no
+ * CUDA device is usable ag2_create fails with AG2_E_NO_DEVICE.
+ */
+#ifndef AG2_H_
+#define AG2_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AG2_ABI_VERSION 1
+
+/* status codes */
+enum {
+  AG2_OK = 0,
+  AG2_E_INVALID = -1,      /* bad argument / bad parameter value */
+  AG2_E_NO_DEVICE = -2,    /* no usable CUDA device (no CPU fallback exists) */
+  AG2_E_CUDA = -3,         /* a CUDA runtime call failed; see ag2_last_error */
+  AG2_E_EMPTY_CLOUD = -4,  /* reference: empty vector (grasp_detector.cpp:86-91) */
+  AG2_E_NO_SAMPLES = -5,
+  AG2_E_NO_WEIGHTS = -6,   /* antipodal_mode 1 without classifier weights */
+  AG2_E_STATE = -7,        /* stage called out of order */
+  AG2_E_IO = -8,           /* file could not be read / parsed */
+  AG2_E_CAPACITY = -9,     /* caller buffer too small */
+  AG2_E_NOMEM = -10
+};
+
+/* antipodal_mode, reference grasp_detector.cpp:5-7 */
+enum { AG2_MODE_NONE = 0, AG2_MODE_PREDICTION = 1, AG2_MODE_GEOMETRIC = 2 };
+
+#define AG2_MAX_ORIENTATIONS 64
+#define AG2_NUM_FINGER_SLOTS 20 /* 2 x 10 placements, finger_hand.cpp:7-13 */
+#define AG2_MAX_DEEPEN_STEPS 62
+#define AG2_IMAGE_SIZE 60       /* Learning(60, ...), grasp_detector.cpp:56 */
+#define AG2_IMAGE_BYTES (60 * 60 * 3)
+
+/*
+ * Parameters.  Mirrors HandSearch::Parameters (hand_search.h:72-91) field for
+ * field, followed by the GraspDetector members that steer the path
+ * (grasp_detector.cpp:17-80).  ag2_default_params() fills the compiled-in
+ * defaults of the reference.
+ */
+typedef struct ag2_params {
+  /* HandSearch::Parameters */
+  double nn_radius_taubin;    /* radius of the local-frame neighbourhood (0.01) */
+  double nn_radius_hands;     /* radius of the hand-search neighbourhood (0.1) */
+  int32_t num_orientations;   /* 8 */
+  int32_t num_threads;        /* accepted; used only by CPU baselines */
+  int32_t num_samples;        /* informational, as in the reference */
+  int32_t reserved0;
+  double finger_width;        /* 0.01 */
+  double hand_outer_diameter; /* 0.09 */
+  double hand_depth;          /* 0.06 */
+  double hand_height;         /* 0.02 */
+  double init_bite;           /* 0.015 (launch files use 0.01) */
+  double cam_tf_left[16];     /* 4x4 row-major camera pose */
+  double cam_tf_right[16];
+  /* GraspDetector */
+  double workspace[6];        /* minX maxX minY maxY minZ maxZ */
+  int32_t antipodal_mode;     /* AG2_MODE_* (reference default PREDICTION) */
+  int32_t filter_half_grasps; /* bool, default 1 */
+  int32_t prune;              /* bool: run S13; the reference skips it when the
+                                 sample_indices param is set (grasp_detector.cpp:150-160) */
+  int32_t num_selected;       /* 50; <=0 keeps all */
+  double min_score_diff;      /* 500.0 */
+  double min_aperture;        /* 0.03 */
+  double max_aperture;        /* 0.07 */
+  /* constants the reference hard-codes, exposed for the scaling studies */
+  double normals_radius;      /* 0.01, hand_search.cpp:91 */
+  uint64_t rng_seed;          /* counter-based replacement of rand() (hand_search.cpp:130) */
+} ag2_params;
+
+/*
+ * One grasp hypothesis: the GraspMsg fields (msg/GraspMsg.msg:5-16,
+ * grasp_hypothesis.cpp:37-50) in double precision plus provenance.  192 bytes.
+ */
+typedef struct ag2_hypothesis {
+  double surface[3];
+  double bottom[3];
+  double top[3];
+  double axis[3];
+  double approach[3];
+  double binormal[3];
+  double width;
+  double score;
+  int32_t sample_id;       /* position in the sample list given to the ctx */
+  int32_t orientation_id;  /* 0 .. num_orientations-1 */
+  uint8_t half_antipodal;
+  uint8_t full_antipodal;
+  uint8_t finger_slot;     /* chosen placement e (0..9) */
+  uint8_t depth_step;      /* deepen steps taken beyond init_bite */
+  int32_t num_in_box;      /* points in the closing region */
+  double hand_top;         /* FingerHand::top_    (hand frame, m) */
+  double hand_bottom;      /* FingerHand::bottom_ (hand frame, m) */
+} ag2_hypothesis;
+
+/* Per (sample, orientation) trace of the finger sweep, for parity tests. */
+typedef struct ag2_sweep_record {
+  uint32_t fingers;     /* bit i: slot i collision-free at init_bite (finger_hand.cpp:17-93) */
+  uint16_t hand;        /* bit i: fingers[i] && fingers[10+i] (finger_hand.cpp:313-325) */
+  int8_t slot;          /* chosen e or -1 */
+  int8_t depth_step;    /* last successful deepen step (0 = init_bite) or -1 */
+  int32_t num_in_box;   /* -1 if the orientation was infeasible */
+  uint8_t antipodal;    /* 0 NO, 1 HALF, 2 FULL (antipodal.cpp:3-5) */
+  uint8_t emitted;      /* 1 if a hypothesis was emitted */
+  uint16_t reserved;
+} ag2_sweep_record;
+
+/* Local frame of one sample (local_frame.h:53-146). */
+typedef struct ag2_frame {
+  double sample[3];
+  double normal[3];
+  double binormal[3];
+  double curvature_axis[3];
+  int32_t valid;           /* 0: no neighbours within nn_radius_taubin -> sample dropped */
+  int32_t majority_cam;
+  int32_t num_neighbors;   /* neighbours within nn_radius_taubin */
+  int32_t reserved;
+} ag2_frame;
+
+/* Stage counters (the reference prints these, grasp_detector.cpp:142,155,222,253). */
+typedef struct ag2_stats {
+  int64_t num_points;
+  int64_t num_samples;
+  int64_t num_frames;
+  int64_t num_hypotheses;       /* emitted by the hand search */
+  int64_t num_pruned;           /* survivors of S13 */
+  int64_t num_antipodal;        /* survivors of mode 1 / 2 */
+  int64_t num_selected;
+  int64_t sum_neighbors_hands;  /* sum over samples of K */
+  int64_t sum_cropped;          /* sum over samples of k' */
+  int64_t sum_in_box;           /* sum over hypotheses of m */
+  int64_t sum_neighbors_normals;/* sum over points of k_n */
+  int64_t gpu_launches;         /* kernels launched since the last ag2_set_cloud */
+  double ms_phase[8];           /* grid, normals, frames, hands, prune, render, lenet, select */
+} ag2_stats;
+
+typedef struct ag2_ctx ag2_ctx;
+
+/* ---- lifecycle ---------------------------------------------------------- */
+
+/* Fills the reference's compiled-in defaults (grasp_detector.cpp:17-80, the
+ * Baxter camera poses of :111-127, workspace of launch/file_detect_grasps.launch:16). */
+int ag2_default_params(ag2_params* p);
+
+/* Replaces: GraspDetector ctor + HandSearch::setParameters (grasp_detector.cpp:15-81,
+ * hand_search.cpp:64-80).  device = CUDA ordinal. */
+int ag2_create(const ag2_params* p, int device, ag2_ctx** out);
+int ag2_destroy(ag2_ctx* ctx);
+/* HandSearch::setParameters / setCamTfLeft / setCamTfRight (hand_search.h:121-133). */
+int ag2_set_params(ag2_ctx* ctx, const ag2_params* p);
+const char* ag2_strerror(int code);
+const char* ag2_last_error(const ag2_ctx* ctx);
+int ag2_abi_version(void);
+
+/* ---- classifier weights ------------------------------------------------- */
+
+/* Replaces Classifier ctor's net_->CopyTrainedLayersFrom (caffe_classifier.cpp:13-14):
+ * parses the caffemodel protobuf wire format (V1 "layers" and V2 "layer"). */
+int ag2_load_lenet_caffemodel(ag2_ctx* ctx, const char* path);
+/* Caffe blob layouts: conv [out,in,kh,kw], ip [out,in]; fp32. */
+int ag2_set_lenet_weights(ag2_ctx* ctx, const float* conv1_w, const float* conv1_b,
+                          const float* conv2_w, const float* conv2_b, const float* ip1_w,
+                          const float* ip1_b, const float* ip2_w, const float* ip2_b);
+/* Xavier fillers named in caffe/sigmoid_lenet.prototxt:17-19,41-43,64-66,82-84
+ * (the trained blob is absent from the reference checkout). */
+int ag2_init_lenet_xavier(ag2_ctx* ctx, uint64_t seed);
+int ag2_get_lenet_weights(ag2_ctx* ctx, float* conv1_w, float* conv1_b, float* conv2_w,
+                          float* conv2_b, float* ip1_w, float* ip1_b, float* ip2_w,
+                          float* ip2_b);
+
+/* ---- inputs (the CloudCamera contract, cloud_camera.h:102-139) ----------- */
+
+/* Processed cloud.  xyz: n points, stride_bytes apart (12 for packed floats, 32
+ * for pcl::PointXYZRGBA).  cam_mask[i] bit c = point i seen by camera c
+ * (camera_source_, cloud_camera.cpp:39-50); num_cams = rows of camera_source_.
+ * normals_or_null: optional precomputed normals, 3 floats per point
+ * (CloudCamera::getNormals, hand_search.cpp:20-29). Host pointers. */
+int ag2_set_cloud(ag2_ctx* ctx, const float* xyz, size_t stride_bytes, size_t n,
+                  const uint8_t* cam_mask, int num_cams, const float* normals_or_null);
+/* Same with DEVICE pointers (packed xyz; used after an NCCL broadcast). */
+int ag2_set_cloud_device(ag2_ctx* ctx, const float* d_xyz, size_t n, const uint8_t* d_cam_mask,
+                         int num_cams, const float* d_normals_or_null);
+/* CloudCamera::setSampleIndices (cloud_camera.h:131) -> calculateLocalFrames(indices),
+ * hand_search.cpp:97-170. */
+int ag2_set_sample_indices(ag2_ctx* ctx, const int32_t* idx, size_t n);
+/* CloudCamera::setSamples (cloud_camera.cpp:254-257) -> calculateLocalFrames(samples),
+ * hand_search.cpp:238-317.  xyz: 3 doubles per sample. */
+int ag2_set_sample_points(ag2_ctx* ctx, const double* xyz, size_t n);
+/* Offset added to the sample position when deriving the rand() replacement
+ * stream, so that a shard of a larger sample list draws like the whole list. */
+int ag2_set_sample_id_offset(ag2_ctx* ctx, int64_t first_sample_id);
+
+/* ---- stages -------------------------------------------------------------- */
+
+/* KdTreeFLANN::setInputCloud + calculateNormalsOMP (hand_search.cpp:11-30,83-94). */
+int ag2_compute_normals(ag2_ctx* ctx);
+/* HandSearch::generateHypotheses (hand_search.cpp:4-61): frames + evaluateHands. */
+int ag2_generate_hypotheses(ag2_ctx* ctx);
+/* GraspDetector::pruneGraspsOnHandParameters (grasp_detector.cpp:363-395). */
+int ag2_prune(ag2_ctx* ctx);
+/* Learning::createGraspImages (learning.cpp:4-33) on the pruned list.
+ * out_or_null: host buffer of num_pruned * AG2_IMAGE_BYTES (HWC u8, the cv::Mat layout). */
+int ag2_render_images(ag2_ctx* ctx, uint8_t* out_or_null);
+/* Classifier::ClassifyBatch + thresholding (grasp_detector.cpp:186-209). */
+int ag2_classify(ag2_ctx* ctx);
+/* mode 2: keep isFullAntipodal (grasp_detector.cpp:212-221); mode 0: keep all. */
+int ag2_select(ag2_ctx* ctx);
+/* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) without clustering. */
+int ag2_detect(ag2_ctx* ctx);
+int ag2_synchronize(ag2_ctx* ctx);
+
+/* ---- outputs ------------------------------------------------------------- */
+
+enum { AG2_LIST_HYPOTHESES = 0, AG2_LIST_PRUNED = 1, AG2_LIST_ANTIPODAL = 2, AG2_LIST_SELECTED = 3 };
+int ag2_num_hypotheses(ag2_ctx* ctx, int which, size_t* n);
+int ag2_get_hypotheses(ag2_ctx* ctx, int which, ag2_hypothesis* out, size_t cap, size_t* n);
+/* Device pointer of a list (records are contiguous); valid until the next stage call. */
+int ag2_get_hypotheses_device(ag2_ctx* ctx, int which, const ag2_hypothesis** d_ptr, size_t* n);
+int ag2_get_stats(ag2_ctx* ctx, ag2_stats* out);
+
+/* ---- introspection used by the parity tests ------------------------------ */
+int ag2_get_normals(ag2_ctx* ctx, float* out /* 3*n, input point order */);
+int ag2_get_frames(ag2_ctx* ctx, ag2_frame* out, size_t cap);
+int ag2_get_sweep_records(ag2_ctx* ctx, ag2_sweep_record* out, size_t cap /* samples*R */);
+/* Fixed-radius query (KdTreeFLANN::radiusSearch semantics): ids in
+ * input point order sorted by (d2, id).  Host pointers. */
+int ag2_radius_search(ag2_ctx* ctx, const float* q /*3*/, double radius, int32_t* idx, float* d2,
+                      size_t cap, size_t* n);
+/* In-box point ids (input order, reference list order) of hypothesis h of list `which`. */
+int ag2_get_in_box(ag2_ctx* ctx, int which, size_t h, int32_t* idx, size_t cap, size_t* n);
+/* ip2 logits of the pruned list after ag2_classify: 2 floats per image. */
+int ag2_get_logits(ag2_ctx* ctx, float* out, size_t cap_images);
+/* Classifier::ClassifyBatch on caller images (HWC u8, 60x60x3): 2 floats per image. */
+int ag2_classify_images(ag2_ctx* ctx, const uint8_t* images, size_t n, float* logits_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AG2_H_ */
