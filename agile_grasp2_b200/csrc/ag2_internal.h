@@ -1,0 +1,219 @@
+// Internal declarations shared by the translation units of libag2.so.
+// Product code: CUDA (sm_100a) only, no CPU fallback, nothing from oracle/.
+#ifndef AG2_INTERNAL_H_
+#define AG2_INTERNAL_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ag2.h"
+
+namespace ag2 {
+
+// ---------------------------------------------------------------- device buffers
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t cap = 0;  // elements
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  // Grows (never shrinks); contents are NOT preserved.
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    release();
+    size_t want = n + n / 8 + 64;
+    cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+    if (e != cudaSuccess) {
+      p = nullptr;
+      return e;
+    }
+    cap = want;
+    return cudaSuccess;
+  }
+};
+
+// ---------------------------------------------------------------- uniform grid (K1-K3)
+// Cell index (cx + nx*(cy + ny*cz)): x runs are contiguous in the sorted arrays,
+// so a fixed-radius query is a loop over (y,z) rows, each ONE contiguous span.
+struct GridDev {
+  float ox, oy, oz;   // origin (bbox min of the finite points)
+  float inv_h;        // 1 / cell size
+  int nx, ny, nz;
+  int n;              // finite points (sorted arrays hold exactly these)
+  const uint32_t* cell_start;  // [ncells + 1]
+  const float4* pts;           // sorted: x, y, z, w = bits of the input-order index
+  const float4* nrm;           // sorted: nx, ny, nz, w = bits of the camera mask
+};
+
+// Host-built constant tables; values are produced on the host EXACTLY as the
+// reference produces them (finger_hand.cpp:7-13,122; hand_search.cpp:179-180,357)
+// and never recomputed with device intrinsics.
+struct HandConst {
+  double fs_lo[20];   // finger_spacing_(i)
+  double fs_hi[20];   // finger_spacing_(i) + finger_width_
+  double depth[AG2_MAX_DEEPEN_STEPS + 2];   // t_0 = init_bite, t_j deepen depths
+  double bottom[AG2_MAX_DEEPEN_STEPS + 2];  // t_j - hand_depth
+  double cos_a[AG2_MAX_ORIENTATIONS];
+  double sin_a[AG2_MAX_ORIENTATIONS];
+  double finger_width, hand_depth, hand_height, neg_hand_height;
+  double cos_friction;        // cos(30 deg), antipodal.cpp:11,23
+  double cam_origin[2][3];    // translation columns of cam_tf_left/right
+  double x_est_lo, x_est_inv_step;  // slot-index estimator (left half); exact fix-up follows
+  int num_depths;             // D + 1 entries in depth[]
+  int num_orientations;
+  float r2_hands;             // (float)(r*r)
+  float rq_hands;             // query half-width with slack
+  float r2_taubin, rq_taubin;
+  float r2_normals, rq_normals;
+  uint64_t rng_seed;
+};
+
+// Per (sample, orientation) auxiliary output of the hand kernel.
+struct BoxRef {
+  uint32_t offset;  // into the in-box pool
+  uint32_t count;
+};
+
+struct LeNetDev {
+  bool loaded = false;
+  DevBuf<float> c1w, c1b, c2w, c2b, i1w, i1b, i2w, i2b;
+  // derived layouts for the tensor-core path are owned by lenet.cu
+  DevBuf<uint8_t> aux;
+  std::vector<float> host[8];
+};
+
+}  // namespace ag2
+
+struct ag2_ctx {
+  ag2_params p;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int sm_count = 148;
+  int64_t launches = 0;
+
+  // input-order cloud
+  size_t n = 0;
+  int num_cams = 1;
+  ag2::DevBuf<float> xyz_in;       // 3n packed
+  ag2::DevBuf<uint8_t> cam_in;     // n
+  ag2::DevBuf<float> normals_in;   // 3n when precomputed normals were given
+  bool normals_given = false;
+  bool have_normals = false;       // sorted normals complete for all points
+  float min_z = 0.f;               // pcl::getMinMax3D z (grasp_detector.cpp:153)
+
+  // grid
+  bool grid_built = false;
+  float origin[3] = {0, 0, 0};
+  float h = 0.01f, inv_h = 100.f;
+  int dim[3] = {1, 1, 1};
+  size_t ncells = 0;
+  size_t n_finite = 0;
+  ag2::DevBuf<uint32_t> cell_of;        // n (input order) cell id or 0xFFFFFFFF
+  ag2::DevBuf<uint32_t> cell_start;     // ncells + 1
+  ag2::DevBuf<uint32_t> cell_fill;      // ncells
+  ag2::DevBuf<uint32_t> tmp_idx;        // n
+  ag2::DevBuf<float4> pts;              // sorted
+  ag2::DevBuf<float4> nrm;              // sorted
+  ag2::DevBuf<uint32_t> sorted_of_orig; // n
+  ag2::DevBuf<uint32_t> scan_tmp;
+  ag2::DevBuf<uint32_t> kn;             // neighbour counts (normals pass)
+  ag2::DevBuf<uint32_t> scalars;        // small device scratch (counters, maxima, flags)
+
+  // samples
+  bool use_points = false;
+  size_t num_samples = 0;
+  int64_t sample_id_offset = 0;
+  ag2::DevBuf<int32_t> sample_idx;
+  ag2::DevBuf<double> sample_xyz;
+  std::vector<int32_t> h_sample_idx;
+  std::vector<double> h_sample_xyz;
+
+  // hot-path outputs
+  ag2::DevBuf<ag2_frame> frames;            // S
+  ag2::DevBuf<uint32_t> kt;                 // S neighbour counts at nn_radius_taubin
+  ag2::DevBuf<ag2_sweep_record> sweeps;     // S*R
+  ag2::DevBuf<ag2_hypothesis> slots;        // S*R
+  ag2::DevBuf<ag2::BoxRef> box_ref;         // S*R
+  ag2::DevBuf<int32_t> box_pool;            // in-box sorted positions
+  ag2::DevBuf<uint32_t> flags;              // 2 * S*R (emitted / pruned)
+  ag2::DevBuf<uint32_t> flag_scan;          // 2 * S*R
+  ag2::DevBuf<uint32_t> list[4];            // slot ids of each AG2_LIST_*
+  size_t list_n[4] = {0, 0, 0, 0};
+  ag2::DevBuf<ag2_hypothesis> list_rec[4];  // contiguous records per list
+  bool list_rec_valid[4] = {false, false, false, false};
+  ag2::DevBuf<uint8_t> images;              // pruned * 10800 (HWC u8)
+  ag2::DevBuf<float> logits;                // pruned * 2
+  ag2::DevBuf<double> scores;               // pruned
+  ag2::DevBuf<float> act;                   // LeNet activations
+  uint32_t max_in_box = 0;
+  bool have_hyps = false, have_pruned = false, have_images = false, have_antipodal = false,
+       have_selected = false;
+
+  ag2::LeNetDev net;
+  ag2::HandConst hc;
+  ag2_stats st;
+  cudaEvent_t ev[18];
+  bool ev_used[18];
+};
+
+namespace ag2 {
+
+// error plumbing -------------------------------------------------------------
+int fail(ag2_ctx* c, int code, const char* what, cudaError_t e, const char* file, int line);
+#define AG2_CUDA(c, expr)                                                          \
+  do {                                                                             \
+    cudaError_t _e = (expr);                                                       \
+    if (_e != cudaSuccess) return ::ag2::fail((c), AG2_E_CUDA, #expr, _e, __FILE__, __LINE__); \
+  } while (0)
+#define AG2_TRY(expr)      \
+  do {                     \
+    int _rc = (expr);      \
+    if (_rc != AG2_OK) return _rc; \
+  } while (0)
+#define AG2_LAUNCH_CHECK(c)                                                        \
+  do {                                                                             \
+    (c)->launches++;                                                               \
+    cudaError_t _e = cudaGetLastError();                                           \
+    if (_e != cudaSuccess) return ::ag2::fail((c), AG2_E_CUDA, "kernel launch", _e, __FILE__, __LINE__); \
+  } while (0)
+
+// stage entry points (each .cu implements its own) ----------------------------
+int build_hand_const(ag2_ctx* c);                   // tables.cpp
+int grid_build(ag2_ctx* c);                         // grid.cu
+GridDev grid_dev(const ag2_ctx* c);
+int exclusive_scan_u32(ag2_ctx* c, uint32_t* data, size_t n);  // in place, total at data[n]
+int normals_compute(ag2_ctx* c);                    // normals.cu
+int frames_compute(ag2_ctx* c);                     // frames.cu
+int hands_compute(ag2_ctx* c);                      // hands.cu
+int lists_build_after_hands(ag2_ctx* c);            // select.cu
+int prune_compute(ag2_ctx* c);
+int select_mode(ag2_ctx* c);
+int select_top(ag2_ctx* c);
+int gather_list_records(ag2_ctx* c, int which);
+int render_compute(ag2_ctx* c);                     // render.cu
+int lenet_upload(ag2_ctx* c);                       // lenet.cu
+int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits);
+int classify_compute(ag2_ctx* c);
+int radius_search_device(ag2_ctx* c, const float* q, double radius, std::vector<int32_t>& idx,
+                         std::vector<float>& d2);   // grid.cu
+int load_caffemodel(const char* path, std::vector<float> out[8], std::string& err);  // caffemodel.cpp
+void xavier_fill(uint64_t seed, std::vector<float> out[8]);
+
+void phase_begin(ag2_ctx* c, int phase);
+void phase_end(ag2_ctx* c, int phase);
+int collect_phase_times(ag2_ctx* c);
+
+}  // namespace ag2
+
+#endif

@@ -1,0 +1,361 @@
+// C ABI (include/ag2.h), part 1: lifecycle, parameters, weights, inputs.
+#include <math.h>
+#include <string.h>
+
+#include <new>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+
+int fail(ag2_ctx* c, int code, const char* what, cudaError_t e, const char* file, int line) {
+  if (c) {
+    char buf[512];
+    snprintf(buf, sizeof(buf), "%s: %s (%s:%d)", what, cudaGetErrorString(e), file, line);
+    c->err = buf;
+  }
+  return code;
+}
+
+void phase_begin(ag2_ctx* c, int phase) {
+  cudaEventRecord(c->ev[2 * phase], c->stream);
+  c->ev_used[2 * phase] = true;
+}
+void phase_end(ag2_ctx* c, int phase) {
+  cudaEventRecord(c->ev[2 * phase + 1], c->stream);
+  c->ev_used[2 * phase + 1] = true;
+}
+int collect_phase_times(ag2_ctx* c) {
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (int ph = 0; ph < 8; ph++) {
+    if (c->ev_used[2 * ph] && c->ev_used[2 * ph + 1]) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, c->ev[2 * ph], c->ev[2 * ph + 1]) == cudaSuccess) c->st.ms_phase[ph] = ms;
+    }
+  }
+  return AG2_OK;
+}
+
+static bool params_ok(const ag2_params* p) {
+  return p && p->num_orientations >= 1 && p->num_orientations <= AG2_MAX_ORIENTATIONS &&
+         p->nn_radius_hands > 0 && p->nn_radius_taubin > 0 && p->normals_radius > 0 && p->finger_width > 0 &&
+         p->hand_outer_diameter > p->finger_width && p->hand_depth > 0 && p->hand_height > 0 &&
+         isfinite(p->init_bite);
+}
+
+static void invalidate_results(ag2_ctx* c) {
+  c->have_hyps = c->have_pruned = c->have_images = c->have_antipodal = c->have_selected = false;
+  for (int i = 0; i < 4; i++) {
+    c->list_n[i] = 0;
+    c->list_rec_valid[i] = false;
+  }
+}
+
+static void mat4_mul(const double* a, const double* b, double* o) {
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) {
+      double s = 0;
+      for (int k = 0; k < 4; k++) s += a[4 * i + k] * b[4 * k + j];
+      o[4 * i + j] = s;
+    }
+}
+// general 4x4 inverse (Gauss-Jordan, partial pivoting)
+static void mat4_inv(const double* m, double* o) {
+  double a[4][8];
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) {
+      a[i][j] = m[4 * i + j];
+      a[i][4 + j] = i == j ? 1.0 : 0.0;
+    }
+  for (int col = 0; col < 4; col++) {
+    int piv = col;
+    for (int r = col + 1; r < 4; r++)
+      if (fabs(a[r][col]) > fabs(a[piv][col])) piv = r;
+    for (int j = 0; j < 8; j++) {
+      double t = a[col][j];
+      a[col][j] = a[piv][j];
+      a[piv][j] = t;
+    }
+    double d = a[col][col];
+    for (int j = 0; j < 8; j++) a[col][j] /= d;
+    for (int r = 0; r < 4; r++) {
+      if (r == col) continue;
+      double f = a[r][col];
+      for (int j = 0; j < 8; j++) a[r][j] -= f * a[col][j];
+    }
+  }
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) o[4 * i + j] = a[i][4 + j];
+}
+
+}  // namespace ag2
+
+using namespace ag2;
+
+extern "C" {
+
+int ag2_abi_version(void) { return AG2_ABI_VERSION; }
+
+const char* ag2_strerror(int code) {
+  switch (code) {
+    case AG2_OK: return "ok";
+    case AG2_E_INVALID: return "invalid argument";
+    case AG2_E_NO_DEVICE: return "no usable CUDA device (libag2 has no CPU fallback)";
+    case AG2_E_CUDA: return "CUDA error";
+    case AG2_E_EMPTY_CLOUD: return "empty point cloud";
+    case AG2_E_NO_SAMPLES: return "no samples set";
+    case AG2_E_NO_WEIGHTS: return "classifier weights not loaded";
+    case AG2_E_STATE: return "stage called out of order";
+    case AG2_E_IO: return "i/o or parse error";
+    case AG2_E_CAPACITY: return "capacity exceeded";
+    case AG2_E_NOMEM: return "out of memory";
+  }
+  return "unknown error";
+}
+
+const char* ag2_last_error(const ag2_ctx* c) { return c ? c->err.c_str() : ""; }
+
+int ag2_default_params(ag2_params* p) {
+  if (!p) return AG2_E_INVALID;
+  memset(p, 0, sizeof(*p));
+  // grasp_detector.cpp:17-80
+  p->nn_radius_taubin = 0.01;
+  p->nn_radius_hands = 0.1;
+  p->num_orientations = 8;
+  p->num_threads = 1;
+  p->num_samples = 1000;
+  p->finger_width = 0.01;
+  p->hand_outer_diameter = 0.09;
+  p->hand_depth = 0.06;
+  p->hand_height = 0.02;
+  p->init_bite = 0.015;
+  // grasp_detector.cpp:111-127: cam_tf_left = base_tf * sqrt_tf^-1, cam_tf_right = base_tf * sqrt_tf
+  const double base_tf[16] = {0, 0.445417, 0.895323, 0.215, 1, 0, 0, -0.015, 0, 0.895323, -0.445417, 0.23, 0, 0, 0, 1};
+  const double sqrt_tf[16] = {0.9366, -0.0162, 0.3500, -0.2863, 0.0151, 0.9999, 0.0058, 0.0058,
+                              -0.3501, -0.0002, 0.9367, 0.0554, 0, 0, 0, 1};
+  double inv[16];
+  mat4_inv(sqrt_tf, inv);
+  mat4_mul(base_tf, inv, p->cam_tf_left);
+  mat4_mul(base_tf, sqrt_tf, p->cam_tf_right);
+  // launch/file_detect_grasps.launch:16
+  const double ws[6] = {0.48, 0.92, -0.6, 0.4, -0.25, 1.0};
+  memcpy(p->workspace, ws, sizeof(ws));
+  p->antipodal_mode = AG2_MODE_PREDICTION;
+  p->filter_half_grasps = 1;
+  p->prune = 1;
+  p->num_selected = 50;
+  p->min_score_diff = 500.0;
+  p->min_aperture = 0.03;
+  p->max_aperture = 0.07;
+  p->normals_radius = 0.01;
+  p->rng_seed = 0;
+  return AG2_OK;
+}
+
+int ag2_create(const ag2_params* p, int device, ag2_ctx** out) {
+  if (!out || !params_ok(p)) return AG2_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    return AG2_E_NO_DEVICE;
+  }
+  if (cudaSetDevice(device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  ag2_ctx* c = new (std::nothrow) ag2_ctx();
+  if (!c) return AG2_E_NOMEM;
+  c->p = *p;
+  c->device = device;
+  memset(&c->st, 0, sizeof(c->st));
+  for (int i = 0; i < 18; i++) c->ev_used[i] = false;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete c;
+    return AG2_E_CUDA;
+  }
+  for (int i = 0; i < 18; i++) cudaEventCreate(&c->ev[i]);
+  if (c->scalars.reserve(64) != cudaSuccess || build_hand_const(c) != AG2_OK) {
+    ag2_destroy(c);
+    return AG2_E_INVALID;
+  }
+  *out = c;
+  return AG2_OK;
+}
+
+int ag2_destroy(ag2_ctx* c) {
+  if (!c) return AG2_OK;
+  cudaSetDevice(c->device);
+  if (c->stream) {
+    cudaStreamSynchronize(c->stream);
+    cudaStreamDestroy(c->stream);
+  }
+  for (int i = 0; i < 18; i++) cudaEventDestroy(c->ev[i]);
+  delete c;
+  return AG2_OK;
+}
+
+int ag2_set_params(ag2_ctx* c, const ag2_params* p) {
+  if (!c || !params_ok(p)) return AG2_E_INVALID;
+  bool regrid = p->normals_radius != c->p.normals_radius || p->nn_radius_hands != c->p.nn_radius_hands;
+  c->p = *p;
+  AG2_TRY(build_hand_const(c));
+  if (regrid) {
+    c->grid_built = false;
+    c->have_normals = false;
+  }
+  invalidate_results(c);
+  return AG2_OK;
+}
+
+int ag2_synchronize(ag2_ctx* c) {
+  if (!c) return AG2_E_INVALID;
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}
+
+// ---- weights
+
+int ag2_set_lenet_weights(ag2_ctx* c, const float* c1w, const float* c1b, const float* c2w, const float* c2b,
+                          const float* i1w, const float* i1b, const float* i2w, const float* i2b) {
+  if (!c || !c1w || !c1b || !c2w || !c2b || !i1w || !i1b || !i2w || !i2b) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  const float* src[8] = {c1w, c1b, c2w, c2b, i1w, i1b, i2w, i2b};
+  static const size_t sizes[8] = {20 * 75, 20, 50 * 500, 50, 500 * 7200, 500, 2 * 500, 2};
+  for (int i = 0; i < 8; i++) c->net.host[i].assign(src[i], src[i] + sizes[i]);
+  return lenet_upload(c);
+}
+
+int ag2_init_lenet_xavier(ag2_ctx* c, uint64_t seed) {
+  if (!c) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  xavier_fill(seed, c->net.host);
+  return lenet_upload(c);
+}
+
+int ag2_load_lenet_caffemodel(ag2_ctx* c, const char* path) {
+  if (!c || !path) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  std::vector<float> w[8];
+  int rc = load_caffemodel(path, w, c->err);
+  if (rc) return rc;
+  for (int i = 0; i < 8; i++) c->net.host[i].swap(w[i]);
+  return lenet_upload(c);
+}
+
+int ag2_get_lenet_weights(ag2_ctx* c, float* c1w, float* c1b, float* c2w, float* c2b, float* i1w, float* i1b,
+                          float* i2w, float* i2b) {
+  if (!c) return AG2_E_INVALID;
+  if (!c->net.loaded) return AG2_E_NO_WEIGHTS;
+  float* dst[8] = {c1w, c1b, c2w, c2b, i1w, i1b, i2w, i2b};
+  for (int i = 0; i < 8; i++)
+    if (dst[i]) memcpy(dst[i], c->net.host[i].data(), c->net.host[i].size() * sizeof(float));
+  return AG2_OK;
+}
+
+// ---- inputs
+
+static int cloud_reset(ag2_ctx* c, size_t n, int num_cams) {
+  c->n = n;
+  c->num_cams = num_cams;
+  c->grid_built = false;
+  c->have_normals = false;
+  invalidate_results(c);
+  int64_t launches_keep = 0;
+  memset(&c->st, 0, sizeof(c->st));
+  c->launches = launches_keep;
+  c->st.num_points = (int64_t)n;
+  c->st.num_samples = (int64_t)c->num_samples;
+  for (int i = 0; i < 18; i++) c->ev_used[i] = false;
+  return AG2_OK;
+}
+
+int ag2_set_cloud(ag2_ctx* c, const float* xyz, size_t stride_bytes, size_t n, const uint8_t* cam_mask, int num_cams,
+                  const float* normals) {
+  if (!c || (n && !xyz) || stride_bytes < 12 || stride_bytes % 4 || num_cams < 1 || num_cams > 8)
+    return AG2_E_INVALID;
+  if (n >= 0x7fffffffu) return AG2_E_CAPACITY;
+  cudaSetDevice(c->device);
+  cloud_reset(c, n, num_cams);
+  if (n == 0) return AG2_OK;
+  AG2_CUDA(c, c->xyz_in.reserve(3 * n));
+  AG2_CUDA(c, c->cam_in.reserve(n));
+  if (stride_bytes == 12) {
+    AG2_CUDA(c, cudaMemcpyAsync(c->xyz_in.p, xyz, 12 * n, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    AG2_CUDA(c, cudaMemcpy2DAsync(c->xyz_in.p, 12, xyz, stride_bytes, 12, n, cudaMemcpyHostToDevice, c->stream));
+  }
+  if (cam_mask) {
+    AG2_CUDA(c, cudaMemcpyAsync(c->cam_in.p, cam_mask, n, cudaMemcpyHostToDevice, c->stream));
+  } else {
+    AG2_CUDA(c, cudaMemsetAsync(c->cam_in.p, 1, n, c->stream));
+  }
+  c->normals_given = normals != nullptr;
+  if (normals) {
+    AG2_CUDA(c, c->normals_in.reserve(3 * n));
+    AG2_CUDA(c, cudaMemcpyAsync(c->normals_in.p, normals, 12 * n, cudaMemcpyHostToDevice, c->stream));
+  }
+  return AG2_OK;
+}
+
+int ag2_set_cloud_device(ag2_ctx* c, const float* d_xyz, size_t n, const uint8_t* d_cam, int num_cams,
+                         const float* d_normals) {
+  if (!c || (n && !d_xyz) || num_cams < 1 || num_cams > 8) return AG2_E_INVALID;
+  if (n >= 0x7fffffffu) return AG2_E_CAPACITY;
+  cudaSetDevice(c->device);
+  cloud_reset(c, n, num_cams);
+  if (n == 0) return AG2_OK;
+  AG2_CUDA(c, c->xyz_in.reserve(3 * n));
+  AG2_CUDA(c, c->cam_in.reserve(n));
+  AG2_CUDA(c, cudaMemcpyAsync(c->xyz_in.p, d_xyz, 12 * n, cudaMemcpyDeviceToDevice, c->stream));
+  if (d_cam) {
+    AG2_CUDA(c, cudaMemcpyAsync(c->cam_in.p, d_cam, n, cudaMemcpyDeviceToDevice, c->stream));
+  } else {
+    AG2_CUDA(c, cudaMemsetAsync(c->cam_in.p, 1, n, c->stream));
+  }
+  c->normals_given = d_normals != nullptr;
+  if (d_normals) {
+    AG2_CUDA(c, c->normals_in.reserve(3 * n));
+    AG2_CUDA(c, cudaMemcpyAsync(c->normals_in.p, d_normals, 12 * n, cudaMemcpyDeviceToDevice, c->stream));
+  }
+  return AG2_OK;
+}
+
+int ag2_set_sample_indices(ag2_ctx* c, const int32_t* idx, size_t n) {
+  if (!c || (n && !idx)) return AG2_E_INVALID;
+  for (size_t i = 0; i < n; i++)
+    if (idx[i] < 0 || (size_t)idx[i] >= c->n) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  c->h_sample_idx.assign(idx, idx + n);
+  c->use_points = false;
+  c->num_samples = n;
+  c->st.num_samples = (int64_t)n;
+  invalidate_results(c);
+  if (n) {
+    AG2_CUDA(c, c->sample_idx.reserve(n));
+    AG2_CUDA(c, cudaMemcpyAsync(c->sample_idx.p, c->h_sample_idx.data(), 4 * n, cudaMemcpyHostToDevice, c->stream));
+  }
+  return AG2_OK;
+}
+
+int ag2_set_sample_points(ag2_ctx* c, const double* xyz, size_t n) {
+  if (!c || (n && !xyz)) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  c->h_sample_xyz.assign(xyz, xyz + 3 * n);
+  c->use_points = true;
+  c->num_samples = n;
+  c->st.num_samples = (int64_t)n;
+  invalidate_results(c);
+  if (n) {
+    AG2_CUDA(c, c->sample_xyz.reserve(3 * n));
+    AG2_CUDA(c, cudaMemcpyAsync(c->sample_xyz.p, c->h_sample_xyz.data(), 24 * n, cudaMemcpyHostToDevice, c->stream));
+  }
+  return AG2_OK;
+}
+
+int ag2_set_sample_id_offset(ag2_ctx* c, int64_t first) {
+  if (!c) return AG2_E_INVALID;
+  c->sample_id_offset = first;
+  return AG2_OK;
+}
+
+}  // extern "C"

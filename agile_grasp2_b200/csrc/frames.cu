@@ -1,0 +1,295 @@
+// K5: local reference frames, replacing HandSearch::calculateLocalFrames
+// (reference hand_search.cpp:97-170 for index samples, :238-317 for xyz samples)
+// and LocalFrame::findAverageNormalAxis (local_frame.cpp:26-59).
+// One CTA per sample: gather the nn_radius_taubin neighbourhood, sort it by
+// (d2, id) (the reference draws `rand() % n` into the distance-sorted list), draw
+// min(50, n) normals with the counter-based replacement of rand(), majority
+// camera, M = N N^T, cyclic Jacobi (double), Gram^6 column argmax, frame axes.
+// All double arithmetic is IEEE and unfused (-fmad=false) in the oracle's order.
+#include <math.h>
+
+#include <algorithm>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+namespace {
+
+constexpr int kFrameThreads = 128;
+
+__device__ __forceinline__ void sample_query(const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
+                                             const double* __restrict__ sxyz, uint32_t s, float q[3]) {
+  if (sxyz) {
+    q[0] = (float)sxyz[3 * (size_t)s];
+    q[1] = (float)sxyz[3 * (size_t)s + 1];
+    q[2] = (float)sxyz[3 * (size_t)s + 2];
+  } else {
+    size_t i = (size_t)sidx[s];
+    q[0] = xyz_in[3 * i];
+    q[1] = xyz_in[3 * i + 1];
+    q[2] = xyz_in[3 * i + 2];
+  }
+}
+
+// warp per sample: neighbour count at the frame radius
+__global__ void k_count_sample_neighbors(GridDev g, const float* __restrict__ xyz_in,
+                                         const int32_t* __restrict__ sidx, const double* __restrict__ sxyz,
+                                         uint32_t S, float r2, float rq, uint32_t* __restrict__ kt,
+                                         uint32_t* __restrict__ max_out) {
+  uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int lane = threadIdx.x & 31;
+  if (s >= S) return;
+  float q[3];
+  sample_query(xyz_in, sidx, sxyz, s, q);
+  QueryWindow w = make_window(g, q[0], q[1], q[2], rq);
+  int rows = w.rows();
+  uint32_t cnt = 0;
+  for (int row = 0; row < rows; row++) {
+    uint32_t b, e;
+    row_span(g, w, row, b, e);
+    for (uint32_t j = b + lane; j < e; j += 32) {
+      float4 p = g.pts[j];
+      cnt += (dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z) < r2);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(AG2_FULL, cnt, o);
+  if (lane == 0) {
+    kt[s] = cnt;
+    atomicMax(max_out, cnt);
+  }
+}
+
+// cyclic Jacobi of a symmetric 3x3 — same sequence of operations as the oracle (D3)
+__device__ void jacobi3(double a[3][3], double d[3], double v[3][3]) {
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) v[i][j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 32; sweep++) {
+    double off = fabs(a[0][1]) + fabs(a[0][2]) + fabs(a[1][2]);
+    if (off == 0.0) break;
+    for (int p = 0; p < 2; p++)
+      for (int q = p + 1; q < 3; q++) {
+        double apq = a[p][q];
+        if (apq == 0.0) continue;
+        double g = 100.0 * fabs(apq);
+        if (sweep > 3 && fabs(a[p][p]) + g == fabs(a[p][p]) && fabs(a[q][q]) + g == fabs(a[q][q])) {
+          a[p][q] = a[q][p] = 0.0;
+          continue;
+        }
+        double h = a[q][q] - a[p][p];
+        double t;
+        if (fabs(h) + g == fabs(h)) {
+          t = apq / h;
+        } else {
+          double theta = 0.5 * h / apq;
+          t = 1.0 / (fabs(theta) + sqrt(1.0 + theta * theta));
+          if (theta < 0.0) t = -t;
+        }
+        double c = 1.0 / sqrt(1.0 + t * t);
+        double s = t * c;
+        double app = a[p][p], aqq = a[q][q];
+        a[p][p] = app - t * apq;
+        a[q][q] = aqq + t * apq;
+        a[p][q] = a[q][p] = 0.0;
+        int r = 3 - p - q;
+        double arp = a[r][p], arq = a[r][q];
+        a[r][p] = a[p][r] = c * arp - s * arq;
+        a[r][q] = a[q][r] = s * arp + c * arq;
+        for (int k = 0; k < 3; k++) {
+          double vkp = v[k][p], vkq = v[k][q];
+          v[k][p] = c * vkp - s * vkq;
+          v[k][q] = s * vkp + c * vkq;
+        }
+      }
+  }
+  for (int i = 0; i < 3; i++) d[i] = a[i][i];
+}
+
+__device__ __forceinline__ double dot3d(const double* a, const double* b) {
+  return a[0] * b[0] + (a[1] * b[1] + a[2] * b[2]);  // Eigen fixed-size reduction order
+}
+
+__global__ void __launch_bounds__(kFrameThreads)
+k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
+         const double* __restrict__ sxyz, uint32_t S, const uint32_t* __restrict__ kt, uint32_t cap,
+         float r2, float rq, int num_cams, uint64_t seed, int64_t id_offset, double cam0x, double cam0y,
+         double cam0z, double cam1x, double cam1y, double cam1z, ag2_frame* __restrict__ out) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* keys = (uint64_t*)smem;
+  uint32_t* vals = (uint32_t*)(keys + cap);
+  __shared__ double N[50][3];
+  __shared__ double colsum[50];
+  __shared__ double M[9];
+  __shared__ int num_source[8];
+  __shared__ uint32_t filled;
+  const uint32_t s = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kFrameThreads / 32;
+  float q[3];
+  sample_query(xyz_in, sidx, sxyz, s, q);
+  const uint32_t count = kt[s];
+  ag2_frame f;
+  if (tid == 0) {
+    f.sample[0] = (double)q[0], f.sample[1] = (double)q[1], f.sample[2] = (double)q[2];
+    for (int a = 0; a < 3; a++) f.normal[a] = f.binormal[a] = f.curvature_axis[a] = 0.0;
+    f.valid = 0, f.majority_cam = 0, f.num_neighbors = (int32_t)count, f.reserved = 0;
+  }
+  if (count == 0) {  // sample dropped (hand_search.cpp:122,157-163)
+    if (tid == 0) out[s] = f;
+    return;
+  }
+  if (tid == 0) filled = 0;
+  if (tid < 8) num_source[tid] = 0;
+  __syncthreads();
+  QueryWindow w = make_window(g, q[0], q[1], q[2], rq);
+  int rows = w.rows();
+  for (int row = warp; row < rows; row += nw) {
+    uint32_t b, e;
+    row_span(g, w, row, b, e);
+    for (uint32_t base = b; base < e; base += 32) {
+      uint32_t j = base + lane;
+      bool hit = false;
+      float d2 = 0.f;
+      uint32_t orig = 0;
+      if (j < e) {
+        float4 p = g.pts[j];
+        d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
+        hit = d2 < r2;
+        orig = __float_as_uint(p.w);
+      }
+      uint32_t ballot = __ballot_sync(AG2_FULL, hit);
+      uint32_t basepos = 0;
+      if (lane == 0 && ballot) basepos = atomicAdd(&filled, (uint32_t)__popc(ballot));
+      basepos = __shfl_sync(AG2_FULL, basepos, 0);
+      if (hit) {
+        uint32_t slot = basepos + __popc(ballot & ((1u << lane) - 1));
+        keys[slot] = nn_key(d2, orig);
+        vals[slot] = j;
+      }
+    }
+  }
+  __syncthreads();
+  const uint32_t n_pad = next_pow2(count);
+  for (uint32_t t = count + tid; t < n_pad; t += kFrameThreads) {
+    keys[t] = ~0ull;
+    vals[t] = 0;
+  }
+  __syncthreads();
+  bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kFrameThreads, BlockSync());
+  const int n = (int)min(50u, count);
+  if (tid < n) {
+    uint32_t r = draw_index(seed, id_offset + (int64_t)s, tid, count);
+    uint32_t pos = vals[r];
+    float4 nv = g.nrm[pos];
+    double nx = (double)nv.x, ny = (double)nv.y, nz = (double)nv.z;
+    uint32_t mask = __float_as_uint(nv.w);
+    for (int cam = 0; cam < num_cams; cam++)
+      if ((mask >> cam) & 1u) atomicAdd(&num_source[cam], 1);
+    double mag = sqrt(nx * nx + (ny * ny + nz * nz));
+    N[tid][0] = nx / mag;
+    N[tid][1] = ny / mag;
+    N[tid][2] = nz / mag;
+  }
+  __syncthreads();
+  if (tid < 9) {  // M = sum_j n_j n_j^T, sequential in draw order
+    int a = tid / 3, b = tid % 3;
+    double acc = 0.0;
+    for (int j = 0; j < n; j++) acc += N[j][a] * N[j][b];
+    M[tid] = acc;
+  }
+  if (tid >= 32 && tid < 32 + n) {  // column sums of (N^T N)^.6 (local_frame.cpp:42)
+    int j = tid - 32;
+    double sacc = 0.0;
+    for (int i = 0; i < n; i++) {
+      double gij = (N[i][0] * N[j][0] + N[i][1] * N[j][1]) + N[i][2] * N[j][2];
+      double g2 = gij * gij;
+      sacc += (g2 * g2) * g2;
+    }
+    colsum[j] = sacc;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  int majority = 0;
+  for (int cam = 1; cam < num_cams; cam++)
+    if (num_source[cam] > num_source[majority]) majority = cam;
+  double A[3][3], d[3], v[3][3];
+  for (int a = 0; a < 3; a++)
+    for (int b = 0; b < 3; b++) A[a][b] = M[a * 3 + b];
+  jacobi3(A, d, v);
+  int min_index = 0;
+  for (int i = 1; i < 3; i++)
+    if (d[i] < d[min_index]) min_index = i;
+  double cax[3] = {v[0][min_index], v[1][min_index], v[2][min_index]};
+  int max_index = 0;
+  double best = -INFINITY;
+  for (int j = 0; j < n; j++)
+    if (colsum[j] > best) {
+      best = colsum[j];
+      max_index = j;
+    }
+  double nm[3] = {N[max_index][0], N[max_index][1], N[max_index][2]};
+  double np[3];
+  for (int a = 0; a < 3; a++) {
+    double P0 = (a == 0 ? 1.0 : 0.0) - cax[a] * cax[0];
+    double P1 = (a == 1 ? 1.0 : 0.0) - cax[a] * cax[1];
+    double P2 = (a == 2 ? 1.0 : 0.0) - cax[a] * cax[2];
+    np[a] = (P0 * nm[0] + P1 * nm[1]) + P2 * nm[2];
+  }
+  double len = sqrt(dot3d(np, np));
+  double nrm[3] = {np[0] / len, np[1] / len, np[2] / len};
+  double bin[3] = {cax[1] * nrm[2] - cax[2] * nrm[1], cax[2] * nrm[0] - cax[0] * nrm[2],
+                   cax[0] * nrm[1] - cax[1] * nrm[0]};
+  int mc = majority > 1 ? 1 : majority;
+  double co[3] = {mc ? cam1x : cam0x, mc ? cam1y : cam0y, mc ? cam1z : cam0z};
+  double s2s[3] = {f.sample[0] - co[0], f.sample[1] - co[1], f.sample[2] - co[2]};
+  if (dot3d(nrm, s2s) > 0)
+    for (int a = 0; a < 3; a++) nrm[a] = -nrm[a];
+  if (dot3d(bin, s2s) > 0)
+    for (int a = 0; a < 3; a++) bin[a] = -bin[a];
+  double ax[3] = {nrm[1] * bin[2] - nrm[2] * bin[1], nrm[2] * bin[0] - nrm[0] * bin[2],
+                  nrm[0] * bin[1] - nrm[1] * bin[0]};
+  for (int a = 0; a < 3; a++) {
+    f.normal[a] = nrm[a];
+    f.binormal[a] = bin[a];
+    f.curvature_axis[a] = ax[a];
+  }
+  f.valid = 1;
+  f.majority_cam = majority;
+  out[s] = f;
+}
+
+}  // namespace
+
+int frames_compute(ag2_ctx* c) {
+  phase_begin(c, 2);
+  cudaStream_t st = c->stream;
+  GridDev g = grid_dev(c);
+  const uint32_t S = (uint32_t)c->num_samples;
+  AG2_CUDA(c, c->frames.reserve(S));
+  AG2_CUDA(c, c->kt.reserve(S));
+  const int32_t* sidx = c->use_points ? nullptr : c->sample_idx.p;
+  const double* sxyz = c->use_points ? c->sample_xyz.p : nullptr;
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 12, 0, 4, st));
+  k_count_sample_neighbors<<<(S * 32 + 127) / 128, 128, 0, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->hc.r2_taubin,
+                                                                c->hc.rq_taubin, c->kt.p, c->scalars.p + 12);
+  AG2_LAUNCH_CHECK(c);
+  uint32_t max_kt = 0;
+  AG2_CUDA(c, cudaMemcpyAsync(&max_kt, c->scalars.p + 12, 4, cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaStreamSynchronize(st));
+  uint32_t cap = 64;
+  while (cap < max_kt) cap <<= 1;
+  size_t smem = (size_t)cap * 12;
+  if (smem > 200 * 1024) {
+    c->err = "frames: a sample has more than 16384 neighbours within nn_radius_taubin";
+    return AG2_E_CAPACITY;
+  }
+  AG2_CUDA(c, cudaFuncSetAttribute(k_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const HandConst& h = c->hc;
+  k_frames<<<S, kFrameThreads, smem, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->kt.p, cap, h.r2_taubin, h.rq_taubin,
+                                           c->num_cams, h.rng_seed, c->sample_id_offset, h.cam_origin[0][0],
+                                           h.cam_origin[0][1], h.cam_origin[0][2], h.cam_origin[1][0],
+                                           h.cam_origin[1][1], h.cam_origin[1][2], c->frames.p);
+  AG2_LAUNCH_CHECK(c);
+  phase_end(c, 2);
+  return AG2_OK;
+}
+
+}  // namespace ag2

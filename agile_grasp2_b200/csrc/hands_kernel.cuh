@@ -1,0 +1,516 @@
+// Included by hands.cu only: the kernel body and its host launcher.
+namespace ag2 {
+namespace {
+
+// Row spans of the query window, tightened to the chord of the sphere in each row.
+__device__ void setup_rows(Shared& sh, const GridDev& g, const float q[3], float r, float rq, int tid) {
+  QueryWindow w = make_window(g, q[0], q[1], q[2], rq);
+  int rows = w.rows();
+  int ny = w.y1 - w.y0 + 1;
+  float h = 1.0f / g.inv_h;
+  for (int row = tid; row < kMaxRows; row += kHandThreads) {
+    uint32_t cnt = 0, begin = 0;
+    if (row < rows) {
+      int cz = w.z0 + row / ny, cy = w.y0 + row % ny;
+      // distance from q to the cell slab in y and z (clamped edge cells are unbounded)
+      float ylo = g.oy + (float)cy * h, yhi = ylo + h;
+      float zlo = g.oz + (float)cz * h, zhi = zlo + h;
+      float dy = 0.f, dz = 0.f;
+      if (q[1] < ylo && cy > 0) dy = ylo - q[1];
+      if (q[1] > yhi && cy < g.ny - 1) dy = q[1] - yhi;
+      if (q[2] < zlo && cz > 0) dz = zlo - q[2];
+      if (q[2] > zhi && cz < g.nz - 1) dz = q[2] - zhi;
+      // conservative: shrink the slab distances, grow the radius
+      dy = fmaxf(0.f, dy * 0.999f - 1e-5f);
+      dz = fmaxf(0.f, dz * 0.999f - 1e-5f);
+      float rem = rq * rq - dy * dy - dz * dz;
+      if (rem > 0.f) {
+        float wx = sqrtf(rem) * 1.001f + 1e-5f;
+        int x0 = cell_coord(q[0] - wx, g.ox, g.inv_h, g.nx);
+        int x1 = cell_coord(q[0] + wx, g.ox, g.inv_h, g.nx);
+        uint32_t c0 = cell_id(g, x0, cy, cz);
+        begin = __ldg(&g.cell_start[c0]);
+        uint32_t end = __ldg(&g.cell_start[c0 + (uint32_t)(x1 - x0) + 1]);
+        cnt = end - begin;
+      }
+    }
+    sh.row_begin[row] = begin;
+    sh.row_prefix[row + 1] = cnt;
+  }
+  if (tid == 0) sh.row_prefix[0] = 0;
+  __syncthreads();
+  // inclusive scan of kMaxRows counts by warp 0 (32 lanes x 32 items)
+  if (tid < 32) {
+    constexpr int per = kMaxRows / 32;
+    uint32_t local = 0;
+    for (int k = 0; k < per; k++) local += sh.row_prefix[1 + tid * per + k];
+    uint32_t incl = local;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(AG2_FULL, incl, o);
+      if (tid >= o) incl += t;
+    }
+    uint32_t run = incl - local;
+    for (int k = 0; k < per; k++) {
+      run += sh.row_prefix[1 + tid * per + k];
+      sh.row_prefix[1 + tid * per + k] = run;
+    }
+    if (tid == 31) sh.total_cand = run;
+  }
+  __syncthreads();
+}
+
+// Stages the next chunk of cropped neighbours, starting at candidate sh.cursor.
+__device__ void fill_chunk(Shared& sh, float4* cache, const HandsArgs& A, const HandConst& hc,
+                           const float q[3], bool count_stats, int tid) {
+  const int lane = tid & 31;
+  if (tid == 0) sh.nkept = 0;
+  __syncthreads();
+  const uint32_t T = sh.total_cand;
+  uint32_t kcount = 0;
+  for (;;) {
+    uint32_t t0 = sh.cursor;
+    uint32_t kept_now = sh.nkept;
+    if (t0 >= T || kept_now + kHandThreads * kBatch > A.cap) break;
+    __syncthreads();  // everyone has read cursor / nkept
+#pragma unroll
+    for (int b = 0; b < kBatch; b++) {
+      uint32_t t = t0 + (uint32_t)b * kHandThreads + (uint32_t)tid;
+      bool keep = false;
+      float dx = 0.f, dy = 0.f, dz = 0.f;
+      uint32_t pos = 0;
+      if (t < T) {
+        // upper_bound over the row prefix: row with prefix[row] <= t < prefix[row+1]
+        int lo = 0, hi = kMaxRows;
+        while (hi - lo > 1) {
+          int mid = (lo + hi) >> 1;
+          if (sh.row_prefix[mid] <= t) lo = mid; else hi = mid;
+        }
+        pos = sh.row_begin[lo] + (t - sh.row_prefix[lo]);
+        float4 p = A.g.pts[pos];
+        // radiusSearch used q - p; hand_search.cpp:209 centres with p - q (exact negation)
+        dx = __fsub_rn(p.x, q[0]);
+        dy = __fsub_rn(p.y, q[1]);
+        dz = __fsub_rn(p.z, q[2]);
+        float d2 = dist2_f(dx, dy, dz);
+        if (d2 < hc.r2_hands) {
+          kcount++;
+          double zf = (sh.F[0][2] * (double)dx + sh.F[1][2] * (double)dy) + sh.F[2][2] * (double)dz;
+          keep = zf > hc.neg_hand_height && zf < hc.hand_height;  // hand_search.cpp:334
+        }
+      }
+      uint32_t ballot = __ballot_sync(AG2_FULL, keep);
+      uint32_t base = 0;
+      if (lane == 0 && ballot) base = atomicAdd(&sh.nkept, (uint32_t)__popc(ballot));
+      base = __shfl_sync(AG2_FULL, base, 0);
+      if (keep) cache[base + __popc(ballot & ((1u << lane) - 1))] = make_float4(dx, dy, dz, __uint_as_float(pos));
+    }
+    __syncthreads();
+    if (tid == 0) sh.cursor = min(T, t0 + (uint32_t)kBatch * kHandThreads);
+    __syncthreads();
+  }
+  if (count_stats) {
+    for (int o = 16; o > 0; o >>= 1) kcount += __shfl_xor_sync(AG2_FULL, kcount, o);
+    if (lane == 0 && kcount) atomicAdd(&sh.sumK, (unsigned long long)kcount);
+    if (tid == 0) sh.sumKc += sh.nkept;
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kHandThreads)
+k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
+  float4* cache = reinterpret_cast<float4*>(smem_raw + ((sizeof(Shared) + 15) & ~(size_t)15));
+  const int tid = threadIdx.x, lane = tid & 31;
+  const uint32_t s = blockIdx.x;
+  const int R = hc.num_orientations, ND = hc.num_depths;
+  const ag2_frame& fr = A.frames[s];
+  // default records
+  for (int r = tid; r < R; r += kHandThreads) {
+    ag2_sweep_record sw;
+    sw.fingers = 0, sw.hand = 0, sw.slot = -1, sw.depth_step = -1, sw.num_in_box = -1;
+    sw.antipodal = 0, sw.emitted = 0, sw.reserved = 0;
+    A.sweeps[(size_t)s * R + r] = sw;
+    A.box_ref[(size_t)s * R + r] = BoxRef{0u, 0u};
+  }
+  if (!fr.valid) return;
+  float q[3] = {(float)fr.sample[0], (float)fr.sample[1], (float)fr.sample[2]};
+  if (tid < 9) {
+    int a = tid / 3, b = tid % 3;
+    sh.F[a][b] = b == 0 ? fr.normal[a] : (b == 1 ? fr.binormal[a] : fr.curvature_axis[a]);
+  }
+  if (tid < 3) sh.sample[tid] = fr.sample[tid];
+  if (tid == 0) {
+    sh.cursor = 0;
+    sh.sumK = 0;
+    sh.sumKc = 0;
+    sh.pool_ok = 1;
+  }
+  for (int r = tid; r < R; r += kHandThreads) {
+    sh.minct[r] = ND;
+    sh.mincb[r] = ND;
+    sh.ymin[r] = d_ordered(INFINITY);
+    sh.m[r] = 0;
+    sh.minx[r] = d_ordered(INFINITY);
+    sh.maxx[r] = d_ordered(-INFINITY);
+    sh.fill[r] = 0;
+    sh.anyl[r] = sh.anyr[r] = 0;
+    for (int k = 0; k < 8; k++) sh.ap[r][k] = d_ordered((k & 1) ? INFINITY : -INFINITY);
+    for (int j = 0; j < ND; j++) sh.occ[r][j] = 0;
+    sh.os[r].feasible = 0;
+  }
+  __syncthreads();
+  // frame_rot = frame * rot (hand_search.cpp:357-358), columns 0 and 1; column 2 == frame column 2
+  for (int t = tid; t < R * 3; t += kHandThreads) {
+    int r = t / 3, a = t % 3;
+    double ca = hc.cos_a[r], sa = hc.sin_a[r];
+    double nsa = -1.0 * sa;
+    sh.FRx[r][a] = (sh.F[a][0] * ca + sh.F[a][1] * sa) + sh.F[a][2] * 0.0;
+    sh.FRy[r][a] = (sh.F[a][0] * nsa + sh.F[a][1] * ca) + sh.F[a][2] * 0.0;
+  }
+  setup_rows(sh, A.g, q, 0.f, hc.rq_hands, tid);
+  const uint32_t T = sh.total_cand;
+  const double inv_dstep = 200.0;  // 1/0.005: estimator only, exact fix-up follows
+  const double inv_sstep = hc.x_est_inv_step;
+
+  // ---------------- pass 1: slot occupancy per depth class, per orientation
+  bool single_chunk = true;
+  for (int chunk = 0;; chunk++) {
+    fill_chunk(sh, cache, A, hc, q, true, tid);
+    const uint32_t nk = sh.nkept;
+    if (chunk == 0 && sh.cursor < T) single_chunk = false;
+    for (int r = 0; r < R; r++) {
+      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
+      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
+      int mct = ND, mcb = ND;
+      double ymin = INFINITY;
+      for (uint32_t i = tid; i < nk; i += kHandThreads) {
+        float4 p = cache[i];
+        double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
+        double x = (ax0 * px + ax1 * py) + ax2 * pz;
+        double y = (ay0 * px + ay1 * py) + ay2 * pz;
+        ymin = fmin(ymin, y);
+        int ct = depth_class(y, hc.depth, ND, inv_dstep);
+        if (ct < ND) {
+          int cb = depth_class(y, hc.bottom, ND, inv_dstep);
+          mct = min(mct, ct);
+          mcb = min(mcb, cb);
+          uint32_t mask = slot_range(x, hc.fs_lo, hc.fs_hi, inv_sstep) |
+                          (slot_range(x, hc.fs_lo + 10, hc.fs_hi + 10, inv_sstep) << 10);
+          if (mask) atomicOr(&sh.occ[r][ct], mask);
+        }
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        mct = min(mct, __shfl_xor_sync(AG2_FULL, mct, o));
+        mcb = min(mcb, __shfl_xor_sync(AG2_FULL, mcb, o));
+      }
+      ymin = warp_min_d(ymin);
+      if (lane == 0) {
+        if (mct < ND) atomicMin(&sh.minct[r], mct);
+        if (mcb < ND) atomicMin(&sh.mincb[r], mcb);
+        atomicMin(&sh.ymin[r], d_ordered(ymin));
+      }
+    }
+    __syncthreads();
+    if (sh.cursor >= T) break;
+  }
+
+  // ---------------- finger logic: one thread per orientation
+  if (tid < R) {
+    const int r = tid;
+    OrientState& o = sh.os[r];
+    const int mct = sh.minct[r], mcb = sh.mincb[r];
+    uint32_t cum = sh.occ[r][0];
+    // evaluateFingers(points, init_bite): all false if a point is below the hand base
+    // or no point is below the bite (finger_hand.cpp:27-42)
+    uint32_t fingers = (mcb <= 0 || mct > 0) ? 0u : (~cum & 0xFFFFFu);
+    ag2_sweep_record sw;
+    sw.fingers = fingers, sw.hand = 0, sw.slot = -1, sw.depth_step = -1, sw.num_in_box = -1;
+    sw.antipodal = 0, sw.emitted = 0, sw.reserved = 0;
+    if (__popc(fingers) > 2) {  // hand_search.cpp:366
+      uint32_t hand = fingers & (fingers >> 10) & 0x3FFu;
+      sw.hand = (uint16_t)hand;
+      if (hand) {
+        int n = __popc(hand);
+        int k = (n + 1) / 2 - 1;  // ceil(n / 2.0) - 1, finger_hand.cpp:112
+        uint32_t hm = hand;
+        for (int i = 0; i < k; i++) hm &= hm - 1;
+        int e = __ffs(hm) - 1;
+        uint32_t pair = (1u << e) | (1u << (10 + e));
+        int last = 0;
+        for (int j = 1; j < ND; j++) {  // deepenHand loop, finger_hand.cpp:122-130
+          cum |= sh.occ[r][j];
+          uint32_t fj = (mcb <= j || mct > j) ? 0u : (~cum & pair);
+          if (__popc(fj) < 2) break;
+          last = j;
+        }
+        o.feasible = 1;
+        o.slot = e;
+        o.last = last;
+        o.top = hc.depth[last];
+        o.bottom = hc.bottom[last];
+        o.left = hc.fs_hi[e];          // finger_spacing_(idx) + finger_width_
+        o.right = hc.fs_lo[10 + e];
+        o.center = 0.5 * (o.left + o.right);
+        double baseline_const = 0.1;
+        o.lc = o.left - 0.5 * (baseline_const - (o.right - o.left));
+        o.sx = 1.0 / baseline_const;
+        o.sy = 1.0 / (o.top - o.bottom);
+        o.sz = 1.0 / (2.0 * hc.hand_height);
+        sw.slot = (int8_t)e;
+        sw.depth_step = (int8_t)last;
+      }
+    }
+    A.sweeps[(size_t)s * R + r] = sw;
+  }
+  __syncthreads();
+  int nfeas = 0;
+  for (int r = 0; r < R; r++) nfeas += sh.os[r].feasible;
+  if (tid == 0) {
+    atomicAdd(&A.stat[0], sh.sumK);
+    atomicAdd(&A.stat[1], sh.sumKc);
+  }
+  if (nfeas == 0) return;
+
+  // ---------------- pass 2: closing-region count and x extent
+  if (!single_chunk) {
+    __syncthreads();
+    if (tid == 0) sh.cursor = 0;
+    __syncthreads();
+  }
+  for (;;) {
+    if (!single_chunk) fill_chunk(sh, cache, A, hc, q, false, tid);
+    const uint32_t nk = sh.nkept;
+    for (int r = 0; r < R; r++) {
+      const OrientState& o = sh.os[r];
+      if (!o.feasible) continue;
+      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
+      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
+      uint32_t cnt = 0;
+      double mn = INFINITY, mx = -INFINITY;
+      for (uint32_t i = tid; i < nk; i += kHandThreads) {
+        float4 p = cache[i];
+        double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
+        double x = (ax0 * px + ax1 * py) + ax2 * pz;
+        double y = (ay0 * px + ay1 * py) + ay2 * pz;
+        if (y < o.top && x > o.left && x < o.right) {  // finger_hand.cpp:170
+          cnt++;
+          mn = fmin(mn, x);
+          mx = fmax(mx, x);
+        }
+      }
+      for (int of = 16; of > 0; of >>= 1) cnt += __shfl_xor_sync(AG2_FULL, cnt, of);
+      mn = warp_min_d(mn);
+      mx = warp_max_d(mx);
+      if (lane == 0 && cnt) {
+        atomicAdd(&sh.m[r], cnt);
+        atomicMin(&sh.minx[r], d_ordered(mn));
+        atomicMax(&sh.maxx[r], d_ordered(mx));
+      }
+    }
+    __syncthreads();
+    if (single_chunk || sh.cursor >= T) break;
+  }
+  if (tid == 0) {
+    uint32_t total = 0, mmax = 0;
+    for (int r = 0; r < R; r++) {
+      if (!sh.os[r].feasible) continue;
+      sh.off[r] = total;
+      total += sh.m[r];
+      mmax = max(mmax, sh.m[r]);
+    }
+    uint32_t base = total ? atomicAdd(&A.pool_counter[0], total) : 0u;
+    if ((unsigned long long)base + total > A.pool_cap) {
+      atomicExch(&A.pool_counter[1], 1u);
+      sh.pool_ok = 0;
+    }
+    for (int r = 0; r < R; r++) sh.off[r] += base;
+    atomicMax(&A.pool_counter[2], mmax);
+    atomicAdd(&A.stat[2], (unsigned long long)total);
+  }
+  __syncthreads();
+
+  // ---------------- pass 3: in-box ids to the pool, antipodal statistics
+  if (!single_chunk) {
+    if (tid == 0) sh.cursor = 0;
+    __syncthreads();
+  }
+  const bool pool_ok = sh.pool_ok != 0;
+  for (;;) {
+    if (!single_chunk) fill_chunk(sh, cache, A, hc, q, false, tid);
+    const uint32_t nk = sh.nkept;
+    for (int r = 0; r < R; r++) {
+      const OrientState& o = sh.os[r];
+      if (!o.feasible || sh.m[r] == 0) continue;
+      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
+      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
+      const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
+      // extremal thresholds on SCALED x (antipodal.cpp:16-17; scaling is monotone)
+      const double lthr = o.sx * (ordered_d(sh.minx[r]) - o.lc) + 0.003;
+      const double rthr = o.sx * (ordered_d(sh.maxx[r]) - o.lc) - 0.003;
+      bool al = false, ar = false;
+      double st[8] = {-INFINITY, INFINITY, -INFINITY, INFINITY, -INFINITY, INFINITY, -INFINITY, INFINITY};
+      for (uint32_t base_i = 0; base_i < nk; base_i += kHandThreads) {
+        uint32_t i = base_i + tid;
+        bool inbox = false;
+        double x = 0, y = 0, px = 0, py = 0, pz = 0;
+        uint32_t pos = 0;
+        if (i < nk) {
+          float4 p = cache[i];
+          px = (double)p.x, py = (double)p.y, pz = (double)p.z;
+          pos = __float_as_uint(p.w);
+          x = (ax0 * px + ax1 * py) + ax2 * pz;
+          y = (ay0 * px + ay1 * py) + ay2 * pz;
+          inbox = y < o.top && x > o.left && x < o.right;
+        }
+        uint32_t ballot = __ballot_sync(AG2_FULL, inbox);
+        uint32_t wbase = 0;
+        if (lane == 0 && ballot) wbase = atomicAdd(&sh.fill[r], (uint32_t)__popc(ballot));
+        wbase = __shfl_sync(AG2_FULL, wbase, 0);
+        if (inbox) {
+          if (pool_ok) A.pool[sh.off[r] + wbase + __popc(ballot & ((1u << lane) - 1))] = (int32_t)pos;
+          double z = (az0 * px + az1 * py) + az2 * pz;
+          double xs = o.sx * (x - o.lc);
+          double ys = o.sy * (y - o.bottom);
+          double zs = o.sz * (z - hc.neg_hand_height);
+          float4 nv = A.g.nrm[pos];
+          double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
+          double nxr = (ax0 * n0 + ax1 * n1) + ax2 * n2;
+          double nyr = (ay0 * n0 + ay1 * n1) + ay2 * n2;
+          double nzr = (az0 * n0 + az1 * n1) + az2 * n2;
+          double ln = (-1.0 * nxr + 0.0 * nyr) + 0.0 * nzr;  // l^T n, antipodal.cpp:21,24
+          double rn = (1.0 * nxr + 0.0 * nyr) + 0.0 * nzr;
+          if (ln > hc.cos_friction && xs < lthr) {
+            al = true;
+            st[0] = fmax(st[0], ys), st[1] = fmin(st[1], ys);
+            st[2] = fmax(st[2], zs), st[3] = fmin(st[3], zs);
+          }
+          if (rn > hc.cos_friction && xs > rthr) {
+            ar = true;
+            st[4] = fmax(st[4], ys), st[5] = fmin(st[5], ys);
+            st[6] = fmax(st[6], zs), st[7] = fmin(st[7], zs);
+          }
+        }
+      }
+      uint32_t bl = __ballot_sync(AG2_FULL, al), br = __ballot_sync(AG2_FULL, ar);
+#pragma unroll
+      for (int k = 0; k < 8; k++) st[k] = (k & 1) ? warp_min_d(st[k]) : warp_max_d(st[k]);
+      if (lane == 0) {
+        if (bl) {
+          sh.anyl[r] = 1;
+          for (int k = 0; k < 4; k++) {
+            if (k & 1) atomicMin(&sh.ap[r][k], d_ordered(st[k])); else atomicMax(&sh.ap[r][k], d_ordered(st[k]));
+          }
+        }
+        if (br) {
+          sh.anyr[r] = 1;
+          for (int k = 4; k < 8; k++) {
+            if (k & 1) atomicMin(&sh.ap[r][k], d_ordered(st[k])); else atomicMax(&sh.ap[r][k], d_ordered(st[k]));
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (single_chunk || sh.cursor >= T) break;
+  }
+
+  // ---------------- records: one thread per orientation
+  if (tid < R && sh.os[tid].feasible) {
+    const int r = tid;
+    const OrientState& o = sh.os[r];
+    const size_t slot_id = (size_t)s * R + r;
+    ag2_sweep_record sw = A.sweeps[slot_id];
+    sw.num_in_box = (int32_t)sh.m[r];
+    if (sh.m[r] > 0) {  // empty closing region: orientation skipped (hand_search.cpp:377-381)
+      int result = 0;
+      if (sh.anyl[r] || sh.anyr[r]) result = 1;
+      if (sh.anyl[r] && sh.anyr[r]) {
+        double top_y = fmin(ordered_d(sh.ap[r][0]), ordered_d(sh.ap[r][4]));
+        double bot_y = fmax(ordered_d(sh.ap[r][1]), ordered_d(sh.ap[r][5]));
+        double top_z = fmin(ordered_d(sh.ap[r][2]), ordered_d(sh.ap[r][6]));
+        double bot_z = fmax(ordered_d(sh.ap[r][3]), ordered_d(sh.ap[r][7]));
+        if (top_y > bot_y && top_z > bot_z) result = 2;
+      }
+      ag2_hypothesis g;
+      const double surface = ordered_d(sh.ymin[r]);  // points.row(1).minCoeff(), finger_hand.cpp:158
+      for (int a = 0; a < 3; a++) {
+        double fx = sh.FRx[r][a], fy = sh.FRy[r][a], fz = sh.F[a][2];
+        g.surface[a] = ((fx * o.center + fy * surface) + fz * 0.0) + sh.sample[a];
+        g.bottom[a] = ((fx * o.center + fy * o.bottom) + fz * 0.0) + sh.sample[a];
+        g.top[a] = ((fx * o.center + fy * o.top) + fz * 0.0) + sh.sample[a];
+        g.binormal[a] = fx;
+        g.approach[a] = fy;
+        g.axis[a] = fz;
+      }
+      g.width = ordered_d(sh.maxx[r]) - ordered_d(sh.minx[r]);
+      g.score = 0.0;
+      g.sample_id = (int32_t)s;
+      g.orientation_id = r;
+      g.half_antipodal = (uint8_t)(result >= 1);
+      g.full_antipodal = (uint8_t)(result == 2);
+      g.finger_slot = (uint8_t)o.slot;
+      g.depth_step = (uint8_t)o.last;
+      g.num_in_box = (int32_t)sh.m[r];
+      g.hand_top = o.top;
+      g.hand_bottom = o.bottom;
+      A.slots[slot_id] = g;
+      A.box_ref[slot_id] = BoxRef{sh.off[r], sh.m[r]};
+      sw.antipodal = (uint8_t)result;
+      sw.emitted = 1;
+    }
+    A.sweeps[slot_id] = sw;
+  }
+}
+
+}  // namespace
+
+int hands_compute(ag2_ctx* c) {
+  phase_begin(c, 3);
+  cudaStream_t st = c->stream;
+  const uint32_t S = (uint32_t)c->num_samples;
+  const int R = c->p.num_orientations;
+  const size_t SR = (size_t)S * R;
+  AG2_CUDA(c, c->sweeps.reserve(SR));
+  AG2_CUDA(c, c->slots.reserve(SR));
+  AG2_CUDA(c, c->box_ref.reserve(SR));
+  if (c->box_pool.cap == 0) AG2_CUDA(c, c->box_pool.reserve(std::max<size_t>((size_t)1 << 22, SR * 256)));
+  const size_t shared_base = (sizeof(Shared) + 15) & ~(size_t)15;
+  const uint32_t cap = 6144;  // staged points per chunk (96 KB)
+  const size_t smem = shared_base + (size_t)cap * sizeof(float4);
+  AG2_CUDA(c, cudaFuncSetAttribute(k_hands, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int attempt = 0; attempt < 8; attempt++) {
+    AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 20, 0, 12 * sizeof(uint32_t), st));
+    HandsArgs A;
+    A.g = grid_dev(c);
+    A.frames = c->frames.p;
+    A.cap = cap;
+    A.sweeps = c->sweeps.p;
+    A.slots = c->slots.p;
+    A.box_ref = c->box_ref.p;
+    A.pool = c->box_pool.p;
+    A.pool_cap = (uint32_t)std::min<size_t>(c->box_pool.cap, 0xFFFFFFFFu);
+    A.pool_counter = c->scalars.p + 20;
+    A.stat = (unsigned long long*)(c->scalars.p + 24);
+    k_hands<<<S, kHandThreads, smem, st>>>(A, c->hc);
+    AG2_LAUNCH_CHECK(c);
+    uint32_t res[12];
+    AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 20, sizeof(res), cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    unsigned long long stat[3];
+    memcpy(stat, &res[4], sizeof(stat));
+    if (res[1]) {  // pool overflow: grow to the exact need and redo
+      if ((size_t)res[0] > 0xFFFFFFF0u) return AG2_E_CAPACITY;
+      AG2_CUDA(c, c->box_pool.reserve((size_t)res[0] + 1024));
+      continue;
+    }
+    c->max_in_box = res[2];
+    c->st.sum_neighbors_hands = (int64_t)stat[0];
+    c->st.sum_cropped = (int64_t)stat[1];
+    c->st.sum_in_box = (int64_t)stat[2];
+    phase_end(c, 3);
+    return AG2_OK;
+  }
+  return AG2_E_CAPACITY;
+}
+
+}  // namespace ag2

@@ -1,0 +1,258 @@
+// K8-K10: the shipped LeNet (caffe/sigmoid_lenet.prototxt) forward pass,
+// replacing Classifier::ClassifyBatch / PredictBatch / PreprocessBatch
+// (reference caffe_classifier.cpp:70-198):
+//   data[B,3,60,60] (u8 image planes as float 0..255, no mean, no scale)
+//   conv1 20@5x5 -> maxpool 2/2 -> conv2 50@5x5 -> maxpool 2/2 -> ip1 500 -> ReLU -> ip2 2
+// and returns the raw ip2 logits (caffe_classifier.cpp:121-126).
+// Round-1 implementation: fp32 CUDA-core kernels with shared-memory staging and
+// register tiling, pooling / bias / ReLU fused into the producing kernel.  fp32
+// accumulate; summation order differs from Caffe's sgemm, hence the stated
+// tolerance on logits.  Built WITH fma contraction.
+#include <math.h>
+
+#include <algorithm>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+namespace {
+
+constexpr int C1_OUT = 20, C2_OUT = 50, IP1_OUT = 500;
+constexpr int P1 = 28, P2 = 12;
+
+// conv1 (3->20, 5x5) + bias + maxpool 2x2.  One CTA per image.
+__global__ void __launch_bounds__(256)
+k_conv1_pool(const uint8_t* __restrict__ images, const float* __restrict__ w, const float* __restrict__ b,
+             float* __restrict__ out /* [n][20][28][28] */) {
+  __shared__ uint8_t in_s[3][60][64];  // u8 planes; converted at use (exact)
+  __shared__ float w_s[C1_OUT * 75];
+  __shared__ float b_s[C1_OUT];
+  const int tid = threadIdx.x;
+  const uint8_t* img = images + (size_t)blockIdx.x * AG2_IMAGE_BYTES;
+  for (int i = tid; i < 3600 * 3; i += 256) {
+    int ch = i % 3, px = i / 3;
+    in_s[ch][px / 60][px % 60] = img[i];  // cv::split; convertTo(CV_32FC3) happens at use
+  }
+  for (int i = tid; i < C1_OUT * 75; i += 256) w_s[i] = w[i];
+  if (tid < C1_OUT) b_s[tid] = b[tid];
+  __syncthreads();
+  float* o = out + (size_t)blockIdx.x * C1_OUT * P1 * P1;
+  // work item: pooled position (py, px) x group of 4 output channels
+  for (int item = tid; item < P1 * P1 * (C1_OUT / 4); item += 256) {
+    int pos = item % (P1 * P1), og = item / (P1 * P1);
+    int py = pos / P1, px = pos % P1;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) acc[a][k] = 0.f;
+    for (int ic = 0; ic < 3; ic++) {
+      float patch[6][6];
+#pragma unroll
+      for (int y = 0; y < 6; y++)
+#pragma unroll
+        for (int x = 0; x < 6; x++) patch[y][x] = (float)in_s[ic][2 * py + y][2 * px + x];
+#pragma unroll
+      for (int a = 0; a < 4; a++) {
+        const float* wk = &w_s[((og * 4 + a) * 3 + ic) * 25];
+#pragma unroll
+        for (int ky = 0; ky < 5; ky++)
+#pragma unroll
+          for (int kx = 0; kx < 5; kx++) {
+            float wv = wk[ky * 5 + kx];
+            acc[a][0] += wv * patch[ky][kx];
+            acc[a][1] += wv * patch[ky][kx + 1];
+            acc[a][2] += wv * patch[ky + 1][kx];
+            acc[a][3] += wv * patch[ky + 1][kx + 1];
+          }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      float m = fmaxf(fmaxf(acc[a][0], acc[a][1]), fmaxf(acc[a][2], acc[a][3]));
+      o[((og * 4 + a) * P1 + py) * P1 + px] = m + b_s[og * 4 + a];
+    }
+  }
+}
+
+// conv2 (20->50, 5x5) + bias + maxpool 2x2.  One CTA per image; output channels in
+// groups of 10 whose weights are staged in shared memory.
+__global__ void __launch_bounds__(288)
+k_conv2_pool(const float* __restrict__ in /* [n][20][28][28] */, const float* __restrict__ w,
+             const float* __restrict__ b, float* __restrict__ out /* [n][50][12][12] */) {
+  extern __shared__ float sm[];
+  float* in_s = sm;                   // 20*28*29
+  float* w_s = in_s + 20 * 28 * 29;   // 10*500
+  const int tid = threadIdx.x;
+  const float* src = in + (size_t)blockIdx.x * 20 * P1 * P1;
+  for (int i = tid; i < 20 * P1 * P1; i += 288) {
+    int c = i / (P1 * P1), r = (i / P1) % P1, x = i % P1;
+    in_s[(c * 28 + r) * 29 + x] = src[i];
+  }
+  float* o = out + (size_t)blockIdx.x * C2_OUT * P2 * P2;
+  const int pos = tid % (P2 * P2), half = tid / (P2 * P2);  // 144 positions x 2 halves of 5 channels
+  const int py = pos / P2, px = pos % P2;
+  for (int og = 0; og < 5; og++) {
+    __syncthreads();
+    for (int i = tid; i < 10 * 500; i += 288) w_s[i] = w[(size_t)og * 10 * 500 + i];
+    __syncthreads();
+    float acc[5][4];
+#pragma unroll
+    for (int a = 0; a < 5; a++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) acc[a][k] = 0.f;
+    for (int ic = 0; ic < 20; ic++) {
+      float patch[6][6];
+#pragma unroll
+      for (int y = 0; y < 6; y++)
+#pragma unroll
+        for (int x = 0; x < 6; x++) patch[y][x] = in_s[(ic * 28 + 2 * py + y) * 29 + 2 * px + x];
+#pragma unroll
+      for (int a = 0; a < 5; a++) {
+        const float* wk = &w_s[((half * 5 + a) * 20 + ic) * 25];
+#pragma unroll
+        for (int ky = 0; ky < 5; ky++)
+#pragma unroll
+          for (int kx = 0; kx < 5; kx++) {
+            float wv = wk[ky * 5 + kx];
+            acc[a][0] += wv * patch[ky][kx];
+            acc[a][1] += wv * patch[ky][kx + 1];
+            acc[a][2] += wv * patch[ky + 1][kx];
+            acc[a][3] += wv * patch[ky + 1][kx + 1];
+          }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 5; a++) {
+      int oc = og * 10 + half * 5 + a;
+      float m = fmaxf(fmaxf(acc[a][0], acc[a][1]), fmaxf(acc[a][2], acc[a][3]));
+      o[(oc * P2 + py) * P2 + px] = m + b[oc];
+    }
+  }
+}
+
+// ip1: H[n][500] = relu(X[n][7200] . W[500][7200]^T + b).  64x64 tile, BK 16, 4x4 per thread.
+__global__ void __launch_bounds__(256)
+k_ip1_relu(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ b,
+           float* __restrict__ H, int n) {
+  constexpr int BM = 64, BN = 64, BK = 16, K = 7200;
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int tx = tid % 16, ty = tid / 16;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+  const int lr = tid / 4, lc = (tid % 4) * 4;  // 64 rows x 16 k, one float4 per thread
+  for (int k0 = 0; k0 < K; k0 += BK) {
+    float4 av = make_float4(0, 0, 0, 0), bv = make_float4(0, 0, 0, 0);
+    if (m0 + lr < n) av = *reinterpret_cast<const float4*>(&X[(size_t)(m0 + lr) * K + k0 + lc]);
+    if (n0 + lr < IP1_OUT) bv = *reinterpret_cast<const float4*>(&W[(size_t)(n0 + lr) * K + k0 + lc]);
+    As[lc][lr] = av.x, As[lc + 1][lr] = av.y, As[lc + 2][lr] = av.z, As[lc + 3][lr] = av.w;
+    Bs[lc][lr] = bv.x, Bs[lc + 1][lr] = bv.y, Bs[lc + 2][lr] = bv.z, Bs[lc + 3][lr] = bv.w;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < BK; k++) {
+      float a[4], bb[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) a[i] = As[k][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; j++) bb[j] = Bs[k][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] += a[i] * bb[j];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    int m = m0 + ty * 4 + i;
+    if (m >= n) continue;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      int o = n0 + tx * 4 + j;
+      if (o < IP1_OUT) H[(size_t)m * IP1_OUT + o] = fmaxf(acc[i][j] + b[o], 0.f);
+    }
+  }
+}
+
+// ip2: logits[n][2]; one warp per image
+__global__ void k_ip2(const float* __restrict__ H, const float* __restrict__ W, const float* __restrict__ b,
+                      float* __restrict__ logits, int n) {
+  int img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (img >= n) return;
+  float a0 = 0.f, a1 = 0.f;
+  for (int k = lane; k < IP1_OUT; k += 32) {
+    float h = H[(size_t)img * IP1_OUT + k];
+    a0 += W[k] * h;
+    a1 += W[IP1_OUT + k] * h;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    a0 += __shfl_xor_sync(AG2_FULL, a0, o);
+    a1 += __shfl_xor_sync(AG2_FULL, a1, o);
+  }
+  if (lane == 0) {
+    logits[2 * img] = a0 + b[0];
+    logits[2 * img + 1] = a1 + b[1];
+  }
+}
+
+}  // namespace
+
+int lenet_upload(ag2_ctx* c) {
+  LeNetDev& L = c->net;
+  static const size_t sizes[8] = {20 * 75, 20, 50 * 500, 50, 500 * 7200, 500, 2 * 500, 2};
+  DevBuf<float>* bufs[8] = {&L.c1w, &L.c1b, &L.c2w, &L.c2b, &L.i1w, &L.i1b, &L.i2w, &L.i2b};
+  for (int i = 0; i < 8; i++) {
+    if (L.host[i].size() != sizes[i]) return AG2_E_INVALID;
+    AG2_CUDA(c, bufs[i]->reserve(sizes[i]));
+    AG2_CUDA(c, cudaMemcpyAsync(bufs[i]->p, L.host[i].data(), sizes[i] * sizeof(float), cudaMemcpyHostToDevice,
+                                c->stream));
+  }
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  L.loaded = true;
+  return AG2_OK;
+}
+
+int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits) {
+  if (!c->net.loaded) return AG2_E_NO_WEIGHTS;
+  if (n == 0) return AG2_OK;
+  cudaStream_t st = c->stream;
+  const LeNetDev& L = c->net;
+  const size_t chunk_max = 4096;
+  const size_t per_img = (size_t)20 * P1 * P1 + (size_t)50 * P2 * P2 + IP1_OUT;
+  AG2_CUDA(c, c->act.reserve(std::min(n, chunk_max) * per_img));
+  const size_t smem2 = (size_t)(20 * 28 * 29 + 10 * 500) * sizeof(float);
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_pool, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  for (size_t off = 0; off < n; off += chunk_max) {
+    const size_t m = std::min(chunk_max, n - off);
+    float* a1 = c->act.p;
+    float* a2 = a1 + m * 20 * P1 * P1;
+    float* hh = a2 + m * 50 * P2 * P2;
+    k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p, a1);
+    AG2_LAUNCH_CHECK(c);
+    k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
+    AG2_LAUNCH_CHECK(c);
+    dim3 g1((unsigned)((m + 63) / 64), (IP1_OUT + 63) / 64);
+    k_ip1_relu<<<g1, 256, 0, st>>>(a2, L.i1w.p, L.i1b.p, hh, (int)m);
+    AG2_LAUNCH_CHECK(c);
+    k_ip2<<<(unsigned)((m * 32 + 255) / 256), 256, 0, st>>>(hh, L.i2w.p, L.i2b.p, d_logits + 2 * off, (int)m);
+    AG2_LAUNCH_CHECK(c);
+  }
+  return AG2_OK;
+}
+
+int classify_compute(ag2_ctx* c) {
+  phase_begin(c, 6);
+  const size_t n = c->list_n[AG2_LIST_PRUNED];
+  AG2_CUDA(c, c->logits.reserve(std::max<size_t>(n, 1) * 2));
+  AG2_TRY(lenet_forward(c, c->images.p, n, c->logits.p));
+  phase_end(c, 6);
+  return AG2_OK;
+}
+
+}  // namespace ag2

@@ -1,0 +1,206 @@
+// K7: grasp images, replacing Learning::createGraspImages / createInstance /
+// convertToImageRGB (reference learning.cpp:4-33, :221-249, :143-209) and the
+// OpenCV tail dilate(3x3) -> cvtColor(BGR2RGB) -> convertTo(CV_8UC3, 255).
+// One CTA per pruned hypothesis:
+//   1. load its in-box ids from the pool, sort them by (d2, id): the reference's
+//      per-cell double sums run in radiusSearch order, so the order is restored
+//      once here and images come out independent of the hand kernel's schedule;
+//   2. recompute the scaled points / rotated normals with the hand kernel's exact
+//      arithmetic, cell = floor(x'/cs) + 60*floor((y'-min y')/cs)  (no clamping);
+//   3. sort (cell, rank) keys; one thread per cell sums its run in rank order
+//      (the reference scans all m points for each of 3600 cells: O(3600 m));
+//   4. normalise, abs, float image in shared memory, 3x3 max, channel swap,
+//      round-half-even x255 -> u8 HWC (the cv::Mat layout).
+#include <math.h>
+
+#include <algorithm>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+namespace {
+
+constexpr int kRenderThreads = 256;
+constexpr int IS = AG2_IMAGE_SIZE;
+
+struct RenderArgs {
+  GridDev g;
+  const uint32_t* list;        // pruned slot ids
+  const ag2_hypothesis* slots;
+  const BoxRef* box_ref;
+  const int32_t* pool;
+  const ag2_frame* frames;
+  uint32_t cap;                // padded capacity (power of two) >= max m
+  uint8_t* out;                // n * 10800
+};
+
+__device__ __forceinline__ long long dord(double v) {
+  long long i = __double_as_longlong(v);
+  return i >= 0 ? i : i ^ 0x7fffffffffffffffll;
+}
+__device__ __forceinline__ double ordd(long long i) {
+  return __longlong_as_double(i >= 0 ? i : i ^ 0x7fffffffffffffffll);
+}
+
+__global__ void __launch_bounds__(kRenderThreads)
+k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* keys = (uint64_t*)smem;                      // cap
+  uint32_t* vals = (uint32_t*)(keys + A.cap);            // cap   (sorted positions)
+  uint32_t* ckeys = vals + A.cap;                        // cap   (cell << 16 | rank)  [m < 65536]
+  float* img = (float*)(ckeys + A.cap);                  // 60*60*3
+  __shared__ long long miny_s;
+  __shared__ double FR[3][3];
+  const int tid = threadIdx.x;
+  const uint32_t slot = A.list[blockIdx.x];
+  const ag2_hypothesis& hyp = A.slots[slot];
+  const BoxRef br = A.box_ref[slot];
+  const uint32_t m = br.count;
+  const ag2_frame& fr = A.frames[hyp.sample_id];
+  const float q[3] = {(float)fr.sample[0], (float)fr.sample[1], (float)fr.sample[2]};
+  if (tid < 9) {
+    int a = tid / 3, b = tid % 3;  // frame_rot columns: binormal, approach, axis
+    FR[a][b] = b == 0 ? hyp.binormal[a] : (b == 1 ? hyp.approach[a] : hyp.axis[a]);
+  }
+  if (tid == 0) miny_s = dord(INFINITY);
+  for (int i = tid; i < IS * IS * 3; i += kRenderThreads) img[i] = 0.f;
+  const uint32_t n_pad = next_pow2(max(m, 2u));
+  for (uint32_t t = tid; t < n_pad; t += kRenderThreads) {
+    if (t < m) {
+      uint32_t pos = (uint32_t)A.pool[br.offset + t];
+      float4 p = A.g.pts[pos];
+      float d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
+      keys[t] = nn_key(d2, __float_as_uint(p.w));
+      vals[t] = pos;
+    } else {
+      keys[t] = ~0ull;
+      vals[t] = 0;
+    }
+  }
+  __syncthreads();
+  bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kRenderThreads, BlockSync());
+  // hand-frame constants of this hypothesis (same values the hand kernel used)
+  const int e = hyp.finger_slot;
+  const double left = hc.fs_hi[e], right = hc.fs_lo[10 + e];
+  const double top = hyp.hand_top, bottom = hyp.hand_bottom;
+  const double baseline_const = 0.1;
+  const double lc = left - 0.5 * (baseline_const - (right - left));
+  const double sx = 1.0 / baseline_const, sy = 1.0 / (top - bottom);
+  const double cellsize = 1.0 / (double)IS;
+  // pass A: min over scaled y (learning.cpp:149)
+  double mny = INFINITY;
+  for (uint32_t t = tid; t < m; t += kRenderThreads) {
+    float4 p = A.g.pts[vals[t]];
+    double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
+    double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
+    mny = fmin(mny, sy * (y - bottom));
+  }
+  mny = warp_min_d(mny);
+  if ((tid & 31) == 0) atomicMin(&miny_s, dord(mny));
+  __syncthreads();
+  const double miny = ordd(miny_s);
+  // pass B: cell of every point
+  for (uint32_t t = tid; t < n_pad; t += kRenderThreads) {
+    uint32_t key = 0xFFFFFFFFu;
+    if (t < m) {
+      float4 p = A.g.pts[vals[t]];
+      double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
+      double x = (FR[0][0] * px + FR[1][0] * py) + FR[2][0] * pz;
+      double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
+      double xs = sx * (x - lc);
+      double ys = sy * (y - bottom) - miny;
+      // floorVector(pts.row(0) / cellsize): true division, floor, int conversion
+      double hc_ = floor(xs / cellsize), vc_ = floor(ys / cellsize);
+      // cell_indices = h + v*60 evaluated in int; guard the int conversion range
+      if (hc_ > -1e6 && hc_ < 1e6 && vc_ > -1e6 && vc_ < 1e6) {
+        int cell = (int)hc_ + (int)vc_ * IS;
+        if (cell >= 0 && cell < IS * IS) key = ((uint32_t)cell << 16) | t;  // else never matched
+      }
+    }
+    ckeys[t] = key;
+  }
+  __syncthreads();
+  bitonic_sort_u32(ckeys, n_pad, (uint32_t)tid, (uint32_t)kRenderThreads, BlockSync());
+  // pass C: one thread per run start sums the run in rank order (learning.cpp:166-192)
+  for (uint32_t t = tid; t < m; t += kRenderThreads) {
+    uint32_t key = ckeys[t];
+    if (key == 0xFFFFFFFFu) continue;
+    uint32_t cell = key >> 16;
+    if (t > 0 && (ckeys[t - 1] >> 16) == cell) continue;  // not a run start
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (uint32_t u = t; u < m; u++) {
+      uint32_t ku = ckeys[u];
+      if ((ku >> 16) != cell) break;
+      float4 nv = A.g.nrm[vals[ku & 0xFFFFu]];
+      double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
+      // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
+      ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
+      ay += (FR[0][1] * n0 + FR[1][1] * n1) + FR[2][1] * n2;
+      az += (FR[0][2] * n0 + FR[1][2] * n1) + FR[2][2] * n2;
+    }
+    double s = 1.0 / sqrt(ax * ax + (ay * ay + az * az));
+    int row = (int)cell / IS, col = (int)cell % IS;
+    float* px = &img[((IS - 1 - row) * IS + col) * 3];
+    px[0] = (float)fabs(s * ax);
+    px[1] = (float)fabs(s * ay);
+    px[2] = (float)fabs(s * az);
+  }
+  __syncthreads();
+  // dilate 3x3 (in-bounds max) -> BGR2RGB -> saturate_cast<uchar>(v * 255) round-half-even
+  uint8_t* out = A.out + (size_t)blockIdx.x * AG2_IMAGE_BYTES;
+  for (int i = tid; i < IS * IS * 3; i += kRenderThreads) {
+    int ch = i % 3, c = (i / 3) % IS, r = i / (3 * IS);
+    int src_ch = 2 - ch;
+    float mx = -INFINITY;
+    for (int dr = -1; dr <= 1; dr++) {
+      int rr = r + dr;
+      if (rr < 0 || rr >= IS) continue;
+      for (int dc = -1; dc <= 1; dc++) {
+        int cc = c + dc;
+        if (cc < 0 || cc >= IS) continue;
+        mx = fmaxf(mx, img[(rr * IS + cc) * 3 + src_ch]);
+      }
+    }
+    float v = __fmul_rn(mx, 255.0f);
+    int iv = __float2int_rn(v);
+    out[i] = (uint8_t)min(max(iv, 0), 255);
+  }
+}
+
+}  // namespace
+
+int render_compute(ag2_ctx* c) {
+  phase_begin(c, 5);
+  const size_t n = c->list_n[AG2_LIST_PRUNED];
+  AG2_CUDA(c, c->images.reserve(std::max<size_t>(n, 1) * AG2_IMAGE_BYTES));
+  if (n) {
+    if (c->max_in_box >= 65536) {
+      c->err = "render: more than 65535 points in a closing region";
+      return AG2_E_CAPACITY;
+    }
+    uint32_t cap = 64;
+    while (cap < c->max_in_box) cap <<= 1;
+    size_t smem = (size_t)cap * 16 + (size_t)IS * IS * 3 * sizeof(float);
+    if (smem > 220 * 1024) {
+      c->err = "render: closing region too large for shared memory";
+      return AG2_E_CAPACITY;
+    }
+    AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RenderArgs A;
+    A.g = grid_dev(c);
+    A.list = c->list[AG2_LIST_PRUNED].p;
+    A.slots = c->slots.p;
+    A.box_ref = c->box_ref.p;
+    A.pool = c->box_pool.p;
+    A.frames = c->frames.p;
+    A.cap = cap;
+    A.out = c->images.p;
+    k_render<<<(unsigned)n, kRenderThreads, smem, c->stream>>>(A, c->hc);
+    AG2_LAUNCH_CHECK(c);
+  }
+  c->have_images = true;
+  phase_end(c, 5);
+  return AG2_OK;
+}
+
+}  // namespace ag2

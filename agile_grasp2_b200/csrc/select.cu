@@ -1,0 +1,240 @@
+// List building around the hand kernel: concatenation in (sample, orientation)
+// order (hand_search.cpp:221-228), S13 prune (grasp_detector.cpp:363-395),
+// mode filters (:170-221) and top-k selection (:238-252).  Integer / compare
+// work over S*R slots: flag -> exclusive scan -> ordered compaction.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+namespace {
+
+constexpr int kT = 256;
+
+__global__ void k_flag_emitted(const ag2_sweep_record* __restrict__ sw, size_t n, uint32_t* __restrict__ flag) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i < n) flag[i] = sw[i].emitted ? 1u : 0u;
+}
+
+struct PruneArgs {
+  double half_width;  // 0.5 * outer_diameter_
+  double min_aperture, max_aperture;
+  float min_x, max_x, min_y, max_y, min_z;  // float arguments of pruneGraspsOnHandParameters
+  int filter_half, enabled;
+};
+
+__global__ void k_flag_pruned(const ag2_sweep_record* __restrict__ sw, const ag2_hypothesis* __restrict__ slots,
+                              size_t n, PruneArgs a, uint32_t* __restrict__ flag) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t keep = 0;
+  if (sw[i].emitted) {
+    if (!a.enabled) {
+      keep = 1;
+    } else {
+      const ag2_hypothesis& g = slots[i];
+      if (!a.filter_half || g.half_antipodal) {
+        double mn[3], mx[3];
+        for (int d = 0; d < 3; d++) {
+          double v0 = g.bottom[d] + a.half_width * g.binormal[d];
+          double v1 = g.bottom[d] - a.half_width * g.binormal[d];
+          double v2 = g.top[d] + a.half_width * g.binormal[d];
+          double v3 = g.top[d] - a.half_width * g.binormal[d];
+          double v4 = g.bottom[d] - 0.10 * g.approach[d];
+          mn[d] = fmin(fmin(fmin(v0, v1), fmin(v2, v3)), v4);
+          mx[d] = fmax(fmax(fmax(v0, v1), fmax(v2, v3)), v4);
+        }
+        double ap = g.width;
+        keep = (ap >= a.min_aperture && ap <= a.max_aperture && mn[2] >= (double)a.min_z &&
+                mn[1] >= (double)a.min_y && mx[1] <= (double)a.max_y && mn[0] >= (double)a.min_x &&
+                mx[0] <= (double)a.max_x)
+                   ? 1u
+                   : 0u;
+      }
+    }
+  }
+  flag[i] = keep;
+}
+
+// mode: 0 keep all of `src`, 2 keep full_antipodal, 1 keep score >= thr (and mark)
+__global__ void k_flag_mode(const uint32_t* __restrict__ src, size_t n, ag2_hypothesis* __restrict__ slots,
+                            const float* __restrict__ logits, int mode, double thr, uint32_t* __restrict__ flag) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ag2_hypothesis& g = slots[src[i]];
+  uint32_t keep = 1;
+  if (mode == AG2_MODE_GEOMETRIC) keep = g.full_antipodal ? 1u : 0u;
+  if (mode == AG2_MODE_PREDICTION) {
+    // grasp_detector.cpp:200: float difference stored in a double
+    double score = (double)__fsub_rn(logits[2 * i + 1], logits[2 * i]);
+    keep = score >= thr ? 1u : 0u;
+    if (keep) {
+      g.score = score;
+      g.full_antipodal = 1;
+    }
+  }
+  flag[i] = keep;
+}
+
+// out[scan[i]] = src ? src[i] : i   for flagged i
+__global__ void k_compact(const uint32_t* __restrict__ flag_scan, const uint32_t* __restrict__ src, size_t n,
+                          uint32_t* __restrict__ out) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t a = flag_scan[i], b = flag_scan[i + 1];
+  if (b != a) out[a] = src ? src[i] : (uint32_t)i;
+}
+
+__global__ void k_gather(const uint32_t* __restrict__ list, size_t n, const ag2_hypothesis* __restrict__ slots,
+                         ag2_hypothesis* __restrict__ out) {
+  // 192-byte records moved as 12 x 16 B per record
+  size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  size_t rec = t / 12, part = t % 12;
+  if (rec >= n) return;
+  const uint4* s = reinterpret_cast<const uint4*>(&slots[list[rec]]);
+  reinterpret_cast<uint4*>(&out[rec])[part] = s[part];
+}
+
+__global__ void k_score_keys(const uint32_t* __restrict__ list, size_t n, const ag2_hypothesis* __restrict__ slots,
+                             uint64_t* __restrict__ keys) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // descending score, ties keep list order (documented deviation D4: partial_sort is unstable)
+  long long o = __double_as_longlong(slots[list[i]].score);
+  unsigned long long u = o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
+  // 32 high bits of the order-preserving code are enough to rank float-born scores
+  // only when they are floats; keep it exact instead: rank by full code on the host side
+  keys[i] = ~u;
+}
+
+}  // namespace
+
+// flags (n entries, 0/1) -> compacted `out`, returns count (one small D2H sync)
+static int compact_list(ag2_ctx* c, size_t n, const uint32_t* src, DevBuf<uint32_t>& out, size_t* count) {
+  cudaStream_t st = c->stream;
+  AG2_CUDA(c, out.reserve(std::max<size_t>(n, 1)));
+  if (n == 0) {
+    *count = 0;
+    return AG2_OK;
+  }
+  AG2_TRY(exclusive_scan_u32(c, c->flags.p, n));
+  k_compact<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->flags.p, src, n, out.p);
+  AG2_LAUNCH_CHECK(c);
+  uint32_t total = 0;
+  AG2_CUDA(c, cudaMemcpyAsync(&total, c->flags.p + n, 4, cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaStreamSynchronize(st));
+  *count = total;
+  return AG2_OK;
+}
+
+int lists_build_after_hands(ag2_ctx* c) {
+  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
+  AG2_CUDA(c, c->flags.reserve(SR + 1));
+  if (SR) {
+    k_flag_emitted<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, SR, c->flags.p);
+    AG2_LAUNCH_CHECK(c);
+  }
+  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_HYPOTHESES], &c->list_n[AG2_LIST_HYPOTHESES]));
+  for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;
+  c->st.num_hypotheses = (int64_t)c->list_n[AG2_LIST_HYPOTHESES];
+  return AG2_OK;
+}
+
+int prune_compute(ag2_ctx* c) {
+  phase_begin(c, 4);
+  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
+  PruneArgs a;
+  a.half_width = 0.5 * c->p.hand_outer_diameter;
+  a.min_aperture = c->p.min_aperture;
+  a.max_aperture = c->p.max_aperture;
+  a.min_x = (float)c->p.workspace[0];
+  a.max_x = (float)c->p.workspace[1];
+  a.min_y = (float)c->p.workspace[2];
+  a.max_y = (float)c->p.workspace[3];
+  a.min_z = c->min_z;
+  a.filter_half = c->p.filter_half_grasps;
+  a.enabled = c->p.prune;
+  AG2_CUDA(c, c->flags.reserve(SR + 1));
+  if (SR) {
+    k_flag_pruned<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, c->slots.p, SR, a, c->flags.p);
+    AG2_LAUNCH_CHECK(c);
+  }
+  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_PRUNED], &c->list_n[AG2_LIST_PRUNED]));
+  c->list_rec_valid[AG2_LIST_PRUNED] = false;
+  c->st.num_pruned = (int64_t)c->list_n[AG2_LIST_PRUNED];
+  phase_end(c, 4);
+  return AG2_OK;
+}
+
+// antipodal list from the pruned list (mode 1 needs logits of the pruned list)
+int select_mode(ag2_ctx* c) {
+  const size_t n = c->list_n[AG2_LIST_PRUNED];
+  AG2_CUDA(c, c->flags.reserve(std::max<size_t>(n, c->num_samples * (size_t)c->p.num_orientations) + 1));
+  if (n) {
+    k_flag_mode<<<(unsigned)((n + kT - 1) / kT), kT, 0, c->stream>>>(
+        c->list[AG2_LIST_PRUNED].p, n, c->slots.p, c->logits.p, c->p.antipodal_mode, c->p.min_score_diff, c->flags.p);
+    AG2_LAUNCH_CHECK(c);
+  }
+  AG2_TRY(compact_list(c, n, c->list[AG2_LIST_PRUNED].p, c->list[AG2_LIST_ANTIPODAL], &c->list_n[AG2_LIST_ANTIPODAL]));
+  for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;  // scores / flags changed in the slots
+  c->st.num_antipodal = (int64_t)c->list_n[AG2_LIST_ANTIPODAL];
+  return AG2_OK;
+}
+
+int select_top(ag2_ctx* c) {
+  phase_begin(c, 7);
+  cudaStream_t st = c->stream;
+  const size_t n = c->list_n[AG2_LIST_ANTIPODAL];
+  AG2_CUDA(c, c->list[AG2_LIST_SELECTED].reserve(std::max<size_t>(n, 1)));
+  if (c->p.antipodal_mode == AG2_MODE_NONE || n == 0) {
+    if (n) AG2_CUDA(c, cudaMemcpyAsync(c->list[AG2_LIST_SELECTED].p, c->list[AG2_LIST_ANTIPODAL].p, n * 4,
+                                       cudaMemcpyDeviceToDevice, st));
+    c->list_n[AG2_LIST_SELECTED] = n;
+  } else {
+    // rank by (score desc, list position asc).  O(n) keys cross PCIe; n is the
+    // number of ANTIPODAL grasps (small next to S*R).
+    DevBuf<uint64_t> keys;
+    AG2_CUDA(c, keys.reserve(n));
+    k_score_keys<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->list[AG2_LIST_ANTIPODAL].p, n, c->slots.p, keys.p);
+    AG2_LAUNCH_CHECK(c);
+    std::vector<uint64_t> hk(n);
+    std::vector<uint32_t> hl(n), order(n);
+    AG2_CUDA(c, cudaMemcpyAsync(hk.data(), keys.p, n * 8, cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaMemcpyAsync(hl.data(), c->list[AG2_LIST_ANTIPODAL].p, n * 4, cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    for (size_t i = 0; i < n; i++) order[i] = (uint32_t)i;
+    size_t k = (c->p.num_selected > 0 && (size_t)c->p.num_selected < n) ? (size_t)c->p.num_selected : n;
+    auto cmp = [&hk](uint32_t a, uint32_t b) { return hk[a] < hk[b] || (hk[a] == hk[b] && a < b); };
+    std::partial_sort(order.begin(), order.begin() + k, order.end(), cmp);
+    std::vector<uint32_t> sel(k);
+    for (size_t i = 0; i < k; i++) sel[i] = hl[order[i]];
+    AG2_CUDA(c, cudaMemcpyAsync(c->list[AG2_LIST_SELECTED].p, sel.data(), k * 4, cudaMemcpyHostToDevice, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    c->list_n[AG2_LIST_SELECTED] = k;
+  }
+  c->list_rec_valid[AG2_LIST_SELECTED] = false;
+  c->st.num_selected = (int64_t)c->list_n[AG2_LIST_SELECTED];
+  phase_end(c, 7);
+  return AG2_OK;
+}
+
+int gather_list_records(ag2_ctx* c, int which) {
+  if (which < 0 || which > 3) return AG2_E_INVALID;
+  if (c->list_rec_valid[which]) return AG2_OK;
+  const size_t n = c->list_n[which];
+  AG2_CUDA(c, c->list_rec[which].reserve(std::max<size_t>(n, 1)));
+  if (n) {
+    size_t threads = n * 12;
+    k_gather<<<(unsigned)((threads + kT - 1) / kT), kT, 0, c->stream>>>(c->list[which].p, n, c->slots.p,
+                                                                      c->list_rec[which].p);
+    AG2_LAUNCH_CHECK(c);
+  }
+  c->list_rec_valid[which] = true;
+  return AG2_OK;
+}
+
+}  // namespace ag2

@@ -4,8 +4,9 @@ Recipe: points are produced by pin-hole ray casting (640x480,
 f = 525 px, c = (319.5, 239.5)) from the reference's camera pose(s)
 (grasp_detector.cpp:111-127) against analytic primitives (table plane, boxes,
 upright cylinders, spheres), Gaussian range noise sigma = 1 mm along the ray,
-transformed to the base frame, stored float32.  Every ray returns (a ray that
-misses all objects hits the table plane), so one view is exactly 307 200 points.
+transformed to the base frame, stored float32.  The table top is the floor of an
+axis-aligned room (back / side walls and ceiling ~1-2 m away), so every ray
+returns within Kinect range and one view is exactly 307 200 points.
 Sample indices are drawn (seeded, without replacement, ascending) from the points
 that lie inside the reference's workspace (launch/file_detect_grasps.launch:16),
 which is what preprocessPointCloud's filterWorkspace + subsampleUniformly select from.
@@ -45,11 +46,18 @@ def _rays(cam_tf: np.ndarray):
     return o, d
 
 
-def _hit_plane(o, d, z0):
+ROOM_MIN = np.array([-0.5, -1.5, TABLE_Z])
+ROOM_MAX = np.array([1.6, 1.5, 1.5])
+
+
+def _hit_room(o, d):
+    """First hit of the inside of the room box (the camera is inside)."""
     with np.errstate(divide="ignore", invalid="ignore"):
-        t = (z0 - o[2]) / d[:, 2]
-    t[~(t > 0)] = np.inf
-    return t
+        t1 = (ROOM_MIN - o) / d
+        t2 = (ROOM_MAX - o) / d
+    t = np.maximum(t1, t2)  # exit distance per axis
+    t[~np.isfinite(t)] = np.inf
+    return np.min(t, axis=1)
 
 
 def _hit_box(o, d, center, size, yaw):
@@ -124,7 +132,7 @@ def _make_objects(rng: np.random.Generator, n_obj: int, kinds=("box", "cyl", "sp
 
 def _cast(cam_tf, objs, rng, noise=0.001):
     o, d = _rays(cam_tf)
-    t = _hit_plane(o, d, TABLE_Z)
+    t = _hit_room(o, d)
     for ob in objs:
         if ob[0] == "box":
             t = np.minimum(t, _hit_box(o, d, ob[1], ob[2], ob[3]))

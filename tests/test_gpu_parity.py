@@ -1,0 +1,188 @@
+"""GPU parity: libag2.so (CUDA, through the C ABI) against the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+from agile_grasp2_b200 import capi, scenes
+from common import angle, both, hyp_int_fields_equal, make_params
+from oracle import binding as ob
+
+pytestmark = pytest.mark.gpu
+POSE_FIELDS = ["surface", "bottom", "top", "axis", "approach", "binormal", "width", "hand_top", "hand_bottom"]
+
+
+@pytest.fixture(scope="module")
+def run_tiny(tiny_scene):
+    p = make_params(capi.MODE_GEOMETRIC)
+    g, o = both(p, tiny_scene)
+    g.detect()
+    o.detect()
+    return g, o, tiny_scene
+
+
+def test_radius_search_sets_bit_exact(run_tiny):
+    g, o, sc = run_tiny
+    rng = np.random.default_rng(0)
+    xyz = sc["xyz"]
+    for r in (0.01, 0.03, 0.1):
+        for i in rng.integers(0, len(xyz), 6):
+            q = xyz[i] + (rng.normal(0, 0.002, 3).astype(np.float32) if i % 2 else 0)
+            gi, gd = g.radius_search(q, r)
+            oi, od = o.radius_search(q, r, brute=True)
+            assert np.array_equal(gi, oi)
+            assert np.array_equal(gd.view(np.uint32), od.view(np.uint32))
+
+
+def test_normals(run_tiny):
+    g, o, _ = run_tiny
+    gn, on = g.normals(), o.normals()
+    assert np.array_equal(np.isnan(gn), np.isnan(on))
+    ok = ~np.isnan(on).any(1)
+    ang = angle(gn[ok], on[ok])
+    bit_equal = np.mean(np.all(gn[ok].view(np.uint32) == on[ok].view(np.uint32), axis=1))
+    print("normals: max angle %.3g rad, bit-equal fraction %.6f" % (ang.max(), bit_equal))
+    assert ang.max() <= 1e-4  # tolerance of north_star
+    assert bit_equal > 0.999
+
+
+def test_frames(run_tiny):
+    g, o, _ = run_tiny
+    gf, of = g.frames(), o.frames()
+    assert np.array_equal(gf["valid"], of["valid"])
+    assert np.array_equal(gf["num_neighbors"], of["num_neighbors"])
+    assert np.array_equal(gf["majority_cam"], of["majority_cam"])
+    v = of["valid"] == 1
+    for f in ("normal", "binormal", "curvature_axis"):
+        assert angle(gf[f][v], of[f][v]).max() <= 1e-6
+    assert np.array_equal(gf["sample"], of["sample"])
+
+
+def test_sweep_records_bit_exact(run_tiny):
+    g, o, _ = run_tiny
+    gs, os_ = g.sweep_records(), o.sweep_records()
+    for f in ("fingers", "hand", "slot", "depth_step", "num_in_box", "antipodal", "emitted"):
+        bad = np.argwhere(gs[f] != os_[f])
+        assert len(bad) == 0, (f, bad[:5], gs[f][tuple(bad[0])], os_[f][tuple(bad[0])])
+
+
+@pytest.mark.parametrize("which", [capi.LIST_HYPOTHESES, capi.LIST_PRUNED, capi.LIST_ANTIPODAL, capi.LIST_SELECTED])
+def test_hypothesis_lists(run_tiny, which):
+    g, o, _ = run_tiny
+    gh, oh = g.hypotheses(which), o.hypotheses(which)
+    assert len(gh) == len(oh)
+    assert hyp_int_fields_equal(gh, oh) is None
+    for f in POSE_FIELDS:
+        assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+    if which == capi.LIST_HYPOTHESES:
+        assert len(gh) > 10
+
+
+def test_in_box_sets(run_tiny):
+    g, o, _ = run_tiny
+    n = g.num(capi.LIST_HYPOTHESES)
+    for h in range(0, n, max(1, n // 12)):
+        assert np.array_equal(g.in_box(capi.LIST_HYPOTHESES, h), o.in_box(capi.LIST_HYPOTHESES, h))
+
+
+def test_stats_match(run_tiny):
+    g, o, _ = run_tiny
+    gs, os_ = g.stats(), o.stats()
+    for k in ("num_frames", "num_hypotheses", "num_pruned", "num_antipodal", "num_selected", "sum_neighbors_hands",
+              "sum_cropped", "sum_in_box", "sum_neighbors_normals"):
+        assert gs[k] == os_[k], k
+    assert gs["gpu_launches"] > 0
+
+
+def test_prediction_mode_images_and_scores(tiny_scene):
+    w = ob.xavier_weights(11, bias_scale=0.5)
+    p = make_params(capi.MODE_PREDICTION, min_score_diff=0.0, num_selected=20)
+    g, o = both(p, tiny_scene, weights=w)
+    g.generate_hypotheses(); o.generate_hypotheses()
+    g.prune(); o.prune()
+    gi, oi = g.render_images(), o.render_images()
+    assert gi.shape == oi.shape and gi.shape[0] > 5
+    diff = gi.astype(int) - oi.astype(int)
+    print("images: %d, differing bytes %d" % (gi.shape[0], np.count_nonzero(diff)))
+    assert np.count_nonzero(diff) == 0
+    g.classify(); o.classify()
+    gl, ol = g.logits(), o.logits()
+    tol = np.maximum(1e-3, 1e-5 * np.abs(ol))
+    print("logits: max abs diff %.3g (scale %.3g)" % (np.abs(gl - ol).max(), np.abs(ol).max()))
+    assert np.all(np.abs(gl - ol) <= tol)
+    g.select(); o.select()
+    gs, os_ = g.hypotheses(capi.LIST_SELECTED), o.hypotheses(capi.LIST_SELECTED)
+    # accept sets identical except scores within tolerance of the threshold
+    ga, oa = g.hypotheses(capi.LIST_ANTIPODAL), o.hypotheses(capi.LIST_ANTIPODAL)
+    key = lambda h: set(zip(h["sample_id"].tolist(), h["orientation_id"].tolist()))
+    sym = key(ga) ^ key(oa)
+    near = {(s, r) for s, r, sc in zip(oh_all(o)["sample_id"], oh_all(o)["orientation_id"], scores_all(o))
+            if abs(sc - p.min_score_diff) <= 1e-3}
+    assert sym <= near
+    assert len(gs) == len(os_)
+
+
+def oh_all(o):
+    return o.hypotheses(capi.LIST_PRUNED)
+
+
+def scores_all(o):
+    l = o.logits()
+    return (l[:, 1] - l[:, 0]).astype(np.float64)
+
+
+def test_classify_images_direct(tiny_scene):
+    w = ob.xavier_weights(5, bias_scale=0.2)
+    p = make_params(capi.MODE_PREDICTION)
+    g = capi.Context(p); o = ob.context(p)
+    g.set_lenet_weights(w); o.set_lenet_weights(w)
+    rng = np.random.default_rng(3)
+    imgs = rng.integers(0, 256, size=(37, 60, 60, 3), dtype=np.uint8)
+    imgs[0] = 0; imgs[1] = 255
+    gl, ol = g.classify_images(imgs), o.classify_images(imgs)
+    tol = np.maximum(1e-3, 1e-5 * np.abs(ol))
+    assert np.all(np.abs(gl - ol) <= tol), np.abs(gl - ol).max()
+
+
+def test_sample_points_and_precomputed_normals(tiny_scene):
+    sc = tiny_scene
+    p = make_params(capi.MODE_GEOMETRIC)
+    o0 = ob.context(p)
+    o0.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); o0.compute_normals()
+    nrm = o0.normals()
+    rng = np.random.default_rng(9)
+    pts = sc["xyz"][sc["samples"][:24]].astype(np.float64) + rng.normal(0, 0.004, (24, 3))
+    g, o = both(p, sc, normals=nrm, sample_points=pts)
+    g.detect(); o.detect()
+    gs, os_ = g.sweep_records(), o.sweep_records()
+    for f in ("fingers", "hand", "slot", "depth_step", "num_in_box", "antipodal", "emitted"):
+        assert np.array_equal(gs[f], os_[f]), f
+    gh, oh = g.hypotheses(), o.hypotheses()
+    assert hyp_int_fields_equal(gh, oh) is None
+    for f in POSE_FIELDS:
+        assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+
+
+def test_plates_known_answer():
+    xyz, nrm = scenes.plates_scene(gap=0.05)
+    p = make_params(capi.MODE_GEOMETRIC, prune=0)
+    sc = dict(xyz=xyz, cam_mask=np.ones(len(xyz), np.uint8), num_cams=1, samples=np.array([0], np.int32))
+    pts = np.array([[0.0, 0.0, 0.0]])
+    g, o = both(p, sc, normals=nrm, sample_points=pts)
+    g.detect(); o.detect()
+    gh, oh = g.hypotheses(), o.hypotheses()
+    assert hyp_int_fields_equal(gh, oh) is None
+    assert np.array_equal(g.sweep_records()["fingers"], o.sweep_records()["fingers"])
+
+
+def test_errors_and_empty():
+    p = make_params()
+    g = capi.Context(p)
+    with pytest.raises(capi.Ag2Error) as e:
+        g.detect()
+    assert e.value.code == capi.AG2_E_EMPTY_CLOUD
+    g.set_cloud(np.zeros((10, 3), np.float32) + np.arange(10, dtype=np.float32)[:, None] * 0.001)
+    with pytest.raises(capi.Ag2Error) as e:
+        g.detect()
+    assert e.value.code == capi.AG2_E_NO_SAMPLES
+    g.set_sample_indices(np.array([0, 5], np.int32))
+    g.detect()
+    assert g.num(capi.LIST_HYPOTHESES) >= 0
