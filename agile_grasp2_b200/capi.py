@@ -347,6 +347,11 @@ class Context:
         if not self.is_oracle:
             self._call("synchronize")
 
+    def stream(self) -> int:
+        h = C.c_void_p()
+        self._call("get_stream", C.byref(h))
+        return int(h.value or 0)
+
     # -- outputs
     def num(self, which: int) -> int:
         n = C.c_size_t()

@@ -213,6 +213,12 @@ int ag2_synchronize(ag2_ctx* c) {
   return AG2_OK;
 }
 
+int ag2_get_stream(ag2_ctx* c, void** stream) {
+  if (!c || !stream) return AG2_E_INVALID;
+  *stream = (void*)c->stream;
+  return AG2_OK;
+}
+
 // ---- weights
 
 int ag2_set_lenet_weights(ag2_ctx* c, const float* c1w, const float* c1b, const float* c2w, const float* c2b,

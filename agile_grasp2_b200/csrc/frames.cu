@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(kFrameThreads)
 k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
          const double* __restrict__ sxyz, uint32_t S, const uint32_t* __restrict__ kt, uint32_t cap,
          float r2, float rq, int num_cams, uint64_t seed, int64_t id_offset, double cam0x, double cam0y,
-         double cam0z, double cam1x, double cam1y, double cam1z, ag2_frame* __restrict__ out) {
+         double cam0z, double cam1x, double cam1y, double cam1z, ag2_frame* __restrict__ out, uint32_t* __restrict__ num_valid) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* keys = (uint64_t*)smem;
   uint32_t* vals = (uint32_t*)(keys + cap);
@@ -254,6 +254,7 @@ k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict_
   f.valid = 1;
   f.majority_cam = majority;
   out[s] = f;
+  atomicAdd(num_valid, 1u);
 }
 
 }  // namespace
@@ -267,7 +268,7 @@ int frames_compute(ag2_ctx* c) {
   AG2_CUDA(c, c->kt.reserve(S));
   const int32_t* sidx = c->use_points ? nullptr : c->sample_idx.p;
   const double* sxyz = c->use_points ? c->sample_xyz.p : nullptr;
-  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 12, 0, 4, st));
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 12, 0, 8, st));  // [12] max k_t, [13] valid frames
   k_count_sample_neighbors<<<(S * 32 + 127) / 128, 128, 0, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->hc.r2_taubin,
                                                                 c->hc.rq_taubin, c->kt.p, c->scalars.p + 12);
   AG2_LAUNCH_CHECK(c);
@@ -286,7 +287,7 @@ int frames_compute(ag2_ctx* c) {
   k_frames<<<S, kFrameThreads, smem, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->kt.p, cap, h.r2_taubin, h.rq_taubin,
                                            c->num_cams, h.rng_seed, c->sample_id_offset, h.cam_origin[0][0],
                                            h.cam_origin[0][1], h.cam_origin[0][2], h.cam_origin[1][0],
-                                           h.cam_origin[1][1], h.cam_origin[1][2], c->frames.p);
+                                           h.cam_origin[1][1], h.cam_origin[1][2], c->frames.p, c->scalars.p + 13);
   AG2_LAUNCH_CHECK(c);
   phase_end(c, 2);
   return AG2_OK;

@@ -493,8 +493,9 @@ int hands_compute(ag2_ctx* c) {
     A.stat = (unsigned long long*)(c->scalars.p + 24);
     k_hands<<<S, kHandThreads, smem, st>>>(A, c->hc);
     AG2_LAUNCH_CHECK(c);
-    uint32_t res[12];
+    uint32_t res[12], nvalid = 0;
     AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 20, sizeof(res), cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaMemcpyAsync(&nvalid, c->scalars.p + 13, 4, cudaMemcpyDeviceToHost, st));
     AG2_CUDA(c, cudaStreamSynchronize(st));
     unsigned long long stat[3];
     memcpy(stat, &res[4], sizeof(stat));
@@ -504,6 +505,7 @@ int hands_compute(ag2_ctx* c) {
       continue;
     }
     c->max_in_box = res[2];
+    c->st.num_frames = (int64_t)nvalid;
     c->st.sum_neighbors_hands = (int64_t)stat[0];
     c->st.sum_cropped = (int64_t)stat[1];
     c->st.sum_in_box = (int64_t)stat[2];

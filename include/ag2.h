@@ -233,6 +233,8 @@ int ag2_select(ag2_ctx* ctx);
 /* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) without clustering. */
 int ag2_detect(ag2_ctx* ctx);
 int ag2_synchronize(ag2_ctx* ctx);
+/* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing. */
+int ag2_get_stream(ag2_ctx* ctx, void** stream);
 
 /* ---- outputs ------------------------------------------------------------- */
 
