@@ -244,9 +244,11 @@ def make_scene(config: str, num_samples: int | None = None, seed: int | None = N
     raise ValueError(config)
 
 
-def plates_scene(gap=0.05, extent=0.06, spacing=0.002, thickness_pts=1):
+def plates_scene(gap=0.05, extent=0.04, spacing=0.002, thickness_pts=1):
     """Known-answer scene: two parallel plates `gap` apart, normals along +-x of a hand
-    frame aligned with the world axes.  Returns xyz, normals (pointing outward)."""
+    frame aligned with the world axes.  Returns xyz, normals (pointing outward).  The plates
+    are shorter than the hand depth so the hand base clears them; sample ON a plate
+    (e.g. [-gap/2, 0, 0]) so the local frame has neighbours."""
     g = np.arange(-extent, extent + 1e-9, spacing)
     yy, zz = np.meshgrid(g, g)
     n = yy.size

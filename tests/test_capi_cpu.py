@@ -1,0 +1,69 @@
+"""CPU tests of the drop-in boundary: libag2.so loads, exports every symbol include/ag2.h
+declares, its PODs have the documented sizes, and it refuses to run without a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from agile_grasp2_b200 import capi
+from oracle import binding as ob
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "ag2.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ag2_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = capi.load().lib
+    syms = declared_symbols()
+    assert len(syms) >= 30
+    missing = [s for s in syms if not hasattr(lib, s)]
+    assert not missing, missing
+
+
+def test_oracle_mirrors_the_stage_api():
+    lib = ob.load().lib
+    for s in ("create", "destroy", "set_cloud", "set_sample_indices", "set_sample_points", "compute_normals",
+              "generate_hypotheses", "prune", "render_images", "classify", "select", "detect", "get_hypotheses"):
+        assert hasattr(lib, "ag2o_" + s)
+
+
+def test_pod_sizes_and_abi_version():
+    assert capi.HYPOTHESIS_DTYPE.itemsize == 192 and capi.SWEEP_DTYPE.itemsize == 16 and capi.FRAME_DTYPE.itemsize == 112
+    assert C.sizeof(capi.Params) == 432
+    lib = capi.load().lib
+    assert lib.ag2_abi_version() == 1
+    lib.ag2_strerror.restype = C.c_char_p
+    assert b"no CPU fallback" in lib.ag2_strerror(capi.AG2_E_NO_DEVICE)
+
+
+def test_default_params_match_reference_defaults():
+    p, q = capi.default_params(), ob.reference_default_params()
+    for f, _ in capi.Params._fields_:
+        a, b = getattr(p, f), getattr(q, f)
+        if hasattr(a, "__len__"):
+            assert np.allclose(list(a), list(b), rtol=0, atol=1e-15), f
+        else:
+            assert a == b, f
+    assert p.init_bite == 0.015 and p.min_score_diff == 500.0 and p.antipodal_mode == 1  # grasp_detector.cpp:43,49,53
+
+
+def test_invalid_params_rejected():
+    p = capi.default_params()
+    p.num_orientations = 0
+    with pytest.raises(capi.Ag2Error) as e:
+        capi.Context(p)
+    assert e.value.code in (capi.AG2_E_INVALID, capi.AG2_E_NO_DEVICE)
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="GPU present")
+def test_no_cpu_fallback():
+    with pytest.raises(capi.Ag2Error) as e:
+        capi.Context(capi.default_params())
+    assert e.value.code == capi.AG2_E_NO_DEVICE

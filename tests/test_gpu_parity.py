@@ -163,7 +163,7 @@ def test_sample_points_and_precomputed_normals(tiny_scene):
 
 def test_plates_known_answer():
     xyz, nrm = scenes.plates_scene(gap=0.05)
-    p = make_params(capi.MODE_GEOMETRIC, prune=0)
+    p = make_params(capi.MODE_GEOMETRIC, prune=0, nn_radius_taubin=0.03)
     sc = dict(xyz=xyz, cam_mask=np.ones(len(xyz), np.uint8), num_cams=1, samples=np.array([0], np.int32))
     pts = np.array([[0.0, 0.0, 0.0]])
     g, o = both(p, sc, normals=nrm, sample_points=pts)
@@ -171,6 +171,7 @@ def test_plates_known_answer():
     gh, oh = g.hypotheses(), o.hypotheses()
     assert hyp_int_fields_equal(gh, oh) is None
     assert np.array_equal(g.sweep_records()["fingers"], o.sweep_records()["fingers"])
+    assert np.any(gh["full_antipodal"] == 1) and np.allclose(gh[gh["full_antipodal"] == 1]["width"], 0.05, atol=1e-6)
 
 
 def test_errors_and_empty():
