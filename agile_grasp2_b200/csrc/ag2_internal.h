@@ -128,6 +128,7 @@ struct ag2_ctx {
   ag2::DevBuf<uint32_t> sorted_of_orig; // n
   ag2::DevBuf<uint32_t> scan_tmp;
   ag2::DevBuf<uint32_t> kn;             // neighbour counts (normals pass)
+  ag2::DevBuf<uint32_t> big_list[2];    // points whose neighbourhood exceeds a launch capacity (ping-pong)
   ag2::DevBuf<uint32_t> scalars;        // small device scratch (counters, maxima, flags)
 
   // samples
@@ -156,6 +157,8 @@ struct ag2_ctx {
   ag2::DevBuf<float> logits;                // pruned * 2
   ag2::DevBuf<double> scores;               // pruned
   ag2::DevBuf<float> act;                   // LeNet activations
+  ag2::DevBuf<uint64_t> sort_keys[2];       // top-k ranking scratch (select.cu)
+  ag2::DevBuf<uint32_t> sort_pos[2];
   uint32_t max_in_box = 0;
   bool have_hyps = false, have_pruned = false, have_images = false, have_antipodal = false,
        have_selected = false;

@@ -131,10 +131,12 @@ k_conv2_pool(const float* __restrict__ in /* [n][20][28][28] */, const float* __
   }
 }
 
-// ip1: H[n][500] = relu(X[n][7200] . W[500][7200]^T + b).  64x64 tile, BK 16, 4x4 per thread.
+// ip1, split-K: part[z][n][500] = X[n][k-range z] . W[500][k-range z]^T.  64x64 tile, BK 16,
+// 4x4 per thread.  The K = 7200 reduction is cut into gridDim.z ranges so that a few hundred
+// images still fill the machine; partials are summed in a fixed order by k_ip2 (deterministic).
 __global__ void __launch_bounds__(256)
-k_ip1_relu(const float* __restrict__ X, const float* __restrict__ W, const float* __restrict__ b,
-           float* __restrict__ H, int n) {
+k_ip1_partial(const float* __restrict__ X, const float* __restrict__ W, float* __restrict__ part, int n,
+              int steps_per_split) {
   constexpr int BM = 64, BN = 64, BK = 16, K = 7200;
   __shared__ float As[BK][BM + 4];
   __shared__ float Bs[BK][BN + 4];
@@ -147,7 +149,9 @@ k_ip1_relu(const float* __restrict__ X, const float* __restrict__ W, const float
 #pragma unroll
     for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
   const int lr = tid / 4, lc = (tid % 4) * 4;  // 64 rows x 16 k, one float4 per thread
-  for (int k0 = 0; k0 < K; k0 += BK) {
+  const int kbeg = blockIdx.z * steps_per_split * BK;
+  const int kend = min(K, kbeg + steps_per_split * BK);
+  for (int k0 = kbeg; k0 < kend; k0 += BK) {
     float4 av = make_float4(0, 0, 0, 0), bv = make_float4(0, 0, 0, 0);
     if (m0 + lr < n) av = *reinterpret_cast<const float4*>(&X[(size_t)(m0 + lr) * K + k0 + lc]);
     if (n0 + lr < IP1_OUT) bv = *reinterpret_cast<const float4*>(&W[(size_t)(n0 + lr) * K + k0 + lc]);
@@ -168,6 +172,7 @@ k_ip1_relu(const float* __restrict__ X, const float* __restrict__ W, const float
     }
     __syncthreads();
   }
+  float* P = part + (size_t)blockIdx.z * n * IP1_OUT;
 #pragma unroll
   for (int i = 0; i < 4; i++) {
     int m = m0 + ty * 4 + i;
@@ -175,19 +180,21 @@ k_ip1_relu(const float* __restrict__ X, const float* __restrict__ W, const float
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       int o = n0 + tx * 4 + j;
-      if (o < IP1_OUT) H[(size_t)m * IP1_OUT + o] = fmaxf(acc[i][j] + b[o], 0.f);
+      if (o < IP1_OUT) P[(size_t)m * IP1_OUT + o] = acc[i][j];
     }
   }
 }
 
-// ip2: logits[n][2]; one warp per image
-__global__ void k_ip2(const float* __restrict__ H, const float* __restrict__ W, const float* __restrict__ b,
-                      float* __restrict__ logits, int n) {
+// split-K reduction + ip1 bias + ReLU + ip2: logits[n][2]; one warp per image
+__global__ void k_ip2(const float* __restrict__ part, int splits, const float* __restrict__ b1,
+                      const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ logits, int n) {
   int img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (img >= n) return;
   float a0 = 0.f, a1 = 0.f;
   for (int k = lane; k < IP1_OUT; k += 32) {
-    float h = H[(size_t)img * IP1_OUT + k];
+    float h = 0.f;
+    for (int z = 0; z < splits; z++) h += part[((size_t)z * n + img) * IP1_OUT + k];
+    h = fmaxf(h + b1[k], 0.f);
     a0 += W[k] * h;
     a1 += W[IP1_OUT + k] * h;
   }
@@ -224,23 +231,30 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
   cudaStream_t st = c->stream;
   const LeNetDev& L = c->net;
   const size_t chunk_max = 4096;
-  const size_t per_img = (size_t)20 * P1 * P1 + (size_t)50 * P2 * P2 + IP1_OUT;
-  AG2_CUDA(c, c->act.reserve(std::min(n, chunk_max) * per_img));
+  const size_t chunk = std::min(n, chunk_max);
+  const int mtiles = (int)((chunk + 63) / 64), ntiles = (IP1_OUT + 63) / 64;
+  // split K so that ip1 launches >= ~2 CTAs per SM (450 k-steps of 16 in total)
+  int splits = std::max(1, std::min(30, (2 * c->sm_count + mtiles * ntiles - 1) / (mtiles * ntiles)));
+  const int steps_per_split = (450 + splits - 1) / splits;
+  splits = (450 + steps_per_split - 1) / steps_per_split;
+  const size_t per_img = (size_t)20 * P1 * P1 + (size_t)50 * P2 * P2 + (size_t)splits * IP1_OUT;
+  AG2_CUDA(c, c->act.reserve(chunk * per_img));
   const size_t smem2 = (size_t)(20 * 28 * 29 + 10 * 500) * sizeof(float);
   AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_pool, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
   for (size_t off = 0; off < n; off += chunk_max) {
     const size_t m = std::min(chunk_max, n - off);
     float* a1 = c->act.p;
     float* a2 = a1 + m * 20 * P1 * P1;
-    float* hh = a2 + m * 50 * P2 * P2;
+    float* part = a2 + m * 50 * P2 * P2;
     k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p, a1);
     AG2_LAUNCH_CHECK(c);
     k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
     AG2_LAUNCH_CHECK(c);
-    dim3 g1((unsigned)((m + 63) / 64), (IP1_OUT + 63) / 64);
-    k_ip1_relu<<<g1, 256, 0, st>>>(a2, L.i1w.p, L.i1b.p, hh, (int)m);
+    dim3 g1((unsigned)((m + 63) / 64), ntiles, splits);
+    k_ip1_partial<<<g1, 256, 0, st>>>(a2, L.i1w.p, part, (int)m, steps_per_split);
     AG2_LAUNCH_CHECK(c);
-    k_ip2<<<(unsigned)((m * 32 + 255) / 256), 256, 0, st>>>(hh, L.i2w.p, L.i2b.p, d_logits + 2 * off, (int)m);
+    k_ip2<<<(unsigned)((m * 32 + 255) / 256), 256, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p,
+                                                            d_logits + 2 * off, (int)m);
     AG2_LAUNCH_CHECK(c);
   }
   return AG2_OK;

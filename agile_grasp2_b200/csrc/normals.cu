@@ -20,8 +20,12 @@ namespace ag2 {
 namespace {
 
 // thread per point: number of neighbours within the radius (sizes the sort buffers)
+constexpr int kTiers = 8;
+__constant__ uint32_t c_tier[kTiers] = {64, 96, 128, 192, 256, 384, 512, 1024};
+
 __global__ void k_count_neighbors(GridDev g, float r2, float rq, uint32_t* __restrict__ kn,
-                                  uint32_t* __restrict__ max_out, unsigned long long* __restrict__ sum_out) {
+                                  uint32_t* __restrict__ max_out, unsigned long long* __restrict__ sum_out,
+                                  uint32_t* __restrict__ tier_hist /* [kTiers]: points with kn > tier */) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t cnt = 0;
   if (i < (uint32_t)g.n) {
@@ -48,6 +52,11 @@ __global__ void k_count_neighbors(GridDev g, float r2, float rq, uint32_t* __res
   if ((threadIdx.x & 31) == 0) {
     atomicMax(max_out, m);
     atomicAdd(sum_out, s);
+  }
+#pragma unroll
+  for (int k = 0; k < kTiers; k++) {
+    uint32_t over = __popc(__ballot_sync(AG2_FULL, cnt > c_tier[k]));
+    if ((threadIdx.x & 31) == 0 && over) atomicAdd(&tier_hist[k], over);
   }
 }
 
@@ -162,99 +171,279 @@ __device__ void solve_normal(const float a[9], float px, float py, float pz, flo
   }
 }
 
-// One warp per point.  smem per warp: cap * (8 + 4) bytes.
-__global__ void k_normals(GridDev g, float r2, float rq, const uint32_t* __restrict__ kn,
-                          const uint32_t* __restrict__ list, uint32_t n_items, uint32_t cap,
-                          float4* __restrict__ nrm_out) {
+// ---------------------------------------------------------------------------
+// k_normals.  A warp owns `bsz` (<= 32) points at a time, taken from a global counter.
+// Per point (warp cooperative):
+//   gather   the candidate spans of the <=16 cell rows are flattened into one
+//            sequence (prefix over rows by shuffles), each lane tests one candidate
+//            per iteration and hits are ballot-compacted into A = (d2 bits, j);
+//   order    exact ascending (d2, id) WITHOUT a comparison sort: hits are grouped
+//            into kNB monotone d2 buckets (shared atomics + warp prefix), and the
+//            rank of an element is bucket start + #smaller (d2, id) inside its
+//            bucket (a handful of compares; ids are fetched only on equal d2), then
+//            its coordinates are written at `rank` of the staging array S;
+//   moments  lanes 0..8 run the nine single-pass float accumulators of
+//            computeMeanAndCovarianceMatrix over S in that order (sequential by
+//            definition).
+// Per bsz points: one thread per point solves eigen33 + viewpoint flip.
+// Shared memory per warp is 20 B x cap + 2.7 KB, so the launch capacity decides the
+// occupancy: the host runs the bulk of the points at a small cap and hands the dense
+// ones (appended to big_list here) to further launches with larger caps.
+constexpr int kNB = 128;     // d2 buckets (4 per lane in the prefix)
+constexpr int kMomStride = 11;
+
+struct NormalsSmem {  // per-warp carve-up (byte offsets, 16-aligned)
+  size_t a, s, cnt, start, rowb, rowp, mom, total;
+};
+__host__ __device__ inline NormalsSmem normals_smem(uint32_t cap) {
+  NormalsSmem L;
+  size_t o = 0;
+  L.a = o, o += (size_t)cap * 8;    // A: (d2 bits, j); later (rank, j)
+  L.s = o, o += (size_t)cap * 12;   // G: grouped (d2 bits, j) 8 B; later S: xyz 12 B
+  L.cnt = o, o += kNB * 4;
+  L.start = o, o += (kNB + 4) * 4;
+  L.rowb = o, o += 32 * 4;
+  L.rowp = o, o += 36 * 4;
+  L.mom = o, o += 32 * kMomStride * 4;
+  L.total = (o + 15) & ~(size_t)15;
+  return L;
+}
+
+__device__ __forceinline__ int d2_bucket(float d2, float bscale) {
+  return min(kNB - 1, (int)__fmul_rn(d2, bscale));  // monotone non-decreasing in d2
+}
+
+struct NormalsArgs {
+  GridDev g;
+  float r2, rq, bscale;
+  const uint32_t* kn;
+  uint32_t n_items, cap, bsz;
+  const uint32_t* list;       // nullptr: items are the cell-sorted points 0..n_items-1
+  uint32_t* big_list;         // out: items whose neighbourhood exceeds cap
+  uint32_t* big_count;
+  uint32_t big_cap;
+  uint32_t* batch_counter;    // dynamic batch scheduling
+  float4* nrm_out;
+};
+
+__global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   extern __shared__ __align__(16) unsigned char smem[];
-  const int warps = blockDim.x >> 5;
+  const GridDev& g = P.g;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint64_t* keys = (uint64_t*)smem + (size_t)warp * cap;
-  uint32_t* vals = (uint32_t*)((uint64_t*)smem + (size_t)warps * cap) + (size_t)warp * cap;
-  for (uint32_t item = blockIdx.x * warps + warp; item < n_items; item += gridDim.x * warps) {
-    uint32_t i = list ? list[item] : item;
-    float4 q = g.pts[i];
-    uint32_t count = kn[i];
-    float4 old = nrm_out[i];
-    if (count < 3) {  // computePointNormal: fewer than 3 neighbours -> NaN
-      if (lane == 0) {
-        float nanv = __int_as_float(0x7fc00000);
-        nrm_out[i] = make_float4(nanv, nanv, nanv, old.w);
-      }
-      continue;
+  const uint32_t cap = P.cap, bsz = P.bsz;
+  const NormalsSmem L = normals_smem(cap);
+  unsigned char* base = smem + (size_t)warp * L.total;
+  uint2* A = (uint2*)(base + L.a);
+  uint2* G = (uint2*)(base + L.s);
+  float* S = (float*)(base + L.s);
+  uint32_t* cnt = (uint32_t*)(base + L.cnt);
+  uint32_t* start = (uint32_t*)(base + L.start);
+  uint32_t* rowb = (uint32_t*)(base + L.rowb);
+  uint32_t* rowp = (uint32_t*)(base + L.rowp);
+  float* mom = (float*)(base + L.mom);
+  const uint32_t n_batches = (P.n_items + bsz - 1) / bsz;
+  // accumulator role of lanes 0..8: operand selectors 0 = x, 1 = y, 2 = z, 3 = constant 1
+  const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
+  const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
+  __shared__ float one_s;
+  if (threadIdx.x == 0) one_s = 1.0f;
+  __syncthreads();
+
+  for (;;) {
+    uint32_t batch = 0;
+    if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
+    batch = __shfl_sync(AG2_FULL, batch, 0);
+    if (batch >= n_batches) break;
+    const uint32_t i0 = batch * bsz;
+    const uint32_t nb = min(bsz, P.n_items - i0);
+    const uint32_t my_i = lane < nb ? (P.list ? P.list[i0 + lane] : i0 + lane) : 0u;
+    const uint32_t my_count = lane < nb ? P.kn[my_i] : 0u;
+    const bool too_big = my_count > cap;
+    if (too_big) {
+      uint32_t slot = atomicAdd(P.big_count, 1u);
+      if (slot < P.big_cap) P.big_list[slot] = my_i;
     }
-    uint32_t n_pad = next_pow2(count);
-    // 1. gather (ordered append per warp)
-    QueryWindow w = make_window(g, q.x, q.y, q.z, rq);
-    int rows = w.rows();
-    uint32_t filled = 0;
-    for (int row = 0; row < rows; row++) {
-      uint32_t b, e;
-      row_span(g, w, row, b, e);
-      for (uint32_t base = b; base < e; base += 32) {
-        uint32_t j = base + lane;
-        bool hit = false;
-        float d2 = 0.f;
-        float4 p = make_float4(0, 0, 0, 0);
-        if (j < e) {
-          p = g.pts[j];
-          d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
-          hit = d2 < r2;
-        }
-        uint32_t ballot = __ballot_sync(AG2_FULL, hit);
-        if (hit) {
-          uint32_t slot = filled + __popc(ballot & ((1u << lane) - 1));
-          keys[slot] = nn_key(d2, __float_as_uint(p.w));
-          vals[slot] = j;
-        }
-        filled += __popc(ballot);
-      }
-    }
-    for (uint32_t t = filled + lane; t < n_pad; t += 32) {
-      keys[t] = ~0ull;
-      vals[t] = 0;
-    }
-    __syncwarp();
-    // 2. sort by (d2, id)
-    bitonic_sort_kv(keys, vals, n_pad, (uint32_t)lane, 32u, WarpSync());
-    // 3. replace each entry by its coordinates (entry-local, no aliasing)
-    for (uint32_t t = lane; t < count; t += 32) {
-      float4 p = g.pts[vals[t]];
-      float2 xy = make_float2(p.x, p.y);
-      *reinterpret_cast<float2*>(&keys[t]) = xy;
-      vals[t] = __float_as_uint(p.z);
-    }
-    __syncwarp();
-    // sequential single-pass float moments (computeMeanAndCovarianceMatrix)
-    float acc = 0.f;
-    if (lane < 9) {
-      // operand selectors: 0 = x, 1 = y, 2 = z, 3 = constant 1
-      const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
-      const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
-      for (uint32_t t = 0; t < count; t++) {
-        float2 xy = *reinterpret_cast<const float2*>(&keys[t]);
-        float z = __uint_as_float(vals[t]);
-        float va = sa == 0 ? xy.x : (sa == 1 ? xy.y : z);
-        float vb = sb == 0 ? xy.x : (sb == 1 ? xy.y : (sb == 2 ? z : 1.0f));
-        // accu[6..8] += p.x : multiplying by 1.0f is exact
-        acc = __fadd_rn(acc, __fmul_rn(va, vb));
-      }
-    }
-    float a[9];
+    for (uint32_t k = 0; k < nb; k++) {
+      const uint32_t i = __shfl_sync(AG2_FULL, my_i, (int)k);
+      const uint32_t count = __shfl_sync(AG2_FULL, my_count, (int)k);
+      if (count < 3 || count > cap) continue;  // NaN normal (solve pass) / a later launch
+      const float4 q = g.pts[i];
+      // ---- gather
+      QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
+      const int rows = w.rows();  // <= 16 whenever the cell size is >= normals_radius
 #pragma unroll
-    for (int k = 0; k < 9; k++) a[k] = __shfl_sync(AG2_FULL, acc, k);
-    if (lane == 0) {
-      float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
-      for (int k = 0; k < 9; k++) a[k] *= inv;
-      float n[3];
-      solve_normal(a, q.x, q.y, q.z, n);
-      nrm_out[i] = make_float4(n[0], n[1], n[2], old.w);
+      for (int b = 0; b < kNB / 32; b++) cnt[lane + 32 * b] = 0;
+      uint32_t filled = 0;
+      for (int r0 = 0; r0 < rows; r0 += 32) {
+        uint32_t rb = 0, rc = 0;
+        if (r0 + lane < rows) {
+          uint32_t b, e;
+          row_span(g, w, r0 + lane, b, e);
+          rb = b, rc = e - b;
+        }
+        uint32_t incl = rc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          uint32_t t = __shfl_up_sync(AG2_FULL, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const uint32_t T = __shfl_sync(AG2_FULL, incl, 31);
+        __syncwarp();
+        rowb[lane] = rb;
+        rowp[lane] = incl - rc;
+        if (lane == 31) rowp[32] = T;
+        __syncwarp();
+        int row = 0;
+        uint32_t row_lo = 0, row_hi = rowp[1], row_b = rowb[0];
+        for (uint32_t t0 = 0; t0 < T; t0 += 32) {
+          const uint32_t t = t0 + lane;
+          bool hit = false;
+          float d2 = 0.f;
+          uint32_t j = 0;
+          if (t < T) {
+            while (t >= row_hi) {
+              row++;
+              row_lo = row_hi;
+              row_hi = rowp[row + 1];
+              row_b = rowb[row];
+            }
+            j = row_b + (t - row_lo);
+            float4 p = g.pts[j];
+            d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
+            hit = d2 < P.r2;
+          }
+          const uint32_t ballot = __ballot_sync(AG2_FULL, hit);
+          if (hit) {
+            A[filled + __popc(ballot & ((1u << lane) - 1))] = make_uint2(__float_as_uint(d2), j);
+            atomicAdd(&cnt[d2_bucket(d2, P.bscale)], 1u);
+          }
+          filled += __popc(ballot);
+        }
+      }
+      __syncwarp();
+      // ---- bucket starts: exclusive prefix over kNB counters, kNB/32 consecutive ones per lane
+      {
+        constexpr int per = kNB / 32;
+        uint32_t cl[per], s = 0;
+#pragma unroll
+        for (int b = 0; b < per; b++) {
+          cl[b] = cnt[per * lane + b];
+          s += cl[b];
+        }
+        uint32_t in2 = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          uint32_t t = __shfl_up_sync(AG2_FULL, in2, o);
+          if (lane >= o) in2 += t;
+        }
+        uint32_t ex = in2 - s;
+#pragma unroll
+        for (int b = 0; b < per; b++) {
+          start[per * lane + b] = ex;
+          cnt[per * lane + b] = ex;  // cursor
+          ex += cl[b];
+        }
+        if (lane == 31) start[kNB] = in2;
+      }
+      __syncwarp();
+      // ---- group by bucket
+      for (uint32_t t = lane; t < count; t += 32) {
+        uint2 e = A[t];
+        G[atomicAdd(&cnt[d2_bucket(__uint_as_float(e.x), P.bscale)], 1u)] = e;
+      }
+      __syncwarp();
+      // ---- exact rank inside the bucket by (d2, input index); (rank, j) parked in A
+      for (uint32_t t = lane; t < count; t += 32) {
+        const uint2 e = G[t];
+        const int b = d2_bucket(__uint_as_float(e.x), P.bscale);
+        const uint32_t lo = start[b], hi = start[b + 1];
+        uint32_t rank = lo;
+        for (uint32_t u = lo; u < hi; u++) {
+          const uint2 o = G[u];
+          if (o.x < e.x) {
+            rank++;
+          } else if (o.x == e.x && u != t) {  // equal distances: FLANN orders by index
+            if (__float_as_uint(g.pts[o.y].w) < __float_as_uint(g.pts[e.y].w)) rank++;
+          }
+        }
+        A[t] = make_uint2(rank, e.y);
+      }
+      __syncwarp();
+      for (uint32_t t = lane; t < count; t += 32) {
+        const uint2 rj = A[t];
+        const float4 p = g.pts[rj.y];
+        S[3 * rj.x] = p.x;
+        S[3 * rj.x + 1] = p.y;
+        S[3 * rj.x + 2] = p.z;
+      }
+      __syncwarp();
+      // ---- sequential single-pass float moments
+      if (lane < 9) {
+        const float* pa = S + sa;
+        // accu[6..8] += p.x : the second operand is the constant 1.0f, the product is exact
+        const float* pb = sb == 3 ? &one_s : S + sb;
+        const uint32_t stride_b = sb == 3 ? 0u : 3u;
+        float acc = 0.f;
+#pragma unroll 4
+        for (uint32_t t = 0; t < count; t++) acc = __fadd_rn(acc, __fmul_rn(pa[3 * t], pb[stride_b * t]));
+        mom[k * kMomStride + lane] = acc;
+      }
+      __syncwarp();
+    }
+    // ---- one thread per point: eigen33 + flip
+    if (lane < nb && !too_big) {
+      const float4 old = P.nrm_out[my_i];
+      if (my_count < 3) {  // computePointNormal: fewer than 3 neighbours -> NaN
+        float nanv = __int_as_float(0x7fc00000);
+        P.nrm_out[my_i] = make_float4(nanv, nanv, nanv, old.w);
+      } else {
+        const float4 q = g.pts[my_i];
+        float a[9];
+        const float inv = 1.0f / (float)my_count;  // Eigen 3.2 operator/=: multiply by the reciprocal
+#pragma unroll
+        for (int k = 0; k < 9; k++) a[k] = mom[lane * kMomStride + k] * inv;
+        float n[3];
+        solve_normal(a, q.x, q.y, q.z, n);
+        P.nrm_out[my_i] = make_float4(n[0], n[1], n[2], old.w);
+      }
     }
     __syncwarp();
   }
 }
 
 }  // namespace
+
+// One launch over `n_items` items (all points, or a list) at capacity `cap`.
+static int launch_normals(ag2_ctx* c, uint32_t n_items, uint32_t cap, const uint32_t* list, uint32_t* big_list,
+                          uint32_t* big_count, uint32_t big_cap, uint32_t* batch_counter) {
+  cudaStream_t st = c->stream;
+  const NormalsSmem L = normals_smem(cap);
+  const int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (110 * 1024) / L.total));
+  const size_t smem = L.total * warps;
+  AG2_CUDA(c, cudaFuncSetAttribute(k_normals, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int blocks_per_sm = (int)std::max<size_t>(1, std::min<size_t>(64 / warps, (226 * 1024) / (smem + 1024)));
+  const uint32_t resident_warps = (uint32_t)(c->sm_count * blocks_per_sm * warps);
+  // batch size: 32 points per warp when there is plenty of work, fewer when a short list of
+  // dense points must still be spread over the whole machine
+  uint32_t bsz = 32;
+  while (bsz > 1 && (n_items + bsz - 1) / bsz < 4 * resident_warps) bsz >>= 1;
+  const uint32_t n_batches = (n_items + bsz - 1) / bsz;
+  const uint32_t grid = (uint32_t)std::max<size_t>(
+      1, std::min<size_t>(((size_t)n_batches + warps - 1) / warps, (size_t)c->sm_count * blocks_per_sm));
+  NormalsArgs P;
+  P.g = grid_dev(c);
+  P.r2 = c->hc.r2_normals, P.rq = c->hc.rq_normals;
+  P.bscale = (float)kNB / c->hc.r2_normals;
+  P.kn = c->kn.p;
+  P.n_items = n_items, P.cap = cap, P.bsz = bsz;
+  P.list = list;
+  P.big_list = big_list, P.big_count = big_count, P.big_cap = big_cap;
+  P.batch_counter = batch_counter;
+  P.nrm_out = c->nrm.p;
+  k_normals<<<grid, warps * 32, smem, st>>>(P);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
 
 int normals_compute(ag2_ctx* c) {
   AG2_TRY(grid_build(c));
@@ -264,34 +453,48 @@ int normals_compute(ag2_ctx* c) {
   GridDev g = grid_dev(c);
   const uint32_t n = (uint32_t)c->n_finite;
   AG2_CUDA(c, c->kn.reserve(n));
-  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));    // [8] max, [10..11] sum
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 32, 0, 32 * 4, st));  // [32..39] tiers, [40..47] list counts, [48..55] batch counters
   k_count_neighbors<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p,
                                                       c->scalars.p + 8,
-                                                      (unsigned long long*)(c->scalars.p + 10));
+                                                      (unsigned long long*)(c->scalars.p + 10), c->scalars.p + 32);
   AG2_LAUNCH_CHECK(c);
-  uint32_t res[4];
+  uint32_t res[4], hist[kTiers];
   AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaMemcpyAsync(hist, c->scalars.p + 32, sizeof(hist), cudaMemcpyDeviceToHost, st));
   AG2_CUDA(c, cudaStreamSynchronize(st));
-  uint32_t max_kn = res[0];
+  const uint32_t max_kn = res[0];
   unsigned long long sum;
   memcpy(&sum, &res[2], 8);
   c->st.sum_neighbors_normals = (int64_t)sum;
-  uint32_t cap = 32;
-  while (cap < max_kn) cap <<= 1;
-  size_t per_warp = (size_t)cap * 12;
-  if (per_warp > 200 * 1024) {
-    c->err = "normals: a point has more than 16384 neighbours within normals_radius";
+  const uint32_t cap_max = (std::max(max_kn, 32u) + 31u) & ~31u;
+  if (normals_smem(cap_max).total > 220 * 1024) {
+    c->err = "normals: a point has more than ~11000 neighbours within normals_radius";
     return AG2_E_CAPACITY;
   }
-  int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (96 * 1024) / per_warp));
-  size_t smem = per_warp * warps;
-  AG2_CUDA(c, cudaFuncSetAttribute(k_normals, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int blocks_per_sm = (int)std::max<size_t>(1, std::min<size_t>(16, (200 * 1024) / smem));
-  uint32_t grid = (uint32_t)std::min<size_t>(((size_t)n + warps - 1) / warps,
-                                             (size_t)c->sm_count * blocks_per_sm);
-  k_normals<<<grid, warps * 32, smem, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, nullptr, n, cap,
-                                            c->nrm.p);
-  AG2_LAUNCH_CHECK(c);
+  // Capacity levels: each launch runs at the smallest tier that leaves at most ~12 % of its
+  // items for the next one; hist[] gives the exact size of every leftover list.
+  static const uint32_t tiers[kTiers] = {64, 96, 128, 192, 256, 384, 512, 1024};
+  uint32_t remaining = n, level = 0;
+  const uint32_t* list = nullptr;
+  int tier = 0;
+  while (remaining > 0 && level < 8) {
+    uint32_t cap = cap_max, left = 0;
+    for (; tier < kTiers; tier++)
+      if (tiers[tier] < cap_max && hist[tier] <= remaining / 8) {
+        cap = tiers[tier];
+        left = hist[tier];
+        tier++;
+        break;
+      }
+    DevBuf<uint32_t>& out = c->big_list[level & 1];
+    if (left) AG2_CUDA(c, out.reserve(left));
+    AG2_TRY(launch_normals(c, remaining, cap, list, out.p, c->scalars.p + 40 + level, left,
+                           c->scalars.p + 48 + level));
+    list = out.p;
+    remaining = left;
+    level++;
+  }
   c->have_normals = true;
   phase_end(c, 1);
   return AG2_OK;

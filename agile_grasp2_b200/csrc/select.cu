@@ -111,6 +111,81 @@ __global__ void k_score_keys(const uint32_t* __restrict__ list, size_t n, const 
   keys[i] = ~u;
 }
 
+
+// ---- ranking by (key asc, position asc): key = complemented order-preserving code of the
+// score, so ascending key == descending score; equal scores keep list order (D4).
+__device__ __forceinline__ bool kv_greater(uint64_t ka, uint32_t va, uint64_t kb, uint32_t vb) {
+  return ka > kb || (ka == kb && va > vb);
+}
+
+constexpr int kSortTile = 4096;  // (8 + 4) B * 4096 = 48 KB of shared memory
+
+// Sorts one tile of (key, pos) pairs in shared memory and writes its first `keep` pairs.
+__global__ void __launch_bounds__(256)
+k_sort_tile(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ pos_in, uint32_t n, uint32_t keep,
+            uint64_t* __restrict__ keys_out, uint32_t* __restrict__ pos_out) {
+  __shared__ uint64_t k_s[kSortTile];
+  __shared__ uint32_t v_s[kSortTile];
+  const uint32_t base = blockIdx.x * kSortTile;
+  const uint32_t cnt = min((uint32_t)kSortTile, n - base);
+  uint32_t n_pad = 2;
+  while (n_pad < cnt) n_pad <<= 1;
+  for (uint32_t t = threadIdx.x; t < n_pad; t += blockDim.x) {
+    k_s[t] = t < cnt ? keys_in[base + t] : ~0ull;
+    v_s[t] = t < cnt ? (pos_in ? pos_in[base + t] : base + t) : 0xFFFFFFFFu;
+  }
+  __syncthreads();
+  for (uint32_t k = 2; k <= n_pad; k <<= 1)
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t t = threadIdx.x; t < (n_pad >> 1); t += blockDim.x) {
+        uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+        bool up = ((i & k) == 0);
+        uint64_t ka = k_s[i], kb = k_s[l];
+        uint32_t va = v_s[i], vb = v_s[l];
+        if (kv_greater(ka, va, kb, vb) == up) {
+          k_s[i] = kb, k_s[l] = ka;
+          v_s[i] = vb, v_s[l] = va;
+        }
+      }
+      __syncthreads();
+    }
+  const uint32_t m = min(keep, cnt);
+  const uint32_t obase = blockIdx.x * keep;  // full tiles precede the ragged one
+  for (uint32_t t = threadIdx.x; t < m; t += blockDim.x) {
+    keys_out[obase + t] = k_s[t];
+    pos_out[obase + t] = v_s[t];
+  }
+}
+
+// One compare-exchange step of a global-memory bitonic sort (lists larger than a tile that
+// must be sorted completely).
+__global__ void k_bitonic_step(uint64_t* __restrict__ keys, uint32_t* __restrict__ pos, uint32_t n_pad, uint32_t k,
+                               uint32_t j) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (n_pad >> 1)) return;
+  uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+  bool up = ((i & k) == 0);
+  uint64_t ka = keys[i], kb = keys[l];
+  uint32_t va = pos[i], vb = pos[l];
+  if (kv_greater(ka, va, kb, vb) == up) {
+    keys[i] = kb, keys[l] = ka;
+    pos[i] = vb, pos[l] = va;
+  }
+}
+
+__global__ void k_pad_keys(uint64_t* __restrict__ keys, uint32_t* __restrict__ pos, uint32_t n, uint32_t n_pad) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_pad) return;
+  if (t >= n) keys[t] = ~0ull;
+  pos[t] = t < n ? t : 0xFFFFFFFFu;
+}
+
+__global__ void k_take_ranked(const uint32_t* __restrict__ pos, uint32_t k, const uint32_t* __restrict__ list,
+                              uint32_t* __restrict__ out) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < k) out[t] = list[pos[t]];
+}
+
 }  // namespace
 
 // flags (n entries, 0/1) -> compacted `out`, returns count (one small D2H sync)
@@ -195,25 +270,49 @@ int select_top(ag2_ctx* c) {
                                        cudaMemcpyDeviceToDevice, st));
     c->list_n[AG2_LIST_SELECTED] = n;
   } else {
-    // rank by (score desc, list position asc).  O(n) keys cross PCIe; n is the
-    // number of ANTIPODAL grasps (small next to S*R).
-    DevBuf<uint64_t> keys;
-    AG2_CUDA(c, keys.reserve(n));
-    k_score_keys<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->list[AG2_LIST_ANTIPODAL].p, n, c->slots.p, keys.p);
+    // rank by (score desc, list position asc) on the device
+    const size_t k = (c->p.num_selected > 0 && (size_t)c->p.num_selected < n) ? (size_t)c->p.num_selected : n;
+    uint32_t n_pad = 2;
+    while (n_pad < n) n_pad <<= 1;
+    AG2_CUDA(c, c->sort_keys[0].reserve(n_pad));
+    AG2_CUDA(c, c->sort_keys[1].reserve(n_pad));
+    AG2_CUDA(c, c->sort_pos[0].reserve(n_pad));
+    AG2_CUDA(c, c->sort_pos[1].reserve(n_pad));
+    k_score_keys<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->list[AG2_LIST_ANTIPODAL].p, n, c->slots.p,
+                                                             c->sort_keys[0].p);
     AG2_LAUNCH_CHECK(c);
-    std::vector<uint64_t> hk(n);
-    std::vector<uint32_t> hl(n), order(n);
-    AG2_CUDA(c, cudaMemcpyAsync(hk.data(), keys.p, n * 8, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaMemcpyAsync(hl.data(), c->list[AG2_LIST_ANTIPODAL].p, n * 4, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
-    for (size_t i = 0; i < n; i++) order[i] = (uint32_t)i;
-    size_t k = (c->p.num_selected > 0 && (size_t)c->p.num_selected < n) ? (size_t)c->p.num_selected : n;
-    auto cmp = [&hk](uint32_t a, uint32_t b) { return hk[a] < hk[b] || (hk[a] == hk[b] && a < b); };
-    std::partial_sort(order.begin(), order.begin() + k, order.end(), cmp);
-    std::vector<uint32_t> sel(k);
-    for (size_t i = 0; i < k; i++) sel[i] = hl[order[i]];
-    AG2_CUDA(c, cudaMemcpyAsync(c->list[AG2_LIST_SELECTED].p, sel.data(), k * 4, cudaMemcpyHostToDevice, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
+    const uint32_t* ranked = nullptr;
+    if (n <= (size_t)kSortTile || k <= (size_t)kSortTile / 2) {
+      // tournament of tile sorts: the global top-k is inside the union of the tiles' top-k
+      int cur = 0;
+      size_t m = n;
+      const uint32_t* pos_in = nullptr;
+      for (;;) {
+        const unsigned tiles = (unsigned)((m + kSortTile - 1) / kSortTile);
+        const uint32_t keep = tiles == 1 ? (uint32_t)std::min(m, k) : (uint32_t)k;
+        k_sort_tile<<<tiles, 256, 0, st>>>(c->sort_keys[cur].p, pos_in, (uint32_t)m, keep, c->sort_keys[cur ^ 1].p,
+                                           c->sort_pos[cur ^ 1].p);
+        AG2_LAUNCH_CHECK(c);
+        cur ^= 1;
+        pos_in = c->sort_pos[cur].p;
+        if (tiles == 1) break;
+        const size_t rem = m - (size_t)(tiles - 1) * kSortTile;
+        m = (size_t)(tiles - 1) * keep + std::min<size_t>(keep, rem);
+      }
+      ranked = c->sort_pos[cur].p;
+    } else {
+      k_pad_keys<<<(n_pad + kT - 1) / kT, kT, 0, st>>>(c->sort_keys[0].p, c->sort_pos[0].p, (uint32_t)n, n_pad);
+      AG2_LAUNCH_CHECK(c);
+      for (uint32_t kk = 2; kk <= n_pad; kk <<= 1)
+        for (uint32_t j = kk >> 1; j > 0; j >>= 1) {
+          k_bitonic_step<<<(n_pad / 2 + kT - 1) / kT, kT, 0, st>>>(c->sort_keys[0].p, c->sort_pos[0].p, n_pad, kk, j);
+          AG2_LAUNCH_CHECK(c);
+        }
+      ranked = c->sort_pos[0].p;
+    }
+    k_take_ranked<<<(unsigned)((k + kT - 1) / kT), kT, 0, st>>>(ranked, (uint32_t)k, c->list[AG2_LIST_ANTIPODAL].p,
+                                                              c->list[AG2_LIST_SELECTED].p);
+    AG2_LAUNCH_CHECK(c);
     c->list_n[AG2_LIST_SELECTED] = k;
   }
   c->list_rec_valid[AG2_LIST_SELECTED] = false;
