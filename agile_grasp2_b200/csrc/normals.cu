@@ -245,8 +245,8 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   // accumulator role of lanes 0..8: operand selectors 0 = x, 1 = y, 2 = z, 3 = constant 1
   const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
   const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
-  __shared__ float one_s;
-  if (threadIdx.x == 0) one_s = 1.0f;
+  __shared__ __align__(16) float ones_s[4];
+  if (threadIdx.x < 4) ones_s[threadIdx.x] = 1.0f;
   __syncthreads();
 
   for (;;) {
@@ -372,20 +372,29 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
       for (uint32_t t = lane; t < count; t += 32) {
         const uint2 rj = A[t];
         const float4 p = g.pts[rj.y];
-        S[3 * rj.x] = p.x;
-        S[3 * rj.x + 1] = p.y;
-        S[3 * rj.x + 2] = p.z;
+        S[rj.x] = p.x;  // SoA: X[cap] Y[cap] Z[cap]
+        S[cap + rj.x] = p.y;
+        S[2 * cap + rj.x] = p.z;
       }
       __syncwarp();
       // ---- sequential single-pass float moments
       if (lane < 9) {
-        const float* pa = S + sa;
         // accu[6..8] += p.x : the second operand is the constant 1.0f, the product is exact
-        const float* pb = sb == 3 ? &one_s : S + sb;
-        const uint32_t stride_b = sb == 3 ? 0u : 3u;
+        const float4* pa = (const float4*)(S + sa * cap);
+        const float4* pb = sb == 3 ? (const float4*)ones_s : (const float4*)(S + sb * cap);
+        const uint32_t step_b = sb == 3 ? 0u : 1u;
         float acc = 0.f;
-#pragma unroll 4
-        for (uint32_t t = 0; t < count; t++) acc = __fadd_rn(acc, __fmul_rn(pa[3 * t], pb[stride_b * t]));
+        const uint32_t n4 = count >> 2;
+        for (uint32_t t = 0; t < n4; t++) {
+          const float4 va = pa[t], vb = pb[step_b * t];
+          acc = __fadd_rn(acc, __fmul_rn(va.x, vb.x));
+          acc = __fadd_rn(acc, __fmul_rn(va.y, vb.y));
+          acc = __fadd_rn(acc, __fmul_rn(va.z, vb.z));
+          acc = __fadd_rn(acc, __fmul_rn(va.w, vb.w));
+        }
+        const float* ra = (const float*)pa;
+        const float* rb_ = (const float*)pb;
+        for (uint32_t t = n4 << 2; t < count; t++) acc = __fadd_rn(acc, __fmul_rn(ra[t], rb_[step_b * t]));
         mom[k * kMomStride + lane] = acc;
       }
       __syncwarp();
@@ -472,7 +481,7 @@ int normals_compute(ag2_ctx* c) {
     c->err = "normals: a point has more than ~11000 neighbours within normals_radius";
     return AG2_E_CAPACITY;
   }
-  // Capacity levels: each launch runs at the smallest tier that leaves at most ~12 % of its
+  // Capacity levels: each launch runs at the smallest tier that leaves at most 25 % of its
   // items for the next one; hist[] gives the exact size of every leftover list.
   static const uint32_t tiers[kTiers] = {64, 96, 128, 192, 256, 384, 512, 1024};
   uint32_t remaining = n, level = 0;
@@ -481,7 +490,7 @@ int normals_compute(ag2_ctx* c) {
   while (remaining > 0 && level < 8) {
     uint32_t cap = cap_max, left = 0;
     for (; tier < kTiers; tier++)
-      if (tiers[tier] < cap_max && hist[tier] <= remaining / 8) {
+      if (tiers[tier] < cap_max && hist[tier] <= remaining / 4) {
         cap = tiers[tier];
         left = hist[tier];
         tier++;
