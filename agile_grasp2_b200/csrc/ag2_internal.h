@@ -58,7 +58,21 @@ struct GridDev {
 // Host-built constant tables; values are produced on the host EXACTLY as the
 // reference produces them (finger_hand.cpp:7-13,122; hand_search.cpp:179-180,357)
 // and never recomputed with device intrinsics.
+// Slot-edge lookup: the 40 values fs_lo[i], fs_hi[i] sorted (U); a point collides with
+// slot i iff fs_lo[i] < x < fs_hi[i], which depends only on k = #(U[j] < x) and on
+// whether x == U[k].  kstart maps a uniform bucket of x to a conservative start for k.
+#define AG2_SLOT_EDGES 40
+#define AG2_SLOT_BUCKETS 256
+struct SlotLut {
+  double U[AG2_SLOT_EDGES];
+  uint32_t M[AG2_SLOT_EDGES + 1];   // U[k-1] < x < U[k]
+  uint32_t Meq[AG2_SLOT_EDGES];     // x == U[k]
+  uint8_t kstart[AG2_SLOT_BUCKETS];
+  double x0, xscale;                // bucket = (int)((x - x0) * xscale), clamped
+};
+
 struct HandConst {
+  SlotLut lut;
   double fs_lo[20];   // finger_spacing_(i)
   double fs_hi[20];   // finger_spacing_(i) + finger_width_
   double depth[AG2_MAX_DEEPEN_STEPS + 2];   // t_0 = init_bite, t_j deepen depths

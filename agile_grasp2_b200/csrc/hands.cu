@@ -9,11 +9,15 @@
 //    to double and cropped with -hh < z_f < hh; survivors are staged in shared
 //    memory as (dx, dy, dz, sorted position) = 16 B;
 //  * per orientation ONE pass over the staged points produces everything
-//    evaluateFingers / deepenHand will ever ask: the 20-slot collision mask of a
-//    point is a bit range found by exact compares against the host-built slot
-//    tables, and it is OR-ed into occ[depth class of y]; the deepen loop is then a
-//    prefix-OR over depth classes done by one thread (no FingerHand copies, no
-//    re-scans);
+//    evaluateFingers / deepenHand will ever ask:
+//      - the 20-slot collision mask of a point depends only on which of the 41
+//        intervals between the (sorted) slot edges its x falls into, so it is one
+//        table lookup (host-built, exact strict/non-strict handling of x == edge);
+//        the mask is OR-ed into occ[depth class of y];
+//      - "a point below the hand base" and "no point below the bite" are monotone
+//        in y, so both follow from the exact minimum of y;
+//    the deepen loop is then a prefix-OR over depth classes done by one thread (no
+//    FingerHand copies, no re-scans);
 //  * pass 2 counts the closing-region points and their x extent, pass 3 writes
 //    their ids to the in-box pool and reduces the antipodal statistics.
 // Neighbourhoods that exceed the staging buffer are processed in chunks; every
@@ -28,9 +32,10 @@
 namespace ag2 {
 namespace {
 
-constexpr int kHandThreads = 256;
+constexpr int kHandThreads = 384;
 constexpr int kMaxRows = 1024;
-constexpr int kBatch = 4;  // candidates per thread per fill batch
+constexpr int kCand = 4;  // consecutive candidates per thread per fill batch
+constexpr int kMaxDepths = AG2_MAX_DEEPEN_STEPS + 2;
 
 struct HandsArgs {
   GridDev g;
@@ -62,46 +67,42 @@ __device__ __forceinline__ int depth_class(double y, const double* thr, int n, d
   return j;
 }
 
-// bits i in [0,10) with lo[i] < x && x < hi[i]; lo, hi ascending
-__device__ __forceinline__ uint32_t slot_range(double x, const double* lo, const double* hi, double inv_step) {
-  double eb = floor((x - lo[0]) * inv_step) + 1.0;
-  int b = eb < 0.0 ? 0 : (eb > 10.0 ? 10 : (int)eb);
-  while (b > 0 && !(lo[b - 1] < x)) b--;
-  while (b < 10 && lo[b] < x) b++;
-  double ea = floor((x - hi[0]) * inv_step) + 1.0;
-  int a = ea < 0.0 ? 0 : (ea > 10.0 ? 10 : (int)ea);
-  while (a > 0 && x < hi[a - 1]) a--;
-  while (a < 10 && !(x < hi[a])) a++;
-  return b > a ? (((1u << b) - 1u) & ~((1u << a) - 1u)) : 0u;
-}
-
-struct OrientState {  // decided by one thread per orientation after pass 1
-  int feasible;
-  int slot, last;
+// Per-orientation state (shared memory, one per orientation of this launch).
+struct Orient {
+  double FRx[3], FRy[3];  // frame_rot columns 0 (closing direction) and 1 (approach)
+  long long ymin;         // ordered double: points.row(1).minCoeff()
+  long long minx, maxx;   // x extent of the closing region
+  long long ap[8];        // antipodal extrema, l: maxy miny maxz minz, r: same (ordered)
+  // decided by one thread after pass 1
   double top, bottom, left, right, center;
-  double lc, sx, sy, sz;      // unit-box scaling (hand_search.cpp:399-409)
+  double lc, sx, sy, sz;  // unit-box scaling (hand_search.cpp:399-409)
+  int feasible, slot, last;
+  uint32_t m, off, fill, anyl, anyr;
 };
 
-struct Shared {
+struct Fixed {
   double F[3][3];
   double sample[3];
-  double FRx[AG2_MAX_ORIENTATIONS][3];  // frame_rot column 0 (closing direction)
-  double FRy[AG2_MAX_ORIENTATIONS][3];  // frame_rot column 1 (approach)
-  uint32_t occ[AG2_MAX_ORIENTATIONS][AG2_MAX_DEEPEN_STEPS + 2];
-  int minct[AG2_MAX_ORIENTATIONS];
-  int mincb[AG2_MAX_ORIENTATIONS];
-  long long ymin[AG2_MAX_ORIENTATIONS];
-  OrientState os[AG2_MAX_ORIENTATIONS];
-  uint32_t m[AG2_MAX_ORIENTATIONS];
-  long long minx[AG2_MAX_ORIENTATIONS], maxx[AG2_MAX_ORIENTATIONS];
-  uint32_t off[AG2_MAX_ORIENTATIONS], fill[AG2_MAX_ORIENTATIONS];
-  uint32_t anyl[AG2_MAX_ORIENTATIONS], anyr[AG2_MAX_ORIENTATIONS];
-  long long ap[AG2_MAX_ORIENTATIONS][8];  // l: maxy miny maxz minz, r: same (ordered)
+  // slot-edge lookup (HandConst::lut copied here: divergent indexing of constant memory serialises)
+  double U[AG2_SLOT_EDGES];
+  uint32_t M[AG2_SLOT_EDGES + 1];
+  uint32_t Meq[AG2_SLOT_EDGES];
+  uint8_t kstart[AG2_SLOT_BUCKETS];
+  double depth[kMaxDepths];
+  double bottom[kMaxDepths];
   uint32_t row_prefix[kMaxRows + 1];
   uint32_t row_begin[kMaxRows];
-  uint32_t nkept, total_cand, cursor, pool_ok;
+  uint32_t nkept, total_cand, cursor, pool_ok, nrows;
   unsigned long long sumK, sumKc;
 };
+
+__host__ __device__ inline size_t hands_smem_base(int R, int ND) {
+  size_t o = (sizeof(Fixed) + 15) & ~(size_t)15;
+  o += (size_t)R * sizeof(Orient);
+  o = (o + 15) & ~(size_t)15;
+  o += (size_t)R * ND * sizeof(uint32_t);
+  return (o + 15) & ~(size_t)15;
+}
 
 }  // namespace
 }  // namespace ag2

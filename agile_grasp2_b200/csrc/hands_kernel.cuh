@@ -3,9 +3,9 @@ namespace ag2 {
 namespace {
 
 // Row spans of the query window, tightened to the chord of the sphere in each row.
-__device__ void setup_rows(Shared& sh, const GridDev& g, const float q[3], float r, float rq, int tid) {
+__device__ void setup_rows(Fixed& sh, const GridDev& g, const float q[3], float rq, int tid) {
   QueryWindow w = make_window(g, q[0], q[1], q[2], rq);
-  int rows = w.rows();
+  int rows = min(w.rows(), kMaxRows);
   int ny = w.y1 - w.y0 + 1;
   float h = 1.0f / g.inv_h;
   for (int row = tid; row < kMaxRows; row += kHandThreads) {
@@ -37,7 +37,10 @@ __device__ void setup_rows(Shared& sh, const GridDev& g, const float q[3], float
     sh.row_begin[row] = begin;
     sh.row_prefix[row + 1] = cnt;
   }
-  if (tid == 0) sh.row_prefix[0] = 0;
+  if (tid == 0) {
+    sh.row_prefix[0] = 0;
+    sh.nrows = (uint32_t)rows;
+  }
   __syncthreads();
   // inclusive scan of kMaxRows counts by warp 0 (32 lanes x 32 items)
   if (tid < 32) {
@@ -59,34 +62,51 @@ __device__ void setup_rows(Shared& sh, const GridDev& g, const float q[3], float
   __syncthreads();
 }
 
-// Stages the next chunk of cropped neighbours, starting at candidate sh.cursor.
-__device__ void fill_chunk(Shared& sh, float4* cache, const HandsArgs& A, const HandConst& hc,
+// Stages the next chunk of cropped neighbours, starting at candidate sh.cursor.  Each
+// thread takes kCand CONSECUTIVE candidates: one binary search over the row prefix, then
+// sequential row advance.
+__device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const HandConst& hc,
                            const float q[3], bool count_stats, int tid) {
   const int lane = tid & 31;
   if (tid == 0) sh.nkept = 0;
   __syncthreads();
   const uint32_t T = sh.total_cand;
+  const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
   uint32_t kcount = 0;
   for (;;) {
-    uint32_t t0 = sh.cursor;
-    uint32_t kept_now = sh.nkept;
-    if (t0 >= T || kept_now + kHandThreads * kBatch > A.cap) break;
+    const uint32_t t0 = sh.cursor;
+    const uint32_t kept_now = sh.nkept;
+    if (t0 >= T || kept_now + kHandThreads * kCand > A.cap) break;
     __syncthreads();  // everyone has read cursor / nkept
+    const uint32_t tb = t0 + (uint32_t)tid * kCand;
+    int row = 0;
+    uint32_t row_end = 0, pos = 0;
+    if (tb < T) {
+      int lo = 0, hi = (int)sh.nrows;  // prefix[lo] <= tb < prefix[hi]
+      while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (sh.row_prefix[mid] <= tb) lo = mid; else hi = mid;
+      }
+      row = lo;
+      row_end = sh.row_prefix[row + 1];
+      pos = sh.row_begin[row] + (tb - sh.row_prefix[row]);
+    }
 #pragma unroll
-    for (int b = 0; b < kBatch; b++) {
-      uint32_t t = t0 + (uint32_t)b * kHandThreads + (uint32_t)tid;
+    for (int b = 0; b < kCand; b++) {
+      const uint32_t t = tb + (uint32_t)b;
       bool keep = false;
       float dx = 0.f, dy = 0.f, dz = 0.f;
-      uint32_t pos = 0;
+      uint32_t ppos = 0;
       if (t < T) {
-        // upper_bound over the row prefix: row with prefix[row] <= t < prefix[row+1]
-        int lo = 0, hi = kMaxRows;
-        while (hi - lo > 1) {
-          int mid = (lo + hi) >> 1;
-          if (sh.row_prefix[mid] <= t) lo = mid; else hi = mid;
+        if (t >= row_end) {
+          do {
+            row++;
+            row_end = sh.row_prefix[row + 1];
+          } while (t >= row_end);
+          pos = sh.row_begin[row];
         }
-        pos = sh.row_begin[lo] + (t - sh.row_prefix[lo]);
-        float4 p = A.g.pts[pos];
+        ppos = pos++;
+        float4 p = A.g.pts[ppos];
         // radiusSearch used q - p; hand_search.cpp:209 centres with p - q (exact negation)
         dx = __fsub_rn(p.x, q[0]);
         dy = __fsub_rn(p.y, q[1]);
@@ -94,7 +114,7 @@ __device__ void fill_chunk(Shared& sh, float4* cache, const HandsArgs& A, const 
         float d2 = dist2_f(dx, dy, dz);
         if (d2 < hc.r2_hands) {
           kcount++;
-          double zf = (sh.F[0][2] * (double)dx + sh.F[1][2] * (double)dy) + sh.F[2][2] * (double)dz;
+          double zf = (az0 * (double)dx + az1 * (double)dy) + az2 * (double)dz;
           keep = zf > hc.neg_hand_height && zf < hc.hand_height;  // hand_search.cpp:334
         }
       }
@@ -102,10 +122,10 @@ __device__ void fill_chunk(Shared& sh, float4* cache, const HandsArgs& A, const 
       uint32_t base = 0;
       if (lane == 0 && ballot) base = atomicAdd(&sh.nkept, (uint32_t)__popc(ballot));
       base = __shfl_sync(AG2_FULL, base, 0);
-      if (keep) cache[base + __popc(ballot & ((1u << lane) - 1))] = make_float4(dx, dy, dz, __uint_as_float(pos));
+      if (keep) cache[base + __popc(ballot & ((1u << lane) - 1))] = make_float4(dx, dy, dz, __uint_as_float(ppos));
     }
     __syncthreads();
-    if (tid == 0) sh.cursor = min(T, t0 + (uint32_t)kBatch * kHandThreads);
+    if (tid == 0) sh.cursor = min(T, t0 + (uint32_t)kCand * kHandThreads);
     __syncthreads();
   }
   if (count_stats) {
@@ -116,14 +136,27 @@ __device__ void fill_chunk(Shared& sh, float4* cache, const HandsArgs& A, const 
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kHandThreads)
+// 20-slot collision mask of a point at hand-frame x: bit i iff fs_lo[i] < x < fs_hi[i].
+__device__ __forceinline__ uint32_t slot_mask(const Fixed& sh, double x, double x0, double xscale) {
+  double bf = (x - x0) * xscale;
+  int bi = bf > 0.0 ? (bf < (double)(AG2_SLOT_BUCKETS - 1) ? (int)bf : AG2_SLOT_BUCKETS - 1) : 0;
+  int k = sh.kstart[bi];
+  while (k < AG2_SLOT_EDGES && sh.U[k] < x) k++;
+  const bool eq = k < AG2_SLOT_EDGES && sh.U[k] == x;
+  return eq ? sh.Meq[k] : sh.M[k];
+}
+
+__global__ void __launch_bounds__(kHandThreads, 2)
 k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Shared& sh = *reinterpret_cast<Shared*>(smem_raw);
-  float4* cache = reinterpret_cast<float4*>(smem_raw + ((sizeof(Shared) + 15) & ~(size_t)15));
+  const int R = hc.num_orientations, ND = hc.num_depths;
+  Fixed& sh = *reinterpret_cast<Fixed*>(smem_raw);
+  Orient* ors = reinterpret_cast<Orient*>(smem_raw + ((sizeof(Fixed) + 15) & ~(size_t)15));
+  uint32_t* occ = reinterpret_cast<uint32_t*>(
+      smem_raw + ((((sizeof(Fixed) + 15) & ~(size_t)15) + (size_t)R * sizeof(Orient) + 15) & ~(size_t)15));
+  float4* cache = reinterpret_cast<float4*>(smem_raw + hands_smem_base(R, ND));
   const int tid = threadIdx.x, lane = tid & 31;
   const uint32_t s = blockIdx.x;
-  const int R = hc.num_orientations, ND = hc.num_depths;
   const ag2_frame& fr = A.frames[s];
   // default records
   for (int r = tid; r < R; r += kHandThreads) {
@@ -146,70 +179,69 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     sh.sumKc = 0;
     sh.pool_ok = 1;
   }
-  for (int r = tid; r < R; r += kHandThreads) {
-    sh.minct[r] = ND;
-    sh.mincb[r] = ND;
-    sh.ymin[r] = d_ordered(INFINITY);
-    sh.m[r] = 0;
-    sh.minx[r] = d_ordered(INFINITY);
-    sh.maxx[r] = d_ordered(-INFINITY);
-    sh.fill[r] = 0;
-    sh.anyl[r] = sh.anyr[r] = 0;
-    for (int k = 0; k < 8; k++) sh.ap[r][k] = d_ordered((k & 1) ? INFINITY : -INFINITY);
-    for (int j = 0; j < ND; j++) sh.occ[r][j] = 0;
-    sh.os[r].feasible = 0;
+  // tables: constant bank -> shared (they are indexed per lane)
+  for (int i = tid; i < AG2_SLOT_EDGES; i += kHandThreads) {
+    sh.U[i] = hc.lut.U[i];
+    sh.Meq[i] = hc.lut.Meq[i];
   }
+  for (int i = tid; i <= AG2_SLOT_EDGES; i += kHandThreads) sh.M[i] = hc.lut.M[i];
+  for (int i = tid; i < AG2_SLOT_BUCKETS; i += kHandThreads) sh.kstart[i] = hc.lut.kstart[i];
+  for (int i = tid; i < ND; i += kHandThreads) {
+    sh.depth[i] = hc.depth[i];
+    sh.bottom[i] = hc.bottom[i];
+  }
+  for (int r = tid; r < R; r += kHandThreads) {
+    Orient& o = ors[r];
+    o.ymin = d_ordered(INFINITY);
+    o.m = 0;
+    o.minx = d_ordered(INFINITY);
+    o.maxx = d_ordered(-INFINITY);
+    o.fill = 0;
+    o.anyl = o.anyr = 0;
+    for (int k = 0; k < 8; k++) o.ap[k] = d_ordered((k & 1) ? INFINITY : -INFINITY);
+    o.feasible = 0;
+  }
+  for (int i = tid; i < R * ND; i += kHandThreads) occ[i] = 0;
   __syncthreads();
   // frame_rot = frame * rot (hand_search.cpp:357-358), columns 0 and 1; column 2 == frame column 2
   for (int t = tid; t < R * 3; t += kHandThreads) {
     int r = t / 3, a = t % 3;
     double ca = hc.cos_a[r], sa = hc.sin_a[r];
     double nsa = -1.0 * sa;
-    sh.FRx[r][a] = (sh.F[a][0] * ca + sh.F[a][1] * sa) + sh.F[a][2] * 0.0;
-    sh.FRy[r][a] = (sh.F[a][0] * nsa + sh.F[a][1] * ca) + sh.F[a][2] * 0.0;
+    ors[r].FRx[a] = (sh.F[a][0] * ca + sh.F[a][1] * sa) + sh.F[a][2] * 0.0;
+    ors[r].FRy[a] = (sh.F[a][0] * nsa + sh.F[a][1] * ca) + sh.F[a][2] * 0.0;
   }
-  setup_rows(sh, A.g, q, 0.f, hc.rq_hands, tid);
+  setup_rows(sh, A.g, q, hc.rq_hands, tid);
   const uint32_t T = sh.total_cand;
   const double inv_dstep = 200.0;  // 1/0.005: estimator only, exact fix-up follows
-  const double inv_sstep = hc.x_est_inv_step;
+  const double lut_x0 = hc.lut.x0, lut_xs = hc.lut.xscale;
 
-  // ---------------- pass 1: slot occupancy per depth class, per orientation
+  // ---------------- pass 1: slot occupancy per depth class and min y, per orientation
   bool single_chunk = true;
   for (int chunk = 0;; chunk++) {
     fill_chunk(sh, cache, A, hc, q, true, tid);
     const uint32_t nk = sh.nkept;
     if (chunk == 0 && sh.cursor < T) single_chunk = false;
     for (int r = 0; r < R; r++) {
-      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
-      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
-      int mct = ND, mcb = ND;
+      const double ax0 = ors[r].FRx[0], ax1 = ors[r].FRx[1], ax2 = ors[r].FRx[2];
+      const double ay0 = ors[r].FRy[0], ay1 = ors[r].FRy[1], ay2 = ors[r].FRy[2];
+      uint32_t* occ_r = occ + r * ND;
       double ymin = INFINITY;
       for (uint32_t i = tid; i < nk; i += kHandThreads) {
         float4 p = cache[i];
         double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
-        double x = (ax0 * px + ax1 * py) + ax2 * pz;
         double y = (ay0 * px + ay1 * py) + ay2 * pz;
         ymin = fmin(ymin, y);
-        int ct = depth_class(y, hc.depth, ND, inv_dstep);
+        int ct = depth_class(y, sh.depth, ND, inv_dstep);
         if (ct < ND) {
-          int cb = depth_class(y, hc.bottom, ND, inv_dstep);
-          mct = min(mct, ct);
-          mcb = min(mcb, cb);
-          uint32_t mask = slot_range(x, hc.fs_lo, hc.fs_hi, inv_sstep) |
-                          (slot_range(x, hc.fs_lo + 10, hc.fs_hi + 10, inv_sstep) << 10);
-          if (mask) atomicOr(&sh.occ[r][ct], mask);
+          double x = (ax0 * px + ax1 * py) + ax2 * pz;
+          uint32_t mask = slot_mask(sh, x, lut_x0, lut_xs);
+          // OR is idempotent and monotone: only touch the word when it would change
+          if (mask & ~occ_r[ct]) atomicOr(&occ_r[ct], mask);
         }
       }
-      for (int o = 16; o > 0; o >>= 1) {
-        mct = min(mct, __shfl_xor_sync(AG2_FULL, mct, o));
-        mcb = min(mcb, __shfl_xor_sync(AG2_FULL, mcb, o));
-      }
       ymin = warp_min_d(ymin);
-      if (lane == 0) {
-        if (mct < ND) atomicMin(&sh.minct[r], mct);
-        if (mcb < ND) atomicMin(&sh.mincb[r], mcb);
-        atomicMin(&sh.ymin[r], d_ordered(ymin));
-      }
+      if (lane == 0) atomicMin(&ors[r].ymin, d_ordered(ymin));
     }
     __syncthreads();
     if (sh.cursor >= T) break;
@@ -218,9 +250,15 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
   // ---------------- finger logic: one thread per orientation
   if (tid < R) {
     const int r = tid;
-    OrientState& o = sh.os[r];
-    const int mct = sh.minct[r], mcb = sh.mincb[r];
-    uint32_t cum = sh.occ[r][0];
+    Orient& o = ors[r];
+    const uint32_t* occ_r = occ + r * ND;
+    // depth classes are monotone in y, so the minima over the points follow from min y:
+    // mct = class of min y against the bite depths; mcb = class of min y against the
+    // hand-base depths, taken over the points with y below the deepest bite (if any)
+    const double ymin = ordered_d(o.ymin);
+    const int mct = depth_class(ymin, sh.depth, ND, inv_dstep);
+    const int mcb = mct < ND ? depth_class(ymin, sh.bottom, ND, inv_dstep) : ND;
+    uint32_t cum = occ_r[0];
     // evaluateFingers(points, init_bite): all false if a point is below the hand base
     // or no point is below the bite (finger_hand.cpp:27-42)
     uint32_t fingers = (mcb <= 0 || mct > 0) ? 0u : (~cum & 0xFFFFFu);
@@ -239,7 +277,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         uint32_t pair = (1u << e) | (1u << (10 + e));
         int last = 0;
         for (int j = 1; j < ND; j++) {  // deepenHand loop, finger_hand.cpp:122-130
-          cum |= sh.occ[r][j];
+          cum |= occ_r[j];
           uint32_t fj = (mcb <= j || mct > j) ? 0u : (~cum & pair);
           if (__popc(fj) < 2) break;
           last = j;
@@ -265,7 +303,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
   }
   __syncthreads();
   int nfeas = 0;
-  for (int r = 0; r < R; r++) nfeas += sh.os[r].feasible;
+  for (int r = 0; r < R; r++) nfeas += ors[r].feasible;
   if (tid == 0) {
     atomicAdd(&A.stat[0], sh.sumK);
     atomicAdd(&A.stat[1], sh.sumKc);
@@ -282,10 +320,11 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     if (!single_chunk) fill_chunk(sh, cache, A, hc, q, false, tid);
     const uint32_t nk = sh.nkept;
     for (int r = 0; r < R; r++) {
-      const OrientState& o = sh.os[r];
+      const Orient& o = ors[r];
       if (!o.feasible) continue;
-      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
-      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
+      const double ax0 = o.FRx[0], ax1 = o.FRx[1], ax2 = o.FRx[2];
+      const double ay0 = o.FRy[0], ay1 = o.FRy[1], ay2 = o.FRy[2];
+      const double top = o.top, left = o.left, right = o.right;
       uint32_t cnt = 0;
       double mn = INFINITY, mx = -INFINITY;
       for (uint32_t i = tid; i < nk; i += kHandThreads) {
@@ -293,7 +332,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
         double x = (ax0 * px + ax1 * py) + ax2 * pz;
         double y = (ay0 * px + ay1 * py) + ay2 * pz;
-        if (y < o.top && x > o.left && x < o.right) {  // finger_hand.cpp:170
+        if (y < top && x > left && x < right) {  // finger_hand.cpp:170
           cnt++;
           mn = fmin(mn, x);
           mx = fmax(mx, x);
@@ -303,9 +342,9 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
       mn = warp_min_d(mn);
       mx = warp_max_d(mx);
       if (lane == 0 && cnt) {
-        atomicAdd(&sh.m[r], cnt);
-        atomicMin(&sh.minx[r], d_ordered(mn));
-        atomicMax(&sh.maxx[r], d_ordered(mx));
+        atomicAdd(&ors[r].m, cnt);
+        atomicMin(&ors[r].minx, d_ordered(mn));
+        atomicMax(&ors[r].maxx, d_ordered(mx));
       }
     }
     __syncthreads();
@@ -314,17 +353,17 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
   if (tid == 0) {
     uint32_t total = 0, mmax = 0;
     for (int r = 0; r < R; r++) {
-      if (!sh.os[r].feasible) continue;
-      sh.off[r] = total;
-      total += sh.m[r];
-      mmax = max(mmax, sh.m[r]);
+      if (!ors[r].feasible) continue;
+      ors[r].off = total;
+      total += ors[r].m;
+      mmax = max(mmax, ors[r].m);
     }
     uint32_t base = total ? atomicAdd(&A.pool_counter[0], total) : 0u;
     if ((unsigned long long)base + total > A.pool_cap) {
       atomicExch(&A.pool_counter[1], 1u);
       sh.pool_ok = 0;
     }
-    for (int r = 0; r < R; r++) sh.off[r] += base;
+    for (int r = 0; r < R; r++) ors[r].off += base;
     atomicMax(&A.pool_counter[2], mmax);
     atomicAdd(&A.stat[2], (unsigned long long)total);
   }
@@ -340,14 +379,17 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     if (!single_chunk) fill_chunk(sh, cache, A, hc, q, false, tid);
     const uint32_t nk = sh.nkept;
     for (int r = 0; r < R; r++) {
-      const OrientState& o = sh.os[r];
-      if (!o.feasible || sh.m[r] == 0) continue;
-      const double ax0 = sh.FRx[r][0], ax1 = sh.FRx[r][1], ax2 = sh.FRx[r][2];
-      const double ay0 = sh.FRy[r][0], ay1 = sh.FRy[r][1], ay2 = sh.FRy[r][2];
+      Orient& o = ors[r];
+      if (!o.feasible || o.m == 0) continue;
+      const double ax0 = o.FRx[0], ax1 = o.FRx[1], ax2 = o.FRx[2];
+      const double ay0 = o.FRy[0], ay1 = o.FRy[1], ay2 = o.FRy[2];
       const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
+      const double top = o.top, left = o.left, right = o.right, bottom = o.bottom;
+      const double sx = o.sx, sy = o.sy, sz = o.sz, lc = o.lc;
+      const uint32_t off = o.off;
       // extremal thresholds on SCALED x (antipodal.cpp:16-17; scaling is monotone)
-      const double lthr = o.sx * (ordered_d(sh.minx[r]) - o.lc) + 0.003;
-      const double rthr = o.sx * (ordered_d(sh.maxx[r]) - o.lc) - 0.003;
+      const double lthr = sx * (ordered_d(o.minx) - lc) + 0.003;
+      const double rthr = sx * (ordered_d(o.maxx) - lc) - 0.003;
       bool al = false, ar = false;
       double st[8] = {-INFINITY, INFINITY, -INFINITY, INFINITY, -INFINITY, INFINITY, -INFINITY, INFINITY};
       for (uint32_t base_i = 0; base_i < nk; base_i += kHandThreads) {
@@ -361,18 +403,18 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
           pos = __float_as_uint(p.w);
           x = (ax0 * px + ax1 * py) + ax2 * pz;
           y = (ay0 * px + ay1 * py) + ay2 * pz;
-          inbox = y < o.top && x > o.left && x < o.right;
+          inbox = y < top && x > left && x < right;
         }
         uint32_t ballot = __ballot_sync(AG2_FULL, inbox);
         uint32_t wbase = 0;
-        if (lane == 0 && ballot) wbase = atomicAdd(&sh.fill[r], (uint32_t)__popc(ballot));
+        if (lane == 0 && ballot) wbase = atomicAdd(&o.fill, (uint32_t)__popc(ballot));
         wbase = __shfl_sync(AG2_FULL, wbase, 0);
         if (inbox) {
-          if (pool_ok) A.pool[sh.off[r] + wbase + __popc(ballot & ((1u << lane) - 1))] = (int32_t)pos;
+          if (pool_ok) A.pool[off + wbase + __popc(ballot & ((1u << lane) - 1))] = (int32_t)pos;
           double z = (az0 * px + az1 * py) + az2 * pz;
-          double xs = o.sx * (x - o.lc);
-          double ys = o.sy * (y - o.bottom);
-          double zs = o.sz * (z - hc.neg_hand_height);
+          double xs = sx * (x - lc);
+          double ys = sy * (y - bottom);
+          double zs = sz * (z - hc.neg_hand_height);
           float4 nv = A.g.nrm[pos];
           double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
           double nxr = (ax0 * n0 + ax1 * n1) + ax2 * n2;
@@ -393,19 +435,21 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         }
       }
       uint32_t bl = __ballot_sync(AG2_FULL, al), br = __ballot_sync(AG2_FULL, ar);
+      if (bl | br) {  // warp-uniform
 #pragma unroll
-      for (int k = 0; k < 8; k++) st[k] = (k & 1) ? warp_min_d(st[k]) : warp_max_d(st[k]);
-      if (lane == 0) {
-        if (bl) {
-          sh.anyl[r] = 1;
-          for (int k = 0; k < 4; k++) {
-            if (k & 1) atomicMin(&sh.ap[r][k], d_ordered(st[k])); else atomicMax(&sh.ap[r][k], d_ordered(st[k]));
+        for (int k = 0; k < 8; k++) st[k] = (k & 1) ? warp_min_d(st[k]) : warp_max_d(st[k]);
+        if (lane == 0) {
+          if (bl) {
+            o.anyl = 1;
+            for (int k = 0; k < 4; k++) {
+              if (k & 1) atomicMin(&o.ap[k], d_ordered(st[k])); else atomicMax(&o.ap[k], d_ordered(st[k]));
+            }
           }
-        }
-        if (br) {
-          sh.anyr[r] = 1;
-          for (int k = 4; k < 8; k++) {
-            if (k & 1) atomicMin(&sh.ap[r][k], d_ordered(st[k])); else atomicMax(&sh.ap[r][k], d_ordered(st[k]));
+          if (br) {
+            o.anyr = 1;
+            for (int k = 4; k < 8; k++) {
+              if (k & 1) atomicMin(&o.ap[k], d_ordered(st[k])); else atomicMax(&o.ap[k], d_ordered(st[k]));
+            }
           }
         }
       }
@@ -415,26 +459,26 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
   }
 
   // ---------------- records: one thread per orientation
-  if (tid < R && sh.os[tid].feasible) {
+  if (tid < R && ors[tid].feasible) {
     const int r = tid;
-    const OrientState& o = sh.os[r];
+    const Orient& o = ors[r];
     const size_t slot_id = (size_t)s * R + r;
     ag2_sweep_record sw = A.sweeps[slot_id];
-    sw.num_in_box = (int32_t)sh.m[r];
-    if (sh.m[r] > 0) {  // empty closing region: orientation skipped (hand_search.cpp:377-381)
+    sw.num_in_box = (int32_t)o.m;
+    if (o.m > 0) {  // empty closing region: orientation skipped (hand_search.cpp:377-381)
       int result = 0;
-      if (sh.anyl[r] || sh.anyr[r]) result = 1;
-      if (sh.anyl[r] && sh.anyr[r]) {
-        double top_y = fmin(ordered_d(sh.ap[r][0]), ordered_d(sh.ap[r][4]));
-        double bot_y = fmax(ordered_d(sh.ap[r][1]), ordered_d(sh.ap[r][5]));
-        double top_z = fmin(ordered_d(sh.ap[r][2]), ordered_d(sh.ap[r][6]));
-        double bot_z = fmax(ordered_d(sh.ap[r][3]), ordered_d(sh.ap[r][7]));
+      if (o.anyl || o.anyr) result = 1;
+      if (o.anyl && o.anyr) {
+        double top_y = fmin(ordered_d(o.ap[0]), ordered_d(o.ap[4]));
+        double bot_y = fmax(ordered_d(o.ap[1]), ordered_d(o.ap[5]));
+        double top_z = fmin(ordered_d(o.ap[2]), ordered_d(o.ap[6]));
+        double bot_z = fmax(ordered_d(o.ap[3]), ordered_d(o.ap[7]));
         if (top_y > bot_y && top_z > bot_z) result = 2;
       }
       ag2_hypothesis g;
-      const double surface = ordered_d(sh.ymin[r]);  // points.row(1).minCoeff(), finger_hand.cpp:158
+      const double surface = ordered_d(o.ymin);  // points.row(1).minCoeff(), finger_hand.cpp:158
       for (int a = 0; a < 3; a++) {
-        double fx = sh.FRx[r][a], fy = sh.FRy[r][a], fz = sh.F[a][2];
+        double fx = o.FRx[a], fy = o.FRy[a], fz = sh.F[a][2];
         g.surface[a] = ((fx * o.center + fy * surface) + fz * 0.0) + sh.sample[a];
         g.bottom[a] = ((fx * o.center + fy * o.bottom) + fz * 0.0) + sh.sample[a];
         g.top[a] = ((fx * o.center + fy * o.top) + fz * 0.0) + sh.sample[a];
@@ -442,7 +486,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         g.approach[a] = fy;
         g.axis[a] = fz;
       }
-      g.width = ordered_d(sh.maxx[r]) - ordered_d(sh.minx[r]);
+      g.width = ordered_d(o.maxx) - ordered_d(o.minx);
       g.score = 0.0;
       g.sample_id = (int32_t)s;
       g.orientation_id = r;
@@ -450,11 +494,11 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
       g.full_antipodal = (uint8_t)(result == 2);
       g.finger_slot = (uint8_t)o.slot;
       g.depth_step = (uint8_t)o.last;
-      g.num_in_box = (int32_t)sh.m[r];
+      g.num_in_box = (int32_t)o.m;
       g.hand_top = o.top;
       g.hand_bottom = o.bottom;
       A.slots[slot_id] = g;
-      A.box_ref[slot_id] = BoxRef{sh.off[r], sh.m[r]};
+      A.box_ref[slot_id] = BoxRef{o.off, o.m};
       sw.antipodal = (uint8_t)result;
       sw.emitted = 1;
     }
@@ -474,9 +518,15 @@ int hands_compute(ag2_ctx* c) {
   AG2_CUDA(c, c->slots.reserve(SR));
   AG2_CUDA(c, c->box_ref.reserve(SR));
   if (c->box_pool.cap == 0) AG2_CUDA(c, c->box_pool.reserve(std::max<size_t>((size_t)1 << 22, SR * 256)));
-  const size_t shared_base = (sizeof(Shared) + 15) & ~(size_t)15;
-  const uint32_t cap = 6144;  // staged points per chunk (96 KB)
-  const size_t smem = shared_base + (size_t)cap * sizeof(float4);
+  // two CTAs per SM: staging capacity = what is left of half the shared memory
+  const size_t base = hands_smem_base(R, c->hc.num_depths);
+  const size_t budget = 112 * 1024;
+  if (base + (size_t)(kHandThreads * kCand + 256) * sizeof(float4) > budget) {
+    c->err = "hands: num_orientations x deepen steps too large for shared memory";
+    return AG2_E_CAPACITY;
+  }
+  const uint32_t cap = (uint32_t)(((budget - base) / sizeof(float4)) & ~(size_t)127);
+  const size_t smem = base + (size_t)cap * sizeof(float4);
   AG2_CUDA(c, cudaFuncSetAttribute(k_hands, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   for (int attempt = 0; attempt < 8; attempt++) {
     AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 20, 0, 12 * sizeof(uint32_t), st));

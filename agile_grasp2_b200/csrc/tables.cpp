@@ -11,6 +11,9 @@
 #include <math.h>
 #include <string.h>
 
+#include <algorithm>
+#include <vector>
+
 #include "ag2_internal.h"
 
 namespace ag2 {
@@ -63,6 +66,37 @@ int build_hand_const(ag2_ctx* c) {
   rr(p.nn_radius_taubin, h.r2_taubin, h.rq_taubin);
   rr(p.normals_radius, h.r2_normals, h.rq_normals);
   h.rng_seed = p.rng_seed;
+  // slot-edge lookup tables (hands.cu): exact by construction, no arithmetic on the edges
+  SlotLut& L = h.lut;
+  std::vector<double> u(h.fs_lo, h.fs_lo + 20);
+  u.insert(u.end(), h.fs_hi, h.fs_hi + 20);
+  std::sort(u.begin(), u.end());
+  for (int k = 0; k < AG2_SLOT_EDGES; k++) L.U[k] = u[k];  // duplicates are harmless: their interval is empty
+  for (int k = 0; k <= AG2_SLOT_EDGES; k++) {
+    uint32_t mask = 0;
+    if (k > 0 && k < AG2_SLOT_EDGES)
+      for (int i = 0; i < 20; i++)
+        if (h.fs_lo[i] <= L.U[k - 1] && h.fs_hi[i] >= L.U[k]) mask |= 1u << i;
+    L.M[k] = mask;
+  }
+  for (int k = 0; k < AG2_SLOT_EDGES; k++) {
+    uint32_t mask = 0;
+    for (int i = 0; i < 20; i++)
+      if (h.fs_lo[i] < L.U[k] && L.U[k] < h.fs_hi[i]) mask |= 1u << i;
+    L.Meq[k] = mask;
+  }
+  const double span = L.U[AG2_SLOT_EDGES - 1] - L.U[0];
+  L.x0 = L.U[0];
+  L.xscale = span > 0 ? (double)AG2_SLOT_BUCKETS / span : 0.0;
+  const double width = span / (double)AG2_SLOT_BUCKETS;
+  for (int b = 0; b < AG2_SLOT_BUCKETS; b++) {
+    // edges strictly below the bucket's lower edge, with 2 % of a bucket as slack for the
+    // rounding of the bucket index on the device; the device scans forward from here
+    const double edge = L.x0 + ((double)b - 0.02) * width;
+    int k = 0;
+    while (k < AG2_SLOT_EDGES && L.U[k] < edge) k++;
+    L.kstart[b] = (uint8_t)k;
+  }
   return AG2_OK;
 }
 
