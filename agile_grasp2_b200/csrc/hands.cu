@@ -24,6 +24,7 @@
 // accumulator is associative (OR / min / max / count), so chunking is exact.
 // FP64 throughout, -fmad=false, same association order as the oracle.
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 

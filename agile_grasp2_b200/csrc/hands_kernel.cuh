@@ -525,7 +525,12 @@ int hands_compute(ag2_ctx* c) {
     c->err = "hands: num_orientations x deepen steps too large for shared memory";
     return AG2_E_CAPACITY;
   }
-  const uint32_t cap = (uint32_t)(((budget - base) / sizeof(float4)) & ~(size_t)127);
+  uint32_t cap = (uint32_t)(((budget - base) / sizeof(float4)) & ~(size_t)127);
+  // test hook: a small staging capacity forces the chunked (multi-pass) path on small scenes
+  if (const char* e = getenv("AG2_HANDS_STAGE_CAP")) {
+    long v = atol(e);
+    if (v >= kHandThreads * kCand + 128 && (uint32_t)v < cap) cap = (uint32_t)v & ~127u;
+  }
   const size_t smem = base + (size_t)cap * sizeof(float4);
   AG2_CUDA(c, cudaFuncSetAttribute(k_hands, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   for (int attempt = 0; attempt < 8; attempt++) {

@@ -11,6 +11,7 @@
 //      the normal toward the viewpoint (0,0,0).
 // Compiled with -fmad=false; every float op below is a separate IEEE operation.
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -484,13 +485,17 @@ int normals_compute(ag2_ctx* c) {
   // Capacity levels: each launch runs at the smallest tier that leaves at most 25 % of its
   // items for the next one; hist[] gives the exact size of every leftover list.
   static const uint32_t tiers[kTiers] = {64, 96, 128, 192, 256, 384, 512, 1024};
+  // test hook: the first level capacity can be forced down so that small scenes exercise the
+  // multi-level path (AG2_NORMALS_FIRST_TIER = index into tiers[])
+  int forced_tier = -1;
+  if (const char* e = getenv("AG2_NORMALS_FIRST_TIER")) forced_tier = atoi(e);
   uint32_t remaining = n, level = 0;
   const uint32_t* list = nullptr;
   int tier = 0;
   while (remaining > 0 && level < 8) {
     uint32_t cap = cap_max, left = 0;
     for (; tier < kTiers; tier++)
-      if (tiers[tier] < cap_max && hist[tier] <= remaining / 4) {
+      if (tiers[tier] < cap_max && (hist[tier] <= remaining / 4 || (level == 0 && tier == forced_tier))) {
         cap = tiers[tier];
         left = hist[tier];
         tier++;

@@ -187,3 +187,55 @@ def test_errors_and_empty():
     g.set_sample_indices(np.array([0, 5], np.int32))
     g.detect()
     assert g.num(capi.LIST_HYPOTHESES) >= 0
+
+
+def _compare_run(g, o, check_normals=True):
+    if check_normals:
+        gn, on = g.normals(), o.normals()
+        assert np.array_equal(np.isnan(gn), np.isnan(on))
+        ok = ~np.isnan(on).any(1)
+        assert angle(gn[ok], on[ok]).max() <= 1e-4
+        assert np.mean(np.all(gn[ok].view(np.uint32) == on[ok].view(np.uint32), axis=1)) > 0.999
+    gs, os_ = g.sweep_records(), o.sweep_records()
+    for f in ("fingers", "hand", "slot", "depth_step", "num_in_box", "antipodal", "emitted"):
+        assert np.array_equal(gs[f], os_[f]), f
+    gh, oh = g.hypotheses(capi.LIST_SELECTED), o.hypotheses(capi.LIST_SELECTED)
+    assert len(gh) == len(oh) and hyp_int_fields_equal(gh, oh) is None
+    for f in POSE_FIELDS:
+        assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+    for k in ("sum_neighbors_hands", "sum_cropped", "sum_in_box", "sum_neighbors_normals"):
+        assert g.stats()[k] == o.stats()[k], k
+
+
+def test_chunked_hand_staging_and_levelled_normals(tiny_scene, monkeypatch):
+    """Forces the multi-chunk path of the hand kernel (small staging buffer) and the
+    multi-level path of the normals kernel (small first capacity) on the tiny scene:
+    results must not change (all accumulators are associative / the ranking is exact)."""
+    monkeypatch.setenv("AG2_HANDS_STAGE_CAP", "1664")
+    monkeypatch.setenv("AG2_NORMALS_FIRST_TIER", "0")
+    p = make_params(capi.MODE_GEOMETRIC)
+    g, o = both(p, tiny_scene)
+    g.detect(); o.detect()
+    _compare_run(g, o)
+    n = g.num(capi.LIST_HYPOTHESES)
+    for h in range(0, n, max(1, n // 6)):
+        assert np.array_equal(g.in_box(capi.LIST_HYPOTHESES, h), o.in_box(capi.LIST_HYPOTHESES, h))
+
+
+def test_c2_full_size_subset():
+    """BASELINE.json config c2 at full cloud size (307 200 points, k_n up to ~500): normals of
+    every point and the sweep of 48 samples against the oracle."""
+    sc = scenes.make_scene("c2", num_samples=48)
+    p = make_params(capi.MODE_GEOMETRIC)
+    p.num_threads = 16
+    g, o = both(p, sc)
+    g.detect(); o.detect()
+    _compare_run(g, o)
+
+
+def test_orientation_and_radius_sweep(tiny_scene):
+    """c5: more orientations and a wider hand-search radius."""
+    p = make_params(capi.MODE_GEOMETRIC, num_orientations=16, nn_radius_hands=0.12)
+    g, o = both(p, tiny_scene)
+    g.detect(); o.detect()
+    _compare_run(g, o, check_normals=False)
