@@ -25,6 +25,7 @@ AG2_E_INVALID, AG2_E_NO_DEVICE, AG2_E_CUDA, AG2_E_EMPTY_CLOUD = -1, -2, -3, -4
 AG2_E_NO_SAMPLES, AG2_E_NO_WEIGHTS, AG2_E_STATE, AG2_E_IO, AG2_E_CAPACITY, AG2_E_NOMEM = -5, -6, -7, -8, -9, -10
 MODE_NONE, MODE_PREDICTION, MODE_GEOMETRIC = 0, 1, 2
 LIST_HYPOTHESES, LIST_PRUNED, LIST_ANTIPODAL, LIST_SELECTED = 0, 1, 2, 3
+LIST_IMPORTANCE, LIST_CLUSTERS = 4, 5
 IMAGE_BYTES = 60 * 60 * 3
 
 
@@ -116,6 +117,20 @@ FRAME_DTYPE = np.dtype(
     align=True,
 )
 assert FRAME_DTYPE.itemsize == 112
+
+
+class IsParams(C.Structure):
+    """ag2_is_params (importance_sampling.cpp:9-15)."""
+
+    _fields_ = [
+        ("num_iterations", C.c_int32),
+        ("num_samples", C.c_int32),
+        ("num_init_samples", C.c_int32),
+        ("method", C.c_int32),
+        ("prob_rand_samples", C.c_double),
+        ("radius", C.c_double),
+        ("seed", C.c_uint64),
+    ]
 
 
 class Stats(C.Structure):
@@ -342,6 +357,24 @@ class Context:
 
     def detect(self):
         self._call("detect")
+
+    def default_is_params(self) -> IsParams:
+        ip = IsParams()
+        rc = self.api.fn("default_is_params")(C.byref(ip))
+        if rc:
+            raise Ag2Error(rc, "default_is_params")
+        return ip
+
+    def detect_importance(self, ip: IsParams):
+        """ImportanceSampling::detectGraspPoses on the samples currently set; result in LIST_IMPORTANCE."""
+        self._call("detect_importance", C.byref(ip))
+        self.n_samples = int(ip.num_samples)
+
+    def importance_samples(self, rnd: int) -> np.ndarray:
+        n = C.c_size_t()
+        out = np.zeros((1 << 20, 3), dtype=np.float64)
+        self._call("get_importance_samples", C.c_int(rnd), _fptr(out), C.c_size_t(out.shape[0]), C.byref(n))
+        return out[: int(n.value)].copy()
 
     def synchronize(self):
         if not self.is_oracle:

@@ -163,10 +163,18 @@ struct ag2_ctx {
   ag2::DevBuf<int32_t> box_pool;            // in-box sorted positions
   ag2::DevBuf<uint32_t> flags;              // 2 * S*R (emitted / pruned)
   ag2::DevBuf<uint32_t> flag_scan;          // 2 * S*R
-  ag2::DevBuf<uint32_t> list[4];            // slot ids of each AG2_LIST_*
-  size_t list_n[4] = {0, 0, 0, 0};
-  ag2::DevBuf<ag2_hypothesis> list_rec[4];  // contiguous records per list
-  bool list_rec_valid[4] = {false, false, false, false};
+  ag2::DevBuf<uint32_t> list[4];            // slot ids of AG2_LIST_HYPOTHESES .. AG2_LIST_SELECTED
+  size_t list_n[6] = {0, 0, 0, 0, 0, 0};
+  // contiguous records per list; lists 4 (importance sampling) and 5 (clusters) exist only as records
+  ag2::DevBuf<ag2_hypothesis> list_rec[6];
+  bool list_rec_valid[6] = {false, false, false, false, false, false};
+  // importance sampling (importance.cu)
+  ag2::DevBuf<double> is_samples;           // samples drawn in the rounds, 3 doubles each
+  size_t is_samples_n = 0;
+  std::vector<size_t> is_round_offset;      // first sample of each round in is_samples
+  ag2::DevBuf<double> is_cand;              // candidate staging
+  ag2::DevBuf<int32_t> is_cand_idx;
+  ag2::DevBuf<uint8_t> is_accept;
   ag2::DevBuf<uint8_t> images;              // pruned * 10800 (HWC u8)
   ag2::DevBuf<float> logits;                // pruned * 2
   ag2::DevBuf<double> scores;               // pruned
@@ -218,6 +226,7 @@ int prune_compute(ag2_ctx* c);
 int select_mode(ag2_ctx* c);
 int select_top(ag2_ctx* c);
 int gather_list_records(ag2_ctx* c, int which);
+int importance_detect(ag2_ctx* c, const ag2_is_params* ip);   // importance.cu
 int render_compute(ag2_ctx* c);                     // render.cu
 int lenet_upload(ag2_ctx* c);                       // lenet.cu
 int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits);

@@ -119,13 +119,13 @@ int ag2_detect(ag2_ctx* c) {
 // ---- outputs
 
 int ag2_num_hypotheses(ag2_ctx* c, int which, size_t* n) {
-  if (!c || !n || which < 0 || which > 3) return AG2_E_INVALID;
+  if (!c || !n || which < 0 || which > 5) return AG2_E_INVALID;
   *n = c->list_n[which];
   return AG2_OK;
 }
 
 int ag2_get_hypotheses_device(ag2_ctx* c, int which, const ag2_hypothesis** d_ptr, size_t* n) {
-  if (!c || which < 0 || which > 3) return AG2_E_INVALID;
+  if (!c || which < 0 || which > 5) return AG2_E_INVALID;
   cudaSetDevice(c->device);
   AG2_TRY(gather_list_records(c, which));
   if (d_ptr) *d_ptr = c->list_rec[which].p;
@@ -134,7 +134,7 @@ int ag2_get_hypotheses_device(ag2_ctx* c, int which, const ag2_hypothesis** d_pt
 }
 
 int ag2_get_hypotheses(ag2_ctx* c, int which, ag2_hypothesis* out, size_t cap, size_t* n) {
-  if (!c || which < 0 || which > 3) return AG2_E_INVALID;
+  if (!c || which < 0 || which > 5) return AG2_E_INVALID;
   const size_t cnt = c->list_n[which];
   if (n) *n = cnt;
   if (cnt > cap) return AG2_E_CAPACITY;

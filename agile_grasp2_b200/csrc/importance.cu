@@ -1,0 +1,271 @@
+// a17: ImportanceSampling::detectGraspPoses (reference importance_sampling.cpp:30-112) and its
+// samplers drawSamplesFromSumOfGaussians / drawSamplesFromMaxOfGaussians (:115-157).
+//
+// What changes against the reference, and why:
+//  * the cell index and the normals are built ONCE; every round is a new sample batch on the
+//    resident cloud (the reference rebuilds the kd-tree and recomputes all N normals per round,
+//    hand_search.cpp:11-24);
+//  * the rounds evaluate the DRAWN xyz samples (calculateLocalFrames(samples), hand_search.cpp:
+//    238-317) — the evident intent; as written the reference's rounds re-evaluate the index
+//    samples because use_incoming_samples_ is never set on this instance;
+//  * rand() / boost::mt19937(time(NULL)) / boost::normal_distribution are replaced by a
+//    counter-based stream (deviation D5): candidate c of round i draws its hand index and its
+//    three N(0,1) values from splitmix64(seed, i, c, j) with Box-Muller.  Candidates are
+//    generated on the host (libm log/cos, identical in the oracle), the O(H) max-of-Gaussians
+//    rejection test of every candidate runs on the device (one warp per candidate), and the
+//    first num_gauss accepted candidates in stream order become the samples.
+//  * the rejection test p(idx) >= max_k p(k) with p = term * exp(c * d2), c = -1/(2 sigma), is
+//    evaluated on the exponent arguments c * d2 (exp is monotone); the two differ only when exp
+//    rounds two different arguments to the same value (documented tie).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "dev_common.cuh"
+
+namespace ag2 {
+namespace {
+
+inline uint64_t h_splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+inline uint64_t is_hash(uint64_t seed, uint64_t round, uint64_t cand, uint64_t j) {
+  uint64_t k = h_splitmix64(seed ^ 0x1234ABCD5678EF01ull);
+  k = h_splitmix64(k + round);
+  k = h_splitmix64(k + cand);
+  return h_splitmix64(k + j);
+}
+inline double is_u01(uint64_t h) { return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
+inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) {
+  double u1 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp));
+  double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
+  return sqrt(-2.0 * log(u1)) * cos(2.0 * M_PI * u2);
+}
+
+// One warp per candidate: accept iff c*d2(x, hand[idx]) >= max_k c*d2(x, hand[k]).
+__global__ void k_is_accept(const double* __restrict__ cand, const int32_t* __restrict__ cand_idx, uint32_t n_cand,
+                            const ag2_hypothesis* __restrict__ hands, uint32_t H, double coef,
+                            uint8_t* __restrict__ accept) {
+  const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (c >= n_cand) return;
+  const double x0 = cand[3 * c], x1 = cand[3 * c + 1], x2 = cand[3 * c + 2];
+  double best = -INFINITY;
+  for (uint32_t k = lane; k < H; k += 32) {
+    const double v0 = x0 - hands[k].surface[0], v1 = x1 - hands[k].surface[1], v2 = x2 - hands[k].surface[2];
+    const double d2 = v0 * v0 + (v1 * v1 + v2 * v2);  // Eigen fixed-size inner product order
+    best = fmax(best, coef * d2);
+  }
+  best = warp_max_d(best);
+  if (lane == 0) {
+    const ag2_hypothesis& h = hands[cand_idx[c]];
+    const double v0 = x0 - h.surface[0], v1 = x1 - h.surface[1], v2 = x2 - h.surface[2];
+    const double d2 = v0 * v0 + (v1 * v1 + v2 * v2);
+    accept[c] = (coef * d2 >= best) ? 1 : 0;
+  }
+}
+
+// rand part of a round: samples.col(j) = cloud->points[r].getVector3fMap().cast<double>()
+__global__ void k_is_gather_points(const float* __restrict__ xyz_in, const int32_t* __restrict__ ridx, uint32_t n,
+                                   double* __restrict__ out) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  size_t r = (size_t)ridx[j];
+  out[3 * j] = (double)xyz_in[3 * r];
+  out[3 * j + 1] = (double)xyz_in[3 * r + 1];
+  out[3 * j + 2] = (double)xyz_in[3 * r + 2];
+}
+
+__global__ void k_is_append(const ag2_hypothesis* __restrict__ src, uint32_t n, int32_t sample_offset,
+                            ag2_hypothesis* __restrict__ dst) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t rec = t / 12, part = t % 12;
+  if (rec >= n) return;
+  uint4 v = reinterpret_cast<const uint4*>(&src[rec])[part];
+  if (part == 10) v.x = (uint32_t)((int32_t)v.x + sample_offset);  // byte 160: sample_id
+  reinterpret_cast<uint4*>(&dst[rec])[part] = v;
+}
+
+int append_selected(ag2_ctx* c, size_t cap, int32_t sample_offset) {
+  AG2_TRY(gather_list_records(c, AG2_LIST_SELECTED));
+  const size_t n = c->list_n[AG2_LIST_SELECTED];
+  if (c->list_n[AG2_LIST_IMPORTANCE] + n > cap) return AG2_E_CAPACITY;
+  if (n) {
+    k_is_append<<<(unsigned)((n * 12 + 255) / 256), 256, 0, c->stream>>>(
+        c->list_rec[AG2_LIST_SELECTED].p, (uint32_t)n, sample_offset,
+        c->list_rec[AG2_LIST_IMPORTANCE].p + c->list_n[AG2_LIST_IMPORTANCE]);
+    AG2_LAUNCH_CHECK(c);
+  }
+  c->list_n[AG2_LIST_IMPORTANCE] += n;
+  return AG2_OK;
+}
+
+}  // namespace
+
+int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
+  static_assert(offsetof(ag2_hypothesis, sample_id) == 160, "k_is_append patches sample_id at byte 160");
+  cudaStream_t st = c->stream;
+  const int iters = ip->num_iterations;
+  const int ns = ip->num_samples;
+  const int n_rand = (int)(ip->prob_rand_samples * ns);  // int num_rand_samples = prob * num_samples
+  const int n_gauss = ns - n_rand;
+  const double sigma = ip->radius;
+  const double coef = -1.0 / (2.0 * sigma);
+  const int R = c->p.num_orientations;
+  const size_t per_round_max = (c->p.num_selected > 0 && c->p.antipodal_mode != AG2_MODE_NONE)
+                                   ? (size_t)c->p.num_selected
+                                   : std::max<size_t>(c->num_samples, (size_t)ns) * (size_t)R;
+  const size_t cap = per_round_max * (size_t)(iters + 1);
+  AG2_CUDA(c, c->list_rec[AG2_LIST_IMPORTANCE].reserve(std::max<size_t>(cap, 1)));
+  AG2_CUDA(c, c->is_samples.reserve(std::max<size_t>((size_t)3 * ns * iters, 3)));
+  c->list_n[AG2_LIST_IMPORTANCE] = 0;
+  c->is_samples_n = 0;
+  c->is_round_offset.clear();
+
+  // 1. initial grasp hypotheses on the samples the caller has set (importance_sampling.cpp:38)
+  AG2_TRY(ag2_detect(c));
+  int32_t sample_offset = 0;
+  AG2_TRY(append_selected(c, cap, sample_offset));
+  sample_offset += (int32_t)c->num_samples;
+  if (c->list_n[AG2_LIST_IMPORTANCE] == 0) return AG2_OK;  // :40-43
+
+  std::vector<double> cand, gauss((size_t)3 * std::max(n_gauss, 1));
+  std::vector<int32_t> cidx, ridx((size_t)std::max(n_rand, 1));
+  std::vector<uint8_t> acc;
+  std::vector<double> surf;
+  for (int it = 0; it < iters; it++) {
+    const size_t H = c->list_n[AG2_LIST_IMPORTANCE];
+    // grasp surfaces of all hands so far (host copy for the candidate generator)
+    {
+      std::vector<ag2_hypothesis> rec(H);
+      AG2_CUDA(c, cudaMemcpyAsync(rec.data(), c->list_rec[AG2_LIST_IMPORTANCE].p, H * sizeof(ag2_hypothesis),
+                                  cudaMemcpyDeviceToHost, st));
+      AG2_CUDA(c, cudaStreamSynchronize(st));
+      surf.resize(3 * H);
+      for (size_t k = 0; k < H; k++)
+        for (int a = 0; a < 3; a++) surf[3 * k + a] = rec[k].surface[a];
+    }
+    // 3.1 samples close to the grasps found so far
+    int got = 0;
+    uint64_t next_cand = 0;
+    for (int batch_no = 0; got < n_gauss; batch_no++) {
+      if (batch_no >= 4096) {
+        c->err = "importance sampling: rejection sampler did not terminate";
+        return AG2_E_STATE;
+      }
+      const size_t B = ip->method == 1 ? (size_t)(n_gauss - got) : std::max<size_t>(256, (size_t)(n_gauss - got) * 8);
+      cand.resize(3 * B);
+      cidx.resize(B);
+      for (size_t b = 0; b < B; b++) {
+        const uint64_t cid = next_cand + b;
+        const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cid, 6) % (uint64_t)H);
+        cidx[b] = (int32_t)idx;
+        for (int a = 0; a < 3; a++)
+          cand[3 * b + a] = surf[3 * idx + a] + is_normal(ip->seed, (uint64_t)it, cid, a) * sigma;
+      }
+      next_cand += B;
+      if (ip->method == 1) {  // sum of Gaussians: every draw is a sample
+        for (size_t b = 0; b < B; b++, got++)
+          for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
+        break;
+      }
+      AG2_CUDA(c, c->is_cand.reserve(3 * B));
+      AG2_CUDA(c, c->is_cand_idx.reserve(B));
+      AG2_CUDA(c, c->is_accept.reserve(B));
+      acc.resize(B);
+      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand.p, cand.data(), 24 * B, cudaMemcpyHostToDevice, st));
+      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, cidx.data(), 4 * B, cudaMemcpyHostToDevice, st));
+      k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B,
+                                                                    c->list_rec[AG2_LIST_IMPORTANCE].p, (uint32_t)H,
+                                                                    coef, c->is_accept.p);
+      AG2_LAUNCH_CHECK(c);
+      AG2_CUDA(c, cudaMemcpyAsync(acc.data(), c->is_accept.p, B, cudaMemcpyDeviceToHost, st));
+      AG2_CUDA(c, cudaStreamSynchronize(st));
+      for (size_t b = 0; b < B && got < n_gauss; b++)
+        if (acc[b]) {
+          for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
+          got++;
+        }
+    }
+    // 3.2 random cloud points
+    for (int j = 0; j < n_rand; j++)
+      ridx[j] = (int32_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)j, 7) % (uint64_t)c->n);
+    // 3.3 the round's sample list, assembled on the device
+    AG2_CUDA(c, c->sample_xyz.reserve((size_t)3 * ns));
+    if (n_gauss)
+      AG2_CUDA(c, cudaMemcpyAsync(c->sample_xyz.p, gauss.data(), (size_t)24 * n_gauss, cudaMemcpyHostToDevice, st));
+    if (n_rand) {
+      AG2_CUDA(c, c->is_cand_idx.reserve((size_t)n_rand));
+      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, ridx.data(), (size_t)4 * n_rand, cudaMemcpyHostToDevice, st));
+      k_is_gather_points<<<(n_rand + 255) / 256, 256, 0, st>>>(c->xyz_in.p, c->is_cand_idx.p, (uint32_t)n_rand,
+                                                             c->sample_xyz.p + (size_t)3 * n_gauss);
+      AG2_LAUNCH_CHECK(c);
+    }
+    AG2_CUDA(c, cudaMemcpyAsync(c->is_samples.p + 3 * c->is_samples_n, c->sample_xyz.p, (size_t)24 * ns,
+                                cudaMemcpyDeviceToDevice, st));
+    c->is_round_offset.push_back(c->is_samples_n);
+    c->is_samples_n += (size_t)ns;
+    AG2_CUDA(c, cudaStreamSynchronize(st));  // ridx / gauss staging is reused by the next round
+    c->use_points = true;
+    c->num_samples = (size_t)ns;
+    c->st.num_samples = (int64_t)ns;
+    c->have_hyps = c->have_pruned = c->have_images = c->have_antipodal = c->have_selected = false;
+    for (int i = 0; i < 4; i++) {
+      c->list_n[i] = 0;
+      c->list_rec_valid[i] = false;
+    }
+    AG2_TRY(ag2_detect(c));
+    AG2_TRY(append_selected(c, cap, sample_offset));
+    sample_offset += ns;
+  }
+  return AG2_OK;
+}
+
+}  // namespace ag2
+
+using namespace ag2;
+
+extern "C" {
+
+int ag2_default_is_params(ag2_is_params* p) {
+  if (!p) return AG2_E_INVALID;
+  memset(p, 0, sizeof(*p));
+  p->num_iterations = 5;       // importance_sampling.cpp:9-15
+  p->num_samples = 50;
+  p->num_init_samples = 100;
+  p->method = 2;
+  p->prob_rand_samples = 0.3;
+  p->radius = 0.02;
+  p->seed = 0;
+  return AG2_OK;
+}
+
+int ag2_detect_importance(ag2_ctx* c, const ag2_is_params* p) {
+  if (!c || !p || p->num_iterations < 0 || p->num_samples < 1 || !(p->radius > 0) || p->prob_rand_samples < 0 ||
+      p->prob_rand_samples > 1 || (p->method != 1 && p->method != 2))
+    return AG2_E_INVALID;
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  if (c->n == 0) return AG2_E_EMPTY_CLOUD;
+  if (c->num_samples == 0) return AG2_E_NO_SAMPLES;
+  return importance_detect(c, p);
+}
+
+int ag2_get_importance_samples(ag2_ctx* c, int round, double* xyz, size_t cap, size_t* n) {
+  if (!c || !n || round < 0 || (size_t)round >= c->is_round_offset.size()) return AG2_E_INVALID;
+  const size_t b = c->is_round_offset[round];
+  const size_t e = (size_t)round + 1 < c->is_round_offset.size() ? c->is_round_offset[round + 1] : c->is_samples_n;
+  *n = e - b;
+  if (e - b > cap) return AG2_E_CAPACITY;
+  if (!xyz) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  AG2_CUDA(c, cudaMemcpyAsync(xyz, c->is_samples.p + 3 * b, (e - b) * 24, cudaMemcpyDeviceToHost, c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}
+
+}  // extern "C"

@@ -322,7 +322,8 @@ int select_top(ag2_ctx* c) {
 }
 
 int gather_list_records(ag2_ctx* c, int which) {
-  if (which < 0 || which > 3) return AG2_E_INVALID;
+  if (which < 0 || which > 5) return AG2_E_INVALID;
+  if (which >= 4) return AG2_OK;  // importance / cluster lists are stored as records
   if (c->list_rec_valid[which]) return AG2_OK;
   const size_t n = c->list_n[which];
   AG2_CUDA(c, c->list_rec[which].reserve(std::max<size_t>(n, 1)));

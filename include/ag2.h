@@ -232,13 +232,41 @@ int ag2_classify(ag2_ctx* ctx);
 int ag2_select(ag2_ctx* ctx);
 /* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) without clustering. */
 int ag2_detect(ag2_ctx* ctx);
+
+/* ImportanceSampling (importance_sampling.cpp:9-15,30-112).  Constants of the reference are the
+ * defaults of ag2_default_is_params; c4 scales num_samples. */
+typedef struct ag2_is_params {
+  int32_t num_iterations;     /* 5 */
+  int32_t num_samples;        /* 50 per round */
+  int32_t num_init_samples;   /* 100 (unused by the reference as well) */
+  int32_t method;             /* 1 = sum of Gaussians, 2 = max of Gaussians (default) */
+  double prob_rand_samples;   /* 0.3 */
+  double radius;              /* 0.02: sigma of the Gaussians */
+  uint64_t seed;              /* counter-based replacement of rand() / boost::mt19937(time) */
+} ag2_is_params;
+int ag2_default_is_params(ag2_is_params* p);
+/* ImportanceSampling::detectGraspPoses (importance_sampling.cpp:30-112) without the final
+ * clustering: detect on the samples currently set, then num_iterations rounds of
+ * {draw samples near the grasps found so far + random cloud points, detect, append}.
+ * The grid and the normals are built once and reused by every round.  Result:
+ * AG2_LIST_IMPORTANCE (records of all rounds; sample_id counts through the rounds). */
+int ag2_detect_importance(ag2_ctx* ctx, const ag2_is_params* p);
+/* Samples drawn in round `round` (0-based), 3 doubles each, for the parity tests. */
+int ag2_get_importance_samples(ag2_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);
 int ag2_synchronize(ag2_ctx* ctx);
 /* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing. */
 int ag2_get_stream(ag2_ctx* ctx, void** stream);
 
 /* ---- outputs ------------------------------------------------------------- */
 
-enum { AG2_LIST_HYPOTHESES = 0, AG2_LIST_PRUNED = 1, AG2_LIST_ANTIPODAL = 2, AG2_LIST_SELECTED = 3 };
+enum {
+  AG2_LIST_HYPOTHESES = 0,
+  AG2_LIST_PRUNED = 1,
+  AG2_LIST_ANTIPODAL = 2,
+  AG2_LIST_SELECTED = 3,
+  AG2_LIST_IMPORTANCE = 4, /* result of ag2_detect_importance */
+  AG2_LIST_CLUSTERS = 5    /* result of ag2_find_clusters */
+};
 int ag2_num_hypotheses(ag2_ctx* ctx, int which, size_t* n);
 int ag2_get_hypotheses(ag2_ctx* ctx, int which, ag2_hypothesis* out, size_t cap, size_t* n);
 /* Device pointer of a list (records are contiguous); valid until the next stage call. */

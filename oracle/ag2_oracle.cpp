@@ -589,6 +589,9 @@ struct ag2o_ctx {
   bool have_hyps = false, have_pruned = false, have_images = false, have_antipodal = false;
   LeNet net;
   ag2_stats st;
+  std::vector<ag2_hypothesis> is_hands;            // importance sampling result (all rounds)
+  std::vector<std::vector<double>> is_round_samples;
+  std::vector<ag2_hypothesis> clusters;            // findClusters result
   size_t num_samples() const { return use_points ? sample_xyz.size() / 3 : sample_idx.size(); }
   int threads() const { return p.num_threads > 0 ? p.num_threads : 1; }
 };
@@ -1308,8 +1311,117 @@ int ag2o_detect(ag2o_ctx* c) {
   return ag2o_select(c);
 }
 
+// ---- ImportanceSampling::detectGraspPoses, importance_sampling.cpp:30-112 (literal form of the
+// samplers :115-157; RNG replaced by the documented counter-based stream D5, see importance.cu)
+namespace {
+inline uint64_t is_hash(uint64_t seed, uint64_t round, uint64_t cand, uint64_t j) {
+  uint64_t k = splitmix64(seed ^ 0x1234ABCD5678EF01ull);
+  k = splitmix64(k + round);
+  k = splitmix64(k + cand);
+  return splitmix64(k + j);
+}
+inline double is_u01(uint64_t h) { return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
+inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) {
+  double u1 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp));
+  double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
+  return std::sqrt(-2.0 * std::log(u1)) * std::cos(2.0 * M_PI * u2);
+}
+void is_append_selected(ag2o_ctx* c, int32_t sample_offset) {
+  for (size_t i : c->selected) {
+    ag2_hypothesis h = c->hyps[i].rec;
+    h.sample_id += sample_offset;
+    c->is_hands.push_back(h);
+  }
+}
+}  // namespace
+
+int ag2o_default_is_params(ag2_is_params* p) {
+  if (!p) return AG2_E_INVALID;
+  std::memset(p, 0, sizeof(*p));
+  p->num_iterations = 5;
+  p->num_samples = 50;
+  p->num_init_samples = 100;
+  p->method = 2;
+  p->prob_rand_samples = 0.3;
+  p->radius = 0.02;
+  return AG2_OK;
+}
+
+int ag2o_detect_importance(ag2o_ctx* c, const ag2_is_params* ip) {
+  if (!c || !ip) return AG2_E_INVALID;
+  c->is_hands.clear();
+  c->is_round_samples.clear();
+  int rc = ag2o_detect(c);  // :38
+  if (rc) return rc;
+  int32_t sample_offset = 0;
+  is_append_selected(c, sample_offset);
+  sample_offset += (int32_t)c->num_samples();
+  if (c->is_hands.empty()) return AG2_OK;
+  const int ns = ip->num_samples;
+  const int num_rand_samples = (int)(ip->prob_rand_samples * ns);  // :47
+  const int num_gauss_samples = ns - num_rand_samples;
+  const double sigma = ip->radius;
+  const double term = 1.0 / std::sqrt(std::pow(2.0 * M_PI, 3.0) * std::pow(sigma, 3.0));  // :53
+  const size_t npts = c->xyz.size() / 3;
+  for (int it = 0; it < ip->num_iterations; it++) {
+    const std::vector<ag2_hypothesis>& hands = c->is_hands;
+    const size_t H = hands.size();
+    std::vector<double> samples((size_t)3 * ns);
+    uint64_t cand = 0;
+    int j = 0;
+    while (j < num_gauss_samples) {  // :132-156 (method 2) / :118-124 (method 1)
+      const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cand, 6) % (uint64_t)H);
+      double x[3];
+      for (int a = 0; a < 3; a++) x[a] = hands[idx].surface[a] + is_normal(ip->seed, (uint64_t)it, cand, a) * sigma;
+      cand++;
+      bool take = true;
+      if (ip->method == 2) {
+        double maxp = 0;
+        for (size_t k = 0; k < H; k++) {
+          V3 d = v3(x[0] - hands[k].surface[0], x[1] - hands[k].surface[1], x[2] - hands[k].surface[2]);
+          double p = dot3(d, d);
+          p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
+          if (p > maxp) maxp = p;
+        }
+        V3 d = v3(x[0] - hands[idx].surface[0], x[1] - hands[idx].surface[1], x[2] - hands[idx].surface[2]);
+        double p = dot3(d, d);
+        p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
+        take = p >= maxp;
+      }
+      if (take) {
+        for (int a = 0; a < 3; a++) samples[3 * (size_t)j + a] = x[a];
+        j++;
+      }
+    }
+    for (int jj = num_gauss_samples; jj < ns; jj++) {  // :79-86
+      size_t r = (size_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)(jj - num_gauss_samples), 7) %
+                          (uint64_t)npts);
+      for (int a = 0; a < 3; a++) samples[3 * (size_t)jj + a] = (double)c->xyz[3 * r + a];
+    }
+    c->is_round_samples.push_back(samples);
+    if ((rc = ag2o_set_sample_points(c, samples.data(), (size_t)ns))) return rc;  // :89
+    if ((rc = ag2o_detect(c))) return rc;                                          // :90
+    is_append_selected(c, sample_offset);                                          // :91
+    sample_offset += ns;
+  }
+  return AG2_OK;
+}
+
+int ag2o_get_importance_samples(ag2o_ctx* c, int round, double* xyz, size_t cap, size_t* n) {
+  if (!c || !n || round < 0 || (size_t)round >= c->is_round_samples.size()) return AG2_E_INVALID;
+  const std::vector<double>& v = c->is_round_samples[round];
+  *n = v.size() / 3;
+  if (v.size() / 3 > cap) return AG2_E_CAPACITY;
+  std::copy(v.begin(), v.end(), xyz);
+  return AG2_OK;
+}
+
 int ag2o_num_hypotheses(ag2o_ctx* c, int which, size_t* n) {
   if (!c || !n) return AG2_E_INVALID;
+  if (which == AG2_LIST_IMPORTANCE || which == AG2_LIST_CLUSTERS) {
+    *n = which == AG2_LIST_IMPORTANCE ? c->is_hands.size() : c->clusters.size();
+    return AG2_OK;
+  }
   std::vector<size_t> tmp;
   const std::vector<size_t>* l = list_of(c, which, tmp);
   if (!l) return AG2_E_INVALID;
@@ -1318,6 +1430,13 @@ int ag2o_num_hypotheses(ag2o_ctx* c, int which, size_t* n) {
 }
 int ag2o_get_hypotheses(ag2o_ctx* c, int which, ag2_hypothesis* out, size_t cap, size_t* n) {
   if (!c) return AG2_E_INVALID;
+  if (which == AG2_LIST_IMPORTANCE || which == AG2_LIST_CLUSTERS) {
+    const std::vector<ag2_hypothesis>& v = which == AG2_LIST_IMPORTANCE ? c->is_hands : c->clusters;
+    if (n) *n = v.size();
+    if (v.size() > cap) return AG2_E_CAPACITY;
+    for (size_t i = 0; i < v.size(); i++) out[i] = v[i];
+    return AG2_OK;
+  }
   std::vector<size_t> tmp;
   const std::vector<size_t>* l = list_of(c, which, tmp);
   if (!l) return AG2_E_INVALID;

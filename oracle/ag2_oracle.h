@@ -37,6 +37,10 @@ int ag2o_classify(ag2o_ctx* ctx);
 int ag2o_select(ag2o_ctx* ctx);
 int ag2o_detect(ag2o_ctx* ctx);
 
+int ag2o_default_is_params(ag2_is_params* p);
+int ag2o_detect_importance(ag2o_ctx* ctx, const ag2_is_params* p);
+int ag2o_get_importance_samples(ag2o_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);
+
 int ag2o_num_hypotheses(ag2o_ctx* ctx, int which, size_t* n);
 int ag2o_get_hypotheses(ag2o_ctx* ctx, int which, ag2_hypothesis* out, size_t cap, size_t* n);
 int ag2o_get_stats(ag2o_ctx* ctx, ag2_stats* out);

@@ -239,3 +239,23 @@ def test_orientation_and_radius_sweep(tiny_scene):
     g, o = both(p, tiny_scene)
     g.detect(); o.detect()
     _compare_run(g, o, check_normals=False)
+
+
+@pytest.mark.parametrize("method", [2, 1])
+def test_importance_sampling_rounds(tiny_scene, method):
+    """a17: ImportanceSampling::detectGraspPoses — identical drawn samples per round and identical
+    accumulated grasp list (rounds reuse the resident grid + normals on the GPU side)."""
+    p = make_params(capi.MODE_NONE, num_selected=20)  # mode 0: every pruned hand is kept
+    g, o = both(p, tiny_scene)
+    ip = g.default_is_params()
+    ip.num_iterations, ip.num_samples, ip.seed, ip.method = 3, 40, 5, method
+    g.detect_importance(ip)
+    o.detect_importance(ip)
+    for r in range(3):
+        gs, os_ = g.importance_samples(r), o.importance_samples(r)
+        assert gs.shape == (40, 3) and np.array_equal(gs, os_), r
+    gh, oh = g.hypotheses(capi.LIST_IMPORTANCE), o.hypotheses(capi.LIST_IMPORTANCE)
+    assert len(gh) == len(oh) and len(gh) > 20
+    assert hyp_int_fields_equal(gh, oh) is None
+    for f in POSE_FIELDS:
+        assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
