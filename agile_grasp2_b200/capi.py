@@ -358,6 +358,34 @@ class Context:
     def detect(self):
         self._call("detect")
 
+    def preprocess_cloud(self, xyz: np.ndarray, cam_mask: Optional[np.ndarray] = None, num_cams: int = 1,
+                         normals: Optional[np.ndarray] = None, filter_workspace: bool = True,
+                         voxelize: bool = True, voxel_size: float = 0.003):
+        """filterWorkspace + voxelizeCloud on the original cloud; the result becomes the ctx's cloud."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
+        cam = None if cam_mask is None else np.ascontiguousarray(cam_mask, dtype=np.uint8)
+        nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32)
+        self._call("preprocess_cloud", _fptr(xyz), C.c_size_t(12), C.c_size_t(len(xyz)), _fptr(cam), C.c_int(num_cams),
+                   _fptr(nrm), C.c_int(int(filter_workspace)), C.c_int(int(voxelize)), C.c_double(voxel_size))
+        self.n_points = len(self.cloud()[0])
+
+    def cloud(self):
+        n = C.c_size_t()
+        self._call("get_cloud", None, None, C.c_size_t(1 << 40), C.byref(n))
+        xyz = np.zeros((int(n.value), 3), dtype=np.float32)
+        cam = np.zeros(int(n.value), dtype=np.uint8)
+        if n.value:
+            self._call("get_cloud", _fptr(xyz), _fptr(cam), C.c_size_t(int(n.value)), C.byref(n))
+        return xyz, cam
+
+    def subsample_uniformly(self, num_samples: int, seed: int = 0) -> np.ndarray:
+        self._call("subsample_uniformly", C.c_int(num_samples), C.c_uint64(seed))
+        n = C.c_size_t()
+        idx = np.zeros(max(num_samples, 1), dtype=np.int32)
+        self._call("get_sample_indices", _fptr(idx), C.c_size_t(idx.size), C.byref(n))
+        self.n_samples = int(n.value)
+        return idx[: int(n.value)].copy()
+
     def default_is_params(self) -> IsParams:
         ip = IsParams()
         rc = self.api.fn("default_is_params")(C.byref(ip))

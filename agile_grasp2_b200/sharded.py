@@ -54,23 +54,49 @@ class ShardedDetector:
             dist.broadcast(t, src=0, group=self.group)
         return t
 
-    def _broadcast_inputs(self, xyz, cam, num_cams, samples):
-        """xyz [N,3] f32, cam [N] u8, samples [S] i32 tensors on self.device on rank 0."""
+    def _broadcast_inputs(self, xyz, cam, num_cams, samples, shape_hint=None):
+        """xyz [N,3] f32, cam [N] u8, samples [S] i32 tensors on self.device on rank 0.
+        shape_hint = (N, S, num_cams) known on every rank skips the size broadcast (and its
+        device->host sync); receive buffers are kept between calls."""
         if self.world == 1:
             return xyz, cam, num_cams, samples
-        meta = torch.zeros(3, dtype=torch.int64, device=self.device)
-        if self.rank == 0:
-            meta[0], meta[1], meta[2] = xyz.shape[0], samples.shape[0], num_cams
-        self._bcast(meta)
-        n, s, num_cams = int(meta[0]), int(meta[1]), int(meta[2])
+        if shape_hint is None:
+            meta = torch.zeros(3, dtype=torch.int64, device=self.device)
+            if self.rank == 0:
+                meta[0], meta[1], meta[2] = xyz.shape[0], samples.shape[0], num_cams
+            self._bcast(meta)
+            n, s, num_cams = int(meta[0]), int(meta[1]), int(meta[2])
+        else:
+            n, s, num_cams = shape_hint
         if self.rank != 0:
-            xyz = torch.empty((n, 3), dtype=torch.float32, device=self.device)
-            cam = torch.empty((n,), dtype=torch.uint8, device=self.device)
-            samples = torch.empty((s,), dtype=torch.int32, device=self.device)
+            key = (n, s)
+            if getattr(self, "_rx_key", None) != key:
+                self._rx = (torch.empty((n, 3), dtype=torch.float32, device=self.device),
+                            torch.empty((n,), dtype=torch.uint8, device=self.device),
+                            torch.empty((s,), dtype=torch.int32, device=self.device))
+                self._rx_key = key
+            xyz, cam, samples = self._rx
         self._bcast(xyz)
         self._bcast(cam)
         self._bcast(samples)
         return xyz, cam, num_cams, samples
+
+    def _gather_fixed(self, local: np.ndarray, cap: int):
+        """One all-gather of fixed-size blocks: [count | cap records] per rank (used when every
+        rank contributes at most `cap` = num_selected records)."""
+        rec = capi.HYPOTHESIS_DTYPE.itemsize
+        buf = np.zeros(16 + cap * rec, dtype=np.uint8)
+        buf[:8] = np.frombuffer(np.int64(len(local)).tobytes(), dtype=np.uint8)
+        buf[16:16 + len(local) * rec] = local.view(np.uint8).reshape(-1)
+        t = torch.from_numpy(buf).to(self.device)
+        out = torch.empty(self.world * buf.size, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        allb = out.cpu().numpy().reshape(self.world, buf.size)
+        parts = []
+        for r in range(self.world):
+            c = int(np.frombuffer(allb[r, :8].tobytes(), dtype=np.int64)[0])
+            parts.append(allb[r, 16:16 + c * rec].copy().view(capi.HYPOTHESIS_DTYPE))
+        return parts
 
     def _gather(self, local: np.ndarray):
         if self.world == 1:
@@ -94,25 +120,30 @@ class ShardedDetector:
         self.ctx.set_sample_indices(samples_all[lo:hi])
         self.ctx.set_sample_id_offset(lo)
         local = np.zeros(0, capi.HYPOTHESIS_DTYPE)
+        p = self.ctx.params
+        # the global top-k is inside the union of the per-rank top-k, so when a top-k is asked for
+        # each rank ships its own SELECTED list (<= num_selected records, one fixed-size all-gather)
+        topk = p.num_selected > 0 and p.antipodal_mode != capi.MODE_NONE
         if hi > lo:
             self.ctx.detect()
-            which = capi.LIST_SELECTED if self.world == 1 else capi.LIST_ANTIPODAL
+            which = capi.LIST_SELECTED if (self.world == 1 or topk) else capi.LIST_ANTIPODAL
             local = self.ctx.hypotheses(which).copy()
             local["sample_id"] += lo
         if self.world == 1:
             return local
-        p = self.ctx.params
+        if topk:
+            return merge_selected(self._gather_fixed(local, p.num_selected), p.num_selected)
         return merge_selected(self._gather(local), p.num_selected, keep_all=p.antipodal_mode == capi.MODE_NONE)
 
-    def detect_device(self, xyz_d, cam_d, num_cams, samples_d):
+    def detect_device(self, xyz_d, cam_d, num_cams, samples_d, shape_hint=None):
         """Cloud resident in HBM on rank 0 (torch CUDA tensors)."""
-        xyz_d, cam_d, num_cams, samples_d = self._broadcast_inputs(xyz_d, cam_d, num_cams, samples_d)
+        xyz_d, cam_d, num_cams, samples_d = self._broadcast_inputs(xyz_d, cam_d, num_cams, samples_d, shape_hint)
         if self.world > 1:
             torch.cuda.current_stream().synchronize()
         self.ctx.set_cloud_device(xyz_d.data_ptr(), xyz_d.shape[0], cam_d.data_ptr(), num_cams)
         return self._run_block(samples_d.cpu().numpy())
 
-    def detect_host(self, xyz_h, cam_h, num_cams, samples_h):
+    def detect_host(self, xyz_h, cam_h, num_cams, samples_h, shape_hint=None):
         """Host buffers (pinned torch CPU tensors on rank 0): H2D inside the call."""
         if self.world == 1:
             self.ctx.set_cloud(xyz_h.numpy(), cam_h.numpy(), num_cams)
@@ -122,7 +153,7 @@ class ShardedDetector:
                                    samples_h.to(self.device, non_blocking=True))
         else:
             xyz_d = cam_d = smp_d = None
-        return self.detect_device(xyz_d, cam_d, num_cams, smp_d)
+        return self.detect_device(xyz_d, cam_d, num_cams, smp_d, shape_hint)
 
     def detect_numpy(self, xyz, cam, num_cams, samples):
         """Backend-neutral entry (gloo CPU tests): numpy inputs on rank 0, None elsewhere."""

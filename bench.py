@@ -270,11 +270,16 @@ def main():
         xyz_d, cam_d, smp_d = xyz_h.cuda(), cam_h.cuda(), smp_h.cuda()
     else:
         xyz_d = cam_d = smp_d = None
+    # sizes of the synthetic workload are the same on every rank (one tiny broadcast at set-up)
+    meta = torch.tensor([n_pts, n_smp, num_cams], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.broadcast(meta, src=0)
+    hint = tuple(int(v) for v in meta.tolist())
     clocks = ClockSampler(local_rank)
     clocks.start()
-    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_device(xyz_d, cam_d, num_cams, smp_d), K, W)
+    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_device(xyz_d, cam_d, num_cams, smp_d, hint), K, W)
     clk = clocks.stop()
-    e2e_ms, _, _, _, sel = timed(lambda: runner.detect_host(xyz_h, cam_h, num_cams, smp_h), K, 1)
+    e2e_ms, _, _, _, sel = timed(lambda: runner.detect_host(xyz_h, cam_h, num_cams, smp_h, hint), K, 1)
     t = torch.tensor([tot_ms, e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

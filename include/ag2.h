@@ -215,6 +215,24 @@ int ag2_set_sample_points(ag2_ctx* ctx, const double* xyz, size_t n);
  * stream, so that a shard of a larger sample list draws like the whole list. */
 int ag2_set_sample_id_offset(ag2_ctx* ctx, int64_t first_sample_id);
 
+/* ---- pre-processing (next row f1) ----------------------------------------- */
+
+/* GraspDetector::preprocessPointCloud steps 1-2 (grasp_detector.cpp:289-303):
+ * CloudCamera::filterWorkspace (cloud_camera.cpp:89-121, bounds = params.workspace) and
+ * CloudCamera::voxelizeCloud (cloud_camera.cpp:124-168, voxel_size 0.003 in the reference) on
+ * the ORIGINAL cloud given as host buffers; the processed cloud becomes the ctx's cloud exactly
+ * as if ag2_set_cloud had been called with it.  Precomputed normals follow the workspace filter
+ * and are dropped by voxelisation (the reference leaves them stale). */
+int ag2_preprocess_cloud(ag2_ctx* ctx, const float* xyz, size_t stride_bytes, size_t n,
+                         const uint8_t* cam_mask, int num_cams, const float* normals_or_null,
+                         int filter_workspace, int voxelize, double voxel_size);
+/* The ctx's (processed) cloud: packed xyz and camera masks.  CloudCamera::getCloudProcessed. */
+int ag2_get_cloud(ag2_ctx* ctx, float* xyz, uint8_t* cam_mask, size_t cap, size_t* n);
+/* CloudCamera::subsampleUniformly (cloud_camera.cpp:171-178): num_samples distinct ascending
+ * indices into the processed cloud become the sample indices. */
+int ag2_subsample_uniformly(ag2_ctx* ctx, int num_samples, uint64_t seed);
+int ag2_get_sample_indices(ag2_ctx* ctx, int32_t* idx, size_t cap, size_t* n);
+
 /* ---- stages -------------------------------------------------------------- */
 
 /* KdTreeFLANN::setInputCloud + calculateNormalsOMP (hand_search.cpp:11-30,83-94). */

@@ -48,7 +48,9 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <array>
 #include <cmath>
+#include <map>
 #include <cstdint>
 #include <cstring>
 #include <limits>
@@ -1309,6 +1311,113 @@ int ag2o_detect(ag2o_ctx* c) {
     if ((rc = ag2o_classify(c))) return rc;
   }
   return ag2o_select(c);
+}
+
+// ---- pre-processing: CloudCamera::filterWorkspace / voxelizeCloud / subsampleUniformly
+// (cloud_camera.cpp:89-121, :124-168, :171-178), literal form with std::set
+int ag2o_preprocess_cloud(ag2o_ctx* c, const float* xyz, size_t stride, size_t n, const uint8_t* cam, int num_cams,
+                          const float* normals, int filter_workspace, int voxelize, double voxel_size) {
+  if (!c || (n && !xyz) || stride < 12) return AG2_E_INVALID;
+  std::vector<float> pts, nrm;
+  std::vector<uint8_t> cm;
+  const double* ws = c->p.workspace;
+  for (size_t i = 0; i < n; i++) {  // filterWorkspace, :92-99
+    const float* p = (const float*)((const char*)xyz + i * stride);
+    if (!filter_workspace || (p[0] > ws[0] && p[0] < ws[1] && p[1] > ws[2] && p[1] < ws[3] && p[2] > ws[4] && p[2] < ws[5])) {
+      pts.insert(pts.end(), p, p + 3);
+      cm.push_back(cam ? cam[i] : (uint8_t)1);
+      if (normals && !voxelize) nrm.insert(nrm.end(), normals + 3 * i, normals + 3 * i + 3);
+    }
+  }
+  if (voxelize && !pts.empty()) {  // voxelizeCloud, :124-168
+    const size_t m = pts.size() / 3;
+    float mn[3] = {INFINITY, INFINITY, INFINITY};
+    for (size_t i = 0; i < m; i++)
+      for (int d = 0; d < 3; d++)
+        if (pts[3 * i + d] < mn[d]) mn[d] = pts[3 * i + d];
+    const float cell = (float)voxel_size;  // Vector3f / double: the scalar is converted to float
+    struct Less {
+      bool operator()(const std::array<int, 3>& a, const std::array<int, 3>& b) const {
+        for (int i = 0; i < 3; i++)
+          if (a[i] != b[i]) return a[i] < b[i];
+        return false;
+      }
+    };
+    std::map<std::array<int, 3>, size_t, Less> bins;  // set + idx_cam_source of the first insertion
+    for (size_t i = 0; i < m; i++) {
+      std::array<int, 3> v;
+      bool finite = true;
+      for (int d = 0; d < 3; d++) {
+        float f = std::floor((pts[3 * i + d] - mn[d]) / cell);
+        if (!(f == f)) finite = false;
+        v[d] = finite ? (int)f : 0;
+      }
+      if (finite) bins.insert(std::make_pair(v, i));  // keeps the first
+    }
+    std::vector<float> vp;
+    std::vector<uint8_t> vc;
+    for (const auto& kv : bins) {
+      for (int d = 0; d < 3; d++) {
+        float t = (float)kv.first[d] * cell;
+        vp.push_back(t + mn[d]);
+      }
+      vc.push_back(cm[kv.second]);
+    }
+    pts.swap(vp);
+    cm.swap(vc);
+  }
+  return ag2o_set_cloud(c, pts.data(), 12, pts.size() / 3, cm.data(), num_cams, nrm.empty() ? nullptr : nrm.data());
+}
+
+int ag2o_get_cloud(ag2o_ctx* c, float* xyz, uint8_t* cam, size_t cap, size_t* n) {
+  if (!c || !n) return AG2_E_INVALID;
+  *n = c->xyz.size() / 3;
+  if (*n > cap) return AG2_E_CAPACITY;
+  if (xyz) std::copy(c->xyz.begin(), c->xyz.end(), xyz);
+  if (cam) std::copy(c->cam.begin(), c->cam.end(), cam);
+  return AG2_OK;
+}
+
+int ag2o_subsample_uniformly(ag2o_ctx* c, int num_samples, uint64_t seed) {
+  if (!c || num_samples < 0) return AG2_E_INVALID;
+  const size_t N0 = c->xyz.size() / 3;
+  if ((size_t)num_samples > N0) return AG2_E_INVALID;
+  std::vector<int32_t> out((size_t)num_samples);
+  auto unif = [seed](uint64_t k) {
+    uint64_t x = splitmix64(seed ^ (0xD1B54A32D192ED03ull * (k + 1)));
+    return (float)((double)(x >> 11) * (1.0 / 9007199254740992.0));
+  };
+  // pcl::RandomSample::applyFilter (Vitter's algorithm A), restated
+  size_t N = N0, top = N0 - (size_t)num_samples, index = 0, i = 0;
+  uint64_t draw = 0;
+  for (size_t m = (size_t)num_samples; m >= 2; m--) {
+    float V = unif(draw++);
+    size_t S = 0;
+    float quot = (float)top / (float)N;
+    while (quot > V) {
+      S++;
+      top--;
+      N--;
+      quot = quot * (float)top / (float)N;
+    }
+    index += S;
+    out[i++] = (int32_t)index++;
+    N--;
+  }
+  if (num_samples >= 1) {
+    index += (size_t)((float)N * unif(draw++));
+    if (index >= N0) index = N0 - 1;
+    out[i++] = (int32_t)index;
+  }
+  return ag2o_set_sample_indices(c, out.data(), out.size());
+}
+
+int ag2o_get_sample_indices(ag2o_ctx* c, int32_t* idx, size_t cap, size_t* n) {
+  if (!c || !n) return AG2_E_INVALID;
+  *n = c->sample_idx.size();
+  if (*n > cap) return AG2_E_CAPACITY;
+  std::copy(c->sample_idx.begin(), c->sample_idx.end(), idx);
+  return AG2_OK;
 }
 
 // ---- ImportanceSampling::detectGraspPoses, importance_sampling.cpp:30-112 (literal form of the

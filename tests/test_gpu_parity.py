@@ -259,3 +259,22 @@ def test_importance_sampling_rounds(tiny_scene, method):
     assert hyp_int_fields_equal(gh, oh) is None
     for f in POSE_FIELDS:
         assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+
+
+@pytest.mark.parametrize("voxelize", [True, False])
+def test_preprocess_cloud(tiny_scene, voxelize):
+    """f1: CloudCamera::filterWorkspace + voxelizeCloud + subsampleUniformly, bit-exact."""
+    p = make_params(capi.MODE_GEOMETRIC)
+    g, o = capi.Context(p), ob.context(p)
+    xyz = tiny_scene["xyz"].copy()
+    xyz[7] = np.nan
+    for c in (g, o):
+        c.preprocess_cloud(xyz, tiny_scene["cam_mask"], tiny_scene["num_cams"], voxelize=voxelize)
+    (gx, gc), (ox, oc) = g.cloud(), o.cloud()
+    assert gx.shape == ox.shape and len(gx) > 1000
+    assert np.array_equal(gx.view(np.uint32), ox.view(np.uint32))
+    assert np.array_equal(gc, oc)
+    gi, oi = g.subsample_uniformly(50, seed=9), o.subsample_uniformly(50, seed=9)
+    assert np.array_equal(gi, oi)
+    g.detect(); o.detect()
+    _compare_run(g, o)

@@ -198,3 +198,31 @@ def test_oracle_golden_regression(tiny_scene):
     assert np.array_equal(o.normals().view(np.uint32), gold["normals_bits"])
     h = o.hypotheses()
     assert np.allclose(h["bottom"], gold["bottom"], atol=1e-12) and np.allclose(h["width"], gold["width"], atol=1e-12)
+
+
+def test_preprocess_vs_numpy(tiny_scene):
+    """f1: workspace filter + voxelisation against an independent numpy formulation
+    (np.unique over lexicographic voxel ids; first point of a voxel gives the camera source)."""
+    p = make_params()
+    o = ob.context(p)
+    xyz, cam = tiny_scene["xyz"].copy(), tiny_scene["cam_mask"]
+    xyz[5] = np.nan
+    o.preprocess_cloud(xyz, cam, tiny_scene["num_cams"], voxelize=True, voxel_size=0.003)
+    oxyz, ocam = o.cloud()
+    ws = np.array(list(p.workspace))
+    x64 = xyz.astype(np.float64)
+    keep = ((x64[:, 0] > ws[0]) & (x64[:, 0] < ws[1]) & (x64[:, 1] > ws[2]) & (x64[:, 1] < ws[3]) &
+            (x64[:, 2] > ws[4]) & (x64[:, 2] < ws[5]))
+    f, fc = xyz[keep], cam[keep]
+    mn = f.min(0)
+    cell = np.float32(0.003)
+    v = np.floor((f - mn) / cell).astype(np.int64)
+    key = (v[:, 0] << 42) | (v[:, 1] << 21) | v[:, 2]
+    uk, first = np.unique(key, return_index=True)
+    vv = v[first]
+    exp = (vv.astype(np.float32) * cell + mn).astype(np.float32)
+    assert oxyz.shape == exp.shape
+    assert np.array_equal(oxyz.view(np.uint32), exp.view(np.uint32))
+    assert np.array_equal(ocam, fc[first])
+    idx = o.subsample_uniformly(100, seed=3)
+    assert len(idx) == 100 and np.all(np.diff(idx) > 0) and idx[-1] < len(oxyz)
