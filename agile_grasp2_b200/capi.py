@@ -38,7 +38,7 @@ class Params(C.Structure):
         ("num_orientations", C.c_int32),
         ("num_threads", C.c_int32),
         ("num_samples", C.c_int32),
-        ("reserved0", C.c_int32),
+        ("min_inliers", C.c_int32),
         ("finger_width", C.c_double),
         ("hand_outer_diameter", C.c_double),
         ("hand_depth", C.c_double),
@@ -385,6 +385,10 @@ class Context:
         self._call("get_sample_indices", _fptr(idx), C.c_size_t(idx.size), C.byref(n))
         self.n_samples = int(n.value)
         return idx[: int(n.value)].copy()
+
+    def find_clusters(self, which_src: int):
+        """HandleSearch::findClusters on list `which_src`; result in LIST_CLUSTERS."""
+        self._call("find_clusters", C.c_int(which_src))
 
     def default_is_params(self) -> IsParams:
         ip = IsParams()

@@ -179,6 +179,7 @@ struct ag2_ctx {
   ag2::DevBuf<float> logits;                // pruned * 2
   ag2::DevBuf<double> scores;               // pruned
   ag2::DevBuf<float> act;                   // LeNet activations
+  ag2::DevBuf<ag2_hypothesis> cluster_tmp;  // moved hands before compaction (cluster.cu)
   ag2::DevBuf<uint64_t> sort_keys[2];       // top-k ranking scratch (select.cu)
   ag2::DevBuf<uint32_t> sort_pos[2];
   uint32_t max_in_box = 0;
@@ -226,6 +227,7 @@ int prune_compute(ag2_ctx* c);
 int select_mode(ag2_ctx* c);
 int select_top(ag2_ctx* c);
 int gather_list_records(ag2_ctx* c, int which);
+int clusters_compute(ag2_ctx* c, const ag2_hypothesis* d_src, size_t n);  // cluster.cu
 int importance_detect(ag2_ctx* c, const ag2_is_params* ip);   // importance.cu
 int render_compute(ag2_ctx* c);                     // render.cu
 int lenet_upload(ag2_ctx* c);                       // lenet.cu

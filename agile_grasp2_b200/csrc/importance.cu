@@ -127,6 +127,13 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
   c->is_samples_n = 0;
   c->is_round_offset.clear();
 
+  // the rounds run detectGraspPoses(cloud_cam, false): no clustering inside (:38, :90)
+  struct NoCluster {
+    ag2_ctx* c;
+    int saved;
+    explicit NoCluster(ag2_ctx* cc) : c(cc), saved(cc->p.min_inliers) { c->p.min_inliers = 0; }
+    ~NoCluster() { c->p.min_inliers = saved; }
+  } no_cluster(c);
   // 1. initial grasp hypotheses on the samples the caller has set (importance_sampling.cpp:38)
   AG2_TRY(ag2_detect(c));
   int32_t sample_offset = 0;
@@ -222,6 +229,11 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
     AG2_TRY(ag2_detect(c));
     AG2_TRY(append_selected(c, cap, sample_offset));
     sample_offset += ns;
+  }
+  // :105-109 clusters over the hands of all rounds -> AG2_LIST_CLUSTERS
+  if (no_cluster.saved > 0) {
+    c->p.min_inliers = no_cluster.saved;
+    AG2_TRY(clusters_compute(c, c->list_rec[AG2_LIST_IMPORTANCE].p, c->list_n[AG2_LIST_IMPORTANCE]));
   }
   return AG2_OK;
 }

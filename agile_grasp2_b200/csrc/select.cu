@@ -104,7 +104,7 @@ __global__ void k_score_keys(const uint32_t* __restrict__ list, size_t n, const 
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   // descending score, ties keep list order (documented deviation D4: partial_sort is unstable)
-  long long o = __double_as_longlong(slots[list[i]].score);
+  long long o = __double_as_longlong(slots[list ? list[i] : (uint32_t)i].score);
   unsigned long long u = o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
   // 32 high bits of the order-preserving code are enough to rank float-born scores
   // only when they are floats; keep it exact instead: rank by full code on the host side
@@ -178,6 +178,14 @@ __global__ void k_pad_keys(uint64_t* __restrict__ keys, uint32_t* __restrict__ p
   if (t >= n_pad) return;
   if (t >= n) keys[t] = ~0ull;
   pos[t] = t < n ? t : 0xFFFFFFFFu;
+}
+
+__global__ void k_take_ranked_rec(const uint32_t* __restrict__ pos, uint32_t k, const ag2_hypothesis* __restrict__ src,
+                                  ag2_hypothesis* __restrict__ out) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t rec = t / 12, part = t % 12;
+  if (rec >= k) return;
+  reinterpret_cast<uint4*>(&out[rec])[part] = reinterpret_cast<const uint4*>(&src[pos[rec]])[part];
 }
 
 __global__ void k_take_ranked(const uint32_t* __restrict__ pos, uint32_t k, const uint32_t* __restrict__ list,
@@ -263,7 +271,17 @@ int select_mode(ag2_ctx* c) {
 int select_top(ag2_ctx* c) {
   phase_begin(c, 7);
   cudaStream_t st = c->stream;
-  const size_t n = c->list_n[AG2_LIST_ANTIPODAL];
+  size_t n = c->list_n[AG2_LIST_ANTIPODAL];
+  // 4. clusters (grasp_detector.cpp:229-236): the top-k then ranks the moved / re-scored hands
+  const bool clustered = c->p.min_inliers > 0 && c->p.antipodal_mode != AG2_MODE_NONE;
+  const ag2_hypothesis* cl_src = nullptr;
+  if (clustered) {
+    AG2_TRY(gather_list_records(c, AG2_LIST_ANTIPODAL));
+    AG2_TRY(clusters_compute(c, c->list_rec[AG2_LIST_ANTIPODAL].p, n));
+    n = c->list_n[AG2_LIST_CLUSTERS];
+    cl_src = c->list_rec[AG2_LIST_CLUSTERS].p;
+    AG2_CUDA(c, c->list_rec[AG2_LIST_SELECTED].reserve(std::max<size_t>(n, 1)));
+  }
   AG2_CUDA(c, c->list[AG2_LIST_SELECTED].reserve(std::max<size_t>(n, 1)));
   if (c->p.antipodal_mode == AG2_MODE_NONE || n == 0) {
     if (n) AG2_CUDA(c, cudaMemcpyAsync(c->list[AG2_LIST_SELECTED].p, c->list[AG2_LIST_ANTIPODAL].p, n * 4,
@@ -278,8 +296,8 @@ int select_top(ag2_ctx* c) {
     AG2_CUDA(c, c->sort_keys[1].reserve(n_pad));
     AG2_CUDA(c, c->sort_pos[0].reserve(n_pad));
     AG2_CUDA(c, c->sort_pos[1].reserve(n_pad));
-    k_score_keys<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->list[AG2_LIST_ANTIPODAL].p, n, c->slots.p,
-                                                             c->sort_keys[0].p);
+    k_score_keys<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(clustered ? nullptr : c->list[AG2_LIST_ANTIPODAL].p, n,
+                                                             clustered ? cl_src : c->slots.p, c->sort_keys[0].p);
     AG2_LAUNCH_CHECK(c);
     const uint32_t* ranked = nullptr;
     if (n <= (size_t)kSortTile || k <= (size_t)kSortTile / 2) {
@@ -310,12 +328,18 @@ int select_top(ag2_ctx* c) {
         }
       ranked = c->sort_pos[0].p;
     }
-    k_take_ranked<<<(unsigned)((k + kT - 1) / kT), kT, 0, st>>>(ranked, (uint32_t)k, c->list[AG2_LIST_ANTIPODAL].p,
-                                                              c->list[AG2_LIST_SELECTED].p);
+    if (clustered) {
+      k_take_ranked_rec<<<(unsigned)((k * 12 + kT - 1) / kT), kT, 0, st>>>(ranked, (uint32_t)k, cl_src,
+                                                                         c->list_rec[AG2_LIST_SELECTED].p);
+    } else {
+      k_take_ranked<<<(unsigned)((k + kT - 1) / kT), kT, 0, st>>>(ranked, (uint32_t)k, c->list[AG2_LIST_ANTIPODAL].p,
+                                                                c->list[AG2_LIST_SELECTED].p);
+    }
     AG2_LAUNCH_CHECK(c);
     c->list_n[AG2_LIST_SELECTED] = k;
   }
-  c->list_rec_valid[AG2_LIST_SELECTED] = false;
+  // with clustering the selected list exists as records only (the hands were moved)
+  c->list_rec_valid[AG2_LIST_SELECTED] = clustered;
   c->st.num_selected = (int64_t)c->list_n[AG2_LIST_SELECTED];
   phase_end(c, 7);
   return AG2_OK;

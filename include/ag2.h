@@ -71,7 +71,7 @@ typedef struct ag2_params {
   int32_t num_orientations;   /* 8 */
   int32_t num_threads;        /* accepted; used only by CPU baselines */
   int32_t num_samples;        /* informational, as in the reference */
-  int32_t reserved0;
+  int32_t min_inliers;        /* HandleSearch::min_inliers_ (grasp_detector.cpp:59-65); 0 = no clustering */
   double finger_width;        /* 0.01 */
   double hand_outer_diameter; /* 0.09 */
   double hand_depth;          /* 0.06 */
@@ -248,7 +248,12 @@ int ag2_render_images(ag2_ctx* ctx, uint8_t* out_or_null);
 int ag2_classify(ag2_ctx* ctx);
 /* mode 2: keep isFullAntipodal (grasp_detector.cpp:212-221); mode 0: keep all. */
 int ag2_select(ag2_ctx* ctx);
-/* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) without clustering. */
+/* HandleSearch::findClusters (handle_search.cpp:4-80, remove_inliers = false) on list
+ * `which_src`; result in AG2_LIST_CLUSTERS (records in source order).  ag2_select runs it on the
+ * antipodal list before the top-k when params.min_inliers > 0 (grasp_detector.cpp:229-236). */
+int ag2_find_clusters(ag2_ctx* ctx, int which_src);
+/* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282), clustering included when
+ * params.min_inliers > 0. */
 int ag2_detect(ag2_ctx* ctx);
 
 /* ImportanceSampling (importance_sampling.cpp:9-15,30-112).  Constants of the reference are the

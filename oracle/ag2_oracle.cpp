@@ -594,6 +594,8 @@ struct ag2o_ctx {
   std::vector<ag2_hypothesis> is_hands;            // importance sampling result (all rounds)
   std::vector<std::vector<double>> is_round_samples;
   std::vector<ag2_hypothesis> clusters;            // findClusters result
+  std::vector<ag2_hypothesis> selected_rec;        // selected list when clustering moved the hands
+  bool selected_is_rec = false;
   size_t num_samples() const { return use_points ? sample_xyz.size() / 3 : sample_idx.size(); }
   int threads() const { return p.num_threads > 0 ? p.num_threads : 1; }
 };
@@ -1136,9 +1138,72 @@ void select_geometric(ag2o_ctx* c) {
 }
 
 // grasp_detector.cpp:238-252 (D4: stable on ties)
+// HandleSearch::findClusters(hand_list, remove_inliers = false), handle_search.cpp:4-80
+void find_clusters(const std::vector<ag2_hypothesis>& hand_list, int min_inliers, std::vector<ag2_hypothesis>& hands_out) {
+  const double AXIS_ALIGN_ANGLE_THRESH = 15.0 * M_PI / 180.0;
+  const double AXIS_ALIGN_DIST_THRESH = 0.005;
+  const double MAX_DIST_THRESH = 0.05;
+  hands_out.clear();
+  for (size_t i = 0; i < hand_list.size(); i++) {
+    const ag2_hypothesis& hi = hand_list[i];
+    int num_inliers = 0;
+    double gpd[3] = {0.0, 0.0, 0.0};
+    double outer[3][3];
+    for (int r = 0; r < 3; r++)
+      for (int q = 0; q < 3; q++) outer[r][q] = hi.axis[r] * hi.axis[q];
+    double avg_score = 0.0;
+    for (size_t j = 0; j < hand_list.size(); j++) {
+      if (i == j) continue;
+      const ag2_hypothesis& hj = hand_list[j];
+      double axis_aligned = dot3(v3(hi.axis[0], hi.axis[1], hi.axis[2]), v3(hj.axis[0], hj.axis[1], hj.axis[2]));
+      bool axis_aligned_binary = std::fabs(axis_aligned) > std::cos(AXIS_ALIGN_ANGLE_THRESH);
+      V3 dp = v3(hi.bottom[0] - hj.bottom[0], hi.bottom[1] - hj.bottom[1], hi.bottom[2] - hj.bottom[2]);
+      bool delta_pos_mag_binary = norm3(dp) <= MAX_DIST_THRESH;
+      double P[3][3];
+      for (int r = 0; r < 3; r++)
+        for (int q = 0; q < 3; q++) P[r][q] = (r == q ? 1.0 : 0.0) - outer[r][q];
+      V3 pr = v3((P[0][0] * dp.x + P[0][1] * dp.y) + P[0][2] * dp.z, (P[1][0] * dp.x + P[1][1] * dp.y) + P[1][2] * dp.z,
+                 (P[2][0] * dp.x + P[2][1] * dp.y) + P[2][2] * dp.z);
+      bool delta_pos_proj_mag_binary = norm3(pr) <= AXIS_ALIGN_DIST_THRESH;
+      if (axis_aligned_binary && delta_pos_mag_binary && delta_pos_proj_mag_binary) {
+        num_inliers++;
+        for (int a = 0; a < 3; a++) gpd[a] += hj.bottom[a];
+        avg_score += hj.score;
+      }
+    }
+    if (num_inliers >= min_inliers) {
+      ag2_hypothesis hand = hi;
+      for (int a = 0; a < 3; a++) {
+        double d = gpd[a] / (double)num_inliers - hi.bottom[a];
+        hand.surface[a] = hi.surface[a] + d;
+        hand.bottom[a] = hi.bottom[a] + d;
+        hand.top[a] = hi.top[a] + d;
+      }
+      hand.score = avg_score / (double)num_inliers;
+      hands_out.push_back(hand);
+    }
+  }
+}
+
 void select_top(ag2o_ctx* c) {
   double t0 = omp_get_wtime();
   c->selected = c->antipodal;
+  c->selected_is_rec = false;
+  if (c->p.min_inliers > 0 && c->p.antipodal_mode != AG2_MODE_NONE) {  // grasp_detector.cpp:229-252
+    std::vector<ag2_hypothesis> src;
+    for (size_t i : c->antipodal) src.push_back(c->hyps[i].rec);
+    find_clusters(src, c->p.min_inliers, c->clusters);
+    c->selected_rec = c->clusters;
+    std::stable_sort(c->selected_rec.begin(), c->selected_rec.end(),
+                     [](const ag2_hypothesis& a, const ag2_hypothesis& b) { return a.score > b.score; });
+    if (c->p.num_selected > 0 && c->selected_rec.size() > (size_t)c->p.num_selected)
+      c->selected_rec.resize((size_t)c->p.num_selected);
+    c->selected_is_rec = true;
+    c->selected.clear();
+    c->st.num_selected = (int64_t)c->selected_rec.size();
+    c->st.ms_phase[7] = (omp_get_wtime() - t0) * 1e3;
+    return;
+  }
   if (c->p.antipodal_mode != AG2_MODE_NONE) {
     std::stable_sort(c->selected.begin(), c->selected.end(), [c](size_t a, size_t b) {
       return c->hyps[a].rec.score > c->hyps[b].rec.score;
@@ -1460,6 +1525,12 @@ int ag2o_detect_importance(ag2o_ctx* c, const ag2_is_params* ip) {
   if (!c || !ip) return AG2_E_INVALID;
   c->is_hands.clear();
   c->is_round_samples.clear();
+  struct NoCluster {  // the rounds call detectGraspPoses(cloud_cam, false)
+    ag2o_ctx* c;
+    int saved;
+    explicit NoCluster(ag2o_ctx* cc) : c(cc), saved(cc->p.min_inliers) { c->p.min_inliers = 0; }
+    ~NoCluster() { c->p.min_inliers = saved; }
+  } no_cluster(c);
   int rc = ag2o_detect(c);  // :38
   if (rc) return rc;
   int32_t sample_offset = 0;
@@ -1513,6 +1584,21 @@ int ag2o_detect_importance(ag2o_ctx* c, const ag2_is_params* ip) {
     is_append_selected(c, sample_offset);                                          // :91
     sample_offset += ns;
   }
+  if (no_cluster.saved > 0) find_clusters(c->is_hands, no_cluster.saved, c->clusters);  // :105-109
+  return AG2_OK;
+}
+
+int ag2o_find_clusters(ag2o_ctx* c, int which_src) {
+  if (!c) return AG2_E_INVALID;
+  size_t n = 0;
+  int rc = ag2o_num_hypotheses(c, which_src, &n);
+  if (rc) return rc;
+  std::vector<ag2_hypothesis> src(std::max<size_t>(n, 1));
+  if ((rc = ag2o_get_hypotheses(c, which_src, src.data(), src.size(), &n))) return rc;
+  src.resize(n);
+  std::vector<ag2_hypothesis> out;
+  find_clusters(src, c->p.min_inliers, out);
+  c->clusters.swap(out);
   return AG2_OK;
 }
 
@@ -1531,6 +1617,10 @@ int ag2o_num_hypotheses(ag2o_ctx* c, int which, size_t* n) {
     *n = which == AG2_LIST_IMPORTANCE ? c->is_hands.size() : c->clusters.size();
     return AG2_OK;
   }
+  if (which == AG2_LIST_SELECTED && c->selected_is_rec) {
+    *n = c->selected_rec.size();
+    return AG2_OK;
+  }
   std::vector<size_t> tmp;
   const std::vector<size_t>* l = list_of(c, which, tmp);
   if (!l) return AG2_E_INVALID;
@@ -1539,8 +1629,9 @@ int ag2o_num_hypotheses(ag2o_ctx* c, int which, size_t* n) {
 }
 int ag2o_get_hypotheses(ag2o_ctx* c, int which, ag2_hypothesis* out, size_t cap, size_t* n) {
   if (!c) return AG2_E_INVALID;
-  if (which == AG2_LIST_IMPORTANCE || which == AG2_LIST_CLUSTERS) {
-    const std::vector<ag2_hypothesis>& v = which == AG2_LIST_IMPORTANCE ? c->is_hands : c->clusters;
+  if (which == AG2_LIST_IMPORTANCE || which == AG2_LIST_CLUSTERS || (which == AG2_LIST_SELECTED && c->selected_is_rec)) {
+    const std::vector<ag2_hypothesis>& v =
+        which == AG2_LIST_IMPORTANCE ? c->is_hands : (which == AG2_LIST_CLUSTERS ? c->clusters : c->selected_rec);
     if (n) *n = v.size();
     if (v.size() > cap) return AG2_E_CAPACITY;
     for (size_t i = 0; i < v.size(); i++) out[i] = v[i];

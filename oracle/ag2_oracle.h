@@ -43,6 +43,7 @@ int ag2o_preprocess_cloud(ag2o_ctx* ctx, const float* xyz, size_t stride_bytes, 
 int ag2o_get_cloud(ag2o_ctx* ctx, float* xyz, uint8_t* cam_mask, size_t cap, size_t* n);
 int ag2o_subsample_uniformly(ag2o_ctx* ctx, int num_samples, uint64_t seed);
 int ag2o_get_sample_indices(ag2o_ctx* ctx, int32_t* idx, size_t cap, size_t* n);
+int ag2o_find_clusters(ag2o_ctx* ctx, int which_src);
 int ag2o_default_is_params(ag2_is_params* p);
 int ag2o_detect_importance(ag2o_ctx* ctx, const ag2_is_params* p);
 int ag2o_get_importance_samples(ag2o_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);

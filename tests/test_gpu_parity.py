@@ -278,3 +278,38 @@ def test_preprocess_cloud(tiny_scene, voxelize):
     assert np.array_equal(gi, oi)
     g.detect(); o.detect()
     _compare_run(g, o)
+
+
+@pytest.fixture(scope="module")
+def dense_scene():
+    return scenes.make_scene("tiny", num_samples=1500)  # enough samples for neighbouring hands to cluster
+
+
+def test_find_clusters(dense_scene):
+    """f2: HandleSearch::findClusters — inlier decisions bit-exact, moved poses / mean scores to 1e-9."""
+    p = make_params(capi.MODE_NONE, min_inliers=1)
+    g, o = both(p, dense_scene)
+    g.detect(); o.detect()
+    for c in (g, o):
+        c.find_clusters(capi.LIST_HYPOTHESES)
+    gc, oc = g.hypotheses(capi.LIST_CLUSTERS), o.hypotheses(capi.LIST_CLUSTERS)
+    assert len(gc) == len(oc) and 0 < len(gc) < g.num(capi.LIST_HYPOTHESES)
+    assert hyp_int_fields_equal(gc, oc) is None
+    for f in POSE_FIELDS + ["score"]:
+        assert np.allclose(gc[f], oc[f], rtol=0, atol=1e-9), f
+
+
+def test_detect_with_clustering(dense_scene):
+    """grasp_detector.cpp:229-252: clusters of the accepted hands, then top-k over the clusters."""
+    w = ob.xavier_weights(3, bias_scale=0.5)
+    p = make_params(capi.MODE_PREDICTION, min_score_diff=-1e9, min_inliers=1, num_selected=8)
+    g, o = both(p, dense_scene, weights=w)
+    g.detect(); o.detect()
+    gc, oc = g.hypotheses(capi.LIST_CLUSTERS), o.hypotheses(capi.LIST_CLUSTERS)
+    assert len(gc) == len(oc) and len(gc) > 3
+    assert hyp_int_fields_equal(gc, oc) is None
+    assert np.allclose(gc["bottom"], oc["bottom"], rtol=0, atol=1e-9)
+    assert np.all(np.abs(gc["score"] - oc["score"]) <= np.maximum(1e-3, 1e-5 * np.abs(oc["score"])))
+    gs, os_ = g.hypotheses(capi.LIST_SELECTED), o.hypotheses(capi.LIST_SELECTED)
+    assert len(gs) == len(os_) == min(8, len(gc))
+    assert np.all(np.diff(gs["score"]) <= 0)
