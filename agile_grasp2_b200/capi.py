@@ -221,6 +221,48 @@ def default_params() -> Params:
     return p
 
 
+def pcd_read(path: str):
+    """ag2_pcd_read: returns (xyz [N,3] f32, normals [N,3] f32 or None, rgba [N] u32 or None)."""
+    lib = load().lib
+    n, hn, hc = C.c_size_t(), C.c_int(), C.c_int()
+    rc = lib.ag2_pcd_info(path.encode(), C.byref(n), C.byref(hn), C.byref(hc))
+    if rc:
+        raise Ag2Error(rc, "ag2_pcd_info", path)
+    N = int(n.value)
+    xyz = np.zeros((max(N, 1), 3), np.float32)
+    nrm = np.zeros((max(N, 1), 3), np.float32) if hn.value else None
+    col = np.zeros(max(N, 1), np.uint32) if hc.value else None
+    rc = lib.ag2_pcd_read(path.encode(), _fptr(xyz), _fptr(nrm), _fptr(col), C.c_size_t(max(N, 1)), C.byref(n))
+    if rc:
+        raise Ag2Error(rc, "ag2_pcd_read", path)
+    return xyz[:N], (None if nrm is None else nrm[:N]), (None if col is None else col[:N])
+
+
+def pcd_write(path: str, xyz, normals=None, rgba=None, binary=True):
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    nrm = None if normals is None else np.ascontiguousarray(normals, np.float32)
+    col = None if rgba is None else np.ascontiguousarray(rgba, np.uint32)
+    rc = load().lib.ag2_pcd_write(path.encode(), _fptr(xyz), _fptr(nrm), _fptr(col), C.c_size_t(len(xyz)),
+                                  C.c_int(int(binary)))
+    if rc:
+        raise Ag2Error(rc, "ag2_pcd_write", path)
+
+
+def serialize_grasp_list(hands: np.ndarray, seq=0, sec=0, nsec=0, frame_id="") -> bytes:
+    hands = np.ascontiguousarray(hands, dtype=HYPOTHESIS_DTYPE)
+    ln = C.c_size_t()
+    lib = load().lib
+    lib.ag2_serialize_grasp_list(_fptr(hands), C.c_size_t(len(hands)), C.c_uint32(seq), C.c_uint32(sec),
+                                 C.c_uint32(nsec), frame_id.encode(), None, C.c_size_t(0), C.byref(ln))
+    out = np.zeros(max(int(ln.value), 1), np.uint8)
+    rc = lib.ag2_serialize_grasp_list(_fptr(hands), C.c_size_t(len(hands)), C.c_uint32(seq), C.c_uint32(sec),
+                                      C.c_uint32(nsec), frame_id.encode(), _fptr(out), C.c_size_t(out.size),
+                                      C.byref(ln))
+    if rc:
+        raise Ag2Error(rc, "ag2_serialize_grasp_list")
+    return out[: int(ln.value)].tobytes()
+
+
 class Context:
     """One ag2_ctx (or ag2o_ctx): one GPU, one in-flight detect call."""
 

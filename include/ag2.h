@@ -311,6 +311,20 @@ int ag2_get_logits(ag2_ctx* ctx, float* out, size_t cap_images);
 /* Classifier::ClassifyBatch on caller images (HWC u8, 60x60x3): 2 floats per image. */
 int ag2_classify_images(ag2_ctx* ctx, const uint8_t* images, size_t n, float* logits_out);
 
+/* ---- on-disk / wire formats (next row f3; host code, no ctx needed) -------- */
+
+/* pcl::io::loadPCDFile (cloud_camera.cpp:231-240): DATA ascii | binary | binary_compressed;
+ * fields x y z [rgb|rgba] [normal_x normal_y normal_z]; other fields are skipped. */
+int ag2_pcd_info(const char* path, size_t* n, int* has_normals, int* has_color);
+int ag2_pcd_read(const char* path, float* xyz /*3*cap*/, float* normals_or_null, uint32_t* rgba_or_null,
+                 size_t cap, size_t* n);
+int ag2_pcd_write(const char* path, const float* xyz, const float* normals_or_null,
+                  const uint32_t* rgba_or_null, size_t n, int binary);
+/* ROS 1 wire format of agile_grasp2/GraspListMsg (msg/GraspListMsg.msg, msg/GraspMsg.msg;
+ * GraspHypothesis::convertToGraspMsg, grasp_hypothesis.cpp:37-50).  out may be NULL to size. */
+int ag2_serialize_grasp_list(const ag2_hypothesis* hands, size_t n, uint32_t seq, uint32_t stamp_sec,
+                             uint32_t stamp_nsec, const char* frame_id, uint8_t* out, size_t cap, size_t* len);
+
 #ifdef __cplusplus
 }
 #endif

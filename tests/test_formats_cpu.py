@@ -1,0 +1,118 @@
+"""f3: PCD reader (ascii / binary / binary_compressed) and GraspListMsg serialisation — host code of
+libag2.so, exercised without a GPU against files written by an independent Python writer."""
+import struct
+
+import numpy as np
+
+from agile_grasp2_b200 import capi
+
+
+def _header(n, data, with_normals, rgb_float=False):
+    f, s, t, c = ["x", "y", "z"], ["4"] * 3, ["F"] * 3, ["1"] * 3
+    f.append("rgb" if rgb_float else "rgba"); s.append("4"); t.append("F" if rgb_float else "U"); c.append("1")
+    if with_normals:
+        f += ["normal_x", "normal_y", "normal_z", "curvature"]; s += ["4"] * 4; t += ["F"] * 4; c += ["1"] * 4
+    return ("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS %s\nSIZE %s\nTYPE %s\nCOUNT %s\n"
+            "WIDTH %d\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %d\nDATA %s\n"
+            % (" ".join(f), " ".join(s), " ".join(t), " ".join(c), n, n, data)).encode()
+
+
+def _lzf_literal(raw: bytes) -> bytes:
+    """A valid LZF stream made of literal runs plus one back-reference (exercises both opcodes)."""
+    out = bytearray()
+    head = raw[:40]
+    body = raw[40:]
+    for i in range(0, len(head), 32):
+        chunk = head[i:i + 32]
+        out.append(len(chunk) - 1); out += chunk
+    # back reference if the next 3 bytes repeat something 8 bytes back; otherwise literals only
+    i = 0
+    pos = len(head)
+    while i < len(body):
+        if pos >= 8 and body[i:i + 3] == raw[pos - 8:pos - 5] and len(body) - i >= 3:
+            out.append((1 << 5) | 0); out.append(7)      # len 3, offset 8
+            i += 3; pos += 3
+            continue
+        chunk = body[i:i + 32]
+        # do not let a literal run cross a point where a back reference is possible: keep it simple
+        out.append(len(chunk) - 1); out += chunk
+        i += len(chunk); pos += len(chunk)
+    return bytes(out)
+
+
+def _cloud(n=257, seed=0):
+    rng = np.random.default_rng(seed)
+    xyz = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    xyz[3] = np.nan
+    nrm = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    rgba = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    return xyz, nrm, rgba
+
+
+def test_pcd_binary_and_compressed(tmp_path):
+    xyz, nrm, rgba = _cloud()
+    n = len(xyz)
+    curv = np.zeros(n, np.float32)
+    rec = np.zeros(n, dtype=[("xyz", "<f4", 3), ("rgba", "<u4"), ("n", "<f4", 3), ("c", "<f4")])
+    rec["xyz"], rec["rgba"], rec["n"], rec["c"] = xyz, rgba, nrm, curv
+    p = tmp_path / "b.pcd"
+    p.write_bytes(_header(n, "binary", True) + rec.tobytes())
+    gx, gn, gc = capi.pcd_read(str(p))
+    assert np.array_equal(gx.view(np.uint32), xyz.view(np.uint32))
+    assert np.array_equal(gn, nrm) and np.array_equal(gc, rgba)
+    # binary_compressed: column-wise fields, LZF
+    soa = b"".join([xyz[:, 0].tobytes(), xyz[:, 1].tobytes(), xyz[:, 2].tobytes(), rgba.tobytes(),
+                    nrm[:, 0].tobytes(), nrm[:, 1].tobytes(), nrm[:, 2].tobytes(), curv.tobytes()])
+    comp = _lzf_literal(soa)
+    p = tmp_path / "c.pcd"
+    p.write_bytes(_header(n, "binary_compressed", True) + struct.pack("<II", len(comp), len(soa)) + comp)
+    gx, gn, gc = capi.pcd_read(str(p))
+    assert np.array_equal(gx.view(np.uint32), xyz.view(np.uint32))
+    assert np.array_equal(gn, nrm) and np.array_equal(gc, rgba)
+
+
+def test_pcd_ascii_and_own_writer(tmp_path):
+    xyz, nrm, rgba = _cloud(100, 1)
+    lines = [" ".join(["%.9g" % v for v in xyz[i]] + [str(int(rgba[i]))]) for i in range(len(xyz))]
+    p = tmp_path / "a.pcd"
+    p.write_bytes(_header(len(xyz), "ascii", False) + ("\n".join(lines) + "\n").encode())
+    gx, gn, gc = capi.pcd_read(str(p))
+    assert gn is None
+    assert np.array_equal(gx.view(np.uint32), xyz.view(np.uint32))  # %.9g round-trips float32
+    assert np.array_equal(gc, rgba)
+    for binary in (True, False):
+        q = tmp_path / ("w%d.pcd" % binary)
+        capi.pcd_write(str(q), xyz, nrm, rgba, binary=binary)
+        gx, gn, gc = capi.pcd_read(str(q))
+        assert np.array_equal(gx.view(np.uint32), xyz.view(np.uint32))
+        assert np.array_equal(gn, nrm) and np.array_equal(gc, rgba)
+
+
+def test_pcd_errors(tmp_path):
+    import pytest
+    with pytest.raises(capi.Ag2Error):
+        capi.pcd_read(str(tmp_path / "missing.pcd"))
+    (tmp_path / "bad.pcd").write_bytes(b"FIELDS a b\nSIZE 4 4\nTYPE F F\nCOUNT 1 1\nPOINTS 1\nDATA ascii\n1 2\n")
+    with pytest.raises(capi.Ag2Error):
+        capi.pcd_read(str(tmp_path / "bad.pcd"))
+
+
+def test_grasp_list_wire_format():
+    h = np.zeros(2, capi.HYPOTHESIS_DTYPE)
+    rng = np.random.default_rng(3)
+    for f in ("surface", "bottom", "top", "axis", "approach", "binormal"):
+        h[f] = rng.normal(0, 1, (2, 3))
+    h["width"], h["score"] = [0.05, 0.061], [512.25, -3.5]
+    b = capi.serialize_grasp_list(h, seq=7, sec=11, nsec=13, frame_id="base")
+    assert len(b) == 12 + 4 + 4 + 4 + 2 * 152
+    seq, sec, nsec, fl = struct.unpack_from("<IIII", b, 0)
+    assert (seq, sec, nsec, fl) == (7, 11, 13, 4) and b[16:20] == b"base"
+    (cnt,) = struct.unpack_from("<I", b, 20)
+    assert cnt == 2
+    off = 24
+    for i in range(2):
+        v = struct.unpack_from("<18d2f", b, off)
+        exp = np.concatenate([h[f][i] for f in ("surface", "bottom", "top", "axis", "approach", "binormal")])
+        assert np.array_equal(np.array(v[:18]), exp)
+        assert v[18] == np.float32(h["width"][i]) and v[19] == np.float32(h["score"][i])
+        off += 152
