@@ -14,6 +14,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <vector>
 
 #include "dev_common.cuh"
 
@@ -169,38 +170,77 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
 
 }  // namespace
 
+// Renders the hypotheses in slots d_list[0..n) into d_out (n * 10800 bytes).
+int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
+  if (n == 0) return AG2_OK;
+  if (c->max_in_box >= 65536) {
+    c->err = "render: more than 65535 points in a closing region";
+    return AG2_E_CAPACITY;
+  }
+  uint32_t cap = 64;
+  while (cap < c->max_in_box) cap <<= 1;
+  size_t smem = (size_t)cap * 16 + (size_t)IS * IS * 3 * sizeof(float);
+  if (smem > 220 * 1024) {
+    c->err = "render: closing region too large for shared memory";
+    return AG2_E_CAPACITY;
+  }
+  AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  RenderArgs A;
+  A.g = grid_dev(c);
+  A.list = d_list;
+  A.slots = c->slots.p;
+  A.box_ref = c->box_ref.p;
+  A.pool = c->box_pool.p;
+  A.frames = c->frames.p;
+  A.cap = cap;
+  A.out = d_out;
+  k_render<<<(unsigned)n, kRenderThreads, smem, c->stream>>>(A, c->hc);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
 int render_compute(ag2_ctx* c) {
   phase_begin(c, 5);
   const size_t n = c->list_n[AG2_LIST_PRUNED];
   AG2_CUDA(c, c->images.reserve(std::max<size_t>(n, 1) * AG2_IMAGE_BYTES));
-  if (n) {
-    if (c->max_in_box >= 65536) {
-      c->err = "render: more than 65535 points in a closing region";
-      return AG2_E_CAPACITY;
-    }
-    uint32_t cap = 64;
-    while (cap < c->max_in_box) cap <<= 1;
-    size_t smem = (size_t)cap * 16 + (size_t)IS * IS * 3 * sizeof(float);
-    if (smem > 220 * 1024) {
-      c->err = "render: closing region too large for shared memory";
-      return AG2_E_CAPACITY;
-    }
-    AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    RenderArgs A;
-    A.g = grid_dev(c);
-    A.list = c->list[AG2_LIST_PRUNED].p;
-    A.slots = c->slots.p;
-    A.box_ref = c->box_ref.p;
-    A.pool = c->box_pool.p;
-    A.frames = c->frames.p;
-    A.cap = cap;
-    A.out = c->images.p;
-    k_render<<<(unsigned)n, kRenderThreads, smem, c->stream>>>(A, c->hc);
-    AG2_LAUNCH_CHECK(c);
-  }
+  AG2_TRY(render_list(c, c->list[AG2_LIST_PRUNED].p, n, c->images.p));
   c->have_images = true;
   phase_end(c, 5);
   return AG2_OK;
 }
 
 }  // namespace ag2
+
+// Learning::createGraspImages (learning.cpp:4-33) for caller-chosen hypotheses of the last
+// ag2_generate_hypotheses call, addressed by (sample_id, orientation_id).
+extern "C" int ag2_render_hypotheses(ag2_ctx* c, const int32_t* sample_ids, const int32_t* orientation_ids, size_t n,
+                                     uint8_t* out) {
+  using namespace ag2;
+  if (!c || (n && (!sample_ids || !orientation_ids || !out))) return AG2_E_INVALID;
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  if (!c->have_hyps) return AG2_E_STATE;
+  if (n == 0) return AG2_OK;
+  const int R = c->p.num_orientations;
+  std::vector<uint32_t> slots(n);
+  for (size_t i = 0; i < n; i++) {
+    if (sample_ids[i] < 0 || (size_t)sample_ids[i] >= c->num_samples || orientation_ids[i] < 0 || orientation_ids[i] >= R)
+      return AG2_E_INVALID;
+    slots[i] = (uint32_t)sample_ids[i] * (uint32_t)R + (uint32_t)orientation_ids[i];
+  }
+  // only emitted hypotheses own a closing region
+  std::vector<ag2_sweep_record> sw(c->num_samples * (size_t)R);
+  AG2_CUDA(c, cudaMemcpyAsync(sw.data(), c->sweeps.p, sw.size() * sizeof(ag2_sweep_record), cudaMemcpyDeviceToHost,
+                              c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (size_t i = 0; i < n; i++)
+    if (!sw[slots[i]].emitted) return AG2_E_INVALID;
+  DevBuf<uint32_t> d_list;
+  DevBuf<uint8_t> d_img;
+  AG2_CUDA(c, d_list.reserve(n));
+  AG2_CUDA(c, d_img.reserve(n * AG2_IMAGE_BYTES));
+  AG2_CUDA(c, cudaMemcpyAsync(d_list.p, slots.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
+  AG2_TRY(render_list(c, d_list.p, n, d_img.p));
+  AG2_CUDA(c, cudaMemcpyAsync(out, d_img.p, n * AG2_IMAGE_BYTES, cudaMemcpyDeviceToHost, c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}

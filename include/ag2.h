@@ -244,6 +244,10 @@ int ag2_prune(ag2_ctx* ctx);
 /* Learning::createGraspImages (learning.cpp:4-33) on the pruned list.
  * out_or_null: host buffer of num_pruned * AG2_IMAGE_BYTES (HWC u8, the cv::Mat layout). */
 int ag2_render_images(ag2_ctx* ctx, uint8_t* out_or_null);
+/* Same for caller-chosen hypotheses of the last ag2_generate_hypotheses call, addressed by
+ * (sample_id, orientation_id) as found in their records; out: n * AG2_IMAGE_BYTES (host). */
+int ag2_render_hypotheses(ag2_ctx* ctx, const int32_t* sample_ids, const int32_t* orientation_ids,
+                          size_t n, uint8_t* out);
 /* Classifier::ClassifyBatch + thresholding (grasp_detector.cpp:186-209). */
 int ag2_classify(ag2_ctx* ctx);
 /* mode 2: keep isFullAntipodal (grasp_detector.cpp:212-221); mode 0: keep all. */
