@@ -9,10 +9,12 @@
 // accumulate; summation order differs from Caffe's sgemm, hence the stated
 // tolerance on logits.  Built WITH fma contraction.
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
 #include "dev_common.cuh"
+#include "tc_ptx.cuh"
 
 namespace ag2 {
 namespace {
@@ -23,7 +25,7 @@ constexpr int P1 = 28, P2 = 12;
 // conv1 (3->20, 5x5) + bias + maxpool 2x2.  One CTA per image.
 __global__ void __launch_bounds__(256)
 k_conv1_pool(const uint8_t* __restrict__ images, const float* __restrict__ w, const float* __restrict__ b,
-             float* __restrict__ out /* [n][20][28][28] */) {
+             float4* __restrict__ out /* [n][5 channel quads][28*28] x 4 channels */) {
   __shared__ uint8_t in_s[3][60][64];  // u8 planes; converted at use (exact)
   __shared__ float w_s[C1_OUT * 75];
   __shared__ float b_s[C1_OUT];
@@ -36,7 +38,7 @@ k_conv1_pool(const uint8_t* __restrict__ images, const float* __restrict__ w, co
   for (int i = tid; i < C1_OUT * 75; i += 256) w_s[i] = w[i];
   if (tid < C1_OUT) b_s[tid] = b[tid];
   __syncthreads();
-  float* o = out + (size_t)blockIdx.x * C1_OUT * P1 * P1;
+  float4* o = out + (size_t)blockIdx.x * (C1_OUT / 4) * P1 * P1;
   // work item: pooled position (py, px) x group of 4 output channels
   for (int item = tid; item < P1 * P1 * (C1_OUT / 4); item += 256) {
     int pos = item % (P1 * P1), og = item / (P1 * P1);
@@ -67,18 +69,18 @@ k_conv1_pool(const uint8_t* __restrict__ images, const float* __restrict__ w, co
           }
       }
     }
+    float m[4];
 #pragma unroll
-    for (int a = 0; a < 4; a++) {
-      float m = fmaxf(fmaxf(acc[a][0], acc[a][1]), fmaxf(acc[a][2], acc[a][3]));
-      o[((og * 4 + a) * P1 + py) * P1 + px] = m + b_s[og * 4 + a];
-    }
+    for (int a = 0; a < 4; a++)
+      m[a] = fmaxf(fmaxf(acc[a][0], acc[a][1]), fmaxf(acc[a][2], acc[a][3])) + b_s[og * 4 + a];
+    o[og * (P1 * P1) + pos] = make_float4(m[0], m[1], m[2], m[3]);
   }
 }
 
 // conv2 (20->50, 5x5) + bias + maxpool 2x2.  One CTA per image; output channels in
 // groups of 10 whose weights are staged in shared memory.
 __global__ void __launch_bounds__(288)
-k_conv2_pool(const float* __restrict__ in /* [n][20][28][28] */, const float* __restrict__ w,
+k_conv2_pool(const float* __restrict__ in /* [n][5][28*28][4], see k_conv1_pool */, const float* __restrict__ w,
              const float* __restrict__ b, float* __restrict__ out /* [n][50][12][12] */) {
   extern __shared__ float sm[];
   float* in_s = sm;                   // 20*28*29
@@ -86,8 +88,8 @@ k_conv2_pool(const float* __restrict__ in /* [n][20][28][28] */, const float* __
   const int tid = threadIdx.x;
   const float* src = in + (size_t)blockIdx.x * 20 * P1 * P1;
   for (int i = tid; i < 20 * P1 * P1; i += 288) {
-    int c = i / (P1 * P1), r = (i / P1) % P1, x = i % P1;
-    in_s[(c * 28 + r) * 29 + x] = src[i];
+    int c = (i / (4 * P1 * P1)) * 4 + i % 4, px = (i / 4) % (P1 * P1);
+    in_s[(c * 28 + px / P1) * 29 + px % P1] = src[i];
   }
   float* o = out + (size_t)blockIdx.x * C2_OUT * P2 * P2;
   const int pos = tid % (P2 * P2), half = tid / (P2 * P2);  // 144 positions x 2 halves of 5 channels
@@ -129,6 +131,290 @@ k_conv2_pool(const float* __restrict__ in /* [n][20][28][28] */, const float* __
       o[(oc * P2 + py) * P2 + px] = m + b[oc];
     }
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// conv2 (20->50, 5x5) + bias + maxpool 2x2 on the 5th-generation tensor cores: an implicit GEMM
+// whose A operand is never materialised.  One CTA per image.
+//
+//   D[position][out channel] = sum over the 25 taps, 20 input channels of in * w
+//
+// The pooled conv1 planes sit in shared memory as [channel quad j][pixel][4 channels]: one
+// pixel of one quad is one 16-byte K chunk, eight pixels that are consecutive in x are one
+// 8-row core matrix of the no-swizzle K-major canonical layout, and image rows are a
+// constant 28 pixels = 448 bytes (the descriptor's SBO) apart.  An M = 128 tile is therefore a
+// block of 8 (x) by 16 (y) output positions, and the A tile of tap (ky, kx) is the SAME bytes
+// read through a descriptor whose start address is moved by (ky*28 + kx) pixels.  Six tiles
+// (x0 = 0, 8, 16; y0 = 0, 8) cover the 24 x 24 outputs; rows 8..15 of the y0 = 8 tiles repeat.
+// K runs over 25 taps x 3 steps of 8 channels (quads 2s and 2s+1; the quad after channel 19
+// is a plane of zeros).  fp32 accuracy comes from a three-term tf32 split
+//   a*b ~= a_hi*b_hi + a_lo*b_hi + a_hi*b_lo      (tc::split_tf32; the dropped lo*lo term and
+// the truncations are <= 2^-21 relative), accumulated in fp32 in tensor memory: 6 tiles x 64
+// columns.  The weights arrive pre-split and pre-tiled per tap (lenet_upload) through a
+// 4-slot ring of bulk copies; one thread issues the copies and the MMAs (1350 per image).
+// ---------------------------------------------------------------------------------------------
+constexpr int TC_PIX = P1 * P1;                                   // 784 pixels per plane
+constexpr int TC_PLANE_BYTES = TC_PIX * 16;                       // 12544
+constexpr int TC_A_PLANES = 11;                                   // 5 hi, 5 lo, 1 zero
+constexpr int TC_A_BYTES = TC_A_PLANES * TC_PLANE_BYTES;          // 137984
+constexpr int TC_BTAP_FLOATS = 2 * 3 * 2 * 64 * 4;                // [hi/lo][k step][chunk][64 n][4] = 3072
+constexpr int TC_BTAP_BYTES = TC_BTAP_FLOATS * 4;                 // 12288
+constexpr int TC_BSLOTS = 4;
+constexpr int TC_SMEM_BYTES = TC_A_BYTES + TC_BSLOTS * TC_BTAP_BYTES + 128;
+constexpr int TC_TMEM_COLS = 512;                                 // 6 x 64 used; power of two
+
+// ip1 on the tensor cores (k_ip1_tc) reduces over K' = 144 positions x 52 channels (50 + 2 zero) =
+// 936 steps of 8, in chunks of 4 channels
+constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
+
+template <bool TILED_OUT>
+__global__ void __launch_bounds__(256, 1)
+k_conv2_tc(const float4* __restrict__ in /* [n][5][784] float4, see k_conv1_pool */,
+           const float* __restrict__ wtc /* [25][TC_BTAP_FLOATS] */, const float* __restrict__ bias,
+           float* __restrict__ out /* plain [n][50][12][12], or tiled for k_ip1_tc */) {
+  extern __shared__ __align__(128) uint8_t tc_smem[];
+  float4* A = reinterpret_cast<float4*>(tc_smem);
+  uint8_t* Bring = tc_smem + TC_A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + TC_A_BYTES + TC_BSLOTS * TC_BTAP_BYTES);
+  uint64_t* empty = full + TC_BSLOTS;
+  uint64_t* done = empty + TC_BSLOTS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int i = 0; i < TC_BSLOTS; i++) tc::mbar_init(&full[i], 1), tc::mbar_init(&empty[i], 1);
+    tc::mbar_init(done, 1);
+    tc::mbar_init_fence();
+  }
+  if (warp == 1) tc::tmem_alloc<TC_TMEM_COLS>(tmem_slot);
+  // stage the image: split every value into its two tf32 terms
+  const float4* src = in + (size_t)blockIdx.x * 5 * TC_PIX;
+  for (int i = tid; i < 5 * TC_PIX; i += 256) {
+    float4 v = src[i], h, l;
+    tc::split_tf32(v.x, h.x, l.x);
+    tc::split_tf32(v.y, h.y, l.y);
+    tc::split_tf32(v.z, h.z, l.z);
+    tc::split_tf32(v.w, h.w, l.w);
+    A[i] = h;
+    A[5 * TC_PIX + i] = l;
+  }
+  for (int i = tid; i < TC_PIX; i += 256) A[10 * TC_PIX + i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_tf32(128, 64);
+      const uint32_t a_base = tc::smem_u32(A), b_base = tc::smem_u32(Bring);
+      // 50 ring items: the 25 taps twice.  First the two cross terms (a_lo*b_hi, a_hi*b_lo; needs
+      // both weight halves), then the main term a_hi*b_hi (hi half only).  The tensor core
+      // truncates when it adds into the fp32 accumulator; with the small terms first the 150
+      // cross MMAs round against a tiny accumulator and only the 75 main MMAs contribute bias.
+      auto load = [&](int i) {
+        const int slot = i % TC_BSLOTS, t = i % 25;
+        const uint32_t bytes = i < 25 ? TC_BTAP_BYTES : TC_BTAP_BYTES / 2;
+        tc::mbar_expect_tx(&full[slot], bytes);
+        tc::bulk_g2s(Bring + slot * TC_BTAP_BYTES, wtc + (size_t)t * TC_BTAP_FLOATS, bytes, &full[slot]);
+      };
+      for (int i = 0; i < TC_BSLOTS - 1; i++) load(i);
+      for (int i = 0; i < 50; i++) {
+        const int slot = i % TC_BSLOTS, t = i % 25;
+        const bool cross = i < 25;
+        tc::mbar_wait(&full[slot], (i / TC_BSLOTS) & 1);
+        tc::fence_after_sync();
+        const int tap_pix = (t / 5) * P1 + t % 5;
+        const uint32_t b_slot = b_base + slot * TC_BTAP_BYTES;
+#pragma unroll
+        for (int s = 0; s < 3; s++) {
+          // chunk 0 = quad 2s, chunk 1 = quad 2s+1 (the zero plane, index 10, for s == 2)
+          const uint32_t a_hi = a_base + (2 * s) * TC_PLANE_BYTES, a_lo = a_base + (5 + 2 * s) * TC_PLANE_BYTES;
+          const uint32_t lbo_hi = (s < 2 ? 1 : 6) * TC_PLANE_BYTES, lbo_lo = TC_PLANE_BYTES;
+          const uint64_t b_hi = tc::smem_desc(b_slot + (0 * 3 + s) * 2048, 1024, 128);
+          const uint64_t b_lo = tc::smem_desc(b_slot + (1 * 3 + s) * 2048, 1024, 128);
+          for (int combo = cross ? 1 : 0; combo < (cross ? 3 : 1); combo++) {
+            const uint32_t a_addr = combo == 1 ? a_lo : a_hi, lbo = combo == 1 ? lbo_lo : lbo_hi;
+            const uint64_t b_desc = combo == 2 ? b_lo : b_hi;
+#pragma unroll
+            for (int tile = 0; tile < 6; tile++) {
+              const int pix = (tile / 3) * 8 * P1 + (tile % 3) * 8 + tap_pix;
+              tc::mma_tf32(tmem + tile * 64, tc::smem_desc(a_addr + pix * 16, lbo, P1 * 16), b_desc, idesc,
+                           (i | s | (combo - 1)) != 0);
+            }
+          }
+        }
+        tc::mma_commit(&empty[slot]);
+        // refill the slot of item i-1 with item i+3 once its MMAs have drained
+        const int ni = i + TC_BSLOTS - 1;
+        if (ni < 50) {
+          if (i >= 1) tc::mbar_wait(&empty[ni % TC_BSLOTS], ((i - 1) / TC_BSLOTS) & 1);
+          load(ni);
+        }
+      }
+      tc::mma_commit(done);
+    }
+    __syncwarp();
+  }
+  tc::mbar_wait(done, 0);
+  tc::fence_after_sync();
+
+  // epilogue: warp w reads TMEM lanes 32*(w%4)..+31 = image rows y0+4*(w%4)..+3, 8 x positions each;
+  // the 2x2 pooling partners are lanes ^1 (x) and ^8 (y).  After the two shuffles the four lanes
+  // of a pooling quad hold the same 50 values; lane q of the quad stores every fourth channel
+  // (plain layout) or every fourth 4-channel chunk (tiled layout for k_ip1_tc).
+  const int wq = warp & 3;
+  const int img = blockIdx.x;
+  for (int tile = warp >> 2; tile < 6; tile += 2) {
+    const int xr = tile % 3, yr = tile / 3;
+    if (yr == 1 && wq < 2) continue;  // rows 8..15 were produced by the y0 = 0 tile
+    float v[64];
+    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + tile * 64;
+    tc::tmem_ld32(taddr, v);
+    tc::tmem_ld32(taddr + 32, v + 32);
+    tc::tmem_ld_wait();
+    const int py = (yr * 8 + wq * 4 + (lane >> 3)) >> 1, px = (xr * 8 + (lane & 7)) >> 1;
+    const int q = (lane & 1) | ((lane >> 2) & 2);
+#pragma unroll
+    for (int ch = 0; ch < C2_OUT; ch++) {
+      float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
+      v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) + __ldg(&bias[ch]);
+    }
+    if (!TILED_OUT) {
+      float* o = out + (size_t)img * C2_OUT * P2 * P2;
+#pragma unroll
+      for (int ch = 0; ch < C2_OUT; ch++)
+        if ((ch & 3) == q) o[(ch * P2 + py) * P2 + px] = v[ch];
+    } else {
+      // [image tile of 128][chunk = pos*13 + ch/4][hi, lo][image row][4 channels]; channels 50, 51 are zero
+      v[50] = v[51] = 0.f;
+      float4* o = reinterpret_cast<float4*>(out) +
+                  ((size_t)(img >> 7) * I1_CHUNKS + (size_t)(py * P2 + px) * 13) * 256 + (img & 127);
+#pragma unroll
+      for (int cq = 0; cq < 13; cq++)
+        if ((cq & 3) == q) {
+          float4 h, l;
+          tc::split_tf32(v[4 * cq], h.x, l.x);
+          tc::split_tf32(v[4 * cq + 1], h.y, l.y);
+          tc::split_tf32(v[4 * cq + 2], h.z, l.z);
+          tc::split_tf32(v[4 * cq + 3], h.w, l.w);
+          o[cq * 256] = h;
+          o[cq * 256 + 128] = l;
+        }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<TC_TMEM_COLS>(tmem);
+}
+
+// ---------------------------------------------------------------------------------------------
+// ip1 (7200 -> 500) on the tensor cores, split-K.  CTA (it, z) computes, for the 128 images of
+// tile `it` and the K' steps [z*steps, (z+1)*steps), the partial products of ALL 500 outputs:
+//   D[out][image] (4 M tiles of 128 x N = 128, the whole 512-column tensor memory)
+// A = the weights, B = the pooled conv2 activations, both already split into tf32 hi / lo
+// terms and stored in the canonical no-swizzle K-major tiles (weights by lenet_upload,
+// activations by k_conv2_tc's epilogue), so one K step is two plain bulk copies (32 KB + 8 KB)
+// and 12 MMAs (4 M tiles x the three-term split); no thread touches the operands.  A 5-stage
+// ring keeps 4 steps of copies in flight.  Partials go to part[z][image][500] and are summed
+// in a fixed order by k_ip2 (deterministic).
+// ---------------------------------------------------------------------------------------------
+constexpr int I1_A_BYTES = 2 * 4 * 2 * 128 * 16;  // [hi/lo][M tile][chunk][128 rows][16 B] = 32768
+constexpr int I1_B_BYTES = 2 * 2 * 128 * 16;      // [chunk][hi/lo][128 images][16 B] = 8192
+constexpr int I1_STAGE_BYTES = I1_A_BYTES + I1_B_BYTES;
+constexpr int I1_STAGES = 5;
+constexpr int I1_SMEM_BYTES = I1_STAGES * I1_STAGE_BYTES + 128;
+
+__global__ void __launch_bounds__(256, 1)
+k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_tc */, const float* __restrict__ wtc /* [936][8192] */,
+         float* __restrict__ part, int n, int steps) {
+  extern __shared__ __align__(128) uint8_t tc_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + I1_STAGES * I1_STAGE_BYTES);
+  uint64_t* empty = full + I1_STAGES;
+  uint64_t* done = empty + I1_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int it = blockIdx.x, z = blockIdx.y;
+
+  if (tid == 0) {
+    for (int i = 0; i < I1_STAGES; i++) tc::mbar_init(&full[i], 1), tc::mbar_init(&empty[i], 1);
+    tc::mbar_init(done, 1);
+    tc::mbar_init_fence();
+  }
+  if (warp == 1) tc::tmem_alloc<512>(tmem_slot);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t idesc = tc::idesc_tf32(128, 128);
+      const uint32_t s_base = tc::smem_u32(tc_smem);
+      const float* srcA = wtc + (size_t)z * steps * (I1_A_BYTES / 4);
+      const float* srcB = act + ((size_t)it * I1_CHUNKS + (size_t)2 * z * steps) * 1024;
+      auto load = [&](int i) {
+        const int slot = i % I1_STAGES;
+        uint8_t* dst = tc_smem + slot * I1_STAGE_BYTES;
+        tc::mbar_expect_tx(&full[slot], I1_STAGE_BYTES);
+        tc::bulk_g2s(dst, srcA + (size_t)i * (I1_A_BYTES / 4), I1_A_BYTES, &full[slot]);
+        tc::bulk_g2s(dst + I1_A_BYTES, srcB + (size_t)i * (I1_B_BYTES / 4), I1_B_BYTES, &full[slot]);
+      };
+      for (int i = 0; i < I1_STAGES - 1 && i < steps; i++) load(i);
+      for (int i = 0; i < steps; i++) {
+        const int slot = i % I1_STAGES;
+        tc::mbar_wait(&full[slot], (i / I1_STAGES) & 1);
+        tc::fence_after_sync();
+        const uint32_t sa = s_base + slot * I1_STAGE_BYTES, sb = sa + I1_A_BYTES;
+#pragma unroll
+        for (int combo = 0; combo < 3; combo++) {
+          const int pa = combo == 1, pb = combo == 2;
+          const uint64_t b_desc = tc::smem_desc(sb + pb * 2048, 4096, 128);
+#pragma unroll
+          for (int mt = 0; mt < 4; mt++)
+            tc::mma_tf32(tmem + mt * 128, tc::smem_desc(sa + ((pa * 4 + mt) * 2) * 2048, 2048, 128), b_desc, idesc,
+                         (i | combo) != 0);
+        }
+        tc::mma_commit(&empty[slot]);
+        const int ni = i + I1_STAGES - 1;
+        if (ni < steps) {
+          if (i >= 1) tc::mbar_wait(&empty[ni % I1_STAGES], ((i - 1) / I1_STAGES) & 1);
+          load(ni);
+        }
+      }
+      tc::mma_commit(done);
+    }
+    __syncwarp();
+  }
+  tc::mbar_wait(done, 0);
+  tc::fence_after_sync();
+
+  // epilogue: lane = output row of the M tile, columns = images; consecutive lanes -> consecutive outputs
+  const int wq = warp & 3, half = warp >> 2;
+  float* P = part + (size_t)z * n * IP1_OUT;
+#pragma unroll 1
+  for (int mt = 0; mt < 4; mt++) {
+    const int o = mt * 128 + wq * 32 + lane;
+#pragma unroll 1
+    for (int cb = 0; cb < 2; cb++) {
+      const int col0 = half * 64 + cb * 32;
+      if (it * 128 + col0 >= n) continue;
+      float v[32];
+      tc::tmem_ld32(tmem + ((uint32_t)(wq * 32) << 16) + mt * 128 + col0, v);
+      tc::tmem_ld_wait();
+      if (o < IP1_OUT) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+          const int img = it * 128 + col0 + j;
+          if (img < n) P[(size_t)img * IP1_OUT + o] = v[j];
+        }
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<512>(tmem);
 }
 
 // ip1, split-K: part[z][n][500] = X[n][k-range z] . W[500][k-range z]^T.  64x64 tile, BK 16,
@@ -220,6 +506,45 @@ int lenet_upload(ag2_ctx* c) {
     AG2_CUDA(c, cudaMemcpyAsync(bufs[i]->p, L.host[i].data(), sizes[i] * sizeof(float), cudaMemcpyHostToDevice,
                                 c->stream));
   }
+  // conv2 weights for k_conv2_tc: per tap [hi/lo][k step s][chunk][64 out channels][4 in channels],
+  // in channel = 8s + 4*chunk + e; rows >= 50 and channels >= 20 are zero
+  std::vector<float> wtc((size_t)25 * TC_BTAP_FLOATS, 0.f);
+  for (int t = 0; t < 25; t++)
+    for (int s = 0; s < 3; s++)
+      for (int ck = 0; ck < 2; ck++)
+        for (int n = 0; n < C2_OUT; n++)
+          for (int e = 0; e < 4; e++) {
+            const int ch = 8 * s + 4 * ck + e;
+            if (ch >= 20) continue;
+            float hi, lo;
+            tc::split_tf32(L.host[2][((size_t)n * 20 + ch) * 25 + t], hi, lo);
+            wtc[(size_t)t * TC_BTAP_FLOATS + (((0 * 3 + s) * 2 + ck) * 64 + n) * 4 + e] = hi;
+            wtc[(size_t)t * TC_BTAP_FLOATS + (((1 * 3 + s) * 2 + ck) * 64 + n) * 4 + e] = lo;
+          }
+  AG2_CUDA(c, L.c2w_tc.reserve(wtc.size()));
+  AG2_CUDA(c, cudaMemcpyAsync(L.c2w_tc.p, wtc.data(), wtc.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  // ip1 weights for k_ip1_tc: [k step][hi/lo][M tile][chunk][128 outputs][4]; K' index
+  // k' = 8*step + 4*chunk + e = position*52 + channel (channels 50, 51 and outputs >= 500 are zero)
+  {
+    std::vector<float> w1((size_t)I1_KSTEPS * (I1_A_BYTES / 4), 0.f);
+    const std::vector<float>& W = L.host[4];
+    for (int ks = 0; ks < I1_KSTEPS; ks++)
+      for (int ck = 0; ck < 2; ck++)
+        for (int e = 0; e < 4; e++) {
+          const int kk = 8 * ks + 4 * ck + e, pos = kk / 52, ch = kk % 52;
+          if (ch >= C2_OUT) continue;
+          for (int o = 0; o < IP1_OUT; o++) {
+            float hi, lo;
+            tc::split_tf32(W[(size_t)o * 7200 + ch * 144 + pos], hi, lo);
+            const size_t base = (size_t)ks * (I1_A_BYTES / 4) + ((size_t)((o >> 7) * 2 + ck) * 128 + (o & 127)) * 4 + e;
+            w1[base] = hi;
+            w1[base + 4 * 2 * 128 * 4] = lo;
+          }
+        }
+    AG2_CUDA(c, L.i1w_tc.reserve(w1.size()));
+    AG2_CUDA(c, cudaMemcpyAsync(L.i1w_tc.p, w1.data(), w1.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   L.loaded = true;
   return AG2_OK;
@@ -232,26 +557,63 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
   const LeNetDev& L = c->net;
   const size_t chunk_max = 4096;
   const size_t chunk = std::min(n, chunk_max);
-  const int mtiles = (int)((chunk + 63) / 64), ntiles = (IP1_OUT + 63) / 64;
-  // split K so that ip1 launches >= ~2 CTAs per SM (450 k-steps of 16 in total)
-  int splits = std::max(1, std::min(30, (2 * c->sm_count + mtiles * ntiles - 1) / (mtiles * ntiles)));
-  const int steps_per_split = (450 + splits - 1) / splits;
-  splits = (450 + steps_per_split - 1) / steps_per_split;
-  const size_t per_img = (size_t)20 * P1 * P1 + (size_t)50 * P2 * P2 + (size_t)splits * IP1_OUT;
-  AG2_CUDA(c, c->act.reserve(chunk * per_img));
+  // test hook: AG2_LENET_SIMT=1 runs the fp32 CUDA-core kernels instead of the tensor-core ones,
+  // 2 = tensor-core conv2 with the CUDA-core ip1
+  static const int simt = getenv("AG2_LENET_SIMT") ? atoi(getenv("AG2_LENET_SIMT")) : 0;
+  int splits, steps_per_split;
+  size_t a2_floats;
+  const int itiles = (int)((chunk + 127) / 128);
+  if (simt) {
+    const int mtiles = (int)((chunk + 63) / 64), ntiles = (IP1_OUT + 63) / 64;
+    // split K so that ip1 launches >= ~2 CTAs per SM (450 k-steps of 16 in total)
+    splits = std::max(1, std::min(30, (2 * c->sm_count + mtiles * ntiles - 1) / (mtiles * ntiles)));
+    steps_per_split = (450 + splits - 1) / splits;
+    splits = (450 + steps_per_split - 1) / steps_per_split;
+    a2_floats = chunk * 50 * P2 * P2;
+  } else {
+    // A divisor of the 936 K' steps: as many splits as fit one wave of CTAs, but never fewer than
+    // 39 (<= 24 steps = 72 MMAs per accumulator).  The tensor core truncates when it adds into
+    // the fp32 accumulator, a bias of ~4e-8 relative per MMA that grows linearly with the chain;
+    // across splits the partials are summed with round-to-nearest by k_ip2.
+    static const int divs[] = {117, 104, 78, 72, 52, 39};
+    splits = 39;
+    for (int d : divs)
+      if ((long)d * itiles <= c->sm_count) {
+        splits = d;
+        break;
+      }
+    steps_per_split = I1_KSTEPS / splits;
+    a2_floats = (size_t)itiles * I1_CHUNKS * 1024;
+  }
+  AG2_CUDA(c, c->act.reserve(chunk * 20 * P1 * P1 + a2_floats + (size_t)splits * chunk * IP1_OUT));
   const size_t smem2 = (size_t)(20 * 28 * 29 + 10 * 500) * sizeof(float);
   AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_pool, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
   for (size_t off = 0; off < n; off += chunk_max) {
     const size_t m = std::min(chunk_max, n - off);
     float* a1 = c->act.p;
-    float* a2 = a1 + m * 20 * P1 * P1;
-    float* part = a2 + m * 50 * P2 * P2;
-    k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p, a1);
+    float* a2 = a1 + chunk * 20 * P1 * P1;
+    float* part = a2 + a2_floats;
+    const float4* a1q = reinterpret_cast<const float4*>(a1);
+    k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
+                                              reinterpret_cast<float4*>(a1));
     AG2_LAUNCH_CHECK(c);
-    k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
+    if (simt == 1)
+      k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
+    else if (simt)
+      k_conv2_tc<false><<<(unsigned)m, 256, TC_SMEM_BYTES, st>>>(a1q, L.c2w_tc.p, L.c2b.p, a2);
+    else
+      k_conv2_tc<true><<<(unsigned)m, 256, TC_SMEM_BYTES, st>>>(a1q, L.c2w_tc.p, L.c2b.p, a2);
     AG2_LAUNCH_CHECK(c);
-    dim3 g1((unsigned)((m + 63) / 64), ntiles, splits);
-    k_ip1_partial<<<g1, 256, 0, st>>>(a2, L.i1w.p, part, (int)m, steps_per_split);
+    if (simt) {
+      dim3 g1((unsigned)((m + 63) / 64), (IP1_OUT + 63) / 64, splits);
+      k_ip1_partial<<<g1, 256, 0, st>>>(a2, L.i1w.p, part, (int)m, steps_per_split);
+    } else {
+      dim3 g1((unsigned)((m + 127) / 128), splits);
+      k_ip1_tc<<<g1, 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
+    }
     AG2_LAUNCH_CHECK(c);
     k_ip2<<<(unsigned)((m * 32 + 255) / 256), 256, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p,
                                                             d_logits + 2 * off, (int)m);

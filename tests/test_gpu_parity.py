@@ -142,6 +142,28 @@ def test_classify_images_direct(tiny_scene):
     assert np.all(np.abs(gl - ol) <= tol), np.abs(gl - ol).max()
 
 
+@pytest.mark.parametrize("n", [1, 129, 4500])
+def test_classify_images_batch_sizes(n):
+    """Image-tile / split-K / chunk boundaries of the tensor-core LeNet: one image, one image past a
+    128-image tile, and more than one 4096-image chunk.  The batch repeats 43 base images, so the
+    oracle classifies 43 and every repeat must reproduce its logits bit for bit."""
+    w = ob.xavier_weights(11, bias_scale=0.2)
+    p = make_params(capi.MODE_PREDICTION)
+    g = capi.Context(p); o = ob.context(p)
+    g.set_lenet_weights(w); o.set_lenet_weights(w)
+    rng = np.random.default_rng(17)
+    base = rng.integers(0, 256, size=(43, 60, 60, 3), dtype=np.uint8)
+    base[rng.random(base.shape) < 0.7] = 0  # sparse, like the occupancy planes of real grasp images
+    idx = np.arange(n) % 43
+    gl = g.classify_images(np.ascontiguousarray(base[idx]))
+    ol = o.classify_images(base[: min(n, 43)])
+    tol = np.maximum(1e-3, 1e-5 * np.abs(ol))
+    assert np.all(np.abs(gl[: len(ol)] - ol) <= tol), np.abs(gl[: len(ol)] - ol).max()
+    for r in range(43, n, 43):
+        m = min(43, n - r)
+        assert np.array_equal(gl[r:r + m], gl[:m]), r
+
+
 def test_sample_points_and_precomputed_normals(tiny_scene):
     sc = tiny_scene
     p = make_params(capi.MODE_GEOMETRIC)
