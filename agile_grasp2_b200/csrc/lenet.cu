@@ -471,15 +471,19 @@ k_ip1_partial(const float* __restrict__ X, const float* __restrict__ W, float* _
   }
 }
 
-// split-K reduction + ip1 bias + ReLU + ip2: logits[n][2]; one warp per image
-__global__ void k_ip2(const float* __restrict__ part, int splits, const float* __restrict__ b1,
-                      const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ logits, int n) {
-  int img = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (img >= n) return;
+// split-K reduction + ip1 bias + ReLU + ip2: logits[n][2]; one CTA of 128 threads per image, the
+// partials of one output are summed in split order, the 500 products in a fixed tree (deterministic)
+__global__ void __launch_bounds__(128)
+k_ip2(const float* __restrict__ part, int splits, const float* __restrict__ b1, const float* __restrict__ W,
+      const float* __restrict__ b, float* __restrict__ logits, int n) {
+  __shared__ float red[2][4];
+  const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   float a0 = 0.f, a1 = 0.f;
-  for (int k = lane; k < IP1_OUT; k += 32) {
+  for (int k = tid; k < IP1_OUT; k += 128) {
+    const float* p = part + (size_t)img * IP1_OUT + k;
     float h = 0.f;
-    for (int z = 0; z < splits; z++) h += part[((size_t)z * n + img) * IP1_OUT + k];
+#pragma unroll 13
+    for (int z = 0; z < splits; z++) h += p[(size_t)z * n * IP1_OUT];
     h = fmaxf(h + b1[k], 0.f);
     a0 += W[k] * h;
     a1 += W[IP1_OUT + k] * h;
@@ -488,10 +492,9 @@ __global__ void k_ip2(const float* __restrict__ part, int splits, const float* _
     a0 += __shfl_xor_sync(AG2_FULL, a0, o);
     a1 += __shfl_xor_sync(AG2_FULL, a1, o);
   }
-  if (lane == 0) {
-    logits[2 * img] = a0 + b[0];
-    logits[2 * img + 1] = a1 + b[1];
-  }
+  if (lane == 0) red[0][warp] = a0, red[1][warp] = a1;
+  __syncthreads();
+  if (tid < 2) logits[2 * img + tid] = ((red[tid][0] + red[tid][1]) + (red[tid][2] + red[tid][3])) + b[tid];
 }
 
 }  // namespace
@@ -615,7 +618,7 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
       k_ip1_tc<<<g1, 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
     }
     AG2_LAUNCH_CHECK(c);
-    k_ip2<<<(unsigned)((m * 32 + 255) / 256), 256, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p,
+    k_ip2<<<(unsigned)m, 128, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p,
                                                             d_logits + 2 * off, (int)m);
     AG2_LAUNCH_CHECK(c);
   }
