@@ -189,14 +189,27 @@ k_conv2_tc(const float4* __restrict__ in /* [n][5][784] float4, see k_conv1_pool
   if (warp == 1) tc::tmem_alloc<TC_TMEM_COLS>(tmem_slot);
   // stage the image: split every value into its two tf32 terms
   const float4* src = in + (size_t)blockIdx.x * 5 * TC_PIX;
-  for (int i = tid; i < 5 * TC_PIX; i += 256) {
-    float4 v = src[i], h, l;
-    tc::split_tf32(v.x, h.x, l.x);
-    tc::split_tf32(v.y, h.y, l.y);
-    tc::split_tf32(v.z, h.z, l.z);
-    tc::split_tf32(v.w, h.w, l.w);
-    A[i] = h;
-    A[5 * TC_PIX + i] = l;
+  {
+    constexpr int kPer = (5 * TC_PIX + 255) / 256;  // 16 float4 per thread, all loads in flight at once
+    float4 v[kPer];
+#pragma unroll
+    for (int u = 0; u < kPer; u++) {
+      const int i = tid + u * 256;
+      v[u] = i < 5 * TC_PIX ? __ldg(&src[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kPer; u++) {
+      const int i = tid + u * 256;
+      float4 h, l;
+      tc::split_tf32(v[u].x, h.x, l.x);
+      tc::split_tf32(v[u].y, h.y, l.y);
+      tc::split_tf32(v[u].z, h.z, l.z);
+      tc::split_tf32(v[u].w, h.w, l.w);
+      if (i < 5 * TC_PIX) {
+        A[i] = h;
+        A[5 * TC_PIX + i] = l;
+      }
+    }
   }
   for (int i = tid; i < TC_PIX; i += 256) A[10 * TC_PIX + i] = make_float4(0.f, 0.f, 0.f, 0.f);
   tc::fence_async_smem();
@@ -206,55 +219,59 @@ k_conv2_tc(const float4* __restrict__ in /* [n][5][784] float4, see k_conv1_pool
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      const uint32_t idesc = tc::idesc_tf32(128, 64);
-      const uint32_t a_base = tc::smem_u32(A), b_base = tc::smem_u32(Bring);
-      // 50 ring items: the 25 taps twice.  First the two cross terms (a_lo*b_hi, a_hi*b_lo; needs
-      // both weight halves), then the main term a_hi*b_hi (hi half only).  The tensor core
-      // truncates when it adds into the fp32 accumulator; with the small terms first the 150
-      // cross MMAs round against a tiny accumulator and only the 75 main MMAs contribute bias.
-      auto load = [&](int i) {
-        const int slot = i % TC_BSLOTS, t = i % 25;
-        const uint32_t bytes = i < 25 ? TC_BTAP_BYTES : TC_BTAP_BYTES / 2;
+    // the whole warp walks the ring (converged); one elected lane issues copies, MMAs and commits
+    const bool leader = tc::elect_one();
+    const uint32_t idesc = tc::idesc_tf32(128, 64);
+    const uint32_t a_base = tc::smem_u32(A), b_base = tc::smem_u32(Bring);
+    // 50 ring items: the 25 taps twice.  First the two cross terms (a_lo*b_hi, a_hi*b_lo; needs
+    // both weight halves), then the main term a_hi*b_hi (hi half only).  The tensor core
+    // truncates when it adds into the fp32 accumulator; with the small terms first the 150
+    // cross MMAs round against a tiny accumulator and only the 75 main MMAs contribute bias.
+    auto load = [&](int i) {
+      const int slot = i % TC_BSLOTS, t = i % 25;
+      const uint32_t bytes = i < 25 ? TC_BTAP_BYTES : TC_BTAP_BYTES / 2;
+      if (leader) {
         tc::mbar_expect_tx(&full[slot], bytes);
         tc::bulk_g2s(Bring + slot * TC_BTAP_BYTES, wtc + (size_t)t * TC_BTAP_FLOATS, bytes, &full[slot]);
-      };
-      for (int i = 0; i < TC_BSLOTS - 1; i++) load(i);
-      for (int i = 0; i < 50; i++) {
-        const int slot = i % TC_BSLOTS, t = i % 25;
-        const bool cross = i < 25;
-        tc::mbar_wait(&full[slot], (i / TC_BSLOTS) & 1);
-        tc::fence_after_sync();
-        const int tap_pix = (t / 5) * P1 + t % 5;
-        const uint32_t b_slot = b_base + slot * TC_BTAP_BYTES;
+      }
+    };
+    // descriptor halves that do not change: high word (SBO, version) and the LBO field
+    const uint64_t a_hi64 = tc::smem_desc(0, 0, P1 * 16), b_hi64 = tc::smem_desc(0, 1024, 128);
+    for (int i = 0; i < TC_BSLOTS - 1; i++) load(i);
+    for (int i = 0; i < 50; i++) {
+      const int slot = i % TC_BSLOTS, t = i % 25;
+      const bool cross = i < 25;
+      tc::mbar_wait(&full[slot], (i / TC_BSLOTS) & 1);
+      tc::fence_after_sync();
+      const uint32_t tap_off = (uint32_t)((t / 5) * P1 + t % 5);  // in 16-byte units (one pixel)
+      const uint32_t b_slot = (b_base + slot * TC_BTAP_BYTES) >> 4;
+      for (int s = 0; s < 3; s++) {
+        // chunk 0 = quad 2s, chunk 1 = quad 2s+1 (the zero plane, index 10, for s == 2)
+        const uint32_t a_hi = ((a_base + (2 * s) * TC_PLANE_BYTES) >> 4) + tap_off;
+        const uint32_t a_lo = ((a_base + (5 + 2 * s) * TC_PLANE_BYTES) >> 4) + tap_off;
+        const uint32_t lbo_hi = ((s < 2 ? 1 : 6) * TC_PLANE_BYTES) >> 4, lbo_lo = TC_PLANE_BYTES >> 4;
+        for (int combo = cross ? 1 : 0; combo < (cross ? 3 : 1); combo++) {
+          const uint64_t a_desc0 = a_hi64 | (uint64_t)(combo == 1 ? a_lo : a_hi) |
+                                   ((uint64_t)(combo == 1 ? lbo_lo : lbo_hi) << 16);
+          const uint64_t b_desc = b_hi64 | (uint64_t)(b_slot + ((combo == 2 ? 3 : 0) + s) * 128);
+          const uint32_t acc = (i | s | (combo - 1)) != 0;
+          if (leader) {
 #pragma unroll
-        for (int s = 0; s < 3; s++) {
-          // chunk 0 = quad 2s, chunk 1 = quad 2s+1 (the zero plane, index 10, for s == 2)
-          const uint32_t a_hi = a_base + (2 * s) * TC_PLANE_BYTES, a_lo = a_base + (5 + 2 * s) * TC_PLANE_BYTES;
-          const uint32_t lbo_hi = (s < 2 ? 1 : 6) * TC_PLANE_BYTES, lbo_lo = TC_PLANE_BYTES;
-          const uint64_t b_hi = tc::smem_desc(b_slot + (0 * 3 + s) * 2048, 1024, 128);
-          const uint64_t b_lo = tc::smem_desc(b_slot + (1 * 3 + s) * 2048, 1024, 128);
-          for (int combo = cross ? 1 : 0; combo < (cross ? 3 : 1); combo++) {
-            const uint32_t a_addr = combo == 1 ? a_lo : a_hi, lbo = combo == 1 ? lbo_lo : lbo_hi;
-            const uint64_t b_desc = combo == 2 ? b_lo : b_hi;
-#pragma unroll
-            for (int tile = 0; tile < 6; tile++) {
-              const int pix = (tile / 3) * 8 * P1 + (tile % 3) * 8 + tap_pix;
-              tc::mma_tf32(tmem + tile * 64, tc::smem_desc(a_addr + pix * 16, lbo, P1 * 16), b_desc, idesc,
-                           (i | s | (combo - 1)) != 0);
-            }
+            for (int tile = 0; tile < 6; tile++)  // the start address field never carries (addresses < 256 KB)
+              tc::mma_tf32(tmem + tile * 64, a_desc0 + (uint64_t)((tile / 3) * 8 * P1 + (tile % 3) * 8), b_desc, idesc,
+                           acc);
           }
         }
-        tc::mma_commit(&empty[slot]);
-        // refill the slot of item i-1 with item i+3 once its MMAs have drained
-        const int ni = i + TC_BSLOTS - 1;
-        if (ni < 50) {
-          if (i >= 1) tc::mbar_wait(&empty[ni % TC_BSLOTS], ((i - 1) / TC_BSLOTS) & 1);
-          load(ni);
-        }
       }
-      tc::mma_commit(done);
+      if (leader) tc::mma_commit(&empty[slot]);
+      // refill the slot of item i-1 with item i+3 once its MMAs have drained
+      const int ni = i + TC_BSLOTS - 1;
+      if (ni < 50) {
+        if (i >= 1) tc::mbar_wait(&empty[ni % TC_BSLOTS], ((i - 1) / TC_BSLOTS) & 1);
+        load(ni);
+      }
     }
+    if (leader) tc::mma_commit(done);
     __syncwarp();
   }
   tc::mbar_wait(done, 0);
@@ -349,42 +366,46 @@ k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_tc */, const float*
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      const uint32_t idesc = tc::idesc_tf32(128, 128);
-      const uint32_t s_base = tc::smem_u32(tc_smem);
-      const float* srcA = wtc + (size_t)z * steps * (I1_A_BYTES / 4);
-      const float* srcB = act + ((size_t)it * I1_CHUNKS + (size_t)2 * z * steps) * 1024;
-      auto load = [&](int i) {
-        const int slot = i % I1_STAGES;
-        uint8_t* dst = tc_smem + slot * I1_STAGE_BYTES;
+    const bool leader = tc::elect_one();
+    const uint32_t idesc = tc::idesc_tf32(128, 128);
+    const uint32_t s_base = tc::smem_u32(tc_smem);
+    const float* srcA = wtc + (size_t)z * steps * (I1_A_BYTES / 4);
+    const float* srcB = act + ((size_t)it * I1_CHUNKS + (size_t)2 * z * steps) * 1024;
+    auto load = [&](int i) {
+      const int slot = i % I1_STAGES;
+      uint8_t* dst = tc_smem + slot * I1_STAGE_BYTES;
+      if (leader) {
         tc::mbar_expect_tx(&full[slot], I1_STAGE_BYTES);
         tc::bulk_g2s(dst, srcA + (size_t)i * (I1_A_BYTES / 4), I1_A_BYTES, &full[slot]);
         tc::bulk_g2s(dst + I1_A_BYTES, srcB + (size_t)i * (I1_B_BYTES / 4), I1_B_BYTES, &full[slot]);
-      };
-      for (int i = 0; i < I1_STAGES - 1 && i < steps; i++) load(i);
-      for (int i = 0; i < steps; i++) {
-        const int slot = i % I1_STAGES;
-        tc::mbar_wait(&full[slot], (i / I1_STAGES) & 1);
-        tc::fence_after_sync();
-        const uint32_t sa = s_base + slot * I1_STAGE_BYTES, sb = sa + I1_A_BYTES;
+      }
+    };
+    const uint64_t a_hi64 = tc::smem_desc(0, 2048, 128), b_hi64 = tc::smem_desc(0, 4096, 128);
+    for (int i = 0; i < I1_STAGES - 1 && i < steps; i++) load(i);
+    for (int i = 0; i < steps; i++) {
+      const int slot = i % I1_STAGES;
+      tc::mbar_wait(&full[slot], (i / I1_STAGES) & 1);
+      tc::fence_after_sync();
+      const uint32_t sa = (s_base + slot * I1_STAGE_BYTES) >> 4, sb = sa + (I1_A_BYTES >> 4);
+      if (leader) {
 #pragma unroll
-        for (int combo = 0; combo < 3; combo++) {
+        for (int combo = 1; combo < 4; combo++) {  // cross terms first, main term last (see k_conv2_tc)
           const int pa = combo == 1, pb = combo == 2;
-          const uint64_t b_desc = tc::smem_desc(sb + pb * 2048, 4096, 128);
+          const uint64_t b_desc = b_hi64 | (uint64_t)(sb + pb * 128);
 #pragma unroll
           for (int mt = 0; mt < 4; mt++)
-            tc::mma_tf32(tmem + mt * 128, tc::smem_desc(sa + ((pa * 4 + mt) * 2) * 2048, 2048, 128), b_desc, idesc,
-                         (i | combo) != 0);
+            tc::mma_tf32(tmem + mt * 128, a_hi64 | (uint64_t)(sa + ((pa * 4 + mt) * 2) * 128), b_desc, idesc,
+                         (i | (combo - 1)) != 0);
         }
         tc::mma_commit(&empty[slot]);
-        const int ni = i + I1_STAGES - 1;
-        if (ni < steps) {
-          if (i >= 1) tc::mbar_wait(&empty[ni % I1_STAGES], ((i - 1) / I1_STAGES) & 1);
-          load(ni);
-        }
       }
-      tc::mma_commit(done);
+      const int ni = i + I1_STAGES - 1;
+      if (ni < steps) {
+        if (i >= 1) tc::mbar_wait(&empty[ni % I1_STAGES], ((i - 1) / I1_STAGES) & 1);
+        load(ni);
+      }
     }
+    if (leader) tc::mma_commit(done);
     __syncwarp();
   }
   tc::mbar_wait(done, 0);

@@ -154,19 +154,40 @@ def roofline_for(phase_ms, st, n_points, peaks):
         return {"kernel": "lenet (conv1+conv2+ip1+ip2)", "bound": "tensor", "achieved": work / t / 1e12,
                 "peak": peaks["bf16_tflops"], "unit": "TFLOP/s", "frac": work / t / 1e12 / peaks["bf16_tflops"],
                 "traffic": traffic, "peak_src": peaks["src"], "ms": phase_ms[dom]}
+    sm_hz = 148 * 1.965e9
+    issue = None
     if dom == "hands":
         work = 25.0 * st["sum_neighbors_hands"] + 192.0 * st["num_hypotheses"]
+        # 13 ops per neighbour (distance + crop), 58 per cropped point and orientation,
+        # 27 per in-box point of an emitted hand; FP64, nominal 64 FMA/clk/SM
+        ops = 13.0 * st["sum_neighbors_hands"] + 58.0 * 8 * st["sum_cropped"] + 27.0 * st["sum_in_box"]
+        issue = {"ops": ops, "achieved": ops / t / 1e12, "peak": 2 * 64 * sm_hz / 1e12, "unit": "TFLOP/s (fp64, nominal peak)"}
     elif dom == "normals":
         work = 24.0 * n_points
+        # 26 flop per neighbour + ~120 per point (eigen33 + flip); FP32, 128 FMA/clk/SM
+        ops = 26.0 * st["sum_neighbors_normals"] + 120.0 * n_points
+        issue = {"ops": ops, "achieved": ops / t / 1e12, "peak": 2 * 128 * sm_hz / 1e12, "unit": "TFLOP/s (fp32, nominal peak)"}
     elif dom == "grid":
         work = 50.0 * n_points
     elif dom == "render":
         work = 24.0 * st["sum_in_box"] + 10800.0 * st["num_pruned"]
     else:
         work = 25.0 * st["num_samples"] * 50
-    return {"kernel": dom, "bound": "hbm", "achieved": work / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-            "frac": work / t / 1e9 / peaks["hbm_gbs"], "traffic": traffic, "peak_src": peaks["src"],
-            "ms": phase_ms[dom]}
+    out = {"kernel": dom, "bound": "hbm", "achieved": work / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+           "frac": work / t / 1e9 / peaks["hbm_gbs"], "traffic": traffic, "peak_src": peaks["src"],
+           "ms": phase_ms[dom]}
+    if issue:
+        # the kernel is issue-bound, not HBM-bound (its gathers are L1/L2 hits): the compulsory-byte
+        # fraction above is small by construction; this is the same kernel against the SM's FP pipe
+        issue["frac"] = issue["achieved"] / issue["peak"]
+        out["issue"] = issue
+    if phase_ms.get("lenet"):
+        tl = phase_ms["lenet"] * 1e-3
+        wl = 45.41e6 * st["num_pruned"]
+        out["lenet_tensor"] = {"bound": "tensor", "achieved": wl / tl / 1e12, "peak": peaks["bf16_tflops"],
+                               "unit": "TFLOP/s", "frac": wl / tl / 1e12 / peaks["bf16_tflops"], "ms": phase_ms["lenet"],
+                               "note": "algorithmic flop only; the three tf32 passes of the split are not counted"}
+    return out
 
 
 def run_reference(args):
