@@ -363,6 +363,11 @@ class Context:
         self._call("set_sample_indices", _fptr(idx), C.c_size_t(idx.size))
         self.n_samples = idx.size
 
+    def set_sample_indices_device(self, d_ptr: int, n: int):
+        """Sample indices already in device memory (int32), e.g. after an NCCL broadcast."""
+        self._call("set_sample_indices_device", C.c_void_p(d_ptr), C.c_size_t(n))
+        self.n_samples = n
+
     def set_sample_points(self, xyz):
         xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
         self._call("set_sample_points", _fptr(xyz), C.c_size_t(xyz.shape[0]))
@@ -370,6 +375,10 @@ class Context:
 
     def set_sample_id_offset(self, first: int):
         self._call("set_sample_id_offset", C.c_int64(first))
+
+    def set_sample_id_map(self, first: int, stride: int):
+        """Sample s of this context is sample first + stride*s of the whole list (strided shard)."""
+        self._call("set_sample_id_map", C.c_int64(first), C.c_int64(stride))
 
     # -- stages
     def compute_normals(self):
@@ -428,6 +437,12 @@ class Context:
         self.n_samples = int(n.value)
         return idx[: int(n.value)].copy()
 
+    def sample_indices(self) -> np.ndarray:
+        n = C.c_size_t()
+        idx = np.zeros(max(self.n_samples, 1), dtype=np.int32)
+        self._call("get_sample_indices", _fptr(idx), C.c_size_t(idx.size), C.byref(n))
+        return idx[: int(n.value)].copy()
+
     def find_clusters(self, which_src: int):
         """HandleSearch::findClusters on list `which_src`; result in LIST_CLUSTERS."""
         self._call("find_clusters", C.c_int(which_src))
@@ -471,6 +486,26 @@ class Context:
         got = C.c_size_t()
         self._call("get_hypotheses", C.c_int(which), _fptr(out), C.c_size_t(out.size), C.byref(got))
         return out[: int(got.value)]
+
+    def normals_shard_points(self, world: int) -> int:
+        n = C.c_size_t()
+        self._call("normals_shard_points", C.c_int(world), C.byref(n))
+        return int(n.value)
+
+    def compute_normals_shard(self, rank: int, world: int, d_out: int, cap_points: int) -> int:
+        n = C.c_size_t()
+        self._call("compute_normals_shard", C.c_int(rank), C.c_int(world), C.c_void_p(d_out), C.c_size_t(cap_points),
+                   C.byref(n))
+        return int(n.value)
+
+    def set_normals_shards(self, d_all: int, cap_points: int, world: int):
+        self._call("set_normals_shards", C.c_void_p(d_all), C.c_size_t(cap_points), C.c_int(world))
+
+    def copy_hypotheses_device(self, which: int, d_ptr: int, cap: int) -> int:
+        """Copies list `which` into caller-owned device memory of `cap` records (rest zero-filled)."""
+        got = C.c_size_t()
+        self._call("copy_hypotheses_device", C.c_int(which), C.c_void_p(d_ptr), C.c_size_t(cap), C.byref(got))
+        return int(got.value)
 
     def stats(self) -> dict:
         s = Stats()

@@ -124,6 +124,7 @@ struct ag2_ctx {
   ag2::DevBuf<float> normals_in;   // 3n when precomputed normals were given
   bool normals_given = false;
   bool have_normals = false;       // sorted normals complete for all points
+  int nrm_rank = 0, nrm_world = 1; // normals_compute covers the granules of this shard only (multi-GPU)
   float min_z = 0.f;               // pcl::getMinMax3D z (grasp_detector.cpp:153)
 
   // grid
@@ -148,10 +149,11 @@ struct ag2_ctx {
   // samples
   bool use_points = false;
   size_t num_samples = 0;
-  int64_t sample_id_offset = 0;
+  int64_t sample_id_offset = 0, sample_id_stride = 1;
   ag2::DevBuf<int32_t> sample_idx;
   ag2::DevBuf<double> sample_xyz;
   std::vector<int32_t> h_sample_idx;
+  bool h_sample_idx_stale = false;  // indices were set from device memory; host copy fetched on demand
   std::vector<double> h_sample_xyz;
 
   // hot-path outputs
@@ -220,6 +222,9 @@ int grid_build(ag2_ctx* c);                         // grid.cu
 GridDev grid_dev(const ag2_ctx* c);
 int exclusive_scan_u32(ag2_ctx* c, uint32_t* data, size_t n);  // in place, total at data[n]
 int normals_compute(ag2_ctx* c);                    // normals.cu
+uint32_t normals_shard_points(uint32_t n, int rank, int world);
+int normals_shard_compute(ag2_ctx* c, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned);
+int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, int world);
 int frames_compute(ag2_ctx* c);                     // frames.cu
 int hands_compute(ag2_ctx* c);                      // hands.cu
 int lists_build_after_hands(ag2_ctx* c);            // select.cu

@@ -88,6 +88,12 @@ static void mat4_inv(const double* m, double* o) {
     for (int j = 0; j < 4; j++) o[4 * i + j] = a[i][4 + j];
 }
 
+namespace {
+__global__ void k_count_bad_indices(const int32_t* __restrict__ idx, size_t n, size_t limit, uint32_t* __restrict__ bad) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (idx[i] < 0 || (size_t)idx[i] >= limit)) atomicAdd(bad, 1u);
+}
+}  // namespace
 }  // namespace ag2
 
 using namespace ag2;
@@ -332,6 +338,7 @@ int ag2_set_sample_indices(ag2_ctx* c, const int32_t* idx, size_t n) {
     if (idx[i] < 0 || (size_t)idx[i] >= c->n) return AG2_E_INVALID;
   cudaSetDevice(c->device);
   c->h_sample_idx.assign(idx, idx + n);
+  c->h_sample_idx_stale = false;
   c->use_points = false;
   c->num_samples = n;
   c->st.num_samples = (int64_t)n;
@@ -340,6 +347,29 @@ int ag2_set_sample_indices(ag2_ctx* c, const int32_t* idx, size_t n) {
     AG2_CUDA(c, c->sample_idx.reserve(n));
     AG2_CUDA(c, cudaMemcpyAsync(c->sample_idx.p, c->h_sample_idx.data(), 4 * n, cudaMemcpyHostToDevice, c->stream));
   }
+  return AG2_OK;
+}
+
+int ag2_set_sample_indices_device(ag2_ctx* c, const int32_t* d_idx, size_t n) {
+  if (!c || (n && !d_idx)) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  if (n) {
+    AG2_CUDA(c, c->sample_idx.reserve(n));
+    AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 14, 0, 4, c->stream));
+    k_count_bad_indices<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(d_idx, n, c->n, c->scalars.p + 14);
+    AG2_LAUNCH_CHECK(c);
+    AG2_CUDA(c, cudaMemcpyAsync(c->sample_idx.p, d_idx, 4 * n, cudaMemcpyDeviceToDevice, c->stream));
+    uint32_t bad = 0;
+    AG2_CUDA(c, cudaMemcpyAsync(&bad, c->scalars.p + 14, 4, cudaMemcpyDeviceToHost, c->stream));
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (bad) return AG2_E_INVALID;
+  }
+  c->h_sample_idx.clear();
+  c->h_sample_idx_stale = n > 0;  // fetched on demand by ag2_get_sample_indices
+  c->use_points = false;
+  c->num_samples = n;
+  c->st.num_samples = (int64_t)n;
+  invalidate_results(c);
   return AG2_OK;
 }
 
@@ -361,6 +391,14 @@ int ag2_set_sample_points(ag2_ctx* c, const double* xyz, size_t n) {
 int ag2_set_sample_id_offset(ag2_ctx* c, int64_t first) {
   if (!c) return AG2_E_INVALID;
   c->sample_id_offset = first;
+  c->sample_id_stride = 1;
+  return AG2_OK;
+}
+
+int ag2_set_sample_id_map(ag2_ctx* c, int64_t first, int64_t stride) {
+  if (!c || stride < 1) return AG2_E_INVALID;
+  c->sample_id_offset = first;
+  c->sample_id_stride = stride;
   return AG2_OK;
 }
 

@@ -133,6 +133,42 @@ int ag2_get_hypotheses_device(ag2_ctx* c, int which, const ag2_hypothesis** d_pt
   return AG2_OK;
 }
 
+int ag2_normals_shard_points(ag2_ctx* c, int world, size_t* shard_points) {
+  if (!c || world < 1 || !shard_points) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  AG2_TRY(grid_build(c));
+  *shard_points = normals_shard_points((uint32_t)c->n_finite, 0, world);
+  return AG2_OK;
+}
+
+int ag2_compute_normals_shard(ag2_ctx* c, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned) {
+  if (!c || world < 1 || rank < 0 || rank >= world || (cap_points && !d_out)) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  return normals_shard_compute(c, rank, world, d_out, cap_points, n_owned);
+}
+
+int ag2_set_normals_shards(ag2_ctx* c, const float* d_all, size_t cap_points, int world) {
+  if (!c || world < 1 || (cap_points && !d_all)) return AG2_E_INVALID;
+  cudaSetDevice(c->device);
+  return normals_shard_assemble(c, d_all, cap_points, world);
+}
+
+int ag2_copy_hypotheses_device(ag2_ctx* c, int which, ag2_hypothesis* d_dst, size_t cap, size_t* n) {
+  if (!c || which < 0 || which > 5 || (cap && !d_dst)) return AG2_E_INVALID;
+  const size_t cnt = c->list_n[which];
+  if (n) *n = cnt;
+  if (cnt > cap) return AG2_E_CAPACITY;
+  cudaSetDevice(c->device);
+  if (cnt) {
+    AG2_TRY(gather_list_records(c, which));
+    AG2_CUDA(c, cudaMemcpyAsync(d_dst, c->list_rec[which].p, cnt * sizeof(ag2_hypothesis), cudaMemcpyDeviceToDevice,
+                                c->stream));
+  }
+  if (cap > cnt) AG2_CUDA(c, cudaMemsetAsync(d_dst + cnt, 0, (cap - cnt) * sizeof(ag2_hypothesis), c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}
+
 int ag2_get_hypotheses(ag2_ctx* c, int which, ag2_hypothesis* out, size_t cap, size_t* n) {
   if (!c || which < 0 || which > 5) return AG2_E_INVALID;
   const size_t cnt = c->list_n[which];

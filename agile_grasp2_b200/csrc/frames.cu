@@ -111,7 +111,7 @@ __device__ __forceinline__ double dot3d(const double* a, const double* b) {
 __global__ void __launch_bounds__(kFrameThreads)
 k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
          const double* __restrict__ sxyz, uint32_t S, const uint32_t* __restrict__ kt, uint32_t cap,
-         float r2, float rq, int num_cams, uint64_t seed, int64_t id_offset, double cam0x, double cam0y,
+         float r2, float rq, int num_cams, uint64_t seed, int64_t id_offset, int64_t id_stride, double cam0x, double cam0y,
          double cam0z, double cam1x, double cam1y, double cam1z, ag2_frame* __restrict__ out, uint32_t* __restrict__ num_valid) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* keys = (uint64_t*)smem;
@@ -176,7 +176,7 @@ k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict_
   bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kFrameThreads, BlockSync());
   const int n = (int)min(50u, count);
   if (tid < n) {
-    uint32_t r = draw_index(seed, id_offset + (int64_t)s, tid, count);
+    uint32_t r = draw_index(seed, id_offset + id_stride * (int64_t)s, tid, count);
     uint32_t pos = vals[r];
     float4 nv = g.nrm[pos];
     double nx = (double)nv.x, ny = (double)nv.y, nz = (double)nv.z;
@@ -285,7 +285,7 @@ int frames_compute(ag2_ctx* c) {
   AG2_CUDA(c, cudaFuncSetAttribute(k_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const HandConst& h = c->hc;
   k_frames<<<S, kFrameThreads, smem, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->kt.p, cap, h.r2_taubin, h.rq_taubin,
-                                           c->num_cams, h.rng_seed, c->sample_id_offset, h.cam_origin[0][0],
+                                           c->num_cams, h.rng_seed, c->sample_id_offset, c->sample_id_stride, h.cam_origin[0][0],
                                            h.cam_origin[0][1], h.cam_origin[0][2], h.cam_origin[1][0],
                                            h.cam_origin[1][1], h.cam_origin[1][2], c->frames.p, c->scalars.p + 13);
   AG2_LAUNCH_CHECK(c);

@@ -24,12 +24,19 @@ namespace {
 constexpr int kTiers = 8;
 __constant__ uint32_t c_tier[kTiers] = {64, 96, 128, 192, 256, 384, 512, 1024};
 
+// Multi-GPU: rank r of w owns the 32-point granules g with g % w == r of the cell-sorted cloud
+// (interleaved, so that every rank sees every density of the scene).
+__host__ __device__ __forceinline__ uint32_t shard_point(uint32_t t, uint32_t rank, uint32_t world) {
+  return (((t >> 5) * world + rank) << 5) | (t & 31u);  // t-th owned point -> cell-sorted position
+}
+
 __global__ void k_count_neighbors(GridDev g, float r2, float rq, uint32_t* __restrict__ kn,
                                   uint32_t* __restrict__ max_out, unsigned long long* __restrict__ sum_out,
-                                  uint32_t* __restrict__ tier_hist /* [kTiers]: points with kn > tier */) {
+                                  uint32_t* __restrict__ tier_hist /* [kTiers]: points with kn > tier */,
+                                  uint32_t shard_rank, uint32_t shard_world) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t cnt = 0;
-  if (i < (uint32_t)g.n) {
+  if (i < (uint32_t)g.n && (i >> 5) % shard_world == shard_rank) {
     float4 q = g.pts[i];
     QueryWindow w = make_window(g, q.x, q.y, q.z, rq);
     int rows = w.rows();
@@ -219,7 +226,8 @@ struct NormalsArgs {
   float r2, rq, bscale;
   const uint32_t* kn;
   uint32_t n_items, cap, bsz;
-  const uint32_t* list;       // nullptr: items are the cell-sorted points 0..n_items-1
+  uint32_t shard_rank, shard_world;
+  const uint32_t* list;       // nullptr: items are the owned cell-sorted points (shard_point), n_items of them
   uint32_t* big_list;         // out: items whose neighbourhood exceeds cap
   uint32_t* big_count;
   uint32_t big_cap;
@@ -257,7 +265,8 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
     if (batch >= n_batches) break;
     const uint32_t i0 = batch * bsz;
     const uint32_t nb = min(bsz, P.n_items - i0);
-    const uint32_t my_i = lane < nb ? (P.list ? P.list[i0 + lane] : i0 + lane) : 0u;
+    const uint32_t my_i =
+        lane < nb ? (P.list ? P.list[i0 + lane] : shard_point(i0 + lane, P.shard_rank, P.shard_world)) : 0u;
     const uint32_t my_count = lane < nb ? P.kn[my_i] : 0u;
     const bool too_big = my_count > cap;
     if (too_big) {
@@ -446,12 +455,74 @@ static int launch_normals(ag2_ctx* c, uint32_t n_items, uint32_t cap, const uint
   P.bscale = (float)kNB / c->hc.r2_normals;
   P.kn = c->kn.p;
   P.n_items = n_items, P.cap = cap, P.bsz = bsz;
+  P.shard_rank = (uint32_t)c->nrm_rank, P.shard_world = (uint32_t)c->nrm_world;
   P.list = list;
   P.big_list = big_list, P.big_count = big_count, P.big_cap = big_cap;
   P.batch_counter = batch_counter;
   P.nrm_out = c->nrm.p;
   k_normals<<<grid, warps * 32, smem, st>>>(P);
   AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
+// number of points rank `rank` of `world` owns among n cell-sorted points (see shard_point)
+uint32_t normals_shard_points(uint32_t n, int rank, int world) {
+  const uint32_t G = (n + 31) / 32;
+  if (G <= (uint32_t)rank) return 0;
+  const uint32_t owned = (G - (uint32_t)rank + (uint32_t)world - 1) / (uint32_t)world;
+  const bool has_tail = (G - 1) % (uint32_t)world == (uint32_t)rank;
+  return owned * 32 - (has_tail ? G * 32 - n : 0);
+}
+
+namespace {
+// owned normals -> compact send buffer, and the gathered buffers of all ranks -> nrm (w = camera bits kept)
+__global__ void k_pack_shard(const float4* __restrict__ nrm, uint32_t n_owned, uint32_t rank, uint32_t world,
+                             float4* __restrict__ out) {
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n_owned) out[t] = nrm[shard_point(t, rank, world)];
+}
+__global__ void k_unpack_shards(const float4* __restrict__ all, uint32_t cap_points, uint32_t world, uint32_t n,
+                                float4* __restrict__ nrm) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t g = i >> 5, r = g % world, t = ((g / world) << 5) | (i & 31u);
+  const float4 v = all[(size_t)r * cap_points + t];
+  nrm[i] = make_float4(v.x, v.y, v.z, nrm[i].w);
+}
+}  // namespace
+
+int normals_shard_compute(ag2_ctx* c, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned) {
+  AG2_TRY(grid_build(c));
+  if (c->normals_given) return AG2_E_STATE;  // normals came with the cloud: nothing to shard
+  const uint32_t n = (uint32_t)c->n_finite;
+  const uint32_t mine = normals_shard_points(n, rank, world);
+  if (n_owned) *n_owned = mine;
+  if (mine > cap_points) return AG2_E_CAPACITY;
+  c->nrm_rank = rank, c->nrm_world = world;
+  c->have_normals = false;
+  int rc = normals_compute(c);
+  c->nrm_rank = 0, c->nrm_world = 1;
+  c->have_normals = false;  // only this rank's granules are filled in
+  if (rc != AG2_OK) return rc;
+  if (mine) {
+    k_pack_shard<<<(mine + 255) / 256, 256, 0, c->stream>>>(c->nrm.p, mine, (uint32_t)rank, (uint32_t)world,
+                                                           reinterpret_cast<float4*>(d_out));
+    AG2_LAUNCH_CHECK(c);
+  }
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}
+
+int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, int world) {
+  AG2_TRY(grid_build(c));
+  const uint32_t n = (uint32_t)c->n_finite;
+  if ((size_t)normals_shard_points(n, 0, world) > cap_points) return AG2_E_CAPACITY;
+  if (n) {
+    k_unpack_shards<<<(n + 255) / 256, 256, 0, c->stream>>>(reinterpret_cast<const float4*>(d_all), (uint32_t)cap_points,
+                                                           (uint32_t)world, n, c->nrm.p);
+    AG2_LAUNCH_CHECK(c);
+  }
+  c->have_normals = true;
   return AG2_OK;
 }
 
@@ -467,7 +538,8 @@ int normals_compute(ag2_ctx* c) {
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 32, 0, 32 * 4, st));  // [32..39] tiers, [40..47] list counts, [48..55] batch counters
   k_count_neighbors<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p,
                                                       c->scalars.p + 8,
-                                                      (unsigned long long*)(c->scalars.p + 10), c->scalars.p + 32);
+                                                      (unsigned long long*)(c->scalars.p + 10), c->scalars.p + 32,
+                                                      (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
   AG2_LAUNCH_CHECK(c);
   uint32_t res[4], hist[kTiers];
   AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
@@ -489,7 +561,7 @@ int normals_compute(ag2_ctx* c) {
   // multi-level path (AG2_NORMALS_FIRST_TIER = index into tiers[])
   int forced_tier = -1;
   if (const char* e = getenv("AG2_NORMALS_FIRST_TIER")) forced_tier = atoi(e);
-  uint32_t remaining = n, level = 0;
+  uint32_t remaining = normals_shard_points(n, c->nrm_rank, c->nrm_world), level = 0;
   const uint32_t* list = nullptr;
   int tier = 0;
   while (remaining > 0 && level < 8) {

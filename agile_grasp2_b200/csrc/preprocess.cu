@@ -302,6 +302,14 @@ int ag2_subsample_uniformly(ag2_ctx* c, int num_samples, uint64_t seed) {
 int ag2_get_sample_indices(ag2_ctx* c, int32_t* idx, size_t cap, size_t* n) {
   if (!c || !n) return AG2_E_INVALID;
   if (c->use_points) return AG2_E_STATE;
+  if (c->h_sample_idx_stale) {
+    cudaSetDevice(c->device);
+    c->h_sample_idx.resize(c->num_samples);
+    AG2_CUDA(c, cudaMemcpyAsync(c->h_sample_idx.data(), c->sample_idx.p, 4 * c->num_samples, cudaMemcpyDeviceToHost,
+                                c->stream));
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->h_sample_idx_stale = false;
+  }
   *n = c->h_sample_idx.size();
   if (*n > cap) return AG2_E_CAPACITY;
   if (*n && !idx) return AG2_E_INVALID;

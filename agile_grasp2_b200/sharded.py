@@ -6,11 +6,20 @@ normals; reference hand_search.cpp:118,194, learning.cpp:12).  Per detect call:
   1. rank 0 holds the cloud; xyz (12 B/pt) + camera mask (1 B/pt) + the sample list are
      broadcast with torch.distributed (NCCL over NVLink on GPUs);
   2. every rank builds the identical cell index (cheaper than shipping it) and evaluates the
-     contiguous block [lo, hi) of the sample list; `set_sample_id_offset(lo)` keeps the
-     counter-based draws identical to a single-GPU run of the whole list;
+     STRIDED shard rank, rank + world, ... of the sample list (sample lists are sorted by point
+     index, i.e. spatially coherent: contiguous blocks would give the ranks different parts of
+     the scene and unequal work); `set_sample_id_map(rank, world)` keeps the counter-based draws
+     identical to a single-GPU run of the whole list;
   3. per-rank antipodal lists (192-byte records) are all-gathered (counts first, then
      records padded to the maximum count) and the global top-`num_selected` is taken with the
-     same ordering rule as the single-GPU path (score descending, list order on ties).
+     same ordering rule as the single-GPU path (score descending, list order on ties).  When a
+     top-k is requested the global top-k lies inside the union of the per-rank top-k lists, so
+     each rank contributes its SELECTED list in one fixed-size all-gather.
+
+On GPUs the whole exchange stays in device memory: ONE broadcast of a packed input buffer
+(`pack_inputs`: xyz | camera mask | samples in one allocation), the sample block handed to the
+library by device pointer, the selected records copied device-to-device into the all-gather send
+buffer, one device->host read of the gathered records at the end.
 
 There is no other data-path collective.  The same code runs over `gloo` with CPU tensors for
 the world_size-2 CPU tests (tests drive it with the oracle context; the product uses libag2).
@@ -25,16 +34,24 @@ from . import capi
 
 
 def partition(n: int, world: int, rank: int):
-    """Contiguous block of rank `rank` when n samples are split over `world` ranks."""
+    """Contiguous block of rank `rank` when n items are split over `world` ranks."""
     base, rem = divmod(n, world)
     lo = rank * base + min(rank, rem)
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def shard_size(n: int, world: int, rank: int) -> int:
+    """Number of samples in the strided shard rank, rank + world, ... of n samples."""
+    return (n - rank + world - 1) // world if n > rank else 0
+
+
 def merge_selected(parts, num_selected: int, keep_all: bool = False) -> np.ndarray:
-    """Concatenates per-rank antipodal lists (rank order == global sample order) and takes the
-    top `num_selected` by (score desc, list position asc) — grasp_detector.cpp:238-252."""
+    """Merges per-rank lists (sample_id already global) back into the single-process list order
+    (sample, orientation) and takes the top `num_selected` by (score desc, list position asc) —
+    grasp_detector.cpp:238-252."""
     allh = np.concatenate(parts) if parts else np.zeros(0, capi.HYPOTHESIS_DTYPE)
+    if len(allh):
+        allh = allh[np.lexsort((allh["orientation_id"], allh["sample_id"]))]
     if keep_all or len(allh) == 0:
         return allh
     order = np.argsort(-allh["score"], kind="stable")
@@ -43,9 +60,32 @@ def merge_selected(parts, num_selected: int, keep_all: bool = False) -> np.ndarr
     return allh[order]
 
 
+def pack_inputs(xyz, cam, samples, device):
+    """One device allocation holding xyz [N,3] f32 | samples [S] i32 | cam [N] u8 (4-byte aligned
+    sections); returns (packed u8 tensor, xyz view, cam view, samples view).  Rank 0 keeps its
+    resident cloud in this form so that a detect call needs a single broadcast."""
+    n, s = int(xyz.shape[0]), int(samples.shape[0])
+    packed = torch.empty(12 * n + 4 * s + n, dtype=torch.uint8, device=device)
+    xv = packed[: 12 * n].view(torch.float32).view(n, 3)
+    sv = packed[12 * n: 12 * n + 4 * s].view(torch.int32)
+    cv = packed[12 * n + 4 * s:]
+    if xyz is not None:
+        xv.copy_(torch.as_tensor(xyz).reshape(n, 3), non_blocking=True)
+        sv.copy_(torch.as_tensor(samples), non_blocking=True)
+        cv.copy_(torch.as_tensor(cam), non_blocking=True)
+    return packed, xv, cv, sv
+
+
+def _packed_views(packed, n, s):
+    return (packed[: 12 * n].view(torch.float32).view(n, 3), packed[12 * n + 4 * s:],
+            packed[12 * n: 12 * n + 4 * s].view(torch.int32))
+
+
 class ShardedDetector:
-    def __init__(self, ctx: capi.Context, rank: int = 0, world: int = 1, device=None, group=None):
+    def __init__(self, ctx: capi.Context, rank: int = 0, world: int = 1, device=None, group=None,
+                 shard_normals: bool = True):
         self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        self.shard_normals = shard_normals  # GPU fast path: normals computed 1/world per rank + all-gather
         self.device = device if device is not None else torch.device("cpu")
 
     # ---- collectives -----------------------------------------------------------------
@@ -115,20 +155,19 @@ class ShardedDetector:
 
     # ---- detect ----------------------------------------------------------------------
     def _run_block(self, samples_all: np.ndarray):
-        lo, hi = partition(len(samples_all), self.world, self.rank)
-        self.lo = lo
-        self.ctx.set_sample_indices(samples_all[lo:hi])
-        self.ctx.set_sample_id_offset(lo)
+        mine = np.ascontiguousarray(samples_all[self.rank::self.world])
+        self.ctx.set_sample_indices(mine)
+        self.ctx.set_sample_id_map(self.rank, self.world)
         local = np.zeros(0, capi.HYPOTHESIS_DTYPE)
         p = self.ctx.params
         # the global top-k is inside the union of the per-rank top-k, so when a top-k is asked for
         # each rank ships its own SELECTED list (<= num_selected records, one fixed-size all-gather)
         topk = p.num_selected > 0 and p.antipodal_mode != capi.MODE_NONE
-        if hi > lo:
+        if len(mine):
             self.ctx.detect()
             which = capi.LIST_SELECTED if (self.world == 1 or topk) else capi.LIST_ANTIPODAL
             local = self.ctx.hypotheses(which).copy()
-            local["sample_id"] += lo
+            local["sample_id"] = self.rank + self.world * local["sample_id"]
         if self.world == 1:
             return local
         if topk:
@@ -143,11 +182,88 @@ class ShardedDetector:
         self.ctx.set_cloud_device(xyz_d.data_ptr(), xyz_d.shape[0], cam_d.data_ptr(), num_cams)
         return self._run_block(samples_d.cpu().numpy())
 
+    def detect_packed(self, packed_d, n, s, num_cams):
+        """GPU fast path.  packed_d: the `pack_inputs` buffer (valid on rank 0, a same-sized receive
+        buffer elsewhere); (n, s, num_cams) known on every rank.  One broadcast, device-resident
+        sample block, device-side all-gather of the per-rank top-k."""
+        import time
+        p = self.ctx.params
+        topk = p.num_selected > 0 and p.antipodal_mode != capi.MODE_NONE
+        t0 = time.perf_counter()
+        if self.world > 1:
+            dist.broadcast(packed_d, src=0, group=self.group)
+            torch.cuda.current_stream().synchronize()
+        t1 = time.perf_counter()
+        xyz_d, cam_d, smp_d = _packed_views(packed_d, n, s)
+        if not topk:  # unbounded lists: the general path
+            self.ctx.set_cloud_device(xyz_d.data_ptr(), n, cam_d.data_ptr(), num_cams)
+            return self._run_block(smp_d.cpu().numpy())
+        self.ctx.set_cloud_device(xyz_d.data_ptr(), n, cam_d.data_ptr(), num_cams)
+        if self.world > 1 and self.shard_normals:
+            # the normals of the whole cloud are needed by every rank: each computes 1/world of them
+            # (interleaved 32-point granules of the cell-sorted cloud), one all-gather installs the rest
+            cap = self.ctx.normals_shard_points(self.world)
+            if getattr(self, "_nrm_cap", None) != cap:
+                self._nrm_tx = torch.empty(cap * 4, dtype=torch.float32, device=self.device)
+                self._nrm_rx = torch.empty(self.world * cap * 4, dtype=torch.float32, device=self.device)
+                self._nrm_cap = cap
+            self.ctx.compute_normals_shard(self.rank, self.world, self._nrm_tx.data_ptr(), cap)
+            dist.all_gather_into_tensor(self._nrm_rx, self._nrm_tx, group=self.group)
+            torch.cuda.current_stream().synchronize()
+            self.ctx.set_normals_shards(self._nrm_rx.data_ptr(), cap, self.world)
+        t1b = time.perf_counter()
+        mine = smp_d[self.rank::self.world].contiguous() if self.world > 1 else smp_d
+        n_mine = shard_size(s, self.world, self.rank)
+        if self.world > 1:
+            torch.cuda.current_stream().synchronize()
+        self.ctx.set_sample_indices_device(mine.data_ptr(), n_mine)
+        self.ctx.set_sample_id_map(self.rank, self.world)
+        rec, cap = capi.HYPOTHESIS_DTYPE.itemsize, p.num_selected
+        if getattr(self, "_tx_cap", None) != cap:
+            self._tx = torch.empty(cap * rec, dtype=torch.uint8, device=self.device)
+            self._rxg = torch.empty(self.world * cap * rec, dtype=torch.uint8, device=self.device)
+            self._tx_cap = cap
+        if n_mine:
+            self.ctx.detect()
+            self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
+        else:
+            self._tx.zero_()
+            torch.cuda.current_stream().synchronize()
+        t2 = time.perf_counter()
+        if self.world > 1:
+            dist.all_gather_into_tensor(self._rxg, self._tx, group=self.group)
+            allr = self._rxg.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(self.world, cap)
+        else:
+            allr = self._tx.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(1, cap)
+        t3 = time.perf_counter()
+        # host-side wall time of the three segments of the last call (ms): input exchange, local
+        # detect (includes waiting for nothing but this rank's GPU), result exchange
+        self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
+                        "gather": (t3 - t2) * 1e3}
+        parts = []
+        for r in range(self.world):
+            blk = allr[r]
+            blk = blk[np.any(blk["approach"] != 0.0, axis=1)].copy()  # zero-filled tail = no record
+            blk["sample_id"] = r + self.world * blk["sample_id"]
+            parts.append(blk)
+        return merge_selected(parts, p.num_selected)
+
     def detect_host(self, xyz_h, cam_h, num_cams, samples_h, shape_hint=None):
         """Host buffers (pinned torch CPU tensors on rank 0): H2D inside the call."""
         if self.world == 1:
             self.ctx.set_cloud(xyz_h.numpy(), cam_h.numpy(), num_cams)
             return self._run_block(samples_h.numpy())
+        if shape_hint is not None:  # sizes known everywhere: stage into the packed buffer, one broadcast
+            n, s, num_cams = shape_hint
+            if getattr(self, "_pk_key", None) != (n, s):
+                self._pk = torch.empty(12 * n + 4 * s + n, dtype=torch.uint8, device=self.device)
+                self._pk_key = (n, s)
+            if self.rank == 0:
+                xv, cv, sv = _packed_views(self._pk, n, s)
+                xv.copy_(xyz_h, non_blocking=True)
+                cv.copy_(cam_h, non_blocking=True)
+                sv.copy_(samples_h, non_blocking=True)
+            return self.detect_packed(self._pk, n, s, num_cams)
         if self.rank == 0:
             xyz_d, cam_d, smp_d = (xyz_h.to(self.device, non_blocking=True), cam_h.to(self.device, non_blocking=True),
                                    samples_h.to(self.device, non_blocking=True))

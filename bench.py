@@ -287,20 +287,28 @@ def main():
         return total_ms, phase, launches, last_stats, out
 
     # resident arm: the cloud sits in HBM on rank 0 before the timed region
-    if rank == 0 or world == 1:
-        xyz_d, cam_d, smp_d = xyz_h.cuda(), cam_h.cuda(), smp_h.cuda()
-    else:
-        xyz_d = cam_d = smp_d = None
     # sizes of the synthetic workload are the same on every rank (one tiny broadcast at set-up)
     meta = torch.tensor([n_pts, n_smp, num_cams], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.broadcast(meta, src=0)
     hint = tuple(int(v) for v in meta.tolist())
+    # resident layout: one allocation (xyz | samples | camera mask), so that the per-call exchange is one broadcast
+    if rank == 0 or world == 1:
+        packed_d = sharded.pack_inputs(xyz_h, cam_h, smp_h, torch.device("cuda", local_rank))[0]
+    else:
+        packed_d = torch.empty(12 * hint[0] + 4 * hint[1] + hint[0], dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
     clocks = ClockSampler(local_rank)
     clocks.start()
-    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_device(xyz_d, cam_d, num_cams, smp_d, hint), K, W)
+    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_packed(packed_d, hint[0], hint[1], hint[2]), K, W)
     clk = clocks.stop()
     e2e_ms, _, _, _, sel = timed(lambda: runner.detect_host(xyz_h, cam_h, num_cams, smp_h, hint), K, 1)
+    per_rank = None
+    if world > 1:  # per-rank view of the step: sample blocks differ in cost, the slowest rank sets the pace
+        mine = {"rank": rank, "ms_per_step": round(tot_ms / K, 4), "phases_ms": {k: round(v, 4) for k, v in phase.items()},
+                "last_call_host_ms": {k: round(v, 4) for k, v in getattr(runner, "last_ms", {}).items()}}
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
     t = torch.tensor([tot_ms, e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -317,6 +325,7 @@ def main():
                         "d2h_bytes_per_step": int(len(sel) * 192 + 64)},
                 "roofline": roofline_for(phase, st, n_pts, peaks),
                 "phases_ms": {k: round(v, 4) for k, v in phase.items()},
+                **({"per_rank": per_rank} if per_rank else {}),
                 "counts": {k: st[k] for k in ("num_hypotheses", "num_pruned", "num_antipodal", "num_selected",
                                               "sum_neighbors_hands", "sum_cropped", "sum_in_box",
                                               "sum_neighbors_normals")}}

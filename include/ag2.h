@@ -208,12 +208,28 @@ int ag2_set_cloud_device(ag2_ctx* ctx, const float* d_xyz, size_t n, const uint8
 /* CloudCamera::setSampleIndices (cloud_camera.h:131) -> calculateLocalFrames(indices),
  * hand_search.cpp:97-170. */
 int ag2_set_sample_indices(ag2_ctx* ctx, const int32_t* idx, size_t n);
+/* Same with a DEVICE pointer (the sample list after an NCCL broadcast); indices are range-checked
+ * on the device. */
+int ag2_set_sample_indices_device(ag2_ctx* ctx, const int32_t* d_idx, size_t n);
 /* CloudCamera::setSamples (cloud_camera.cpp:254-257) -> calculateLocalFrames(samples),
  * hand_search.cpp:238-317.  xyz: 3 doubles per sample. */
 int ag2_set_sample_points(ag2_ctx* ctx, const double* xyz, size_t n);
 /* Offset added to the sample position when deriving the rand() replacement
  * stream, so that a shard of a larger sample list draws like the whole list. */
 int ag2_set_sample_id_offset(ag2_ctx* ctx, int64_t first_sample_id);
+/* General form: sample s of this context is sample first + stride*s of the whole list (a strided
+ * shard; stride >= 1).  ag2_set_sample_id_offset(first) == ag2_set_sample_id_map(first, 1). */
+int ag2_set_sample_id_map(ag2_ctx* ctx, int64_t first_sample_id, int64_t stride);
+
+/* ---- multi-GPU: the normals (calculateNormalsOMP, hand_search.cpp:83-94) sharded by point ------
+ * Every rank holds the same cloud.  Rank r of w computes the normals of the 32-point granules
+ * g % w == r of the cell-sorted cloud into caller-owned DEVICE memory (4 floats per point,
+ * cap_points >= *shard_points), the ranks all-gather those buffers (NCCL), and
+ * ag2_set_normals_shards installs the gathered w x cap_points x 4 floats.  Afterwards the
+ * context is exactly as after ag2_compute_normals. */
+int ag2_normals_shard_points(ag2_ctx* ctx, int world, size_t* shard_points /* of rank 0 = the largest */);
+int ag2_compute_normals_shard(ag2_ctx* ctx, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned);
+int ag2_set_normals_shards(ag2_ctx* ctx, const float* d_all, size_t cap_points, int world);
 
 /* ---- pre-processing (next row f1) ----------------------------------------- */
 
@@ -298,6 +314,10 @@ int ag2_num_hypotheses(ag2_ctx* ctx, int which, size_t* n);
 int ag2_get_hypotheses(ag2_ctx* ctx, int which, ag2_hypothesis* out, size_t cap, size_t* n);
 /* Device pointer of a list (records are contiguous); valid until the next stage call. */
 int ag2_get_hypotheses_device(ag2_ctx* ctx, int which, const ag2_hypothesis** d_ptr, size_t* n);
+/* Copies a list into caller-owned DEVICE memory of `cap` records and zero-fills the rest (a valid
+ * record never has an all-zero approach vector); the buffer is complete when the call returns.
+ * This is the send buffer of the multi-GPU all-gather (grasp lists of all ranks). */
+int ag2_copy_hypotheses_device(ag2_ctx* ctx, int which, ag2_hypothesis* d_dst, size_t cap, size_t* n);
 int ag2_get_stats(ag2_ctx* ctx, ag2_stats* out);
 
 /* ---- introspection used by the parity tests ------------------------------ */

@@ -580,7 +580,7 @@ struct ag2o_ctx {
   bool use_points = false;
   std::vector<int32_t> sample_idx;
   std::vector<double> sample_xyz;
-  int64_t sample_id_offset = 0;
+  int64_t sample_id_offset = 0, sample_id_stride = 1;
   std::vector<ag2_frame> frames;
   std::vector<ag2_sweep_record> sweeps;
   std::vector<Hyp> hyps;
@@ -697,7 +697,7 @@ void compute_frames(ag2o_ctx* c) {
       N.resize(n);
       int num_source[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       for (int j = 0; j < n; j++) {
-        uint32_t r = draw(c->p.rng_seed, c->sample_id_offset + s, j, (uint32_t)nn.size());
+        uint32_t r = draw(c->p.rng_seed, c->sample_id_offset + c->sample_id_stride * (int64_t)s, j, (uint32_t)nn.size());
         int32_t id = nn[r].idx;
         const float* nf = &c->normals[3 * (size_t)id];
         N[j] = v3((double)nf[0], (double)nf[1], (double)nf[2]);
@@ -1319,6 +1319,13 @@ int ag2o_set_sample_points(ag2o_ctx* c, const double* xyz, size_t n) {
 int ag2o_set_sample_id_offset(ag2o_ctx* c, int64_t first) {
   if (!c) return AG2_E_INVALID;
   c->sample_id_offset = first;
+  c->sample_id_stride = 1;
+  return AG2_OK;
+}
+int ag2o_set_sample_id_map(ag2o_ctx* c, int64_t first, int64_t stride) {
+  if (!c || stride < 1) return AG2_E_INVALID;
+  c->sample_id_offset = first;
+  c->sample_id_stride = stride;
   return AG2_OK;
 }
 

@@ -335,3 +335,49 @@ def test_detect_with_clustering(dense_scene):
     gs, os_ = g.hypotheses(capi.LIST_SELECTED), o.hypotheses(capi.LIST_SELECTED)
     assert len(gs) == len(os_) == min(8, len(gc))
     assert np.all(np.diff(gs["score"]) <= 0)
+
+
+def test_sharded_packed_path_world1(tiny_scene):
+    """The multi-GPU fast path (packed input buffer, device-resident sample block, device copy of the
+    selected records) at world size 1 returns exactly what ag2_detect + ag2_get_hypotheses return."""
+    import torch
+    from agile_grasp2_b200 import sharded
+    sc = tiny_scene
+    p = make_params(capi.MODE_PREDICTION, min_score_diff=-1e9, num_selected=20)
+    a, b = capi.Context(p), capi.Context(p)
+    a.init_lenet_xavier(3); b.init_lenet_xavier(3)
+    a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"]); a.detect()
+    want = a.hypotheses(capi.LIST_SELECTED)
+    dev = torch.device("cuda", 0)
+    packed = sharded.pack_inputs(torch.from_numpy(sc["xyz"]), torch.from_numpy(sc["cam_mask"]),
+                                 torch.from_numpy(np.asarray(sc["samples"], np.int32)), dev)[0]
+    torch.cuda.synchronize()
+    run = sharded.ShardedDetector(b, rank=0, world=1, device=dev)
+    got = run.detect_packed(packed, len(sc["xyz"]), len(sc["samples"]), sc["num_cams"])
+    assert len(want) > 0 and got.tobytes() == want.tobytes()
+    assert np.array_equal(b.sample_indices(), np.asarray(sc["samples"], np.int32))
+    with pytest.raises(capi.Ag2Error):  # device-side range check
+        bad = torch.tensor([0, len(sc["xyz"])], dtype=torch.int32, device=dev)
+        b.set_sample_indices_device(bad.data_ptr(), 2)
+
+
+@pytest.mark.parametrize("world", [1, 3, 8])
+def test_normals_shards_assemble_to_the_full_result(tiny_scene, world):
+    """Multi-GPU normals on one GPU: every 'rank' computes its interleaved granules into its own
+    buffer, the buffers are concatenated (what the all-gather does) and installed; the normals and
+    everything downstream are bit-identical to ag2_compute_normals."""
+    import torch
+    sc = tiny_scene
+    p = make_params(capi.MODE_GEOMETRIC)
+    a, b = capi.Context(p), capi.Context(p)
+    for c in (a, b):
+        c.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); c.set_sample_indices(sc["samples"])
+    a.compute_normals()
+    cap = b.normals_shard_points(world)
+    allb = torch.full((world, cap, 4), float("nan"), dtype=torch.float32, device="cuda")
+    owned = [b.compute_normals_shard(r, world, allb[r].data_ptr(), cap) for r in range(world)]
+    assert sum(owned) == len(a.normals()) and max(owned) == owned[0] <= cap
+    b.set_normals_shards(allb.data_ptr(), cap, world)
+    assert a.normals().tobytes() == b.normals().tobytes()
+    a.detect(); b.detect()
+    assert a.hypotheses(capi.LIST_SELECTED).tobytes() == b.hypotheses(capi.LIST_SELECTED).tobytes()

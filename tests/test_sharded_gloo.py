@@ -20,6 +20,7 @@ def test_partition_covers_everything():
             assert blocks[0][0] == 0 and blocks[-1][1] == n
             assert all(blocks[i][1] == blocks[i + 1][0] for i in range(w - 1))
             assert max(b[1] - b[0] for b in blocks) - min(b[1] - b[0] for b in blocks) <= 1
+            assert [sharded.shard_size(n, w, r) for r in range(w)] == [len(range(r, n, w)) for r in range(w)]
 
 
 def _worker(rank, world, port, out_dir):
@@ -50,4 +51,4 @@ def test_two_rank_result_equals_single_process(tmp_path):
     assert len(a) == len(ref)
     for f in ("sample_id", "orientation_id", "full_antipodal", "finger_slot", "depth_step", "num_in_box"):
         assert np.array_equal(a[f], ref[f]), f
-    assert np.array_equal(a["bottom"], ref["bottom"])  # the id offset keeps the rand() replacement stream identical
+    assert np.array_equal(a["bottom"], ref["bottom"])  # the id map keeps the rand() replacement stream identical
