@@ -48,6 +48,7 @@ struct DevBuf {
 struct GridDev {
   float ox, oy, oz;   // origin (bbox min of the finite points)
   float inv_h;        // 1 / cell size
+  float h;            // cell size
   int nx, ny, nz;
   int n;              // finite points (sorted arrays hold exactly these)
   const uint32_t* cell_start;  // [ncells + 1]

@@ -53,6 +53,42 @@ __device__ __forceinline__ void row_span(const GridDev& g, const QueryWindow& w,
   end = __ldg(&g.cell_start[c0 + (uint32_t)(w.x1 - w.x0) + 1]);
 }
 
+// Same, with the cells that cannot hold a point within the radius trimmed away: the whole row when
+// its (y, z) slab is farther than the radius from q, and the end cells of the row whose near face
+// is farther than the remaining chord.  r2m = radius^2 with a small margin (the caller's exact
+// test decides membership; the margin only has to cover the float rounding of the cell faces,
+// ~1e-7 m).  Cells on the border of the grid are unbounded outwards (cell_coord clamps).
+__device__ __forceinline__ void row_span_trim(const GridDev& g, const QueryWindow& w, int row, float qx, float qy,
+                                              float qz, float r2m, uint32_t& begin, uint32_t& end) {
+  const int ny = w.y1 - w.y0 + 1;
+  const int cz = w.z0 + row / ny;
+  const int cy = w.y0 + row % ny;
+  const float h = g.h;
+  const float ylo = g.oy + (float)cy * h, zlo = g.oz + (float)cz * h;
+  float dy = 0.f, dz = 0.f;
+  if (qy < ylo && cy > 0) dy = ylo - qy;
+  if (qy > ylo + h && cy < g.ny - 1) dy = qy - (ylo + h);
+  if (qz < zlo && cz > 0) dz = zlo - qz;
+  if (qz > zlo + h && cz < g.nz - 1) dz = qz - (zlo + h);
+  const float rem = r2m - dy * dy - dz * dz;
+  if (rem < 0.f) {
+    begin = end = 0;
+    return;
+  }
+  int x0 = w.x0, x1 = w.x1;
+  while (x0 < x1) {  // leading cells entirely to the left of the chord
+    const float d = qx - (g.ox + (float)(x0 + 1) * h);
+    if (d > 0.f && d * d > rem) x0++; else break;
+  }
+  while (x1 > x0) {  // trailing cells entirely to the right
+    const float d = (g.ox + (float)x1 * h) - qx;
+    if (d > 0.f && d * d > rem) x1--; else break;
+  }
+  const uint32_t c0 = cell_id(g, x0, cy, cz);
+  begin = __ldg(&g.cell_start[c0]);
+  end = __ldg(&g.cell_start[c0 + (uint32_t)(x1 - x0) + 1]);
+}
+
 __device__ __forceinline__ uint32_t next_pow2(uint32_t v) {
   uint32_t p = 1;
   while (p < v) p <<= 1;

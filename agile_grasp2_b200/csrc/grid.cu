@@ -41,12 +41,25 @@ __global__ void k_bbox(const float* __restrict__ xyz, size_t n, int* __restrict_
     }
     cnt += __shfl_xor_sync(AG2_FULL, cnt, o);
   }
-  if ((threadIdx.x & 31) == 0) {
-    for (int d = 0; d < 3; d++) {
-      atomicMin(&out[d], float_ordered(mn[d]));
-      atomicMax(&out[3 + d], float_ordered(mx[d]));
-    }
-    atomicAdd((unsigned*)&out[6], cnt);
+  // one set of atomics per CTA (7 addresses shared by the whole grid)
+  __shared__ float s_mn[kThreads / 32][3], s_mx[kThreads / 32][3];
+  __shared__ unsigned s_cnt[kThreads / 32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    for (int d = 0; d < 3; d++) s_mn[warp][d] = mn[d], s_mx[warp][d] = mx[d];
+    s_cnt[warp] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int d = threadIdx.x;
+    float a = s_mn[0][d], b = s_mx[0][d];
+    for (int k = 1; k < kThreads / 32; k++) a = fminf(a, s_mn[k][d]), b = fmaxf(b, s_mx[k][d]);
+    atomicMin(&out[d], float_ordered(a));
+    atomicMax(&out[3 + d], float_ordered(b));
+  } else if (threadIdx.x == 3) {
+    unsigned t = 0;
+    for (int k = 0; k < kThreads / 32; k++) t += s_cnt[k];
+    atomicAdd((unsigned*)&out[6], t);
   }
 }
 
@@ -213,6 +226,7 @@ GridDev grid_dev(const ag2_ctx* c) {
   GridDev g;
   g.ox = c->origin[0], g.oy = c->origin[1], g.oz = c->origin[2];
   g.inv_h = c->inv_h;
+  g.h = c->h;
   g.nx = c->dim[0], g.ny = c->dim[1], g.nz = c->dim[2];
   g.n = (int)c->n_finite;
   g.cell_start = c->cell_start.p;
@@ -260,7 +274,7 @@ int grid_build(ag2_ctx* c) {
     init[6] = 0;
   }
   AG2_CUDA(c, cudaMemcpyAsync(c->scalars.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
-  int blocks = (int)std::min<size_t>((n + kThreads - 1) / kThreads, (size_t)c->sm_count * 8);
+  int blocks = (int)std::min<size_t>((n + kThreads - 1) / kThreads, (size_t)c->sm_count * 4);
   k_bbox<<<blocks, kThreads, 0, st>>>(c->xyz_in.p, n, (int*)c->scalars.p);
   AG2_LAUNCH_CHECK(c);
   int res[7];

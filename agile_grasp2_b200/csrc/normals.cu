@@ -42,7 +42,7 @@ __global__ void k_count_neighbors(GridDev g, float r2, float rq, uint32_t* __res
     int rows = w.rows();
     for (int row = 0; row < rows; row++) {
       uint32_t b, e;
-      row_span(g, w, row, b, e);
+      row_span_trim(g, w, row, q.x, q.y, q.z, r2 * 1.002f, b, e);
       for (uint32_t j = b; j < e; j++) {
         float4 p = g.pts[j];
         float d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
         uint32_t rb = 0, rc = 0;
         if (r0 + lane < rows) {
           uint32_t b, e;
-          row_span(g, w, r0 + lane, b, e);
+          row_span_trim(g, w, r0 + lane, q.x, q.y, q.z, P.r2 * 1.002f, b, e);
           rb = b, rc = e - b;
         }
         uint32_t incl = rc;
