@@ -148,13 +148,14 @@ class Stats(C.Structure):
         ("sum_neighbors_normals", C.c_int64),
         ("gpu_launches", C.c_int64),
         ("ms_phase", C.c_double * 8),
+        ("ms_gap", C.c_double * 8),
     ]
 
     def as_dict(self) -> dict:
-        d = {k: int(getattr(self, k)) for k, _ in self._fields_[:-1]}
-        d["ms_phase"] = dict(
-            zip(["grid", "normals", "frames", "hands", "prune", "render", "lenet", "select"], list(self.ms_phase))
-        )
+        d = {k: int(getattr(self, k)) for k, _ in self._fields_[:-2]}
+        names = ["grid", "normals", "frames", "hands", "prune", "render", "lenet", "select"]
+        d["ms_phase"] = dict(zip(names, list(self.ms_phase)))
+        d["ms_gap"] = dict(zip(names, list(self.ms_gap)))
         return d
 
 

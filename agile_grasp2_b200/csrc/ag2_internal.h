@@ -179,6 +179,7 @@ struct ag2_ctx {
   ag2::DevBuf<int32_t> is_cand_idx;
   ag2::DevBuf<uint8_t> is_accept;
   ag2::DevBuf<uint8_t> images;              // pruned * 10800 (HWC u8)
+  ag2::DevBuf<uint8_t> render_scratch;      // sort arrays of k_render when a closing region exceeds shared memory
   ag2::DevBuf<float> logits;                // pruned * 2
   ag2::DevBuf<double> scores;               // pruned
   ag2::DevBuf<float> act;                   // LeNet activations

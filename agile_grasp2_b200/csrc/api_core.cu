@@ -32,6 +32,11 @@ int collect_phase_times(ag2_ctx* c) {
       float ms = 0.f;
       if (cudaEventElapsedTime(&ms, c->ev[2 * ph], c->ev[2 * ph + 1]) == cudaSuccess) c->st.ms_phase[ph] = ms;
     }
+    c->st.ms_gap[ph] = 0.0;
+    if (ph > 0 && c->ev_used[2 * ph - 1] && c->ev_used[2 * ph]) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, c->ev[2 * ph - 1], c->ev[2 * ph]) == cudaSuccess && ms > 0.f) c->st.ms_gap[ph] = ms;
+    }
   }
   return AG2_OK;
 }

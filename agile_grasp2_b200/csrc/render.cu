@@ -12,6 +12,7 @@
 //   4. normalise, abs, float image in shared memory, 3x3 max, channel swap,
 //      round-half-even x255 -> u8 HWC (the cv::Mat layout).
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <vector>
@@ -32,6 +33,9 @@ struct RenderArgs {
   const int32_t* pool;
   const ag2_frame* frames;
   uint32_t cap;                // padded capacity (power of two) >= max m
+  uint32_t n;                  // images
+  uint8_t* scratch;            // nullptr: sort arrays in shared memory, one CTA per image; else
+                               // gridDim.x regions of cap*16 bytes in global memory, CTAs loop over images
   uint8_t* out;                // n * 10800
 };
 
@@ -46,14 +50,16 @@ __device__ __forceinline__ double ordd(long long i) {
 __global__ void __launch_bounds__(kRenderThreads)
 k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   extern __shared__ __align__(16) unsigned char smem[];
-  uint64_t* keys = (uint64_t*)smem;                      // cap
+  float* img = (float*)smem;                             // 60*60*3
+  unsigned char* arrays = A.scratch ? A.scratch + (size_t)blockIdx.x * A.cap * 16 : smem + IS * IS * 3 * sizeof(float);
+  uint64_t* keys = (uint64_t*)arrays;                    // cap
   uint32_t* vals = (uint32_t*)(keys + A.cap);            // cap   (sorted positions)
   uint32_t* ckeys = vals + A.cap;                        // cap   (cell << 16 | rank)  [m < 65536]
-  float* img = (float*)(ckeys + A.cap);                  // 60*60*3
   __shared__ long long miny_s;
   __shared__ double FR[3][3];
   const int tid = threadIdx.x;
-  const uint32_t slot = A.list[blockIdx.x];
+  for (uint32_t image = blockIdx.x; image < A.n; image += gridDim.x) {
+  const uint32_t slot = A.list[image];
   const ag2_hypothesis& hyp = A.slots[slot];
   const BoxRef br = A.box_ref[slot];
   const uint32_t m = br.count;
@@ -148,7 +154,7 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   }
   __syncthreads();
   // dilate 3x3 (in-bounds max) -> BGR2RGB -> saturate_cast<uchar>(v * 255) round-half-even
-  uint8_t* out = A.out + (size_t)blockIdx.x * AG2_IMAGE_BYTES;
+  uint8_t* out = A.out + (size_t)image * AG2_IMAGE_BYTES;
   for (int i = tid; i < IS * IS * 3; i += kRenderThreads) {
     int ch = i % 3, c = (i / 3) % IS, r = i / (3 * IS);
     int src_ch = 2 - ch;
@@ -166,6 +172,8 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     int iv = __float2int_rn(v);
     out[i] = (uint8_t)min(max(iv, 0), 255);
   }
+  __syncthreads();  // img, FR and the sort arrays are reused by the next image of this CTA
+  }
 }
 
 }  // namespace
@@ -179,10 +187,19 @@ int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
   }
   uint32_t cap = 64;
   while (cap < c->max_in_box) cap <<= 1;
-  size_t smem = (size_t)cap * 16 + (size_t)IS * IS * 3 * sizeof(float);
-  if (smem > 220 * 1024) {
-    c->err = "render: closing region too large for shared memory";
-    return AG2_E_CAPACITY;
+  const size_t img_bytes = (size_t)IS * IS * 3 * sizeof(float);
+  size_t smem = (size_t)cap * 16 + img_bytes;
+  // closing regions of more than 8192 points (fused multi-view clouds, c4) do not fit beside the
+  // image: the sort arrays then live in global memory (L2 resident) and a fixed set of CTAs
+  // walks the images
+  // test hook: AG2_RENDER_SPILL=1 forces the global-memory path on small scenes
+  const bool force_spill = getenv("AG2_RENDER_SPILL") && atoi(getenv("AG2_RENDER_SPILL")) != 0;
+  const bool spill = force_spill || smem > 220 * 1024;
+  unsigned grid = (unsigned)n;
+  if (spill) {
+    smem = img_bytes;
+    grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * 4);
+    AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 16));
   }
   AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RenderArgs A;
@@ -193,8 +210,10 @@ int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
   A.pool = c->box_pool.p;
   A.frames = c->frames.p;
   A.cap = cap;
+  A.n = (uint32_t)n;
+  A.scratch = spill ? c->render_scratch.p : nullptr;
   A.out = d_out;
-  k_render<<<(unsigned)n, kRenderThreads, smem, c->stream>>>(A, c->hc);
+  k_render<<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }

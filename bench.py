@@ -263,8 +263,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    gaps = {}
+
     def timed(fn, iters, warm):
         phase = {}
+        gaps.clear()
         total_ms, launches, last_stats = 0.0, 0, None
         for it in range(warm + iters):
             flush.zero_()
@@ -283,6 +286,8 @@ def main():
                 launches += st["gpu_launches"]
                 for k, v in st["ms_phase"].items():
                     phase[k] = phase.get(k, 0.0) + v / iters
+                for k, v in st.get("ms_gap", {}).items():
+                    gaps[k] = gaps.get(k, 0.0) + v / iters
                 last_stats = st
         return total_ms, phase, launches, last_stats, out
 
@@ -302,6 +307,7 @@ def main():
     clocks.start()
     tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_packed(packed_d, hint[0], hint[1], hint[2]), K, W)
     clk = clocks.stop()
+    gaps_resident = dict(gaps)
     e2e_ms, _, _, _, sel = timed(lambda: runner.detect_host(xyz_h, cam_h, num_cams, smp_h, hint), K, 1)
     per_rank = None
     if world > 1:  # per-rank view of the step: sample blocks differ in cost, the slowest rank sets the pace
@@ -325,6 +331,7 @@ def main():
                         "d2h_bytes_per_step": int(len(sel) * 192 + 64)},
                 "roofline": roofline_for(phase, st, n_pts, peaks),
                 "phases_ms": {k: round(v, 4) for k, v in phase.items()},
+                "gaps_before_phase_ms": {k: round(v, 4) for k, v in gaps_resident.items()},
                 **({"per_rank": per_rank} if per_rank else {}),
                 "counts": {k: st[k] for k in ("num_hypotheses", "num_pruned", "num_antipodal", "num_selected",
                                               "sum_neighbors_hands", "sum_cropped", "sum_in_box",

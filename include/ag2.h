@@ -157,6 +157,8 @@ typedef struct ag2_stats {
   int64_t sum_neighbors_normals;/* sum over points of k_n */
   int64_t gpu_launches;         /* kernels launched since the last ag2_set_cloud */
   double ms_phase[8];           /* grid, normals, frames, hands, prune, render, lenet, select */
+  double ms_gap[8];             /* stream time between the end of the previous timed phase and the start of this
+                                   one (host round trips, copies, untimed launches) */
 } ag2_stats;
 
 typedef struct ag2_ctx ag2_ctx;

@@ -1336,6 +1336,30 @@ int ag2o_compute_normals(ag2o_ctx* c) {
   if (!c->normals_given) compute_normals(c);
   return AG2_OK;
 }
+// test helper (no counterpart in ag2.h): normals of selected points only, the same per-point code
+// as compute_normals, so that multi-million-point clouds can be spot-checked in seconds
+int ag2o_point_normals(ag2o_ctx* c, const int32_t* idx, size_t n, float* out) {
+  if (!c || !idx || !out) return AG2_E_INVALID;
+  if (c->xyz.empty()) return AG2_E_EMPTY_CLOUD;
+  ensure_tree(c);
+  const size_t N = c->xyz.size() / 3;
+#pragma omp parallel num_threads(c->threads())
+  {
+    std::vector<Neighbor> nn;
+#pragma omp for schedule(dynamic, 8)
+    for (long long k = 0; k < (long long)n; k++) {
+      float* o = out + 3 * (size_t)k;
+      if (idx[k] < 0 || (size_t)idx[k] >= N) {
+        o[0] = o[1] = o[2] = std::numeric_limits<float>::quiet_NaN();
+        continue;
+      }
+      const float* p = &c->xyz[3 * (size_t)idx[k]];
+      radius_search(c, p, c->p.normals_radius, nn);
+      pcl_normal(c->xyz.data(), nn, p, o);
+    }
+  }
+  return AG2_OK;
+}
 int ag2o_generate_hypotheses(ag2o_ctx* c) {
   if (!c) return AG2_E_INVALID;
   if (c->xyz.empty()) return AG2_E_EMPTY_CLOUD;

@@ -77,6 +77,17 @@ def context(params: capi.Params, threads: int | None = None) -> capi.Context:
     return capi.Context(p, api=load())
 
 
+def point_normals(ctx: capi.Context, idx) -> np.ndarray:
+    """Oracle normals of selected cloud points only (the per-point code of compute_normals)."""
+    idx = np.ascontiguousarray(idx, dtype=np.int32)
+    out = np.zeros((len(idx), 3), np.float32)
+    rc = load().lib.ag2o_point_normals(ctx._h, idx.ctypes.data_as(C.c_void_p), C.c_size_t(len(idx)),
+                                       out.ctypes.data_as(C.c_void_p))
+    if rc:
+        raise capi.Ag2Error(rc, "ag2o_point_normals")
+    return out
+
+
 def eigen33(cov: np.ndarray):
     cov = np.ascontiguousarray(cov, dtype=np.float32).reshape(9)
     val = C.c_float()

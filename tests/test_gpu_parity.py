@@ -244,6 +244,18 @@ def test_chunked_hand_staging_and_levelled_normals(tiny_scene, monkeypatch):
         assert np.array_equal(g.in_box(capi.LIST_HYPOTHESES, h), o.in_box(capi.LIST_HYPOTHESES, h))
 
 
+def test_render_spill_path(tiny_scene, monkeypatch):
+    """Closing regions too large for shared memory (c4 densities) sort in global memory with a fixed
+    set of CTAs walking the images; forced here on the tiny scene: image bytes equal the oracle's."""
+    monkeypatch.setenv("AG2_RENDER_SPILL", "1")
+    p = make_params(capi.MODE_PREDICTION, min_score_diff=0.0)
+    g, o = both(p, tiny_scene, weights=ob.xavier_weights(2))
+    for c in (g, o):
+        c.generate_hypotheses(); c.prune()
+    gi, oi = g.render_images(), o.render_images()
+    assert gi.shape == oi.shape and gi.shape[0] > 5 and np.array_equal(gi, oi)
+
+
 def test_c2_full_size_subset():
     """BASELINE.json config c2 at full cloud size (307 200 points, k_n up to ~500): normals of
     every point and the sweep of 48 samples against the oracle."""
