@@ -2,14 +2,16 @@
 // convertToImageRGB (reference learning.cpp:4-33, :221-249, :143-209) and the
 // OpenCV tail dilate(3x3) -> cvtColor(BGR2RGB) -> convertTo(CV_8UC3, 255).
 // One CTA per pruned hypothesis:
-//   1. load its in-box ids from the pool, sort them by (d2, id): the reference's
-//      per-cell double sums run in radiusSearch order, so the order is restored
-//      once here and images come out independent of the hand kernel's schedule;
-//   2. recompute the scaled points / rotated normals with the hand kernel's exact
-//      arithmetic, cell = floor(x'/cs) + 60*floor((y'-min y')/cs)  (no clamping);
-//   3. sort (cell, rank) keys; one thread per cell sums its run in rank order
-//      (the reference scans all m points for each of 3600 cells: O(3600 m));
-//   4. normalise, abs, float image in shared memory, 3x3 max, channel swap,
+//   1. min over the scaled y of its in-box points, then the image cell of every point, computed
+//      with the hand kernel's exact arithmetic: cell = floor(x'/cs) + 60*floor((y'-min y')/cs)
+//      (no clamping), and a histogram over the 3600 cells;
+//   2. counting sort by cell (prefix over the histogram, scatter with a shared-memory cursor);
+//   3. the reference's per-cell double sums run in radiusSearch order (ascending (d2, id)); only the
+//      order inside a cell matters, so each (short) run is ordered by counting smaller keys - no
+//      sort of the whole closing region;
+//   4. one thread per occupied cell sums its run in that order (the reference scans all m points
+//      for each of 3600 cells: O(3600 m));
+//   5. normalise, abs, float image in shared memory, 3x3 max, channel swap,
 //      round-half-even x255 -> u8 HWC (the cv::Mat layout).
 #include <math.h>
 #include <stdlib.h>
@@ -32,10 +34,10 @@ struct RenderArgs {
   const BoxRef* box_ref;
   const int32_t* pool;
   const ag2_frame* frames;
-  uint32_t cap;                // padded capacity (power of two) >= max m
+  uint32_t cap;                // capacity (multiple of 8) >= max m
   uint32_t n;                  // images
   uint8_t* scratch;            // nullptr: sort arrays in shared memory, one CTA per image; else
-                               // gridDim.x regions of cap*16 bytes in global memory, CTAs loop over images
+                               // gridDim.x regions of cap*20 bytes in global memory, CTAs loop over images
   uint8_t* out;                // n * 10800
 };
 
@@ -51,10 +53,15 @@ __global__ void __launch_bounds__(kRenderThreads)
 k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   extern __shared__ __align__(16) unsigned char smem[];
   float* img = (float*)smem;                             // 60*60*3
-  unsigned char* arrays = A.scratch ? A.scratch + (size_t)blockIdx.x * A.cap * 16 : smem + IS * IS * 3 * sizeof(float);
-  uint64_t* keys = (uint64_t*)arrays;                    // cap
-  uint32_t* vals = (uint32_t*)(keys + A.cap);            // cap   (sorted positions)
-  uint32_t* ckeys = vals + A.cap;                        // cap   (cell << 16 | rank)  [m < 65536]
+  unsigned char* arrays = A.scratch ? A.scratch + (size_t)blockIdx.x * A.cap * 20 : smem + IS * IS * 3 * sizeof(float);
+  uint64_t* run_key = (uint64_t*)arrays;                 // cap: (d2, id) of the point in run slot s
+  uint32_t* run_pos = (uint32_t*)(run_key + A.cap);      // cap: its sorted position
+  uint32_t* ord_pos = run_pos + A.cap;                   // cap: the runs again, each in ascending (d2, id) order
+  uint16_t* cellv = (uint16_t*)(ord_pos + A.cap);        // cap: cell of in-box point t (0xFFFF = none)
+  uint16_t* run_cell = cellv + A.cap;                    // cap: cell of run slot s
+  // per image cell: count, then (first run slot | slots still to hand out << 16); [3600] = end sentinel
+  __shared__ uint32_t cellc[IS * IS + 1];
+  __shared__ uint32_t warp_tot[kRenderThreads / 32];
   __shared__ long long miny_s;
   __shared__ double FR[3][3];
   const int tid = threadIdx.x;
@@ -71,21 +78,8 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   }
   if (tid == 0) miny_s = dord(INFINITY);
   for (int i = tid; i < IS * IS * 3; i += kRenderThreads) img[i] = 0.f;
-  const uint32_t n_pad = next_pow2(max(m, 2u));
-  for (uint32_t t = tid; t < n_pad; t += kRenderThreads) {
-    if (t < m) {
-      uint32_t pos = (uint32_t)A.pool[br.offset + t];
-      float4 p = A.g.pts[pos];
-      float d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
-      keys[t] = nn_key(d2, __float_as_uint(p.w));
-      vals[t] = pos;
-    } else {
-      keys[t] = ~0ull;
-      vals[t] = 0;
-    }
-  }
+  for (int i = tid; i <= IS * IS; i += kRenderThreads) cellc[i] = 0;
   __syncthreads();
-  bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kRenderThreads, BlockSync());
   // hand-frame constants of this hypothesis (same values the hand kernel used)
   const int e = hyp.finger_slot;
   const double left = hc.fs_hi[e], right = hc.fs_lo[10 + e];
@@ -97,7 +91,7 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   // pass A: min over scaled y (learning.cpp:149)
   double mny = INFINITY;
   for (uint32_t t = tid; t < m; t += kRenderThreads) {
-    float4 p = A.g.pts[vals[t]];
+    float4 p = A.g.pts[A.pool[br.offset + t]];
     double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
     double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
     mny = fmin(mny, sy * (y - bottom));
@@ -106,39 +100,89 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   if ((tid & 31) == 0) atomicMin(&miny_s, dord(mny));
   __syncthreads();
   const double miny = ordd(miny_s);
-  // pass B: cell of every point
-  for (uint32_t t = tid; t < n_pad; t += kRenderThreads) {
-    uint32_t key = 0xFFFFFFFFu;
-    if (t < m) {
-      float4 p = A.g.pts[vals[t]];
-      double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
-      double x = (FR[0][0] * px + FR[1][0] * py) + FR[2][0] * pz;
-      double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
-      double xs = sx * (x - lc);
-      double ys = sy * (y - bottom) - miny;
-      // floorVector(pts.row(0) / cellsize): true division, floor, int conversion
-      double hc_ = floor(xs / cellsize), vc_ = floor(ys / cellsize);
-      // cell_indices = h + v*60 evaluated in int; guard the int conversion range
-      if (hc_ > -1e6 && hc_ < 1e6 && vc_ > -1e6 && vc_ < 1e6) {
-        int cell = (int)hc_ + (int)vc_ * IS;
-        if (cell >= 0 && cell < IS * IS) key = ((uint32_t)cell << 16) | t;  // else never matched
-      }
+  // pass B: cell of every point, histogram over the 3600 cells
+  for (uint32_t t = tid; t < m; t += kRenderThreads) {
+    uint32_t cell = 0xFFFFu;
+    float4 p = A.g.pts[A.pool[br.offset + t]];
+    double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
+    double x = (FR[0][0] * px + FR[1][0] * py) + FR[2][0] * pz;
+    double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
+    double xs = sx * (x - lc);
+    double ys = sy * (y - bottom) - miny;
+    // floorVector(pts.row(0) / cellsize): true division, floor, int conversion
+    double hc_ = floor(xs / cellsize), vc_ = floor(ys / cellsize);
+    // cell_indices = h + v*60 evaluated in int; guard the int conversion range
+    if (hc_ > -1e6 && hc_ < 1e6 && vc_ > -1e6 && vc_ < 1e6) {
+      int ci = (int)hc_ + (int)vc_ * IS;
+      if (ci >= 0 && ci < IS * IS) cell = (uint32_t)ci;  // else never matched
     }
-    ckeys[t] = key;
+    cellv[t] = (uint16_t)cell;
+    if (cell != 0xFFFFu) atomicAdd(&cellc[cell], 1u);
   }
   __syncthreads();
-  bitonic_sort_u32(ckeys, n_pad, (uint32_t)tid, (uint32_t)kRenderThreads, BlockSync());
-  // pass C: one thread per run start sums the run in rank order (learning.cpp:166-192)
+  // exclusive prefix over the cells: 15 consecutive cells per thread, block scan of the partial sums
+  {
+    constexpr int kPer = (IS * IS + kRenderThreads - 1) / kRenderThreads;
+    uint32_t loc[kPer], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      const int ci = tid * kPer + k;
+      loc[k] = ci < IS * IS ? cellc[ci] : 0u;
+      sum += loc[k];
+    }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t v = __shfl_up_sync(AG2_FULL, incl, o);
+      if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int wv = 0; wv < (tid >> 5); wv++) base += warp_tot[wv];
+    uint32_t run = base + incl - sum;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      const int ci = tid * kPer + k;
+      if (ci < IS * IS) cellc[ci] = run | (loc[k] << 16);
+      run += loc[k];
+    }
+    if (tid == kRenderThreads - 1) cellc[IS * IS] = run;  // number of binned points
+  }
+  __syncthreads();
+  // scatter into the cell runs (any order inside a run) with the radiusSearch key (d2, id)
   for (uint32_t t = tid; t < m; t += kRenderThreads) {
-    uint32_t key = ckeys[t];
-    if (key == 0xFFFFFFFFu) continue;
-    uint32_t cell = key >> 16;
-    if (t > 0 && (ckeys[t - 1] >> 16) == cell) continue;  // not a run start
+    const uint32_t cell = cellv[t];
+    if (cell == 0xFFFFu) continue;
+    const uint32_t old = atomicSub(&cellc[cell], 1u << 16);
+    const uint32_t s = (old & 0xFFFFu) + (old >> 16) - 1u;
+    const uint32_t pos = (uint32_t)A.pool[br.offset + t];
+    const float4 p = A.g.pts[pos];
+    const float d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
+    run_key[s] = nn_key(d2, __float_as_uint(p.w));
+    run_pos[s] = pos;
+    run_cell[s] = (uint16_t)cell;
+  }
+  __syncthreads();
+  // The reference's per-cell double sums run in radiusSearch order (ascending (d2, id)); only the
+  // order INSIDE a cell matters, so each run is ordered by counting smaller keys (runs are short).
+  const uint32_t binned = cellc[IS * IS];
+  for (uint32_t s = tid; s < binned; s += kRenderThreads) {
+    const uint32_t cell = run_cell[s];
+    const uint32_t a = cellc[cell] & 0xFFFFu, b = cellc[cell + 1] & 0xFFFFu;
+    const uint64_t key = run_key[s];
+    uint32_t r = 0;
+    for (uint32_t u = a; u < b; u++) r += run_key[u] < key;
+    ord_pos[a + r] = run_pos[s];
+  }
+  __syncthreads();
+  // one thread per occupied cell sums its run in that order (learning.cpp:166-192)
+  for (uint32_t cell = tid; cell < (uint32_t)(IS * IS); cell += kRenderThreads) {
+    const uint32_t a = cellc[cell] & 0xFFFFu, b = cellc[cell + 1] & 0xFFFFu;
+    if (a == b) continue;
     double ax = 0.0, ay = 0.0, az = 0.0;
-    for (uint32_t u = t; u < m; u++) {
-      uint32_t ku = ckeys[u];
-      if ((ku >> 16) != cell) break;
-      float4 nv = A.g.nrm[vals[ku & 0xFFFFu]];
+    for (uint32_t u = a; u < b; u++) {
+      float4 nv = A.g.nrm[ord_pos[u]];
       double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
       // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
       ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
@@ -185,21 +229,20 @@ int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
     c->err = "render: more than 65535 points in a closing region";
     return AG2_E_CAPACITY;
   }
-  uint32_t cap = 64;
-  while (cap < c->max_in_box) cap <<= 1;
+  const uint32_t cap = (std::max<uint32_t>((uint32_t)c->max_in_box, 8u) + 7u) & ~7u;
   const size_t img_bytes = (size_t)IS * IS * 3 * sizeof(float);
-  size_t smem = (size_t)cap * 16 + img_bytes;
+  size_t smem = (size_t)cap * 20 + img_bytes;
   // closing regions of more than 8192 points (fused multi-view clouds, c4) do not fit beside the
   // image: the sort arrays then live in global memory (L2 resident) and a fixed set of CTAs
   // walks the images
   // test hook: AG2_RENDER_SPILL=1 forces the global-memory path on small scenes
   const bool force_spill = getenv("AG2_RENDER_SPILL") && atoi(getenv("AG2_RENDER_SPILL")) != 0;
-  const bool spill = force_spill || smem > 220 * 1024;
+  const bool spill = force_spill || smem > 200 * 1024;
   unsigned grid = (unsigned)n;
   if (spill) {
     smem = img_bytes;
     grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * 4);
-    AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 16));
+    AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 20));
   }
   AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   RenderArgs A;
