@@ -102,6 +102,7 @@ struct BoxRef {
 struct LeNetDev {
   bool loaded = false;
   DevBuf<float> c1w, c1b, c2w, c2b, i1w, i1b, i2w, i2b;
+  DevBuf<float> c1w_tc;  // conv1 weights split into tf32 terms, two taps per K step
   DevBuf<float> i1w_tc;  // ip1 weights, same treatment, per K step and 128-output tile
   DevBuf<float> c2w_tc;  // conv2 weights split into tf32 terms and tiled per tap (lenet.cu)
   std::vector<float> host[8];

@@ -163,6 +163,121 @@ constexpr int TC_BSLOTS = 4;
 constexpr int TC_SMEM_BYTES = TC_A_BYTES + TC_BSLOTS * TC_BTAP_BYTES + 128;
 constexpr int TC_TMEM_COLS = 512;                                 // 6 x 64 used; power of two
 
+// ---------------------------------------------------------------------------------------------
+// conv1 (3->20, 5x5) + bias + maxpool 2x2 on the tensor cores: the same zero-copy implicit GEMM as
+// conv2 (below), on the 60 x 60 input image.  The u8 image is expanded in shared memory to one
+// 16-byte K chunk per pixel, (c0, c1, c2, 0) as fp32 - exact in tf32, so only the weights are
+// split (2 MMAs per K step: w_lo first, then w_hi).  Image rows are 60 pixels = 960 bytes (SBO)
+// apart; an M = 128 tile is 8 (x) by 16 (y) of the 56 x 56 outputs; tap (ky, kx) moves the start
+// address by ky*60 + kx pixels.  One K step of 8 = TWO taps: the second chunk is simply the same
+// tile one tap further, i.e. LBO = 16 bytes inside a kernel row and (60-4)*16 bytes across rows;
+// 25 taps = 13 steps (the 26th tap has zero weights).  N = 32 columns (20 channels).  Four passes
+// of 7 tiles (y0 = 0, 16, 32, 40; 224 of 256 allocated tensor-memory columns), so two CTAs fit an
+// SM and one CTA's epilogue overlaps the other's MMAs.  728 MMAs per image.
+// ---------------------------------------------------------------------------------------------
+constexpr int C1_PIX = 60 * 60 + 4;                       // one pixel past the end is read by the zero-weight tap
+constexpr int C1_A_BYTES = C1_PIX * 16;                   // 57664
+constexpr int C1_B_FLOATS = 13 * 2 * 2 * 32 * 4;          // [k step][lo/hi... see lenet_upload] = 6656
+constexpr int C1_B_BYTES = C1_B_FLOATS * 4;               // 26624
+constexpr int C1_SMEM_BYTES = C1_A_BYTES + C1_B_BYTES + 64;
+
+__global__ void __launch_bounds__(256, 2)
+k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* [13][hi, lo][2 chunks][32][4] */,
+           const float* __restrict__ bias, float4* __restrict__ out /* [n][5][784] float4 */) {
+  extern __shared__ __align__(128) uint8_t tc_smem[];
+  float4* A = reinterpret_cast<float4*>(tc_smem);
+  uint8_t* B = tc_smem + C1_A_BYTES;
+  uint64_t* wbar = reinterpret_cast<uint64_t*>(tc_smem + C1_A_BYTES + C1_B_BYTES);
+  uint64_t* done = wbar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    tc::mbar_init(wbar, 1);
+    tc::mbar_init(done, 1);
+    tc::mbar_init_fence();
+  }
+  if (warp == 1) tc::tmem_alloc<256>(tmem_slot);
+  __syncthreads();
+  if (tid == 0) {  // the weights: one bulk copy
+    tc::mbar_expect_tx(wbar, C1_B_BYTES);
+    tc::bulk_g2s(B, wtc, C1_B_BYTES, wbar);
+  }
+  // expand the image: 4 pixels = 12 bytes = 3 aligned words per step (cv::split + convertTo(CV_32F) are exact)
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(images + (size_t)blockIdx.x * AG2_IMAGE_BYTES);
+  for (int g4 = tid; g4 < 900; g4 += 256) {
+    const uint32_t w0 = __ldg(&src[3 * g4]), w1 = __ldg(&src[3 * g4 + 1]), w2 = __ldg(&src[3 * g4 + 2]);
+    A[4 * g4 + 0] = make_float4((float)(w0 & 255u), (float)((w0 >> 8) & 255u), (float)((w0 >> 16) & 255u), 0.f);
+    A[4 * g4 + 1] = make_float4((float)(w0 >> 24), (float)(w1 & 255u), (float)((w1 >> 8) & 255u), 0.f);
+    A[4 * g4 + 2] = make_float4((float)((w1 >> 16) & 255u), (float)(w1 >> 24), (float)(w2 & 255u), 0.f);
+    A[4 * g4 + 3] = make_float4((float)((w2 >> 8) & 255u), (float)((w2 >> 16) & 255u), (float)(w2 >> 24), 0.f);
+  }
+  if (tid < 4) A[3600 + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const int wq = warp & 3;
+  float4* o = out + (size_t)blockIdx.x * 5 * (P1 * P1);
+
+  for (int pass = 0; pass < 4; pass++) {
+    const int y0 = pass < 3 ? 16 * pass : 40;
+    if (warp == 0) {
+      const bool leader = tc::elect_one();
+      if (pass == 0) tc::mbar_wait(wbar, 0);
+      tc::fence_after_sync();
+      if (leader) {
+        const uint32_t idesc = tc::idesc_tf32(128, 32);
+        const uint32_t a_base = tc::smem_u32(A) >> 4, b_base = tc::smem_u32(B) >> 4;
+        const uint64_t b_hi64 = tc::smem_desc(0, 512, 128);
+#pragma unroll 1
+        for (int prec = 1; prec >= 0; prec--) {  // w_lo (small terms) first, w_hi last: see k_conv2_tc
+#pragma unroll 1
+          for (int s = 0; s < 13; s++) {
+            const int t0 = 2 * s;  // taps t0 and t0 + 1
+            const uint32_t off = (uint32_t)((t0 / 5) * 60 + t0 % 5);
+            // second chunk = the next tap of the kernel, in 16-byte units (the 26th tap, zero weights, stays inside the image)
+            const uint32_t lbo = (t0 % 5 == 4 && s < 12) ? (60 - 4) : 1;
+            const uint64_t a_desc0 = ((uint64_t)(960 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)lbo << 16) |
+                                     (uint64_t)(a_base + (uint32_t)(y0 * 60) + off);
+            const uint64_t b_desc = b_hi64 | (uint64_t)(b_base + ((s * 2 + prec) * 2) * 32);
+            const uint32_t acc = !(prec == 1 && s == 0);
+#pragma unroll
+            for (int tile = 0; tile < 7; tile++) tc::mma_tf32(tmem + tile * 32, a_desc0 + (uint64_t)(tile * 8), b_desc, idesc, acc);
+          }
+        }
+        tc::mma_commit(done);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(done, pass & 1);
+    tc::fence_after_sync();
+    // epilogue: lane = 8 x positions of image row y0 + 4*wq + lane/8; pool partners are lanes ^1 and ^8
+    if (!(pass == 3 && wq < 2)) {  // rows 40..47 of the last pass repeat the previous one
+      for (int tile = warp >> 2; tile < 7; tile += 2) {
+        float v[32];
+        tc::tmem_ld32(tmem + ((uint32_t)(wq * 32) << 16) + tile * 32, v);
+        tc::tmem_ld_wait();
+        const int py = (y0 + wq * 4 + (lane >> 3)) >> 1, px = (tile * 8 + (lane & 7)) >> 1;
+        const int q = (lane & 1) | ((lane >> 2) & 2);
+#pragma unroll
+        for (int ch = 0; ch < C1_OUT; ch++) {
+          float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
+          v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) + __ldg(&bias[ch]);
+        }
+#pragma unroll
+        for (int cq = 0; cq < 5; cq++)
+          if ((cq & 3) == q) o[cq * (P1 * P1) + py * P1 + px] = make_float4(v[4 * cq], v[4 * cq + 1], v[4 * cq + 2], v[4 * cq + 3]);
+      }
+    }
+    tc::fence_before_sync();
+    __syncthreads();  // the accumulators are overwritten by the next pass
+    tc::fence_after_sync();
+  }
+  if (warp == 1) tc::tmem_dealloc<256>(tmem);
+}
+
 // ip1 on the tensor cores (k_ip1_tc) reduces over K' = 144 positions x 52 channels (50 + 2 zero) =
 // 936 steps of 8, in chunks of 4 channels
 constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
@@ -547,6 +662,25 @@ int lenet_upload(ag2_ctx* c) {
           }
   AG2_CUDA(c, L.c2w_tc.reserve(wtc.size()));
   AG2_CUDA(c, cudaMemcpyAsync(L.c2w_tc.p, wtc.data(), wtc.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+  // conv1 weights for k_conv1_tc: [k step s][hi, lo][chunk = tap 2s, 2s+1][32 out channels][c0, c1, c2, 0]
+  {
+    std::vector<float> w0((size_t)C1_B_FLOATS, 0.f);
+    for (int s2 = 0; s2 < 13; s2++)
+      for (int ck = 0; ck < 2; ck++) {
+        const int t = 2 * s2 + ck;
+        if (t >= 25) continue;
+        for (int n = 0; n < C1_OUT; n++)
+          for (int ic = 0; ic < 3; ic++) {
+            float hi, lo;
+            tc::split_tf32(L.host[0][((size_t)n * 3 + ic) * 25 + t], hi, lo);
+            w0[(((size_t)(s2 * 2 + 0) * 2 + ck) * 32 + n) * 4 + ic] = hi;
+            w0[(((size_t)(s2 * 2 + 1) * 2 + ck) * 32 + n) * 4 + ic] = lo;
+          }
+      }
+    AG2_CUDA(c, L.c1w_tc.reserve(w0.size()));
+    AG2_CUDA(c, cudaMemcpyAsync(L.c1w_tc.p, w0.data(), w0.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   // ip1 weights for k_ip1_tc: [k step][hi/lo][M tile][chunk][128 outputs][4]; K' index
   // k' = 8*step + 4*chunk + e = position*52 + channel (channels 50, 51 and outputs >= 500 are zero)
   {
@@ -582,7 +716,7 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
   const size_t chunk_max = 4096;
   const size_t chunk = std::min(n, chunk_max);
   // test hook: AG2_LENET_SIMT=1 runs the fp32 CUDA-core kernels instead of the tensor-core ones,
-  // 2 = tensor-core conv2 with the CUDA-core ip1
+  // 2 = CUDA-core conv1 and ip1 around the tensor-core conv2
   static const int simt = getenv("AG2_LENET_SIMT") ? atoi(getenv("AG2_LENET_SIMT")) : 0;
   int splits, steps_per_split;
   size_t a2_floats;
@@ -615,14 +749,19 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
   AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM_BYTES));
   for (size_t off = 0; off < n; off += chunk_max) {
     const size_t m = std::min(chunk_max, n - off);
     float* a1 = c->act.p;
     float* a2 = a1 + chunk * 20 * P1 * P1;
     float* part = a2 + a2_floats;
     const float4* a1q = reinterpret_cast<const float4*>(a1);
-    k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
-                                              reinterpret_cast<float4*>(a1));
+    if (simt)
+      k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
+                                                reinterpret_cast<float4*>(a1));
+    else
+      k_conv1_tc<<<(unsigned)m, 256, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
+                                                          reinterpret_cast<float4*>(a1));
     AG2_LAUNCH_CHECK(c);
     if (simt == 1)
       k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);

@@ -66,7 +66,7 @@ def main():
     sgn = lambda a: float(np.mean((np.abs(a) - np.abs(ref)) / np.abs(ref)))
     print("logit magnitude: median %.1f max %.1f" % (np.median(np.abs(ref)), np.abs(ref).max()))
     print("%-34s max rel %.2e   mean signed rel (|x| vs |ref|) %+.2e" % ("oracle (fp32 CPU)", rel(ol), sgn(ol)))
-    for mode, name in (("1", "CUDA cores fp32"), ("2", "tensor conv2 + CUDA-core ip1"), ("0", "tensor conv2 + ip1")):
+    for mode, name in (("1", "CUDA cores fp32"), ("2", "tensor conv2 + CUDA-core ip1"), ("0", "tensor conv1 + conv2 + ip1")):
         for rep in (n, 4500):
             out = "/tmp/lenet_err_%s_%d.npy" % (mode, rep)
             env = dict(os.environ, AG2_LENET_SIMT=mode)
