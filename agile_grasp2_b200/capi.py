@@ -444,6 +444,17 @@ class Context:
         self._call("get_sample_indices", _fptr(idx), C.c_size_t(idx.size), C.byref(n))
         return idx[: int(n.value)].copy()
 
+    def render_point_sets(self, pts, normals, offsets, aligns: bool = False) -> np.ndarray:
+        """Learning::createGraspImage(points, normals, grasp): images of explicit unit-box point sets."""
+        pts = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 3)
+        normals = np.ascontiguousarray(normals, dtype=np.float64).reshape(-1, 3)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        n = len(offsets) - 1
+        out = np.zeros((max(n, 1), 60, 60, 3), dtype=np.uint8)
+        self._call("render_point_sets", _fptr(pts), _fptr(normals), _fptr(offsets), C.c_size_t(n),
+                   C.c_int(1 if aligns else 0), _fptr(out))
+        return out[:n]
+
     def find_clusters(self, which_src: int):
         """HandleSearch::findClusters on list `which_src`; result in LIST_CLUSTERS."""
         self._call("find_clusters", C.c_int(which_src))

@@ -39,6 +39,12 @@ struct RenderArgs {
   uint8_t* scratch;            // nullptr: sort arrays in shared memory, one CTA per image; else
                                // gridDim.x regions of cap*20 bytes in global memory, CTAs loop over images
   uint8_t* out;                // n * 10800
+  // EXPLICIT mode (Learning::createGraspImage(points, normals, grasp), learning.cpp:69-90): image i is
+  // drawn from caller-supplied unit-box points / normals [xoff[i], xoff[i+1]), 3 doubles each
+  const double* xpts;
+  const double* xnrm;
+  const uint32_t* xoff;
+  int aligns;                  // subtract the minimum y first (always done on the detection path)
 };
 
 __device__ __forceinline__ long long dord(double v) {
@@ -49,6 +55,7 @@ __device__ __forceinline__ double ordd(long long i) {
   return __longlong_as_double(i >= 0 ? i : i ^ 0x7fffffffffffffffll);
 }
 
+template <bool EXPLICIT>
 __global__ void __launch_bounds__(kRenderThreads)
 k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -66,24 +73,33 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   __shared__ double FR[3][3];
   const int tid = threadIdx.x;
   for (uint32_t image = blockIdx.x; image < A.n; image += gridDim.x) {
-  const uint32_t slot = A.list[image];
+  const uint32_t slot = EXPLICIT ? 0u : A.list[image];
   const ag2_hypothesis& hyp = A.slots[slot];
-  const BoxRef br = A.box_ref[slot];
+  BoxRef br;
+  if (EXPLICIT) {
+    br.offset = A.xoff[image];
+    br.count = A.xoff[image + 1] - A.xoff[image];
+  } else {
+    br = A.box_ref[slot];
+  }
   const uint32_t m = br.count;
-  const ag2_frame& fr = A.frames[hyp.sample_id];
-  const float q[3] = {(float)fr.sample[0], (float)fr.sample[1], (float)fr.sample[2]};
-  if (tid < 9) {
-    int a = tid / 3, b = tid % 3;  // frame_rot columns: binormal, approach, axis
-    FR[a][b] = b == 0 ? hyp.binormal[a] : (b == 1 ? hyp.approach[a] : hyp.axis[a]);
+  float q[3] = {0.f, 0.f, 0.f};
+  if (!EXPLICIT) {
+    const ag2_frame& fr = A.frames[hyp.sample_id];
+    q[0] = (float)fr.sample[0], q[1] = (float)fr.sample[1], q[2] = (float)fr.sample[2];
+    if (tid < 9) {
+      int a = tid / 3, b = tid % 3;  // frame_rot columns: binormal, approach, axis
+      FR[a][b] = b == 0 ? hyp.binormal[a] : (b == 1 ? hyp.approach[a] : hyp.axis[a]);
+    }
   }
   if (tid == 0) miny_s = dord(INFINITY);
   for (int i = tid; i < IS * IS * 3; i += kRenderThreads) img[i] = 0.f;
   for (int i = tid; i <= IS * IS; i += kRenderThreads) cellc[i] = 0;
   __syncthreads();
   // hand-frame constants of this hypothesis (same values the hand kernel used)
-  const int e = hyp.finger_slot;
+  const int e = EXPLICIT ? 0 : hyp.finger_slot;
   const double left = hc.fs_hi[e], right = hc.fs_lo[10 + e];
-  const double top = hyp.hand_top, bottom = hyp.hand_bottom;
+  const double top = EXPLICIT ? 1.0 : hyp.hand_top, bottom = EXPLICIT ? 0.0 : hyp.hand_bottom;
   const double baseline_const = 0.1;
   const double lc = left - 0.5 * (baseline_const - (right - left));
   const double sx = 1.0 / baseline_const, sy = 1.0 / (top - bottom);
@@ -91,24 +107,34 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   // pass A: min over scaled y (learning.cpp:149)
   double mny = INFINITY;
   for (uint32_t t = tid; t < m; t += kRenderThreads) {
-    float4 p = A.g.pts[A.pool[br.offset + t]];
-    double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
-    double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
-    mny = fmin(mny, sy * (y - bottom));
+    if (EXPLICIT) {
+      mny = fmin(mny, A.xpts[3 * (size_t)(br.offset + t) + 1]);
+    } else {
+      float4 p = A.g.pts[A.pool[br.offset + t]];
+      double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
+      double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
+      mny = fmin(mny, sy * (y - bottom));
+    }
   }
   mny = warp_min_d(mny);
   if ((tid & 31) == 0) atomicMin(&miny_s, dord(mny));
   __syncthreads();
-  const double miny = ordd(miny_s);
+  const double miny = (EXPLICIT && !A.aligns) ? 0.0 : ordd(miny_s);
   // pass B: cell of every point, histogram over the 3600 cells
   for (uint32_t t = tid; t < m; t += kRenderThreads) {
     uint32_t cell = 0xFFFFu;
-    float4 p = A.g.pts[A.pool[br.offset + t]];
-    double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
-    double x = (FR[0][0] * px + FR[1][0] * py) + FR[2][0] * pz;
-    double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
-    double xs = sx * (x - lc);
-    double ys = sy * (y - bottom) - miny;
+    double xs, ys;
+    if (EXPLICIT) {
+      xs = A.xpts[3 * (size_t)(br.offset + t)];
+      ys = A.aligns ? A.xpts[3 * (size_t)(br.offset + t) + 1] - miny : A.xpts[3 * (size_t)(br.offset + t) + 1];
+    } else {
+      float4 p = A.g.pts[A.pool[br.offset + t]];
+      double px = (double)__fsub_rn(p.x, q[0]), py = (double)__fsub_rn(p.y, q[1]), pz = (double)__fsub_rn(p.z, q[2]);
+      double x = (FR[0][0] * px + FR[1][0] * py) + FR[2][0] * pz;
+      double y = (FR[0][1] * px + FR[1][1] * py) + FR[2][1] * pz;
+      xs = sx * (x - lc);
+      ys = sy * (y - bottom) - miny;
+    }
     // floorVector(pts.row(0) / cellsize): true division, floor, int conversion
     double hc_ = floor(xs / cellsize), vc_ = floor(ys / cellsize);
     // cell_indices = h + v*60 evaluated in int; guard the int conversion range
@@ -156,11 +182,16 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     if (cell == 0xFFFFu) continue;
     const uint32_t old = atomicSub(&cellc[cell], 1u << 16);
     const uint32_t s = (old & 0xFFFFu) + (old >> 16) - 1u;
-    const uint32_t pos = (uint32_t)A.pool[br.offset + t];
-    const float4 p = A.g.pts[pos];
-    const float d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
-    run_key[s] = nn_key(d2, __float_as_uint(p.w));
-    run_pos[s] = pos;
+    if (EXPLICIT) {  // per-cell sums run in the order of the caller's list
+      run_key[s] = (uint64_t)t;
+      run_pos[s] = br.offset + t;
+    } else {
+      const uint32_t pos = (uint32_t)A.pool[br.offset + t];
+      const float4 p = A.g.pts[pos];
+      const float d2 = dist2_f(q[0] - p.x, q[1] - p.y, q[2] - p.z);
+      run_key[s] = nn_key(d2, __float_as_uint(p.w));
+      run_pos[s] = pos;
+    }
     run_cell[s] = (uint16_t)cell;
   }
   __syncthreads();
@@ -182,12 +213,17 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     if (a == b) continue;
     double ax = 0.0, ay = 0.0, az = 0.0;
     for (uint32_t u = a; u < b; u++) {
-      float4 nv = A.g.nrm[ord_pos[u]];
-      double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
-      // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
-      ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
-      ay += (FR[0][1] * n0 + FR[1][1] * n1) + FR[2][1] * n2;
-      az += (FR[0][2] * n0 + FR[1][2] * n1) + FR[2][2] * n2;
+      if (EXPLICIT) {
+        const double* nv = A.xnrm + 3 * (size_t)ord_pos[u];
+        ax += nv[0], ay += nv[1], az += nv[2];
+      } else {
+        float4 nv = A.g.nrm[ord_pos[u]];
+        double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
+        // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
+        ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
+        ay += (FR[0][1] * n0 + FR[1][1] * n1) + FR[2][1] * n2;
+        az += (FR[0][2] * n0 + FR[1][2] * n1) + FR[2][2] * n2;
+      }
     }
     double s = 1.0 / sqrt(ax * ax + (ay * ay + az * az));
     int row = (int)cell / IS, col = (int)cell % IS;
@@ -222,17 +258,17 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
 
 }  // namespace
 
-// Renders the hypotheses in slots d_list[0..n) into d_out (n * 10800 bytes).
-int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
-  if (n == 0) return AG2_OK;
-  if (c->max_in_box >= 65536) {
+// Launches k_render for n images whose largest point set has max_points points.
+template <bool EXPLICIT>
+static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) {
+  if (max_points >= 65536) {
     c->err = "render: more than 65535 points in a closing region";
     return AG2_E_CAPACITY;
   }
-  const uint32_t cap = (std::max<uint32_t>((uint32_t)c->max_in_box, 8u) + 7u) & ~7u;
+  const uint32_t cap = (std::max<uint32_t>((uint32_t)max_points, 8u) + 7u) & ~7u;
   const size_t img_bytes = (size_t)IS * IS * 3 * sizeof(float);
   size_t smem = (size_t)cap * 20 + img_bytes;
-  // closing regions of more than 8192 points (fused multi-view clouds, c4) do not fit beside the
+  // closing regions of more than ~8000 points (fused multi-view clouds, c4) do not fit beside the
   // image: the sort arrays then live in global memory (L2 resident) and a fixed set of CTAs
   // walks the images
   // test hook: AG2_RENDER_SPILL=1 forces the global-memory path on small scenes
@@ -244,21 +280,27 @@ int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
     grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * 4);
     AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 20));
   }
-  AG2_CUDA(c, cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  RenderArgs A;
+  AG2_CUDA(c, cudaFuncSetAttribute(k_render<EXPLICIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   A.g = grid_dev(c);
+  A.cap = cap;
+  A.n = (uint32_t)n;
+  A.scratch = spill ? c->render_scratch.p : nullptr;
+  k_render<EXPLICIT><<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
+// Renders the hypotheses in slots d_list[0..n) into d_out (n * 10800 bytes).
+int render_list(ag2_ctx* c, const uint32_t* d_list, size_t n, uint8_t* d_out) {
+  if (n == 0) return AG2_OK;
+  RenderArgs A = {};
   A.list = d_list;
   A.slots = c->slots.p;
   A.box_ref = c->box_ref.p;
   A.pool = c->box_pool.p;
   A.frames = c->frames.p;
-  A.cap = cap;
-  A.n = (uint32_t)n;
-  A.scratch = spill ? c->render_scratch.p : nullptr;
   A.out = d_out;
-  k_render<<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
-  AG2_LAUNCH_CHECK(c);
-  return AG2_OK;
+  return launch_render<false>(c, A, n, c->max_in_box);
 }
 
 int render_compute(ag2_ctx* c) {
@@ -303,6 +345,47 @@ extern "C" int ag2_render_hypotheses(ag2_ctx* c, const int32_t* sample_ids, cons
   AG2_CUDA(c, cudaMemcpyAsync(d_list.p, slots.data(), n * 4, cudaMemcpyHostToDevice, c->stream));
   AG2_TRY(render_list(c, d_list.p, n, d_img.p));
   AG2_CUDA(c, cudaMemcpyAsync(out, d_img.p, n * AG2_IMAGE_BYTES, cudaMemcpyDeviceToHost, c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
+}
+
+// Learning::createGraspImage(points, normals, grasp) (learning.cpp:69-90; convertToImageRGB :143-209 with
+// aligns = false, then convertTo(CV_8UC3, 255)): images of caller-supplied unit-box point sets.  This is
+// the image generator of the ClassificationNode service (classification_node.cpp:75-141).
+extern "C" int ag2_render_point_sets(ag2_ctx* c, const double* pts, const double* normals, const uint32_t* offsets,
+                                     size_t n_images, int aligns, uint8_t* out) {
+  using namespace ag2;
+  if (!c || !offsets || (n_images && !out)) return AG2_E_INVALID;
+  if (n_images == 0) return AG2_OK;
+  const size_t total = offsets[n_images];
+  size_t max_points = 0;
+  for (size_t i = 0; i < n_images; i++) {
+    if (offsets[i + 1] < offsets[i]) return AG2_E_INVALID;
+    max_points = std::max<size_t>(max_points, offsets[i + 1] - offsets[i]);
+  }
+  if (total && (!pts || !normals)) return AG2_E_INVALID;
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  DevBuf<double> d_pts, d_nrm;
+  DevBuf<uint32_t> d_off;
+  DevBuf<uint8_t> d_img;
+  AG2_CUDA(c, d_pts.reserve(std::max<size_t>(3 * total, 1)));
+  AG2_CUDA(c, d_nrm.reserve(std::max<size_t>(3 * total, 1)));
+  AG2_CUDA(c, d_off.reserve(n_images + 1));
+  AG2_CUDA(c, d_img.reserve(n_images * AG2_IMAGE_BYTES));
+  if (total) {
+    AG2_CUDA(c, cudaMemcpyAsync(d_pts.p, pts, 24 * total, cudaMemcpyHostToDevice, c->stream));
+    AG2_CUDA(c, cudaMemcpyAsync(d_nrm.p, normals, 24 * total, cudaMemcpyHostToDevice, c->stream));
+  }
+  AG2_CUDA(c, cudaMemcpyAsync(d_off.p, offsets, 4 * (n_images + 1), cudaMemcpyHostToDevice, c->stream));
+  RenderArgs A = {};
+  A.slots = c->slots.p;  // unused in this mode
+  A.xpts = d_pts.p, A.xnrm = d_nrm.p, A.xoff = d_off.p;
+  A.aligns = aligns;
+  A.out = d_img.p;
+  // the kernel only reads GridDev fields on the hypothesis path; a context without a cloud is fine
+  int rc = launch_render<true>(c, A, n_images, max_points);
+  if (rc != AG2_OK) return rc;
+  AG2_CUDA(c, cudaMemcpyAsync(out, d_img.p, n_images * AG2_IMAGE_BYTES, cudaMemcpyDeviceToHost, c->stream));
   AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   return AG2_OK;
 }

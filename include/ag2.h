@@ -266,6 +266,14 @@ int ag2_render_images(ag2_ctx* ctx, uint8_t* out_or_null);
  * (sample_id, orientation_id) as found in their records; out: n * AG2_IMAGE_BYTES (host). */
 int ag2_render_hypotheses(ag2_ctx* ctx, const int32_t* sample_ids, const int32_t* orientation_ids,
                           size_t n, uint8_t* out);
+/* Learning::createGraspImage(points, normals, grasp) (learning.cpp:69-90): images of caller-supplied
+ * unit-box point sets, the generator behind the ClassificationNode service
+ * (classification_node.cpp:75-141).  Image i is drawn from points / normals
+ * [offsets[i], offsets[i+1]) (3 doubles each, host pointers); aligns = 0 reproduces the reference
+ * (convertToImageRGB(ins, false)), aligns != 0 subtracts the minimum y first as the detection
+ * path does.  out: n_images x 10800 bytes (60 x 60 x 3, HWC). */
+int ag2_render_point_sets(ag2_ctx* ctx, const double* pts, const double* normals, const uint32_t* offsets,
+                          size_t n_images, int aligns, uint8_t* out);
 /* Classifier::ClassifyBatch + thresholding (grasp_detector.cpp:186-209). */
 int ag2_classify(ag2_ctx* ctx);
 /* mode 2: keep isFullAntipodal (grasp_detector.cpp:212-221); mode 0: keep all. */

@@ -13,8 +13,29 @@
 
 class Learning {
  public:
-  Learning(int size, int num_threads) : size_(size), num_threads_(num_threads) {
+  Learning(int size, int num_threads) : size_(size), num_threads_(num_threads), own_(nullptr) {
     if (size != AG2_IMAGE_SIZE) throw std::runtime_error("Learning: only 60 x 60 grasp images are supported");
+  }
+  ~Learning() { ag2_destroy(own_); }
+  Learning(const Learning&) = delete;
+  Learning& operator=(const Learning&) = delete;
+
+  // learning.cpp:69-90: image of explicit unit-box points / normals (convertToImageRGB with aligns = false).
+  // The grasp argument only carries the binormal into the Instance, which the image does not use; idx > -1
+  // (write a jpeg to a fixed path) and is_plotting are left out.
+  ag2shim::Image createGraspImage(const ag2shim::Matrix3Xd& points, const ag2shim::Matrix3Xd& normals,
+                                  const GraspHypothesis& /*grasp*/, int /*idx*/ = -1, bool /*is_plotting*/ = false) {
+    if (points.cols() != normals.cols()) throw std::runtime_error("Learning: points / normals size mismatch");
+    if (!own_) {
+      ag2_params p;
+      ag2_default_params(&p);
+      ag2shim::check(ag2_create(&p, 0, &own_), "ag2_create");
+    }
+    const uint32_t off[2] = {0u, (uint32_t)points.cols()};
+    ag2shim::Image img;
+    ag2shim::check(ag2_render_point_sets(own_, points.data(), normals.data(), off, 1, 0, img.data.data()),
+                   "ag2_render_point_sets", own_);
+    return img;
   }
 
   // learning.cpp:4-33.  The hands must come from the last generateHypotheses / detect call of ONE
@@ -42,6 +63,7 @@ class Learning {
 
  private:
   int size_, num_threads_;
+  ag2_ctx* own_;  // context of the point-set path (the hypothesis path uses the context the hands came from)
 };
 
 typedef std::pair<std::string, float> Prediction;  // caffe_classifier.h:52

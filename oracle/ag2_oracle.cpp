@@ -1055,18 +1055,31 @@ void prune(ag2o_ctx* c) {
   c->st.ms_phase[4] = (omp_get_wtime() - t0) * 1e3;
 }
 
-// Learning::convertToImageRGB(ins, aligns=true) + convertTo (learning.cpp:143-209,16)
-void render_one(const Hyp& h, uint8_t* out) {
+// Learning::convertToImageRGB(ins, aligns) + convertTo (learning.cpp:143-209,16) for m unit-box points
+// pts / nrm (3 doubles each)
+void render_points(const double* pts, const double* nrm, size_t m, bool aligns, uint8_t* out);
+
+void render_one(const Hyp& h, uint8_t* out) { render_points(h.pts.data(), h.nrm.data(), h.in_box.size(), true, out); }
+
+void render_points(const double* h_pts, const double* h_nrm, size_t m, bool aligns, uint8_t* out) {
   const int S = AG2_IMAGE_SIZE;
-  size_t m = h.in_box.size();
-  double miny = std::numeric_limits<double>::infinity();
-  for (size_t j = 0; j < m; j++) miny = std::min(miny, h.pts[3 * j + 1]);
+  double miny = 0.0;
+  if (aligns) {
+    miny = std::numeric_limits<double>::infinity();
+    for (size_t j = 0; j < m; j++) miny = std::min(miny, h_pts[3 * j + 1]);
+  }
   double cellsize = 1.0 / (double)S;
   std::vector<int> cell(m);
   for (size_t j = 0; j < m; j++) {
-    double y = h.pts[3 * j + 1] - miny;
-    int hc = (int)std::floor(h.pts[3 * j] / cellsize);
-    int vc = (int)std::floor(y / cellsize);
+    double y = aligns ? h_pts[3 * j + 1] - miny : h_pts[3 * j + 1];
+    double hcd = std::floor(h_pts[3 * j] / cellsize), vcd = std::floor(y / cellsize);
+    // floorVector -> int (learning.cpp:212-218); far-away points never match a cell index
+    if (!(hcd > -1e6 && hcd < 1e6 && vcd > -1e6 && vcd < 1e6)) {
+      cell[j] = -1;
+      continue;
+    }
+    int hc = (int)hcd;
+    int vc = (int)vcd;
     cell[j] = hc + vc * S;
   }
   // The reference scans all points per cell (O(3600 m)); the accumulation order per
@@ -1076,9 +1089,9 @@ void render_one(const Hyp& h, uint8_t* out) {
   for (size_t j = 0; j < m; j++) {
     int ci = cell[j];
     if (ci < 0 || ci >= S * S) continue;  // never matched by the i-loop (learning.cpp:166-174)
-    acc[3 * ci] += h.nrm[3 * j];
-    acc[3 * ci + 1] += h.nrm[3 * j + 1];
-    acc[3 * ci + 2] += h.nrm[3 * j + 2];
+    acc[3 * ci] += h_nrm[3 * j];
+    acc[3 * ci + 1] += h_nrm[3 * j + 1];
+    acc[3 * ci + 2] += h_nrm[3 * j + 2];
     cnt[ci]++;
   }
   std::vector<float> img(3 * S * S, 0.f);
@@ -1728,6 +1741,18 @@ int ag2o_get_in_box(ag2o_ctx* c, int which, size_t h, int32_t* idx, size_t cap, 
   std::copy(hy.in_box.begin(), hy.in_box.end(), idx);
   return AG2_OK;
 }
+// Learning::createGraspImage(points, normals, grasp) (learning.cpp:69-90): explicit unit-box point sets
+int ag2o_render_point_sets(ag2o_ctx* c, const double* pts, const double* normals, const uint32_t* offsets,
+                           size_t n_images, int aligns, uint8_t* out) {
+  if (!c || !offsets || (n_images && !out)) return AG2_E_INVALID;
+  if (offsets[n_images] && (!pts || !normals)) return AG2_E_INVALID;
+#pragma omp parallel for num_threads(c->threads()) schedule(dynamic, 4)
+  for (long long i = 0; i < (long long)n_images; i++)
+    render_points(pts + 3 * (size_t)offsets[i], normals + 3 * (size_t)offsets[i], offsets[i + 1] - offsets[i], aligns != 0,
+                  out + (size_t)i * AG2_IMAGE_BYTES);
+  return AG2_OK;
+}
+
 int ag2o_get_logits(ag2o_ctx* c, float* out, size_t cap_images) {
   if (!c || !out) return AG2_E_INVALID;
   if (c->logits.size() / 2 > cap_images) return AG2_E_CAPACITY;

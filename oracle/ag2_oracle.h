@@ -29,6 +29,8 @@ int ag2o_set_sample_indices(ag2o_ctx* ctx, const int32_t* idx, size_t n);
 int ag2o_set_sample_points(ag2o_ctx* ctx, const double* xyz, size_t n);
 int ag2o_set_sample_id_offset(ag2o_ctx* ctx, int64_t first_sample_id);
 int ag2o_set_sample_id_map(ag2o_ctx* ctx, int64_t first_sample_id, int64_t stride);
+int ag2o_render_point_sets(ag2o_ctx* ctx, const double* pts, const double* normals, const uint32_t* offsets,
+                           size_t n_images, int aligns, uint8_t* out);
 int ag2o_point_normals(ag2o_ctx* ctx, const int32_t* idx, size_t n, float* out3);
 
 int ag2o_compute_normals(ag2o_ctx* ctx);

@@ -2,9 +2,11 @@
 // grasp images, classify) and the detect_grasps_file flow (src/nodes/grasp_detection_node.cpp:98-120) written
 // against the header-only shims in include/agile_grasp2/, with assertions.  Usage:
 //   test_shim <cloud.pcd> <out.bin>
-// out.bin: uint64 n_processed, uint64 n_samples, int32 samples[], uint64 n_hands, ag2_hypothesis hands[]
+// out.bin: uint64 n_processed, uint64 n_samples, int32 samples[], uint64 n_hands, ag2_hypothesis hands[],
+//          uint64 n_pairs, double pair_scores[] (ClassificationNode flow on the first two hands)
 // (compared with the oracle by tests/test_cpp_shim.py).
 #include <agile_grasp2/caffe_classifier.h>
+#include <agile_grasp2/classification_node.h>
 #include <agile_grasp2/cloud_camera.h>
 #include <agile_grasp2/grasp_detector.h>
 #include <agile_grasp2/hand_search.h>
@@ -103,6 +105,15 @@ int main(int argc, char** argv) {
     std::vector<uint8_t> wire = GraspHypothesis::toGraspListMsg(hands, "base", 1, 2, 3);
     CHECK(wire.size() == 16 + 4 + 4 + hands.size() * 152);
 
+    // ---- ClassificationNode service flow (classification_node.cpp:26-171): two pairs of per-face densities
+    ClassificationNode cls_node("", "", "");
+    std::vector<GraspHypothesis> two(hands.begin(), hands.begin() + std::min<size_t>(hands.size(), 2));
+    std::vector<float> densities;
+    for (size_t k = 0; k < 2 * two.size() * 6; k++) densities.push_back(k % 5 == 3 ? 0.0f : 0.35f + 0.11f * (float)(k % 7));
+    std::vector<double> pair_scores = cls_node.classify(two, densities);
+    CHECK(pair_scores.size() == 2);
+    for (double s : pair_scores) CHECK(std::isfinite(s));
+
     // ---- dump for the oracle comparison
     FILE* f = std::fopen(argv[2], "wb");
     CHECK(f != nullptr);
@@ -117,6 +128,9 @@ int main(int argc, char** argv) {
     v = hands.size();
     std::fwrite(&v, 8, 1, f);
     for (const GraspHypothesis& h : hands) std::fwrite(&h.record(), sizeof(ag2_hypothesis), 1, f);
+    v = pair_scores.size();
+    std::fwrite(&v, 8, 1, f);
+    std::fwrite(pair_scores.data(), 8, pair_scores.size(), f);
     std::fclose(f);
     std::printf("test_shim ok: %zu processed points, %zu hypotheses, %zu selected, %zu importance hands\n", n_proc,
                 hyps.size(), hands.size(), is_hands.size());

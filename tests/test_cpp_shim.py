@@ -58,3 +58,47 @@ def test_cpp_shim_flow_matches_oracle(tiny_scene, tmp_path):
     order_o = np.lexsort((oh["orientation_id"], oh["sample_id"]))
     assert hyp_int_fields_equal(hands[order_g], oh[order_o]) is None
     assert np.allclose(hands[order_g]["bottom"], oh[order_o]["bottom"], rtol=0, atol=1e-9)
+    # ClassificationNode flow: the same densities through a numpy restatement of the point generator
+    # (classification_node.cpp:77-133), the oracle's image and LeNet
+    pos = 24 + 4 * n_smp + 192 * n_h
+    (n_pairs,) = struct.unpack_from("<Q", raw, pos)
+    pair_scores = np.frombuffer(raw, np.float64, n_pairs, pos + 8)
+    two = hands[:2]
+    dens = np.array([0.0 if k % 5 == 3 else np.float32(0.35) + np.float32(0.11) * np.float32(k % 7)
+                     for k in range(2 * len(two) * 6)], np.float32)
+    want = []
+    for i in range(2):
+        sc = []
+        for j, h in enumerate(two):
+            pts, nrm = _fill_unit_box(h, dens, i * len(two) * 6 + j * 6)
+            img = o.render_point_sets(pts, nrm, [0, len(pts)], aligns=False)
+            lg = o.classify_images(img)[0]
+            sc.append(np.float32(lg[1] - lg[0]))
+        want.append(float(np.float32(sum(sc, np.float32(0.0)))) / len(two))
+    assert np.allclose(pair_scores, want, rtol=2e-5, atol=2e-3), (pair_scores, want)
+
+
+def _fill_unit_box(h, dens, start):
+    min_sp, length = np.float32([0.04, 0.02]), np.float32([0.9, 0.9, 0.9, 0.9, 0.5, 0.5])
+    x_start, y_start, var = np.float32([0.25, 0.25, 0.75, 0.75, 0.25, 0.25]), np.float32(0.1), [1, 1, 1, 1, 0, 0]
+    frame = np.stack([h["binormal"], h["approach"], h["axis"]], axis=1)  # columns
+    faces = np.stack([h["binormal"], -1.0 * h["binormal"], -1.0 * h["approach"]], axis=1)
+    ncol = np.zeros((3, 3))
+    for k in range(3):
+        for r in range(3):
+            s = 0.0
+            for a in range(3):
+                s += frame[a, r] * faces[a, k]
+            ncol[r, k] = s
+    pts, nrm = [], []
+    for i in range(6):
+        d = dens[start + i]
+        if not d > 0:
+            continue
+        spacing = float(np.float32(min_sp[i // 4] / d))
+        n = int(np.floor(float(length[i]) / spacing)) + 1
+        p = [float(x_start[i]), float(y_start), 0.0]
+        for _ in range(n):
+            pts.append(list(p)); nrm.append(ncol[:, i // 2].copy())
+            p[var[i]] += spacing
+    return np.array(pts).reshape(-1, 3), np.array(nrm).reshape(-1, 3)

@@ -393,3 +393,21 @@ def test_normals_shards_assemble_to_the_full_result(tiny_scene, world):
     assert a.normals().tobytes() == b.normals().tobytes()
     a.detect(); b.detect()
     assert a.hypotheses(capi.LIST_SELECTED).tobytes() == b.hypotheses(capi.LIST_SELECTED).tobytes()
+
+
+@pytest.mark.parametrize("aligns", [False, True])
+def test_render_point_sets_vs_oracle(aligns):
+    """Learning::createGraspImage(points, normals, grasp) (the ClassificationNode image generator): explicit
+    unit-box point sets, including an empty set, points outside the image and cells hit many times."""
+    rng = np.random.default_rng(23)
+    sizes = [0, 1, 37, 900, 5000]
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+    pts = rng.uniform(-0.05, 1.05, (offs[-1], 3))
+    pts[offs[3]:offs[3] + 300, :2] = [0.41, 0.52]  # 300 points in one cell: in-run ordering of a long run
+    pts[offs[4] + 5] = [1e9, -1e9, 0.0]             # far outside: never matched
+    nrm = rng.normal(size=(offs[-1], 3))
+    g = capi.Context(make_params(capi.MODE_PREDICTION)); o = ob.context(make_params(capi.MODE_PREDICTION))
+    gi, oi = g.render_point_sets(pts, nrm, offs, aligns), o.render_point_sets(pts, nrm, offs, aligns)
+    assert gi.shape == oi.shape == (5, 60, 60, 3)
+    assert np.array_equal(gi, oi)
+    assert not gi[0].any() and gi[3].any()
