@@ -47,7 +47,9 @@ def make_params(capi):
     return p
 
 
-def make_workload(scenes, n_gpus):
+def make_workload(scenes, n_gpus, name="c2"):
+    if name == "c3":  # BASELINE.json configs[2]: fixed 10 000 samples, sharded over the GPUs (strong scaling)
+        return scenes.make_scene("c3")
     sc = scenes.make_scene("c2", num_samples=S_PER_GPU * n_gpus)
     return sc
 
@@ -208,7 +210,12 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def workload_config(n_gpus):
+def workload_config(n_gpus, name="c2"):
+    if name == "c3":
+        return {"workload": "c3: synthetic two-view clutter cloud, 614400 points, 10000 samples x %d orientations in "
+                            "total (strong scaling), antipodal_mode=1 (LeNet, seeded Xavier weights), num_selected=50" % R,
+                "points": 614400, "samples_total": 10000, "orientations": R, "gpus": n_gpus,
+                "l2": "flushed between timed steps (256 MiB write)", "parallelism": "sample-sharded x%d" % n_gpus}
     return {"workload": "c2: synthetic Kinect-resolution single view, 307200 points, %d samples x %d orientations "
                         "per GPU, antipodal_mode=1 (LeNet, seeded Xavier weights), num_selected=50" % (S_PER_GPU, R),
             "points": 307200, "samples_per_gpu": S_PER_GPU, "orientations": R, "gpus": n_gpus,
@@ -222,6 +229,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"],
+                    help="c2 (default, the metric's configuration, weak scaling) or c3 (10 000 samples in total, strong scaling)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -242,7 +251,7 @@ def main():
     W = max(3, args.warmup)
     K = max(1, args.steps)
     p = make_params(capi)
-    sc = make_workload(scenes, world) if rank == 0 or world == 1 else None
+    sc = make_workload(scenes, world, args.workload) if rank == 0 or world == 1 else None
     ctx = capi.Context(p, device=local_rank)
     ctx.init_lenet_xavier(1)
     ext = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
@@ -320,11 +329,12 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     tot_ms, e2e_ms = float(t[0]), float(t[1])
     if rank == 0:
-        pairs = float(S_PER_GPU * world * R)
+        pairs = float(hint[1] * R)  # all samples of the call x orientations
         peaks = measured_peaks()
         line = {"metric": METRIC, "value": pairs * K / (tot_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
-                "warmup": W, "ms_per_step": tot_ms / K, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world),
+                "warmup": W, "ms_per_step": tot_ms / K, "higher_is_better": True,
+                "scaling": "strong" if args.workload == "c3" else "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world, args.workload),
                 "clocks": clk, "gpu_launches": int(launches),
                 "e2e": {"value": pairs * K / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms / K,
                         "h2d_bytes_per_step": int(n_pts * 13 + n_smp * 4),
@@ -336,7 +346,7 @@ def main():
                 "counts": {k: st[k] for k in ("num_hypotheses", "num_pruned", "num_antipodal", "num_selected",
                                               "sum_neighbors_hands", "sum_cropped", "sum_in_box",
                                               "sum_neighbors_normals")}}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.workload == "c2":
             from oracle import binding as ob  # cpu_baseline leg: the oracle is the thing timed here, nothing else
             cb = cpu_reference(ob, capi, scenes, p, 1, 1, S_PER_GPU)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
