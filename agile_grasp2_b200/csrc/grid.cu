@@ -195,11 +195,6 @@ __global__ void k_finalize(const uint32_t* __restrict__ tmp_idx, uint32_t n_fini
   sorted_of_orig[me] = dst;
 }
 
-__global__ void k_fill_u32(uint32_t* p, size_t n, uint32_t v) {
-  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (i < n) p[i] = v;
-}
-
 // One block: fixed-radius query used by ag2_radius_search (test introspection).
 __global__ void k_radius_query(GridDev g, float qx, float qy, float qz, float r2, float rq,
                                uint64_t* __restrict__ keys, uint32_t cap, uint32_t* __restrict__ count) {

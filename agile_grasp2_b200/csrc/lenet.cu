@@ -4,9 +4,12 @@
 //   data[B,3,60,60] (u8 image planes as float 0..255, no mean, no scale)
 //   conv1 20@5x5 -> maxpool 2/2 -> conv2 50@5x5 -> maxpool 2/2 -> ip1 500 -> ReLU -> ip2 2
 // and returns the raw ip2 logits (caffe_classifier.cpp:121-126).
-// Round-1 implementation: fp32 CUDA-core kernels with shared-memory staging and
-// register tiling, pooling / bias / ReLU fused into the producing kernel.  fp32
-// accumulate; summation order differs from Caffe's sgemm, hence the stated
+// conv1, conv2 and ip1 run on the tensor cores (k_conv1_tc, k_conv2_tc, k_ip1_tc: tcgen05 MMA,
+// tf32 operands split into hi + lo terms for fp32 accuracy, accumulators in tensor memory; PTX
+// wrappers in tc_ptx.cuh), pooling / bias fused into the epilogues; k_ip2 finishes the split-K
+// sum, bias, ReLU and the 500 -> 2 product.  The fp32 CUDA-core kernels of the first version
+// (k_conv1_pool, k_conv2_pool, k_ip1_partial) are kept as an independent cross-check
+// (AG2_LENET_SIMT=1).  Summation order differs from Caffe's sgemm either way, hence the stated
 // tolerance on logits.  Built WITH fma contraction.
 #include <math.h>
 #include <stdlib.h>

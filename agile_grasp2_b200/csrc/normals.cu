@@ -1,14 +1,16 @@
 // K4: surface normals, replacing pcl::NormalEstimationOMP (reference
-// hand_search.cpp:83-94).  One warp per point:
+// hand_search.cpp:83-94).  A count pass (thread per point) sizes the work; then one warp per point:
 //   1. gather the r = normals_radius neighbourhood from the cell rows (float d2,
 //      strict <, FLANN L2_Simple order) into shared memory as (d2, id) keys,
-//   2. bitonic-sort the keys: PCL feeds computeMeanAndCovarianceMatrix the
-//      neighbours in radiusSearch order (ascending (d2, id)), and the single-pass
-//      FLOAT moment sums are order dependent at the 1e-3 rad level, so the order
-//      is part of the semantics,
+//   2. order the keys exactly (bucketed rank, see k_normals): PCL feeds
+//      computeMeanAndCovarianceMatrix the neighbours in radiusSearch order (ascending
+//      (d2, id)), and the single-pass FLOAT moment sums are order dependent at the
+//      1e-3 rad level, so the order is part of the semantics,
 //   3. nine lanes run the nine sequential float accumulators in that order,
-//   4. lane 0 solves the 3x3 eigenproblem exactly as pcl::eigen33 does and flips
-//      the normal toward the viewpoint (0,0,0).
+//   4. one thread per point solves the 3x3 eigenproblem exactly as pcl::eigen33 does and
+//      flips the normal toward the viewpoint (0,0,0).
+// Multi-GPU: a rank can be asked for the interleaved 32-point granules it owns only
+// (normals_shard_compute / normals_shard_assemble).
 // Compiled with -fmad=false; every float op below is a separate IEEE operation.
 #include <math.h>
 #include <stdlib.h>
