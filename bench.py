@@ -67,7 +67,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -225,7 +225,7 @@ def workload_config(n_gpus, name="c2"):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -300,6 +300,8 @@ def main():
                 last_stats = st
         return total_ms, phase, launches, last_stats, out
 
+    clocks = ClockSampler(local_rank)  # 20 ms period; started early so that nvidia-smi is up when the timed steps run
+    clocks.start()
     # resident arm: the cloud sits in HBM on rank 0 before the timed region
     # sizes of the synthetic workload are the same on every rank (one tiny broadcast at set-up)
     meta = torch.tensor([n_pts, n_smp, num_cams], dtype=torch.int64, device="cuda")
@@ -312,8 +314,6 @@ def main():
     else:
         packed_d = torch.empty(12 * hint[0] + 4 * hint[1] + hint[0], dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
-    clocks = ClockSampler(local_rank)
-    clocks.start()
     tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_packed(packed_d, hint[0], hint[1], hint[2]), K, W)
     clk = clocks.stop()
     gaps_resident = dict(gaps)
