@@ -62,6 +62,7 @@ class ClockSampler:
 
     def __init__(self, index=0):
         self.rows, self.proc, self.index = [], None, index
+        self.t_begin = self.t_end = None  # wall-clock window of the timed steps; samples outside are dropped
 
     def start(self):
         try:
@@ -75,7 +76,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
 
     def stop(self):
         if not self.proc:
@@ -87,7 +88,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        inside = [r for t, r in self.rows if self.t_begin is None or (self.t_begin <= t <= (self.t_end or t))]
+        for r in (inside or [r for _, r in self.rows][-1:]):
             try:
                 sm.append(float(r[0]))
                 mx.append(float(r[1]))
@@ -274,11 +276,13 @@ def main():
 
     gaps = {}
 
-    def timed(fn, iters, warm):
+    def timed(fn, iters, warm, clock_window=None):
         phase = {}
         gaps.clear()
         total_ms, launches, last_stats = 0.0, 0, None
         for it in range(warm + iters):
+            if it == warm and clock_window is not None:
+                clock_window.t_begin = time.time()
             flush.zero_()
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -290,6 +294,8 @@ def main():
             wall = (time.perf_counter() - t0) * 1e3
             ms = max(e0.elapsed_time(e1), wall if world > 1 else 0.0)
             if it >= warm:
+                if clock_window is not None:
+                    clock_window.t_end = time.time()
                 st = ctx.stats()
                 total_ms += ms
                 launches += st["gpu_launches"]
@@ -314,7 +320,7 @@ def main():
     else:
         packed_d = torch.empty(12 * hint[0] + 4 * hint[1] + hint[0], dtype=torch.uint8, device="cuda")
     torch.cuda.synchronize()
-    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_packed(packed_d, hint[0], hint[1], hint[2]), K, W)
+    tot_ms, phase, launches, st, _ = timed(lambda: runner.detect_packed(packed_d, hint[0], hint[1], hint[2]), K, W, clocks)
     clk = clocks.stop()
     gaps_resident = dict(gaps)
     e2e_ms, _, _, _, sel = timed(lambda: runner.detect_host(xyz_h, cam_h, num_cams, smp_h, hint), K, 1)
