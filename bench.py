@@ -171,6 +171,13 @@ def roofline_for(phase_ms, st, n_points, peaks):
         # 26 flop per neighbour + ~120 per point (eigen33 + flip); FP32, 128 FMA/clk/SM
         ops = 26.0 * st["sum_neighbors_normals"] + 120.0 * n_points
         issue = {"ops": ops, "achieved": ops / t / 1e12, "peak": 2 * 128 * sm_hz / 1e12, "unit": "TFLOP/s (fp32, nominal peak)"}
+        try:  # warp instructions of the phase (ncu, profiles/traffic.json) against 4 issue slots per SM and clock
+            winst = json.load(open(tpath)).get("normals_inst")
+        except Exception:
+            winst = None
+        if winst:
+            issue["warp_inst"] = winst
+            issue["issue_slot_frac"] = winst / t / (4 * sm_hz)
     elif dom == "grid":
         work = 50.0 * n_points
     elif dom == "render":
