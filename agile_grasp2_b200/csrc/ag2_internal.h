@@ -145,6 +145,8 @@ struct ag2_ctx {
   ag2::DevBuf<uint32_t> sorted_of_orig; // n
   ag2::DevBuf<uint32_t> scan_tmp;
   ag2::DevBuf<uint32_t> kn;             // neighbour counts (normals pass)
+  bool pruned_precomputed = false, selected_precomputed = false;  // small lists: built eagerly in one launch
+  size_t pruned_count = 0, selected_count = 0;
   ag2::DevBuf<uint32_t> big_list[2];    // points whose neighbourhood exceeds a launch capacity (ping-pong)
   ag2::DevBuf<uint32_t> scalars;        // small device scratch (counters, maxima, flags)
 

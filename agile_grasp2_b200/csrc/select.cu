@@ -3,6 +3,7 @@
 // mode filters (:170-221) and top-k selection (:238-252).  Integer / compare
 // work over S*R slots: flag -> exclusive scan -> ordered compaction.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -27,57 +28,53 @@ struct PruneArgs {
   int filter_half, enabled;
 };
 
+__device__ __forceinline__ bool prune_keep(const ag2_hypothesis& g, const PruneArgs& a) {
+  if (!a.enabled) return true;
+  if (a.filter_half && !g.half_antipodal) return false;
+  double mn[3], mx[3];
+  for (int d = 0; d < 3; d++) {
+    double v0 = g.bottom[d] + a.half_width * g.binormal[d];
+    double v1 = g.bottom[d] - a.half_width * g.binormal[d];
+    double v2 = g.top[d] + a.half_width * g.binormal[d];
+    double v3 = g.top[d] - a.half_width * g.binormal[d];
+    double v4 = g.bottom[d] - 0.10 * g.approach[d];
+    mn[d] = fmin(fmin(fmin(v0, v1), fmin(v2, v3)), v4);
+    mx[d] = fmax(fmax(fmax(v0, v1), fmax(v2, v3)), v4);
+  }
+  double ap = g.width;
+  return ap >= a.min_aperture && ap <= a.max_aperture && mn[2] >= (double)a.min_z && mn[1] >= (double)a.min_y &&
+         mx[1] <= (double)a.max_y && mn[0] >= (double)a.min_x && mx[0] <= (double)a.max_x;
+}
+
 __global__ void k_flag_pruned(const ag2_sweep_record* __restrict__ sw, const ag2_hypothesis* __restrict__ slots,
                               size_t n, PruneArgs a, uint32_t* __restrict__ flag) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t keep = 0;
-  if (sw[i].emitted) {
-    if (!a.enabled) {
-      keep = 1;
-    } else {
-      const ag2_hypothesis& g = slots[i];
-      if (!a.filter_half || g.half_antipodal) {
-        double mn[3], mx[3];
-        for (int d = 0; d < 3; d++) {
-          double v0 = g.bottom[d] + a.half_width * g.binormal[d];
-          double v1 = g.bottom[d] - a.half_width * g.binormal[d];
-          double v2 = g.top[d] + a.half_width * g.binormal[d];
-          double v3 = g.top[d] - a.half_width * g.binormal[d];
-          double v4 = g.bottom[d] - 0.10 * g.approach[d];
-          mn[d] = fmin(fmin(fmin(v0, v1), fmin(v2, v3)), v4);
-          mx[d] = fmax(fmax(fmax(v0, v1), fmax(v2, v3)), v4);
-        }
-        double ap = g.width;
-        keep = (ap >= a.min_aperture && ap <= a.max_aperture && mn[2] >= (double)a.min_z &&
-                mn[1] >= (double)a.min_y && mx[1] <= (double)a.max_y && mn[0] >= (double)a.min_x &&
-                mx[0] <= (double)a.max_x)
-                   ? 1u
-                   : 0u;
-      }
-    }
-  }
-  flag[i] = keep;
+  flag[i] = (sw[i].emitted && prune_keep(slots[i], a)) ? 1u : 0u;
 }
 
 // mode: 0 keep all of `src`, 2 keep full_antipodal, 1 keep score >= thr (and mark)
+__device__ __forceinline__ bool mode_keep(ag2_hypothesis& g, const float* __restrict__ logits, size_t i, int mode,
+                                          double thr) {
+  if (mode == AG2_MODE_GEOMETRIC) return g.full_antipodal != 0;
+  if (mode == AG2_MODE_PREDICTION) {
+    // grasp_detector.cpp:200: float difference stored in a double
+    double score = (double)__fsub_rn(logits[2 * i + 1], logits[2 * i]);
+    if (score >= thr) {
+      g.score = score;
+      g.full_antipodal = 1;
+      return true;
+    }
+    return false;
+  }
+  return true;
+}
+
 __global__ void k_flag_mode(const uint32_t* __restrict__ src, size_t n, ag2_hypothesis* __restrict__ slots,
                             const float* __restrict__ logits, int mode, double thr, uint32_t* __restrict__ flag) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
-  ag2_hypothesis& g = slots[src[i]];
-  uint32_t keep = 1;
-  if (mode == AG2_MODE_GEOMETRIC) keep = g.full_antipodal ? 1u : 0u;
-  if (mode == AG2_MODE_PREDICTION) {
-    // grasp_detector.cpp:200: float difference stored in a double
-    double score = (double)__fsub_rn(logits[2 * i + 1], logits[2 * i]);
-    keep = score >= thr ? 1u : 0u;
-    if (keep) {
-      g.score = score;
-      g.full_antipodal = 1;
-    }
-  }
-  flag[i] = keep;
+  flag[i] = mode_keep(slots[src[i]], logits, i, mode, thr) ? 1u : 0u;
 }
 
 // out[scan[i]] = src ? src[i] : i   for flagged i
@@ -99,18 +96,20 @@ __global__ void k_gather(const uint32_t* __restrict__ list, size_t n, const ag2_
   reinterpret_cast<uint4*>(&out[rec])[part] = s[part];
 }
 
+// complemented order-preserving code of a double: ascending key == descending score
+__device__ __forceinline__ uint64_t score_key(double score) {
+  long long o = __double_as_longlong(score);
+  unsigned long long u = o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
+  return ~u;
+}
+
 __global__ void k_score_keys(const uint32_t* __restrict__ list, size_t n, const ag2_hypothesis* __restrict__ slots,
                              uint64_t* __restrict__ keys) {
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (i >= n) return;
   // descending score, ties keep list order (documented deviation D4: partial_sort is unstable)
-  long long o = __double_as_longlong(slots[list ? list[i] : (uint32_t)i].score);
-  unsigned long long u = o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
-  // 32 high bits of the order-preserving code are enough to rank float-born scores
-  // only when they are floats; keep it exact instead: rank by full code on the host side
-  keys[i] = ~u;
+  keys[i] = score_key(slots[list ? list[i] : (uint32_t)i].score);
 }
-
 
 // ---- ranking by (key asc, position asc): key = complemented order-preserving code of the
 // score, so ascending key == descending score; equal scores keep list order (D4).
@@ -194,6 +193,109 @@ __global__ void k_take_ranked(const uint32_t* __restrict__ pos, uint32_t k, cons
   if (t < k) out[t] = list[pos[t]];
 }
 
+// ---- small lists: one CTA does flag -> scan -> ordered compaction in a single launch ----------
+// With S*R in the thousands the multi-kernel path above is nothing but launch latency (five
+// launches and a host round trip per list).
+constexpr int kFT = 1024;
+constexpr size_t kFusedMaxSlots = 1u << 16;  // S*R handled by the single-CTA kernel after the hand sweep
+constexpr uint32_t kFusedMaxSelect = 4096;   // pruned hands ranked inside one CTA's shared memory
+
+// exclusive position of this thread's flag among the CTA's flags; `total` = number of flags set
+__device__ __forceinline__ uint32_t block_flag_scan(bool f, uint32_t* warp_sums /* [33] */, uint32_t& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t ballot = __ballot_sync(AG2_FULL, f);
+  if (lane == 0) warp_sums[warp] = __popc(ballot);
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t v = warp_sums[lane];
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(AG2_FULL, incl, o);
+      if (lane >= o) incl += t;
+    }
+    warp_sums[lane] = incl - v;
+    if (lane == 31) warp_sums[32] = incl;
+  }
+  __syncthreads();
+  const uint32_t r = warp_sums[warp] + __popc(ballot & ((1u << lane) - 1));
+  total = warp_sums[32];
+  __syncthreads();
+  return r;
+}
+
+// hypotheses list (emitted slots) and pruned list (emitted slots that pass S13) in slot order
+__global__ void __launch_bounds__(kFT)
+k_lists_after_hands(const ag2_sweep_record* __restrict__ sw, const ag2_hypothesis* __restrict__ slots, uint32_t n,
+                    PruneArgs a, uint32_t* __restrict__ hyp_out, uint32_t* __restrict__ pruned_out,
+                    uint32_t* __restrict__ counts /* [2] */) {
+  __shared__ uint32_t ws[33];
+  uint32_t base_h = 0, base_p = 0;
+  for (uint32_t t0 = 0; t0 < n; t0 += kFT) {
+    const uint32_t i = t0 + threadIdx.x;
+    const bool em = i < n && sw[i].emitted;
+    const bool keep = em && prune_keep(slots[i], a);
+    uint32_t th, tp;
+    const uint32_t rh = block_flag_scan(em, ws, th);
+    const uint32_t rp = block_flag_scan(keep, ws, tp);
+    if (em) hyp_out[base_h + rh] = i;
+    if (keep) pruned_out[base_p + rp] = i;
+    base_h += th, base_p += tp;
+  }
+  if (threadIdx.x == 0) counts[0] = base_h, counts[1] = base_p;
+}
+
+// mode filter over the pruned list -> antipodal list, then its top-k by (score desc, position asc)
+// -> selected list.  n <= kFusedMaxSelect.
+__global__ void __launch_bounds__(kFT)
+k_select_small(const uint32_t* __restrict__ src, uint32_t n, ag2_hypothesis* __restrict__ slots,
+               const float* __restrict__ logits, int mode, double thr, int num_selected,
+               uint32_t* __restrict__ anti_out, uint32_t* __restrict__ sel_out, uint32_t* __restrict__ counts /* [2] */) {
+  extern __shared__ __align__(16) unsigned char sel_smem[];
+  uint64_t* k_s = reinterpret_cast<uint64_t*>(sel_smem);
+  uint32_t* v_s = reinterpret_cast<uint32_t*>(sel_smem + (size_t)kFusedMaxSelect * 8);
+  uint32_t* ws = v_s + kFusedMaxSelect;
+  uint32_t n_a = 0;
+  for (uint32_t t0 = 0; t0 < n; t0 += kFT) {
+    const uint32_t i = t0 + threadIdx.x;
+    bool keep = false;
+    uint32_t slot = 0;
+    if (i < n) {
+      slot = src[i];
+      keep = mode_keep(slots[slot], logits, i, mode, thr);
+    }
+    uint32_t tot;
+    const uint32_t r = block_flag_scan(keep, ws, tot);
+    if (keep) {
+      anti_out[n_a + r] = slot;
+      k_s[n_a + r] = score_key(slots[slot].score);
+      v_s[n_a + r] = n_a + r;
+    }
+    n_a += tot;
+  }
+  uint32_t n_pad = 2;
+  while (n_pad < n_a) n_pad <<= 1;
+  for (uint32_t t = n_a + threadIdx.x; t < n_pad; t += kFT) k_s[t] = ~0ull, v_s[t] = 0xFFFFFFFFu;
+  __syncthreads();
+  for (uint32_t k = 2; k <= n_pad; k <<= 1)
+    for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+      for (uint32_t t = threadIdx.x; t < (n_pad >> 1); t += kFT) {
+        uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+        bool up = ((i & k) == 0);
+        uint64_t ka = k_s[i], kb = k_s[l];
+        uint32_t va = v_s[i], vb = v_s[l];
+        if (kv_greater(ka, va, kb, vb) == up) {
+          k_s[i] = kb, k_s[l] = ka;
+          v_s[i] = vb, v_s[l] = va;
+        }
+      }
+      __syncthreads();
+    }
+  const uint32_t k = (num_selected > 0 && (uint32_t)num_selected < n_a) ? (uint32_t)num_selected : n_a;
+  for (uint32_t t = threadIdx.x; t < k; t += kFT) sel_out[t] = anti_out[v_s[t]];
+  if (threadIdx.x == 0) counts[0] = n_a, counts[1] = k;
+}
+
 }  // namespace
 
 // flags (n entries, 0/1) -> compacted `out`, returns count (one small D2H sync)
@@ -214,22 +316,7 @@ static int compact_list(ag2_ctx* c, size_t n, const uint32_t* src, DevBuf<uint32
   return AG2_OK;
 }
 
-int lists_build_after_hands(ag2_ctx* c) {
-  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
-  AG2_CUDA(c, c->flags.reserve(SR + 1));
-  if (SR) {
-    k_flag_emitted<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, SR, c->flags.p);
-    AG2_LAUNCH_CHECK(c);
-  }
-  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_HYPOTHESES], &c->list_n[AG2_LIST_HYPOTHESES]));
-  for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;
-  c->st.num_hypotheses = (int64_t)c->list_n[AG2_LIST_HYPOTHESES];
-  return AG2_OK;
-}
-
-int prune_compute(ag2_ctx* c) {
-  phase_begin(c, 4);
-  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
+static PruneArgs prune_args(const ag2_ctx* c) {
   PruneArgs a;
   a.half_width = 0.5 * c->p.hand_outer_diameter;
   a.min_aperture = c->p.min_aperture;
@@ -241,12 +328,62 @@ int prune_compute(ag2_ctx* c) {
   a.min_z = c->min_z;
   a.filter_half = c->p.filter_half_grasps;
   a.enabled = c->p.prune;
+  return a;
+}
+
+// test hook: AG2_LISTS_MULTIKERNEL=1 forces the multi-kernel list path
+static bool fused_lists_allowed() {
+  const char* e = getenv("AG2_LISTS_MULTIKERNEL");
+  return !(e && atoi(e) != 0);
+}
+
+int lists_build_after_hands(ag2_ctx* c) {
+  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
+  c->pruned_precomputed = c->selected_precomputed = false;
+  for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;
+  if (SR && SR <= kFusedMaxSlots && fused_lists_allowed()) {
+    // both lists in one launch; the prune stage then only publishes its count
+    cudaStream_t st = c->stream;
+    AG2_CUDA(c, c->list[AG2_LIST_HYPOTHESES].reserve(SR));
+    AG2_CUDA(c, c->list[AG2_LIST_PRUNED].reserve(SR));
+    k_lists_after_hands<<<1, kFT, 0, st>>>(c->sweeps.p, c->slots.p, (uint32_t)SR, prune_args(c),
+                                           c->list[AG2_LIST_HYPOTHESES].p, c->list[AG2_LIST_PRUNED].p,
+                                           c->scalars.p + 56);
+    AG2_LAUNCH_CHECK(c);
+    uint32_t counts[2];
+    AG2_CUDA(c, cudaMemcpyAsync(counts, c->scalars.p + 56, 8, cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    c->list_n[AG2_LIST_HYPOTHESES] = counts[0];
+    c->pruned_count = counts[1];
+    c->pruned_precomputed = true;
+    c->st.num_hypotheses = (int64_t)counts[0];
+    return AG2_OK;
+  }
   AG2_CUDA(c, c->flags.reserve(SR + 1));
   if (SR) {
-    k_flag_pruned<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, c->slots.p, SR, a, c->flags.p);
+    k_flag_emitted<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, SR, c->flags.p);
     AG2_LAUNCH_CHECK(c);
   }
-  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_PRUNED], &c->list_n[AG2_LIST_PRUNED]));
+  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_HYPOTHESES], &c->list_n[AG2_LIST_HYPOTHESES]));
+  c->st.num_hypotheses = (int64_t)c->list_n[AG2_LIST_HYPOTHESES];
+  return AG2_OK;
+}
+
+int prune_compute(ag2_ctx* c) {
+  phase_begin(c, 4);
+  const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
+  c->selected_precomputed = false;
+  if (c->pruned_precomputed) {
+    c->list_n[AG2_LIST_PRUNED] = c->pruned_count;
+  } else {
+    AG2_CUDA(c, c->flags.reserve(SR + 1));
+    if (SR) {
+      k_flag_pruned<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, c->slots.p, SR, prune_args(c),
+                                                                         c->flags.p);
+      AG2_LAUNCH_CHECK(c);
+    }
+    AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_PRUNED], &c->list_n[AG2_LIST_PRUNED]));
+  }
   c->list_rec_valid[AG2_LIST_PRUNED] = false;
   c->st.num_pruned = (int64_t)c->list_n[AG2_LIST_PRUNED];
   phase_end(c, 4);
@@ -256,6 +393,30 @@ int prune_compute(ag2_ctx* c) {
 // antipodal list from the pruned list (mode 1 needs logits of the pruned list)
 int select_mode(ag2_ctx* c) {
   const size_t n = c->list_n[AG2_LIST_PRUNED];
+  c->selected_precomputed = false;
+  const bool clustered = c->p.min_inliers > 0 && c->p.antipodal_mode != AG2_MODE_NONE;
+  if (n && n <= kFusedMaxSelect && !clustered && c->p.antipodal_mode != AG2_MODE_NONE && fused_lists_allowed()) {
+    // filter + rank + take in one launch; select_top then only publishes the count
+    cudaStream_t st = c->stream;
+    AG2_CUDA(c, c->list[AG2_LIST_ANTIPODAL].reserve(n));
+    AG2_CUDA(c, c->list[AG2_LIST_SELECTED].reserve(n));
+    const size_t smem = (size_t)kFusedMaxSelect * 12 + 33 * 4;
+    AG2_CUDA(c, cudaFuncSetAttribute(k_select_small, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_select_small<<<1, kFT, smem, st>>>(c->list[AG2_LIST_PRUNED].p, (uint32_t)n, c->slots.p, c->logits.p,
+                                         c->p.antipodal_mode, c->p.min_score_diff, c->p.num_selected,
+                                         c->list[AG2_LIST_ANTIPODAL].p, c->list[AG2_LIST_SELECTED].p,
+                                         c->scalars.p + 58);
+    AG2_LAUNCH_CHECK(c);
+    uint32_t counts[2];
+    AG2_CUDA(c, cudaMemcpyAsync(counts, c->scalars.p + 58, 8, cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    c->list_n[AG2_LIST_ANTIPODAL] = counts[0];
+    c->selected_count = counts[1];
+    c->selected_precomputed = true;
+    for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;  // scores / flags changed in the slots
+    c->st.num_antipodal = (int64_t)counts[0];
+    return AG2_OK;
+  }
   AG2_CUDA(c, c->flags.reserve(std::max<size_t>(n, c->num_samples * (size_t)c->p.num_orientations) + 1));
   if (n) {
     k_flag_mode<<<(unsigned)((n + kT - 1) / kT), kT, 0, c->stream>>>(
@@ -272,6 +433,13 @@ int select_top(ag2_ctx* c) {
   phase_begin(c, 7);
   cudaStream_t st = c->stream;
   size_t n = c->list_n[AG2_LIST_ANTIPODAL];
+  if (c->selected_precomputed) {
+    c->list_n[AG2_LIST_SELECTED] = c->selected_count;
+    c->list_rec_valid[AG2_LIST_SELECTED] = false;
+    c->st.num_selected = (int64_t)c->selected_count;
+    phase_end(c, 7);
+    return AG2_OK;
+  }
   // 4. clusters (grasp_detector.cpp:229-236): the top-k then ranks the moved / re-scored hands
   const bool clustered = c->p.min_inliers > 0 && c->p.antipodal_mode != AG2_MODE_NONE;
   const ag2_hypothesis* cl_src = nullptr;

@@ -244,6 +244,28 @@ def test_chunked_hand_staging_and_levelled_normals(tiny_scene, monkeypatch):
         assert np.array_equal(g.in_box(capi.LIST_HYPOTHESES, h), o.in_box(capi.LIST_HYPOTHESES, h))
 
 
+@pytest.mark.parametrize("mode", [capi.MODE_GEOMETRIC, capi.MODE_PREDICTION])
+def test_single_launch_and_multi_kernel_lists_agree(tiny_scene, monkeypatch, mode):
+    """Small runs build the hypothesis + pruned lists in one single-CTA launch and filter + rank + take the
+    selection in another; large ones use flag / scan / compact kernels and tile sorts. Same lists either way."""
+    sc = tiny_scene
+    p = make_params(mode, min_score_diff=0.0, num_selected=7)
+    out = []
+    for forced in ("0", "1"):
+        monkeypatch.setenv("AG2_LISTS_MULTIKERNEL", forced)
+        with capi.Context(p) as g:
+            if mode == capi.MODE_PREDICTION:
+                g.set_lenet_weights(ob.xavier_weights(3, bias_scale=0.1))
+            g.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); g.set_sample_indices(sc["samples"])
+            g.detect()
+            out.append([g.hypotheses(w).tobytes() for w in
+                        (capi.LIST_HYPOTHESES, capi.LIST_PRUNED, capi.LIST_ANTIPODAL, capi.LIST_SELECTED)]
+                       + [repr(sorted((k, v) for k, v in g.stats().items() if k.startswith("num_")))])
+    sz = capi.HYPOTHESIS_DTYPE.itemsize
+    assert len(out[0][3]) == min(7 * sz, len(out[0][2])), (out[0][4], [len(x) // sz for x in out[0][:4]])
+    assert out[0] == out[1]
+
+
 def test_render_spill_path(tiny_scene, monkeypatch):
     """Closing regions too large for shared memory (c4 densities) sort in global memory with a fixed
     set of CTAs walking the images; forced here on the tiny scene: image bytes equal the oracle's."""
