@@ -471,6 +471,15 @@ class Context:
         self._call("detect_importance", C.byref(ip))
         self.n_samples = int(ip.num_samples)
 
+    def draw_importance_samples(self, ip: IsParams, rnd: int, hands: np.ndarray) -> np.ndarray:
+        """The sample points of round `rnd` drawn from `hands` (all hands found so far), as
+        detect_importance draws them; [num_samples, 3] float64."""
+        hands = np.ascontiguousarray(hands, dtype=HYPOTHESIS_DTYPE)
+        out = np.zeros((int(ip.num_samples), 3), dtype=np.float64)
+        self._call("draw_importance_samples", C.byref(ip), C.c_int(rnd), hands.ctypes.data_as(C.c_void_p),
+                   C.c_size_t(len(hands)), _fptr(out))
+        return out
+
     def importance_samples(self, rnd: int) -> np.ndarray:
         n = C.c_size_t()
         out = np.zeros((1 << 20, 3), dtype=np.float64)

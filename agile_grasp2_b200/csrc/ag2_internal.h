@@ -181,6 +181,8 @@ struct ag2_ctx {
   ag2::DevBuf<double> is_cand;              // candidate staging
   ag2::DevBuf<int32_t> is_cand_idx;
   ag2::DevBuf<uint8_t> is_accept;
+  ag2::DevBuf<ag2_hypothesis> is_hands_in;  // ag2_draw_importance_samples: caller's hands, drawn samples
+  ag2::DevBuf<double> is_draw;
   ag2::DevBuf<uint8_t> images;              // pruned * 10800 (HWC u8)
   ag2::DevBuf<uint8_t> render_scratch;      // sort arrays of k_render when a closing region exceeds shared memory
   ag2::DevBuf<float> logits;                // pruned * 2

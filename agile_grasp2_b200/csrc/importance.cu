@@ -105,6 +105,91 @@ int append_selected(ag2_ctx* c, size_t cap, int32_t sample_offset) {
   return AG2_OK;
 }
 
+// The sample batch of round `it` (importance_sampling.cpp:47-86): n_gauss draws close to the
+// hands found so far (d_hands: H records on the device; h_hands: the same on the host, or
+// nullptr to have them read back) followed by n_rand random cloud points, written to d_out
+// (3 * num_samples doubles on the device).  Returns with the stream idle.
+int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis* d_hands, size_t H,
+               const ag2_hypothesis* h_hands, double* d_out) {
+  cudaStream_t st = c->stream;
+  const int ns = ip->num_samples;
+  const int n_rand = (int)(ip->prob_rand_samples * ns);  // int num_rand_samples = prob * num_samples
+  const int n_gauss = ns - n_rand;
+  const double sigma = ip->radius;
+  const double coef = -1.0 / (2.0 * sigma);
+  std::vector<double> cand, gauss((size_t)3 * std::max(n_gauss, 1));
+  std::vector<int32_t> cidx, ridx((size_t)std::max(n_rand, 1));
+  std::vector<uint8_t> acc;
+  std::vector<double> surf(3 * H);
+  {
+    // grasp surfaces of all hands so far (host copy for the candidate generator)
+    std::vector<ag2_hypothesis> rec;
+    if (!h_hands) {
+      rec.resize(H);
+      AG2_CUDA(c, cudaMemcpyAsync(rec.data(), d_hands, H * sizeof(ag2_hypothesis), cudaMemcpyDeviceToHost, st));
+      AG2_CUDA(c, cudaStreamSynchronize(st));
+      h_hands = rec.data();
+    }
+    for (size_t k = 0; k < H; k++)
+      for (int a = 0; a < 3; a++) surf[3 * k + a] = h_hands[k].surface[a];
+  }
+  // 3.1 samples close to the grasps found so far
+  int got = 0;
+  uint64_t next_cand = 0;
+  for (int batch_no = 0; got < n_gauss; batch_no++) {
+    if (batch_no >= 4096) {
+      c->err = "importance sampling: rejection sampler did not terminate";
+      return AG2_E_STATE;
+    }
+    const size_t B = ip->method == 1 ? (size_t)(n_gauss - got) : std::max<size_t>(256, (size_t)(n_gauss - got) * 8);
+    cand.resize(3 * B);
+    cidx.resize(B);
+    for (size_t b = 0; b < B; b++) {
+      const uint64_t cid = next_cand + b;
+      const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cid, 6) % (uint64_t)H);
+      cidx[b] = (int32_t)idx;
+      for (int a = 0; a < 3; a++)
+        cand[3 * b + a] = surf[3 * idx + a] + is_normal(ip->seed, (uint64_t)it, cid, a) * sigma;
+    }
+    next_cand += B;
+    if (ip->method == 1) {  // sum of Gaussians: every draw is a sample
+      for (size_t b = 0; b < B; b++, got++)
+        for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
+      break;
+    }
+    AG2_CUDA(c, c->is_cand.reserve(3 * B));
+    AG2_CUDA(c, c->is_cand_idx.reserve(B));
+    AG2_CUDA(c, c->is_accept.reserve(B));
+    acc.resize(B);
+    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand.p, cand.data(), 24 * B, cudaMemcpyHostToDevice, st));
+    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, cidx.data(), 4 * B, cudaMemcpyHostToDevice, st));
+    k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B, d_hands,
+                                                                  (uint32_t)H, coef, c->is_accept.p);
+    AG2_LAUNCH_CHECK(c);
+    AG2_CUDA(c, cudaMemcpyAsync(acc.data(), c->is_accept.p, B, cudaMemcpyDeviceToHost, st));
+    AG2_CUDA(c, cudaStreamSynchronize(st));
+    for (size_t b = 0; b < B && got < n_gauss; b++)
+      if (acc[b]) {
+        for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
+        got++;
+      }
+  }
+  // 3.2 random cloud points
+  for (int j = 0; j < n_rand; j++)
+    ridx[j] = (int32_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)j, 7) % (uint64_t)c->n);
+  // 3.3 the round's sample list, assembled on the device
+  if (n_gauss) AG2_CUDA(c, cudaMemcpyAsync(d_out, gauss.data(), (size_t)24 * n_gauss, cudaMemcpyHostToDevice, st));
+  if (n_rand) {
+    AG2_CUDA(c, c->is_cand_idx.reserve((size_t)n_rand));
+    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, ridx.data(), (size_t)4 * n_rand, cudaMemcpyHostToDevice, st));
+    k_is_gather_points<<<(n_rand + 255) / 256, 256, 0, st>>>(c->xyz_in.p, c->is_cand_idx.p, (uint32_t)n_rand,
+                                                           d_out + (size_t)3 * n_gauss);
+    AG2_LAUNCH_CHECK(c);
+  }
+  AG2_CUDA(c, cudaStreamSynchronize(st));  // the host staging vectors go out of scope
+  return AG2_OK;
+}
+
 }  // namespace
 
 int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
@@ -112,10 +197,6 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
   cudaStream_t st = c->stream;
   const int iters = ip->num_iterations;
   const int ns = ip->num_samples;
-  const int n_rand = (int)(ip->prob_rand_samples * ns);  // int num_rand_samples = prob * num_samples
-  const int n_gauss = ns - n_rand;
-  const double sigma = ip->radius;
-  const double coef = -1.0 / (2.0 * sigma);
   const int R = c->p.num_orientations;
   const size_t per_round_max = (c->p.num_selected > 0 && c->p.antipodal_mode != AG2_MODE_NONE)
                                    ? (size_t)c->p.num_selected
@@ -141,83 +222,14 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
   sample_offset += (int32_t)c->num_samples;
   if (c->list_n[AG2_LIST_IMPORTANCE] == 0) return AG2_OK;  // :40-43
 
-  std::vector<double> cand, gauss((size_t)3 * std::max(n_gauss, 1));
-  std::vector<int32_t> cidx, ridx((size_t)std::max(n_rand, 1));
-  std::vector<uint8_t> acc;
-  std::vector<double> surf;
   for (int it = 0; it < iters; it++) {
-    const size_t H = c->list_n[AG2_LIST_IMPORTANCE];
-    // grasp surfaces of all hands so far (host copy for the candidate generator)
-    {
-      std::vector<ag2_hypothesis> rec(H);
-      AG2_CUDA(c, cudaMemcpyAsync(rec.data(), c->list_rec[AG2_LIST_IMPORTANCE].p, H * sizeof(ag2_hypothesis),
-                                  cudaMemcpyDeviceToHost, st));
-      AG2_CUDA(c, cudaStreamSynchronize(st));
-      surf.resize(3 * H);
-      for (size_t k = 0; k < H; k++)
-        for (int a = 0; a < 3; a++) surf[3 * k + a] = rec[k].surface[a];
-    }
-    // 3.1 samples close to the grasps found so far
-    int got = 0;
-    uint64_t next_cand = 0;
-    for (int batch_no = 0; got < n_gauss; batch_no++) {
-      if (batch_no >= 4096) {
-        c->err = "importance sampling: rejection sampler did not terminate";
-        return AG2_E_STATE;
-      }
-      const size_t B = ip->method == 1 ? (size_t)(n_gauss - got) : std::max<size_t>(256, (size_t)(n_gauss - got) * 8);
-      cand.resize(3 * B);
-      cidx.resize(B);
-      for (size_t b = 0; b < B; b++) {
-        const uint64_t cid = next_cand + b;
-        const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cid, 6) % (uint64_t)H);
-        cidx[b] = (int32_t)idx;
-        for (int a = 0; a < 3; a++)
-          cand[3 * b + a] = surf[3 * idx + a] + is_normal(ip->seed, (uint64_t)it, cid, a) * sigma;
-      }
-      next_cand += B;
-      if (ip->method == 1) {  // sum of Gaussians: every draw is a sample
-        for (size_t b = 0; b < B; b++, got++)
-          for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
-        break;
-      }
-      AG2_CUDA(c, c->is_cand.reserve(3 * B));
-      AG2_CUDA(c, c->is_cand_idx.reserve(B));
-      AG2_CUDA(c, c->is_accept.reserve(B));
-      acc.resize(B);
-      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand.p, cand.data(), 24 * B, cudaMemcpyHostToDevice, st));
-      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, cidx.data(), 4 * B, cudaMemcpyHostToDevice, st));
-      k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B,
-                                                                    c->list_rec[AG2_LIST_IMPORTANCE].p, (uint32_t)H,
-                                                                    coef, c->is_accept.p);
-      AG2_LAUNCH_CHECK(c);
-      AG2_CUDA(c, cudaMemcpyAsync(acc.data(), c->is_accept.p, B, cudaMemcpyDeviceToHost, st));
-      AG2_CUDA(c, cudaStreamSynchronize(st));
-      for (size_t b = 0; b < B && got < n_gauss; b++)
-        if (acc[b]) {
-          for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
-          got++;
-        }
-    }
-    // 3.2 random cloud points
-    for (int j = 0; j < n_rand; j++)
-      ridx[j] = (int32_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)j, 7) % (uint64_t)c->n);
-    // 3.3 the round's sample list, assembled on the device
     AG2_CUDA(c, c->sample_xyz.reserve((size_t)3 * ns));
-    if (n_gauss)
-      AG2_CUDA(c, cudaMemcpyAsync(c->sample_xyz.p, gauss.data(), (size_t)24 * n_gauss, cudaMemcpyHostToDevice, st));
-    if (n_rand) {
-      AG2_CUDA(c, c->is_cand_idx.reserve((size_t)n_rand));
-      AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, ridx.data(), (size_t)4 * n_rand, cudaMemcpyHostToDevice, st));
-      k_is_gather_points<<<(n_rand + 255) / 256, 256, 0, st>>>(c->xyz_in.p, c->is_cand_idx.p, (uint32_t)n_rand,
-                                                             c->sample_xyz.p + (size_t)3 * n_gauss);
-      AG2_LAUNCH_CHECK(c);
-    }
+    AG2_TRY(draw_round(c, ip, it, c->list_rec[AG2_LIST_IMPORTANCE].p, c->list_n[AG2_LIST_IMPORTANCE], nullptr,
+                       c->sample_xyz.p));
     AG2_CUDA(c, cudaMemcpyAsync(c->is_samples.p + 3 * c->is_samples_n, c->sample_xyz.p, (size_t)24 * ns,
                                 cudaMemcpyDeviceToDevice, st));
     c->is_round_offset.push_back(c->is_samples_n);
     c->is_samples_n += (size_t)ns;
-    AG2_CUDA(c, cudaStreamSynchronize(st));  // ridx / gauss staging is reused by the next round
     c->use_points = true;
     c->num_samples = (size_t)ns;
     c->st.num_samples = (int64_t)ns;
@@ -265,6 +277,23 @@ int ag2_detect_importance(ag2_ctx* c, const ag2_is_params* p) {
   if (c->n == 0) return AG2_E_EMPTY_CLOUD;
   if (c->num_samples == 0) return AG2_E_NO_SAMPLES;
   return importance_detect(c, p);
+}
+
+int ag2_draw_importance_samples(ag2_ctx* c, const ag2_is_params* p, int round, const ag2_hypothesis* hands,
+                                size_t n_hands, double* xyz_out) {
+  if (!c || !p || !hands || !xyz_out || n_hands == 0 || round < 0 || p->num_samples < 1 || !(p->radius > 0) ||
+      p->prob_rand_samples < 0 || p->prob_rand_samples > 1 || (p->method != 1 && p->method != 2))
+    return AG2_E_INVALID;
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  if (c->n == 0) return AG2_E_EMPTY_CLOUD;
+  AG2_CUDA(c, c->is_hands_in.reserve(n_hands));
+  AG2_CUDA(c, c->is_draw.reserve((size_t)3 * p->num_samples));
+  AG2_CUDA(c, cudaMemcpyAsync(c->is_hands_in.p, hands, n_hands * sizeof(ag2_hypothesis), cudaMemcpyHostToDevice,
+                              c->stream));
+  AG2_TRY(draw_round(c, p, round, c->is_hands_in.p, n_hands, hands, c->is_draw.p));
+  AG2_CUDA(c, cudaMemcpyAsync(xyz_out, c->is_draw.p, (size_t)24 * p->num_samples, cudaMemcpyDeviceToHost, c->stream));
+  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return AG2_OK;
 }
 
 int ag2_get_importance_samples(ag2_ctx* c, int round, double* xyz, size_t cap, size_t* n) {

@@ -174,6 +174,56 @@ class ShardedDetector:
             return merge_selected(self._gather_fixed(local, p.num_selected), p.num_selected)
         return merge_selected(self._gather(local), p.num_selected, keep_all=p.antipodal_mode == capi.MODE_NONE)
 
+    def _run_block_points(self, points_all: np.ndarray):
+        """Same as _run_block for xyz samples (importance-sampling rounds)."""
+        mine = np.ascontiguousarray(points_all[self.rank::self.world])
+        p = self.ctx.params
+        topk = p.num_selected > 0 and p.antipodal_mode != capi.MODE_NONE
+        local = np.zeros(0, capi.HYPOTHESIS_DTYPE)
+        if len(mine):
+            self.ctx.set_sample_points(mine)
+            self.ctx.set_sample_id_map(self.rank, self.world)
+            self.ctx.detect()
+            which = capi.LIST_SELECTED if (self.world == 1 or topk) else capi.LIST_ANTIPODAL
+            local = self.ctx.hypotheses(which).copy()
+            local["sample_id"] = self.rank + self.world * local["sample_id"]
+        if self.world == 1:
+            return local
+        if topk:
+            return merge_selected(self._gather_fixed(local, p.num_selected), p.num_selected)
+        return merge_selected(self._gather(local), p.num_selected, keep_all=p.antipodal_mode == capi.MODE_NONE)
+
+    def detect_importance_numpy(self, xyz, cam, num_cams, samples, ip):
+        """ImportanceSampling::detectGraspPoses (importance_sampling.cpp:30-103) over all ranks: the
+        cloud is broadcast once and its index and normals stay resident on every rank; every round's
+        samples are sharded like a plain detect call and the per-round selections merged, so all
+        ranks hold the same hands found so far and draw the SAME next batch from them (counter-based
+        stream; no collective for the sampler).  Returns the hands of all rounds (the single-GPU
+        LIST_IMPORTANCE: per-round selection order, sample_id counting through the rounds).  The
+        final clustering of the reference (:105-109) is left to the caller."""
+        if self.ctx.params.min_inliers > 0:
+            raise ValueError("sharded importance sampling returns the unclustered hands: set min_inliers = 0")
+        if self.rank == 0:
+            tx, tc, ts = (torch.from_numpy(np.ascontiguousarray(xyz)).to(self.device),
+                          torch.from_numpy(np.ascontiguousarray(cam)).to(self.device),
+                          torch.from_numpy(np.ascontiguousarray(samples, dtype=np.int32)).to(self.device))
+        else:
+            tx = tc = ts = None
+        tx, tc, num_cams, ts = self._broadcast_inputs(tx, tc, num_cams, ts)
+        self.ctx.set_cloud(tx.cpu().numpy(), tc.cpu().numpy(), num_cams)
+        smp = ts.cpu().numpy()
+        hands = self._run_block(smp)
+        offset = len(smp)
+        if len(hands) == 0:
+            return hands
+        for it in range(int(ip.num_iterations)):
+            pts = self.ctx.draw_importance_samples(ip, it, hands)
+            sel = self._run_block_points(pts)
+            sel["sample_id"] += offset
+            offset += len(pts)
+            hands = np.concatenate([hands, sel])
+        return hands
+
     def detect_device(self, xyz_d, cam_d, num_cams, samples_d, shape_hint=None):
         """Cloud resident in HBM on rank 0 (torch CUDA tensors)."""
         xyz_d, cam_d, num_cams, samples_d = self._broadcast_inputs(xyz_d, cam_d, num_cams, samples_d, shape_hint)

@@ -304,6 +304,13 @@ int ag2_default_is_params(ag2_is_params* p);
  * The grid and the normals are built once and reused by every round.  Result:
  * AG2_LIST_IMPORTANCE (records of all rounds; sample_id counts through the rounds). */
 int ag2_detect_importance(ag2_ctx* ctx, const ag2_is_params* p);
+/* One step of the above for callers that run the rounds themselves (the multi-GPU host shards every
+ * round's samples over the ranks and merges the selections): draws the num_samples sample points of
+ * round `round` (0-based) from `hands` = all hands found so far (host records, n_hands > 0), exactly as
+ * ag2_detect_importance does (importance_sampling.cpp:47-86, :115-157); xyz_out: 3 * num_samples
+ * doubles on the host.  Needs the cloud (random part); does not touch the ctx's samples or lists. */
+int ag2_draw_importance_samples(ag2_ctx* ctx, const ag2_is_params* p, int round, const ag2_hypothesis* hands,
+                                size_t n_hands, double* xyz_out);
 /* Samples drawn in round `round` (0-based), 3 doubles each, for the parity tests. */
 int ag2_get_importance_samples(ag2_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);
 int ag2_synchronize(ag2_ctx* ctx);

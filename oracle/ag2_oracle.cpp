@@ -1544,6 +1544,47 @@ inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) 
   double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
   return std::sqrt(-2.0 * std::log(u1)) * std::cos(2.0 * M_PI * u2);
 }
+// the sample batch of one round, importance_sampling.cpp:47-86 with the samplers :115-157
+void is_draw_round(ag2o_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis* hands, size_t H,
+                   double* samples) {
+  const int ns = ip->num_samples;
+  const int num_rand_samples = (int)(ip->prob_rand_samples * ns);  // :47
+  const int num_gauss_samples = ns - num_rand_samples;
+  const double sigma = ip->radius;
+  const double term = 1.0 / std::sqrt(std::pow(2.0 * M_PI, 3.0) * std::pow(sigma, 3.0));  // :53
+  const size_t npts = c->xyz.size() / 3;
+  uint64_t cand = 0;
+  int j = 0;
+  while (j < num_gauss_samples) {  // :132-156 (method 2) / :118-124 (method 1)
+    const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cand, 6) % (uint64_t)H);
+    double x[3];
+    for (int a = 0; a < 3; a++) x[a] = hands[idx].surface[a] + is_normal(ip->seed, (uint64_t)it, cand, a) * sigma;
+    cand++;
+    bool take = true;
+    if (ip->method == 2) {
+      double maxp = 0;
+      for (size_t k = 0; k < H; k++) {
+        V3 d = v3(x[0] - hands[k].surface[0], x[1] - hands[k].surface[1], x[2] - hands[k].surface[2]);
+        double p = dot3(d, d);
+        p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
+        if (p > maxp) maxp = p;
+      }
+      V3 d = v3(x[0] - hands[idx].surface[0], x[1] - hands[idx].surface[1], x[2] - hands[idx].surface[2]);
+      double p = dot3(d, d);
+      p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
+      take = p >= maxp;
+    }
+    if (take) {
+      for (int a = 0; a < 3; a++) samples[3 * (size_t)j + a] = x[a];
+      j++;
+    }
+  }
+  for (int jj = num_gauss_samples; jj < ns; jj++) {  // :79-86
+    size_t r = (size_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)(jj - num_gauss_samples), 7) %
+                        (uint64_t)npts);
+    for (int a = 0; a < 3; a++) samples[3 * (size_t)jj + a] = (double)c->xyz[3 * r + a];
+  }
+}
 void is_append_selected(ag2o_ctx* c, int32_t sample_offset) {
   for (size_t i : c->selected) {
     ag2_hypothesis h = c->hyps[i].rec;
@@ -1582,46 +1623,9 @@ int ag2o_detect_importance(ag2o_ctx* c, const ag2_is_params* ip) {
   sample_offset += (int32_t)c->num_samples();
   if (c->is_hands.empty()) return AG2_OK;
   const int ns = ip->num_samples;
-  const int num_rand_samples = (int)(ip->prob_rand_samples * ns);  // :47
-  const int num_gauss_samples = ns - num_rand_samples;
-  const double sigma = ip->radius;
-  const double term = 1.0 / std::sqrt(std::pow(2.0 * M_PI, 3.0) * std::pow(sigma, 3.0));  // :53
-  const size_t npts = c->xyz.size() / 3;
   for (int it = 0; it < ip->num_iterations; it++) {
-    const std::vector<ag2_hypothesis>& hands = c->is_hands;
-    const size_t H = hands.size();
     std::vector<double> samples((size_t)3 * ns);
-    uint64_t cand = 0;
-    int j = 0;
-    while (j < num_gauss_samples) {  // :132-156 (method 2) / :118-124 (method 1)
-      const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cand, 6) % (uint64_t)H);
-      double x[3];
-      for (int a = 0; a < 3; a++) x[a] = hands[idx].surface[a] + is_normal(ip->seed, (uint64_t)it, cand, a) * sigma;
-      cand++;
-      bool take = true;
-      if (ip->method == 2) {
-        double maxp = 0;
-        for (size_t k = 0; k < H; k++) {
-          V3 d = v3(x[0] - hands[k].surface[0], x[1] - hands[k].surface[1], x[2] - hands[k].surface[2]);
-          double p = dot3(d, d);
-          p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
-          if (p > maxp) maxp = p;
-        }
-        V3 d = v3(x[0] - hands[idx].surface[0], x[1] - hands[idx].surface[1], x[2] - hands[idx].surface[2]);
-        double p = dot3(d, d);
-        p = term * std::exp((-1.0 / (2.0 * sigma)) * p);
-        take = p >= maxp;
-      }
-      if (take) {
-        for (int a = 0; a < 3; a++) samples[3 * (size_t)j + a] = x[a];
-        j++;
-      }
-    }
-    for (int jj = num_gauss_samples; jj < ns; jj++) {  // :79-86
-      size_t r = (size_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)(jj - num_gauss_samples), 7) %
-                          (uint64_t)npts);
-      for (int a = 0; a < 3; a++) samples[3 * (size_t)jj + a] = (double)c->xyz[3 * r + a];
-    }
+    is_draw_round(c, ip, it, c->is_hands.data(), c->is_hands.size(), samples.data());
     c->is_round_samples.push_back(samples);
     if ((rc = ag2o_set_sample_points(c, samples.data(), (size_t)ns))) return rc;  // :89
     if ((rc = ag2o_detect(c))) return rc;                                          // :90
@@ -1629,6 +1633,14 @@ int ag2o_detect_importance(ag2o_ctx* c, const ag2_is_params* ip) {
     sample_offset += ns;
   }
   if (no_cluster.saved > 0) find_clusters(c->is_hands, no_cluster.saved, c->clusters);  // :105-109
+  return AG2_OK;
+}
+
+int ag2o_draw_importance_samples(ag2o_ctx* c, const ag2_is_params* ip, int round, const ag2_hypothesis* hands,
+                                 size_t n_hands, double* xyz_out) {
+  if (!c || !ip || !hands || !xyz_out || n_hands == 0 || round < 0) return AG2_E_INVALID;
+  if (c->xyz.empty()) return AG2_E_EMPTY_CLOUD;
+  is_draw_round(c, ip, round, hands, n_hands, xyz_out);
   return AG2_OK;
 }
 

@@ -50,6 +50,8 @@ int ag2o_get_sample_indices(ag2o_ctx* ctx, int32_t* idx, size_t cap, size_t* n);
 int ag2o_find_clusters(ag2o_ctx* ctx, int which_src);
 int ag2o_default_is_params(ag2_is_params* p);
 int ag2o_detect_importance(ag2o_ctx* ctx, const ag2_is_params* p);
+int ag2o_draw_importance_samples(ag2o_ctx* ctx, const ag2_is_params* p, int round, const ag2_hypothesis* hands,
+                                 size_t n_hands, double* xyz_out);
 int ag2o_get_importance_samples(ag2o_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);
 
 int ag2o_num_hypotheses(ag2o_ctx* ctx, int which, size_t* n);

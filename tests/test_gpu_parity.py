@@ -317,6 +317,30 @@ def test_importance_sampling_rounds(tiny_scene, method):
         assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
 
 
+@pytest.mark.parametrize("mode", [capi.MODE_NONE, capi.MODE_PREDICTION])
+def test_importance_rounds_driven_by_the_sharded_host(tiny_scene, mode):
+    """The multi-GPU host runs the rounds itself (ag2_draw_importance_samples + one sharded detect per
+    round); with one rank the result is the list ag2_detect_importance builds."""
+    from agile_grasp2_b200 import sharded
+    sc = tiny_scene
+    p = make_params(mode, num_selected=12, min_score_diff=-1e9)
+    with capi.Context(p) as a, capi.Context(p) as b:
+        a.init_lenet_xavier(3); b.init_lenet_xavier(3)
+        ip = a.default_is_params()
+        ip.num_iterations, ip.num_samples, ip.seed = 3, 40, 9
+        a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"])
+        a.detect_importance(ip)
+        want = a.hypotheses(capi.LIST_IMPORTANCE)
+        got = sharded.ShardedDetector(b).detect_importance_numpy(sc["xyz"], sc["cam_mask"], sc["num_cams"],
+                                                                  sc["samples"], ip)
+        assert got.tobytes() == want.tobytes(), (len(got), len(want))
+        assert len(want) > 12
+        # the drawn batches themselves
+        for r in range(3):
+            upto = want[want["sample_id"] < len(sc["samples"]) + 40 * r]
+            assert np.array_equal(b.draw_importance_samples(ip, r, upto), a.importance_samples(r)), r
+
+
 @pytest.mark.parametrize("voxelize", [True, False])
 def test_preprocess_cloud(tiny_scene, voxelize):
     """f1: CloudCamera::filterWorkspace + voxelizeCloud + subsampleUniformly, bit-exact."""
