@@ -26,6 +26,10 @@ namespace {
 
 constexpr int kRenderThreads = 256;
 constexpr int IS = AG2_IMAGE_SIZE;
+constexpr int IP = IS + 2;                       // image with a one-cell zero border (dilate needs no bounds tests)
+constexpr size_t kImgBytes = (size_t)IP * IP * 8;   // per cell: u16x2 (out ch 0, out ch 1) | u16x2 (out ch 2, 0)
+constexpr size_t kOutBytes = (size_t)AG2_IMAGE_BYTES;
+constexpr uint32_t kSmallCap = 3072;             // size class 1: three CTAs per SM
 
 struct RenderArgs {
   GridDev g;
@@ -34,10 +38,11 @@ struct RenderArgs {
   const BoxRef* box_ref;
   const int32_t* pool;
   const ag2_frame* frames;
-  uint32_t cap;                // capacity (multiple of 8) >= max m
+  uint32_t cap;                // capacity (multiple of 8) >= largest m of this launch
+  uint32_t m_lo, m_hi;         // size class of this launch: images with m outside [m_lo, m_hi] are skipped
   uint32_t n;                  // images
-  uint8_t* scratch;            // nullptr: sort arrays in shared memory, one CTA per image; else
-                               // gridDim.x regions of cap*20 bytes in global memory, CTAs loop over images
+  uint8_t* scratch;            // nullptr: sort arrays in shared memory; else gridDim.x regions of cap*16 bytes
+                               // in global memory (closing regions too large for shared memory)
   uint8_t* out;                // n * 10800
   // EXPLICIT mode (Learning::createGraspImage(points, normals, grasp), learning.cpp:69-90): image i is
   // drawn from caller-supplied unit-box points / normals [xoff[i], xoff[i+1]), 3 doubles each
@@ -47,6 +52,23 @@ struct RenderArgs {
   int aligns;                  // subtract the minimum y first (always done on the detection path)
 };
 
+// Shared-memory plan.  Region 1 holds the 64-bit keys while the runs are ordered and the image
+// afterwards; region 2 holds run_pos / ord / run_cell until the cell sums are done and the output
+// bytes afterwards.
+struct RenderSmem {
+  size_t r1, r2, total;
+};
+__host__ __device__ inline RenderSmem render_smem(uint32_t cap, bool scratch) {
+  RenderSmem L;
+  const size_t arr = scratch ? 0 : (size_t)cap * 8;
+  L.r1 = 0;
+  const size_t s1 = arr > kImgBytes ? arr : kImgBytes;
+  L.r2 = (s1 + 15) & ~(size_t)15;
+  const size_t s2 = arr > kOutBytes ? arr : kOutBytes;
+  L.total = L.r2 + ((s2 + 15) & ~(size_t)15);
+  return L;
+}
+
 __device__ __forceinline__ long long dord(double v) {
   long long i = __double_as_longlong(v);
   return i >= 0 ? i : i ^ 0x7fffffffffffffffll;
@@ -54,18 +76,26 @@ __device__ __forceinline__ long long dord(double v) {
 __device__ __forceinline__ double ordd(long long i) {
   return __longlong_as_double(i >= 0 ? i : i ^ 0x7fffffffffffffffll);
 }
+// saturate_cast<uchar>(v * 255): float product, round half to even, clamp
+__device__ __forceinline__ uint32_t to_u8(double v) {
+  const int iv = __float2int_rn(__fmul_rn((float)fabs(v), 255.0f));
+  return (uint32_t)min(max(iv, 0), 255);
+}
 
 template <bool EXPLICIT>
 __global__ void __launch_bounds__(kRenderThreads)
 k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   extern __shared__ __align__(16) unsigned char smem[];
-  float* img = (float*)smem;                             // 60*60*3
-  unsigned char* arrays = A.scratch ? A.scratch + (size_t)blockIdx.x * A.cap * 20 : smem + IS * IS * 3 * sizeof(float);
-  uint64_t* run_key = (uint64_t*)arrays;                 // cap: (d2, id) of the point in run slot s
-  uint32_t* run_pos = (uint32_t*)(run_key + A.cap);      // cap: its sorted position
-  uint32_t* ord_pos = run_pos + A.cap;                   // cap: the runs again, each in ascending (d2, id) order
-  uint16_t* cellv = (uint16_t*)(ord_pos + A.cap);        // cap: cell of in-box point t (0xFFFF = none)
-  uint16_t* run_cell = cellv + A.cap;                    // cap: cell of run slot s
+  const RenderSmem L = render_smem(A.cap, A.scratch != nullptr);
+  unsigned char* arr = A.scratch ? A.scratch + (size_t)blockIdx.x * A.cap * 16 : nullptr;
+  uint64_t* run_key = (uint64_t*)(arr ? arr : smem + L.r1);        // cap: (d2, id) of the point in run slot s
+  unsigned char* a2 = arr ? arr + (size_t)A.cap * 8 : smem + L.r2;
+  uint32_t* run_pos = (uint32_t*)a2;                               // cap: its sorted position
+  uint16_t* cellv = (uint16_t*)(run_pos + A.cap);                  // cap: cell of in-box point t (0xFFFF = none)
+  uint16_t* ord = cellv;                                           //      later: run slots, each run in (d2, id) order
+  uint16_t* run_cell = cellv + A.cap;                              // cap: cell of run slot s
+  uint2* img = (uint2*)(smem + L.r1);                              // IP x IP cells, after the runs are ordered
+  uint8_t* outb = smem + L.r2;                                     // 10800 output bytes, after the cell sums
   // per image cell: count, then (first run slot | slots still to hand out << 16); [3600] = end sentinel
   __shared__ uint32_t cellc[IS * IS + 1];
   __shared__ uint32_t warp_tot[kRenderThreads / 32];
@@ -83,6 +113,7 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     br = A.box_ref[slot];
   }
   const uint32_t m = br.count;
+  if (m < A.m_lo || m > A.m_hi) continue;  // another launch's size class
   float q[3] = {0.f, 0.f, 0.f};
   if (!EXPLICIT) {
     const ag2_frame& fr = A.frames[hyp.sample_id];
@@ -93,7 +124,6 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     }
   }
   if (tid == 0) miny_s = dord(INFINITY);
-  for (int i = tid; i < IS * IS * 3; i += kRenderThreads) img[i] = 0.f;
   for (int i = tid; i <= IS * IS; i += kRenderThreads) cellc[i] = 0;
   __syncthreads();
   // hand-frame constants of this hypothesis (same values the hand kernel used)
@@ -194,7 +224,7 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     }
     run_cell[s] = (uint16_t)cell;
   }
-  __syncthreads();
+  __syncthreads();  // cellv is dead from here on: its memory becomes `ord`
   // The reference's per-cell double sums run in radiusSearch order (ascending (d2, id)); only the
   // order INSIDE a cell matters, so each run is ordered by counting smaller keys (runs are short).
   const uint32_t binned = cellc[IS * IS];
@@ -204,20 +234,24 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     const uint64_t key = run_key[s];
     uint32_t r = 0;
     for (uint32_t u = a; u < b; u++) r += run_key[u] < key;
-    ord_pos[a + r] = run_pos[s];
+    ord[a + r] = (uint16_t)s;
   }
+  __syncthreads();  // run_key is dead from here on: its memory (or region 1) becomes the image
+  for (int i = tid; i < (int)(kImgBytes / 16); i += kRenderThreads) ((uint4*)img)[i] = make_uint4(0, 0, 0, 0);
   __syncthreads();
-  // one thread per occupied cell sums its run in that order (learning.cpp:166-192)
+  // one thread per occupied cell sums its run in that order (learning.cpp:166-192); the cell value
+  // goes through the tail's x255 rounding here (monotone, so it commutes with the 3x3 max)
   for (uint32_t cell = tid; cell < (uint32_t)(IS * IS); cell += kRenderThreads) {
     const uint32_t a = cellc[cell] & 0xFFFFu, b = cellc[cell + 1] & 0xFFFFu;
     if (a == b) continue;
     double ax = 0.0, ay = 0.0, az = 0.0;
     for (uint32_t u = a; u < b; u++) {
+      const uint32_t pos = run_pos[ord[u]];
       if (EXPLICIT) {
-        const double* nv = A.xnrm + 3 * (size_t)ord_pos[u];
+        const double* nv = A.xnrm + 3 * (size_t)pos;
         ax += nv[0], ay += nv[1], az += nv[2];
       } else {
-        float4 nv = A.g.nrm[ord_pos[u]];
+        float4 nv = A.g.nrm[pos];
         double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
         // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
         ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
@@ -227,32 +261,36 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     }
     double s = 1.0 / sqrt(ax * ax + (ay * ay + az * az));
     int row = (int)cell / IS, col = (int)cell % IS;
-    float* px = &img[((IS - 1 - row) * IS + col) * 3];
-    px[0] = (float)fabs(s * ax);
-    px[1] = (float)fabs(s * ay);
-    px[2] = (float)fabs(s * az);
+    // BGR2RGB: output channel k holds source channel 2 - k
+    img[(IS - 1 - row + 1) * IP + col + 1] = make_uint2(to_u8(s * az) | (to_u8(s * ay) << 16), to_u8(s * ax));
+  }
+  __syncthreads();  // run_pos / ord / run_cell are dead from here on: region 2 becomes the output bytes
+  // dilate 3x3 (in-bounds max; values are >= 0, so the zero border is neutral) -> u8 HWC
+  for (int pix = tid; pix < IS * IS; pix += kRenderThreads) {
+    const int r = pix / IS, c = pix % IS;
+    const uint2* p0 = img + r * IP + c;
+    uint2 m0, m1, m2;
+    {
+      const uint2 a = p0[0], b = p0[1], d = p0[2];
+      m0 = make_uint2(__vimax3_u16x2(a.x, b.x, d.x), __vimax3_u16x2(a.y, b.y, d.y));
+    }
+    {
+      const uint2 a = p0[IP], b = p0[IP + 1], d = p0[IP + 2];
+      m1 = make_uint2(__vimax3_u16x2(a.x, b.x, d.x), __vimax3_u16x2(a.y, b.y, d.y));
+    }
+    {
+      const uint2 a = p0[2 * IP], b = p0[2 * IP + 1], d = p0[2 * IP + 2];
+      m2 = make_uint2(__vimax3_u16x2(a.x, b.x, d.x), __vimax3_u16x2(a.y, b.y, d.y));
+    }
+    const uint32_t w0 = __vimax3_u16x2(m0.x, m1.x, m2.x), w1 = __vimax3_u16x2(m0.y, m1.y, m2.y);
+    outb[3 * pix] = (uint8_t)(w0 & 0xFFu);
+    outb[3 * pix + 1] = (uint8_t)(w0 >> 16);
+    outb[3 * pix + 2] = (uint8_t)(w1 & 0xFFu);
   }
   __syncthreads();
-  // dilate 3x3 (in-bounds max) -> BGR2RGB -> saturate_cast<uchar>(v * 255) round-half-even
-  uint8_t* out = A.out + (size_t)image * AG2_IMAGE_BYTES;
-  for (int i = tid; i < IS * IS * 3; i += kRenderThreads) {
-    int ch = i % 3, c = (i / 3) % IS, r = i / (3 * IS);
-    int src_ch = 2 - ch;
-    float mx = -INFINITY;
-    for (int dr = -1; dr <= 1; dr++) {
-      int rr = r + dr;
-      if (rr < 0 || rr >= IS) continue;
-      for (int dc = -1; dc <= 1; dc++) {
-        int cc = c + dc;
-        if (cc < 0 || cc >= IS) continue;
-        mx = fmaxf(mx, img[(rr * IS + cc) * 3 + src_ch]);
-      }
-    }
-    float v = __fmul_rn(mx, 255.0f);
-    int iv = __float2int_rn(v);
-    out[i] = (uint8_t)min(max(iv, 0), 255);
-  }
-  __syncthreads();  // img, FR and the sort arrays are reused by the next image of this CTA
+  uint4* out = (uint4*)(A.out + (size_t)image * AG2_IMAGE_BYTES);  // 10800 = 675 x 16, base 256-byte aligned
+  for (int i = tid; i < (int)(kOutBytes / 16); i += kRenderThreads) out[i] = ((const uint4*)outb)[i];
+  __syncthreads();  // every region is reused by the next image of this CTA
   }
 }
 
@@ -265,29 +303,36 @@ static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) 
     c->err = "render: more than 65535 points in a closing region";
     return AG2_E_CAPACITY;
   }
-  const uint32_t cap = (std::max<uint32_t>((uint32_t)max_points, 8u) + 7u) & ~7u;
-  const size_t img_bytes = (size_t)IS * IS * 3 * sizeof(float);
-  size_t smem = (size_t)cap * 20 + img_bytes;
-  // closing regions of more than ~8000 points (fused multi-view clouds, c4) do not fit beside the
-  // image: the sort arrays then live in global memory (L2 resident) and a fixed set of CTAs
-  // walks the images
-  // test hook: AG2_RENDER_SPILL=1 forces the global-memory path on small scenes
+  static_assert(kOutBytes % 16 == 0 && kImgBytes % 16 == 0, "vector copies");
+  const uint32_t cap_max = (std::max<uint32_t>((uint32_t)max_points, 8u) + 7u) & ~7u;
+  // test hooks: AG2_RENDER_SPILL=1 forces the global-memory path, AG2_RENDER_SMALL_CAP=<n> the boundary
+  // between the two size classes (small scenes then exercise both launches)
   const bool force_spill = getenv("AG2_RENDER_SPILL") && atoi(getenv("AG2_RENDER_SPILL")) != 0;
-  const bool spill = force_spill || smem > 200 * 1024;
-  unsigned grid = (unsigned)n;
-  if (spill) {
-    smem = img_bytes;
-    grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * 4);
-    AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 20));
-  }
-  AG2_CUDA(c, cudaFuncSetAttribute(k_render<EXPLICIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  uint32_t small_cap = kSmallCap;
+  if (const char* e = getenv("AG2_RENDER_SMALL_CAP")) small_cap = (std::max(atoi(e), 8) + 7) & ~7;
   A.g = grid_dev(c);
-  A.cap = cap;
   A.n = (uint32_t)n;
-  A.scratch = spill ? c->render_scratch.p : nullptr;
-  k_render<EXPLICIT><<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
-  AG2_LAUNCH_CHECK(c);
-  return AG2_OK;
+  auto launch = [&](uint32_t cap, uint32_t m_lo, uint32_t m_hi, bool one_cta_per_image) -> int {
+    // Closing regions of more than ~12 000 points (fused multi-view clouds, c4) do not fit shared
+    // memory: the sort arrays then live in global memory (L2 resident).
+    const bool spill = force_spill || render_smem(cap, false).total > 180 * 1024;
+    const size_t smem = render_smem(cap, spill).total;
+    unsigned grid = (unsigned)n;
+    if (spill || !one_cta_per_image) grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * (spill ? 4 : 2));
+    if (spill) AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 16));
+    AG2_CUDA(c, cudaFuncSetAttribute(k_render<EXPLICIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    A.cap = cap, A.m_lo = m_lo, A.m_hi = m_hi;
+    A.scratch = spill ? c->render_scratch.p : nullptr;
+    k_render<EXPLICIT><<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
+    AG2_LAUNCH_CHECK(c);
+    return AG2_OK;
+  };
+  // Shared memory per CTA is sized by the LARGEST image of a launch, so one dense closing region
+  // would cost every image its occupancy: images up to kSmallCap points go first (one CTA each,
+  // three CTAs per SM), the larger ones in a second launch whose CTAs walk the list and skip the rest.
+  if (cap_max <= small_cap) return launch(cap_max, 0u, 0xFFFFFFFFu, true);
+  AG2_TRY(launch(small_cap, 0u, small_cap, true));
+  return launch(cap_max, small_cap + 1u, 0xFFFFFFFFu, false);
 }
 
 // Renders the hypotheses in slots d_list[0..n) into d_out (n * 10800 bytes).

@@ -266,10 +266,13 @@ def test_single_launch_and_multi_kernel_lists_agree(tiny_scene, monkeypatch, mod
     assert out[0] == out[1]
 
 
-def test_render_spill_path(tiny_scene, monkeypatch):
+@pytest.mark.parametrize("hook", [("AG2_RENDER_SPILL", "1"), ("AG2_RENDER_SMALL_CAP", "200"),
+                                  ("AG2_RENDER_SMALL_CAP", "8")])
+def test_render_spill_and_size_class_paths(tiny_scene, monkeypatch, hook):
     """Closing regions too large for shared memory (c4 densities) sort in global memory with a fixed
-    set of CTAs walking the images; forced here on the tiny scene: image bytes equal the oracle's."""
-    monkeypatch.setenv("AG2_RENDER_SPILL", "1")
+    set of CTAs walking the images; images above a size boundary go to a second launch with a larger
+    capacity. Both forced here on the tiny scene: image bytes equal the oracle's."""
+    monkeypatch.setenv(*hook)
     p = make_params(capi.MODE_PREDICTION, min_score_diff=0.0)
     g, o = both(p, tiny_scene, weights=ob.xavier_weights(2))
     for c in (g, o):
