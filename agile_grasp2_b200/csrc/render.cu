@@ -24,12 +24,12 @@
 namespace ag2 {
 namespace {
 
-constexpr int kRenderThreads = 256;
+constexpr int kRenderThreads = 512;  // measured against 256 and 1024 on c2 / c3
 constexpr int IS = AG2_IMAGE_SIZE;
 constexpr int IP = IS + 2;                       // image with a one-cell zero border (dilate needs no bounds tests)
 constexpr size_t kImgBytes = (size_t)IP * IP * 8;   // per cell: u16x2 (out ch 0, out ch 1) | u16x2 (out ch 2, 0)
 constexpr size_t kOutBytes = (size_t)AG2_IMAGE_BYTES;
-constexpr uint32_t kSmallCap = 3072;             // size class 1: three CTAs per SM
+constexpr uint32_t kSmallCap = 4096;             // size class 1: two CTAs per SM
 
 struct RenderArgs {
   GridDev g;
@@ -176,7 +176,7 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     if (cell != 0xFFFFu) atomicAdd(&cellc[cell], 1u);
   }
   __syncthreads();
-  // exclusive prefix over the cells: 15 consecutive cells per thread, block scan of the partial sums
+  // exclusive prefix over the cells: kPer consecutive cells per thread, block scan of the partial sums
   {
     constexpr int kPer = (IS * IS + kRenderThreads - 1) / kRenderThreads;
     uint32_t loc[kPer], sum = 0;
@@ -313,6 +313,7 @@ static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) 
   A.g = grid_dev(c);
   A.n = (uint32_t)n;
   auto launch = [&](uint32_t cap, uint32_t m_lo, uint32_t m_hi, bool one_cta_per_image) -> int {
+    auto kernel = k_render<EXPLICIT>;
     // Closing regions of more than ~12 000 points (fused multi-view clouds, c4) do not fit shared
     // memory: the sort arrays then live in global memory (L2 resident).
     const bool spill = force_spill || render_smem(cap, false).total > 180 * 1024;
@@ -320,16 +321,17 @@ static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) 
     unsigned grid = (unsigned)n;
     if (spill || !one_cta_per_image) grid = (unsigned)std::min<size_t>(n, (size_t)c->sm_count * (spill ? 4 : 2));
     if (spill) AG2_CUDA(c, c->render_scratch.reserve((size_t)grid * cap * 16));
-    AG2_CUDA(c, cudaFuncSetAttribute(k_render<EXPLICIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    AG2_CUDA(c, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     A.cap = cap, A.m_lo = m_lo, A.m_hi = m_hi;
     A.scratch = spill ? c->render_scratch.p : nullptr;
-    k_render<EXPLICIT><<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
+    kernel<<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
     AG2_LAUNCH_CHECK(c);
     return AG2_OK;
   };
   // Shared memory per CTA is sized by the LARGEST image of a launch, so one dense closing region
   // would cost every image its occupancy: images up to kSmallCap points go first (one CTA each,
-  // three CTAs per SM), the larger ones in a second launch whose CTAs walk the list and skip the rest.
+  // two CTAs = 32 warps per SM), the larger ones in a second launch whose CTAs walk the list and skip
+  // the rest.  Boundary measured on c3: 2048 -> 1.41 ms, 3072 -> 1.28, 4096 -> 1.06, 5400 -> 1.07.
   if (cap_max <= small_cap) return launch(cap_max, 0u, 0xFFFFFFFFu, true);
   AG2_TRY(launch(small_cap, 0u, small_cap, true));
   return launch(cap_max, small_cap + 1u, 0xFFFFFFFFu, false);
