@@ -224,25 +224,67 @@ __device__ __forceinline__ uint32_t block_flag_scan(bool f, uint32_t* warp_sums 
   return r;
 }
 
-// hypotheses list (emitted slots) and pruned list (emitted slots that pass S13) in slot order
+// hypotheses list (emitted slots) and pruned list (emitted slots that pass S13) in slot order.
+// Thread t flags slots t, t + 1024, ... (coalesced), keeps its flags as bit masks, and ONE scan over
+// the (tile, warp) ballot counts places every slot of every tile.
+constexpr int kListTiles = (int)(kFusedMaxSlots / kFT);  // <= 64: one bit per tile in a 64-bit mask
 __global__ void __launch_bounds__(kFT)
 k_lists_after_hands(const ag2_sweep_record* __restrict__ sw, const ag2_hypothesis* __restrict__ slots, uint32_t n,
                     PruneArgs a, uint32_t* __restrict__ hyp_out, uint32_t* __restrict__ pruned_out,
                     uint32_t* __restrict__ counts /* [2] */) {
-  __shared__ uint32_t ws[33];
-  uint32_t base_h = 0, base_p = 0;
-  for (uint32_t t0 = 0; t0 < n; t0 += kFT) {
-    const uint32_t i = t0 + threadIdx.x;
+  __shared__ uint32_t wc_e[kListTiles * 32], wc_k[kListTiles * 32];  // per (tile, warp): emitted / kept
+  __shared__ uint32_t wt_e[33], wt_k[33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t tiles = (n + kFT - 1) / kFT;
+  unsigned long long em_bits = 0, keep_bits = 0;
+  for (uint32_t k = 0; k < tiles; k++) {
+    const uint32_t i = k * kFT + threadIdx.x;
     const bool em = i < n && sw[i].emitted;
     const bool keep = em && prune_keep(slots[i], a);
-    uint32_t th, tp;
-    const uint32_t rh = block_flag_scan(em, ws, th);
-    const uint32_t rp = block_flag_scan(keep, ws, tp);
-    if (em) hyp_out[base_h + rh] = i;
-    if (keep) pruned_out[base_p + rp] = i;
-    base_h += th, base_p += tp;
+    em_bits |= (unsigned long long)em << k;
+    keep_bits |= (unsigned long long)keep << k;
+    const uint32_t be = __ballot_sync(AG2_FULL, em), bk = __ballot_sync(AG2_FULL, keep);
+    if (lane == 0) wc_e[k * 32 + warp] = __popc(be), wc_k[k * 32 + warp] = __popc(bk);
   }
-  if (threadIdx.x == 0) counts[0] = base_h, counts[1] = base_p;
+  __syncthreads();
+  // exclusive scan of the tiles * 32 counts: two consecutive entries per thread
+  {
+    const uint32_t m = tiles * 32, t0 = 2 * threadIdx.x;
+    const uint32_t e0 = t0 < m ? wc_e[t0] : 0u, e1 = t0 + 1 < m ? wc_e[t0 + 1] : 0u;
+    const uint32_t k0 = t0 < m ? wc_k[t0] : 0u, k1 = t0 + 1 < m ? wc_k[t0 + 1] : 0u;
+    uint32_t ie = e0 + e1, ik = k0 + k1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t te = __shfl_up_sync(AG2_FULL, ie, o), tk = __shfl_up_sync(AG2_FULL, ik, o);
+      if (lane >= o) ie += te, ik += tk;
+    }
+    if (lane == 31) wt_e[warp] = ie, wt_k[warp] = ik;
+    __syncthreads();
+    if (warp == 0) {
+      const uint32_t ve = wt_e[lane], vk = wt_k[lane];
+      uint32_t se = ve, sk = vk;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t te = __shfl_up_sync(AG2_FULL, se, o), tk = __shfl_up_sync(AG2_FULL, sk, o);
+        if (lane >= o) se += te, sk += tk;
+      }
+      wt_e[lane] = se - ve, wt_k[lane] = sk - vk;
+      if (lane == 31) wt_e[32] = se, wt_k[32] = sk;
+    }
+    __syncthreads();
+    const uint32_t xe = wt_e[warp] + ie - (e0 + e1), xk = wt_k[warp] + ik - (k0 + k1);
+    if (t0 < m) wc_e[t0] = xe, wc_k[t0] = xk;
+    if (t0 + 1 < m) wc_e[t0 + 1] = xe + e0, wc_k[t0 + 1] = xk + k0;
+  }
+  __syncthreads();
+  for (uint32_t k = 0; k < tiles; k++) {
+    const bool em = (em_bits >> k) & 1ull, keep = (keep_bits >> k) & 1ull;
+    const uint32_t be = __ballot_sync(AG2_FULL, em), bk = __ballot_sync(AG2_FULL, keep);
+    const uint32_t lt = (1u << lane) - 1u, i = k * kFT + threadIdx.x;
+    if (em) hyp_out[wc_e[k * 32 + warp] + __popc(be & lt)] = i;
+    if (keep) pruned_out[wc_k[k * 32 + warp] + __popc(bk & lt)] = i;
+  }
+  if (threadIdx.x == 0) counts[0] = wt_e[32], counts[1] = wt_k[32];
 }
 
 // mode filter over the pruned list -> antipodal list, then its top-k by (score desc, position asc)

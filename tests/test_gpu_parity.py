@@ -248,7 +248,7 @@ def test_chunked_hand_staging_and_levelled_normals(tiny_scene, monkeypatch):
 def test_single_launch_and_multi_kernel_lists_agree(tiny_scene, monkeypatch, mode):
     """Small runs build the hypothesis + pruned lists in one single-CTA launch and filter + rank + take the
     selection in another; large ones use flag / scan / compact kernels and tile sorts. Same lists either way."""
-    sc = tiny_scene
+    sc = scenes.make_scene("tiny", num_samples=700)  # 5 600 slots: six tiles of the single-launch scan
     p = make_params(mode, min_score_diff=0.0, num_selected=7)
     out = []
     for forced in ("0", "1"):
