@@ -249,6 +249,19 @@ def pcd_write(path: str, xyz, normals=None, rgba=None, binary=True):
         raise Ag2Error(rc, "ag2_pcd_write", path)
 
 
+def merge_selected_blocks(blocks: np.ndarray, num_selected: int) -> np.ndarray:
+    """ag2_merge_selected: blocks [world, cap] records of an all-gather -> the single-GPU selection."""
+    blocks = np.ascontiguousarray(blocks, dtype=HYPOTHESIS_DTYPE)
+    world, cap = blocks.shape
+    out = np.zeros(world * cap, dtype=HYPOTHESIS_DTYPE)
+    n = C.c_size_t()
+    rc = load().fn("merge_selected")(blocks.ctypes.data_as(C.c_void_p), C.c_int(world), C.c_size_t(cap),
+                                     C.c_int(int(num_selected)), out.ctypes.data_as(C.c_void_p), C.byref(n))
+    if rc:
+        raise Ag2Error(rc, "merge_selected")
+    return out[: int(n.value)]
+
+
 def serialize_grasp_list(hands: np.ndarray, seq=0, sec=0, nsec=0, frame_id="") -> bytes:
     hands = np.ascontiguousarray(hands, dtype=HYPOTHESIS_DTYPE)
     ln = C.c_size_t()

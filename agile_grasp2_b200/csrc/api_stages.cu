@@ -310,4 +310,35 @@ int ag2_classify_images(ag2_ctx* c, const uint8_t* images, size_t n, float* logi
   return AG2_OK;
 }
 
+int ag2_merge_selected(const ag2_hypothesis* blocks, int world, size_t cap, int num_selected, ag2_hypothesis* out,
+                       size_t* n_out) {
+  if (!blocks || !out || !n_out || world < 1) return AG2_E_INVALID;
+  std::vector<ag2_hypothesis> all;
+  all.reserve((size_t)world * cap);
+  for (int r = 0; r < world; r++)
+    for (size_t i = 0; i < cap; i++) {
+      const ag2_hypothesis& h = blocks[(size_t)r * cap + i];
+      if (h.approach[0] == 0.0 && h.approach[1] == 0.0 && h.approach[2] == 0.0) continue;  // padding
+      all.push_back(h);
+      all.back().sample_id = r + world * h.sample_id;
+    }
+  std::stable_sort(all.begin(), all.end(), [](const ag2_hypothesis& a, const ag2_hypothesis& b) {
+    return a.sample_id != b.sample_id ? a.sample_id < b.sample_id : a.orientation_id < b.orientation_id;
+  });
+  // the device ranking's key (select.cu score_key): order-preserving code of the double, descending
+  auto code = [](double v) {
+    long long o;
+    memcpy(&o, &v, 8);
+    return o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
+  };
+  std::stable_sort(all.begin(), all.end(), [&](const ag2_hypothesis& a, const ag2_hypothesis& b) {
+    return code(a.score) > code(b.score);
+  });
+  size_t n = all.size();
+  if (num_selected > 0 && (size_t)num_selected < n) n = (size_t)num_selected;
+  std::copy(all.begin(), all.begin() + n, out);
+  *n_out = n;
+  return AG2_OK;
+}
+
 }  // extern "C"

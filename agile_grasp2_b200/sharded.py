@@ -273,9 +273,10 @@ class ShardedDetector:
             self._tx = torch.empty(cap * rec, dtype=torch.uint8, device=self.device)
             self._rxg = torch.empty(self.world * cap * rec, dtype=torch.uint8, device=self.device)
             self._tx_cap = cap
+        n_sel = 0
         if n_mine:
             self.ctx.detect()
-            self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
+            n_sel = self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
         else:
             self._tx.zero_()
             torch.cuda.current_stream().synchronize()
@@ -290,13 +291,9 @@ class ShardedDetector:
         # detect (includes waiting for nothing but this rank's GPU), result exchange
         self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
                         "gather": (t3 - t2) * 1e3}
-        parts = []
-        for r in range(self.world):
-            blk = allr[r]
-            blk = blk[np.any(blk["approach"] != 0.0, axis=1)].copy()  # zero-filled tail = no record
-            blk["sample_id"] = r + self.world * blk["sample_id"]
-            parts.append(blk)
-        return merge_selected(parts, p.num_selected)
+        if self.world == 1:  # one rank: the device ranking already is the final order
+            return allr[0][:n_sel].copy()
+        return capi.merge_selected_blocks(allr, p.num_selected)  # native: the same rule as merge_selected
 
     def detect_host(self, xyz_h, cam_h, num_cams, samples_h, shape_hint=None):
         """Host buffers (pinned torch CPU tensors on rank 0): H2D inside the call."""

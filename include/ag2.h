@@ -366,6 +366,14 @@ int ag2_pcd_write(const char* path, const float* xyz, const float* normals_or_nu
 int ag2_serialize_grasp_list(const ag2_hypothesis* hands, size_t n, uint32_t seq, uint32_t stamp_sec,
                              uint32_t stamp_nsec, const char* frame_id, uint8_t* out, size_t cap, size_t* len);
 
+/* Multi-GPU host: merges the per-rank SELECTED blocks of an all-gather (`world` blocks of `cap` records,
+ * block r from the rank that evaluated samples r, r + world, ...; records with an all-zero approach
+ * vector are padding) into the single-GPU selection: sample_id -> r + world * sample_id, list order
+ * (sample, orientation), then the top num_selected by score with ties in list order
+ * (grasp_detector.cpp:238-252; num_selected <= 0 keeps all).  Host-only, needs no ctx.  out: world * cap records. */
+int ag2_merge_selected(const ag2_hypothesis* blocks, int world, size_t cap, int num_selected, ag2_hypothesis* out,
+                       size_t* n_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,3 +67,27 @@ def test_no_cpu_fallback():
     with pytest.raises(capi.Ag2Error) as e:
         capi.Context(capi.default_params())
     assert e.value.code == capi.AG2_E_NO_DEVICE
+
+
+def test_native_merge_of_per_rank_selections_equals_the_python_rule():
+    """ag2_merge_selected (host-only C) against sharded.merge_selected on random per-rank blocks with
+    padding, score ties and sample ids that interleave across ranks."""
+    from agile_grasp2_b200 import sharded
+    rng = np.random.default_rng(5)
+    for world, cap, k in ((1, 8, 5), (2, 50, 50), (3, 16, 7), (8, 50, 50), (4, 6, 0)):
+        blocks = np.zeros((world, cap), capi.HYPOTHESIS_DTYPE)
+        parts = []
+        for r in range(world):
+            n = int(rng.integers(0, cap + 1))
+            b = blocks[r, :n]
+            b["approach"] = rng.normal(size=(n, 3)) + 3.0
+            b["score"] = rng.integers(-3, 4, size=n).astype(np.float64) * 0.5  # many ties
+            b["sample_id"] = np.sort(rng.integers(0, 40, size=n))
+            b["orientation_id"] = rng.integers(0, 8, size=n)
+            b["width"] = rng.random(n)
+            loc = b.copy()
+            loc["sample_id"] = r + world * loc["sample_id"]
+            parts.append(loc)
+        want = sharded.merge_selected(parts, k)
+        got = capi.merge_selected_blocks(blocks, k)
+        assert got.tobytes() == want.tobytes(), (world, cap, k)
