@@ -273,26 +273,27 @@ class ShardedDetector:
             self._tx = torch.empty(cap * rec, dtype=torch.uint8, device=self.device)
             self._rxg = torch.empty(self.world * cap * rec, dtype=torch.uint8, device=self.device)
             self._tx_cap = cap
-        n_sel = 0
+        if self.world == 1:  # one rank: the device ranking already is the final order, read it directly
+            self.ctx.detect()
+            out = self.ctx.hypotheses(capi.LIST_SELECTED)
+            t2 = time.perf_counter()
+            self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
+                            "gather": 0.0}
+            return out
         if n_mine:
             self.ctx.detect()
-            n_sel = self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
+            self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
         else:
             self._tx.zero_()
             torch.cuda.current_stream().synchronize()
         t2 = time.perf_counter()
-        if self.world > 1:
-            dist.all_gather_into_tensor(self._rxg, self._tx, group=self.group)
-            allr = self._rxg.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(self.world, cap)
-        else:
-            allr = self._tx.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(1, cap)
+        dist.all_gather_into_tensor(self._rxg, self._tx, group=self.group)
+        allr = self._rxg.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(self.world, cap)
         t3 = time.perf_counter()
         # host-side wall time of the three segments of the last call (ms): input exchange, local
         # detect (includes waiting for nothing but this rank's GPU), result exchange
         self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
                         "gather": (t3 - t2) * 1e3}
-        if self.world == 1:  # one rank: the device ranking already is the final order
-            return allr[0][:n_sel].copy()
         return capi.merge_selected_blocks(allr, p.num_selected)  # native: the same rule as merge_selected
 
     def detect_host(self, xyz_h, cam_h, num_cams, samples_h, shape_hint=None):
