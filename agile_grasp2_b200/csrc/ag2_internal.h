@@ -148,6 +148,10 @@ struct ag2_ctx {
   bool pruned_precomputed = false, selected_precomputed = false;  // small lists: built eagerly in one launch
   size_t pruned_count = 0, selected_count = 0;
   ag2::DevBuf<uint32_t> big_list[2];    // points whose neighbourhood exceeds a launch capacity (ping-pong)
+  ag2::DevBuf<uint32_t> tier_list;      // normals: points grouped by neighbourhood-size tier, [tier][owned points]
+  ag2::DevBuf<uint32_t> tier_cnt;       // normals: per-tier counts + per-launch batch counters
+  cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};  // independent normals launches run side by side
+  cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
   ag2::DevBuf<uint32_t> scalars;        // small device scratch (counters, maxima, flags)
 
   // samples

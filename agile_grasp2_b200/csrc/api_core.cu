@@ -185,6 +185,14 @@ int ag2_create(const ag2_params* p, int device, ag2_ctx** out) {
     return AG2_E_CUDA;
   }
   for (int i = 0; i < 18; i++) cudaEventCreate(&c->ev[i]);
+  cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
+  for (int i = 0; i < 4; i++) {
+    if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) {
+      ag2_destroy(c);
+      return AG2_E_CUDA;
+    }
+    cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
+  }
   if (c->scalars.reserve(64) != cudaSuccess || build_hand_const(c) != AG2_OK) {
     ag2_destroy(c);
     return AG2_E_INVALID;
@@ -201,6 +209,14 @@ int ag2_destroy(ag2_ctx* c) {
     cudaStreamDestroy(c->stream);
   }
   for (int i = 0; i < 18; i++) cudaEventDestroy(c->ev[i]);
+  for (int i = 0; i < 4; i++) {
+    if (c->aux[i]) {
+      cudaStreamSynchronize(c->aux[i]);
+      cudaStreamDestroy(c->aux[i]);
+    }
+    if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
+  }
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   delete c;
   return AG2_OK;
 }

@@ -432,12 +432,270 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   }
 }
 
+// ---------------------------------------------------------------------------
+// Tiered path.  The count pass groups the points by neighbourhood size into tiers; every
+// non-empty tier is ONE launch sized for exactly that capacity, and the launches are
+// independent, so they run side by side on the ctx's auxiliary streams.
+//   the sparsest tiers (by default 0..3, <= 96 neighbours; any of 0..7 can): k_normals_quad,
+//               four lanes per point;
+//   the others: k_normals, one warp per point.
+constexpr int kQuadTiers = 8;
+constexpr int kAllTiers = 13;
+constexpr uint32_t kTierCapHost[kAllTiers] = {48, 64, 80, 96, 112, 128, 160, 208, 256, 384, 512, 1024, 0xffffffffu};
+__constant__ uint32_t c_tier_cap[kAllTiers] = {48, 64, 80, 96, 112, 128, 160, 208, 256, 384, 512, 1024, 0xffffffffu};
+
+// thread per point: neighbour count, NaN normal below three neighbours, tier membership lists
+// (one warp-aggregated atomic per tier present in the warp, so consecutive cell-sorted points stay
+// consecutive in their list and keep their cache locality).
+__global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float rq, uint32_t* __restrict__ kn,
+                                                     uint32_t* __restrict__ max_out,
+                                                     unsigned long long* __restrict__ sum_out,
+                                                     uint32_t* __restrict__ tier_count, uint32_t* __restrict__ tier_list,
+                                                     uint32_t stride, float4* __restrict__ nrm_out,
+                                                     uint32_t shard_rank, uint32_t shard_world) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31;
+  const bool owned = i < (uint32_t)g.n && (i >> 5) % shard_world == shard_rank;
+  uint32_t cnt = 0;
+  if (owned) {
+    const float4 q = g.pts[i];
+    const QueryWindow w = make_window(g, q.x, q.y, q.z, rq);
+    const int rows = w.rows();
+    for (int row = 0; row < rows; row++) {
+      uint32_t b, e;
+      row_span_trim(g, w, row, q.x, q.y, q.z, r2 * 1.002f, b, e);
+      for (uint32_t j = b; j < e; j++) {
+        const float4 p = g.pts[j];
+        cnt += (dist2_f(q.x - p.x, q.y - p.y, q.z - p.z) < r2);
+      }
+    }
+    kn[i] = cnt;
+    if (cnt < 3) {  // computePointNormal: fewer than 3 neighbours -> NaN
+      const float nanv = __int_as_float(0x7fc00000);
+      nrm_out[i] = make_float4(nanv, nanv, nanv, nrm_out[i].w);
+    }
+  }
+  uint32_t m = cnt;
+  unsigned long long s = cnt;
+  for (int o = 16; o > 0; o >>= 1) {
+    m = max(m, __shfl_xor_sync(AG2_FULL, m, o));
+    s += __shfl_xor_sync(AG2_FULL, s, o);
+  }
+  if (lane == 0) {
+    atomicMax(max_out, m);
+    atomicAdd(sum_out, s);
+  }
+  int tier = -1;
+  if (owned && cnt >= 3) {
+    tier = 0;
+    while (cnt > c_tier_cap[tier]) tier++;
+  }
+  const uint32_t peers = __match_any_sync(AG2_FULL, tier);
+  if (tier >= 0) {
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(&tier_count[tier], (uint32_t)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    tier_list[(size_t)tier * stride + base + __popc(peers & ((1u << lane) - 1u))] = i;
+  }
+}
+
+// k_normals_quad: FOUR lanes per point, eight points per warp.  The four lanes share one
+// shared-memory neighbour list; nothing crosses a group, so all synchronisation is on the
+// group's own four-lane mask and groups of a warp drift apart freely.
+//   gather   the group walks the point's cell rows four candidates at a time (float d2, strict <);
+//            hits are compacted with a group ballot and appended as 32-bit keys (q << jbits) | j,
+//            j = cell-sorted position (jbits = bits of n), q = a monotone quantisation of d2 on
+//            the remaining bits;
+//   order    counting sort on the top five key bits into a byte permutation (shared atomics);
+//            each lane then owns eight consecutive buckets = one contiguous segment and insertion-
+//            sorts it.  Keys with different q are ordered by q; EQUAL q falls back to the exact
+//            (d2, input index) comparison, recomputing d2 with the gather's own float sequence --
+//            so the result is exactly FLANN's radiusSearch order;
+//   moments  lanes 0..2 of the group run three of the nine sequential float accumulators each;
+//            lane 0 then solves eigen33 and flips the normal.
+// Lists are laid out [entry][group] per warp, so the four consecutive entries a group touches
+// fall into distinct banks whatever the other groups do.  Shared memory is 5 B x cap + 128 B per
+// point (a quarter of that per thread), which is what gives this kernel its occupancy.
+constexpr int kQuadThreads = 128;
+
+struct QuadArgs {
+  GridDev g;
+  float r2, rq, qscale;
+  uint32_t qmax, jbits;
+  const uint32_t* kn;
+  const uint32_t* list;
+  uint32_t n_items, cap;
+  float4* nrm_out;
+};
+
+__host__ __device__ inline size_t quad_smem_per_warp(uint32_t cap) { return (size_t)cap * 40 + 1024; }
+
+__global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const GridDev& g = P.g;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, sub = lane & 3;
+  const uint32_t gshift = grp * 4, gmask = 0xFu << gshift;
+  const uint32_t cap = P.cap;
+  unsigned char* base = smem + (size_t)warp * quad_smem_per_warp(cap);
+  uint32_t* L = (uint32_t*)base + grp;                      // L[t * 8]
+  uint8_t* ord = base + (size_t)cap * 32 + grp;             // ord[t * 8]
+  uint32_t* cur = (uint32_t*)(base + (size_t)cap * 40) + grp;  // cur[b * 8], 32 buckets
+  const uint32_t item = (blockIdx.x * kQuadThreads + threadIdx.x) >> 2;
+  if (item >= P.n_items) return;  // whole groups leave together
+  const uint32_t i = P.list[item];
+  const uint32_t count = P.kn[i];  // 3 <= count <= cap: the tier list holds nothing else
+  const float4 q = g.pts[i];
+  const uint32_t jbits = P.jbits, jmask = (1u << jbits) - 1u;
+  const float r2 = P.r2;
+  // ---- gather
+  uint32_t n = 0;
+  {
+    const QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
+    const int rows = w.rows();
+    for (int row = 0; row < rows; row++) {
+      uint32_t b, e;
+      row_span_trim(g, w, row, q.x, q.y, q.z, r2 * 1.002f, b, e);
+      for (uint32_t j0 = b; j0 < e; j0 += 4) {
+        const uint32_t j = j0 + sub;
+        bool hit = false;
+        float d2 = 0.f;
+        if (j < e) {
+          const float4 p = g.pts[j];
+          d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
+          hit = d2 < r2;
+        }
+        const uint32_t bits = (__ballot_sync(gmask, hit) >> gshift) & 0xFu;
+        if (hit) {
+          const uint32_t qv = min(P.qmax, (uint32_t)__fmul_rn(d2, P.qscale));  // monotone in d2
+          const uint32_t pos = n + __popc(bits & ((1u << sub) - 1u));
+          if (pos < cap) L[pos * 8] = (qv << jbits) | j;
+        }
+        n += __popc(bits);
+      }
+    }
+    n = min(n, cap);  // == count by construction (same walk, same predicate as the count pass)
+  }
+  // ---- counting sort on the top five bits -> byte permutation grouped by bucket
+#pragma unroll
+  for (int k = 0; k < 8; k++) cur[(sub * 8 + k) * 8] = 0;
+  __syncwarp(gmask);
+  for (uint32_t t = sub; t < n; t += 4) atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
+  __syncwarp(gmask);
+  uint32_t lo, hi;  // this lane's buckets sub*8 .. sub*8+7 occupy ord[lo, hi)
+  {
+    uint32_t c8[8], tot = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      c8[k] = cur[(sub * 8 + k) * 8];
+      tot += c8[k];
+    }
+    uint32_t incl = tot;
+    uint32_t up = __shfl_up_sync(gmask, incl, 1, 4);
+    if (sub >= 1) incl += up;
+    up = __shfl_up_sync(gmask, incl, 2, 4);
+    if (sub >= 2) incl += up;
+    lo = incl - tot, hi = incl;
+    uint32_t run = lo;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      cur[(sub * 8 + k) * 8] = run;
+      run += c8[k];
+    }
+  }
+  __syncwarp(gmask);
+  for (uint32_t t = sub; t < n; t += 4) {
+    const uint32_t pos = atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
+    ord[pos * 8] = (uint8_t)t;
+  }
+  __syncwarp(gmask);
+  // ---- insertion sort of the lane's segment (elements never leave their bucket); `top` is the
+  //      last key of the sorted prefix, so an element already in place costs one comparison
+  auto before = [&](uint32_t ka, uint32_t kb) -> bool {  // does ka precede kb in radiusSearch order?
+    const uint32_t qa = ka >> jbits, qb = kb >> jbits;
+    if (qa != qb) return qa < qb;
+    const float4 pa = g.pts[ka & jmask], pb = g.pts[kb & jmask];
+    const float da = dist2_f(q.x - pa.x, q.y - pa.y, q.z - pa.z);
+    const float db = dist2_f(q.x - pb.x, q.y - pb.y, q.z - pb.z);
+    return da < db || (da == db && __float_as_uint(pa.w) < __float_as_uint(pb.w));
+  };
+  if (lo < hi) {
+    uint32_t top = L[(uint32_t)ord[lo * 8] * 8];
+    for (uint32_t t = lo + 1; t < hi; t++) {
+      const uint32_t o = ord[t * 8];
+      const uint32_t k = L[o * 8];
+      if (before(top, k)) {
+        top = k;
+        continue;
+      }
+      uint32_t u = t;
+      do {
+        const uint32_t o2 = ord[(u - 1) * 8];
+        if (before(L[o2 * 8], k)) break;
+        ord[u * 8] = (uint8_t)o2;
+        u--;
+      } while (u > lo);
+      ord[u * 8] = (uint8_t)o;
+    }
+  }
+  __syncwarp(gmask);
+  // ---- sequential single-pass float moments (accu[0..8] of computeMeanAndCovarianceMatrix):
+  //      lane 0: xx xy xz, lane 1: yy yz zz, lane 2: x y z (times the constant 1, exact)
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+  if (sub < 3) {
+#pragma unroll 4
+    for (uint32_t t = 0; t < n; t++) {
+      const float4 p = g.pts[L[(uint32_t)ord[t * 8] * 8] & jmask];
+      const float A0 = sub == 1 ? p.y : p.x, B0 = sub == 0 ? p.x : (sub == 1 ? p.y : 1.0f);
+      const float A1 = sub == 0 ? p.x : p.y, B1 = sub == 0 ? p.y : (sub == 1 ? p.z : 1.0f);
+      const float A2 = sub == 0 ? p.x : p.z, B2 = sub == 2 ? 1.0f : p.z;
+      a0 = __fadd_rn(a0, __fmul_rn(A0, B0));
+      a1 = __fadd_rn(a1, __fmul_rn(A1, B1));
+      a2 = __fadd_rn(a2, __fmul_rn(A2, B2));
+    }
+  }
+  float a[9];
+  const int l0 = (int)gshift;
+  a[0] = a0, a[1] = a1, a[2] = a2;
+  a[3] = __shfl_sync(gmask, a0, l0 + 1), a[4] = __shfl_sync(gmask, a1, l0 + 1), a[5] = __shfl_sync(gmask, a2, l0 + 1);
+  a[6] = __shfl_sync(gmask, a0, l0 + 2), a[7] = __shfl_sync(gmask, a1, l0 + 2), a[8] = __shfl_sync(gmask, a2, l0 + 2);
+  if (sub == 0) {
+    const float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
+#pragma unroll
+    for (int k = 0; k < 9; k++) a[k] = a[k] * inv;
+    float nv[3];
+    solve_normal(a, q.x, q.y, q.z, nv);
+    P.nrm_out[i] = make_float4(nv[0], nv[1], nv[2], P.nrm_out[i].w);
+  }
+}
+
 }  // namespace
 
+// Four-lanes-per-point launch over one tier list at capacity `cap` (< 256: byte permutation).
+static int launch_normals_quad(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list) {
+  const size_t smem = quad_smem_per_warp(cap) * (kQuadThreads / 32);
+  uint32_t jbits = 1;
+  while (jbits < 27 && (1ull << jbits) < (unsigned long long)c->n_finite) jbits++;
+  const uint32_t qbits = 32 - jbits;
+  QuadArgs P;
+  P.g = grid_dev(c);
+  P.r2 = c->hc.r2_normals, P.rq = c->hc.rq_normals;
+  P.qscale = ldexpf(1.0f, (int)qbits) / c->hc.r2_normals;
+  P.qmax = (uint32_t)((1ull << qbits) - 1ull);
+  P.jbits = jbits;
+  P.kn = c->kn.p;
+  P.list = list;
+  P.n_items = n_items, P.cap = cap;
+  P.nrm_out = c->nrm.p;
+  const uint32_t per_cta = kQuadThreads / 4;
+  k_normals_quad<<<(n_items + per_cta - 1) / per_cta, kQuadThreads, smem, st>>>(P);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
 // One launch over `n_items` items (all points, or a list) at capacity `cap`.
-static int launch_normals(ag2_ctx* c, uint32_t n_items, uint32_t cap, const uint32_t* list, uint32_t* big_list,
-                          uint32_t* big_count, uint32_t big_cap, uint32_t* batch_counter) {
-  cudaStream_t st = c->stream;
+static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list,
+                          uint32_t* big_list, uint32_t* big_count, uint32_t big_cap, uint32_t* batch_counter) {
   const NormalsSmem L = normals_smem(cap);
   const int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (110 * 1024) / L.total));
   const size_t smem = L.total * warps;
@@ -528,6 +786,65 @@ int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, in
   return AG2_OK;
 }
 
+// Tiered path: count pass with tier lists, then one launch per non-empty tier on the auxiliary streams.
+static int normals_compute_tiered(ag2_ctx* c) {
+  cudaStream_t st = c->stream;
+  GridDev g = grid_dev(c);
+  const uint32_t n = (uint32_t)c->n_finite;
+  const uint32_t owned = normals_shard_points(n, c->nrm_rank, c->nrm_world);
+  // The four sparsest tiers (<= 96 neighbours) run on k_normals_quad, the rest on k_normals: measured
+  // best on c2 and c3.  AG2_NORMALS_QUAD_TIERS = 0..8 moves the boundary (tests).
+  uint32_t quad_tiers = 4;
+  if (const char* e = getenv("AG2_NORMALS_QUAD_TIERS")) quad_tiers = (uint32_t)std::min(kQuadTiers, std::max(0, atoi(e)));
+  AG2_CUDA(c, c->kn.reserve(n));
+  AG2_CUDA(c, c->tier_list.reserve((size_t)kAllTiers * std::max(owned, 1u)));
+  AG2_CUDA(c, c->tier_cnt.reserve(32));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
+  AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, 32 * 4, st));
+  k_count_tiers<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
+                                                 (unsigned long long*)(c->scalars.p + 10), c->tier_cnt.p,
+                                                 c->tier_list.p, owned, c->nrm.p, (uint32_t)c->nrm_rank,
+                                                 (uint32_t)c->nrm_world);
+  AG2_LAUNCH_CHECK(c);
+  uint32_t res[4], cnt[kAllTiers];
+  AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaMemcpyAsync(cnt, c->tier_cnt.p, sizeof(cnt), cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaStreamSynchronize(st));
+  const uint32_t max_kn = res[0];
+  unsigned long long sum;
+  memcpy(&sum, &res[2], 8);
+  c->st.sum_neighbors_normals = (int64_t)sum;
+  const uint32_t cap_max = (std::max(max_kn, 32u) + 31u) & ~31u;
+  if (normals_smem(cap_max).total > 220 * 1024) {
+    c->err = "normals: a point has more than ~11000 neighbours within normals_radius";
+    return AG2_E_CAPACITY;
+  }
+  AG2_CUDA(c, cudaFuncSetAttribute(k_normals_quad, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(quad_smem_per_warp(kTierCapHost[kQuadTiers - 1]) * (kQuadThreads / 32))));
+  AG2_CUDA(c, cudaEventRecord(c->ev_fork, st));
+  for (int i = 0; i < 4; i++) AG2_CUDA(c, cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
+  int used = 0;
+  // dense tiers first: their launches run longest
+  for (int k = 0; k < kAllTiers; k++) {
+    const int tier = kAllTiers - 1 - k;
+    if (!cnt[tier]) continue;
+    cudaStream_t s2 = c->aux[used++ & 3];
+    const uint32_t* list = c->tier_list.p + (size_t)tier * owned;
+    if (tier < (int)quad_tiers) {
+      AG2_TRY(launch_normals_quad(c, s2, cnt[tier], kTierCapHost[tier], list));
+    } else {
+      const uint32_t cap = std::min(kTierCapHost[tier], cap_max);
+      AG2_TRY(launch_normals(c, s2, cnt[tier], cap, list, c->tier_cnt.p + 30, c->tier_cnt.p + 31, 0,
+                             c->tier_cnt.p + 16 + tier));
+    }
+  }
+  for (int i = 0; i < std::min(used, 4); i++) {
+    AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
+    AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
+  }
+  return AG2_OK;
+}
+
 int normals_compute(ag2_ctx* c) {
   AG2_TRY(grid_build(c));
   if (c->have_normals) return AG2_OK;
@@ -535,6 +852,15 @@ int normals_compute(ag2_ctx* c) {
   cudaStream_t st = c->stream;
   GridDev g = grid_dev(c);
   const uint32_t n = (uint32_t)c->n_finite;
+  // test / measurement hook: AG2_NORMALS_WARP=1 runs every point on the warp-per-point kernel, in
+  // capacity levels chained through overflow lists (the path before the tiers existed)
+  const char* warp_only = getenv("AG2_NORMALS_WARP");
+  if (!(warp_only && atoi(warp_only) != 0) && n <= (1u << 27)) {
+    AG2_TRY(normals_compute_tiered(c));
+    c->have_normals = true;
+    phase_end(c, 1);
+    return AG2_OK;
+  }
   AG2_CUDA(c, c->kn.reserve(n));
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));    // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 32, 0, 32 * 4, st));  // [32..39] tiers, [40..47] list counts, [48..55] batch counters
@@ -577,7 +903,7 @@ int normals_compute(ag2_ctx* c) {
       }
     DevBuf<uint32_t>& out = c->big_list[level & 1];
     if (left) AG2_CUDA(c, out.reserve(left));
-    AG2_TRY(launch_normals(c, remaining, cap, list, out.p, c->scalars.p + 40 + level, left,
+    AG2_TRY(launch_normals(c, st, remaining, cap, list, out.p, c->scalars.p + 40 + level, left,
                            c->scalars.p + 48 + level));
     list = out.p;
     remaining = left;

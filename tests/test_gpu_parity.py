@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 
 from agile_grasp2_b200 import capi, scenes
-from common import angle, both, hyp_int_fields_equal, make_params
+from common import angle, both, hyp_int_fields_equal, load_scene, make_params
 from oracle import binding as ob
 
 pytestmark = pytest.mark.gpu
@@ -460,3 +460,50 @@ def test_render_point_sets_vs_oracle(aligns):
     assert gi.shape == oi.shape == (5, 60, 60, 3)
     assert np.array_equal(gi, oi)
     assert not gi[0].any() and gi[3].any()
+
+
+def _lattice_scene():
+    """Two regular 2 mm lattices (a level one and a tilted one): nearly every neighbourhood holds many
+    EXACTLY equal float distances, so the (d2, input index) tie order of the radius search is exercised."""
+    u, v = np.meshgrid(np.arange(100, dtype=np.float64), np.arange(100, dtype=np.float64), indexing="ij")
+    a = np.stack([0.60 + 0.002 * u, -0.10 + 0.002 * v, np.full_like(u, -0.20)], -1).reshape(-1, 3)
+    b = np.stack([0.60 + 0.002 * u, 0.15 + 0.002 * v, -0.20 + 0.001 * u], -1).reshape(-1, 3)
+    xyz = np.concatenate([a, b]).astype(np.float32)
+    rng = np.random.default_rng(5)
+    xyz = xyz[rng.permutation(len(xyz))]  # input order != cell order
+    return dict(name="lattice", xyz=xyz, cam_mask=np.ones(len(xyz), np.uint8), num_cams=1,
+                samples=np.arange(0, len(xyz), 997, dtype=np.int32))
+
+
+@pytest.mark.parametrize("scene,quad_tiers", [("tiny", None), ("tiny", "8"), ("tiny", "0"), ("lattice", "8"),
+                                              ("lattice", None)])
+def test_normals_quad_per_point_and_warp_per_point_agree(tiny_scene, monkeypatch, scene, quad_tiers):
+    """Points are grouped by neighbourhood size into tiers, one launch per tier, side by side. Sparse tiers
+    run four lanes per point (k_normals_quad; up to 208 neighbours when AG2_NORMALS_QUAD_TIERS=8), the
+    others one warp per point (k_normals); AG2_NORMALS_WARP=1 runs k_normals everywhere in chained
+    capacity levels. All reproduce the radius-search order exactly, so the normals are bit-identical --
+    and equal to the oracle's."""
+    sc = _lattice_scene() if scene == "lattice" else tiny_scene
+    if quad_tiers is not None:
+        monkeypatch.setenv("AG2_NORMALS_QUAD_TIERS", quad_tiers)
+    monkeypatch.setenv("AG2_NORMALS_FIRST_TIER", "0")  # forced run: first level capacity 64
+    p = make_params(capi.MODE_GEOMETRIC)
+    out = []
+    for forced in ("0", "1"):
+        monkeypatch.setenv("AG2_NORMALS_WARP", forced)
+        with capi.Context(p) as g:
+            load_scene(g, sc)
+            g.compute_normals()
+            out.append(g.normals().copy())
+    assert np.array_equal(out[0].view(np.uint32), out[1].view(np.uint32))
+    o = ob.context(p)
+    load_scene(o, sc)
+    o.compute_normals()
+    on = o.normals()
+    assert np.array_equal(np.isnan(out[0]), np.isnan(on))
+    ok = ~np.isnan(on).any(1)
+    assert ok.sum() > 1000
+    assert angle(out[0][ok], on[ok]).max() <= 1e-4
+    bit_equal = np.mean(np.all(out[0][ok].view(np.uint32) == on[ok].view(np.uint32), axis=1))
+    print("%s: bit-equal fraction %.6f" % (scene, bit_equal))
+    assert bit_equal > 0.999
