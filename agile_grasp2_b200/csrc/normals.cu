@@ -181,6 +181,30 @@ __device__ void solve_normal(const float a[9], float px, float py, float pz, flo
   }
 }
 
+// Raw moment sums of a point (accu[0..8] of computeMeanAndCovarianceMatrix before the division), padded
+// to three float4.  The neighbourhood kernels only produce these; k_eigen finishes every point of
+// the cloud in one full-occupancy launch instead of a few lanes at the end of each warp's batch.
+constexpr int kMomWords = 12;
+
+__global__ void __launch_bounds__(256) k_eigen(GridDev g, const uint32_t* __restrict__ kn,
+                                               const float* __restrict__ mom, float4* __restrict__ nrm_out,
+                                               uint32_t shard_rank, uint32_t shard_world) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (uint32_t)g.n || (i >> 5) % shard_world != shard_rank) return;
+  const uint32_t count = kn[i];
+  if (count < 3) return;  // NaN already written
+  const float4* m4 = reinterpret_cast<const float4*>(mom + (size_t)i * kMomWords);
+  const float4 m0 = m4[0], m1 = m4[1], m2 = m4[2];
+  float a[9] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x};
+  const float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
+#pragma unroll
+  for (int k = 0; k < 9; k++) a[k] = a[k] * inv;
+  const float4 q = g.pts[i];
+  float n[3];
+  solve_normal(a, q.x, q.y, q.z, n);
+  nrm_out[i] = make_float4(n[0], n[1], n[2], nrm_out[i].w);
+}
+
 // ---------------------------------------------------------------------------
 // k_normals.  A warp owns `bsz` (<= 32) points at a time, taken from a global counter.
 // Per point (warp cooperative):
@@ -194,16 +218,15 @@ __device__ void solve_normal(const float a[9], float px, float py, float pz, flo
 //            its coordinates are written at `rank` of the staging array S;
 //   moments  lanes 0..8 run the nine single-pass float accumulators of
 //            computeMeanAndCovarianceMatrix over S in that order (sequential by
-//            definition).
-// Per bsz points: one thread per point solves eigen33 + viewpoint flip.
-// Shared memory per warp is 20 B x cap + 2.7 KB, so the launch capacity decides the
+//            definition) and store the raw sums; k_eigen (thread per point, one launch
+//            for the whole cloud) solves eigen33 and flips the normal.
+// Shared memory per warp is 20 B x cap + 1.3 KB, so the launch capacity decides the
 // occupancy: the host runs the bulk of the points at a small cap and hands the dense
 // ones (appended to big_list here) to further launches with larger caps.
 constexpr int kNB = 128;     // d2 buckets (4 per lane in the prefix)
-constexpr int kMomStride = 11;
 
 struct NormalsSmem {  // per-warp carve-up (byte offsets, 16-aligned)
-  size_t a, s, cnt, start, rowb, rowp, mom, total;
+  size_t a, s, cnt, start, rowb, rowp, total;
 };
 __host__ __device__ inline NormalsSmem normals_smem(uint32_t cap) {
   NormalsSmem L;
@@ -214,7 +237,6 @@ __host__ __device__ inline NormalsSmem normals_smem(uint32_t cap) {
   L.start = o, o += (kNB + 4) * 4;
   L.rowb = o, o += 32 * 4;
   L.rowp = o, o += 36 * 4;
-  L.mom = o, o += 32 * kMomStride * 4;
   L.total = (o + 15) & ~(size_t)15;
   return L;
 }
@@ -234,6 +256,7 @@ struct NormalsArgs {
   uint32_t* big_count;
   uint32_t big_cap;
   uint32_t* batch_counter;    // dynamic batch scheduling
+  float* mom_out;             // [n][kMomWords] raw moment sums; k_eigen turns them into normals
   float4* nrm_out;
 };
 
@@ -251,7 +274,6 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   uint32_t* start = (uint32_t*)(base + L.start);
   uint32_t* rowb = (uint32_t*)(base + L.rowb);
   uint32_t* rowp = (uint32_t*)(base + L.rowp);
-  float* mom = (float*)(base + L.mom);
   const uint32_t n_batches = (P.n_items + bsz - 1) / bsz;
   // accumulator role of lanes 0..8: operand selectors 0 = x, 1 = y, 2 = z, 3 = constant 1
   const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
@@ -407,26 +429,14 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
         const float* ra = (const float*)pa;
         const float* rb_ = (const float*)pb;
         for (uint32_t t = n4 << 2; t < count; t++) acc = __fadd_rn(acc, __fmul_rn(ra[t], rb_[step_b * t]));
-        mom[k * kMomStride + lane] = acc;
+        P.mom_out[(size_t)i * kMomWords + lane] = acc;
       }
       __syncwarp();
     }
-    // ---- one thread per point: eigen33 + flip
-    if (lane < nb && !too_big) {
-      const float4 old = P.nrm_out[my_i];
-      if (my_count < 3) {  // computePointNormal: fewer than 3 neighbours -> NaN
-        float nanv = __int_as_float(0x7fc00000);
-        P.nrm_out[my_i] = make_float4(nanv, nanv, nanv, old.w);
-      } else {
-        const float4 q = g.pts[my_i];
-        float a[9];
-        const float inv = 1.0f / (float)my_count;  // Eigen 3.2 operator/=: multiply by the reciprocal
-#pragma unroll
-        for (int k = 0; k < 9; k++) a[k] = mom[lane * kMomStride + k] * inv;
-        float n[3];
-        solve_normal(a, q.x, q.y, q.z, n);
-        P.nrm_out[my_i] = make_float4(n[0], n[1], n[2], old.w);
-      }
+    // ---- fewer than 3 neighbours -> NaN (computePointNormal); everything else is k_eigen's
+    if (lane < nb && my_count < 3) {
+      const float nanv = __int_as_float(0x7fc00000);
+      P.nrm_out[my_i] = make_float4(nanv, nanv, nanv, P.nrm_out[my_i].w);
     }
     __syncwarp();
   }
@@ -512,8 +522,8 @@ __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float 
 //            sorts it.  Keys with different q are ordered by q; EQUAL q falls back to the exact
 //            (d2, input index) comparison, recomputing d2 with the gather's own float sequence --
 //            so the result is exactly FLANN's radiusSearch order;
-//   moments  lanes 0..2 of the group run three of the nine sequential float accumulators each;
-//            lane 0 then solves eigen33 and flips the normal.
+//   moments  lanes 0..2 of the group run three of the nine sequential float accumulators each and
+//            store the raw sums for k_eigen.
 // Lists are laid out [entry][group] per warp, so the four consecutive entries a group touches
 // fall into distinct banks whatever the other groups do.  Shared memory is 5 B x cap + 128 B per
 // point (a quarter of that per thread), which is what gives this kernel its occupancy.
@@ -526,7 +536,7 @@ struct QuadArgs {
   const uint32_t* kn;
   const uint32_t* list;
   uint32_t n_items, cap;
-  float4* nrm_out;
+  float* mom_out;
 };
 
 __host__ __device__ inline size_t quad_smem_per_warp(uint32_t cap) { return (size_t)cap * 40 + 1024; }
@@ -544,8 +554,7 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
   const uint32_t item = (blockIdx.x * kQuadThreads + threadIdx.x) >> 2;
   if (item >= P.n_items) return;  // whole groups leave together
   const uint32_t i = P.list[item];
-  const uint32_t count = P.kn[i];  // 3 <= count <= cap: the tier list holds nothing else
-  const float4 q = g.pts[i];
+  const float4 q = g.pts[i];  // 3 <= kn[i] <= cap: the tier list holds nothing else
   const uint32_t jbits = P.jbits, jmask = (1u << jbits) - 1u;
   const float r2 = P.r2;
   // ---- gather
@@ -654,18 +663,9 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
       a2 = __fadd_rn(a2, __fmul_rn(A2, B2));
     }
   }
-  float a[9];
-  const int l0 = (int)gshift;
-  a[0] = a0, a[1] = a1, a[2] = a2;
-  a[3] = __shfl_sync(gmask, a0, l0 + 1), a[4] = __shfl_sync(gmask, a1, l0 + 1), a[5] = __shfl_sync(gmask, a2, l0 + 1);
-  a[6] = __shfl_sync(gmask, a0, l0 + 2), a[7] = __shfl_sync(gmask, a1, l0 + 2), a[8] = __shfl_sync(gmask, a2, l0 + 2);
-  if (sub == 0) {
-    const float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
-#pragma unroll
-    for (int k = 0; k < 9; k++) a[k] = a[k] * inv;
-    float nv[3];
-    solve_normal(a, q.x, q.y, q.z, nv);
-    P.nrm_out[i] = make_float4(nv[0], nv[1], nv[2], P.nrm_out[i].w);
+  if (sub < 3) {
+    float* m = P.mom_out + (size_t)i * kMomWords + sub * 3;
+    m[0] = a0, m[1] = a1, m[2] = a2;
   }
 }
 
@@ -686,7 +686,7 @@ static int launch_normals_quad(ag2_ctx* c, cudaStream_t st, uint32_t n_items, ui
   P.kn = c->kn.p;
   P.list = list;
   P.n_items = n_items, P.cap = cap;
-  P.nrm_out = c->nrm.p;
+  P.mom_out = c->nrm_mom.p;
   const uint32_t per_cta = kQuadThreads / 4;
   k_normals_quad<<<(n_items + per_cta - 1) / per_cta, kQuadThreads, smem, st>>>(P);
   AG2_LAUNCH_CHECK(c);
@@ -719,6 +719,7 @@ static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_
   P.list = list;
   P.big_list = big_list, P.big_count = big_count, P.big_cap = big_cap;
   P.batch_counter = batch_counter;
+  P.mom_out = c->nrm_mom.p;
   P.nrm_out = c->nrm.p;
   k_normals<<<grid, warps * 32, smem, st>>>(P);
   AG2_LAUNCH_CHECK(c);
@@ -798,7 +799,8 @@ static int normals_compute_tiered(ag2_ctx* c) {
   if (const char* e = getenv("AG2_NORMALS_QUAD_TIERS")) quad_tiers = (uint32_t)std::min(kQuadTiers, std::max(0, atoi(e)));
   AG2_CUDA(c, c->kn.reserve(n));
   AG2_CUDA(c, c->tier_list.reserve((size_t)kAllTiers * std::max(owned, 1u)));
-  AG2_CUDA(c, c->tier_cnt.reserve(32));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
+  AG2_CUDA(c, c->tier_cnt.reserve(32));
+  AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, 32 * 4, st));
   k_count_tiers<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
@@ -842,6 +844,9 @@ static int normals_compute_tiered(ag2_ctx* c) {
     AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
     AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
   }
+  k_eigen<<<(n + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p, (uint32_t)c->nrm_rank,
+                                           (uint32_t)c->nrm_world);
+  AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }
 
@@ -862,6 +867,7 @@ int normals_compute(ag2_ctx* c) {
     return AG2_OK;
   }
   AG2_CUDA(c, c->kn.reserve(n));
+  AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));    // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 32, 0, 32 * 4, st));  // [32..39] tiers, [40..47] list counts, [48..55] batch counters
   k_count_neighbors<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p,
@@ -909,6 +915,9 @@ int normals_compute(ag2_ctx* c) {
     remaining = left;
     level++;
   }
+  k_eigen<<<(n + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p, (uint32_t)c->nrm_rank,
+                                           (uint32_t)c->nrm_world);
+  AG2_LAUNCH_CHECK(c);
   c->have_normals = true;
   phase_end(c, 1);
   return AG2_OK;
