@@ -282,11 +282,12 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   if (threadIdx.x < 4) ones_s[threadIdx.x] = 1.0f;
   __syncthreads();
 
-  for (;;) {
-    uint32_t batch = 0;
-    if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
-    batch = __shfl_sync(AG2_FULL, batch, 0);
-    if (batch >= n_batches) break;
+  uint32_t batch = 0;
+  if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
+  batch = __shfl_sync(AG2_FULL, batch, 0);
+  while (batch < n_batches) {
+    uint32_t next = 0;  // the following batch is claimed now, so the atomic's round trip hides behind this one
+    if (lane == 0) next = atomicAdd(P.batch_counter, 1u);
     const uint32_t i0 = batch * bsz;
     const uint32_t nb = min(bsz, P.n_items - i0);
     const uint32_t my_i =
@@ -329,20 +330,37 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
         __syncwarp();
         int row = 0;
         uint32_t row_lo = 0, row_hi = rowp[1], row_b = rowb[0];
+        // the candidate of the NEXT iteration is located and loaded one iteration ahead
+        uint32_t j_next = 0;
+        float4 p_next = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lane < T) {
+          while (lane >= row_hi) {
+            row++;
+            row_lo = row_hi;
+            row_hi = rowp[row + 1];
+            row_b = rowb[row];
+          }
+          j_next = row_b + ((uint32_t)lane - row_lo);
+          p_next = g.pts[j_next];
+        }
         for (uint32_t t0 = 0; t0 < T; t0 += 32) {
           const uint32_t t = t0 + lane;
-          bool hit = false;
-          float d2 = 0.f;
-          uint32_t j = 0;
-          if (t < T) {
-            while (t >= row_hi) {
+          const uint32_t j = j_next;
+          const float4 p = p_next;
+          const uint32_t tn = t + 32;
+          if (tn < T) {
+            while (tn >= row_hi) {
               row++;
               row_lo = row_hi;
               row_hi = rowp[row + 1];
               row_b = rowb[row];
             }
-            j = row_b + (t - row_lo);
-            float4 p = g.pts[j];
+            j_next = row_b + (tn - row_lo);
+            p_next = g.pts[j_next];
+          }
+          bool hit = false;
+          float d2 = 0.f;
+          if (t < T) {
             d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
             hit = d2 < P.r2;
           }
@@ -403,12 +421,21 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
         A[t] = make_uint2(rank, e.y);
       }
       __syncwarp();
-      for (uint32_t t = lane; t < count; t += 32) {
-        const uint2 rj = A[t];
-        const float4 p = g.pts[rj.y];
-        S[rj.x] = p.x;  // SoA: X[cap] Y[cap] Z[cap]
-        S[cap + rj.x] = p.y;
-        S[2 * cap + rj.x] = p.z;
+      for (uint32_t t = lane; t < count; t += 128) {  // four loads in flight per lane
+        uint2 rj[4];
+        float4 p[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          rj[u] = A[min(t + 32u * u, count - 1)];
+          p[u] = g.pts[rj[u].y];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (t + 32u * u < count) {
+            S[rj[u].x] = p[u].x;  // SoA: X[cap] Y[cap] Z[cap]
+            S[cap + rj[u].x] = p[u].y;
+            S[2 * cap + rj[u].x] = p[u].z;
+          }
       }
       __syncwarp();
       // ---- sequential single-pass float moments
@@ -438,6 +465,7 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
       const float nanv = __int_as_float(0x7fc00000);
       P.nrm_out[my_i] = make_float4(nanv, nanv, nanv, P.nrm_out[my_i].w);
     }
+    batch = __shfl_sync(AG2_FULL, next, 0);
     __syncwarp();
   }
 }
