@@ -825,6 +825,10 @@ static int normals_compute_tiered(ag2_ctx* c) {
   // best on c2 and c3.  AG2_NORMALS_QUAD_TIERS = 0..8 moves the boundary (tests).
   uint32_t quad_tiers = 4;
   if (const char* e = getenv("AG2_NORMALS_QUAD_TIERS")) quad_tiers = (uint32_t)std::min(kQuadTiers, std::max(0, atoi(e)));
+  // A lone k_normals_quad launch cannot finish faster than one group's chain of dependent accesses
+  // (~130 us); a short list is better off on k_normals, whose floor is a tenth of that.
+  uint32_t quad_min = 8192;
+  if (const char* e = getenv("AG2_NORMALS_QUAD_MIN")) quad_min = (uint32_t)std::max(0, atoi(e));
   AG2_CUDA(c, c->kn.reserve(n));
   AG2_CUDA(c, c->tier_list.reserve((size_t)kAllTiers * std::max(owned, 1u)));
   AG2_CUDA(c, c->tier_cnt.reserve(32));
@@ -860,7 +864,7 @@ static int normals_compute_tiered(ag2_ctx* c) {
     if (!cnt[tier]) continue;
     cudaStream_t s2 = c->aux[used++ & 3];
     const uint32_t* list = c->tier_list.p + (size_t)tier * owned;
-    if (tier < (int)quad_tiers) {
+    if (tier < (int)quad_tiers && cnt[tier] >= quad_min) {
       AG2_TRY(launch_normals_quad(c, s2, cnt[tier], kTierCapHost[tier], list));
     } else {
       const uint32_t cap = std::min(kTierCapHost[tier], cap_max);
