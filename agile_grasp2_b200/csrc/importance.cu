@@ -21,12 +21,48 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
+#include <thread>
 #include <vector>
 
 #include "dev_common.cuh"
 
 namespace ag2 {
 namespace {
+
+// AG2_IS_TRACE=1: host wall-clock of the segments of a multi-round run on stderr (profiling aid)
+struct IsTrace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  IsTrace() : on(getenv("AG2_IS_TRACE") && atoi(getenv("AG2_IS_TRACE")) != 0), t0(std::chrono::steady_clock::now()) {}
+  void lap(const char* what, int round) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[ag2 importance] round %d %-10s %8.3f ms\n", round, what,
+            std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+
+// Host-side helper threads of the candidate generator: the draws are counter-based (every candidate is a pure
+// function of (seed, round, candidate id)), so any split over threads gives the same stream.
+template <class F>
+void parallel_for(size_t n, F f) {
+  const unsigned hw = std::thread::hardware_concurrency();
+  const unsigned nt = std::min<unsigned>(hw ? hw : 1u, 16u);
+  if (n < 2048 || nt <= 1) {
+    f((size_t)0, n);
+    return;
+  }
+  const size_t chunk = (n + nt - 1) / nt;
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < nt; t++) {
+    const size_t b = (size_t)t * chunk, e = std::min(n, b + chunk);
+    if (b < e) th.emplace_back([=] { f(b, e); });
+  }
+  f((size_t)0, std::min(n, chunk));
+  for (auto& x : th) x.join();
+}
 
 inline uint64_t h_splitmix64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;
@@ -49,25 +85,34 @@ inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) 
 
 // One warp per candidate: accept iff c*d2(x, hand[idx]) >= max_k c*d2(x, hand[k]).
 __global__ void k_is_accept(const double* __restrict__ cand, const int32_t* __restrict__ cand_idx, uint32_t n_cand,
-                            const ag2_hypothesis* __restrict__ hands, uint32_t H, double coef,
-                            uint8_t* __restrict__ accept) {
+                            const ag2_hypothesis* __restrict__ hands, const double* __restrict__ surf /* 3H, packed */,
+                            uint32_t H, double coef, uint8_t* __restrict__ accept) {
   const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= n_cand) return;
   const double x0 = cand[3 * c], x1 = cand[3 * c + 1], x2 = cand[3 * c + 2];
-  double best = -INFINITY;
-  for (uint32_t k = lane; k < H; k += 32) {
-    const double v0 = x0 - hands[k].surface[0], v1 = x1 - hands[k].surface[1], v2 = x2 - hands[k].surface[2];
-    const double d2 = v0 * v0 + (v1 * v1 + v2 * v2);  // Eigen fixed-size inner product order
-    best = fmax(best, coef * d2);
-  }
-  best = warp_max_d(best);
-  if (lane == 0) {
+  // own = coef * d2 to the generating hand; the candidate is rejected as soon as ANY hand scores strictly higher
+  // (the same decision as comparing with the maximum over all hands, which nearly every candidate fails early)
+  double own;
+  {
     const ag2_hypothesis& h = hands[cand_idx[c]];
     const double v0 = x0 - h.surface[0], v1 = x1 - h.surface[1], v2 = x2 - h.surface[2];
-    const double d2 = v0 * v0 + (v1 * v1 + v2 * v2);
-    accept[c] = (coef * d2 >= best) ? 1 : 0;
+    own = coef * (v0 * v0 + (v1 * v1 + v2 * v2));  // Eigen fixed-size inner product order
   }
+  bool ok = true;
+  for (uint32_t k0 = 0; k0 < H; k0 += 32) {
+    const uint32_t k = k0 + lane;
+    bool higher = false;
+    if (k < H) {
+      const double v0 = x0 - surf[3 * k], v1 = x1 - surf[3 * k + 1], v2 = x2 - surf[3 * k + 2];
+      higher = coef * (v0 * v0 + (v1 * v1 + v2 * v2)) > own;
+    }
+    if (__any_sync(AG2_FULL, higher)) {
+      ok = false;
+      break;
+    }
+  }
+  if (lane == 0) accept[c] = ok ? 1 : 0;
 }
 
 // rand part of a round: samples.col(j) = cloud->points[r].getVector3fMap().cast<double>()
@@ -133,6 +178,10 @@ int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis
     for (size_t k = 0; k < H; k++)
       for (int a = 0; a < 3; a++) surf[3 * k + a] = h_hands[k].surface[a];
   }
+  if (ip->method != 1 && n_gauss > 0) {
+    AG2_CUDA(c, c->is_surf.reserve(3 * H));
+    AG2_CUDA(c, cudaMemcpyAsync(c->is_surf.p, surf.data(), 24 * H, cudaMemcpyHostToDevice, st));
+  }
   // 3.1 samples close to the grasps found so far
   int got = 0;
   uint64_t next_cand = 0;
@@ -141,15 +190,30 @@ int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis
       c->err = "importance sampling: rejection sampler did not terminate";
       return AG2_E_STATE;
     }
-    const size_t B = ip->method == 1 ? (size_t)(n_gauss - got) : std::max<size_t>(256, (size_t)(n_gauss - got) * 8);
+    // batch size: the accepted samples are the first n_gauss accepted candidates in id order whatever the
+    // batching, so it only trades round trips against wasted candidates: 8 x the missing samples at first, then
+    // missing / observed acceptance rate with a quarter to spare
+    size_t B = (size_t)(n_gauss - got);
+    if (ip->method != 1) {
+      const double rate = next_cand ? std::max((double)got / (double)next_cand, 1e-4) : 0.125;
+      B = (size_t)std::min(4.0e6, std::max(256.0, 1.25 * (double)(n_gauss - got) / rate));
+    }
     cand.resize(3 * B);
     cidx.resize(B);
-    for (size_t b = 0; b < B; b++) {
-      const uint64_t cid = next_cand + b;
-      const size_t idx = (size_t)(is_hash(ip->seed, (uint64_t)it, cid, 6) % (uint64_t)H);
-      cidx[b] = (int32_t)idx;
-      for (int a = 0; a < 3; a++)
-        cand[3 * b + a] = surf[3 * idx + a] + is_normal(ip->seed, (uint64_t)it, cid, a) * sigma;
+    {
+      double* cand_p = cand.data();
+      int32_t* cidx_p = cidx.data();
+      const double* surf_p = surf.data();
+      const uint64_t seed = ip->seed, first = next_cand;
+      parallel_for(B, [=](size_t b0, size_t b1) {
+        for (size_t b = b0; b < b1; b++) {
+          const uint64_t cid = first + b;
+          const size_t idx = (size_t)(is_hash(seed, (uint64_t)it, cid, 6) % (uint64_t)H);
+          cidx_p[b] = (int32_t)idx;
+          for (int a = 0; a < 3; a++)
+            cand_p[3 * b + a] = surf_p[3 * idx + a] + is_normal(seed, (uint64_t)it, cid, a) * sigma;
+        }
+      });
     }
     next_cand += B;
     if (ip->method == 1) {  // sum of Gaussians: every draw is a sample
@@ -164,7 +228,7 @@ int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis
     AG2_CUDA(c, cudaMemcpyAsync(c->is_cand.p, cand.data(), 24 * B, cudaMemcpyHostToDevice, st));
     AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, cidx.data(), 4 * B, cudaMemcpyHostToDevice, st));
     k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B, d_hands,
-                                                                  (uint32_t)H, coef, c->is_accept.p);
+                                                                  c->is_surf.p, (uint32_t)H, coef, c->is_accept.p);
     AG2_LAUNCH_CHECK(c);
     AG2_CUDA(c, cudaMemcpyAsync(acc.data(), c->is_accept.p, B, cudaMemcpyDeviceToHost, st));
     AG2_CUDA(c, cudaStreamSynchronize(st));
@@ -216,7 +280,10 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
     ~NoCluster() { c->p.min_inliers = saved; }
   } no_cluster(c);
   // 1. initial grasp hypotheses on the samples the caller has set (importance_sampling.cpp:38)
+  IsTrace trace;
   AG2_TRY(ag2_detect(c));
+  if (trace.on) cudaStreamSynchronize(st);
+  trace.lap("detect", -1);
   int32_t sample_offset = 0;
   AG2_TRY(append_selected(c, cap, sample_offset));
   sample_offset += (int32_t)c->num_samples;
@@ -226,6 +293,7 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
     AG2_CUDA(c, c->sample_xyz.reserve((size_t)3 * ns));
     AG2_TRY(draw_round(c, ip, it, c->list_rec[AG2_LIST_IMPORTANCE].p, c->list_n[AG2_LIST_IMPORTANCE], nullptr,
                        c->sample_xyz.p));
+    trace.lap("draw", it);
     AG2_CUDA(c, cudaMemcpyAsync(c->is_samples.p + 3 * c->is_samples_n, c->sample_xyz.p, (size_t)24 * ns,
                                 cudaMemcpyDeviceToDevice, st));
     c->is_round_offset.push_back(c->is_samples_n);
@@ -239,7 +307,11 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
       c->list_rec_valid[i] = false;
     }
     AG2_TRY(ag2_detect(c));
+    if (trace.on) cudaStreamSynchronize(st);
+    trace.lap("detect", it);
     AG2_TRY(append_selected(c, cap, sample_offset));
+    if (trace.on) cudaStreamSynchronize(st);
+    trace.lap("append", it);
     sample_offset += ns;
   }
   // :105-109 clusters over the hands of all rounds -> AG2_LIST_CLUSTERS
