@@ -73,11 +73,11 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
   const uint32_t T = sh.total_cand;
   const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
   uint32_t kcount = 0;
+  uint32_t t0 = sh.cursor;  // advances by one batch per iteration in every thread alike; published on exit
   for (;;) {
-    const uint32_t t0 = sh.cursor;
     const uint32_t kept_now = sh.nkept;
     if (t0 >= T || kept_now + kHandThreads * kCand > A.cap) break;
-    __syncthreads();  // everyone has read cursor / nkept
+    __syncthreads();  // everyone has read nkept
     const uint32_t tb = t0 + (uint32_t)tid * kCand;
     int row = 0;
     uint32_t row_end = 0, pos = 0;
@@ -91,13 +91,15 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
       row_end = sh.row_prefix[row + 1];
       pos = sh.row_begin[row] + (tb - sh.row_prefix[row]);
     }
+    // positions first, then all loads in flight, then the tests
+    uint32_t pp[kCand];
+    bool val[kCand];
 #pragma unroll
     for (int b = 0; b < kCand; b++) {
       const uint32_t t = tb + (uint32_t)b;
-      bool keep = false;
-      float dx = 0.f, dy = 0.f, dz = 0.f;
-      uint32_t ppos = 0;
-      if (t < T) {
+      val[b] = t < T;
+      pp[b] = 0;
+      if (val[b]) {
         if (t >= row_end) {
           do {
             row++;
@@ -105,29 +107,52 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
           } while (t >= row_end);
           pos = sh.row_begin[row];
         }
-        ppos = pos++;
-        float4 p = A.g.pts[ppos];
+        pp[b] = pos++;
+      }
+    }
+    float4 pv[kCand];
+#pragma unroll
+    for (int b = 0; b < kCand; b++) pv[b] = val[b] ? A.g.pts[pp[b]] : make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t keepmask = 0;
+#pragma unroll
+    for (int b = 0; b < kCand; b++) {
+      if (val[b]) {
         // radiusSearch used q - p; hand_search.cpp:209 centres with p - q (exact negation)
-        dx = __fsub_rn(p.x, q[0]);
-        dy = __fsub_rn(p.y, q[1]);
-        dz = __fsub_rn(p.z, q[2]);
-        float d2 = dist2_f(dx, dy, dz);
+        const float dx = __fsub_rn(pv[b].x, q[0]);
+        const float dy = __fsub_rn(pv[b].y, q[1]);
+        const float dz = __fsub_rn(pv[b].z, q[2]);
+        const float d2 = dist2_f(dx, dy, dz);
         if (d2 < hc.r2_hands) {
           kcount++;
-          double zf = (az0 * (double)dx + az1 * (double)dy) + az2 * (double)dz;
-          keep = zf > hc.neg_hand_height && zf < hc.hand_height;  // hand_search.cpp:334
+          const double zf = (az0 * (double)dx + az1 * (double)dy) + az2 * (double)dz;
+          if (zf > hc.neg_hand_height && zf < hc.hand_height) keepmask |= 1u << b;  // hand_search.cpp:334
         }
+        pv[b] = make_float4(dx, dy, dz, __uint_as_float(pp[b]));
       }
-      uint32_t ballot = __ballot_sync(AG2_FULL, keep);
-      uint32_t base = 0;
-      if (lane == 0 && ballot) base = atomicAdd(&sh.nkept, (uint32_t)__popc(ballot));
-      base = __shfl_sync(AG2_FULL, base, 0);
-      if (keep) cache[base + __popc(ballot & ((1u << lane) - 1))] = make_float4(dx, dy, dz, __uint_as_float(ppos));
     }
-    __syncthreads();
-    if (tid == 0) sh.cursor = min(T, t0 + (uint32_t)kCand * kHandThreads);
-    __syncthreads();
+    // one warp scan + one shared atomic per warp and batch (the order inside the staging buffer is free:
+    // every consumer is an associative reduction or a set)
+    const uint32_t mine = (uint32_t)__popc(keepmask);
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(AG2_FULL, incl, o);
+      if (lane >= o) incl += up;
+    }
+    const uint32_t wtot = __shfl_sync(AG2_FULL, incl, 31);
+    uint32_t base = 0;
+    if (lane == 31 && wtot) base = atomicAdd(&sh.nkept, wtot);
+    base = __shfl_sync(AG2_FULL, base, 31);
+    uint32_t w = base + incl - mine;
+#pragma unroll
+    for (int b = 0; b < kCand; b++)
+      if (keepmask & (1u << b)) cache[w++] = pv[b];
+    t0 = min(T, t0 + (uint32_t)kCand * kHandThreads);
+    __syncthreads();  // nkept final for this batch
   }
+  __syncthreads();  // nobody still reads the old cursor
+  if (tid == 0) sh.cursor = t0;
+  __syncthreads();
   if (count_stats) {
     for (int o = 16; o > 0; o >>= 1) kcount += __shfl_xor_sync(AG2_FULL, kcount, o);
     if (lane == 0 && kcount) atomicAdd(&sh.sumK, (unsigned long long)kcount);
