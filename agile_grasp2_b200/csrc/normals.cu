@@ -220,7 +220,7 @@ __global__ void __launch_bounds__(256) k_eigen(GridDev g, const uint32_t* __rest
 //            computeMeanAndCovarianceMatrix over S in that order (sequential by
 //            definition) and store the raw sums; k_eigen (thread per point, one launch
 //            for the whole cloud) solves eigen33 and flips the normal.
-// Shared memory per warp is 20 B x cap + 1.3 KB, so the launch capacity decides the
+// Shared memory per warp is 16 B x cap + 1.3 KB, so the launch capacity decides the
 // occupancy: the host runs the bulk of the points at a small cap and hands the dense
 // ones (appended to big_list here) to further launches with larger caps.
 constexpr int kNB = 128;     // d2 buckets (4 per lane in the prefix)
@@ -231,8 +231,8 @@ struct NormalsSmem {  // per-warp carve-up (byte offsets, 16-aligned)
 __host__ __device__ inline NormalsSmem normals_smem(uint32_t cap) {
   NormalsSmem L;
   size_t o = 0;
-  L.a = o, o += (size_t)cap * 8;    // A: (d2 bits, j); later (rank, j)
-  L.s = o, o += (size_t)cap * 12;   // G: grouped (d2 bits, j) 8 B; later S: xyz 12 B
+  L.a = o, o += (size_t)cap * 8;    // A: (d2 bits, j); later J: positions in radiusSearch order | Z
+  L.s = o, o += (size_t)cap * 8;    // G: (d2 bits, j) grouped by bucket; later X | Y
   L.cnt = o, o += kNB * 4;
   L.start = o, o += (kNB + 4) * 4;
   L.rowb = o, o += 32 * 4;
@@ -269,7 +269,11 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   unsigned char* base = smem + (size_t)warp * L.total;
   uint2* A = (uint2*)(base + L.a);
   uint2* G = (uint2*)(base + L.s);
-  float* S = (float*)(base + L.s);
+  // after the ranking: J | Z reuse A's bytes, X | Y reuse G's (A and G are dead by then)
+  uint32_t* J = (uint32_t*)(base + L.a);
+  float* Zs = (float*)(base + L.a) + cap;
+  float* Xs = (float*)(base + L.s);
+  float* Ys = (float*)(base + L.s) + cap;
   uint32_t* cnt = (uint32_t*)(base + L.cnt);
   uint32_t* start = (uint32_t*)(base + L.start);
   uint32_t* rowb = (uint32_t*)(base + L.rowb);
@@ -404,7 +408,7 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
         G[atomicAdd(&cnt[d2_bucket(__uint_as_float(e.x), P.bscale)], 1u)] = e;
       }
       __syncwarp();
-      // ---- exact rank inside the bucket by (d2, input index); (rank, j) parked in A
+      // ---- exact rank inside the bucket by (d2, input index); j goes to J[rank]
       for (uint32_t t = lane; t < count; t += 32) {
         const uint2 e = G[t];
         const int b = d2_bucket(__uint_as_float(e.x), P.bscale);
@@ -418,31 +422,27 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
             if (__float_as_uint(g.pts[o.y].w) < __float_as_uint(g.pts[e.y].w)) rank++;
           }
         }
-        A[t] = make_uint2(rank, e.y);
+        J[rank] = e.y;
       }
       __syncwarp();
       for (uint32_t t = lane; t < count; t += 128) {  // four loads in flight per lane
-        uint2 rj[4];
         float4 p[4];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-          rj[u] = A[min(t + 32u * u, count - 1)];
-          p[u] = g.pts[rj[u].y];
-        }
+        for (int u = 0; u < 4; u++) p[u] = g.pts[J[min(t + 32u * u, count - 1)]];
 #pragma unroll
         for (int u = 0; u < 4; u++)
           if (t + 32u * u < count) {
-            S[rj[u].x] = p[u].x;  // SoA: X[cap] Y[cap] Z[cap]
-            S[cap + rj[u].x] = p[u].y;
-            S[2 * cap + rj[u].x] = p[u].z;
+            Xs[t + 32u * u] = p[u].x;
+            Ys[t + 32u * u] = p[u].y;
+            Zs[t + 32u * u] = p[u].z;
           }
       }
       __syncwarp();
       // ---- sequential single-pass float moments
       if (lane < 9) {
         // accu[6..8] += p.x : the second operand is the constant 1.0f, the product is exact
-        const float4* pa = (const float4*)(S + sa * cap);
-        const float4* pb = sb == 3 ? (const float4*)ones_s : (const float4*)(S + sb * cap);
+        const float4* pa = (const float4*)(sa == 0 ? Xs : (sa == 1 ? Ys : Zs));
+        const float4* pb = (const float4*)(sb == 3 ? ones_s : (sb == 0 ? Xs : (sb == 1 ? Ys : Zs)));
         const uint32_t step_b = sb == 3 ? 0u : 1u;
         float acc = 0.f;
         const uint32_t n4 = count >> 2;
