@@ -471,6 +471,208 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
 }
 
 // ---------------------------------------------------------------------------
+// k_normals_cta: one CTA (four warps) per point, for the DENSE tiers.  Same algorithm as k_normals
+// (flattened candidate sequence, ballot compaction, monotone d2 buckets, exact rank inside the
+// bucket, coordinates staged in search order, nine sequential accumulators on lanes 0..8 of warp 0),
+// but the 16 B x cap of shared memory now belong to 128 threads instead of 32: a neighbourhood of a
+// thousand points no longer leaves the SM with a handful of warps.  Points are claimed from a global
+// counter, the next one a point ahead.
+constexpr int kCtaThreads = 128;
+constexpr int kCtaNB = 512;  // d2 buckets
+
+struct CtaSmem {
+  size_t a, s, cnt, start, rowb, rowp, misc, total;
+};
+__host__ __device__ inline CtaSmem cta_smem(uint32_t cap) {
+  CtaSmem L;
+  size_t o = 0;
+  L.a = o, o += (size_t)cap * 8;   // A: (d2 bits, j); later J | Z
+  L.s = o, o += (size_t)cap * 8;   // G: bucket-grouped (d2 bits, j); later X | Y
+  L.cnt = o, o += kCtaNB * 4;
+  L.start = o, o += (kCtaNB + 4) * 4;
+  L.rowb = o, o += 32 * 4;
+  L.rowp = o, o += 36 * 4;
+  L.misc = o, o += 16 * 4;         // [0] hits so far, [1] T, [2] claimed point, [4..7] warp totals, [8..11] ones
+  L.total = (o + 15) & ~(size_t)15;
+  return L;
+}
+
+__global__ void __launch_bounds__(kCtaThreads) k_normals_cta(NormalsArgs P) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const GridDev& g = P.g;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t cap = P.cap;
+  const CtaSmem L = cta_smem(cap);
+  uint2* A = (uint2*)(smem + L.a);
+  uint2* G = (uint2*)(smem + L.s);
+  uint32_t* J = (uint32_t*)(smem + L.a);
+  float* Zs = (float*)(smem + L.a) + cap;
+  float* Xs = (float*)(smem + L.s);
+  float* Ys = (float*)(smem + L.s) + cap;
+  uint32_t* cnt = (uint32_t*)(smem + L.cnt);
+  uint32_t* start = (uint32_t*)(smem + L.start);
+  uint32_t* rowb = (uint32_t*)(smem + L.rowb);
+  uint32_t* rowp = (uint32_t*)(smem + L.rowp);
+  uint32_t* misc = (uint32_t*)(smem + L.misc);
+  float* ones_s = (float*)(misc + 8);
+  const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
+  const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
+  const float bscale = (float)kCtaNB / P.r2;
+  if (tid < 4) ones_s[tid] = 1.0f;
+  if (tid == 0) misc[2] = atomicAdd(P.batch_counter, 1u);
+  __syncthreads();
+  uint32_t item = misc[2];
+  while (item < P.n_items) {
+    __syncthreads();  // everyone has read misc[2]
+    if (tid == 0) misc[2] = atomicAdd(P.batch_counter, 1u);  // the next point, read at the end of this one
+    const uint32_t i = P.list[item];
+    const uint32_t count = P.kn[i];  // 3 <= count <= cap (tier list)
+    const float4 q = g.pts[i];
+    const QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
+    const int rows = w.rows();
+    for (int b = tid; b < kCtaNB; b += kCtaThreads) cnt[b] = 0;
+    if (tid == 0) misc[0] = 0;
+    // ---- gather
+    for (int r0 = 0; r0 < rows; r0 += 32) {
+      __syncthreads();  // rowb / rowp of the previous round are no longer read; counters zeroed
+      if (warp == 0) {
+        uint32_t rb = 0, rc = 0;
+        if (r0 + lane < rows) {
+          uint32_t b, e;
+          row_span_trim(g, w, r0 + lane, q.x, q.y, q.z, P.r2 * 1.002f, b, e);
+          rb = b, rc = e - b;
+        }
+        uint32_t incl = rc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          uint32_t t = __shfl_up_sync(AG2_FULL, incl, o);
+          if (lane >= o) incl += t;
+        }
+        rowb[lane] = rb;
+        rowp[lane] = incl - rc;
+        if (lane == 31) {
+          rowp[32] = incl;
+          misc[1] = incl;
+        }
+      }
+      __syncthreads();
+      const uint32_t T = misc[1];
+      int row = 0;
+      uint32_t row_lo = 0, row_hi = rowp[1], row_b = rowb[0];
+      for (uint32_t t0 = 0; t0 < T; t0 += kCtaThreads) {
+        const uint32_t t = t0 + tid;
+        bool hit = false;
+        float d2 = 0.f;
+        uint32_t j = 0;
+        if (t < T) {
+          while (t >= row_hi) {
+            row++;
+            row_lo = row_hi;
+            row_hi = rowp[row + 1];
+            row_b = rowb[row];
+          }
+          j = row_b + (t - row_lo);
+          const float4 p = g.pts[j];
+          d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
+          hit = d2 < P.r2;
+        }
+        const uint32_t ballot = __ballot_sync(AG2_FULL, hit);
+        uint32_t wbase = 0;
+        if (lane == 0 && ballot) wbase = atomicAdd(&misc[0], (uint32_t)__popc(ballot));
+        wbase = __shfl_sync(AG2_FULL, wbase, 0);
+        if (hit) {
+          const uint32_t slot = wbase + __popc(ballot & ((1u << lane) - 1));
+          if (slot < cap) A[slot] = make_uint2(__float_as_uint(d2), j);
+          atomicAdd(&cnt[min(kCtaNB - 1, (int)__fmul_rn(d2, bscale))], 1u);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- bucket starts: exclusive prefix over kCtaNB counters, four consecutive ones per thread
+    {
+      constexpr int per = kCtaNB / kCtaThreads;
+      uint32_t cl[per], sum = 0;
+#pragma unroll
+      for (int b = 0; b < per; b++) {
+        cl[b] = cnt[per * tid + b];
+        sum += cl[b];
+      }
+      uint32_t in2 = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(AG2_FULL, in2, o);
+        if (lane >= o) in2 += t;
+      }
+      if (lane == 31) misc[4 + warp] = in2;
+      __syncthreads();
+      uint32_t wofs = 0;
+      for (int k = 0; k < warp; k++) wofs += misc[4 + k];
+      uint32_t ex = wofs + in2 - sum;
+#pragma unroll
+      for (int b = 0; b < per; b++) {
+        start[per * tid + b] = ex;
+        cnt[per * tid + b] = ex;  // cursor
+        ex += cl[b];
+      }
+      if (tid == kCtaThreads - 1) start[kCtaNB] = ex;
+    }
+    __syncthreads();
+    // ---- group by bucket
+    for (uint32_t t = tid; t < count; t += kCtaThreads) {
+      const uint2 e = A[t];
+      G[atomicAdd(&cnt[min(kCtaNB - 1, (int)__fmul_rn(__uint_as_float(e.x), bscale))], 1u)] = e;
+    }
+    __syncthreads();
+    // ---- exact rank inside the bucket by (d2, input index); j goes to J[rank]
+    for (uint32_t t = tid; t < count; t += kCtaThreads) {
+      const uint2 e = G[t];
+      const int b = min(kCtaNB - 1, (int)__fmul_rn(__uint_as_float(e.x), bscale));
+      const uint32_t lo = start[b], hi = start[b + 1];
+      uint32_t rank = lo;
+      for (uint32_t u = lo; u < hi; u++) {
+        const uint2 o = G[u];
+        if (o.x < e.x) {
+          rank++;
+        } else if (o.x == e.x && u != t) {  // equal distances: FLANN orders by index
+          if (__float_as_uint(g.pts[o.y].w) < __float_as_uint(g.pts[e.y].w)) rank++;
+        }
+      }
+      J[rank] = e.y;
+    }
+    __syncthreads();
+    // ---- coordinates in search order
+    for (uint32_t t = tid; t < count; t += kCtaThreads) {
+      const float4 p = g.pts[J[t]];
+      Xs[t] = p.x;
+      Ys[t] = p.y;
+      Zs[t] = p.z;
+    }
+    __syncthreads();
+    // ---- sequential single-pass float moments (warp 0, lanes 0..8)
+    if (tid < 9) {
+      const float4* pa = (const float4*)(sa == 0 ? Xs : (sa == 1 ? Ys : Zs));
+      const float4* pb = (const float4*)(sb == 3 ? ones_s : (sb == 0 ? Xs : (sb == 1 ? Ys : Zs)));
+      const uint32_t step_b = sb == 3 ? 0u : 1u;
+      float acc = 0.f;
+      const uint32_t n4 = count >> 2;
+      for (uint32_t t = 0; t < n4; t++) {
+        const float4 va = pa[t], vb = pb[step_b * t];
+        acc = __fadd_rn(acc, __fmul_rn(va.x, vb.x));
+        acc = __fadd_rn(acc, __fmul_rn(va.y, vb.y));
+        acc = __fadd_rn(acc, __fmul_rn(va.z, vb.z));
+        acc = __fadd_rn(acc, __fmul_rn(va.w, vb.w));
+      }
+      const float* ra = (const float*)pa;
+      const float* rb_ = (const float*)pb;
+      for (uint32_t t = n4 << 2; t < count; t++) acc = __fadd_rn(acc, __fmul_rn(ra[t], rb_[step_b * t]));
+      P.mom_out[(size_t)i * kMomWords + tid] = acc;
+    }
+    __syncthreads();
+    item = misc[2];
+  }
+}
+
+// ---------------------------------------------------------------------------
 // Tiered path.  The count pass groups the points by neighbourhood size into tiers; every
 // non-empty tier is ONE launch sized for exactly that capacity, and the launches are
 // independent, so they run side by side on the ctx's auxiliary streams.
@@ -754,6 +956,30 @@ static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_
   return AG2_OK;
 }
 
+// CTA-per-point launch over one tier list at capacity `cap` (dense tiers).
+static int launch_normals_cta(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list,
+                              uint32_t* counter) {
+  const CtaSmem L = cta_smem(cap);
+  AG2_CUDA(c, cudaFuncSetAttribute(k_normals_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(16, (226 * 1024) / (L.total + 1024)));
+  NormalsArgs P;
+  P.g = grid_dev(c);
+  P.r2 = c->hc.r2_normals, P.rq = c->hc.rq_normals;
+  P.bscale = 0.f;
+  P.kn = c->kn.p;
+  P.n_items = n_items, P.cap = cap, P.bsz = 1;
+  P.shard_rank = 0, P.shard_world = 1;
+  P.list = list;
+  P.big_list = nullptr, P.big_count = nullptr, P.big_cap = 0;
+  P.batch_counter = counter;
+  P.mom_out = c->nrm_mom.p;
+  P.nrm_out = c->nrm.p;
+  const uint32_t grid = (uint32_t)std::min<size_t>(n_items, (size_t)c->sm_count * per_sm);
+  k_normals_cta<<<grid, kCtaThreads, L.total, st>>>(P);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
 // number of points rank `rank` of `world` owns among n cell-sorted points (see shard_point)
 uint32_t normals_shard_points(uint32_t n, int rank, int world) {
   const uint32_t G = (n + 31) / 32;
@@ -827,6 +1053,9 @@ static int normals_compute_tiered(ag2_ctx* c) {
   if (const char* e = getenv("AG2_NORMALS_QUAD_TIERS")) quad_tiers = (uint32_t)std::min(kQuadTiers, std::max(0, atoi(e)));
   // A lone k_normals_quad launch cannot finish faster than one group's chain of dependent accesses
   // (~130 us); a short list is better off on k_normals, whose floor is a tenth of that.
+  // dense tiers (capacity 512 and up by default) run one CTA per point; AG2_NORMALS_CTA_FROM = first such tier
+  int cta_from = 10;
+  if (const char* e = getenv("AG2_NORMALS_CTA_FROM")) cta_from = std::max(0, atoi(e));
   uint32_t quad_min = 8192;
   if (const char* e = getenv("AG2_NORMALS_QUAD_MIN")) quad_min = (uint32_t)std::max(0, atoi(e));
   AG2_CUDA(c, c->kn.reserve(n));
@@ -866,6 +1095,9 @@ static int normals_compute_tiered(ag2_ctx* c) {
     const uint32_t* list = c->tier_list.p + (size_t)tier * owned;
     if (tier < (int)quad_tiers && cnt[tier] >= quad_min) {
       AG2_TRY(launch_normals_quad(c, s2, cnt[tier], kTierCapHost[tier], list));
+    } else if (tier >= cta_from) {
+      AG2_TRY(launch_normals_cta(c, s2, cnt[tier], std::min(kTierCapHost[tier], cap_max), list,
+                                 c->tier_cnt.p + 16 + tier));
     } else {
       const uint32_t cap = std::min(kTierCapHost[tier], cap_max);
       AG2_TRY(launch_normals(c, s2, cnt[tier], cap, list, c->tier_cnt.p + 30, c->tier_cnt.p + 31, 0,

@@ -476,15 +476,19 @@ def _lattice_scene():
 
 
 @pytest.mark.parametrize("scene,quad_tiers", [("tiny", None), ("tiny", "8"), ("tiny", "0"), ("lattice", "8"),
-                                              ("lattice", None)])
+                                              ("lattice", None), ("tiny", "cta"), ("lattice", "cta")])
 def test_normals_quad_per_point_and_warp_per_point_agree(tiny_scene, monkeypatch, scene, quad_tiers):
     """Points are grouped by neighbourhood size into tiers, one launch per tier, side by side. Sparse tiers
     run four lanes per point (k_normals_quad; up to 208 neighbours when AG2_NORMALS_QUAD_TIERS=8), the
-    others one warp per point (k_normals); AG2_NORMALS_WARP=1 runs k_normals everywhere in chained
-    capacity levels. All reproduce the radius-search order exactly, so the normals are bit-identical --
+    dense ones (capacity 512 and up; every tier with AG2_NORMALS_CTA_FROM=0) one CTA per point
+    (k_normals_cta), the others one warp per point (k_normals); AG2_NORMALS_WARP=1 runs k_normals
+    everywhere in chained capacity levels. All reproduce the radius-search order exactly, so the normals are bit-identical --
     and equal to the oracle's."""
     sc = _lattice_scene() if scene == "lattice" else tiny_scene
-    if quad_tiers is not None:
+    if quad_tiers == "cta":  # every tier on the CTA-per-point kernel of the dense tiers
+        monkeypatch.setenv("AG2_NORMALS_QUAD_TIERS", "0")
+        monkeypatch.setenv("AG2_NORMALS_CTA_FROM", "0")
+    elif quad_tiers is not None:
         monkeypatch.setenv("AG2_NORMALS_QUAD_TIERS", quad_tiers)
     monkeypatch.setenv("AG2_NORMALS_FIRST_TIER", "0")  # forced run: first level capacity 64
     p = make_params(capi.MODE_GEOMETRIC)
