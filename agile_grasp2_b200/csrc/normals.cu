@@ -741,10 +741,10 @@ __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float 
 }
 
 // k_normals_quad: FOUR lanes per point, eight points per warp.  The four lanes share one
-// shared-memory neighbour list; nothing crosses a group, so all synchronisation is on the
-// group's own four-lane mask and groups of a warp drift apart freely.
-//   gather   the group walks the point's cell rows four candidates at a time (float d2, strict <);
-//            hits are compacted with a group ballot and appended as 32-bit keys (q << jbits) | j,
+// shared-memory neighbour list; no data crosses a group.
+//   gather   the group's cell rows (trimmed by its four lanes, four rows each) are flattened into one
+//            candidate sequence and walked four at a time (float d2, strict <); hits are compacted
+//            with the group's four bits of a warp ballot and appended as 32-bit keys (q << jbits) | j,
 //            j = cell-sorted position (jbits = bits of n), q = a monotone quantisation of d2 on
 //            the remaining bits;
 //   order    counting sort on the top five key bits into a byte permutation (shared atomics);
@@ -769,42 +769,83 @@ struct QuadArgs {
   float* mom_out;
 };
 
-__host__ __device__ inline size_t quad_smem_per_warp(uint32_t cap) { return (size_t)cap * 40 + 1024; }
+__host__ __device__ inline size_t quad_smem_per_warp(uint32_t cap) { return (size_t)cap * 40 + 1024 + 1088; }
 
 __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
   extern __shared__ __align__(16) unsigned char smem[];
   const GridDev& g = P.g;
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, sub = lane & 3;
-  const uint32_t gshift = grp * 4, gmask = 0xFu << gshift;
+  const uint32_t gshift = grp * 4;
   const uint32_t cap = P.cap;
   unsigned char* base = smem + (size_t)warp * quad_smem_per_warp(cap);
   uint32_t* L = (uint32_t*)base + grp;                      // L[t * 8]
   uint8_t* ord = base + (size_t)cap * 32 + grp;             // ord[t * 8]
   uint32_t* cur = (uint32_t*)(base + (size_t)cap * 40) + grp;  // cur[b * 8], 32 buckets
-  const uint32_t item = (blockIdx.x * kQuadThreads + threadIdx.x) >> 2;
-  if (item >= P.n_items) return;  // whole groups leave together
+  uint32_t* rowb = (uint32_t*)(base + (size_t)cap * 40 + 1024) + grp;  // rowb[r * 8], 16 rows: first position
+  uint32_t* rowp = rowb + 16 * 8;                                      // rowp[r * 8], 17 entries: candidate prefix
+  // No lane leaves early, so every warp-wide primitive below runs on the full mask: a sub-warp mask that
+  // differs between the groups makes the hardware issue the primitive once per group.  Groups past the end of
+  // the list redo its last point (same values written twice).
+  const uint32_t item = min((blockIdx.x * kQuadThreads + threadIdx.x) >> 2, P.n_items - 1);
   const uint32_t i = P.list[item];
   const float4 q = g.pts[i];  // 3 <= kn[i] <= cap: the tier list holds nothing else
   const uint32_t jbits = P.jbits, jmask = (1u << jbits) - 1u;
   const float r2 = P.r2;
-  // ---- gather
+  // ---- gather: the group's candidate rows flattened into one sequence, four candidates per step; the step
+  //      count is the warp's maximum so that the ballot is warp-uniform
   uint32_t n = 0;
   {
     const QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
     const int rows = w.rows();
-    for (int row = 0; row < rows; row++) {
-      uint32_t b, e;
-      row_span_trim(g, w, row, q.x, q.y, q.z, r2 * 1.002f, b, e);
-      for (uint32_t j0 = b; j0 < e; j0 += 4) {
-        const uint32_t j = j0 + sub;
+    int rows_max = rows;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rows_max = max(rows_max, __shfl_xor_sync(AG2_FULL, rows_max, o));
+    for (int r0 = 0; r0 < rows_max; r0 += 16) {
+      __syncwarp();  // the previous table is no longer read
+#pragma unroll
+      for (int k = 0; k < 4; k++) {  // each lane trims four of the sixteen rows
+        const int r = (int)sub + 4 * k;
+        uint32_t b = 0, e = 0;
+        if (r0 + r < rows) row_span_trim(g, w, r0 + r, q.x, q.y, q.z, r2 * 1.002f, b, e);
+        rowb[r * 8] = b;
+        rowp[r * 8] = e - b;
+      }
+      __syncwarp();
+      if (sub == 0) {
+        uint32_t run = 0;
+#pragma unroll
+        for (int r = 0; r < 16; r++) {
+          const uint32_t c = rowp[r * 8];
+          rowp[r * 8] = run;
+          run += c;
+        }
+        rowp[16 * 8] = run;
+      }
+      __syncwarp();
+      const uint32_t T = rowp[16 * 8];
+      uint32_t T_max = T;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) T_max = max(T_max, __shfl_xor_sync(AG2_FULL, T_max, o));
+      int row = 0;
+      uint32_t row_lo = 0, row_hi = rowp[8], row_b = rowb[0];
+      for (uint32_t t0 = 0; t0 < T_max; t0 += 4) {
+        const uint32_t t = t0 + sub;
         bool hit = false;
         float d2 = 0.f;
-        if (j < e) {
+        uint32_t j = 0;
+        if (t < T) {
+          while (t >= row_hi) {
+            row++;
+            row_lo = row_hi;
+            row_hi = rowp[(row + 1) * 8];
+            row_b = rowb[row * 8];
+          }
+          j = row_b + (t - row_lo);
           const float4 p = g.pts[j];
           d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
           hit = d2 < r2;
         }
-        const uint32_t bits = (__ballot_sync(gmask, hit) >> gshift) & 0xFu;
+        const uint32_t bits = (__ballot_sync(AG2_FULL, hit) >> gshift) & 0xFu;
         if (hit) {
           const uint32_t qv = min(P.qmax, (uint32_t)__fmul_rn(d2, P.qscale));  // monotone in d2
           const uint32_t pos = n + __popc(bits & ((1u << sub) - 1u));
@@ -818,9 +859,9 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
   // ---- counting sort on the top five bits -> byte permutation grouped by bucket
 #pragma unroll
   for (int k = 0; k < 8; k++) cur[(sub * 8 + k) * 8] = 0;
-  __syncwarp(gmask);
+  __syncwarp();
   for (uint32_t t = sub; t < n; t += 4) atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
-  __syncwarp(gmask);
+  __syncwarp();
   uint32_t lo, hi;  // this lane's buckets sub*8 .. sub*8+7 occupy ord[lo, hi)
   {
     uint32_t c8[8], tot = 0;
@@ -830,9 +871,9 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
       tot += c8[k];
     }
     uint32_t incl = tot;
-    uint32_t up = __shfl_up_sync(gmask, incl, 1, 4);
+    uint32_t up = __shfl_up_sync(AG2_FULL, incl, 1, 4);
     if (sub >= 1) incl += up;
-    up = __shfl_up_sync(gmask, incl, 2, 4);
+    up = __shfl_up_sync(AG2_FULL, incl, 2, 4);
     if (sub >= 2) incl += up;
     lo = incl - tot, hi = incl;
     uint32_t run = lo;
@@ -842,12 +883,12 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
       run += c8[k];
     }
   }
-  __syncwarp(gmask);
+  __syncwarp();
   for (uint32_t t = sub; t < n; t += 4) {
     const uint32_t pos = atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
     ord[pos * 8] = (uint8_t)t;
   }
-  __syncwarp(gmask);
+  __syncwarp();
   // ---- insertion sort of the lane's segment (elements never leave their bucket); `top` is the
   //      last key of the sorted prefix, so an element already in place costs one comparison
   auto before = [&](uint32_t ka, uint32_t kb) -> bool {  // does ka precede kb in radiusSearch order?
@@ -877,7 +918,7 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
       ord[u * 8] = (uint8_t)o;
     }
   }
-  __syncwarp(gmask);
+  __syncwarp();
   // ---- sequential single-pass float moments (accu[0..8] of computeMeanAndCovarianceMatrix):
   //      lane 0: xx xy xz, lane 1: yy yz zz, lane 2: x y z (times the constant 1, exact)
   float a0 = 0.f, a1 = 0.f, a2 = 0.f;
