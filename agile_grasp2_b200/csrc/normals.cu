@@ -286,12 +286,18 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   if (threadIdx.x < 4) ones_s[threadIdx.x] = 1.0f;
   __syncthreads();
 
-  uint32_t batch = 0;
-  if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
-  batch = __shfl_sync(AG2_FULL, batch, 0);
+  // Batches of one point (short tier lists) are dealt out round-robin, no counter; larger batches are claimed
+  // from the global counter, the following one a batch ahead so that the atomic's round trip hides behind this one.
+  const bool dealt = bsz == 1;
+  const uint32_t warp_id = blockIdx.x * (blockDim.x >> 5) + warp, n_warps = gridDim.x * (blockDim.x >> 5);
+  uint32_t batch = warp_id;
+  if (!dealt) {
+    if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
+    batch = __shfl_sync(AG2_FULL, batch, 0);
+  }
   while (batch < n_batches) {
-    uint32_t next = 0;  // the following batch is claimed now, so the atomic's round trip hides behind this one
-    if (lane == 0) next = atomicAdd(P.batch_counter, 1u);
+    uint32_t next = batch + n_warps;
+    if (!dealt && lane == 0) next = atomicAdd(P.batch_counter, 1u);
     const uint32_t i0 = batch * bsz;
     const uint32_t nb = min(bsz, P.n_items - i0);
     const uint32_t my_i =
@@ -403,9 +409,18 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
       }
       __syncwarp();
       // ---- group by bucket
-      for (uint32_t t = lane; t < count; t += 32) {
-        uint2 e = A[t];
-        G[atomicAdd(&cnt[d2_bucket(__uint_as_float(e.x), P.bscale)], 1u)] = e;
+      for (uint32_t t = lane; t < count; t += 128) {  // four shared atomics in flight per lane
+        uint2 e[4];
+        uint32_t slot[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          e[u] = A[min(t + 32u * u, count - 1)];
+          slot[u] = 0;
+          if (t + 32u * u < count) slot[u] = atomicAdd(&cnt[d2_bucket(__uint_as_float(e[u].x), P.bscale)], 1u);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+          if (t + 32u * u < count) G[slot[u]] = e[u];
       }
       __syncwarp();
       // ---- exact rank inside the bucket by (d2, input index); j goes to J[rank]
