@@ -286,17 +286,21 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   if (threadIdx.x < 4) ones_s[threadIdx.x] = 1.0f;
   __syncthreads();
 
-  // Batches of one point (short tier lists) are dealt out round-robin, no counter; larger batches are claimed
-  // from the global counter, the following one a batch ahead so that the atomic's round trip hides behind this one.
+  // Batches of one point (short tier lists) are dealt out without a counter, every warp a contiguous run of the
+  // list -- consecutive entries are neighbours in space, so the run re-reads what L1 already holds; larger
+  // batches are claimed from the global counter, the following one a batch ahead so that the atomic's round trip
+  // hides behind this one.
   const bool dealt = bsz == 1;
   const uint32_t warp_id = blockIdx.x * (blockDim.x >> 5) + warp, n_warps = gridDim.x * (blockDim.x >> 5);
-  uint32_t batch = warp_id;
+  const uint32_t run = (n_batches + n_warps - 1) / n_warps;
+  uint32_t batch = warp_id * run;
+  const uint32_t batch_end = dealt ? min(n_batches, batch + run) : n_batches;
   if (!dealt) {
     if (lane == 0) batch = atomicAdd(P.batch_counter, 1u);
     batch = __shfl_sync(AG2_FULL, batch, 0);
   }
-  while (batch < n_batches) {
-    uint32_t next = batch + n_warps;
+  while (batch < batch_end) {
+    uint32_t next = batch + 1;
     if (!dealt && lane == 0) next = atomicAdd(P.batch_counter, 1u);
     const uint32_t i0 = batch * bsz;
     const uint32_t nb = min(bsz, P.n_items - i0);
