@@ -189,8 +189,8 @@ constexpr int kMomWords = 12;
 __global__ void __launch_bounds__(256) k_eigen(GridDev g, const uint32_t* __restrict__ kn,
                                                const float* __restrict__ mom, float4* __restrict__ nrm_out,
                                                uint32_t shard_rank, uint32_t shard_world) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= (uint32_t)g.n || (i >> 5) % shard_world != shard_rank) return;
+  const uint32_t i = shard_point(blockIdx.x * blockDim.x + threadIdx.x, shard_rank, shard_world);
+  if (i >= (uint32_t)g.n) return;
   const uint32_t count = kn[i];
   if (count < 3) return;  // NaN already written
   const float4* m4 = reinterpret_cast<const float4*>(mom + (size_t)i * kMomWords);
@@ -712,9 +712,10 @@ __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float 
                                                      uint32_t* __restrict__ tier_count, uint32_t* __restrict__ tier_list,
                                                      uint32_t stride, float4* __restrict__ nrm_out,
                                                      uint32_t shard_rank, uint32_t shard_world) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  // thread t of the launch = the t-th point this rank owns (whole warps of work at any world size)
+  const uint32_t i = shard_point(blockIdx.x * blockDim.x + threadIdx.x, shard_rank, shard_world);
   const uint32_t lane = threadIdx.x & 31;
-  const bool owned = i < (uint32_t)g.n && (i >> 5) % shard_world == shard_rank;
+  const bool owned = i < (uint32_t)g.n;
   uint32_t cnt = 0;
   if (owned) {
     const float4 q = g.pts[i];
@@ -1124,7 +1125,7 @@ static int normals_compute_tiered(ag2_ctx* c) {
   AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, 32 * 4, st));
-  k_count_tiers<<<(n + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
+  k_count_tiers<<<(((owned + 31) & ~31u) + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
                                                  (unsigned long long*)(c->scalars.p + 10), c->tier_cnt.p,
                                                  c->tier_list.p, owned, c->nrm.p, (uint32_t)c->nrm_rank,
                                                  (uint32_t)c->nrm_world);
@@ -1168,8 +1169,8 @@ static int normals_compute_tiered(ag2_ctx* c) {
     AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
     AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
   }
-  k_eigen<<<(n + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p, (uint32_t)c->nrm_rank,
-                                           (uint32_t)c->nrm_world);
+  k_eigen<<<(((owned + 31) & ~31u) + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
+                                                               (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }
@@ -1239,9 +1240,12 @@ int normals_compute(ag2_ctx* c) {
     remaining = left;
     level++;
   }
-  k_eigen<<<(n + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p, (uint32_t)c->nrm_rank,
-                                           (uint32_t)c->nrm_world);
-  AG2_LAUNCH_CHECK(c);
+  {
+    const uint32_t own = normals_shard_points(n, c->nrm_rank, c->nrm_world);
+    k_eigen<<<(((own + 31) & ~31u) + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
+                                                               (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
+    AG2_LAUNCH_CHECK(c);
+  }
   c->have_normals = true;
   phase_end(c, 1);
   return AG2_OK;
