@@ -1125,7 +1125,7 @@ static int normals_compute_tiered(ag2_ctx* c) {
   AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, 32 * 4, st));
-  k_count_tiers<<<(((owned + 31) & ~31u) + 127) / 128, 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
+  k_count_tiers<<<std::max(1u, (((owned + 31) & ~31u) + 127) / 128), 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
                                                  (unsigned long long*)(c->scalars.p + 10), c->tier_cnt.p,
                                                  c->tier_list.p, owned, c->nrm.p, (uint32_t)c->nrm_rank,
                                                  (uint32_t)c->nrm_world);
@@ -1169,7 +1169,7 @@ static int normals_compute_tiered(ag2_ctx* c) {
     AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
     AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
   }
-  k_eigen<<<(((owned + 31) & ~31u) + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
+  k_eigen<<<std::max(1u, (((owned + 31) & ~31u) + 255) / 256), 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
                                                                (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
@@ -1242,7 +1242,7 @@ int normals_compute(ag2_ctx* c) {
   }
   {
     const uint32_t own = normals_shard_points(n, c->nrm_rank, c->nrm_world);
-    k_eigen<<<(((own + 31) & ~31u) + 255) / 256, 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
+    k_eigen<<<std::max(1u, (((own + 31) & ~31u) + 255) / 256), 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
                                                                (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
     AG2_LAUNCH_CHECK(c);
   }
