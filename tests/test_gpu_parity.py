@@ -444,6 +444,25 @@ def test_normals_shards_assemble_to_the_full_result(tiny_scene, world):
     assert a.hypotheses(capi.LIST_SELECTED).tobytes() == b.hypotheses(capi.LIST_SELECTED).tobytes()
 
 
+def test_normals_shards_of_a_cloud_smaller_than_the_world(tiny_scene):
+    """70 points are three 32-point granules: at world 8 the ranks 3..7 own nothing and must still go through
+    the count pass and the per-tier launches; the assembled normals equal the single-GPU ones (most are NaN:
+    so few points rarely have three neighbours within the radius)."""
+    import torch
+    xyz = np.ascontiguousarray(tiny_scene["xyz"][:70])
+    p = make_params(capi.MODE_GEOMETRIC)
+    a, b = capi.Context(p), capi.Context(p)
+    for c in (a, b):
+        c.set_cloud(xyz, np.ones(70, np.uint8), 1)
+    a.compute_normals()
+    cap = b.normals_shard_points(8)
+    allb = torch.full((8, cap, 4), float("nan"), dtype=torch.float32, device="cuda")
+    owned = [b.compute_normals_shard(r, 8, allb[r].data_ptr(), cap) for r in range(8)]
+    assert owned == [32, 32, 6, 0, 0, 0, 0, 0]
+    b.set_normals_shards(allb.data_ptr(), cap, 8)
+    assert a.normals().tobytes() == b.normals().tobytes()
+
+
 @pytest.mark.parametrize("aligns", [False, True])
 def test_render_point_sets_vs_oracle(aligns):
     """Learning::createGraspImage(points, normals, grasp) (the ClassificationNode image generator): explicit
