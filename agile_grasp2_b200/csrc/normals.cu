@@ -946,12 +946,11 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
 #pragma unroll 4
     for (uint32_t t = 0; t < n; t++) {
       const float4 p = g.pts[L[(uint32_t)ord[t * 8] * 8] & jmask];
-      const float A0 = sub == 1 ? p.y : p.x, B0 = sub == 0 ? p.x : (sub == 1 ? p.y : 1.0f);
-      const float A1 = sub == 0 ? p.x : p.y, B1 = sub == 0 ? p.y : (sub == 1 ? p.z : 1.0f);
-      const float A2 = sub == 0 ? p.x : p.z, B2 = sub == 2 ? 1.0f : p.z;
-      a0 = __fadd_rn(a0, __fmul_rn(A0, B0));
-      a1 = __fadd_rn(a1, __fmul_rn(A1, B1));
-      a2 = __fadd_rn(a2, __fmul_rn(A2, B2));
+      // m = x | y | 1 by lane; products m*(x,y,z), except lane 1: y*y, y*z, z*z (five selects instead of eight)
+      const float m = sub == 0 ? p.x : (sub == 1 ? p.y : 1.0f);
+      a0 = __fadd_rn(a0, __fmul_rn(m, sub == 1 ? p.y : p.x));
+      a1 = __fadd_rn(a1, __fmul_rn(m, sub == 1 ? p.z : p.y));
+      a2 = __fadd_rn(a2, __fmul_rn(sub == 1 ? p.z : m, p.z));
     }
   }
   if (sub < 3) {
