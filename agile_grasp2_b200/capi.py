@@ -503,6 +503,12 @@ class Context:
         if not self.is_oracle:
             self._call("synchronize")
 
+    def measure_fp_peaks(self):
+        """(fp32, fp64) FMA throughput of this ctx's GPU in TFLOP/s (ag2_measure_fp_peaks)."""
+        a, b = C.c_double(), C.c_double()
+        self._call("measure_fp_peaks", C.byref(a), C.byref(b))
+        return float(a.value), float(b.value)
+
     def stream(self) -> int:
         h = C.c_void_p()
         self._call("get_stream", C.byref(h))
@@ -595,3 +601,166 @@ class Context:
         out = np.zeros((images.shape[0], 2), dtype=np.float32)
         self._call("classify_images", _fptr(images), C.c_size_t(images.shape[0]), _fptr(out))
         return out
+
+
+class _BorrowedContext(Context):
+    """An ag2_ctx owned by a Group (weights, statistics, stream); closing it does nothing."""
+
+    def __init__(self, handle, params: Params, api: Api):
+        self.api = api
+        self.is_oracle = False
+        self._h = handle
+        self.params = params.copy()
+        self.n_points = 0
+        self.n_samples = 0
+
+    def close(self):
+        self._h = C.c_void_p()
+
+
+class GroupId(C.Structure):
+    """ag2_group_id: an ncclUniqueId, created on rank 0 and handed to the other ranks by the caller."""
+
+    _fields_ = [("bytes", C.c_ubyte * 128)]
+
+
+def group_unique_id() -> bytes:
+    gid = GroupId()
+    rc = load().fn("group_unique_id")(C.byref(gid))
+    if rc:
+        raise Ag2Error(rc, "ag2_group_unique_id")
+    return bytes(gid.bytes)
+
+
+class Group:
+    """ag2_group: the path over several GPUs behind the C ABI (csrc/group.cu).
+
+    Group(params, n_gpus=N)                      one process, N host threads inside the library
+    Group(params, uid=..., rank=r, world=w, device=d)   one process per rank (torchrun); collective
+    """
+
+    def __init__(self, params: Params, n_gpus: int = 0, uid: Optional[bytes] = None, rank: int = 0, world: int = 1,
+                 device: int = 0):
+        self.api = load()
+        self._h = C.c_void_p()
+        self.params = params.copy()
+        if n_gpus:
+            rc = self.api.fn("group_create")(C.byref(self.params), C.c_int(n_gpus), C.byref(self._h))
+            self.rank, self.world = 0, n_gpus
+        else:
+            gid = GroupId()
+            if uid is not None:
+                C.memmove(C.byref(gid), uid, min(len(uid), 128))
+            rc = self.api.fn("group_create_rank")(C.byref(self.params), C.byref(gid) if world > 1 else None,
+                                                  C.c_int(rank), C.c_int(world), C.c_int(device), C.byref(self._h))
+            self.rank, self.world = rank, world
+        if rc:
+            raise Ag2Error(rc, "ag2_group_create")
+        w, nl = C.c_int(), C.c_int()
+        self.api.fn("group_size")(self._h, C.byref(w), C.byref(nl))
+        self.n_local = int(nl.value)
+        self._out = None
+
+    def close(self):
+        if self._h:
+            self.api.fn("group_destroy")(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int, what: str):
+        if rc:
+            f = self.api.lib.ag2_group_last_error
+            f.restype = C.c_char_p
+            raise Ag2Error(rc, what, (f(self._h) or b"").decode())
+
+    def local_ctx(self, i: int = 0) -> Context:
+        h = C.c_void_p()
+        self._check(self.api.fn("group_local_ctx")(self._h, C.c_int(i), C.byref(h)), "ag2_group_local_ctx")
+        return _BorrowedContext(h, self.params, self.api)
+
+    def init_lenet_xavier(self, seed: int):
+        for i in range(self.n_local):
+            self.local_ctx(i).init_lenet_xavier(seed)
+
+    def set_lenet_weights(self, weights: dict):
+        for i in range(self.n_local):
+            self.local_ctx(i).set_lenet_weights(weights)
+
+    def peer_stores(self) -> bool:
+        v = C.c_int()
+        self._check(self.api.fn("group_transport")(self._h, C.byref(v)), "ag2_group_transport")
+        return bool(v.value)
+
+    def _result_buffer(self, cap: int) -> np.ndarray:
+        if self._out is None or len(self._out) < cap:
+            self._out = np.zeros(max(cap, 1), dtype=HYPOTHESIS_DTYPE)
+        return self._out
+
+    def _cap(self, n_samples: int, rounds: int = 0, per_round: int = 0) -> int:
+        p = self.params
+        if p.num_selected > 0 and p.antipodal_mode != MODE_NONE:
+            return int(p.num_selected) * (rounds + 1)
+        return (n_samples + rounds * per_round) * int(p.num_orientations)
+
+    def detect_ptr(self, xyz_ptr: int, n: int, cam_ptr: int, num_cams: int, smp_ptr: int, n_samples: int,
+                   on_device: bool) -> np.ndarray:
+        """Raw-pointer form (host pointers, or device pointers on rank 0's GPU); pointers are read on rank 0 only."""
+        out = self._result_buffer(self._cap(n_samples))
+        got = C.c_size_t()
+        rc = self.api.fn("group_detect")(self._h, C.c_void_p(xyz_ptr or None), C.c_size_t(n), C.c_void_p(cam_ptr or None),
+                                         C.c_int(num_cams), C.c_void_p(smp_ptr or None), C.c_size_t(n_samples),
+                                         C.c_int(int(on_device)), _fptr(out), C.c_size_t(len(out)), C.byref(got))
+        self._check(rc, "ag2_group_detect")
+        return out[: int(got.value)].copy()
+
+    def io_bytes(self):
+        """(host->device, device->host) bytes the first local rank moved in the last call."""
+        a, b = C.c_size_t(), C.c_size_t()
+        self._check(self.api.fn("group_io_bytes")(self._h, C.byref(a), C.byref(b)), "ag2_group_io_bytes")
+        return int(a.value), int(b.value)
+
+    def detect_importance_ptr(self, xyz_ptr: int, n: int, cam_ptr: int, num_cams: int, smp_ptr: int, n_samples: int,
+                              on_device: bool, ip: IsParams) -> np.ndarray:
+        out = self._result_buffer(self._cap(int(n_samples), int(ip.num_iterations), int(ip.num_samples)))
+        got = C.c_size_t()
+        rc = self.api.fn("group_detect_importance")(
+            self._h, C.c_void_p(xyz_ptr or None), C.c_size_t(int(n)), C.c_void_p(cam_ptr or None), C.c_int(num_cams),
+            C.c_void_p(smp_ptr or None), C.c_size_t(int(n_samples)), C.c_int(int(on_device)), C.byref(ip), _fptr(out),
+            C.c_size_t(len(out)), C.byref(got))
+        self._check(rc, "ag2_group_detect_importance")
+        return out[: int(got.value)].copy()
+
+    def detect(self, xyz, cam_mask, num_cams: int, samples, n: Optional[int] = None, n_samples: Optional[int] = None):
+        """numpy inputs on rank 0 (None elsewhere, with n / n_samples given)."""
+        if xyz is not None:
+            xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
+            cam = None if cam_mask is None else np.ascontiguousarray(cam_mask, dtype=np.uint8)
+            smp = np.ascontiguousarray(samples, dtype=np.int32)
+            self._keep = (xyz, cam, smp)
+            return self.detect_ptr(xyz.ctypes.data, len(xyz), 0 if cam is None else cam.ctypes.data, num_cams,
+                                   smp.ctypes.data, len(smp), False)
+        return self.detect_ptr(0, int(n), 0, num_cams, 0, int(n_samples), False)
+
+    def detect_importance(self, xyz, cam_mask, num_cams: int, samples, ip: IsParams, n: Optional[int] = None,
+                          n_samples: Optional[int] = None) -> np.ndarray:
+        if xyz is not None:
+            xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
+            cam = None if cam_mask is None else np.ascontiguousarray(cam_mask, dtype=np.uint8)
+            smp = np.ascontiguousarray(samples, dtype=np.int32)
+            n, n_samples = len(xyz), len(smp)
+            ptrs = (xyz.ctypes.data, 0 if cam is None else cam.ctypes.data, smp.ctypes.data)
+        else:
+            ptrs = (0, 0, 0)
+        self._keep = (xyz, cam_mask, samples)
+        return self.detect_importance_ptr(ptrs[0], int(n), ptrs[1], num_cams, ptrs[2], int(n_samples), False, ip)

@@ -18,18 +18,28 @@ template <typename T>
 struct DevBuf {
   T* p = nullptr;
   size_t cap = 0;  // elements
+  bool external = false;  // storage belongs to someone else (a multi-GPU exchange window, group.cu)
   DevBuf() = default;
   DevBuf(const DevBuf&) = delete;
   DevBuf& operator=(const DevBuf&) = delete;
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p && !external) cudaFree(p);
     p = nullptr;
     cap = 0;
+    external = false;
+  }
+  // Uses caller-owned storage of `n` elements instead of an allocation of its own (never freed here).
+  void adopt(T* ptr, size_t n) {
+    release();
+    p = ptr;
+    cap = n;
+    external = ptr != nullptr;
   }
   // Grows (never shrinks); contents are NOT preserved.
   cudaError_t reserve(size_t n) {
     if (n <= cap) return cudaSuccess;
+    if (external) return cudaErrorMemoryAllocation;  // the owner sizes external storage
     release();
     size_t want = n + n / 8 + 64;
     cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
@@ -127,6 +137,16 @@ struct ag2_ctx {
   bool normals_given = false;
   bool have_normals = false;       // sorted normals complete for all points
   int nrm_rank = 0, nrm_world = 1; // normals_compute covers the granules of this shard only (multi-GPU)
+  // multi-GPU (group.cu): k_eigen stores every finished normal of this rank's granules into the sorted
+  // normals of ALL ranks through peer-mapped pointers; 0 peers = single GPU, store into c->nrm only
+  float4* nrm_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int nrm_peers = 0;
+  // deferred read-backs: small device scalars copied to pinned host memory by asynchronous copies and
+  // folded into the statistics (and checked for capacity errors) after the next synchronisation of the
+  // ctx stream (finish_pending) -- a stage that only needs a number for its statistics does not stall
+  uint32_t* h_pin = nullptr;       // kPinWords words of pinned host memory
+  bool pend_normals = false;       // h_pin[0..4]: max k_n, -, sum k_n (u64), points over the last tier capacity
+  uint32_t max_kn_hint = 0;        // densest normals neighbourhood of the previous cloud (sizes speculative launches)
   float min_z = 0.f;               // pcl::getMinMax3D z (grasp_detector.cpp:153)
 
   // grid
@@ -234,7 +254,12 @@ int build_hand_const(ag2_ctx* c);                   // tables.cpp
 int grid_build(ag2_ctx* c);                         // grid.cu
 GridDev grid_dev(const ag2_ctx* c);
 int exclusive_scan_u32(ag2_ctx* c, uint32_t* data, size_t n);  // in place, total at data[n]
-int normals_compute(ag2_ctx* c);                    // normals.cu
+int normals_compute(ag2_ctx* c);                    // normals.cu: normals_moments + normals_finish
+int normals_moments(ag2_ctx* c);                    // count pass + one launch per neighbourhood-size tier (raw moment sums)
+int normals_finish(ag2_ctx* c);                     // k_eigen over the owned points (stores to all peers when set)
+int finish_pending(ag2_ctx* c);                     // api_core.cu: after a stream sync, folds the deferred read-backs
+int sync_and_finish(ag2_ctx* c);                    // cudaStreamSynchronize(c->stream) + finish_pending
+constexpr int kPinWords = 64;
 uint32_t normals_shard_points(uint32_t n, int rank, int world);
 int normals_shard_compute(ag2_ctx* c, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned);
 int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, int world);
@@ -256,6 +281,12 @@ int radius_search_device(ag2_ctx* c, const float* q, double radius, std::vector<
 int load_caffemodel(const char* path, std::vector<float> out[8], std::string& err);  // caffemodel.cpp
 void xavier_fill(uint64_t seed, std::vector<float> out[8]);
 
+int cloud_reset(ag2_ctx* c, size_t n, int num_cams);   // api_core.cu: a new cloud of n points (grid, normals, results dropped)
+void invalidate_results(ag2_ctx* c);
+// host merge of per-rank selections (api_stages.cu): rank r's records are recs[r][0..counts[r]), its samples the
+// strided shard r, r + world, ...; result in single-GPU order, see ag2_merge_selected
+void merge_rank_lists(const ag2_hypothesis* const* recs, const size_t* counts, int world, int num_selected, bool keep_all,
+                      std::vector<ag2_hypothesis>& out);
 void phase_begin(ag2_ctx* c, int phase);
 void phase_end(ag2_ctx* c, int phase);
 int collect_phase_times(ag2_ctx* c);

@@ -25,8 +25,31 @@ void phase_end(ag2_ctx* c, int phase) {
   cudaEventRecord(c->ev[2 * phase + 1], c->stream);
   c->ev_used[2 * phase + 1] = true;
 }
-int collect_phase_times(ag2_ctx* c) {
+// After a synchronisation of the ctx stream: folds the scalars that earlier stages sent to pinned memory
+// into the statistics and reports the capacity errors they carry.
+int finish_pending(ag2_ctx* c) {
+  if (c->pend_normals) {
+    c->pend_normals = false;
+    unsigned long long sum;
+    memcpy(&sum, c->h_pin + 2, 8);
+    c->st.sum_neighbors_normals = (int64_t)sum;
+    c->max_kn_hint = c->h_pin[0];
+    if (c->h_pin[4]) {
+      c->have_normals = false;
+      c->err = "normals: a point has more than 13600 neighbours within normals_radius";
+      return AG2_E_CAPACITY;
+    }
+  }
+  return AG2_OK;
+}
+
+int sync_and_finish(ag2_ctx* c) {
   AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  return finish_pending(c);
+}
+
+int collect_phase_times(ag2_ctx* c) {
+  AG2_TRY(sync_and_finish(c));
   for (int ph = 0; ph < 8; ph++) {
     if (c->ev_used[2 * ph] && c->ev_used[2 * ph + 1]) {
       float ms = 0.f;
@@ -48,7 +71,7 @@ static bool params_ok(const ag2_params* p) {
          isfinite(p->init_bite);
 }
 
-static void invalidate_results(ag2_ctx* c) {
+void invalidate_results(ag2_ctx* c) {
   c->have_hyps = c->have_pruned = c->have_images = c->have_antipodal = c->have_selected = false;
   for (int i = 0; i < 4; i++) {
     c->list_n[i] = 0;
@@ -193,6 +216,12 @@ int ag2_create(const ag2_params* p, int device, ag2_ctx** out) {
     }
     cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
   }
+  if (cudaHostAlloc((void**)&c->h_pin, kPinWords * sizeof(uint32_t), cudaHostAllocDefault) != cudaSuccess) {
+    c->h_pin = nullptr;
+    ag2_destroy(c);
+    return AG2_E_NOMEM;
+  }
+  memset(c->h_pin, 0, kPinWords * sizeof(uint32_t));
   if (c->scalars.reserve(64) != cudaSuccess || build_hand_const(c) != AG2_OK) {
     ag2_destroy(c);
     return AG2_E_INVALID;
@@ -217,6 +246,7 @@ int ag2_destroy(ag2_ctx* c) {
     if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
   }
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->h_pin) cudaFreeHost(c->h_pin);
   delete c;
   return AG2_OK;
 }
@@ -236,8 +266,7 @@ int ag2_set_params(ag2_ctx* c, const ag2_params* p) {
 
 int ag2_synchronize(ag2_ctx* c) {
   if (!c) return AG2_E_INVALID;
-  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
-  return AG2_OK;
+  return sync_and_finish(c);
 }
 
 int ag2_get_stream(ag2_ctx* c, void** stream) {
@@ -287,7 +316,11 @@ int ag2_get_lenet_weights(ag2_ctx* c, float* c1w, float* c1b, float* c2w, float*
 
 // ---- inputs
 
-static int cloud_reset(ag2_ctx* c, size_t n, int num_cams) {
+}  // extern "C"
+namespace ag2 {
+int cloud_reset(ag2_ctx* c, size_t n, int num_cams) {
+  // sample INDICES were validated against the previous cloud: a new cloud drops them (sample points stay)
+  if (!c->use_points) c->num_samples = 0;
   c->n = n;
   c->num_cams = num_cams;
   c->grid_built = false;
@@ -301,6 +334,8 @@ static int cloud_reset(ag2_ctx* c, size_t n, int num_cams) {
   for (int i = 0; i < 18; i++) c->ev_used[i] = false;
   return AG2_OK;
 }
+}  // namespace ag2
+extern "C" {
 
 int ag2_set_cloud(ag2_ctx* c, const float* xyz, size_t stride_bytes, size_t n, const uint8_t* cam_mask, int num_cams,
                   const float* normals) {

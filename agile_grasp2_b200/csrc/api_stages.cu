@@ -40,13 +40,39 @@ int ready(ag2_ctx* c) {
 
 }  // namespace
 
+namespace ag2 {
+void merge_rank_lists(const ag2_hypothesis* const* recs, const size_t* counts, int world, int num_selected, bool keep_all,
+                      std::vector<ag2_hypothesis>& all) {
+  all.clear();
+  for (int r = 0; r < world; r++)
+    for (size_t i = 0; i < counts[r]; i++) {
+      all.push_back(recs[r][i]);
+      all.back().sample_id = r + world * recs[r][i].sample_id;
+    }
+  std::stable_sort(all.begin(), all.end(), [](const ag2_hypothesis& a, const ag2_hypothesis& b) {
+    return a.sample_id != b.sample_id ? a.sample_id < b.sample_id : a.orientation_id < b.orientation_id;
+  });
+  if (keep_all) return;
+  // the device ranking's key (select.cu score_key): order-preserving code of the double, descending
+  auto code = [](double v) {
+    long long o;
+    memcpy(&o, &v, 8);
+    return o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
+  };
+  std::stable_sort(all.begin(), all.end(), [&](const ag2_hypothesis& a, const ag2_hypothesis& b) {
+    return code(a.score) > code(b.score);
+  });
+  if (num_selected > 0 && (size_t)num_selected < all.size()) all.resize((size_t)num_selected);
+}
+}  // namespace ag2
+
 extern "C" {
 
 int ag2_compute_normals(ag2_ctx* c) {
   AG2_TRY(ready(c));
   AG2_TRY(grid_build(c));
   AG2_TRY(normals_compute(c));
-  return AG2_OK;
+  return sync_and_finish(c);  // capacity errors of the phase surface here
 }
 
 int ag2_generate_hypotheses(ag2_ctx* c) {
@@ -180,8 +206,7 @@ int ag2_get_hypotheses(ag2_ctx* c, int which, ag2_hypothesis* out, size_t cap, s
   AG2_TRY(gather_list_records(c, which));
   AG2_CUDA(c, cudaMemcpyAsync(out, c->list_rec[which].p, cnt * sizeof(ag2_hypothesis), cudaMemcpyDeviceToHost,
                               c->stream));
-  AG2_CUDA(c, cudaStreamSynchronize(c->stream));
-  return AG2_OK;
+  return sync_and_finish(c);
 }
 
 int ag2_get_stats(ag2_ctx* c, ag2_stats* out) {
@@ -313,31 +338,22 @@ int ag2_classify_images(ag2_ctx* c, const uint8_t* images, size_t n, float* logi
 int ag2_merge_selected(const ag2_hypothesis* blocks, int world, size_t cap, int num_selected, ag2_hypothesis* out,
                        size_t* n_out) {
   if (!blocks || !out || !n_out || world < 1) return AG2_E_INVALID;
-  std::vector<ag2_hypothesis> all;
-  all.reserve((size_t)world * cap);
-  for (int r = 0; r < world; r++)
+  std::vector<std::vector<ag2_hypothesis>> parts((size_t)world);
+  std::vector<const ag2_hypothesis*> ptrs((size_t)world);
+  std::vector<size_t> counts((size_t)world);
+  for (int r = 0; r < world; r++) {
     for (size_t i = 0; i < cap; i++) {
       const ag2_hypothesis& h = blocks[(size_t)r * cap + i];
       if (h.approach[0] == 0.0 && h.approach[1] == 0.0 && h.approach[2] == 0.0) continue;  // padding
-      all.push_back(h);
-      all.back().sample_id = r + world * h.sample_id;
+      parts[r].push_back(h);
     }
-  std::stable_sort(all.begin(), all.end(), [](const ag2_hypothesis& a, const ag2_hypothesis& b) {
-    return a.sample_id != b.sample_id ? a.sample_id < b.sample_id : a.orientation_id < b.orientation_id;
-  });
-  // the device ranking's key (select.cu score_key): order-preserving code of the double, descending
-  auto code = [](double v) {
-    long long o;
-    memcpy(&o, &v, 8);
-    return o >= 0 ? ((unsigned long long)o | 0x8000000000000000ull) : ~(unsigned long long)o;
-  };
-  std::stable_sort(all.begin(), all.end(), [&](const ag2_hypothesis& a, const ag2_hypothesis& b) {
-    return code(a.score) > code(b.score);
-  });
-  size_t n = all.size();
-  if (num_selected > 0 && (size_t)num_selected < n) n = (size_t)num_selected;
-  std::copy(all.begin(), all.begin() + n, out);
-  *n_out = n;
+    ptrs[r] = parts[r].data();
+    counts[r] = parts[r].size();
+  }
+  std::vector<ag2_hypothesis> all;
+  ag2::merge_rank_lists(ptrs.data(), counts.data(), world, num_selected, false, all);
+  std::copy(all.begin(), all.end(), out);
+  *n_out = all.size();
   return AG2_OK;
 }
 

@@ -274,7 +274,7 @@ int frames_compute(ag2_ctx* c) {
   AG2_LAUNCH_CHECK(c);
   uint32_t max_kt = 0;
   AG2_CUDA(c, cudaMemcpyAsync(&max_kt, c->scalars.p + 12, 4, cudaMemcpyDeviceToHost, st));
-  AG2_CUDA(c, cudaStreamSynchronize(st));
+  AG2_TRY(sync_and_finish(c));
   uint32_t cap = 64;
   while (cap < max_kt) cap <<= 1;
   size_t smem = (size_t)cap * 12;

@@ -576,7 +576,7 @@ int hands_compute(ag2_ctx* c) {
     uint32_t res[12], nvalid = 0;
     AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 20, sizeof(res), cudaMemcpyDeviceToHost, st));
     AG2_CUDA(c, cudaMemcpyAsync(&nvalid, c->scalars.p + 13, 4, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
+    AG2_TRY(sync_and_finish(c));
     unsigned long long stat[3];
     memcpy(stat, &res[4], sizeof(stat));
     if (res[1]) {  // pool overflow: grow to the exact need and redo

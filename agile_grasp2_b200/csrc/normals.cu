@@ -186,23 +186,35 @@ __device__ void solve_normal(const float a[9], float px, float py, float pz, flo
 // the cloud in one full-occupancy launch instead of a few lanes at the end of each warp's batch.
 constexpr int kMomWords = 12;
 
+// Destination arrays of k_eigen: the sorted normals of every rank (multi-GPU: peer-mapped pointers into
+// the other GPUs' memory, group.cu) or just this context's own.
+struct NrmDst {
+  float4* p[8];
+  int n;
+};
+
 __global__ void __launch_bounds__(256) k_eigen(GridDev g, const uint32_t* __restrict__ kn,
-                                               const float* __restrict__ mom, float4* __restrict__ nrm_out,
-                                               uint32_t shard_rank, uint32_t shard_world) {
+                                               const float* __restrict__ mom, const float4* nrm_own /* may alias dst.p[] */,
+                                               NrmDst dst, uint32_t shard_rank, uint32_t shard_world) {
   const uint32_t i = shard_point(blockIdx.x * blockDim.x + threadIdx.x, shard_rank, shard_world);
   if (i >= (uint32_t)g.n) return;
   const uint32_t count = kn[i];
-  if (count < 3) return;  // NaN already written
-  const float4* m4 = reinterpret_cast<const float4*>(mom + (size_t)i * kMomWords);
-  const float4 m0 = m4[0], m1 = m4[1], m2 = m4[2];
-  float a[9] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x};
-  const float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
+  const float nanv = __int_as_float(0x7fc00000);
+  float n[3] = {nanv, nanv, nanv};  // computePointNormal: fewer than 3 neighbours -> NaN
+  if (count >= 3) {
+    const float4* m4 = reinterpret_cast<const float4*>(mom + (size_t)i * kMomWords);
+    const float4 m0 = m4[0], m1 = m4[1], m2 = m4[2];
+    float a[9] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w, m2.x};
+    const float inv = 1.0f / (float)count;  // Eigen 3.2 operator/=: multiply by the reciprocal
 #pragma unroll
-  for (int k = 0; k < 9; k++) a[k] = a[k] * inv;
-  const float4 q = g.pts[i];
-  float n[3];
-  solve_normal(a, q.x, q.y, q.z, n);
-  nrm_out[i] = make_float4(n[0], n[1], n[2], nrm_out[i].w);
+    for (int k = 0; k < 9; k++) a[k] = a[k] * inv;
+    const float4 q = g.pts[i];
+    solve_normal(a, q.x, q.y, q.z, n);
+  }
+  // w = camera bits: every rank built the same cell-sorted cloud, so the value is the destination's own
+  const float4 v = make_float4(n[0], n[1], n[2], nrm_own[i].w);
+  // a warp's 32 points are one granule = 512 contiguous bytes per destination (NVLink stores when remote)
+  for (int r = 0; r < dst.n; r++) dst.p[r][i] = v;
 }
 
 // ---------------------------------------------------------------------------
@@ -250,6 +262,10 @@ struct NormalsArgs {
   float r2, rq, bscale;
   const uint32_t* kn;
   uint32_t n_items, cap, bsz;
+  const uint32_t* n_items_dev;  // when set: the item count lives in device memory (tier sizes of the count pass);
+                                // the kernel then derives its own batch size and n_items / bsz above are unused
+  uint32_t skip_from;           // with n_items_dev: the launch does nothing when the count is >= skip_from (the
+                                // four-lanes-per-point kernel takes such a tier); 0 = never
   uint32_t shard_rank, shard_world;
   const uint32_t* list;       // nullptr: items are the owned cell-sorted points (shard_point), n_items of them
   uint32_t* big_list;         // out: items whose neighbourhood exceeds cap
@@ -264,7 +280,16 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   extern __shared__ __align__(16) unsigned char smem[];
   const GridDev& g = P.g;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t cap = P.cap, bsz = P.bsz;
+  uint32_t n_items = P.n_items, bsz = P.bsz;
+  if (P.n_items_dev) {
+    // launched at full residency before the count is known on the host: same batch-size rule as the host's
+    n_items = *P.n_items_dev;
+    if (n_items == 0 || (P.skip_from && n_items >= P.skip_from)) return;
+    const uint32_t resident_warps = gridDim.x * (blockDim.x >> 5);
+    bsz = 32;
+    while (bsz > 1 && (n_items + bsz - 1) / bsz < 4 * resident_warps) bsz >>= 1;
+  }
+  const uint32_t cap = P.cap;
   const NormalsSmem L = normals_smem(cap);
   unsigned char* base = smem + (size_t)warp * L.total;
   uint2* A = (uint2*)(base + L.a);
@@ -278,7 +303,7 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
   uint32_t* start = (uint32_t*)(base + L.start);
   uint32_t* rowb = (uint32_t*)(base + L.rowb);
   uint32_t* rowp = (uint32_t*)(base + L.rowp);
-  const uint32_t n_batches = (P.n_items + bsz - 1) / bsz;
+  const uint32_t n_batches = (n_items + bsz - 1) / bsz;
   // accumulator role of lanes 0..8: operand selectors 0 = x, 1 = y, 2 = z, 3 = constant 1
   const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
   const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
@@ -303,12 +328,12 @@ __global__ void __launch_bounds__(256) k_normals(NormalsArgs P) {
     uint32_t next = batch + 1;
     if (!dealt && lane == 0) next = atomicAdd(P.batch_counter, 1u);
     const uint32_t i0 = batch * bsz;
-    const uint32_t nb = min(bsz, P.n_items - i0);
+    const uint32_t nb = min(bsz, n_items - i0);
     const uint32_t my_i =
         lane < nb ? (P.list ? P.list[i0 + lane] : shard_point(i0 + lane, P.shard_rank, P.shard_world)) : 0u;
     const uint32_t my_count = lane < nb ? P.kn[my_i] : 0u;
     const bool too_big = my_count > cap;
-    if (too_big) {
+    if (too_big && P.big_count) {
       uint32_t slot = atomicAdd(P.big_count, 1u);
       if (slot < P.big_cap) P.big_list[slot] = my_i;
     }
@@ -537,11 +562,13 @@ __global__ void __launch_bounds__(kCtaThreads) k_normals_cta(NormalsArgs P) {
   const int sa = lane < 3 ? 0 : (lane < 5 ? 1 : (lane == 5 ? 2 : lane - 6));
   const int sb = lane < 3 ? lane : (lane < 5 ? lane - 2 : (lane == 5 ? 2 : 3));
   const float bscale = (float)kCtaNB / P.r2;
+  const uint32_t n_items = P.n_items_dev ? *P.n_items_dev : P.n_items;
+  if (n_items == 0) return;
   if (tid < 4) ones_s[tid] = 1.0f;
   if (tid == 0) misc[2] = atomicAdd(P.batch_counter, 1u);
   __syncthreads();
   uint32_t item = misc[2];
-  while (item < P.n_items) {
+  while (item < n_items) {
     __syncthreads();  // everyone has read misc[2]
     if (tid == 0) misc[2] = atomicAdd(P.batch_counter, 1u);  // the next point, read at the end of this one
     const uint32_t i = P.list[item];
@@ -698,10 +725,16 @@ __global__ void __launch_bounds__(kCtaThreads) k_normals_cta(NormalsArgs P) {
 //   the sparsest tiers (by default 0..3, <= 96 neighbours; any of 0..7 can): k_normals_quad,
 //               four lanes per point;
 //   the others: k_normals, one warp per point.
+// The last capacity is what one CTA's shared memory holds (16 B per neighbour); a denser point is an error
+// (AG2_E_CAPACITY, reported at the next synchronisation).
 constexpr int kQuadTiers = 8;
-constexpr int kAllTiers = 13;
-constexpr uint32_t kTierCapHost[kAllTiers] = {48, 64, 80, 96, 112, 128, 160, 208, 256, 384, 512, 1024, 0xffffffffu};
-__constant__ uint32_t c_tier_cap[kAllTiers] = {48, 64, 80, 96, 112, 128, 160, 208, 256, 384, 512, 1024, 0xffffffffu};
+constexpr int kAllTiers = 16;
+constexpr uint32_t kTierCapHost[kAllTiers] = {48,  64,  80,  96,   112,  128,  160,  208,
+                                              256, 384, 512, 1024, 2048, 4096, 8192, 13600};
+__constant__ uint32_t c_tier_cap[kAllTiers] = {48,  64,  80,  96,   112,  128,  160,  208,
+                                               256, 384, 512, 1024, 2048, 4096, 8192, 13600};
+// tier_cnt layout: [0..15] tier sizes, [16..31] batch counters of the tier launches, [32] points over the last capacity
+constexpr int kTierCntWords = 48;
 
 // thread per point: neighbour count, NaN normal below three neighbours, tier membership lists
 // (one warp-aggregated atomic per tier present in the warp, so consecutive cell-sorted points stay
@@ -747,8 +780,12 @@ __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float 
   }
   int tier = -1;
   if (owned && cnt >= 3) {
-    tier = 0;
-    while (cnt > c_tier_cap[tier]) tier++;
+    if (cnt > c_tier_cap[kAllTiers - 1]) {
+      atomicAdd(&tier_count[32], 1u);  // no launch can hold this neighbourhood: reported as AG2_E_CAPACITY
+    } else {
+      tier = 0;
+      while (cnt > c_tier_cap[tier]) tier++;
+    }
   }
   const uint32_t peers = __match_any_sync(AG2_FULL, tier);
   if (tier >= 0) {
@@ -786,6 +823,8 @@ struct QuadArgs {
   const uint32_t* kn;
   const uint32_t* list;
   uint32_t n_items, cap;
+  const uint32_t* n_items_dev;  // when set: item count in device memory
+  uint32_t min_items;           // the launch does nothing below this count (>= 1: an empty list is skipped)
   float* mom_out;
 };
 
@@ -803,166 +842,178 @@ __global__ void __launch_bounds__(kQuadThreads) k_normals_quad(QuadArgs P) {
   uint32_t* cur = (uint32_t*)(base + (size_t)cap * 40) + grp;  // cur[b * 8], 32 buckets
   uint32_t* rowb = (uint32_t*)(base + (size_t)cap * 40 + 1024) + grp;  // rowb[r * 8], 16 rows: first position
   uint32_t* rowp = rowb + 16 * 8;                                      // rowp[r * 8], 17 entries: candidate prefix
-  // No lane leaves early, so every warp-wide primitive below runs on the full mask: a sub-warp mask that
-  // differs between the groups makes the hardware issue the primitive once per group.  Groups past the end of
-  // the list redo its last point (same values written twice).
-  const uint32_t item = min((blockIdx.x * kQuadThreads + threadIdx.x) >> 2, P.n_items - 1);
-  const uint32_t i = P.list[item];
-  const float4 q = g.pts[i];  // 3 <= kn[i] <= cap: the tier list holds nothing else
-  const uint32_t jbits = P.jbits, jmask = (1u << jbits) - 1u;
-  const float r2 = P.r2;
-  // ---- gather: the group's candidate rows flattened into one sequence, four candidates per step; the step
-  //      count is the warp's maximum so that the ballot is warp-uniform
-  uint32_t n = 0;
-  {
-    const QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
-    const int rows = w.rows();
-    int rows_max = rows;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) rows_max = max(rows_max, __shfl_xor_sync(AG2_FULL, rows_max, o));
-    for (int r0 = 0; r0 < rows_max; r0 += 16) {
-      __syncwarp();  // the previous table is no longer read
-#pragma unroll
-      for (int k = 0; k < 4; k++) {  // each lane trims four of the sixteen rows
-        const int r = (int)sub + 4 * k;
-        uint32_t b = 0, e = 0;
-        if (r0 + r < rows) row_span_trim(g, w, r0 + r, q.x, q.y, q.z, r2 * 1.002f, b, e);
-        rowb[r * 8] = b;
-        rowp[r * 8] = e - b;
-      }
-      __syncwarp();
-      if (sub == 0) {
-        uint32_t run = 0;
-#pragma unroll
-        for (int r = 0; r < 16; r++) {
-          const uint32_t c = rowp[r * 8];
-          rowp[r * 8] = run;
-          run += c;
+  // The item count may live in device memory (tier sizes of the count pass): the launch is then sized for the
+  // worst case and its CTAs stride over the list, most of them leaving at once.
+  const uint32_t n_items = P.n_items_dev ? *P.n_items_dev : P.n_items;
+  if (n_items < P.min_items) return;  // a short tier runs on k_normals (launched next to this one)
+  for (uint32_t item0 = blockIdx.x * (kQuadThreads / 4); item0 < n_items; item0 += gridDim.x * (kQuadThreads / 4)) {
+    if (item0 + warp * 8 >= n_items) continue;  // warp-uniform: nothing below synchronises across warps
+    // No lane leaves early, so every warp-wide primitive below runs on the full mask: a sub-warp mask that
+    // differs between the groups makes the hardware issue the primitive once per group.  Groups past the end of
+    // the list redo its last point (same values written twice).
+    const uint32_t item = min(item0 + (threadIdx.x >> 2), n_items - 1);
+    const uint32_t i = P.list[item];
+    const float4 q = g.pts[i];  // 3 <= kn[i] <= cap: the tier list holds nothing else
+    const uint32_t jbits = P.jbits, jmask = (1u << jbits) - 1u;
+    const float r2 = P.r2;
+    // ---- gather: the group's candidate rows flattened into one sequence, four candidates per step; the step
+    //      count is the warp's maximum so that the ballot is warp-uniform
+    uint32_t n = 0;
+    {
+      const QueryWindow w = make_window(g, q.x, q.y, q.z, P.rq);
+      const int rows = w.rows();
+      int rows_max = rows;
+  #pragma unroll
+      for (int o = 16; o > 0; o >>= 1) rows_max = max(rows_max, __shfl_xor_sync(AG2_FULL, rows_max, o));
+      for (int r0 = 0; r0 < rows_max; r0 += 16) {
+        __syncwarp();  // the previous table is no longer read
+  #pragma unroll
+        for (int k = 0; k < 4; k++) {  // each lane trims four of the sixteen rows
+          const int r = (int)sub + 4 * k;
+          uint32_t b = 0, e = 0;
+          if (r0 + r < rows) row_span_trim(g, w, r0 + r, q.x, q.y, q.z, r2 * 1.002f, b, e);
+          rowb[r * 8] = b;
+          rowp[r * 8] = e - b;
         }
-        rowp[16 * 8] = run;
-      }
-      __syncwarp();
-      const uint32_t T = rowp[16 * 8];
-      uint32_t T_max = T;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) T_max = max(T_max, __shfl_xor_sync(AG2_FULL, T_max, o));
-      int row = 0;
-      uint32_t row_lo = 0, row_hi = rowp[8], row_b = rowb[0];
-      for (uint32_t t0 = 0; t0 < T_max; t0 += 4) {
-        const uint32_t t = t0 + sub;
-        bool hit = false;
-        float d2 = 0.f;
-        uint32_t j = 0;
-        if (t < T) {
-          while (t >= row_hi) {
-            row++;
-            row_lo = row_hi;
-            row_hi = rowp[(row + 1) * 8];
-            row_b = rowb[row * 8];
+        __syncwarp();
+        if (sub == 0) {
+          uint32_t run = 0;
+  #pragma unroll
+          for (int r = 0; r < 16; r++) {
+            const uint32_t c = rowp[r * 8];
+            rowp[r * 8] = run;
+            run += c;
           }
-          j = row_b + (t - row_lo);
-          const float4 p = g.pts[j];
-          d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
-          hit = d2 < r2;
+          rowp[16 * 8] = run;
         }
-        const uint32_t bits = (__ballot_sync(AG2_FULL, hit) >> gshift) & 0xFu;
-        if (hit) {
-          const uint32_t qv = min(P.qmax, (uint32_t)__fmul_rn(d2, P.qscale));  // monotone in d2
-          const uint32_t pos = n + __popc(bits & ((1u << sub) - 1u));
-          if (pos < cap) L[pos * 8] = (qv << jbits) | j;
+        __syncwarp();
+        const uint32_t T = rowp[16 * 8];
+        uint32_t T_max = T;
+  #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) T_max = max(T_max, __shfl_xor_sync(AG2_FULL, T_max, o));
+        int row = 0;
+        uint32_t row_lo = 0, row_hi = rowp[8], row_b = rowb[0];
+        for (uint32_t t0 = 0; t0 < T_max; t0 += 4) {
+          const uint32_t t = t0 + sub;
+          bool hit = false;
+          float d2 = 0.f;
+          uint32_t j = 0;
+          if (t < T) {
+            while (t >= row_hi) {
+              row++;
+              row_lo = row_hi;
+              row_hi = rowp[(row + 1) * 8];
+              row_b = rowb[row * 8];
+            }
+            j = row_b + (t - row_lo);
+            const float4 p = g.pts[j];
+            d2 = dist2_f(q.x - p.x, q.y - p.y, q.z - p.z);
+            hit = d2 < r2;
+          }
+          const uint32_t bits = (__ballot_sync(AG2_FULL, hit) >> gshift) & 0xFu;
+          if (hit) {
+            const uint32_t qv = min(P.qmax, (uint32_t)__fmul_rn(d2, P.qscale));  // monotone in d2
+            const uint32_t pos = n + __popc(bits & ((1u << sub) - 1u));
+            if (pos < cap) L[pos * 8] = (qv << jbits) | j;
+          }
+          n += __popc(bits);
         }
-        n += __popc(bits);
+      }
+      n = min(n, cap);  // == count by construction (same walk, same predicate as the count pass)
+    }
+    // ---- counting sort on the top five bits -> byte permutation grouped by bucket
+  #pragma unroll
+    for (int k = 0; k < 8; k++) cur[(sub * 8 + k) * 8] = 0;
+    __syncwarp();
+    for (uint32_t t = sub; t < n; t += 4) atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
+    __syncwarp();
+    uint32_t lo, hi;  // this lane's buckets sub*8 .. sub*8+7 occupy ord[lo, hi)
+    {
+      uint32_t c8[8], tot = 0;
+  #pragma unroll
+      for (int k = 0; k < 8; k++) {
+        c8[k] = cur[(sub * 8 + k) * 8];
+        tot += c8[k];
+      }
+      uint32_t incl = tot;
+      uint32_t up = __shfl_up_sync(AG2_FULL, incl, 1, 4);
+      if (sub >= 1) incl += up;
+      up = __shfl_up_sync(AG2_FULL, incl, 2, 4);
+      if (sub >= 2) incl += up;
+      lo = incl - tot, hi = incl;
+      uint32_t run = lo;
+  #pragma unroll
+      for (int k = 0; k < 8; k++) {
+        cur[(sub * 8 + k) * 8] = run;
+        run += c8[k];
       }
     }
-    n = min(n, cap);  // == count by construction (same walk, same predicate as the count pass)
-  }
-  // ---- counting sort on the top five bits -> byte permutation grouped by bucket
-#pragma unroll
-  for (int k = 0; k < 8; k++) cur[(sub * 8 + k) * 8] = 0;
-  __syncwarp();
-  for (uint32_t t = sub; t < n; t += 4) atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
-  __syncwarp();
-  uint32_t lo, hi;  // this lane's buckets sub*8 .. sub*8+7 occupy ord[lo, hi)
-  {
-    uint32_t c8[8], tot = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      c8[k] = cur[(sub * 8 + k) * 8];
-      tot += c8[k];
+    __syncwarp();
+    for (uint32_t t = sub; t < n; t += 4) {
+      const uint32_t pos = atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
+      ord[pos * 8] = (uint8_t)t;
     }
-    uint32_t incl = tot;
-    uint32_t up = __shfl_up_sync(AG2_FULL, incl, 1, 4);
-    if (sub >= 1) incl += up;
-    up = __shfl_up_sync(AG2_FULL, incl, 2, 4);
-    if (sub >= 2) incl += up;
-    lo = incl - tot, hi = incl;
-    uint32_t run = lo;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      cur[(sub * 8 + k) * 8] = run;
-      run += c8[k];
-    }
-  }
-  __syncwarp();
-  for (uint32_t t = sub; t < n; t += 4) {
-    const uint32_t pos = atomicAdd(&cur[(L[t * 8] >> 27) * 8], 1u);
-    ord[pos * 8] = (uint8_t)t;
-  }
-  __syncwarp();
-  // ---- insertion sort of the lane's segment (elements never leave their bucket); `top` is the
-  //      last key of the sorted prefix, so an element already in place costs one comparison
-  auto before = [&](uint32_t ka, uint32_t kb) -> bool {  // does ka precede kb in radiusSearch order?
-    const uint32_t qa = ka >> jbits, qb = kb >> jbits;
-    if (qa != qb) return qa < qb;
-    const float4 pa = g.pts[ka & jmask], pb = g.pts[kb & jmask];
-    const float da = dist2_f(q.x - pa.x, q.y - pa.y, q.z - pa.z);
-    const float db = dist2_f(q.x - pb.x, q.y - pb.y, q.z - pb.z);
-    return da < db || (da == db && __float_as_uint(pa.w) < __float_as_uint(pb.w));
-  };
-  if (lo < hi) {
-    uint32_t top = L[(uint32_t)ord[lo * 8] * 8];
-    for (uint32_t t = lo + 1; t < hi; t++) {
-      const uint32_t o = ord[t * 8];
-      const uint32_t k = L[o * 8];
-      if (before(top, k)) {
-        top = k;
-        continue;
+    __syncwarp();
+    // ---- insertion sort of the lane's segment (elements never leave their bucket); `top` is the
+    //      last key of the sorted prefix, so an element already in place costs one comparison
+    auto before = [&](uint32_t ka, uint32_t kb) -> bool {  // does ka precede kb in radiusSearch order?
+      const uint32_t qa = ka >> jbits, qb = kb >> jbits;
+      if (qa != qb) return qa < qb;
+      const float4 pa = g.pts[ka & jmask], pb = g.pts[kb & jmask];
+      const float da = dist2_f(q.x - pa.x, q.y - pa.y, q.z - pa.z);
+      const float db = dist2_f(q.x - pb.x, q.y - pb.y, q.z - pb.z);
+      return da < db || (da == db && __float_as_uint(pa.w) < __float_as_uint(pb.w));
+    };
+    if (lo < hi) {
+      uint32_t top = L[(uint32_t)ord[lo * 8] * 8];
+      for (uint32_t t = lo + 1; t < hi; t++) {
+        const uint32_t o = ord[t * 8];
+        const uint32_t k = L[o * 8];
+        if (before(top, k)) {
+          top = k;
+          continue;
+        }
+        uint32_t u = t;
+        do {
+          const uint32_t o2 = ord[(u - 1) * 8];
+          if (before(L[o2 * 8], k)) break;
+          ord[u * 8] = (uint8_t)o2;
+          u--;
+        } while (u > lo);
+        ord[u * 8] = (uint8_t)o;
       }
-      uint32_t u = t;
-      do {
-        const uint32_t o2 = ord[(u - 1) * 8];
-        if (before(L[o2 * 8], k)) break;
-        ord[u * 8] = (uint8_t)o2;
-        u--;
-      } while (u > lo);
-      ord[u * 8] = (uint8_t)o;
     }
-  }
-  __syncwarp();
-  // ---- sequential single-pass float moments (accu[0..8] of computeMeanAndCovarianceMatrix):
-  //      lane 0: xx xy xz, lane 1: yy yz zz, lane 2: x y z (times the constant 1, exact)
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-  if (sub < 3) {
-#pragma unroll 4
-    for (uint32_t t = 0; t < n; t++) {
-      const float4 p = g.pts[L[(uint32_t)ord[t * 8] * 8] & jmask];
-      // m = x | y | 1 by lane; products m*(x,y,z), except lane 1: y*y, y*z, z*z (five selects instead of eight)
-      const float m = sub == 0 ? p.x : (sub == 1 ? p.y : 1.0f);
-      a0 = __fadd_rn(a0, __fmul_rn(m, sub == 1 ? p.y : p.x));
-      a1 = __fadd_rn(a1, __fmul_rn(m, sub == 1 ? p.z : p.y));
-      a2 = __fadd_rn(a2, __fmul_rn(sub == 1 ? p.z : m, p.z));
+    __syncwarp();
+    // ---- sequential single-pass float moments (accu[0..8] of computeMeanAndCovarianceMatrix):
+    //      lane 0: xx xy xz, lane 1: yy yz zz, lane 2: x y z (times the constant 1, exact)
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+    if (sub < 3) {
+  #pragma unroll 4
+      for (uint32_t t = 0; t < n; t++) {
+        const float4 p = g.pts[L[(uint32_t)ord[t * 8] * 8] & jmask];
+        // m = x | y | 1 by lane; products m*(x,y,z), except lane 1: y*y, y*z, z*z (five selects instead of eight)
+        const float m = sub == 0 ? p.x : (sub == 1 ? p.y : 1.0f);
+        a0 = __fadd_rn(a0, __fmul_rn(m, sub == 1 ? p.y : p.x));
+        a1 = __fadd_rn(a1, __fmul_rn(m, sub == 1 ? p.z : p.y));
+        a2 = __fadd_rn(a2, __fmul_rn(sub == 1 ? p.z : m, p.z));
+      }
     }
-  }
-  if (sub < 3) {
-    float* m = P.mom_out + (size_t)i * kMomWords + sub * 3;
-    m[0] = a0, m[1] = a1, m[2] = a2;
+    if (sub < 3) {
+      float* m = P.mom_out + (size_t)i * kMomWords + sub * 3;
+      m[0] = a0, m[1] = a1, m[2] = a2;
+    }
+    __syncwarp();  // the lists are reused by the next item
   }
 }
 
 }  // namespace
 
-// Four-lanes-per-point launch over one tier list at capacity `cap` (< 256: byte permutation).
-static int launch_normals_quad(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list) {
+// Launches over a tier list.  `n_dev` (device memory) holds the item count when the host does not know it
+// yet: the launch is then sized for the worst case (`n_upper` items / full residency) and reads the count itself.
+
+// Four lanes per point at capacity `cap` (< 256: byte permutation); does nothing below `min_items` items.
+static int launch_normals_quad(ag2_ctx* c, cudaStream_t st, uint32_t n_upper, const uint32_t* n_dev, uint32_t min_items,
+                               uint32_t cap, const uint32_t* list) {
   const size_t smem = quad_smem_per_warp(cap) * (kQuadThreads / 32);
   uint32_t jbits = 1;
   while (jbits < 27 && (1ull << jbits) < (unsigned long long)c->n_finite) jbits++;
@@ -975,17 +1026,23 @@ static int launch_normals_quad(ag2_ctx* c, cudaStream_t st, uint32_t n_items, ui
   P.jbits = jbits;
   P.kn = c->kn.p;
   P.list = list;
-  P.n_items = n_items, P.cap = cap;
+  P.n_items = n_upper, P.cap = cap;
+  P.n_items_dev = n_dev;
+  P.min_items = std::max(min_items, 1u);
   P.mom_out = c->nrm_mom.p;
   const uint32_t per_cta = kQuadThreads / 4;
-  k_normals_quad<<<(n_items + per_cta - 1) / per_cta, kQuadThreads, smem, st>>>(P);
+  // CTAs stride over the list; a few waves of resident CTAs is all a launch ever needs
+  const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(16, (226 * 1024) / (smem + 1024)));
+  const uint32_t grid = std::max(1u, std::min((n_upper + per_cta - 1) / per_cta, (uint32_t)c->sm_count * per_sm * 4u));
+  k_normals_quad<<<grid, kQuadThreads, smem, st>>>(P);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }
 
-// One launch over `n_items` items (all points, or a list) at capacity `cap`.
-static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list,
-                          uint32_t* big_list, uint32_t* big_count, uint32_t big_cap, uint32_t* batch_counter) {
+// One warp per point over `n_items` items (all owned points when `list` is null, else a list) at capacity `cap`.
+static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, const uint32_t* n_dev, uint32_t skip_from,
+                          uint32_t cap, const uint32_t* list, uint32_t* big_list, uint32_t* big_count, uint32_t big_cap,
+                          uint32_t* batch_counter) {
   const NormalsSmem L = normals_smem(cap);
   const int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (110 * 1024) / L.total));
   const size_t smem = L.total * warps;
@@ -993,18 +1050,21 @@ static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_
   const int blocks_per_sm = (int)std::max<size_t>(1, std::min<size_t>(64 / warps, (226 * 1024) / (smem + 1024)));
   const uint32_t resident_warps = (uint32_t)(c->sm_count * blocks_per_sm * warps);
   // batch size: 32 points per warp when there is plenty of work, fewer when a short list of
-  // dense points must still be spread over the whole machine
+  // dense points must still be spread over the whole machine (the kernel applies the same rule to a device-side count)
   uint32_t bsz = 32;
   while (bsz > 1 && (n_items + bsz - 1) / bsz < 4 * resident_warps) bsz >>= 1;
   const uint32_t n_batches = (n_items + bsz - 1) / bsz;
-  const uint32_t grid = (uint32_t)std::max<size_t>(
+  uint32_t grid = (uint32_t)std::max<size_t>(
       1, std::min<size_t>(((size_t)n_batches + warps - 1) / warps, (size_t)c->sm_count * blocks_per_sm));
+  if (n_dev)  // count unknown here: full residency, but never more warps than there can be items
+    grid = (uint32_t)std::max<size_t>(1, std::min<size_t>(((size_t)n_items + warps - 1) / warps, (size_t)c->sm_count * blocks_per_sm));
   NormalsArgs P;
   P.g = grid_dev(c);
   P.r2 = c->hc.r2_normals, P.rq = c->hc.rq_normals;
   P.bscale = (float)kNB / c->hc.r2_normals;
   P.kn = c->kn.p;
   P.n_items = n_items, P.cap = cap, P.bsz = bsz;
+  P.n_items_dev = n_dev, P.skip_from = skip_from;
   P.shard_rank = (uint32_t)c->nrm_rank, P.shard_world = (uint32_t)c->nrm_world;
   P.list = list;
   P.big_list = big_list, P.big_count = big_count, P.big_cap = big_cap;
@@ -1016,25 +1076,29 @@ static int launch_normals(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_
   return AG2_OK;
 }
 
-// CTA-per-point launch over one tier list at capacity `cap` (dense tiers).
-static int launch_normals_cta(ag2_ctx* c, cudaStream_t st, uint32_t n_items, uint32_t cap, const uint32_t* list,
-                              uint32_t* counter) {
+// One CTA per point over a tier list at capacity `cap` (dense tiers).
+static int launch_normals_cta(ag2_ctx* c, cudaStream_t st, uint32_t n_upper, const uint32_t* n_dev, uint32_t cap,
+                              const uint32_t* list, uint32_t* counter, bool unlikely) {
   const CtaSmem L = cta_smem(cap);
-  AG2_CUDA(c, cudaFuncSetAttribute(k_normals_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(16, (226 * 1024) / (L.total + 1024)));
   NormalsArgs P;
   P.g = grid_dev(c);
   P.r2 = c->hc.r2_normals, P.rq = c->hc.rq_normals;
   P.bscale = 0.f;
   P.kn = c->kn.p;
-  P.n_items = n_items, P.cap = cap, P.bsz = 1;
+  P.n_items = n_upper, P.cap = cap, P.bsz = 1;
+  P.n_items_dev = n_dev, P.skip_from = 0;
   P.shard_rank = 0, P.shard_world = 1;
   P.list = list;
   P.big_list = nullptr, P.big_count = nullptr, P.big_cap = 0;
   P.batch_counter = counter;
   P.mom_out = c->nrm_mom.p;
   P.nrm_out = c->nrm.p;
-  const uint32_t grid = (uint32_t)std::min<size_t>(n_items, (size_t)c->sm_count * per_sm);
+  // CTAs claim points from a counter, so any grid is correct.  A tier that the previous cloud's densest
+  // neighbourhood says will be empty gets a token grid: its CTAs need most of an SM's shared memory each and
+  // would otherwise queue behind the launches that do have work.
+  uint32_t grid = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_upper, (size_t)c->sm_count * per_sm));
+  if (unlikely) grid = std::min(grid, 4u);
   k_normals_cta<<<grid, kCtaThreads, L.total, st>>>(P);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
@@ -1101,8 +1165,25 @@ int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, in
   return AG2_OK;
 }
 
-// Tiered path: count pass with tier lists, then one launch per non-empty tier on the auxiliary streams.
-static int normals_compute_tiered(ag2_ctx* c) {
+// k_eigen over the owned points: normals into this context's sorted array, or into every rank's (multi-GPU).
+static int launch_eigen(ag2_ctx* c) {
+  const uint32_t own = normals_shard_points((uint32_t)c->n_finite, c->nrm_rank, c->nrm_world);
+  NrmDst dst;
+  dst.n = 0;
+  for (int r = 0; r < c->nrm_peers && r < 8; r++) dst.p[dst.n++] = c->nrm_peer[r];
+  if (dst.n == 0) dst.p[dst.n++] = c->nrm.p;
+  for (int r = dst.n; r < 8; r++) dst.p[r] = nullptr;
+  k_eigen<<<std::max(1u, (((own + 31) & ~31u) + 255) / 256), 256, 0, c->stream>>>(
+      grid_dev(c), c->kn.p, c->nrm_mom.p, c->nrm.p, dst, (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}
+
+// Tiered path: count pass with tier lists, then one launch per tier on the auxiliary streams.  The host never
+// learns the tier sizes: every launch is sized for the worst case and reads its item count from device memory
+// (an empty tier costs a launch that exits at once), so the phase has no host round trip and the launches are
+// queued while the count pass still runs.
+static int normals_moments_tiered(ag2_ctx* c) {
   cudaStream_t st = c->stream;
   GridDev g = grid_dev(c);
   const uint32_t n = (uint32_t)c->n_finite;
@@ -1118,78 +1199,66 @@ static int normals_compute_tiered(ag2_ctx* c) {
   if (const char* e = getenv("AG2_NORMALS_CTA_FROM")) cta_from = std::max(0, atoi(e));
   uint32_t quad_min = 8192;
   if (const char* e = getenv("AG2_NORMALS_QUAD_MIN")) quad_min = (uint32_t)std::max(0, atoi(e));
+  quad_min = std::max(quad_min, 1u);
   AG2_CUDA(c, c->kn.reserve(n));
   AG2_CUDA(c, c->tier_list.reserve((size_t)kAllTiers * std::max(owned, 1u)));
-  AG2_CUDA(c, c->tier_cnt.reserve(32));
-  AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));  // [0..12] tier sizes, [16..31] batch counters / unused overflow slots
+  AG2_CUDA(c, c->tier_cnt.reserve(kTierCntWords));
+  AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
-  AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, 32 * 4, st));
+  AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, kTierCntWords * 4, st));
   k_count_tiers<<<std::max(1u, (((owned + 31) & ~31u) + 127) / 128), 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
                                                  (unsigned long long*)(c->scalars.p + 10), c->tier_cnt.p,
                                                  c->tier_list.p, owned, c->nrm.p, (uint32_t)c->nrm_rank,
                                                  (uint32_t)c->nrm_world);
   AG2_LAUNCH_CHECK(c);
-  uint32_t res[4], cnt[kAllTiers];
-  AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
-  AG2_CUDA(c, cudaMemcpyAsync(cnt, c->tier_cnt.p, sizeof(cnt), cudaMemcpyDeviceToHost, st));
-  AG2_CUDA(c, cudaStreamSynchronize(st));
-  const uint32_t max_kn = res[0];
-  unsigned long long sum;
-  memcpy(&sum, &res[2], 8);
-  c->st.sum_neighbors_normals = (int64_t)sum;
-  const uint32_t cap_max = (std::max(max_kn, 32u) + 31u) & ~31u;
-  if (normals_smem(cap_max).total > 220 * 1024) {
-    c->err = "normals: a point has more than ~11000 neighbours within normals_radius";
-    return AG2_E_CAPACITY;
+  // statistics and the capacity check travel to pinned memory behind the count pass; nobody waits for them here
+  AG2_CUDA(c, cudaMemcpyAsync(c->h_pin, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 4, c->tier_cnt.p + 32, 4, cudaMemcpyDeviceToHost, st));
+  c->pend_normals = true;
+  static bool attr_set = false;
+  if (!attr_set) {
+    AG2_CUDA(c, cudaFuncSetAttribute(k_normals_quad, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(quad_smem_per_warp(kTierCapHost[kQuadTiers - 1]) * (kQuadThreads / 32))));
+    AG2_CUDA(c, cudaFuncSetAttribute(k_normals_cta, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)cta_smem(kTierCapHost[kAllTiers - 1]).total));
+    attr_set = true;
   }
-  AG2_CUDA(c, cudaFuncSetAttribute(k_normals_quad, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   (int)(quad_smem_per_warp(kTierCapHost[kQuadTiers - 1]) * (kQuadThreads / 32))));
   AG2_CUDA(c, cudaEventRecord(c->ev_fork, st));
   for (int i = 0; i < 4; i++) AG2_CUDA(c, cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
   int used = 0;
   // dense tiers first: their launches run longest
   for (int k = 0; k < kAllTiers; k++) {
     const int tier = kAllTiers - 1 - k;
-    if (!cnt[tier]) continue;
-    cudaStream_t s2 = c->aux[used++ & 3];
+    // a tier above c's densest possible neighbourhood cannot hold a point: a cloud of n points has no
+    // neighbourhood larger than n (keeps the launch count of small scenes down)
+    if (tier > 0 && kTierCapHost[tier - 1] >= n) continue;
     const uint32_t* list = c->tier_list.p + (size_t)tier * owned;
-    if (tier < (int)quad_tiers && cnt[tier] >= quad_min) {
-      AG2_TRY(launch_normals_quad(c, s2, cnt[tier], kTierCapHost[tier], list));
-    } else if (tier >= cta_from) {
-      AG2_TRY(launch_normals_cta(c, s2, cnt[tier], std::min(kTierCapHost[tier], cap_max), list,
-                                 c->tier_cnt.p + 16 + tier));
-    } else {
-      const uint32_t cap = std::min(kTierCapHost[tier], cap_max);
-      AG2_TRY(launch_normals(c, s2, cnt[tier], cap, list, c->tier_cnt.p + 30, c->tier_cnt.p + 31, 0,
-                             c->tier_cnt.p + 16 + tier));
+    const uint32_t* n_dev = c->tier_cnt.p + tier;
+    const uint32_t cap = kTierCapHost[tier];
+    if (tier >= cta_from || tier >= 12) {  // above 1024 neighbours only the CTA kernel has the shared memory
+      const bool unlikely = tier >= 12 && kTierCapHost[tier - 1] >= 2u * std::max(c->max_kn_hint, 512u);
+      AG2_TRY(launch_normals_cta(c, c->aux[used++ & 3], owned, n_dev, cap, list, c->tier_cnt.p + 16 + tier, unlikely));
+      continue;
     }
+    const bool quad = tier < (int)quad_tiers;
+    if (quad) AG2_TRY(launch_normals_quad(c, c->aux[used++ & 3], owned, n_dev, quad_min, cap, list));
+    // the warp-per-point launch of a quad tier only runs when the tier is too short for k_normals_quad
+    AG2_TRY(launch_normals(c, c->aux[used++ & 3], owned, n_dev, quad ? quad_min : 0u, cap, list, nullptr, nullptr, 0,
+                           c->tier_cnt.p + 16 + tier));
   }
   for (int i = 0; i < std::min(used, 4); i++) {
     AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
     AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
   }
-  k_eigen<<<std::max(1u, (((owned + 31) & ~31u) + 255) / 256), 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
-                                                               (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
-  AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }
 
-int normals_compute(ag2_ctx* c) {
-  AG2_TRY(grid_build(c));
-  if (c->have_normals) return AG2_OK;
-  phase_begin(c, 1);
+// Chained capacity levels on the warp-per-point kernel (the path before the tiers existed; test /
+// measurement hook AG2_NORMALS_WARP=1, and clouds of more than 2^27 points).
+static int normals_moments_chained(ag2_ctx* c) {
   cudaStream_t st = c->stream;
   GridDev g = grid_dev(c);
   const uint32_t n = (uint32_t)c->n_finite;
-  // test / measurement hook: AG2_NORMALS_WARP=1 runs every point on the warp-per-point kernel, in
-  // capacity levels chained through overflow lists (the path before the tiers existed)
-  const char* warp_only = getenv("AG2_NORMALS_WARP");
-  if (!(warp_only && atoi(warp_only) != 0) && n <= (1u << 27)) {
-    AG2_TRY(normals_compute_tiered(c));
-    c->have_normals = true;
-    phase_end(c, 1);
-    return AG2_OK;
-  }
   AG2_CUDA(c, c->kn.reserve(n));
   AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));    // [8] max, [10..11] sum
@@ -1209,7 +1278,7 @@ int normals_compute(ag2_ctx* c) {
   c->st.sum_neighbors_normals = (int64_t)sum;
   const uint32_t cap_max = (std::max(max_kn, 32u) + 31u) & ~31u;
   if (normals_smem(cap_max).total > 220 * 1024) {
-    c->err = "normals: a point has more than ~11000 neighbours within normals_radius";
+    c->err = "normals: a point has more than ~13600 neighbours within normals_radius";
     return AG2_E_CAPACITY;
   }
   // Capacity levels: each launch runs at the smallest tier that leaves at most 25 % of its
@@ -1233,21 +1302,35 @@ int normals_compute(ag2_ctx* c) {
       }
     DevBuf<uint32_t>& out = c->big_list[level & 1];
     if (left) AG2_CUDA(c, out.reserve(left));
-    AG2_TRY(launch_normals(c, st, remaining, cap, list, out.p, c->scalars.p + 40 + level, left,
+    AG2_TRY(launch_normals(c, st, remaining, nullptr, 0, cap, list, out.p, c->scalars.p + 40 + level, left,
                            c->scalars.p + 48 + level));
     list = out.p;
     remaining = left;
     level++;
   }
-  {
-    const uint32_t own = normals_shard_points(n, c->nrm_rank, c->nrm_world);
-    k_eigen<<<std::max(1u, (((own + 31) & ~31u) + 255) / 256), 256, 0, st>>>(g, c->kn.p, c->nrm_mom.p, c->nrm.p,
-                                                               (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
-    AG2_LAUNCH_CHECK(c);
-  }
+  return AG2_OK;
+}
+
+int normals_moments(ag2_ctx* c) {
+  AG2_TRY(grid_build(c));
+  if (c->have_normals) return AG2_OK;
+  phase_begin(c, 1);
+  const char* warp_only = getenv("AG2_NORMALS_WARP");
+  if (!(warp_only && atoi(warp_only) != 0) && c->n_finite <= (1u << 27)) return normals_moments_tiered(c);
+  return normals_moments_chained(c);
+}
+
+int normals_finish(ag2_ctx* c) {
+  if (c->have_normals) return AG2_OK;
+  AG2_TRY(launch_eigen(c));
   c->have_normals = true;
   phase_end(c, 1);
   return AG2_OK;
+}
+
+int normals_compute(ag2_ctx* c) {
+  AG2_TRY(normals_moments(c));
+  return normals_finish(c);
 }
 
 }  // namespace ag2

@@ -1,28 +1,13 @@
-"""Multi-GPU host: one process per GPU, samples sharded, grasps all-gathered.
+"""Host logic of the sample sharding, restated in Python for the CPU tests.
 
-The path shards by grasp sample (samples are independent in every stage after the
-normals; reference hand_search.cpp:118,194, learning.cpp:12).  Per detect call:
-
-  1. rank 0 holds the cloud; xyz (12 B/pt) + camera mask (1 B/pt) + the sample list are
-     broadcast with torch.distributed (NCCL over NVLink on GPUs);
-  2. every rank builds the identical cell index (cheaper than shipping it) and evaluates the
-     STRIDED shard rank, rank + world, ... of the sample list (sample lists are sorted by point
-     index, i.e. spatially coherent: contiguous blocks would give the ranks different parts of
-     the scene and unequal work); `set_sample_id_map(rank, world)` keeps the counter-based draws
-     identical to a single-GPU run of the whole list;
-  3. per-rank antipodal lists (192-byte records) are all-gathered (counts first, then
-     records padded to the maximum count) and the global top-`num_selected` is taken with the
-     same ordering rule as the single-GPU path (score descending, list order on ties).  When a
-     top-k is requested the global top-k lies inside the union of the per-rank top-k lists, so
-     each rank contributes its SELECTED list in one fixed-size all-gather.
-
-On GPUs the whole exchange stays in device memory: ONE broadcast of a packed input buffer
-(`pack_inputs`: xyz | camera mask | samples in one allocation), the sample block handed to the
-library by device pointer, the selected records copied device-to-device into the all-gather send
-buffer, one device->host read of the gathered records at the end.
-
-There is no other data-path collective.  The same code runs over `gloo` with CPU tensors for
-the world_size-2 CPU tests (tests drive it with the oracle context; the product uses libag2).
+The multi-GPU data path is native: csrc/group.cu behind ag2_group_* (include/ag2.h) owns the NCCL
+communicator, the peer-memory windows and the exchanges; `capi.Group` binds it and bench.py /
+tests/multi_gpu_check.py call that.  This module keeps the SAME host logic -- strided sample shards
+(rank, rank + world, ...), `set_sample_id_map(rank, world)` so that a shard draws like the whole list,
+per-rank top-k lists merged with the single-GPU ordering rule (grasp_detector.cpp:238-252), importance-sampling
+rounds in which every rank draws the same batch from the merged hands -- over `torch.distributed` with CPU
+tensors, so that the world_size-2 `gloo` tests can run it against the oracle context on a box without GPUs
+(tests/test_sharded_gloo.py).  It is not on the product's GPU path.
 """
 from __future__ import annotations
 
@@ -60,32 +45,9 @@ def merge_selected(parts, num_selected: int, keep_all: bool = False) -> np.ndarr
     return allh[order]
 
 
-def pack_inputs(xyz, cam, samples, device):
-    """One device allocation holding xyz [N,3] f32 | samples [S] i32 | cam [N] u8 (4-byte aligned
-    sections); returns (packed u8 tensor, xyz view, cam view, samples view).  Rank 0 keeps its
-    resident cloud in this form so that a detect call needs a single broadcast."""
-    n, s = int(xyz.shape[0]), int(samples.shape[0])
-    packed = torch.empty(12 * n + 4 * s + n, dtype=torch.uint8, device=device)
-    xv = packed[: 12 * n].view(torch.float32).view(n, 3)
-    sv = packed[12 * n: 12 * n + 4 * s].view(torch.int32)
-    cv = packed[12 * n + 4 * s:]
-    if xyz is not None:
-        xv.copy_(torch.as_tensor(xyz).reshape(n, 3), non_blocking=True)
-        sv.copy_(torch.as_tensor(samples), non_blocking=True)
-        cv.copy_(torch.as_tensor(cam), non_blocking=True)
-    return packed, xv, cv, sv
-
-
-def _packed_views(packed, n, s):
-    return (packed[: 12 * n].view(torch.float32).view(n, 3), packed[12 * n + 4 * s:],
-            packed[12 * n: 12 * n + 4 * s].view(torch.int32))
-
-
 class ShardedDetector:
-    def __init__(self, ctx: capi.Context, rank: int = 0, world: int = 1, device=None, group=None,
-                 shard_normals: bool = True):
+    def __init__(self, ctx: capi.Context, rank: int = 0, world: int = 1, device=None, group=None):
         self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
-        self.shard_normals = shard_normals  # GPU fast path: normals computed 1/world per rank + all-gather
         self.device = device if device is not None else torch.device("cpu")
 
     # ---- collectives -----------------------------------------------------------------
@@ -223,101 +185,6 @@ class ShardedDetector:
             offset += len(pts)
             hands = np.concatenate([hands, sel])
         return hands
-
-    def detect_device(self, xyz_d, cam_d, num_cams, samples_d, shape_hint=None):
-        """Cloud resident in HBM on rank 0 (torch CUDA tensors)."""
-        xyz_d, cam_d, num_cams, samples_d = self._broadcast_inputs(xyz_d, cam_d, num_cams, samples_d, shape_hint)
-        if self.world > 1:
-            torch.cuda.current_stream().synchronize()
-        self.ctx.set_cloud_device(xyz_d.data_ptr(), xyz_d.shape[0], cam_d.data_ptr(), num_cams)
-        return self._run_block(samples_d.cpu().numpy())
-
-    def detect_packed(self, packed_d, n, s, num_cams):
-        """GPU fast path.  packed_d: the `pack_inputs` buffer (valid on rank 0, a same-sized receive
-        buffer elsewhere); (n, s, num_cams) known on every rank.  One broadcast, device-resident
-        sample block, device-side all-gather of the per-rank top-k."""
-        import time
-        p = self.ctx.params
-        topk = p.num_selected > 0 and p.antipodal_mode != capi.MODE_NONE
-        t0 = time.perf_counter()
-        if self.world > 1:
-            dist.broadcast(packed_d, src=0, group=self.group)
-            torch.cuda.current_stream().synchronize()
-        t1 = time.perf_counter()
-        xyz_d, cam_d, smp_d = _packed_views(packed_d, n, s)
-        if not topk:  # unbounded lists: the general path
-            self.ctx.set_cloud_device(xyz_d.data_ptr(), n, cam_d.data_ptr(), num_cams)
-            return self._run_block(smp_d.cpu().numpy())
-        self.ctx.set_cloud_device(xyz_d.data_ptr(), n, cam_d.data_ptr(), num_cams)
-        if self.world > 1 and self.shard_normals:
-            # the normals of the whole cloud are needed by every rank: each computes 1/world of them
-            # (interleaved 32-point granules of the cell-sorted cloud), one all-gather installs the rest
-            cap = self.ctx.normals_shard_points(self.world)
-            if getattr(self, "_nrm_cap", None) != cap:
-                self._nrm_tx = torch.empty(cap * 4, dtype=torch.float32, device=self.device)
-                self._nrm_rx = torch.empty(self.world * cap * 4, dtype=torch.float32, device=self.device)
-                self._nrm_cap = cap
-            self.ctx.compute_normals_shard(self.rank, self.world, self._nrm_tx.data_ptr(), cap)
-            dist.all_gather_into_tensor(self._nrm_rx, self._nrm_tx, group=self.group)
-            torch.cuda.current_stream().synchronize()
-            self.ctx.set_normals_shards(self._nrm_rx.data_ptr(), cap, self.world)
-        t1b = time.perf_counter()
-        mine = smp_d[self.rank::self.world].contiguous() if self.world > 1 else smp_d
-        n_mine = shard_size(s, self.world, self.rank)
-        if self.world > 1:
-            torch.cuda.current_stream().synchronize()
-        self.ctx.set_sample_indices_device(mine.data_ptr(), n_mine)
-        self.ctx.set_sample_id_map(self.rank, self.world)
-        rec, cap = capi.HYPOTHESIS_DTYPE.itemsize, p.num_selected
-        if getattr(self, "_tx_cap", None) != cap:
-            self._tx = torch.empty(cap * rec, dtype=torch.uint8, device=self.device)
-            self._rxg = torch.empty(self.world * cap * rec, dtype=torch.uint8, device=self.device)
-            self._tx_cap = cap
-        if self.world == 1:  # one rank: the device ranking already is the final order, read it directly
-            self.ctx.detect()
-            out = self.ctx.hypotheses(capi.LIST_SELECTED)
-            t2 = time.perf_counter()
-            self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
-                            "gather": 0.0}
-            return out
-        if n_mine:
-            self.ctx.detect()
-            self.ctx.copy_hypotheses_device(capi.LIST_SELECTED, self._tx.data_ptr(), cap)
-        else:
-            self._tx.zero_()
-            torch.cuda.current_stream().synchronize()
-        t2 = time.perf_counter()
-        dist.all_gather_into_tensor(self._rxg, self._tx, group=self.group)
-        allr = self._rxg.cpu().numpy().view(capi.HYPOTHESIS_DTYPE).reshape(self.world, cap)
-        t3 = time.perf_counter()
-        # host-side wall time of the three segments of the last call (ms): input exchange, local
-        # detect (includes waiting for nothing but this rank's GPU), result exchange
-        self.last_ms = {"bcast": (t1 - t0) * 1e3, "normals": (t1b - t1) * 1e3, "detect": (t2 - t1b) * 1e3,
-                        "gather": (t3 - t2) * 1e3}
-        return capi.merge_selected_blocks(allr, p.num_selected)  # native: the same rule as merge_selected
-
-    def detect_host(self, xyz_h, cam_h, num_cams, samples_h, shape_hint=None):
-        """Host buffers (pinned torch CPU tensors on rank 0): H2D inside the call."""
-        if self.world == 1:
-            self.ctx.set_cloud(xyz_h.numpy(), cam_h.numpy(), num_cams)
-            return self._run_block(samples_h.numpy())
-        if shape_hint is not None:  # sizes known everywhere: stage into the packed buffer, one broadcast
-            n, s, num_cams = shape_hint
-            if getattr(self, "_pk_key", None) != (n, s):
-                self._pk = torch.empty(12 * n + 4 * s + n, dtype=torch.uint8, device=self.device)
-                self._pk_key = (n, s)
-            if self.rank == 0:
-                xv, cv, sv = _packed_views(self._pk, n, s)
-                xv.copy_(xyz_h, non_blocking=True)
-                cv.copy_(cam_h, non_blocking=True)
-                sv.copy_(samples_h, non_blocking=True)
-            return self.detect_packed(self._pk, n, s, num_cams)
-        if self.rank == 0:
-            xyz_d, cam_d, smp_d = (xyz_h.to(self.device, non_blocking=True), cam_h.to(self.device, non_blocking=True),
-                                   samples_h.to(self.device, non_blocking=True))
-        else:
-            xyz_d = cam_d = smp_d = None
-        return self.detect_device(xyz_d, cam_d, num_cams, smp_d, shape_hint)
 
     def detect_numpy(self, xyz, cam, num_cams, samples):
         """Backend-neutral entry (gloo CPU tests): numpy inputs on rank 0, None elsewhere."""

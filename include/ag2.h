@@ -201,7 +201,11 @@ int ag2_get_lenet_weights(ag2_ctx* ctx, float* conv1_w, float* conv1_b, float* c
  * for pcl::PointXYZRGBA).  cam_mask[i] bit c = point i seen by camera c
  * (camera_source_, cloud_camera.cpp:39-50); num_cams = rows of camera_source_.
  * normals_or_null: optional precomputed normals, 3 floats per point
- * (CloudCamera::getNormals, hand_search.cpp:20-29). Host pointers. */
+ * (CloudCamera::getNormals, hand_search.cpp:20-29). Host pointers.  The copies are asynchronous:
+ * PINNED host buffers must stay valid and unchanged until the next call on this ctx that returns
+ * results (any stage call synchronises); pageable buffers may be reused at once.
+ * Call order: the cloud first, then the samples -- a new cloud drops sample INDICES set before
+ * (they were validated against the old cloud; ag2_detect then returns AG2_E_NO_SAMPLES). */
 int ag2_set_cloud(ag2_ctx* ctx, const float* xyz, size_t stride_bytes, size_t n,
                   const uint8_t* cam_mask, int num_cams, const float* normals_or_null);
 /* Same with DEVICE pointers (packed xyz; used after an NCCL broadcast). */
@@ -317,6 +321,11 @@ int ag2_synchronize(ag2_ctx* ctx);
 /* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing. */
 int ag2_get_stream(ag2_ctx* ctx, void** stream);
 
+/* Measurement aid (no reference counterpart): FMA throughput of this ctx's GPU right now, in TFLOP/s --
+ * the denominators of the issue-bound rooflines bench.py reports for the normals and hand-sweep kernels
+ * ("FP64 peak from a same-run FMA microbenchmark"). */
+int ag2_measure_fp_peaks(ag2_ctx* ctx, double* fp32_tflops, double* fp64_tflops);
+
 /* ---- outputs ------------------------------------------------------------- */
 
 enum {
@@ -373,6 +382,59 @@ int ag2_serialize_grasp_list(const ag2_hypothesis* hands, size_t n, uint32_t seq
  * (grasp_detector.cpp:238-252; num_selected <= 0 keeps all).  Host-only, needs no ctx.  out: world * cap records. */
 int ag2_merge_selected(const ag2_hypothesis* blocks, int world, size_t cap, int num_selected, ag2_hypothesis* out,
                        size_t* n_out);
+
+
+/* ---- multi-GPU: the same path over 1..8 GPUs of one box --------------------------
+ * The reference's caller hands ONE cloud to GraspDetector::detectGraspPoses /
+ * ImportanceSampling::detectGraspPoses (grasp_detection_node.cpp:109-115,135-138) and gets one list
+ * back; its only parallelism is OpenMP over samples (hand_search.cpp:118,194).  A group keeps that
+ * contract over several GPUs: rank 0 supplies the cloud and the sample list, every rank returns the
+ * same merged selection, byte for byte what one GPU returns for the whole list.  Inside, the path
+ * is sharded by grasp sample (strided shards), the normals by 32-point granules of the cell-sorted
+ * cloud, and the exchanges run on peer memory over NVLink: ranks pull rank 0's staged cloud, the
+ * normals kernel stores each result into the arrays of all ranks, the selected records are stored
+ * into every rank's result window; device-side flags order the steps, no host synchronisation
+ * between ranks.  NCCL bootstraps the group and is the fallback transport (AG2_GROUP_NCCL=1).
+ * One rank = one GPU = one ag2_ctx (classifier weights are set on the ctx of every LOCAL rank). */
+typedef struct ag2_group ag2_group;
+typedef struct ag2_group_id { unsigned char bytes[128]; } ag2_group_id;  /* an ncclUniqueId */
+
+/* One process, n_gpus ranks on devices 0..n_gpus-1, one host thread per GPU inside the library.
+ * This is what the C++ shim's GraspDetector uses when Params::num_gpus > 1. */
+int ag2_group_create(const ag2_params* p, int n_gpus, ag2_group** out);
+/* One process per rank (torchrun, mpirun): rank 0 calls ag2_group_unique_id and hands the id to the
+ * others by any channel; then every rank calls ag2_group_create_rank (collective). */
+int ag2_group_unique_id(ag2_group_id* out);
+int ag2_group_create_rank(const ag2_params* p, const ag2_group_id* id, int rank, int world, int device,
+                          ag2_group** out);
+int ag2_group_destroy(ag2_group* g);
+int ag2_group_size(const ag2_group* g, int* world, int* n_local);
+/* ctx of the i-th LOCAL rank: weights (ag2_set_lenet_weights ...), ag2_get_stats, ag2_get_stream. */
+int ag2_group_local_ctx(ag2_group* g, int i, ag2_ctx** ctx);
+const char* ag2_group_last_error(const ag2_group* g);
+/* 1 when the exchanges run on peer memory (NVLink loads / stores), 0 on the NCCL fallback; valid after
+ * the first detect call. */
+int ag2_group_transport(const ag2_group* g, int* peer_stores);
+/* Bytes the FIRST local rank moved between host and device in the last call (cloud + samples in, result
+ * window out); every other rank of a multi-process group reports h2d = 0. */
+int ag2_group_io_bytes(const ag2_group* g, size_t* h2d, size_t* d2h);
+/* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) over the group.  Collective when ranks are
+ * processes: every rank calls it with the same n, num_cams, n_samples; xyz (packed, 3 floats per point),
+ * cam_mask (or NULL) and samples (indices into the cloud) are read on rank 0 only -- host pointers, or
+ * device pointers on rank 0's GPU when on_device != 0.  out: the merged selection (top num_selected by
+ * score, ties in (sample, orientation) order), identical on every rank; sample_id counts in the
+ * caller's list. */
+int ag2_group_detect(ag2_group* g, const float* xyz, size_t n, const uint8_t* cam_mask, int num_cams,
+                     const int32_t* samples, size_t n_samples, int on_device, ag2_hypothesis* out, size_t cap,
+                     size_t* n_out);
+/* ImportanceSampling::detectGraspPoses (importance_sampling.cpp:30-112) over the group: the cloud, its
+ * index and its normals stay resident on every rank; every round's samples are sharded like a plain
+ * call and all ranks draw the same next batch from the merged hands.  out: the hands of all rounds
+ * (ag2_detect_importance's AG2_LIST_IMPORTANCE), or their clusters when params.min_inliers > 0
+ * (:105-109). */
+int ag2_group_detect_importance(ag2_group* g, const float* xyz, size_t n, const uint8_t* cam_mask, int num_cams,
+                                const int32_t* samples, size_t n_samples, int on_device, const ag2_is_params* ip,
+                                ag2_hypothesis* out, size_t cap, size_t* n_out);
 
 #ifdef __cplusplus
 }

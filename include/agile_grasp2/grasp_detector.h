@@ -9,6 +9,8 @@
 
 #include <ag2.h>
 
+#include <algorithm>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -30,9 +32,12 @@ class GraspDetector {
     std::vector<double> gripper_width_range;  // [0.03, 0.07]
     uint64_t rng_seed = 0;
     bool prune = true;  // false when the sample_indices param is set (:150-160)
+    // new: GPUs of this box the detect calls are sharded over (ag2_group_create; one host thread per GPU inside
+    // the library, exchanges on NVLink peer memory).  1 = the single-GPU ctx.  Results do not depend on it.
+    int num_gpus = 1;
   };
 
-  explicit GraspDetector(const Params& prm) : prm_(prm), ctx_(nullptr), use_incoming_samples_(false) {
+  explicit GraspDetector(const Params& prm) : prm_(prm), ctx_(nullptr), group_(nullptr), use_incoming_samples_(false) {
     ag2_default_params(&p_);
     if (prm.workspace.size() == 6)
       for (int i = 0; i < 6; i++) p_.workspace[i] = prm.workspace[i];
@@ -60,17 +65,24 @@ class GraspDetector {
       p_.max_aperture = prm.gripper_width_range[1];
     }
     ag2shim::check(ag2_create(&p_, 0, &ctx_), "ag2_create");
-    if (p_.antipodal_mode == AG2_MODE_PREDICTION) {  // new Classifier(...), grasp_detector.cpp:55
-      int rc = prm.trained_file.empty() ? ag2_init_lenet_xavier(ctx_, 1)
-                                        : ag2_load_lenet_caffemodel(ctx_, prm.trained_file.c_str());
+    loadClassifier(ctx_);
+    if (prm.num_gpus > 1) {
+      int rc = ag2_group_create(&p_, prm.num_gpus, &group_);
       if (rc != AG2_OK) {
-        std::string msg = "GraspDetector: cannot load " + prm.trained_file + ": " + ag2_last_error(ctx_);
         ag2_destroy(ctx_);
-        throw std::runtime_error(msg);
+        ag2shim::check(rc, "ag2_group_create");
+      }
+      for (int i = 0; i < prm.num_gpus; i++) {
+        ag2_ctx* rc_ctx = nullptr;
+        ag2_group_local_ctx(group_, i, &rc_ctx);
+        loadClassifier(rc_ctx);
       }
     }
   }
-  virtual ~GraspDetector() { ag2_destroy(ctx_); }
+  virtual ~GraspDetector() {
+    ag2_group_destroy(group_);
+    ag2_destroy(ctx_);
+  }
   GraspDetector(const GraspDetector&) = delete;
   GraspDetector& operator=(const GraspDetector&) = delete;
 
@@ -94,6 +106,8 @@ class GraspDetector {
       return std::vector<GraspHypothesis>();  // :86-91
     ag2_params p = p_;
     if (!clusters_grasps) p.min_inliers = 0;
+    if (group_ && !use_incoming_samples_ && p.min_inliers == 0 && cloud_cam.getNormals().cols() == 0)
+      return detectOnGroup(cloud_cam, nullptr);
     ag2shim::check(ag2_set_params(ctx_, &p), "ag2_set_params", ctx_);
     ag2shim::upload(ctx_, cloud_cam, use_incoming_samples_);
     int rc = ag2_detect(ctx_);
@@ -111,9 +125,43 @@ class GraspDetector {
   }
 
  protected:
+  void loadClassifier(ag2_ctx* c) {
+    if (p_.antipodal_mode != AG2_MODE_PREDICTION) return;  // new Classifier(...), grasp_detector.cpp:55
+    int rc = prm_.trained_file.empty() ? ag2_init_lenet_xavier(c, 1) : ag2_load_lenet_caffemodel(c, prm_.trained_file.c_str());
+    if (rc != AG2_OK) {
+      std::string msg = "GraspDetector: cannot load " + prm_.trained_file + ": " + ag2_last_error(c);
+      ag2_group_destroy(group_);
+      ag2_destroy(ctx_);
+      throw std::runtime_error(msg);
+    }
+  }
+  // the same call over all GPUs of the group (index samples, normals computed by the path); ip != 0: the
+  // importance-sampling rounds
+  std::vector<GraspHypothesis> detectOnGroup(const CloudCamera& cc, const ag2_is_params* ip) {
+    const CloudCamera::PointCloudRGB& cloud = cc.getCloudProcessed();
+    const std::vector<uint8_t> mask = cc.cameraMask();
+    const std::vector<int32_t> idx(cc.getSampleIndices().begin(), cc.getSampleIndices().end());
+    if (idx.empty()) return std::vector<GraspHypothesis>();
+    const size_t per_call = p_.num_selected > 0 && p_.antipodal_mode != AG2_MODE_NONE ? (size_t)p_.num_selected
+                                                                                       : idx.size() * (size_t)p_.num_orientations;
+    size_t cap = per_call, n = 0;
+    if (ip) cap = per_call + (size_t)ip->num_iterations * std::max<size_t>(per_call, (size_t)ip->num_samples * p_.num_orientations);
+    std::vector<ag2_hypothesis> rec(cap ? cap : 1);
+    int rc = ip ? ag2_group_detect_importance(group_, cloud.xyz.data(), cloud.size(), mask.data(), cc.getCameraSource().rows(),
+                                              idx.data(), idx.size(), 0, ip, rec.data(), rec.size(), &n)
+                : ag2_group_detect(group_, cloud.xyz.data(), cloud.size(), mask.data(), cc.getCameraSource().rows(),
+                                   idx.data(), idx.size(), 0, rec.data(), rec.size(), &n);
+    if (rc != AG2_OK) throw std::runtime_error(std::string("ag2_group_detect: ") + ag2_strerror(rc) + ": " + ag2_group_last_error(group_));
+    std::vector<GraspHypothesis> out;
+    out.reserve(n);
+    for (size_t i = 0; i < n; i++) out.push_back(GraspHypothesis(rec[i], nullptr));
+    return out;
+  }
+
   Params prm_;
   ag2_params p_;
   ag2_ctx* ctx_;
+  ag2_group* group_;
   bool use_incoming_samples_;
 };
 
@@ -125,6 +173,8 @@ class ImportanceSampling : public GraspDetector {
   // importance_sampling.cpp:30-112 (the unconditional plot at :103 is left out: no graphics stack)
   std::vector<GraspHypothesis> detectGraspPoses(const CloudCamera& cloud_cam_in, bool /*clusters*/ = true) override {
     if (cloud_cam_in.getCloudProcessed().size() == 0) return std::vector<GraspHypothesis>();
+    ip_.seed = prm_.rng_seed;
+    if (group_ && !use_incoming_samples_ && cloud_cam_in.getNormals().cols() == 0) return detectOnGroup(cloud_cam_in, &ip_);
     ag2shim::check(ag2_set_params(ctx_, &p_), "ag2_set_params", ctx_);
     ag2shim::upload(ctx_, cloud_cam_in, use_incoming_samples_);
     ip_.seed = prm_.rng_seed;

@@ -102,3 +102,16 @@ def _fill_unit_box(h, dens, start):
             pts.append(list(p)); nrm.append(ncol[:, i // 2].copy())
             p[var[i]] += spacing
     return np.array(pts).reshape(-1, 3), np.array(nrm).reshape(-1, 3)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif("__import__('torch').cuda.device_count() < 2")
+def test_cpp_group_two_gpus_equals_one(tiny_scene, tmp_path):
+    """tests/cpp/test_group.cpp: GraspDetector / ImportanceSampling with Params::num_gpus = 2 (ag2_group_create:
+    host threads inside libag2, NVLink peer memory) against the same calls on one GPU, byte for byte."""
+    binp = os.path.join(ROOT, "tests", "cpp", "test_group")
+    assert os.path.exists(binp), "build tests/cpp first (__graft_entry__.build())"
+    pcd = str(tmp_path / "cloud.pcd")
+    capi.pcd_write(pcd, tiny_scene["xyz"], binary=True)
+    r = subprocess.run([binp, pcd, "120", "2"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "TEST_GROUP OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

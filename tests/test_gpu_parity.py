@@ -321,24 +321,24 @@ def test_importance_sampling_rounds(tiny_scene, method):
 
 
 @pytest.mark.parametrize("mode", [capi.MODE_NONE, capi.MODE_PREDICTION])
-def test_importance_rounds_driven_by_the_sharded_host(tiny_scene, mode):
-    """The multi-GPU host runs the rounds itself (ag2_draw_importance_samples + one sharded detect per
-    round); with one rank the result is the list ag2_detect_importance builds."""
-    from agile_grasp2_b200 import sharded
+def test_importance_rounds_driven_by_the_group_host(tiny_scene, mode):
+    """The multi-GPU host (ag2_group_detect_importance, csrc/group.cu) runs the rounds itself
+    (ag2_draw_importance_samples + one sharded detect per round); with one rank the result is the list
+    ag2_detect_importance builds."""
     sc = tiny_scene
     p = make_params(mode, num_selected=12, min_score_diff=-1e9)
-    with capi.Context(p) as a, capi.Context(p) as b:
-        a.init_lenet_xavier(3); b.init_lenet_xavier(3)
+    with capi.Context(p) as a, capi.Group(p, rank=0, world=1, device=0) as grp:
+        a.init_lenet_xavier(3); grp.init_lenet_xavier(3)
         ip = a.default_is_params()
         ip.num_iterations, ip.num_samples, ip.seed = 3, 40, 9
         a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"])
         a.detect_importance(ip)
         want = a.hypotheses(capi.LIST_IMPORTANCE)
-        got = sharded.ShardedDetector(b).detect_importance_numpy(sc["xyz"], sc["cam_mask"], sc["num_cams"],
-                                                                  sc["samples"], ip)
+        got = grp.detect_importance(sc["xyz"], sc["cam_mask"], sc["num_cams"], sc["samples"], ip)
         assert got.tobytes() == want.tobytes(), (len(got), len(want))
         assert len(want) > 12
         # the drawn batches themselves
+        b = grp.local_ctx(0)
         for r in range(3):
             upto = want[want["sample_id"] < len(sc["samples"]) + 40 * r]
             assert np.array_equal(b.draw_importance_samples(ip, r, upto), a.importance_samples(r)), r
@@ -398,28 +398,62 @@ def test_detect_with_clustering(dense_scene):
     assert np.all(np.diff(gs["score"]) <= 0)
 
 
-def test_sharded_packed_path_world1(tiny_scene):
-    """The multi-GPU fast path (packed input buffer, device-resident sample block, device copy of the
-    selected records) at world size 1 returns exactly what ag2_detect + ag2_get_hypotheses return."""
+def test_group_of_one_rank_equals_plain_detect(tiny_scene):
+    """ag2_group_detect at world size 1 -- inputs staged in the exchange window, sample shard taken on the
+    device, normals written into the window-backed array, selected records read from the result path -- returns
+    exactly what ag2_detect + ag2_get_hypotheses return, with host pointers and with device pointers."""
     import torch
-    from agile_grasp2_b200 import sharded
     sc = tiny_scene
     p = make_params(capi.MODE_PREDICTION, min_score_diff=-1e9, num_selected=20)
-    a, b = capi.Context(p), capi.Context(p)
-    a.init_lenet_xavier(3); b.init_lenet_xavier(3)
-    a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"]); a.detect()
-    want = a.hypotheses(capi.LIST_SELECTED)
-    dev = torch.device("cuda", 0)
-    packed = sharded.pack_inputs(torch.from_numpy(sc["xyz"]), torch.from_numpy(sc["cam_mask"]),
-                                 torch.from_numpy(np.asarray(sc["samples"], np.int32)), dev)[0]
-    torch.cuda.synchronize()
-    run = sharded.ShardedDetector(b, rank=0, world=1, device=dev)
-    got = run.detect_packed(packed, len(sc["xyz"]), len(sc["samples"]), sc["num_cams"])
-    assert len(want) > 0 and got.tobytes() == want.tobytes()
-    assert np.array_equal(b.sample_indices(), np.asarray(sc["samples"], np.int32))
-    with pytest.raises(capi.Ag2Error):  # device-side range check
-        bad = torch.tensor([0, len(sc["xyz"])], dtype=torch.int32, device=dev)
-        b.set_sample_indices_device(bad.data_ptr(), 2)
+    with capi.Context(p) as a, capi.Group(p, rank=0, world=1, device=0) as grp:
+        a.init_lenet_xavier(3); grp.init_lenet_xavier(3)
+        a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"]); a.detect()
+        want = a.hypotheses(capi.LIST_SELECTED)
+        got = grp.detect(sc["xyz"], sc["cam_mask"], sc["num_cams"], sc["samples"])
+        assert len(want) > 0 and got.tobytes() == want.tobytes()
+        dev = torch.device("cuda", 0)
+        xd, cd = torch.from_numpy(sc["xyz"]).to(dev), torch.from_numpy(sc["cam_mask"]).to(dev)
+        sd = torch.from_numpy(np.asarray(sc["samples"], np.int32)).to(dev)
+        torch.cuda.synchronize()
+        for _ in range(2):  # the second call reuses windows, grid buffers and tier launches
+            got = grp.detect_ptr(xd.data_ptr(), len(sc["xyz"]), cd.data_ptr(), sc["num_cams"], sd.data_ptr(),
+                                 len(sc["samples"]), True)
+            assert got.tobytes() == want.tobytes()
+        assert grp.io_bytes()[0] == 0
+        assert np.array_equal(grp.local_ctx(0).sample_indices(), np.asarray(sc["samples"], np.int32))
+        # device-side range check of the sample shard
+        with pytest.raises(capi.Ag2Error):
+            grp.detect(sc["xyz"], sc["cam_mask"], sc["num_cams"], np.array([0, len(sc["xyz"])], np.int32))
+        # a smaller and a larger cloud through the same group (window regrowth)
+        half = len(sc["xyz"]) // 2
+        smp = np.asarray(sc["samples"], np.int32)
+        smp = smp[smp < half]
+        a.set_cloud(sc["xyz"][:half], sc["cam_mask"][:half], sc["num_cams"]); a.set_sample_indices(smp); a.detect()
+        assert grp.detect(sc["xyz"][:half], sc["cam_mask"][:half], sc["num_cams"], smp).tobytes() == \
+            a.hypotheses(capi.LIST_SELECTED).tobytes()
+    with capi.Context(p) as b:
+        b.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"])
+        with pytest.raises(capi.Ag2Error):  # device-side range check
+            bad = torch.tensor([0, len(sc["xyz"])], dtype=torch.int32, device=dev)
+            b.set_sample_indices_device(bad.data_ptr(), 2)
+
+
+@pytest.mark.skipif("__import__('torch').cuda.device_count() < 2")
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
+def test_group_of_two_gpus_in_one_process_equals_one_gpu(tiny_scene, monkeypatch, transport):
+    """ag2_group_create(n_gpus = 2): two ranks as host threads of this process, exchanges on peer memory (or
+    NCCL); the merged selection equals the single-GPU one byte for byte (runs where the box has two GPUs)."""
+    sc = tiny_scene
+    monkeypatch.setenv("AG2_GROUP_NCCL", "1" if transport == "nccl" else "0")
+    p = make_params(capi.MODE_PREDICTION, min_score_diff=-1e9, num_selected=20)
+    with capi.Context(p) as a, capi.Group(p, n_gpus=2) as grp:
+        a.init_lenet_xavier(3); grp.init_lenet_xavier(3)
+        a.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"]); a.set_sample_indices(sc["samples"]); a.detect()
+        want = a.hypotheses(capi.LIST_SELECTED)
+        for _ in range(2):
+            got = grp.detect(sc["xyz"], sc["cam_mask"], sc["num_cams"], sc["samples"])
+            assert got.tobytes() == want.tobytes()
+        assert grp.peer_stores() == (transport == "peer")
 
 
 @pytest.mark.parametrize("world", [1, 3, 8])
