@@ -146,6 +146,7 @@ struct ag2_ctx {
   // ctx stream (finish_pending) -- a stage that only needs a number for its statistics does not stall
   uint32_t* h_pin = nullptr;       // kPinWords words of pinned host memory
   bool pend_normals = false;       // h_pin[0..4]: max k_n, -, sum k_n (u64), points over the last tier capacity
+  bool normals_attr_set = false;   // dynamic shared-memory limits of the normals kernels raised on this device
   uint32_t max_kn_hint = 0;        // densest normals neighbourhood of the previous cloud (sizes speculative launches)
   float min_z = 0.f;               // pcl::getMinMax3D z (grasp_detector.cpp:153)
 

@@ -791,11 +791,15 @@ struct ag2_group {
     if (workers.empty()) return f(0);
     hb.reset();
     for (size_t i = 0; i < workers.size(); i++) workers[i]->submit([&f, i] { return f((int)i); });
+    // the first error wins, but a rank that only gave up because another one failed does not hide the cause
     int rc = AG2_OK;
+    bool secondary = true;
     for (size_t i = 0; i < workers.size(); i++) {
       const int r = workers[i]->join_job();
-      if (rc == AG2_OK && r != AG2_OK) {
+      const bool sec = r == AG2_E_STATE && ranks[i]->err.find("another rank") != std::string::npos;
+      if (r != AG2_OK && (rc == AG2_OK || (secondary && !sec))) {
         rc = r;
+        secondary = sec;
         err = "rank " + std::to_string(i) + ": " + ranks[i]->err;
       }
     }

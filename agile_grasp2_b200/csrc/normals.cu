@@ -1215,13 +1215,12 @@ static int normals_moments_tiered(ag2_ctx* c) {
   AG2_CUDA(c, cudaMemcpyAsync(c->h_pin, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));
   AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 4, c->tier_cnt.p + 32, 4, cudaMemcpyDeviceToHost, st));
   c->pend_normals = true;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!c->normals_attr_set) {  // per device, not per process: a group runs one ctx per GPU in one process
     AG2_CUDA(c, cudaFuncSetAttribute(k_normals_quad, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(quad_smem_per_warp(kTierCapHost[kQuadTiers - 1]) * (kQuadThreads / 32))));
     AG2_CUDA(c, cudaFuncSetAttribute(k_normals_cta, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)cta_smem(kTierCapHost[kAllTiers - 1]).total));
-    attr_set = true;
+    c->normals_attr_set = true;
   }
   AG2_CUDA(c, cudaEventRecord(c->ev_fork, st));
   for (int i = 0; i < 4; i++) AG2_CUDA(c, cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));

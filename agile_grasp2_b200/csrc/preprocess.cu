@@ -5,12 +5,17 @@
 //   workspace filter  flag (strict >, < on float coordinates promoted to double; NaN fails)
 //                     -> exclusive scan -> ordered compaction of xyz / camera mask / normals;
 //   voxelisation      min corner (float), voxel = floor((p - min) / (float)cell) per axis; the
-//                     reference inserts the voxels into a std::set ordered by (x, y, z) and
-//                     remembers the FIRST point of each voxel for its camera source.  Here a
-//                     direct-address table over the voxel box (id = (vx*ny + vy)*nz + vz, so
-//                     ascending id == the set's order) takes atomicMin(point index); occupied
-//                     entries are compacted in id order and emit the voxel corner
-//                     fl(fl((float)v * cell) + min) exactly as the reference's float expression;
+//                     reference inserts the voxels into a std::set ordered by (x, y, z) and pushes
+//                     the index of every point that OPENS a voxel onto idx_cam_source, i.e. in scan
+//                     order; it then gives the i-th voxel of the SORTED set the camera source of
+//                     idx_cam_source[i], the i-th opener in scan order -- not of the voxel's own
+//                     first point (cloud_camera.cpp:139-153).  That is what the reference computes,
+//                     so it is reproduced: a direct-address table over the voxel box
+//                     (id = (vx*ny + vy)*nz + vz, ascending id == the set's order) takes
+//                     atomicMin(point index); the openers (table[voxel(i)] == i) are compacted in
+//                     point order into first_seen[]; occupied entries are compacted in id order,
+//                     emit the voxel corner fl(fl((float)v * cell) + min) exactly as the
+//                     reference's float expression, and entry a takes cam[first_seen[a]];
 //   subsampling       uniform, without replacement, ascending (Vitter's algorithm A as in
 //                     pcl::RandomSample) with the counter-based RNG replacing rand() (D1).
 // Documented deviations: the reference's camera_source re-indexing in filterWorkspace uses
@@ -114,9 +119,25 @@ __global__ void k_vox_flag(const uint32_t* __restrict__ table, size_t ncells, ui
   if (i < ncells) flag[i] = table[i] != 0xFFFFFFFFu ? 1u : 0u;
 }
 
+// idx_cam_source (cloud_camera.cpp:139-141): the points that open a voxel, in scan order
+__global__ void k_vox_opener_flag(const float* __restrict__ xyz, size_t n, Vox v, const uint32_t* __restrict__ table,
+                                  uint32_t* __restrict__ flag) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  size_t id;
+  flag[i] = (voxel_of(v, xyz + 3 * i, id) && table[id] == (uint32_t)i) ? 1u : 0u;
+}
+__global__ void k_vox_opener_list(const float* __restrict__ xyz, size_t n, Vox v, const uint32_t* __restrict__ table,
+                                  const uint32_t* __restrict__ scan, uint32_t* __restrict__ first_seen) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  size_t id;
+  if (voxel_of(v, xyz + 3 * i, id) && table[id] == (uint32_t)i) first_seen[scan[i]] = (uint32_t)i;
+}
+
 __global__ void k_vox_emit(const uint32_t* __restrict__ table, const uint32_t* __restrict__ scan, size_t ncells,
-                           Vox v, const uint8_t* __restrict__ cam, float* __restrict__ xyz_out,
-                           uint8_t* __restrict__ cam_out) {
+                           Vox v, const uint8_t* __restrict__ cam, const uint32_t* __restrict__ first_seen,
+                           float* __restrict__ xyz_out, uint8_t* __restrict__ cam_out) {
   size_t id = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (id >= ncells) return;
   uint32_t a = scan[id], b = scan[id + 1];
@@ -128,7 +149,7 @@ __global__ void k_vox_emit(const uint32_t* __restrict__ table, const uint32_t* _
   xyz_out[3 * (size_t)a] = __fadd_rn(__fmul_rn((float)cx, v.cell), v.mn[0]);
   xyz_out[3 * (size_t)a + 1] = __fadd_rn(__fmul_rn((float)cy, v.cell), v.mn[1]);
   xyz_out[3 * (size_t)a + 2] = __fadd_rn(__fmul_rn((float)cz, v.cell), v.mn[2]);
-  cam_out[a] = cam[table[id]];  // camera source of the first point that fell into the voxel
+  cam_out[a] = cam[first_seen[a]];  // camera_source_(j, idx_cam_source[i]), i = position in the sorted set
 }
 
 }  // namespace
@@ -224,7 +245,15 @@ int preprocess_cloud(ag2_ctx* c, const float* xyz, size_t stride_bytes, size_t n
   AG2_CUDA(c, cudaStreamSynchronize(st));
   AG2_CUDA(c, v_xyz.reserve(3 * (size_t)std::max(nv, 1u)));
   AG2_CUDA(c, v_cam.reserve(std::max(nv, 1u)));
-  k_vox_emit<<<cb, kT, 0, st>>>(table.p, vflag.p, ncells, v, f_cam.p, v_xyz.p, v_cam.p);
+  // idx_cam_source: openers in point order (flag is free again: at least nf + 1 words)
+  DevBuf<uint32_t> first_seen;
+  AG2_CUDA(c, first_seen.reserve(std::max(nv, 1u)));
+  k_vox_opener_flag<<<(nf + kT - 1) / kT, kT, 0, st>>>(f_xyz.p, nf, v, table.p, flag.p);
+  AG2_LAUNCH_CHECK(c);
+  AG2_TRY(exclusive_scan_u32(c, flag.p, nf));
+  k_vox_opener_list<<<(nf + kT - 1) / kT, kT, 0, st>>>(f_xyz.p, nf, v, table.p, flag.p, first_seen.p);
+  AG2_LAUNCH_CHECK(c);
+  k_vox_emit<<<cb, kT, 0, st>>>(table.p, vflag.p, ncells, v, f_cam.p, first_seen.p, v_xyz.p, v_cam.p);
   AG2_LAUNCH_CHECK(c);
   AG2_TRY(ag2_set_cloud_device(c, v_xyz.p, nv, v_cam.p, num_cams, nullptr));
   AG2_CUDA(c, cudaStreamSynchronize(st));

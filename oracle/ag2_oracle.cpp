@@ -1452,7 +1452,8 @@ int ag2o_preprocess_cloud(ag2o_ctx* c, const float* xyz, size_t stride, size_t n
         return false;
       }
     };
-    std::map<std::array<int, 3>, size_t, Less> bins;  // set + idx_cam_source of the first insertion
+    std::map<std::array<int, 3>, size_t, Less> bins;  // the std::set (the mapped value is unused)
+    std::vector<size_t> idx_cam_source;               // :139-141: points that open a voxel, in scan order
     for (size_t i = 0; i < m; i++) {
       std::array<int, 3> v;
       bool finite = true;
@@ -1461,16 +1462,19 @@ int ag2o_preprocess_cloud(ag2o_ctx* c, const float* xyz, size_t stride, size_t n
         if (!(f == f)) finite = false;
         v[d] = finite ? (int)f : 0;
       }
-      if (finite) bins.insert(std::make_pair(v, i));  // keeps the first
+      if (finite && bins.insert(std::make_pair(v, i)).second) idx_cam_source.push_back(i);
     }
     std::vector<float> vp;
     std::vector<uint8_t> vc;
+    size_t vi = 0;
     for (const auto& kv : bins) {
       for (int d = 0; d < 3; d++) {
         float t = (float)kv.first[d] * cell;
         vp.push_back(t + mn[d]);
       }
-      vc.push_back(cm[kv.second]);
+      // :147-153 as written: the i-th voxel of the SORTED set takes the camera source of the i-th opener in
+      // scan order (idx_cam_source[i]), not of its own first point
+      vc.push_back(cm[idx_cam_source[vi++]]);
     }
     pts.swap(vp);
     cm.swap(vc);

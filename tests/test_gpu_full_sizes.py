@@ -151,3 +151,69 @@ def test_c4_full_size_importance_sampling():
     assert len(gh) == len(oh) and hyp_int_fields_equal(gh, oh) is None
     for f in POSE:
         assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+
+
+@pytest.fixture(scope="module")
+def c3_with_normals():
+    """The c3 cloud and its normals computed once on the GPU (checked against the oracle by test_c3_full_size)."""
+    sc = scenes.make_scene("c3")
+    with capi.Context(make_params(capi.MODE_GEOMETRIC)) as g:
+        g.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"])
+        g.compute_normals()
+        gn = g.normals().copy()
+    return sc, gn
+
+
+@pytest.mark.parametrize("R", [8, 16, 32])
+@pytest.mark.parametrize("radius", [0.06, 0.08, 0.10, 0.12])
+def test_c5_orientation_radius_sweep_on_the_clutter_cloud(c3_with_normals, R, radius):
+    """c5 (BASELINE.json configs[4]): num_orientations 8 -> 32 x nn_radius_hands 0.06 -> 0.12 on the c3 cloud.  The
+    complete sweep of a 40-sample strided subset against the oracle (the GPU's normals go in on both sides, which
+    isolates hand_search.cpp:173-235,319-426 / finger_hand.cpp / antipodal.cpp), every record field bit-exact,
+    poses to 1e-9 m.  R = 32 changes the shared-memory carve-up of k_hands (hands_smem_base), r = 0.06 the number of
+    cell rows per query and r = 0.12 the staging chunks."""
+    sc, gn = c3_with_normals
+    sub = np.ascontiguousarray(sc["samples"][11::250])
+    assert len(sub) == 40
+    p = make_params(capi.MODE_GEOMETRIC, num_threads=16, num_orientations=R, nn_radius_hands=radius)
+    g, o = capi.Context(p), ob.context(p)
+    for c in (g, o):
+        c.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"], normals=gn)
+        c.set_sample_indices(sub)
+        c.detect()
+    gsw, osw = g.sweep_records(), o.sweep_records()
+    assert gsw.shape == (40, R)
+    for f in ("fingers", "hand", "slot", "depth_step", "num_in_box", "antipodal", "emitted"):
+        assert np.array_equal(gsw[f], osw[f]), (f, R, radius)
+    for which in (capi.LIST_HYPOTHESES, capi.LIST_PRUNED, capi.LIST_ANTIPODAL, capi.LIST_SELECTED):
+        gh, oh = g.hypotheses(which), o.hypotheses(which)
+        assert len(gh) == len(oh) and hyp_int_fields_equal(gh, oh) is None, which
+        for f in POSE:
+            assert np.allclose(gh[f], oh[f], rtol=0, atol=1e-9), f
+    assert gsw["emitted"].sum() > 0
+    # K grows with the radius: the statistics the bench's roofline uses are the oracle's
+    gs, os_ = g.stats(), o.stats()
+    for k in ("sum_neighbors_hands", "sum_cropped", "sum_in_box", "num_hypotheses"):
+        assert gs[k] == os_[k], k
+    g.close()
+
+
+def test_c5_limits_of_the_orientation_and_depth_tables(tiny_scene=None):
+    """The largest tables k_hands accepts: AG2_MAX_ORIENTATIONS = 64 orientations and a deepen list of 61 steps
+    (hand_depth 0.31 from init_bite 0.01: shared memory base of ~40 KB per CTA).  Either it runs and matches the
+    oracle bit for bit, or it refuses with AG2_E_CAPACITY -- never a silent truncation; one step more than
+    AG2_MAX_DEEPEN_STEPS is rejected when the parameters are set."""
+    sc = scenes.make_scene("tiny", num_samples=12)
+    p = make_params(capi.MODE_GEOMETRIC, num_orientations=64, hand_depth=0.31, nn_radius_hands=0.12)
+    g, o = both(p, sc)
+    try:
+        g.detect()
+    except capi.Ag2Error as e:
+        assert e.code == capi.AG2_E_CAPACITY
+        return
+    o.detect()
+    gsw, osw = g.sweep_records(), o.sweep_records()
+    for f in ("fingers", "hand", "slot", "depth_step", "num_in_box", "antipodal", "emitted"):
+        assert np.array_equal(gsw[f], osw[f]), f
+    with pytest.raises(capi.Ag2Error):
+        capi.Context(make_params(capi.MODE_GEOMETRIC, hand_depth=0.33))

@@ -420,7 +420,9 @@ def test_group_of_one_rank_equals_plain_detect(tiny_scene):
                                  len(sc["samples"]), True)
             assert got.tobytes() == want.tobytes()
         assert grp.io_bytes()[0] == 0
-        assert np.array_equal(grp.local_ctx(0).sample_indices(), np.asarray(sc["samples"], np.int32))
+        b = grp.local_ctx(0)
+        b.n_samples = len(sc["samples"])
+        assert np.array_equal(b.sample_indices(), np.asarray(sc["samples"], np.int32))
         # device-side range check of the sample shard
         with pytest.raises(capi.Ag2Error):
             grp.detect(sc["xyz"], sc["cam_mask"], sc["num_cams"], np.array([0, len(sc["xyz"])], np.int32))
@@ -564,3 +566,61 @@ def test_normals_quad_per_point_and_warp_per_point_agree(tiny_scene, monkeypatch
     bit_equal = np.mean(np.all(out[0][ok].view(np.uint32) == on[ok].view(np.uint32), axis=1))
     print("%s: bit-equal fraction %.6f" % (scene, bit_equal))
     assert bit_equal > 0.999
+
+
+# ---- the known-answer scenes of tests/test_oracle_pins.py (hand-derived expectations there), GPU against oracle ----
+def _known_answer_scenes():
+    from common import cylinder_scene, shell_around, thin_box_scene
+    from test_oracle_pins import deepen_scene
+    cx, cn, cs = cylinder_scene()
+    bx, bn, bs = thin_box_scene()
+    sx, sn = shell_around(bs)
+    dx, dn, ds = deepen_scene()
+    return {
+        "cylinder": (cx, cn, cs, dict(nn_radius_taubin=0.01)),
+        "thin_box": (bx, bn, bs, dict(nn_radius_taubin=0.03)),
+        "below_hand_base": (np.concatenate([bx, sx]), np.concatenate([bn, sn]), bs, dict(nn_radius_taubin=0.03)),
+        "deepen_boundary": (dx, dn, ds, dict(nn_radius_taubin=0.03, init_bite=0.01, hand_depth=0.025)),
+    }
+
+
+@pytest.mark.parametrize("name", ["cylinder", "thin_box", "below_hand_base", "deepen_boundary"])
+def test_known_answer_scenes_gpu_equals_oracle(name):
+    xyz, nrm, sample, kw = _known_answer_scenes()[name]
+    p = make_params(capi.MODE_GEOMETRIC, prune=0, **kw)
+    g, o = capi.Context(p), ob.context(p)
+    for c in (g, o):
+        c.set_cloud(xyz, np.ones(len(xyz), np.uint8), 1, normals=nrm)
+        c.set_sample_points(sample[None, :])
+        c.detect()
+    _compare_run(g, o, check_normals=False)
+    gf, of = g.frames(), o.frames()
+    assert np.array_equal(gf["valid"], of["valid"]) and angle(gf["curvature_axis"], of["curvature_axis"]).max() <= 1e-6
+    gh = g.hypotheses()
+    if name == "below_hand_base":
+        assert len(gh) == 0 and np.all(g.sweep_records()["fingers"] == 0)
+    if name == "cylinder":
+        assert abs(gh[gh["full_antipodal"] == 1]["width"].max() - 0.06) < 1e-6
+    if name == "deepen_boundary":
+        assert gh["depth_step"].max() == 3 and gh["hand_top"].max() == 0.025
+    g.close()
+
+
+@pytest.mark.parametrize("aligns", [False, True])
+def test_image_cells_on_a_sixtieth_boundary_gpu_equals_oracle(aligns):
+    """learning.cpp:152-156 on the device: points on k/60, one ulp below and above, aliasing cells."""
+    rng = np.random.default_rng(12)
+    pts = []
+    for k in range(60):
+        pts.append([k / 60.0, ((7 * k) % 60) / 60.0, 0.5])
+        pts.append([np.nextafter(k / 60.0, 0.0) if k else 0.0, ((11 * k + 3) % 60) / 60.0, 0.25])
+        pts.append([np.nextafter(k / 60.0, 1.0), ((13 * k + 5) % 60) / 60.0, 0.75])
+    pts += [[1.0, 0.2, 0.5], [1.0 + 1.0 / 60, 0.3, 0.5], [0.5, 1.0 - 1e-12, 0.5], [0.5, 1.0, 0.5], [-1.0 / 60, 0.5, 0.5]]
+    pts = np.array(pts, np.float64)
+    nrm = rng.normal(size=pts.shape)
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    p = make_params()
+    with capi.Context(p) as g:
+        got = g.render_point_sets(pts, nrm, [0, len(pts)], aligns=aligns)[0]
+    want = ob.context(p).render_point_sets(pts, nrm, [0, len(pts)], aligns=aligns)[0]
+    assert np.array_equal(got, want), int(np.sum(got != want))
