@@ -82,6 +82,14 @@ struct SlotLut {
   double x0, xscale;                // bucket = (int)((x - x0) * xscale), clamped
 };
 
+// Device tables of the FP32 filter (uint32 words, uploaded by build_hand_const; layout shared with hands.cu):
+// a bucket entry is the answer itself (depth class / 20-slot mask) when no threshold is near the bucket, else
+// 0x80000000 | k for the ONE threshold k near it (compare against lo[k] / hi[k] = threshold -+ eps32, exact FP64
+// evaluation in between), or 0x80000000 | 0xFFFF when several thresholds are near (always exact).
+constexpr int kYLutBuckets = 256, kXLutBuckets = 1024;
+constexpr int kLutY = 0, kLutX = kLutY + kYLutBuckets, kLutYLo = kLutX + kXLutBuckets, kLutYHi = kLutYLo + 64,
+              kLutXLo = kLutYHi + 64, kLutXHi = kLutXLo + AG2_SLOT_EDGES, kLutWords = kLutXHi + AG2_SLOT_EDGES;
+
 struct HandConst {
   SlotLut lut;
   double fs_lo[20];   // finger_spacing_(i)
@@ -96,6 +104,10 @@ struct HandConst {
   double x_est_lo, x_est_inv_step;  // slot-index estimator (left half); exact fix-up follows
   int num_depths;             // D + 1 entries in depth[]
   int num_orientations;
+  // FP32 filter of the hand sweep (hands.cu): |x32 - x64| <= eps32 for hand-frame coordinates of staged points
+  float eps32;
+  float ylut_v0, ylut_scale;  // bucket = (int)((v - v0) * scale), clamped to the table
+  float xlut_v0, xlut_scale;
   float r2_hands;             // (float)(r*r)
   float rq_hands;             // query half-width with slack
   float r2_taubin, rq_taubin;
@@ -224,6 +236,7 @@ struct ag2_ctx {
 
   ag2::LeNetDev net;
   ag2::HandConst hc;
+  ag2::DevBuf<uint32_t> hands_lut;          // kLutWords words: tables of the FP32 filter of k_hands
   ag2_stats st;
   cudaEvent_t ev[18];
   bool ev_used[18];

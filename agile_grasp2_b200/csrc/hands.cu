@@ -22,7 +22,13 @@
 //    their ids to the in-box pool and reduces the antipodal statistics.
 // Neighbourhoods that exceed the staging buffer are processed in chunks; every
 // accumulator is associative (OR / min / max / count), so chunking is exact.
-// FP64 throughout, -fmad=false, same association order as the oracle.
+// FP32 filter, FP64 decision: every predicate of the sweep compares a hand-frame coordinate a . p (|a| = 1,
+// p a float difference shorter than the search radius) with a threshold.  The coordinate is first evaluated in
+// FP32 (three operations, error <= eps32, tables.cpp); a bucket table turns it into the depth class / slot mask /
+// in-box decision whenever it is farther than eps32 from every threshold, and only the rest (a fraction of 1e-3)
+// is redone in FP64 with -fmad=false in the oracle's association order.  Minima / maxima that end up in a record
+// (min y = grasp surface, x extent of the closing region) are taken exactly: FP32 finds the candidates within
+// 2 eps32 of the float extremum, FP64 evaluates those.  Results are bit-identical to the all-FP64 sweep.
 #include <math.h>
 #include <stdlib.h>
 
@@ -40,6 +46,7 @@ constexpr int kMaxDepths = AG2_MAX_DEEPEN_STEPS + 2;
 
 struct HandsArgs {
   GridDev g;
+  const uint32_t* lut;         // tables of the FP32 filter (kLutWords words, ag2_internal.h)
   const ag2_frame* frames;
   uint32_t cap;                // staging capacity (points)
   ag2_sweep_record* sweeps;    // S*R
@@ -71,6 +78,9 @@ __device__ __forceinline__ int depth_class(double y, const double* thr, int n, d
 // Per-orientation state (shared memory, one per orientation of this launch).
 struct Orient {
   double FRx[3], FRy[3];  // frame_rot columns 0 (closing direction) and 1 (approach)
+  float fx[3], fy[3];     // the same rounded to float: coefficients of the FP32 filter
+  // closing-region box in float, shrunk / grown by the filter's error bound: certainly inside / certainly outside
+  float top_in, top_out, left_in, left_out, right_in, right_out;
   long long ymin;         // ordered double: points.row(1).minCoeff()
   long long minx, maxx;   // x extent of the closing region
   long long ap[8];        // antipodal extrema, l: maxy miny maxz minz, r: same (ordered)
@@ -82,6 +92,9 @@ struct Orient {
 };
 
 struct Fixed {
+  uint32_t lut[kLutWords];  // FP32 filter tables (copied from HandsArgs::lut)
+  float Fz[3];              // hand axis (frame column 2) in float; crop bounds |z| certainly inside / outside
+  float hh_in, hh_out;
   double F[3][3];
   double sample[3];
   // slot-edge lookup (HandConst::lut copied here: divergent indexing of constant memory serialises)
@@ -93,7 +106,7 @@ struct Fixed {
   double bottom[kMaxDepths];
   uint32_t row_prefix[kMaxRows + 1];
   uint32_t row_begin[kMaxRows];
-  uint32_t nkept, total_cand, cursor, pool_ok, nrows;
+  uint32_t nkept, total_cand, cursor, pool_ok, nrows, next_batch;
   unsigned long long sumK, sumKc;
 };
 
@@ -103,6 +116,17 @@ __host__ __device__ inline size_t hands_smem_base(int R, int ND) {
   o = (o + 15) & ~(size_t)15;
   o += (size_t)R * ND * sizeof(uint32_t);
   return (o + 15) & ~(size_t)15;
+}
+
+__device__ __forceinline__ int lut_bucket(float v, float v0, float scale, int nb) {
+  return min(max((int)((v - v0) * scale), 0), nb - 1);
+}
+__device__ __forceinline__ float dot3f(const float a0, const float a1, const float a2, const float4& p) {
+  return fmaf(a2, p.z, fmaf(a1, p.y, a0 * p.x));
+}
+__device__ __forceinline__ double dot3d_ref(const double* a, const float4& p) {
+  // the reference's FP64 sequence (hand_search.cpp:359: frame_rot^T * points, no contraction)
+  return (a[0] * (double)p.x + a[1] * (double)p.y) + a[2] * (double)p.z;
 }
 
 }  // namespace

@@ -62,23 +62,36 @@ __device__ void setup_rows(Fixed& sh, const GridDev& g, const float q[3], float 
   __syncthreads();
 }
 
-// Stages the next chunk of cropped neighbours, starting at candidate sh.cursor.  Each
-// thread takes kCand CONSECUTIVE candidates: one binary search over the row prefix, then
-// sequential row advance.
+// Stages the next chunk of cropped neighbours, starting at candidate sh.cursor (a multiple of the batch size, or
+// T).  Warps take batches of 32 x kCand consecutive candidates from a shared counter -- no block-wide barrier
+// inside the loop.  A warp takes a batch only while (points staged so far) + (everything all warps may still be
+// adding) fits the staging buffer: the LAST batch ever taken saw nkept + kInFlight <= cap, and what was not yet
+// counted in that nkept is at most one batch per warp, so the buffer cannot overflow; a refused warp stops, and
+// since nkept only grows every later request is refused too: the batches taken are a prefix of the sequence.
+// Each thread takes kCand CONSECUTIVE candidates: one binary search over the row prefix, then sequential row advance.
 __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const HandConst& hc,
                            const float q[3], bool count_stats, int tid) {
   const int lane = tid & 31;
-  if (tid == 0) sh.nkept = 0;
-  __syncthreads();
+  constexpr uint32_t kBatch = 32u * kCand;
+  constexpr uint32_t kInFlight = (kHandThreads / 32) * kBatch;
   const uint32_t T = sh.total_cand;
+  if (tid == 0) {
+    sh.nkept = 0;
+    sh.next_batch = (sh.cursor + kBatch - 1) / kBatch;
+  }
+  __syncthreads();
   const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
+  const float fz0 = sh.Fz[0], fz1 = sh.Fz[1], fz2 = sh.Fz[2], hh_in = sh.hh_in, hh_out = sh.hh_out;
   uint32_t kcount = 0;
-  uint32_t t0 = sh.cursor;  // advances by one batch per iteration in every thread alike; published on exit
   for (;;) {
-    const uint32_t kept_now = sh.nkept;
-    if (t0 >= T || kept_now + kHandThreads * kCand > A.cap) break;
-    __syncthreads();  // everyone has read nkept
-    const uint32_t tb = t0 + (uint32_t)tid * kCand;
+    uint32_t batch = 0xFFFFFFFFu;
+    if (lane == 0) {
+      const uint32_t seen = *reinterpret_cast<volatile uint32_t*>(&sh.nkept);
+      if (seen + kInFlight <= A.cap) batch = atomicAdd(&sh.next_batch, 1u);
+    }
+    batch = __shfl_sync(AG2_FULL, batch, 0);
+    if (batch == 0xFFFFFFFFu || (unsigned long long)batch * kBatch >= T) break;
+    const uint32_t tb = batch * kBatch + (uint32_t)lane * kCand;
     int row = 0;
     uint32_t row_end = 0, pos = 0;
     if (tb < T) {
@@ -124,8 +137,14 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
         const float d2 = dist2_f(dx, dy, dz);
         if (d2 < hc.r2_hands) {
           kcount++;
-          const double zf = (az0 * (double)dx + az1 * (double)dy) + az2 * (double)dz;
-          if (zf > hc.neg_hand_height && zf < hc.hand_height) keepmask |= 1u << b;  // hand_search.cpp:334
+          // crop -hh < z < hh (hand_search.cpp:334): FP32 first, FP64 only within eps32 of the bounds
+          const float z32 = fabsf(fmaf(fz2, dz, fmaf(fz1, dy, fz0 * dx)));
+          bool keep = z32 < hh_in;
+          if (!keep && !(z32 > hh_out)) {
+            const double zf = (az0 * (double)dx + az1 * (double)dy) + az2 * (double)dz;
+            keep = zf > hc.neg_hand_height && zf < hc.hand_height;
+          }
+          if (keep) keepmask |= 1u << b;
         }
         pv[b] = make_float4(dx, dy, dz, __uint_as_float(pp[b]));
       }
@@ -147,17 +166,15 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
 #pragma unroll
     for (int b = 0; b < kCand; b++)
       if (keepmask & (1u << b)) cache[w++] = pv[b];
-    t0 = min(T, t0 + (uint32_t)kCand * kHandThreads);
-    __syncthreads();  // nkept final for this batch
   }
-  __syncthreads();  // nobody still reads the old cursor
-  if (tid == 0) sh.cursor = t0;
-  __syncthreads();
+  __syncthreads();  // every batch taken is staged, nkept is final
+  if (tid == 0) sh.cursor = (uint32_t)min((unsigned long long)T, (unsigned long long)sh.next_batch * kBatch);
   if (count_stats) {
     for (int o = 16; o > 0; o >>= 1) kcount += __shfl_xor_sync(AG2_FULL, kcount, o);
     if (lane == 0 && kcount) atomicAdd(&sh.sumK, (unsigned long long)kcount);
-    if (tid == 0) sh.sumKc += sh.nkept;
   }
+  __syncthreads();
+  if (count_stats && tid == 0) sh.sumKc += sh.nkept;
   __syncthreads();
 }
 
@@ -169,6 +186,42 @@ __device__ __forceinline__ uint32_t slot_mask(const Fixed& sh, double x, double 
   while (k < AG2_SLOT_EDGES && sh.U[k] < x) k++;
   const bool eq = k < AG2_SLOT_EDGES && sh.U[k] == x;
   return eq ? sh.Meq[k] : sh.M[k];
+}
+
+// FP32 filter look-ups.  A bucket entry without the top bit is the answer.  With it, one threshold k is near the
+// bucket: certain below lo[k] / above hi[k] (two shared loads, no call); only a coordinate within eps32 of the
+// threshold, or a bucket with several thresholds nearby, takes the exact FP64 evaluation.
+__device__ __noinline__ int exact_class(const Fixed& sh, const Orient& o, const float4 p, int ND) {
+  return depth_class(dot3d_ref(o.FRy, p), sh.depth, ND, 200.0);
+}
+__device__ __noinline__ uint32_t exact_mask(const Fixed& sh, const Orient& o, const float4 p, double x0, double xscale) {
+  return slot_mask(sh, dot3d_ref(o.FRx, p), x0, xscale);
+}
+__device__ __forceinline__ int class_of(const Fixed& sh, const Orient& o, const float4& p, float yf, uint32_t v, int ND) {
+  if (!(v & 0x80000000u)) return (int)v;
+  const uint32_t k = v & 0xFFFFu;
+  if (k != 0xFFFFu) {
+    if (yf < __uint_as_float(sh.lut[kLutYLo + k])) return (int)k;
+    if (yf > __uint_as_float(sh.lut[kLutYHi + k])) return (int)k + 1;
+  }
+  return exact_class(sh, o, p, ND);
+}
+__device__ __forceinline__ uint32_t mask_of(const Fixed& sh, const Orient& o, const float4& p, float xf, uint32_t v,
+                                            double x0, double xscale) {
+  if (!(v & 0x80000000u)) return v;
+  const uint32_t k = v & 0xFFFFu;
+  if (k != 0xFFFFu) {
+    if (xf < __uint_as_float(sh.lut[kLutXLo + k])) return sh.M[k];
+    if (xf > __uint_as_float(sh.lut[kLutXHi + k])) return sh.M[k + 1];
+  }
+  return exact_mask(sh, o, p, x0, xscale);
+}
+// closing-region membership y < top && left < x < right (finger_hand.cpp:170), FP32 first
+__device__ __forceinline__ bool in_box(const Orient& o, const float4& p, float xf, float yf) {
+  if (yf < o.top_in && xf > o.left_in && xf < o.right_in) return true;
+  if (yf > o.top_out || xf < o.left_out || xf > o.right_out) return false;
+  const double x = dot3d_ref(o.FRx, p), y = dot3d_ref(o.FRy, p);
+  return y < o.top && x > o.left && x < o.right;
 }
 
 __global__ void __launch_bounds__(kHandThreads, 2)
@@ -205,6 +258,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     sh.pool_ok = 1;
   }
   // tables: constant bank -> shared (they are indexed per lane)
+  for (int i = tid; i < kLutWords; i += kHandThreads) sh.lut[i] = __ldg(&A.lut[i]);
   for (int i = tid; i < AG2_SLOT_EDGES; i += kHandThreads) {
     sh.U[i] = hc.lut.U[i];
     sh.Meq[i] = hc.lut.Meq[i];
@@ -235,11 +289,20 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     double nsa = -1.0 * sa;
     ors[r].FRx[a] = (sh.F[a][0] * ca + sh.F[a][1] * sa) + sh.F[a][2] * 0.0;
     ors[r].FRy[a] = (sh.F[a][0] * nsa + sh.F[a][1] * ca) + sh.F[a][2] * 0.0;
+    ors[r].fx[a] = (float)ors[r].FRx[a];
+    ors[r].fy[a] = (float)ors[r].FRy[a];
+  }
+  if (tid < 3) sh.Fz[tid] = (float)sh.F[tid][2];
+  if (tid == 3) {
+    sh.hh_in = nextafterf((float)(hc.hand_height - (double)hc.eps32), -INFINITY);
+    sh.hh_out = nextafterf((float)(hc.hand_height + (double)hc.eps32), INFINITY);
   }
   setup_rows(sh, A.g, q, hc.rq_hands, tid);
   const uint32_t T = sh.total_cand;
   const double inv_dstep = 200.0;  // 1/0.005: estimator only, exact fix-up follows
   const double lut_x0 = hc.lut.x0, lut_xs = hc.lut.xscale;
+  const float e2 = 2.0f * hc.eps32;
+  const float yl0 = hc.ylut_v0, yls = hc.ylut_scale, xl0 = hc.xlut_v0, xls = hc.xlut_scale;
 
   // ---------------- pass 1: slot occupancy per depth class and min y, per orientation
   bool single_chunk = true;
@@ -248,25 +311,66 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     const uint32_t nk = sh.nkept;
     if (chunk == 0 && sh.cursor < T) single_chunk = false;
     for (int r = 0; r < R; r++) {
-      const double ax0 = ors[r].FRx[0], ax1 = ors[r].FRx[1], ax2 = ors[r].FRx[2];
-      const double ay0 = ors[r].FRy[0], ay1 = ors[r].FRy[1], ay2 = ors[r].FRy[2];
+      Orient& o = ors[r];
+      const float fx0 = o.fx[0], fx1 = o.fx[1], fx2 = o.fx[2];
+      const float fy0 = o.fy[0], fy1 = o.fy[1], fy2 = o.fy[2];
       uint32_t* occ_r = occ + r * ND;
-      double ymin = INFINITY;
-      for (uint32_t i = tid; i < nk; i += kHandThreads) {
-        float4 p = cache[i];
-        double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
-        double y = (ay0 * px + ay1 * py) + ay2 * pz;
-        ymin = fmin(ymin, y);
-        int ct = depth_class(y, sh.depth, ND, inv_dstep);
-        if (ct < ND) {
-          double x = (ax0 * px + ax1 * py) + ax2 * pz;
-          uint32_t mask = slot_mask(sh, x, lut_x0, lut_xs);
-          // OR is idempotent and monotone: only touch the word when it would change
-          if (mask & ~occ_r[ct]) atomicOr(&occ_r[ct], mask);
+      // FP32 minimum of y over this thread's points, its position, and whether another point came within 2 eps32
+      float m = INFINITY;
+      uint32_t imin = 0xFFFFFFFFu;
+      bool amb = false;
+      // four points per iteration: their loads, dot products and table look-ups are independent of each other
+      constexpr int U = 4;
+      for (uint32_t i0 = tid; i0 < nk; i0 += U * kHandThreads) {
+        float4 p[U];
+        float yf[U], xf[U];
+        uint32_t vy[U], vx[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) p[u] = cache[min(i0 + u * kHandThreads, nk - 1)];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          yf[u] = dot3f(fy0, fy1, fy2, p[u]);
+          xf[u] = dot3f(fx0, fx1, fx2, p[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          vy[u] = sh.lut[kLutY + lut_bucket(yf[u], yl0, yls, kYLutBuckets)];
+          vx[u] = sh.lut[kLutX + lut_bucket(xf[u], xl0, xls, kXLutBuckets)];
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+          const uint32_t i = i0 + u * kHandThreads;
+          if (i >= nk) break;
+          if (yf[u] < m + e2) {
+            amb = !(yf[u] < m - e2);
+            if (yf[u] < m) m = yf[u], imin = i;
+          }
+          const int ct = class_of(sh, o, p[u], yf[u], vy[u], ND);
+          if (ct < ND) {
+            const uint32_t mask = mask_of(sh, o, p[u], xf[u], vx[u], lut_x0, lut_xs);
+            // OR is idempotent and monotone: only touch the word when it would change
+            if (mask & ~occ_r[ct]) atomicOr(&occ_r[ct], mask);
+          }
         }
       }
-      ymin = warp_min_d(ymin);
-      if (lane == 0) atomicMin(&ors[r].ymin, d_ordered(ymin));
+      // exact min y (points.row(1).minCoeff(), finger_hand.cpp:158): the point that attains it has a float
+      // coordinate within 2 eps32 of the float minimum -- of the whole chunk, hence also of its own warp's points --
+      // so only the lanes that close to their warp's float minimum evaluate their candidates in FP64
+      float wm = m;
+      for (int of = 16; of > 0; of >>= 1) wm = fminf(wm, __shfl_xor_sync(AG2_FULL, wm, of));
+      if (imin != 0xFFFFFFFFu && m <= wm + e2) {
+        double ymin;
+        if (!amb) {
+          ymin = dot3d_ref(o.FRy, cache[imin]);
+        } else {  // several of this thread's points are that close: all of them, exactly
+          ymin = INFINITY;
+          for (uint32_t i = tid; i < nk; i += kHandThreads) {
+            const float4 q4 = cache[i];
+            if (dot3f(fy0, fy1, fy2, q4) <= m + e2) ymin = fmin(ymin, dot3d_ref(o.FRy, q4));
+          }
+        }
+        atomicMin(&o.ymin, d_ordered(ymin));
+      }
     }
     __syncthreads();
     if (sh.cursor >= T) break;
@@ -320,6 +424,14 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         o.sx = 1.0 / baseline_const;
         o.sy = 1.0 / (o.top - o.bottom);
         o.sz = 1.0 / (2.0 * hc.hand_height);
+        // the closing region in float, shrunk (certainly inside) and grown (certainly outside) by eps32
+        const double ep = (double)hc.eps32;
+        o.top_in = nextafterf((float)(o.top - ep), -INFINITY);
+        o.top_out = nextafterf((float)(o.top + ep), INFINITY);
+        o.left_in = nextafterf((float)(o.left + ep), INFINITY);
+        o.left_out = nextafterf((float)(o.left - ep), -INFINITY);
+        o.right_in = nextafterf((float)(o.right - ep), -INFINITY);
+        o.right_out = nextafterf((float)(o.right + ep), INFINITY);
         sw.slot = (int8_t)e;
         sw.depth_step = (int8_t)last;
       }
@@ -347,17 +459,14 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
     for (int r = 0; r < R; r++) {
       const Orient& o = ors[r];
       if (!o.feasible) continue;
-      const double ax0 = o.FRx[0], ax1 = o.FRx[1], ax2 = o.FRx[2];
-      const double ay0 = o.FRy[0], ay1 = o.FRy[1], ay2 = o.FRy[2];
-      const double top = o.top, left = o.left, right = o.right;
+      const float fx0 = o.fx[0], fx1 = o.fx[1], fx2 = o.fx[2];
+      const float fy0 = o.fy[0], fy1 = o.fy[1], fy2 = o.fy[2];
       uint32_t cnt = 0;
       double mn = INFINITY, mx = -INFINITY;
       for (uint32_t i = tid; i < nk; i += kHandThreads) {
-        float4 p = cache[i];
-        double px = (double)p.x, py = (double)p.y, pz = (double)p.z;
-        double x = (ax0 * px + ax1 * py) + ax2 * pz;
-        double y = (ay0 * px + ay1 * py) + ay2 * pz;
-        if (y < top && x > left && x < right) {  // finger_hand.cpp:170
+        const float4 p = cache[i];
+        if (in_box(o, p, dot3f(fx0, fx1, fx2, p), dot3f(fy0, fy1, fy2, p))) {
+          const double x = dot3d_ref(o.FRx, p);  // the extent ends up in the record: exact
           cnt++;
           mn = fmin(mn, x);
           mx = fmax(mx, x);
@@ -409,7 +518,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
       const double ax0 = o.FRx[0], ax1 = o.FRx[1], ax2 = o.FRx[2];
       const double ay0 = o.FRy[0], ay1 = o.FRy[1], ay2 = o.FRy[2];
       const double az0 = sh.F[0][2], az1 = sh.F[1][2], az2 = sh.F[2][2];
-      const double top = o.top, left = o.left, right = o.right, bottom = o.bottom;
+      const double bottom = o.bottom;
       const double sx = o.sx, sy = o.sy, sz = o.sz, lc = o.lc;
       const uint32_t off = o.off;
       // extremal thresholds on SCALED x (antipodal.cpp:16-17; scaling is monotone)
@@ -423,12 +532,14 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
         double x = 0, y = 0, px = 0, py = 0, pz = 0;
         uint32_t pos = 0;
         if (i < nk) {
-          float4 p = cache[i];
-          px = (double)p.x, py = (double)p.y, pz = (double)p.z;
+          const float4 p = cache[i];
           pos = __float_as_uint(p.w);
-          x = (ax0 * px + ax1 * py) + ax2 * pz;
-          y = (ay0 * px + ay1 * py) + ay2 * pz;
-          inbox = y < top && x > left && x < right;
+          inbox = in_box(o, p, dot3f(o.fx[0], o.fx[1], o.fx[2], p), dot3f(o.fy[0], o.fy[1], o.fy[2], p));
+          if (inbox) {
+            px = (double)p.x, py = (double)p.y, pz = (double)p.z;
+            x = (ax0 * px + ax1 * py) + ax2 * pz;
+            y = (ay0 * px + ay1 * py) + ay2 * pz;
+          }
         }
         uint32_t ballot = __ballot_sync(AG2_FULL, inbox);
         uint32_t wbase = 0;
@@ -545,7 +656,8 @@ int hands_compute(ag2_ctx* c) {
   if (c->box_pool.cap == 0) AG2_CUDA(c, c->box_pool.reserve(std::max<size_t>((size_t)1 << 22, SR * 256)));
   // two CTAs per SM: staging capacity = what is left of half the shared memory
   const size_t base = hands_smem_base(R, c->hc.num_depths);
-  const size_t budget = 112 * 1024;
+  size_t budget = 112 * 1024;
+  if (const char* e = getenv("AG2_HANDS_BUDGET_KB")) budget = (size_t)std::min(224L, std::max(64L, atol(e))) * 1024;  // measurement hook
   if (base + (size_t)(kHandThreads * kCand + 256) * sizeof(float4) > budget) {
     c->err = "hands: num_orientations x deepen steps too large for shared memory";
     return AG2_E_CAPACITY;
@@ -562,6 +674,7 @@ int hands_compute(ag2_ctx* c) {
     AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 20, 0, 12 * sizeof(uint32_t), st));
     HandsArgs A;
     A.g = grid_dev(c);
+    A.lut = c->hands_lut.p;
     A.frames = c->frames.p;
     A.cap = cap;
     A.sweeps = c->sweeps.p;

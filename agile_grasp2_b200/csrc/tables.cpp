@@ -18,6 +18,38 @@
 
 namespace ag2 {
 
+namespace {
+// One bucket table of the FP32 filter (see ag2_internal.h): `edges` ascending (duplicates allowed), value(k) = the
+// answer for a coordinate with exactly k edges below it.
+template <class F>
+void build_filter_lut(const double* edges, int ne, int nb, double v0, double width, double eps, uint32_t* out, F value) {
+  const double delta = 0.01 * width + 2.0 * eps;  // float rounding of the bucket index + the filter's own error
+  for (int b = 0; b < nb; b++) {
+    const double lo = b == 0 ? -INFINITY : v0 + (double)b * width;
+    const double hi = b == nb - 1 ? INFINITY : v0 + (double)(b + 1) * width;
+    int first = -1, cnt = 0;
+    for (int k = 0; k < ne; k++)
+      if (edges[k] >= lo - delta && edges[k] <= hi + delta) {
+        if (first < 0) first = k;
+        cnt++;
+      }
+    if (cnt == 0) {
+      const double mid = b == 0 ? hi - 0.5 * width : lo + 0.5 * width;
+      int k = 0;
+      while (k < ne && edges[k] < mid) k++;
+      out[b] = value(k);
+    } else {
+      out[b] = 0x80000000u | (cnt == 1 ? (uint32_t)first : 0xFFFFu);
+    }
+  }
+}
+inline uint32_t f2u(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+}
+}  // namespace
+
 int build_hand_const(ag2_ctx* c) {
   const ag2_params& p = c->p;
   HandConst& h = c->hc;
@@ -97,6 +129,41 @@ int build_hand_const(ag2_ctx* c) {
     while (k < AG2_SLOT_EDGES && L.U[k] < edge) k++;
     L.kstart[b] = (uint8_t)k;
   }
+  // ---- FP32 filter tables.  A hand-frame coordinate is a . p with |a| = 1 and p a float difference shorter than
+  // nn_radius_hands; evaluated with three float operations on float-rounded coefficients it is within
+  // 4.2e-7 * radius of the FP64 value the reference computes (coefficient rounding 3 x 2^-24 x radius, three
+  // roundings of partial sums below sqrt(3) x radius).  eps32 is ten times that.
+  const double eps = 4e-6 * std::max(p.nn_radius_hands, 0.01);
+  h.eps32 = (float)eps;
+  std::vector<uint32_t> lut((size_t)kLutWords, 0u);
+  {
+    const double y_lo = h.depth[0] - 0.005, y_hi = h.depth[nd - 1] + 0.005;
+    const double wy = (y_hi - y_lo) / (double)kYLutBuckets;
+    h.ylut_v0 = (float)y_lo, h.ylut_scale = (float)(1.0 / wy);
+    // the device computes the bucket with the float-rounded origin and scale; delta above covers the difference
+    build_filter_lut(h.depth, nd, kYLutBuckets, (double)h.ylut_v0, 1.0 / (double)h.ylut_scale, eps, lut.data() + kLutY,
+                     [](int k) { return (uint32_t)k; });
+    const double wx = span > 0 ? span * 1.02 / (double)kXLutBuckets : 1.0;
+    const double x_lo = L.U[0] - 0.01 * span;
+    h.xlut_v0 = (float)x_lo, h.xlut_scale = (float)(1.0 / wx);
+    build_filter_lut(L.U, AG2_SLOT_EDGES, kXLutBuckets, (double)h.xlut_v0, 1.0 / (double)h.xlut_scale, eps,
+                     lut.data() + kLutX, [&](int k) { return L.M[k]; });
+    for (int k = 0; k < 64; k++) {
+      const double t = k < nd ? h.depth[k] : INFINITY;
+      lut[kLutYLo + k] = f2u(nextafterf((float)(t - eps), -INFINITY));
+      lut[kLutYHi + k] = f2u(nextafterf((float)(t + eps), INFINITY));
+    }
+    for (int k = 0; k < AG2_SLOT_EDGES; k++) {
+      lut[kLutXLo + k] = f2u(nextafterf((float)(L.U[k] - eps), -INFINITY));
+      lut[kLutXHi + k] = f2u(nextafterf((float)(L.U[k] + eps), INFINITY));
+    }
+  }
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  if (c->hands_lut.reserve(kLutWords) != cudaSuccess) return AG2_E_NOMEM;
+  // synchronous copy from a stack-lifetime vector, after whatever still reads the old tables; parameters change rarely
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (cudaMemcpy(c->hands_lut.p, lut.data(), (size_t)kLutWords * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+    return AG2_E_CUDA;
   return AG2_OK;
 }
 
