@@ -84,8 +84,9 @@ struct SlotLut {
 
 // Device tables of the FP32 filter (uint32 words, uploaded by build_hand_const; layout shared with hands.cu):
 // a bucket entry is the answer itself (depth class / 20-slot mask) when no threshold is near the bucket, else
-// 0x80000000 | k for the ONE threshold k near it (compare against lo[k] / hi[k] = threshold -+ eps32, exact FP64
-// evaluation in between), or 0x80000000 | 0xFFFF when several thresholds are near (always exact).
+// 0x80000000 | last << 8 | first for the ONE threshold (or run of thresholds within eps32 of each other) near it
+// (certain below lo[first] / above hi[last] = threshold -+ eps32, exact FP64 evaluation in between), or
+// 0x80000000 | 0xFFFF when separate thresholds are near (always exact).
 constexpr int kYLutBuckets = 256, kXLutBuckets = 1024;
 constexpr int kLutY = 0, kLutX = kLutY + kYLutBuckets, kLutYLo = kLutX + kXLutBuckets, kLutYHi = kLutYLo + 64,
               kLutXLo = kLutYHi + 64, kLutXHi = kLutXLo + AG2_SLOT_EDGES, kLutWords = kLutXHi + AG2_SLOT_EDGES;

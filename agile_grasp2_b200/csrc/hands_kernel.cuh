@@ -199,20 +199,20 @@ __device__ __noinline__ uint32_t exact_mask(const Fixed& sh, const Orient& o, co
 }
 __device__ __forceinline__ int class_of(const Fixed& sh, const Orient& o, const float4& p, float yf, uint32_t v, int ND) {
   if (!(v & 0x80000000u)) return (int)v;
-  const uint32_t k = v & 0xFFFFu;
-  if (k != 0xFFFFu) {
-    if (yf < __uint_as_float(sh.lut[kLutYLo + k])) return (int)k;
-    if (yf > __uint_as_float(sh.lut[kLutYHi + k])) return (int)k + 1;
+  if ((v & 0xFFFFu) != 0xFFFFu) {
+    const uint32_t k0 = v & 0xFFu, k1 = (v >> 8) & 0xFFu;
+    if (yf < __uint_as_float(sh.lut[kLutYLo + k0])) return (int)k0;
+    if (yf > __uint_as_float(sh.lut[kLutYHi + k1])) return (int)k1 + 1;
   }
   return exact_class(sh, o, p, ND);
 }
 __device__ __forceinline__ uint32_t mask_of(const Fixed& sh, const Orient& o, const float4& p, float xf, uint32_t v,
                                             double x0, double xscale) {
   if (!(v & 0x80000000u)) return v;
-  const uint32_t k = v & 0xFFFFu;
-  if (k != 0xFFFFu) {
-    if (xf < __uint_as_float(sh.lut[kLutXLo + k])) return sh.M[k];
-    if (xf > __uint_as_float(sh.lut[kLutXHi + k])) return sh.M[k + 1];
+  if ((v & 0xFFFFu) != 0xFFFFu) {
+    const uint32_t k0 = v & 0xFFu, k1 = (v >> 8) & 0xFFu;
+    if (xf < __uint_as_float(sh.lut[kLutXLo + k0])) return sh.M[k0];
+    if (xf > __uint_as_float(sh.lut[kLutXHi + k1])) return sh.M[k1 + 1];
   }
   return exact_mask(sh, o, p, x0, xscale);
 }

@@ -27,19 +27,23 @@ void build_filter_lut(const double* edges, int ne, int nb, double v0, double wid
   for (int b = 0; b < nb; b++) {
     const double lo = b == 0 ? -INFINITY : v0 + (double)b * width;
     const double hi = b == nb - 1 ? INFINITY : v0 + (double)(b + 1) * width;
-    int first = -1, cnt = 0;
+    int first = -1, last = -1;
     for (int k = 0; k < ne; k++)
       if (edges[k] >= lo - delta && edges[k] <= hi + delta) {
         if (first < 0) first = k;
-        cnt++;
+        last = k;
       }
-    if (cnt == 0) {
+    if (first < 0) {
       const double mid = b == 0 ? hi - 0.5 * width : lo + 0.5 * width;
       int k = 0;
       while (k < ne && edges[k] < mid) k++;
       out[b] = value(k);
+    } else if (edges[last] - edges[first] <= eps) {
+      // one threshold, or thresholds the FP32 coordinate cannot tell apart (the slot table holds 0 and 5.2e-18):
+      // certain below lo[first] / above hi[last], exact in between
+      out[b] = 0x80000000u | ((uint32_t)last << 8) | (uint32_t)first;
     } else {
-      out[b] = 0x80000000u | (cnt == 1 ? (uint32_t)first : 0xFFFFu);
+      out[b] = 0x80000000u | 0xFFFFu;
     }
   }
 }
