@@ -159,6 +159,9 @@ struct ag2_ctx {
   // ctx stream (finish_pending) -- a stage that only needs a number for its statistics does not stall
   uint32_t* h_pin = nullptr;       // kPinWords words of pinned host memory
   bool pend_normals = false;       // h_pin[0..4]: max k_n, -, sum k_n (u64), points over the last tier capacity
+  bool pend_select = false;        // h_pin[27..28]: antipodal / selected counts of the single-launch select path
+  bool pend_frames = false;        // h_pin[5]: largest frame neighbourhood (capacity check)
+  bool frames_attr_set = false;
   bool normals_attr_set = false;   // dynamic shared-memory limits of the normals kernels raised on this device
   uint32_t max_kn_hint = 0;        // densest normals neighbourhood of the previous cloud (sizes speculative launches)
   float min_z = 0.f;               // pcl::getMinMax3D z (grasp_detector.cpp:153)
@@ -202,6 +205,7 @@ struct ag2_ctx {
   // hot-path outputs
   ag2::DevBuf<ag2_frame> frames;            // S
   ag2::DevBuf<uint32_t> kt;                 // S neighbour counts at nn_radius_taubin
+  ag2::DevBuf<uint32_t> frames_big;         // [2] sizes + two lists: samples whose frame neighbourhood exceeds 1024 / 4096
   ag2::DevBuf<ag2_sweep_record> sweeps;     // S*R
   ag2::DevBuf<ag2_hypothesis> slots;        // S*R
   ag2::DevBuf<ag2::BoxRef> box_ref;         // S*R
@@ -279,9 +283,16 @@ uint32_t normals_shard_points(uint32_t n, int rank, int world);
 int normals_shard_compute(ag2_ctx* c, int rank, int world, float* d_out, size_t cap_points, size_t* n_owned);
 int normals_shard_assemble(ag2_ctx* c, const float* d_all, size_t cap_points, int world);
 int frames_compute(ag2_ctx* c);                     // frames.cu
-int hands_compute(ag2_ctx* c);                      // hands.cu
-int lists_build_after_hands(ag2_ctx* c);            // select.cu
+int hands_compute(ag2_ctx* c);                      // hands.cu: launch + synchronise + finish, retried when the pool grows
+int hands_launch(ag2_ctx* c);                       // k_hands + read-backs to pinned memory (no synchronisation)
+int hands_finish(ag2_ctx* c);                       // after a synchronisation: AG2_OK / kHandsRetry / error
+constexpr int kHandsRetry = 1;
+int lists_build_after_hands(ag2_ctx* c);            // select.cu: launch + synchronise + finish
+int lists_launch(ag2_ctx* c);                       // hypothesis list (and, for small runs, the pruned list) enqueued
+int lists_finish(ag2_ctx* c);                       // after a synchronisation: counts from pinned memory
 int prune_compute(ag2_ctx* c);
+int prune_launch(ag2_ctx* c);
+int prune_finish(ag2_ctx* c);
 int select_mode(ag2_ctx* c);
 int select_top(ag2_ctx* c);
 int gather_list_records(ag2_ctx* c, int which);

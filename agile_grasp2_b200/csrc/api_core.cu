@@ -40,6 +40,21 @@ int finish_pending(ag2_ctx* c) {
       return AG2_E_CAPACITY;
     }
   }
+  if (c->pend_select) {
+    c->pend_select = false;
+    c->list_n[AG2_LIST_ANTIPODAL] = c->h_pin[27];
+    c->list_n[AG2_LIST_SELECTED] = c->selected_count = c->h_pin[28];
+    c->st.num_antipodal = (int64_t)c->h_pin[27];
+    c->st.num_selected = (int64_t)c->h_pin[28];
+  }
+  if (c->pend_frames) {
+    c->pend_frames = false;
+    if (c->h_pin[5] > 16384u) {
+      c->have_hyps = false;
+      c->err = "frames: a sample has more than 16384 neighbours within nn_radius_taubin";
+      return AG2_E_CAPACITY;
+    }
+  }
   return AG2_OK;
 }
 

@@ -109,7 +109,8 @@ int ag2_render_images(ag2_ctx* c, uint8_t* out) {
   return AG2_OK;
 }
 
-int ag2_classify(ag2_ctx* c) {
+// the two stages below without their closing synchronisation (ag2_detect has one for the whole call)
+static int classify_stage(ag2_ctx* c) {
   AG2_TRY(ready(c));
   if (!c->have_images) return AG2_E_STATE;
   if (!c->net.loaded) return AG2_E_NO_WEIGHTS;
@@ -119,7 +120,7 @@ int ag2_classify(ag2_ctx* c) {
   return AG2_OK;
 }
 
-int ag2_select(ag2_ctx* c) {
+static int select_stage(ag2_ctx* c) {
   AG2_TRY(ready(c));
   if (!c->have_pruned) return AG2_E_STATE;
   if (c->p.antipodal_mode != AG2_MODE_PREDICTION) {
@@ -132,14 +133,45 @@ int ag2_select(ag2_ctx* c) {
   return AG2_OK;
 }
 
+int ag2_classify(ag2_ctx* c) {
+  AG2_TRY(classify_stage(c));
+  return sync_and_finish(c);
+}
+
+int ag2_select(ag2_ctx* c) {
+  AG2_TRY(select_stage(c));
+  return sync_and_finish(c);
+}
+
 int ag2_detect(ag2_ctx* c) {
-  AG2_TRY(ag2_generate_hypotheses(c));
-  AG2_TRY(ag2_prune(c));
+  AG2_TRY(ready(c));
+  if (c->num_samples == 0) return AG2_E_NO_SAMPLES;
+  // Same stages as the calls above, but the host waits only where it must: once for the size of the cell index
+  // (grid_build), once after the hand sweep + lists + prune step (list sizes decide the next launches), once at the
+  // end.  Everything in between is queued without a round trip; statistics and capacity checks ride on those waits.
+  AG2_TRY(grid_build(c));
+  AG2_TRY(normals_compute(c));
+  AG2_TRY(frames_compute(c));
+  int rc = kHandsRetry;
+  for (int attempt = 0; attempt < 8 && rc == kHandsRetry; attempt++) {
+    AG2_TRY(hands_launch(c));
+    AG2_TRY(lists_launch(c));
+    AG2_TRY(prune_launch(c));
+    AG2_TRY(sync_and_finish(c));
+    rc = hands_finish(c);
+  }
+  if (rc == kHandsRetry) rc = AG2_E_CAPACITY;
+  AG2_TRY(rc);
+  AG2_TRY(lists_finish(c));
+  AG2_TRY(prune_finish(c));
+  c->have_hyps = c->have_pruned = true;
+  c->have_images = c->have_antipodal = c->have_selected = false;
   if (c->p.antipodal_mode == AG2_MODE_PREDICTION) {
     AG2_TRY(ag2_render_images(c, nullptr));
-    AG2_TRY(ag2_classify(c));
+    AG2_TRY(classify_stage(c));
   }
-  return ag2_select(c);
+  AG2_TRY(select_stage(c));
+  return sync_and_finish(c);
 }
 
 // ---- outputs

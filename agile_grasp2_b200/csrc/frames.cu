@@ -16,6 +16,10 @@ namespace ag2 {
 namespace {
 
 constexpr int kFrameThreads = 128;
+// k_frames sorts a neighbourhood in shared memory (12 B per neighbour, power-of-two capacity).  Three launches cover
+// all sizes without the host knowing the largest one: every sample at capacity 1024, and two short persistent
+// launches over the (usually empty) lists of denser ones at 4096 and 16384.
+constexpr uint32_t kFrameCap0 = 1024, kFrameCap1 = 4096, kFrameCap2 = 16384;
 
 __device__ __forceinline__ void sample_query(const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
                                              const double* __restrict__ sxyz, uint32_t s, float q[3]) {
@@ -35,7 +39,8 @@ __device__ __forceinline__ void sample_query(const float* __restrict__ xyz_in, c
 __global__ void k_count_sample_neighbors(GridDev g, const float* __restrict__ xyz_in,
                                          const int32_t* __restrict__ sidx, const double* __restrict__ sxyz,
                                          uint32_t S, float r2, float rq, uint32_t* __restrict__ kt,
-                                         uint32_t* __restrict__ max_out) {
+                                         uint32_t* __restrict__ max_out, uint32_t* __restrict__ big_list /* [2][S] */,
+                                         uint32_t* __restrict__ big_n /* [2] */) {
   uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (s >= S) return;
@@ -56,6 +61,12 @@ __global__ void k_count_sample_neighbors(GridDev g, const float* __restrict__ xy
   if (lane == 0) {
     kt[s] = cnt;
     atomicMax(max_out, cnt);
+    // neighbourhoods beyond the first launch's capacity go to the lists of the larger ones (order is free: every
+    // sample writes its own frame)
+    if (cnt > kFrameCap0) {
+      const int cls = cnt > kFrameCap1 ? 1 : 0;
+      big_list[(size_t)cls * S + atomicAdd(&big_n[cls], 1u)] = s;
+    }
   }
 }
 
@@ -108,12 +119,39 @@ __device__ __forceinline__ double dot3d(const double* a, const double* b) {
   return a[0] * b[0] + (a[1] * b[1] + a[2] * b[2]);  // Eigen fixed-size reduction order
 }
 
-__global__ void __launch_bounds__(kFrameThreads)
-k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
-         const double* __restrict__ sxyz, uint32_t S, const uint32_t* __restrict__ kt, uint32_t cap,
-         float r2, float rq, int num_cams, uint64_t seed, int64_t id_offset, int64_t id_stride, double cam0x, double cam0y,
-         double cam0z, double cam1x, double cam1y, double cam1z, ag2_frame* __restrict__ out, uint32_t* __restrict__ num_valid) {
-  extern __shared__ __align__(16) unsigned char smem[];
+struct FrameArgs {
+  GridDev g;
+  const float* xyz_in;
+  const int32_t* sidx;
+  const double* sxyz;
+  uint32_t S;
+  const uint32_t* kt;
+  uint32_t cap, lo;            // this launch handles neighbourhoods of lo < count <= cap (and count == 0 when lo == 0)
+  const uint32_t* list;        // null: sample = blockIdx.x; else the CTAs stride over list[0 .. *list_n)
+  const uint32_t* list_n;
+  float r2, rq;
+  int num_cams;
+  uint64_t seed;
+  int64_t id_offset, id_stride;
+  double cam0x, cam0y, cam0z, cam1x, cam1y, cam1z;
+  ag2_frame* out;
+  uint32_t* num_valid;
+};
+
+__device__ void frame_of_sample(const FrameArgs& P, const uint32_t s, unsigned char* smem) {
+  const GridDev& g = P.g;
+  const float* xyz_in = P.xyz_in;
+  const int32_t* sidx = P.sidx;
+  const double* sxyz = P.sxyz;
+  const uint32_t* kt = P.kt;
+  const uint32_t cap = P.cap;
+  const float r2 = P.r2, rq = P.rq;
+  const int num_cams = P.num_cams;
+  const uint64_t seed = P.seed;
+  const int64_t id_offset = P.id_offset, id_stride = P.id_stride;
+  const double cam0x = P.cam0x, cam0y = P.cam0y, cam0z = P.cam0z, cam1x = P.cam1x, cam1y = P.cam1y, cam1z = P.cam1z;
+  ag2_frame* out = P.out;
+  uint32_t* num_valid = P.num_valid;
   uint64_t* keys = (uint64_t*)smem;
   uint32_t* vals = (uint32_t*)(keys + cap);
   __shared__ double N[50][3];
@@ -121,11 +159,11 @@ k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict_
   __shared__ double M[9];
   __shared__ int num_source[8];
   __shared__ uint32_t filled;
-  const uint32_t s = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kFrameThreads / 32;
   float q[3];
   sample_query(xyz_in, sidx, sxyz, s, q);
   const uint32_t count = kt[s];
+  if (count > cap || (count <= P.lo && !(count == 0 && P.lo == 0))) return;  // another launch's (uniform per CTA)
   ag2_frame f;
   if (tid == 0) {
     f.sample[0] = (double)q[0], f.sample[1] = (double)q[1], f.sample[2] = (double)q[2];
@@ -257,6 +295,19 @@ k_frames(GridDev g, const float* __restrict__ xyz_in, const int32_t* __restrict_
   atomicAdd(num_valid, 1u);
 }
 
+__global__ void __launch_bounds__(kFrameThreads) k_frames(const FrameArgs P) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  if (!P.list) {
+    frame_of_sample(P, blockIdx.x, smem);
+    return;
+  }
+  const uint32_t n = *P.list_n;
+  for (uint32_t it = blockIdx.x; it < n; it += gridDim.x) {
+    frame_of_sample(P, P.list[it], smem);
+    __syncthreads();  // thread 0 finishes the frame alone; the shared arrays are reused
+  }
+}
+
 }  // namespace
 
 int frames_compute(ag2_ctx* c) {
@@ -268,26 +319,37 @@ int frames_compute(ag2_ctx* c) {
   AG2_CUDA(c, c->kt.reserve(S));
   const int32_t* sidx = c->use_points ? nullptr : c->sample_idx.p;
   const double* sxyz = c->use_points ? c->sample_xyz.p : nullptr;
+  AG2_CUDA(c, c->frames_big.reserve(2 * (size_t)std::max(S, 1u) + 2));
+  uint32_t* big_n = c->frames_big.p;  // [2] list sizes, then the two lists
+  uint32_t* big_list = c->frames_big.p + 2;
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 12, 0, 8, st));  // [12] max k_t, [13] valid frames
+  AG2_CUDA(c, cudaMemsetAsync(big_n, 0, 8, st));
   k_count_sample_neighbors<<<(S * 32 + 127) / 128, 128, 0, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->hc.r2_taubin,
-                                                                c->hc.rq_taubin, c->kt.p, c->scalars.p + 12);
+                                                                c->hc.rq_taubin, c->kt.p, c->scalars.p + 12, big_list, big_n);
   AG2_LAUNCH_CHECK(c);
-  uint32_t max_kt = 0;
-  AG2_CUDA(c, cudaMemcpyAsync(&max_kt, c->scalars.p + 12, 4, cudaMemcpyDeviceToHost, st));
-  AG2_TRY(sync_and_finish(c));
-  uint32_t cap = 64;
-  while (cap < max_kt) cap <<= 1;
-  size_t smem = (size_t)cap * 12;
-  if (smem > 200 * 1024) {
-    c->err = "frames: a sample has more than 16384 neighbours within nn_radius_taubin";
-    return AG2_E_CAPACITY;
+  // the largest neighbourhood only matters for the capacity check: it travels to pinned memory, nobody waits
+  AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 5, c->scalars.p + 12, 4, cudaMemcpyDeviceToHost, st));
+  c->pend_frames = true;
+  if (!c->frames_attr_set) {
+    AG2_CUDA(c, cudaFuncSetAttribute(k_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kFrameCap2 * 12)));
+    c->frames_attr_set = true;
   }
-  AG2_CUDA(c, cudaFuncSetAttribute(k_frames, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const HandConst& h = c->hc;
-  k_frames<<<S, kFrameThreads, smem, st>>>(g, c->xyz_in.p, sidx, sxyz, S, c->kt.p, cap, h.r2_taubin, h.rq_taubin,
-                                           c->num_cams, h.rng_seed, c->sample_id_offset, c->sample_id_stride, h.cam_origin[0][0],
-                                           h.cam_origin[0][1], h.cam_origin[0][2], h.cam_origin[1][0],
-                                           h.cam_origin[1][1], h.cam_origin[1][2], c->frames.p, c->scalars.p + 13);
+  FrameArgs P;
+  P.g = g, P.xyz_in = c->xyz_in.p, P.sidx = sidx, P.sxyz = sxyz, P.S = S, P.kt = c->kt.p;
+  P.r2 = h.r2_taubin, P.rq = h.rq_taubin, P.num_cams = c->num_cams, P.seed = h.rng_seed;
+  P.id_offset = c->sample_id_offset, P.id_stride = c->sample_id_stride;
+  P.cam0x = h.cam_origin[0][0], P.cam0y = h.cam_origin[0][1], P.cam0z = h.cam_origin[0][2];
+  P.cam1x = h.cam_origin[1][0], P.cam1y = h.cam_origin[1][1], P.cam1z = h.cam_origin[1][2];
+  P.out = c->frames.p, P.num_valid = c->scalars.p + 13;
+  P.cap = kFrameCap0, P.lo = 0, P.list = nullptr, P.list_n = nullptr;
+  k_frames<<<S, kFrameThreads, (size_t)kFrameCap0 * 12, st>>>(P);
+  AG2_LAUNCH_CHECK(c);
+  P.cap = kFrameCap1, P.lo = kFrameCap0, P.list = big_list, P.list_n = big_n;
+  k_frames<<<std::min<uint32_t>(S, (uint32_t)c->sm_count * 4), kFrameThreads, (size_t)kFrameCap1 * 12, st>>>(P);
+  AG2_LAUNCH_CHECK(c);
+  P.cap = kFrameCap2, P.lo = kFrameCap1, P.list = big_list + S, P.list_n = big_n + 1;
+  k_frames<<<std::min<uint32_t>(S, (uint32_t)c->sm_count), kFrameThreads, (size_t)kFrameCap2 * 12, st>>>(P);
   AG2_LAUNCH_CHECK(c);
   phase_end(c, 2);
   return AG2_OK;

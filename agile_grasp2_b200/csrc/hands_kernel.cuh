@@ -492,13 +492,16 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
       total += ors[r].m;
       mmax = max(mmax, ors[r].m);
     }
-    uint32_t base = total ? atomicAdd(&A.pool_counter[0], total) : 0u;
-    if ((unsigned long long)base + total > A.pool_cap) {
-      atomicExch(&A.pool_counter[1], 1u);
+    // 64-bit cursor: the ids of a fused cloud's closing regions can exceed 2^32 in total; what does not fit the
+    // pool (BoxRef offsets are 32 bits) is counted, not written, and the host grows the pool or refuses
+    const unsigned long long base =
+        total ? atomicAdd(reinterpret_cast<unsigned long long*>(A.pool_counter), (unsigned long long)total) : 0ull;
+    if (base + total > A.pool_cap) {
+      atomicExch(&A.pool_counter[2], 1u);
       sh.pool_ok = 0;
     }
-    for (int r = 0; r < R; r++) ors[r].off += base;
-    atomicMax(&A.pool_counter[2], mmax);
+    for (int r = 0; r < R; r++) ors[r].off += (uint32_t)base;
+    atomicMax(&A.pool_counter[3], mmax);
     atomicAdd(&A.stat[2], (unsigned long long)total);
   }
   __syncthreads();
@@ -644,7 +647,7 @@ k_hands(HandsArgs A, const __grid_constant__ HandConst hc) {
 
 }  // namespace
 
-int hands_compute(ag2_ctx* c) {
+int hands_launch(ag2_ctx* c) {
   phase_begin(c, 3);
   cudaStream_t st = c->stream;
   const uint32_t S = (uint32_t)c->num_samples;
@@ -670,40 +673,59 @@ int hands_compute(ag2_ctx* c) {
   }
   const size_t smem = base + (size_t)cap * sizeof(float4);
   AG2_CUDA(c, cudaFuncSetAttribute(k_hands, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  for (int attempt = 0; attempt < 8; attempt++) {
-    AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 20, 0, 12 * sizeof(uint32_t), st));
-    HandsArgs A;
-    A.g = grid_dev(c);
-    A.lut = c->hands_lut.p;
-    A.frames = c->frames.p;
-    A.cap = cap;
-    A.sweeps = c->sweeps.p;
-    A.slots = c->slots.p;
-    A.box_ref = c->box_ref.p;
-    A.pool = c->box_pool.p;
-    A.pool_cap = (uint32_t)std::min<size_t>(c->box_pool.cap, 0xFFFFFFFFu);
-    A.pool_counter = c->scalars.p + 20;
-    A.stat = (unsigned long long*)(c->scalars.p + 24);
-    k_hands<<<S, kHandThreads, smem, st>>>(A, c->hc);
-    AG2_LAUNCH_CHECK(c);
-    uint32_t res[12], nvalid = 0;
-    AG2_CUDA(c, cudaMemcpyAsync(res, c->scalars.p + 20, sizeof(res), cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaMemcpyAsync(&nvalid, c->scalars.p + 13, 4, cudaMemcpyDeviceToHost, st));
-    AG2_TRY(sync_and_finish(c));
-    unsigned long long stat[3];
-    memcpy(stat, &res[4], sizeof(stat));
-    if (res[1]) {  // pool overflow: grow to the exact need and redo
-      if ((size_t)res[0] > 0xFFFFFFF0u) return AG2_E_CAPACITY;
-      AG2_CUDA(c, c->box_pool.reserve((size_t)res[0] + 1024));
-      continue;
+  AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 20, 0, 12 * sizeof(uint32_t), st));
+  HandsArgs A;
+  A.g = grid_dev(c);
+  A.lut = c->hands_lut.p;
+  A.frames = c->frames.p;
+  A.cap = cap;
+  A.sweeps = c->sweeps.p;
+  A.slots = c->slots.p;
+  A.box_ref = c->box_ref.p;
+  A.pool = c->box_pool.p;
+  A.pool_cap = (uint32_t)std::min<size_t>(c->box_pool.cap, 0xFFFFFFFFu);
+  A.pool_counter = c->scalars.p + 20;  // [0..1] 64-bit cursor, [2] overflow flag, [3] max m
+  A.stat = (unsigned long long*)(c->scalars.p + 24);
+  k_hands<<<S, kHandThreads, smem, st>>>(A, c->hc);
+  AG2_LAUNCH_CHECK(c);
+  // cursor, overflow flag, statistics: to pinned memory behind the kernel; hands_finish reads them after the
+  // next synchronisation (ag2_detect has ONE for the sweep, the two lists and the prune step together)
+  AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 8, c->scalars.p + 20, 12 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 20, c->scalars.p + 13, 4, cudaMemcpyDeviceToHost, st));
+  phase_end(c, 3);
+  return AG2_OK;
+}
+
+// After a synchronisation: AG2_OK, kHandsRetry (the in-box pool was too small and has been grown: launch again),
+// or an error.
+int hands_finish(ag2_ctx* c) {
+  const uint32_t* res = c->h_pin + 8;
+  unsigned long long need, stat[3];
+  memcpy(&need, res, 8);
+  memcpy(stat, res + 4, sizeof(stat));
+  if (res[2]) {  // pool overflow: grow to the exact need and redo
+    if (need > 0xFFFFFFF0ull) {
+      c->err = "hands: the closing regions of this call hold more than 2^32 point ids; split the sample list";
+      return AG2_E_CAPACITY;
     }
-    c->max_in_box = res[2];
-    c->st.num_frames = (int64_t)nvalid;
-    c->st.sum_neighbors_hands = (int64_t)stat[0];
-    c->st.sum_cropped = (int64_t)stat[1];
-    c->st.sum_in_box = (int64_t)stat[2];
-    phase_end(c, 3);
-    return AG2_OK;
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+    AG2_CUDA(c, c->box_pool.reserve((size_t)need + 1024));
+    return kHandsRetry;
+  }
+  c->max_in_box = res[3];
+  c->st.num_frames = (int64_t)c->h_pin[20];
+  c->st.sum_neighbors_hands = (int64_t)stat[0];
+  c->st.sum_cropped = (int64_t)stat[1];
+  c->st.sum_in_box = (int64_t)stat[2];
+  return AG2_OK;
+}
+
+int hands_compute(ag2_ctx* c) {
+  for (int attempt = 0; attempt < 8; attempt++) {
+    AG2_TRY(hands_launch(c));
+    AG2_TRY(sync_and_finish(c));
+    const int rc = hands_finish(c);
+    if (rc != kHandsRetry) return rc;
   }
   return AG2_E_CAPACITY;
 }

@@ -340,21 +340,23 @@ k_select_small(const uint32_t* __restrict__ src, uint32_t n, ag2_hypothesis* __r
 
 }  // namespace
 
-// flags (n entries, 0/1) -> compacted `out`, returns count (one small D2H sync)
-static int compact_list(ag2_ctx* c, size_t n, const uint32_t* src, DevBuf<uint32_t>& out, size_t* count) {
+// flags (n entries, 0/1) -> compacted `out`; the count goes to pinned memory (*h_count is valid after the next
+// synchronisation of the stream)
+static int compact_list_async(ag2_ctx* c, size_t n, const uint32_t* src, DevBuf<uint32_t>& out, uint32_t* h_count) {
   cudaStream_t st = c->stream;
   AG2_CUDA(c, out.reserve(std::max<size_t>(n, 1)));
-  if (n == 0) {
-    *count = 0;
-    return AG2_OK;
-  }
+  *h_count = 0;
+  if (n == 0) return AG2_OK;
   AG2_TRY(exclusive_scan_u32(c, c->flags.p, n));
   k_compact<<<(unsigned)((n + kT - 1) / kT), kT, 0, st>>>(c->flags.p, src, n, out.p);
   AG2_LAUNCH_CHECK(c);
-  uint32_t total = 0;
-  AG2_CUDA(c, cudaMemcpyAsync(&total, c->flags.p + n, 4, cudaMemcpyDeviceToHost, st));
-  AG2_CUDA(c, cudaStreamSynchronize(st));
-  *count = total;
+  AG2_CUDA(c, cudaMemcpyAsync(h_count, c->flags.p + n, 4, cudaMemcpyDeviceToHost, st));
+  return AG2_OK;
+}
+static int compact_list(ag2_ctx* c, size_t n, const uint32_t* src, DevBuf<uint32_t>& out, size_t* count) {
+  AG2_TRY(compact_list_async(c, n, src, out, c->h_pin + 30));
+  AG2_TRY(sync_and_finish(c));
+  *count = c->h_pin[30];
   return AG2_OK;
 }
 
@@ -379,10 +381,12 @@ static bool fused_lists_allowed() {
   return !(e && atoi(e) != 0);
 }
 
-int lists_build_after_hands(ag2_ctx* c) {
+// h_pin[24] hypotheses, [25] pruned (single-launch path), [26] pruned (multi-kernel path)
+int lists_launch(ag2_ctx* c) {
   const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
   c->pruned_precomputed = c->selected_precomputed = false;
   for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;
+  c->h_pin[24] = c->h_pin[25] = 0;
   if (SR && SR <= kFusedMaxSlots && fused_lists_allowed()) {
     // both lists in one launch; the prune stage then only publishes its count
     cudaStream_t st = c->stream;
@@ -392,13 +396,8 @@ int lists_build_after_hands(ag2_ctx* c) {
                                            c->list[AG2_LIST_HYPOTHESES].p, c->list[AG2_LIST_PRUNED].p,
                                            c->scalars.p + 56);
     AG2_LAUNCH_CHECK(c);
-    uint32_t counts[2];
-    AG2_CUDA(c, cudaMemcpyAsync(counts, c->scalars.p + 56, 8, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
-    c->list_n[AG2_LIST_HYPOTHESES] = counts[0];
-    c->pruned_count = counts[1];
+    AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 24, c->scalars.p + 56, 8, cudaMemcpyDeviceToHost, st));
     c->pruned_precomputed = true;
-    c->st.num_hypotheses = (int64_t)counts[0];
     return AG2_OK;
   }
   AG2_CUDA(c, c->flags.reserve(SR + 1));
@@ -406,30 +405,50 @@ int lists_build_after_hands(ag2_ctx* c) {
     k_flag_emitted<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, SR, c->flags.p);
     AG2_LAUNCH_CHECK(c);
   }
-  AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_HYPOTHESES], &c->list_n[AG2_LIST_HYPOTHESES]));
-  c->st.num_hypotheses = (int64_t)c->list_n[AG2_LIST_HYPOTHESES];
+  return compact_list_async(c, SR, nullptr, c->list[AG2_LIST_HYPOTHESES], c->h_pin + 24);
+}
+
+int lists_finish(ag2_ctx* c) {
+  c->list_n[AG2_LIST_HYPOTHESES] = c->h_pin[24];
+  c->st.num_hypotheses = (int64_t)c->h_pin[24];
+  if (c->pruned_precomputed) c->pruned_count = c->h_pin[25];
   return AG2_OK;
 }
 
-int prune_compute(ag2_ctx* c) {
+int lists_build_after_hands(ag2_ctx* c) {
+  AG2_TRY(lists_launch(c));
+  AG2_TRY(sync_and_finish(c));
+  return lists_finish(c);
+}
+
+int prune_launch(ag2_ctx* c) {
   phase_begin(c, 4);
   const size_t SR = c->num_samples * (size_t)c->p.num_orientations;
   c->selected_precomputed = false;
-  if (c->pruned_precomputed) {
-    c->list_n[AG2_LIST_PRUNED] = c->pruned_count;
-  } else {
+  if (!c->pruned_precomputed) {
     AG2_CUDA(c, c->flags.reserve(SR + 1));
     if (SR) {
       k_flag_pruned<<<(unsigned)((SR + kT - 1) / kT), kT, 0, c->stream>>>(c->sweeps.p, c->slots.p, SR, prune_args(c),
                                                                          c->flags.p);
       AG2_LAUNCH_CHECK(c);
     }
-    AG2_TRY(compact_list(c, SR, nullptr, c->list[AG2_LIST_PRUNED], &c->list_n[AG2_LIST_PRUNED]));
+    AG2_TRY(compact_list_async(c, SR, nullptr, c->list[AG2_LIST_PRUNED], c->h_pin + 26));
   }
-  c->list_rec_valid[AG2_LIST_PRUNED] = false;
-  c->st.num_pruned = (int64_t)c->list_n[AG2_LIST_PRUNED];
   phase_end(c, 4);
   return AG2_OK;
+}
+
+int prune_finish(ag2_ctx* c) {
+  c->list_n[AG2_LIST_PRUNED] = c->pruned_precomputed ? c->pruned_count : (size_t)c->h_pin[26];
+  c->list_rec_valid[AG2_LIST_PRUNED] = false;
+  c->st.num_pruned = (int64_t)c->list_n[AG2_LIST_PRUNED];
+  return AG2_OK;
+}
+
+int prune_compute(ag2_ctx* c) {
+  AG2_TRY(prune_launch(c));
+  AG2_TRY(sync_and_finish(c));
+  return prune_finish(c);
 }
 
 // antipodal list from the pruned list (mode 1 needs logits of the pruned list)
@@ -449,14 +468,12 @@ int select_mode(ag2_ctx* c) {
                                          c->list[AG2_LIST_ANTIPODAL].p, c->list[AG2_LIST_SELECTED].p,
                                          c->scalars.p + 58);
     AG2_LAUNCH_CHECK(c);
-    uint32_t counts[2];
-    AG2_CUDA(c, cudaMemcpyAsync(counts, c->scalars.p + 58, 8, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
-    c->list_n[AG2_LIST_ANTIPODAL] = counts[0];
-    c->selected_count = counts[1];
+    // the two counts follow the kernel to pinned memory; finish_pending publishes them after the next
+    // synchronisation (the end of ag2_detect / ag2_classify / ag2_select)
+    AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 27, c->scalars.p + 58, 8, cudaMemcpyDeviceToHost, st));
+    c->pend_select = true;
     c->selected_precomputed = true;
     for (int i = 0; i < 4; i++) c->list_rec_valid[i] = false;  // scores / flags changed in the slots
-    c->st.num_antipodal = (int64_t)counts[0];
     return AG2_OK;
   }
   AG2_CUDA(c, c->flags.reserve(std::max<size_t>(n, c->num_samples * (size_t)c->p.num_orientations) + 1));
@@ -475,10 +492,8 @@ int select_top(ag2_ctx* c) {
   phase_begin(c, 7);
   cudaStream_t st = c->stream;
   size_t n = c->list_n[AG2_LIST_ANTIPODAL];
-  if (c->selected_precomputed) {
-    c->list_n[AG2_LIST_SELECTED] = c->selected_count;
+  if (c->selected_precomputed) {  // the single-launch path of select_mode has built the list; counts: finish_pending
     c->list_rec_valid[AG2_LIST_SELECTED] = false;
-    c->st.num_selected = (int64_t)c->selected_count;
     phase_end(c, 7);
     return AG2_OK;
   }
