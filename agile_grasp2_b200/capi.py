@@ -730,6 +730,14 @@ class Group:
         self._check(self.api.fn("group_io_bytes")(self._h, C.byref(a), C.byref(b)), "ag2_group_io_bytes")
         return int(a.value), int(b.value)
 
+    def last_timing(self) -> dict:
+        """Per-segment account of the first local rank's last detect call (ag2_group_last_timing), ms."""
+        a = (C.c_double * 10)()
+        self._check(self.api.fn("group_last_timing")(self._h, a), "ag2_group_last_timing")
+        names = ["inputs", "grid", "normals_own", "normals_store", "normals_wait", "detect", "results_wait",
+                 "host_exchange", "host_total", "device_total"]
+        return {k: round(float(v), 4) for k, v in zip(names, a)}
+
     def detect_importance_ptr(self, xyz_ptr: int, n: int, cam_ptr: int, num_cams: int, smp_ptr: int, n_samples: int,
                               on_device: bool, ip: IsParams) -> np.ndarray:
         out = self._result_buffer(self._cap(int(n_samples), int(ip.num_iterations), int(ip.num_samples)))

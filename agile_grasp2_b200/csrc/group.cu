@@ -37,6 +37,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <chrono>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -234,6 +235,19 @@ struct Rank {
   std::string err;
   // statistics of the last call (ms, host clock): filled for the bench's per-rank view
   size_t io_h2d = 0, io_d2h = 0;  // host <-> device bytes of the last call
+  // segment marks of the last detect call on the ctx stream (per-rank account of a step, ag2_group_last_timing):
+  // 0 start | 1 inputs pulled | 2 cell index built | 3 own moments done | 4 own normals stored to all ranks |
+  // 5 all normals in, samples taken | 6 local detect done | 7 results of all ranks in
+  cudaEvent_t tev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool tev_set[8] = {false, false, false, false, false, false, false, false};
+  double host_tail_ms = 0.0, host_total_ms = 0.0;
+  void mark(int i) {
+    if (!tev[i] && cudaEventCreate(&tev[i]) != cudaSuccess) {
+      tev[i] = nullptr;
+      return;
+    }
+    tev_set[i] = cudaEventRecord(tev[i], ctx->stream) == cudaSuccess;
+  }
 
   int fail(int code, const std::string& what) {
     err = what;
@@ -453,9 +467,12 @@ struct Rank {
     k_copy2<<<c->sm_count * 4, 256, 0, st>>>(src + off_xyz, reinterpret_cast<unsigned char*>(c->xyz_in.p), 12 * n,
                                              src + off_cam, c->cam_in.p, n);
     G_LAUNCH();
+    mark(1);
     G_TRY(grid_build(c));
+    mark(2);
     if (world == 1) {
       G_TRY(normals_compute(c));
+      mark(5);
       return AG2_OK;
     }
     if (use_peer) {
@@ -463,6 +480,7 @@ struct Rank {
       G_TRY(post(F_GRID));
       c->nrm_rank = rank, c->nrm_world = world;
       int rc = normals_moments(c);
+      mark(3);
       if (rc == AG2_OK) rc = wait(F_GRID, all_mask());
       if (rc == AG2_OK) {
         c->nrm_peers = world;
@@ -471,7 +489,9 @@ struct Rank {
       }
       c->nrm_rank = 0, c->nrm_world = 1, c->nrm_peers = 0;
       G_TRY(rc);
+      mark(4);
       G_TRY(post_wait(F_NRM));
+      mark(5);
       return AG2_OK;
     }
     // NCCL transport: packed shard -> all-gather -> unpack
@@ -482,6 +502,7 @@ struct Rank {
     G_TRY(normals_shard_compute(c, rank, world, tx, shard_cap, &owned));
     G_NCCL(ncclAllGather(tx, xchg.p, 16 * shard_cap, ncclChar, comm, st));
     G_TRY(normals_shard_assemble(c, reinterpret_cast<const float*>(xchg.p), shard_cap, world));
+    mark(5);
     return AG2_OK;
   }
 
@@ -542,6 +563,7 @@ struct Rank {
       G_LAUNCH();
       G_NCCL(ncclAllGather(base + res_block(epoch, rank), base + res_block(epoch, 0), res_stride, ncclChar, comm, st));
     }
+    mark(7);
     // flag window (error words) and this epoch's half of the result blocks
     G_CUDA(cudaMemcpyAsync(h_res, base, kFlagBytes, cudaMemcpyDeviceToHost, st));
     G_CUDA(cudaMemcpyAsync(h_res + res_block(epoch, 0), base + res_block(epoch, 0), (size_t)world * res_stride,
@@ -639,6 +661,9 @@ struct Rank {
     G_TRY(check_args(n, s, num_cams));
     G_TRY(ensure_windows(n, s, ctx->p.num_selected > 0 ? (size_t)ctx->p.num_selected : 1));
     epoch++;
+    const auto t_begin = std::chrono::steady_clock::now();
+    for (int i = 0; i < 8; i++) tev_set[i] = false;
+    mark(0);
     int rc = load_cloud(xyz, n, cam, num_cams, smp, s, on_device);
     if (rc == AG2_OK) rc = take_samples(s);
     if (rc != AG2_OK) {
@@ -648,7 +673,13 @@ struct Rank {
     if (ctx->num_samples) rc = ag2_detect(ctx);
     if (rc == AG2_E_EMPTY_CLOUD || rc == AG2_E_NO_SAMPLES) rc = AG2_OK;  // an empty shard contributes nothing
     if (rc != AG2_OK && hb) hb->abort();
-    return exchange_results(rc, out);
+    mark(6);
+    const auto t_detect = std::chrono::steady_clock::now();
+    rc = exchange_results(rc, out);
+    const auto t_end = std::chrono::steady_clock::now();
+    host_tail_ms = std::chrono::duration<double, std::milli>(t_end - t_detect).count();
+    host_total_ms = std::chrono::duration<double, std::milli>(t_end - t_begin).count();
+    return rc;
   }
 
   // ImportanceSampling::detectGraspPoses (importance_sampling.cpp:30-112) over all ranks: the cloud, its index and
@@ -714,6 +745,8 @@ struct Rank {
     close_windows();
     if (h_res) cudaFreeHost(h_res);
     h_res = nullptr;
+    for (int i = 0; i < 8; i++)
+      if (tev[i]) cudaEventDestroy(tev[i]), tev[i] = nullptr;
     xchg.release();
     if (comm) ncclCommDestroy(comm);
     comm = nullptr;
@@ -957,6 +990,24 @@ const char* ag2_group_last_error(const ag2_group* g) {
 int ag2_group_transport(const ag2_group* g, int* peer_stores) {
   if (!g || !peer_stores || g->ranks.empty()) return AG2_E_INVALID;
   *peer_stores = g->ranks[0]->use_peer ? 1 : 0;
+  return AG2_OK;
+}
+
+int ag2_group_last_timing(const ag2_group* g, double* ms) {
+  if (!g || g->ranks.empty() || !ms) return AG2_E_INVALID;
+  const Rank* r = g->ranks[0];
+  for (int i = 0; i < 10; i++) ms[i] = 0.0;
+  int prev = 0;
+  for (int i = 1; i < 8; i++) {
+    if (!r->tev_set[i] || !r->tev_set[prev]) continue;
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r->tev[prev], r->tev[i]) == cudaSuccess) ms[i - 1] = t;
+    prev = i;
+  }
+  ms[7] = r->host_tail_ms;
+  ms[8] = r->host_total_ms;
+  float t = 0.f;
+  if (r->tev_set[0] && r->tev_set[7] && cudaEventElapsedTime(&t, r->tev[0], r->tev[7]) == cudaSuccess) ms[9] = t;
   return AG2_OK;
 }
 

@@ -361,10 +361,12 @@ def main():
         torch.cuda.synchronize()
 
     gaps = {}
+    segs = {}
 
     def timed(fn, iters, warm, clock_window=None):
         phase = {}
         gaps.clear()
+        segs.clear()
         total_ms, launches, last_stats, out = 0.0, 0, None, None
         for it in range(warm + iters):
             if it == warm and clock_window is not None:
@@ -391,6 +393,9 @@ def main():
                     phase[k] = phase.get(k, 0.0) + v / iters
                 for k, v in st.get("ms_gap", {}).items():
                     gaps[k] = gaps.get(k, 0.0) + v / iters
+                if ip is None:
+                    for k, v in grp.last_timing().items():
+                        segs[k] = segs.get(k, 0.0) + v / iters
                 last_stats = st
         return total_ms, phase, launches, last_stats, out
 
@@ -400,6 +405,7 @@ def main():
     tot_ms, phase, launches, st, sel = timed(lambda: call((xyz_d, cam_d, smp_d), True), K, W, clocks)
     clk = clocks.stop()
     gaps_resident = dict(gaps)
+    segs_resident = {k: round(v, 4) for k, v in segs.items()}
     e2e_ms, _, _, _, _ = timed(lambda: call((xyz_h, cam_h, smp_h), False), K, 1)
     io_h2d, io_d2h = grp.io_bytes()
     # ---- result check (outside the timed region): the sharded call against one GPU alone, byte for byte
@@ -421,7 +427,8 @@ def main():
         barrier()
     per_rank = None
     if world > 1:  # per-rank view of the step: sample shards differ in cost, the slowest rank sets the pace
-        mine = {"rank": rank, "ms_per_step": round(tot_ms / K, 4), "phases_ms": {k: round(v, 4) for k, v in phase.items()}}
+        mine = {"rank": rank, "ms_per_step": round(tot_ms / K, 4), "phases_ms": {k: round(v, 4) for k, v in phase.items()},
+                "segments_ms": segs_resident}
         per_rank = [None] * world
         dist.all_gather_object(per_rank, mine)
     t = torch.tensor([tot_ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -444,6 +451,7 @@ def main():
                                       "how": "ag2_measure_fp_peaks: 8 FMA chains x 256 threads x 8 CTAs per SM, best of 3, this process"},
                 "phases_ms": {k: round(v, 4) for k, v in phase.items()},
                 "gaps_before_phase_ms": {k: round(v, 4) for k, v in gaps_resident.items()},
+                "segments_ms": segs_resident,
                 "transport": ("peer memory (NVLink loads/stores, device-side flags)" if grp.peer_stores() else "nccl") if world > 1 else "single GPU",
                 **({"sharded_equals_single": equal} if equal is not None else {}),
                 **({"per_rank": per_rank} if per_rank else {}),

@@ -418,6 +418,12 @@ int ag2_group_transport(const ag2_group* g, int* peer_stores);
 /* Bytes the FIRST local rank moved between host and device in the last call (cloud + samples in, result
  * window out); every other rank of a multi-process group reports h2d = 0. */
 int ag2_group_io_bytes(const ag2_group* g, size_t* h2d, size_t* d2h);
+/* Per-segment account of the FIRST local rank's last ag2_group_detect call, ms[10]: device time (CUDA events on
+ * the ctx stream) of [0] inputs staged and pulled, [1] cell index, [2] own normal moments, [3] wait for all cell
+ * indexes + own normals stored to all ranks, [4] wait for all normals + sample shard, [5] local detect (frames ..
+ * select), [6] results stored to all ranks + wait; host clock of [7] result exchange incl. D2H and merge, [8] the
+ * whole call; [9] device time start .. results in. */
+int ag2_group_last_timing(const ag2_group* g, double* ms);
 /* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) over the group.  Collective when ranks are
  * processes: every rank calls it with the same n, num_cams, n_samples; xyz (packed, 3 floats per point),
  * cam_mask (or NULL) and samples (indices into the cloud) are read on rank 0 only -- host pointers, or
