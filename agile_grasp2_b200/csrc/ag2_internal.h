@@ -224,7 +224,7 @@ struct ag2_ctx {
   ag2::DevBuf<double> is_cand;              // candidate staging
   ag2::DevBuf<int32_t> is_cand_idx;
   ag2::DevBuf<double> is_surf;              // grasp surfaces of the hands found so far, packed 3 doubles each
-  ag2::DevBuf<uint8_t> is_accept;
+  ag2::DevBuf<uint32_t> is_flag;            // accept flags of a candidate batch, then their exclusive scan
   ag2::DevBuf<ag2_hypothesis> is_hands_in;  // ag2_draw_importance_samples: caller's hands, drawn samples
   ag2::DevBuf<double> is_draw;
   ag2::DevBuf<uint8_t> images;              // pruned * 10800 (HWC u8)

@@ -10,10 +10,11 @@
 //    samples because use_incoming_samples_ is never set on this instance;
 //  * rand() / boost::mt19937(time(NULL)) / boost::normal_distribution are replaced by a
 //    counter-based stream (deviation D5): candidate c of round i draws its hand index and its
-//    three N(0,1) values from splitmix64(seed, i, c, j) with Box-Muller.  Candidates are
-//    generated on the host (libm log/cos, identical in the oracle), the O(H) max-of-Gaussians
-//    rejection test of every candidate runs on the device (one warp per candidate), and the
-//    first num_gauss accepted candidates in stream order become the samples.
+//    three N(0,1) values from splitmix64(seed, i, c, j) with Box-Muller on the exactly
+//    reproducible log / cos of include/ag2_detmath.h (the same source is compiled into the
+//    oracle).  Everything runs on the device: one thread generates a candidate, one warp runs its
+//    O(H) max-of-Gaussians rejection test, a scan of the accept flags picks the first num_gauss
+//    accepted candidates in stream order; the host only learns how many were accepted per batch.
 //  * the rejection test p(idx) >= max_k p(k) with p = term * exp(c * d2), c = -1/(2 sigma), is
 //    evaluated on the exponent arguments c * d2 (exp is monotone); the two differ only when exp
 //    rounds two different arguments to the same value (documented tie).
@@ -22,9 +23,9 @@
 
 #include <algorithm>
 #include <chrono>
-#include <thread>
 #include <vector>
 
+#include "../../include/ag2_detmath.h"
 #include "dev_common.cuh"
 
 namespace ag2 {
@@ -44,49 +45,72 @@ struct IsTrace {
   }
 };
 
-// Host-side helper threads of the candidate generator: the draws are counter-based (every candidate is a pure
-// function of (seed, round, candidate id)), so any split over threads gives the same stream.
-template <class F>
-void parallel_for(size_t n, F f) {
-  const unsigned hw = std::thread::hardware_concurrency();
-  const unsigned nt = std::min<unsigned>(hw ? hw : 1u, 16u);
-  if (n < 2048 || nt <= 1) {
-    f((size_t)0, n);
-    return;
-  }
-  const size_t chunk = (n + nt - 1) / nt;
-  std::vector<std::thread> th;
-  for (unsigned t = 1; t < nt; t++) {
-    const size_t b = (size_t)t * chunk, e = std::min(n, b + chunk);
-    if (b < e) th.emplace_back([=] { f(b, e); });
-  }
-  f((size_t)0, std::min(n, chunk));
-  for (auto& x : th) x.join();
-}
-
-inline uint64_t h_splitmix64(uint64_t x) {
+__host__ __device__ inline uint64_t h_splitmix64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
   x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
   return x ^ (x >> 31);
 }
-inline uint64_t is_hash(uint64_t seed, uint64_t round, uint64_t cand, uint64_t j) {
+__host__ __device__ inline uint64_t is_hash(uint64_t seed, uint64_t round, uint64_t cand, uint64_t j) {
   uint64_t k = h_splitmix64(seed ^ 0x1234ABCD5678EF01ull);
   k = h_splitmix64(k + round);
   k = h_splitmix64(k + cand);
   return h_splitmix64(k + j);
 }
-inline double is_u01(uint64_t h) { return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
-inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) {
-  double u1 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp));
-  double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
-  return sqrt(-2.0 * log(u1)) * cos(2.0 * M_PI * u2);
+__host__ __device__ inline double is_u01(uint64_t h) { return ((double)(h >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
+__host__ __device__ inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) {
+  const double u1 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp));
+  const double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
+  return ag2_det_normal(u1, u2);
+}
+
+// grasp surfaces of the hands found so far, packed 3 doubles each
+__global__ void k_is_surf(const ag2_hypothesis* __restrict__ hands, uint32_t H, double* __restrict__ surf) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= H) return;
+  surf[3 * k] = hands[k].surface[0], surf[3 * k + 1] = hands[k].surface[1], surf[3 * k + 2] = hands[k].surface[2];
+}
+
+// One thread per candidate `first + b` of round `it`: the hand it is drawn around and the point
+// surface + N(0, I) * sigma (importance_sampling.cpp:118-121,134-139).
+__global__ void k_is_generate(uint64_t seed, uint64_t it, uint64_t first, uint32_t B, const double* __restrict__ surf,
+                              uint32_t H, double sigma, double* __restrict__ cand, int32_t* __restrict__ cand_idx) {
+  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const uint64_t cid = first + b;
+  const uint32_t idx = (uint32_t)(is_hash(seed, it, cid, 6) % (uint64_t)H);
+  cand_idx[b] = (int32_t)idx;
+  for (int a = 0; a < 3; a++)
+    cand[3 * (size_t)b + a] = ag2_dm_add(surf[3 * (size_t)idx + a], ag2_dm_mul(is_normal(seed, it, cid, a), sigma));
+}
+
+// The accepted candidates of a batch whose rank among the accepted ones is below `need` become samples
+// got, got + 1, ... (scan = exclusive prefix of the accept flags, total at scan[B]).
+__global__ void k_is_take(const double* __restrict__ cand, const uint32_t* __restrict__ scan, uint32_t B, uint32_t need,
+                          double* __restrict__ out) {
+  const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const uint32_t r = scan[b];
+  if (scan[b + 1] == r || r >= need) return;
+  out[3 * (size_t)r] = cand[3 * (size_t)b], out[3 * (size_t)r + 1] = cand[3 * (size_t)b + 1];
+  out[3 * (size_t)r + 2] = cand[3 * (size_t)b + 2];
+}
+
+// rand part of a round: samples.col(j) = cloud->points[r].getVector3fMap().cast<double>(), r drawn per sample
+__global__ void k_is_random_points(uint64_t seed, uint64_t it, const float* __restrict__ xyz_in, uint64_t n_points,
+                                   uint32_t n, double* __restrict__ out) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const size_t r = (size_t)(is_hash(seed, it, 0xFFFFFFFFull + (uint64_t)j, 7) % n_points);
+  out[3 * j] = (double)xyz_in[3 * r];
+  out[3 * j + 1] = (double)xyz_in[3 * r + 1];
+  out[3 * j + 2] = (double)xyz_in[3 * r + 2];
 }
 
 // One warp per candidate: accept iff c*d2(x, hand[idx]) >= max_k c*d2(x, hand[k]).
 __global__ void k_is_accept(const double* __restrict__ cand, const int32_t* __restrict__ cand_idx, uint32_t n_cand,
                             const ag2_hypothesis* __restrict__ hands, const double* __restrict__ surf /* 3H, packed */,
-                            uint32_t H, double coef, uint8_t* __restrict__ accept) {
+                            uint32_t H, double coef, uint32_t* __restrict__ accept) {
   const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (c >= n_cand) return;
@@ -112,18 +136,7 @@ __global__ void k_is_accept(const double* __restrict__ cand, const int32_t* __re
       break;
     }
   }
-  if (lane == 0) accept[c] = ok ? 1 : 0;
-}
-
-// rand part of a round: samples.col(j) = cloud->points[r].getVector3fMap().cast<double>()
-__global__ void k_is_gather_points(const float* __restrict__ xyz_in, const int32_t* __restrict__ ridx, uint32_t n,
-                                   double* __restrict__ out) {
-  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  size_t r = (size_t)ridx[j];
-  out[3 * j] = (double)xyz_in[3 * r];
-  out[3 * j + 1] = (double)xyz_in[3 * r + 1];
-  out[3 * j + 2] = (double)xyz_in[3 * r + 2];
+  if (lane == 0) accept[c] = ok ? 1u : 0u;
 }
 
 __global__ void k_is_append(const ag2_hypothesis* __restrict__ src, uint32_t n, int32_t sample_offset,
@@ -150,37 +163,21 @@ int append_selected(ag2_ctx* c, size_t cap, int32_t sample_offset) {
   return AG2_OK;
 }
 
-// The sample batch of round `it` (importance_sampling.cpp:47-86): n_gauss draws close to the
-// hands found so far (d_hands: H records on the device; h_hands: the same on the host, or
-// nullptr to have them read back) followed by n_rand random cloud points, written to d_out
-// (3 * num_samples doubles on the device).  Returns with the stream idle.
-int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis* d_hands, size_t H,
-               const ag2_hypothesis* h_hands, double* d_out) {
+// The sample batch of round `it` (importance_sampling.cpp:47-86): n_gauss draws close to the hands found so far
+// (d_hands: H records on the device) followed by n_rand random cloud points, written to d_out (3 * num_samples
+// doubles on the device).  All on the device; per batch of candidates the host reads back one number (how many
+// were accepted) to decide whether another batch is needed.
+int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis* d_hands, size_t H, double* d_out) {
   cudaStream_t st = c->stream;
   const int ns = ip->num_samples;
   const int n_rand = (int)(ip->prob_rand_samples * ns);  // int num_rand_samples = prob * num_samples
   const int n_gauss = ns - n_rand;
   const double sigma = ip->radius;
   const double coef = -1.0 / (2.0 * sigma);
-  std::vector<double> cand, gauss((size_t)3 * std::max(n_gauss, 1));
-  std::vector<int32_t> cidx, ridx((size_t)std::max(n_rand, 1));
-  std::vector<uint8_t> acc;
-  std::vector<double> surf(3 * H);
-  {
-    // grasp surfaces of all hands so far (host copy for the candidate generator)
-    std::vector<ag2_hypothesis> rec;
-    if (!h_hands) {
-      rec.resize(H);
-      AG2_CUDA(c, cudaMemcpyAsync(rec.data(), d_hands, H * sizeof(ag2_hypothesis), cudaMemcpyDeviceToHost, st));
-      AG2_CUDA(c, cudaStreamSynchronize(st));
-      h_hands = rec.data();
-    }
-    for (size_t k = 0; k < H; k++)
-      for (int a = 0; a < 3; a++) surf[3 * k + a] = h_hands[k].surface[a];
-  }
-  if (ip->method != 1 && n_gauss > 0) {
+  if (n_gauss > 0) {
     AG2_CUDA(c, c->is_surf.reserve(3 * H));
-    AG2_CUDA(c, cudaMemcpyAsync(c->is_surf.p, surf.data(), 24 * H, cudaMemcpyHostToDevice, st));
+    k_is_surf<<<(unsigned)((H + 255) / 256), 256, 0, st>>>(d_hands, (uint32_t)H, c->is_surf.p);
+    AG2_LAUNCH_CHECK(c);
   }
   // 3.1 samples close to the grasps found so far
   int got = 0;
@@ -198,59 +195,35 @@ int draw_round(ag2_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis
       const double rate = next_cand ? std::max((double)got / (double)next_cand, 1e-4) : 0.125;
       B = (size_t)std::min(4.0e6, std::max(256.0, 1.25 * (double)(n_gauss - got) / rate));
     }
-    cand.resize(3 * B);
-    cidx.resize(B);
-    {
-      double* cand_p = cand.data();
-      int32_t* cidx_p = cidx.data();
-      const double* surf_p = surf.data();
-      const uint64_t seed = ip->seed, first = next_cand;
-      parallel_for(B, [=](size_t b0, size_t b1) {
-        for (size_t b = b0; b < b1; b++) {
-          const uint64_t cid = first + b;
-          const size_t idx = (size_t)(is_hash(seed, (uint64_t)it, cid, 6) % (uint64_t)H);
-          cidx_p[b] = (int32_t)idx;
-          for (int a = 0; a < 3; a++)
-            cand_p[3 * b + a] = surf_p[3 * idx + a] + is_normal(seed, (uint64_t)it, cid, a) * sigma;
-        }
-      });
-    }
-    next_cand += B;
-    if (ip->method == 1) {  // sum of Gaussians: every draw is a sample
-      for (size_t b = 0; b < B; b++, got++)
-        for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
-      break;
-    }
     AG2_CUDA(c, c->is_cand.reserve(3 * B));
     AG2_CUDA(c, c->is_cand_idx.reserve(B));
-    AG2_CUDA(c, c->is_accept.reserve(B));
-    acc.resize(B);
-    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand.p, cand.data(), 24 * B, cudaMemcpyHostToDevice, st));
-    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, cidx.data(), 4 * B, cudaMemcpyHostToDevice, st));
-    k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B, d_hands,
-                                                                  c->is_surf.p, (uint32_t)H, coef, c->is_accept.p);
+    k_is_generate<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(ip->seed, (uint64_t)it, next_cand, (uint32_t)B, c->is_surf.p,
+                                                              (uint32_t)H, sigma, c->is_cand.p, c->is_cand_idx.p);
     AG2_LAUNCH_CHECK(c);
-    AG2_CUDA(c, cudaMemcpyAsync(acc.data(), c->is_accept.p, B, cudaMemcpyDeviceToHost, st));
-    AG2_CUDA(c, cudaStreamSynchronize(st));
-    for (size_t b = 0; b < B && got < n_gauss; b++)
-      if (acc[b]) {
-        for (int a = 0; a < 3; a++) gauss[3 * (size_t)got + a] = cand[3 * b + a];
-        got++;
-      }
+    next_cand += B;
+    if (ip->method == 1) {  // sum of Gaussians: every draw is a sample (importance_sampling.cpp:115-125)
+      AG2_CUDA(c, cudaMemcpyAsync(d_out + 3 * (size_t)got, c->is_cand.p, 24 * B, cudaMemcpyDeviceToDevice, st));
+      got += (int)B;
+      break;
+    }
+    AG2_CUDA(c, c->is_flag.reserve(B + 1));
+    k_is_accept<<<(unsigned)((B * 32 + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_cand_idx.p, (uint32_t)B, d_hands,
+                                                                  c->is_surf.p, (uint32_t)H, coef, c->is_flag.p);
+    AG2_LAUNCH_CHECK(c);
+    AG2_TRY(exclusive_scan_u32(c, c->is_flag.p, B));
+    k_is_take<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(c->is_cand.p, c->is_flag.p, (uint32_t)B, (uint32_t)(n_gauss - got),
+                                                          d_out + 3 * (size_t)got);
+    AG2_LAUNCH_CHECK(c);
+    AG2_CUDA(c, cudaMemcpyAsync(c->h_pin + 32, c->is_flag.p + B, 4, cudaMemcpyDeviceToHost, st));
+    AG2_TRY(sync_and_finish(c));
+    got += (int)std::min<uint32_t>(c->h_pin[32], (uint32_t)(n_gauss - got));
   }
   // 3.2 random cloud points
-  for (int j = 0; j < n_rand; j++)
-    ridx[j] = (int32_t)(is_hash(ip->seed, (uint64_t)it, 0xFFFFFFFFull + (uint64_t)j, 7) % (uint64_t)c->n);
-  // 3.3 the round's sample list, assembled on the device
-  if (n_gauss) AG2_CUDA(c, cudaMemcpyAsync(d_out, gauss.data(), (size_t)24 * n_gauss, cudaMemcpyHostToDevice, st));
   if (n_rand) {
-    AG2_CUDA(c, c->is_cand_idx.reserve((size_t)n_rand));
-    AG2_CUDA(c, cudaMemcpyAsync(c->is_cand_idx.p, ridx.data(), (size_t)4 * n_rand, cudaMemcpyHostToDevice, st));
-    k_is_gather_points<<<(n_rand + 255) / 256, 256, 0, st>>>(c->xyz_in.p, c->is_cand_idx.p, (uint32_t)n_rand,
-                                                           d_out + (size_t)3 * n_gauss);
+    k_is_random_points<<<(n_rand + 255) / 256, 256, 0, st>>>(ip->seed, (uint64_t)it, c->xyz_in.p, (uint64_t)c->n,
+                                                           (uint32_t)n_rand, d_out + (size_t)3 * n_gauss);
     AG2_LAUNCH_CHECK(c);
   }
-  AG2_CUDA(c, cudaStreamSynchronize(st));  // the host staging vectors go out of scope
   return AG2_OK;
 }
 
@@ -291,8 +264,7 @@ int importance_detect(ag2_ctx* c, const ag2_is_params* ip) {
 
   for (int it = 0; it < iters; it++) {
     AG2_CUDA(c, c->sample_xyz.reserve((size_t)3 * ns));
-    AG2_TRY(draw_round(c, ip, it, c->list_rec[AG2_LIST_IMPORTANCE].p, c->list_n[AG2_LIST_IMPORTANCE], nullptr,
-                       c->sample_xyz.p));
+    AG2_TRY(draw_round(c, ip, it, c->list_rec[AG2_LIST_IMPORTANCE].p, c->list_n[AG2_LIST_IMPORTANCE], c->sample_xyz.p));
     trace.lap("draw", it);
     AG2_CUDA(c, cudaMemcpyAsync(c->is_samples.p + 3 * c->is_samples_n, c->sample_xyz.p, (size_t)24 * ns,
                                 cudaMemcpyDeviceToDevice, st));
@@ -362,7 +334,7 @@ int ag2_draw_importance_samples(ag2_ctx* c, const ag2_is_params* p, int round, c
   AG2_CUDA(c, c->is_draw.reserve((size_t)3 * p->num_samples));
   AG2_CUDA(c, cudaMemcpyAsync(c->is_hands_in.p, hands, n_hands * sizeof(ag2_hypothesis), cudaMemcpyHostToDevice,
                               c->stream));
-  AG2_TRY(draw_round(c, p, round, c->is_hands_in.p, n_hands, hands, c->is_draw.p));
+  AG2_TRY(draw_round(c, p, round, c->is_hands_in.p, n_hands, c->is_draw.p));
   AG2_CUDA(c, cudaMemcpyAsync(xyz_out, c->is_draw.p, (size_t)24 * p->num_samples, cudaMemcpyDeviceToHost, c->stream));
   AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   return AG2_OK;

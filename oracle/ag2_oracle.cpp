@@ -44,6 +44,7 @@
  * Build: g++ -O3 -fopenmp -ffp-contract=off -fno-fast-math (oracle/Makefile).
  */
 #include "ag2_oracle.h"
+#include "../include/ag2_detmath.h"  // shared with the device sampler by design (deviation D5)
 
 #include <omp.h>
 
@@ -1546,7 +1547,9 @@ inline double is_u01(uint64_t h) { return ((double)(h >> 11) + 0.5) * (1.0 / 900
 inline double is_normal(uint64_t seed, uint64_t round, uint64_t cand, int comp) {
   double u1 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp));
   double u2 = is_u01(is_hash(seed, round, cand, 2 * (uint64_t)comp + 1));
-  return std::sqrt(-2.0 * std::log(u1)) * std::cos(2.0 * M_PI * u2);
+  // Box-Muller on the exactly reproducible log / cos of include/ag2_detmath.h (deviation D5): the same source is
+  // compiled into the device generator, which is what makes the candidates identical bit for bit
+  return ag2_det_normal(u1, u2);
 }
 // the sample batch of one round, importance_sampling.cpp:47-86 with the samplers :115-157
 void is_draw_round(ag2o_ctx* c, const ag2_is_params* ip, int it, const ag2_hypothesis* hands, size_t H,
