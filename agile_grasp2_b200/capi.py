@@ -602,6 +602,11 @@ class Context:
         self._call("classify_images", _fptr(images), C.c_size_t(images.shape[0]), _fptr(out))
         return out
 
+    def classify_images_static_ptr(self, d_images: int, n: int, d_logits: int) -> None:
+        """ag2_classify_images_static: device pointers in and out, fixed scratch inside libag2.so, no
+        allocation; enqueued on the ctx stream (synchronize() before reading the logits)."""
+        self._call("classify_images_static", C.c_void_p(d_images), C.c_size_t(n), C.c_void_p(d_logits))
+
 
 class _BorrowedContext(Context):
     """An ag2_ctx owned by a Group (weights, statistics, stream); closing it does nothing."""

@@ -15,6 +15,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <mutex>
 
 #include "dev_common.cuh"
 #include "tc_ptx.cuh"
@@ -797,4 +798,100 @@ int classify_compute(ag2_ctx* c) {
   return AG2_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// ag2_classify_images_static: the same forward pass for callers that may not allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart
+// in the reference.  The activations (pooled conv1
+// planes, tiled conv2 output, split-K partials of ip1) live in ONE file-scope device array of fixed
+// size instead of the ctx's growing buffer; images and logits are the caller's device buffers.
+// The kernels, their launch shapes and the split-K choice are those of lenet_forward, so the logits
+// are the same bits.  Every GPU that loads libag2.so holds the array (about 26.7 MB) until exit.
+// ---------------------------------------------------------------------------------------------
 }  // namespace ag2
+
+#define AG2_STATIC_A1_FLOATS ((size_t)AG2_CLASSIFY_STATIC_MAX_IMAGES * 20 * 28 * 28) /* pooled conv1 planes */
+#define AG2_STATIC_A2_FLOATS ((size_t)2 * 936 * 1024)                                /* one tile of 128 images, tiled for ip1 */
+#define AG2_STATIC_PART_FLOATS ((size_t)117 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)  /* at most 117 K splits */
+#define AG2_STATIC_FLOATS (AG2_STATIC_A1_FLOATS + AG2_STATIC_A2_FLOATS + AG2_STATIC_PART_FLOATS)
+
+static __device__ __align__(256) float g_classify_static_scratch[AG2_STATIC_FLOATS];
+
+namespace ag2 {
+namespace {
+
+// The array's name is only a stand-in on the host: its device address is asked for once per device,
+// with that device current, and kept here.
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+float* g_static_ptr[kMaxDevices];
+bool g_static_ready[kMaxDevices];
+
+int static_scratch_setup(ag2_ctx* c, float** out) {
+  if (c->device < 0 || c->device >= kMaxDevices) return AG2_E_INVALID;
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ready[c->device]) {
+    float* p = nullptr;
+    AG2_CUDA(c, cudaGetSymbolAddress((void**)&p, g_classify_static_scratch));
+    cudaPointerAttributes at;
+    AG2_CUDA(c, cudaPointerGetAttributes(&at, p));
+    if (at.type != cudaMemoryTypeDevice || at.device != c->device) {
+      c->err = "ag2_classify_images_static: the scratch array did not resolve to memory of the ctx's device";
+      return AG2_E_CUDA;
+    }
+    AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+    AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
+    AG2_CUDA(c, cudaFuncSetAttribute(k_conv1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM_BYTES));
+    g_static_ptr[c->device] = p;
+    g_static_ready[c->device] = true;
+  }
+  *out = g_static_ptr[c->device];
+  return AG2_OK;
+}
+
+}  // namespace
+}  // namespace ag2
+
+extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits) {
+  using namespace ag2;
+  if (!c || (n && (!d_images || !d_logits))) return AG2_E_INVALID;
+  if (n > AG2_CLASSIFY_STATIC_MAX_IMAGES) {
+    char buf[200];
+    snprintf(buf, sizeof(buf),
+             "ag2_classify_images_static: %zu images exceed the fixed scratch (AG2_CLASSIFY_STATIC_MAX_IMAGES = %d)", n,
+             AG2_CLASSIFY_STATIC_MAX_IMAGES);
+    c->err = buf;
+    return AG2_E_CAPACITY;
+  }
+  if (cudaSetDevice(c->device) != cudaSuccess) return AG2_E_NO_DEVICE;
+  if (!c->net.loaded) return AG2_E_NO_WEIGHTS;
+  if (n == 0) return AG2_OK;
+  float* scratch = nullptr;
+  AG2_TRY(static_scratch_setup(c, &scratch));
+  const LeNetDev& L = c->net;
+  cudaStream_t st = c->stream;
+  // lenet_forward's split choice for one tile of images: the largest divisor of the 936 K' steps that fits one wave
+  static const int divs[] = {117, 104, 78, 72, 52, 39};
+  int splits = 39;
+  for (int d : divs)
+    if (d <= c->sm_count) {
+      splits = d;
+      break;
+    }
+  const int steps_per_split = I1_KSTEPS / splits;
+  float* a1 = scratch;
+  float* a2 = a1 + AG2_STATIC_A1_FLOATS;
+  float* part = a2 + AG2_STATIC_A2_FLOATS;
+  // Nothing has to start at zero: every word a valid image's logits depend on is written earlier in this call
+  // (k_conv2_tc writes the two zero channels of each chunk itself); rows of the image tile beyond n keep the last
+  // call's values and only feed accumulator columns that are never stored.
+  const unsigned m = (unsigned)n;
+  k_conv1_tc<<<m, 256, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1));
+  AG2_LAUNCH_CHECK(c);
+  k_conv2_tc<true><<<m, 256, TC_SMEM_BYTES, st>>>(reinterpret_cast<const float4*>(a1), L.c2w_tc.p, L.c2b.p, a2);
+  AG2_LAUNCH_CHECK(c);
+  k_ip1_tc<<<dim3(1, splits), 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
+  AG2_LAUNCH_CHECK(c);
+  k_ip2<<<m, 128, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p, d_logits, (int)m);
+  AG2_LAUNCH_CHECK(c);
+  return AG2_OK;
+}

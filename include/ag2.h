@@ -360,6 +360,19 @@ int ag2_get_in_box(ag2_ctx* ctx, int which, size_t h, int32_t* idx, size_t cap, 
 int ag2_get_logits(ag2_ctx* ctx, float* out, size_t cap_images);
 /* Classifier::ClassifyBatch on caller images (HWC u8, 60x60x3): 2 floats per image. */
 int ag2_classify_images(ag2_ctx* ctx, const uint8_t* images, size_t n, float* logits_out);
+/* The same classifier pass for callers that may not allocate (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * d_images (n x 10800 bytes, HWC u8) and d_logits (2 floats per image) are
+ * DEVICE buffers of the ctx's GPU, owned by the caller; the activations live in a fixed array inside
+ * libag2.so (about 26.7 MB, held by every GPU that loads the library until exit), so the call makes
+ * no cudaMalloc / cudaFree and at most AG2_CLASSIFY_STATIC_MAX_IMAGES images go in one call
+ * (more: AG2_E_CAPACITY, nothing launched).  The kernels are enqueued on the ctx stream and the call
+ * returns without waiting: the logits are ready after ag2_synchronize, or for work ordered behind
+ * ag2_get_stream's stream.  The weights must have been set before (that step allocates).  All calls
+ * on one GPU, from any ctx, share the array: two calls that overlap on the GPU (two ctx of one
+ * device) race; calls on one ctx are ordered by its stream.  Logits equal ag2_classify_images'. */
+#define AG2_CLASSIFY_STATIC_MAX_IMAGES 64
+int ag2_classify_images_static(ag2_ctx* ctx, const uint8_t* d_images, size_t n, float* d_logits);
 
 /* ---- on-disk / wire formats (next row f3; host code, no ctx needed) -------- */
 
