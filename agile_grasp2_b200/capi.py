@@ -210,8 +210,28 @@ def load() -> Api:
     """Loads libag2.so (the CUDA library).  Raises if it is missing."""
     global _api
     if _api is None:
+        _preload_bundled_nccl()
         _api = Api(LIB_PATH, "ag2_")
     return _api
+
+
+def _preload_bundled_nccl():
+    """libag2.so needs libnccl.so.2 and so does torch, which ships a newer one than the system's: whichever is loaded
+    first serves both.  Loading torch's copy first (when there is one) keeps a later `import torch` working in a
+    process that loaded libag2.so before it; libag2 only uses calls that are the same in both."""
+    import importlib.util
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+    except Exception:
+        spec = None
+    for d in (spec.submodule_search_locations if spec else []):
+        path = os.path.join(d, "lib", "libnccl.so.2")
+        if os.path.exists(path):
+            try:
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+            except OSError:
+                pass
+            return
 
 
 def default_params() -> Params:

@@ -4,8 +4,8 @@
 //   data[B,3,60,60] (u8 image planes as float 0..255, no mean, no scale)
 //   conv1 20@5x5 -> maxpool 2/2 -> conv2 50@5x5 -> maxpool 2/2 -> ip1 500 -> ReLU -> ip2 2
 // and returns the raw ip2 logits (caffe_classifier.cpp:121-126).
-// conv1, conv2 and ip1 run on the tensor cores (k_conv1_tc, k_conv2_tc, k_ip1_tc: tcgen05 MMA,
-// tf32 operands split into hi + lo terms for fp32 accuracy, accumulators in tensor memory; PTX
+// conv1, conv2 and ip1 run on the tensor cores (k_conv1_tc, k_conv2_h, k_ip1_tc: tcgen05 MMA,
+// tf32 (conv1, ip1) or fp16 (conv2) operands split into hi + lo terms for fp32 accuracy, accumulators in tensor memory; PTX
 // wrappers in tc_ptx.cuh), pooling / bias fused into the epilogues; k_ip2 finishes the split-K
 // sum, bias, ReLU and the 500 -> 2 product.  The fp32 CUDA-core kernels of the first version
 // (k_conv1_pool, k_conv2_pool, k_ip1_partial) are kept as an independent cross-check
@@ -13,6 +13,8 @@
 // tolerance on logits.  Built WITH fma contraction.
 #include <math.h>
 #include <stdlib.h>
+
+#include <cmath>
 
 #include <algorithm>
 #include <mutex>
@@ -138,34 +140,20 @@ k_conv2_pool(const float* __restrict__ in /* [n][5][28*28][4], see k_conv1_pool 
 }
 
 // ---------------------------------------------------------------------------------------------
-// conv2 (20->50, 5x5) + bias + maxpool 2x2 on the 5th-generation tensor cores: an implicit GEMM
-// whose A operand is never materialised.  One CTA per image.
+// The convolutions on the 5th-generation tensor cores: implicit GEMMs whose A operand is never
+// materialised (conv2 below; conv1 applies the same idea to the 60 x 60 input).
 //
-//   D[position][out channel] = sum over the 25 taps, 20 input channels of in * w
+//   D[position][out channel] = sum over the 25 taps and the input channels of in * w
 //
-// The pooled conv1 planes sit in shared memory as [channel quad j][pixel][4 channels]: one
-// pixel of one quad is one 16-byte K chunk, eight pixels that are consecutive in x are one
-// 8-row core matrix of the no-swizzle K-major canonical layout, and image rows are a
-// constant 28 pixels = 448 bytes (the descriptor's SBO) apart.  An M = 128 tile is therefore a
-// block of 8 (x) by 16 (y) output positions, and the A tile of tap (ky, kx) is the SAME bytes
-// read through a descriptor whose start address is moved by (ky*28 + kx) pixels.  Six tiles
-// (x0 = 0, 8, 16; y0 = 0, 8) cover the 24 x 24 outputs; rows 8..15 of the y0 = 8 tiles repeat.
-// K runs over 25 taps x 3 steps of 8 channels (quads 2s and 2s+1; the quad after channel 19
-// is a plane of zeros).  fp32 accuracy comes from a three-term tf32 split
-//   a*b ~= a_hi*b_hi + a_lo*b_hi + a_hi*b_lo      (tc::split_tf32; the dropped lo*lo term and
-// the truncations are <= 2^-21 relative), accumulated in fp32 in tensor memory: 6 tiles x 64
-// columns.  The weights arrive pre-split and pre-tiled per tap (lenet_upload) through a
-// 4-slot ring of bulk copies; one thread issues the copies and the MMAs (1350 per image).
+// An input plane sits in shared memory as [pixel][one 16-byte chunk of channels]: one pixel is one
+// K chunk, eight pixels that are consecutive in x are one 8-row core matrix of the no-swizzle
+// K-major canonical layout, and image rows are a constant number of pixels (28 for conv2: 448
+// bytes, the descriptor's SBO) apart.  An M = 128 tile is therefore a block of 8 (x) by 16 (y)
+// output positions, and the A tile of tap (ky, kx) is the SAME bytes read through a descriptor
+// whose start address is moved by (ky*28 + kx) pixels.  For conv2 six tiles (x0 = 0, 8, 16;
+// y0 = 0, 8) cover the 24 x 24 outputs; rows 8..15 of the y0 = 8 tiles repeat.
 // ---------------------------------------------------------------------------------------------
-constexpr int TC_PIX = P1 * P1;                                   // 784 pixels per plane
-constexpr int TC_PLANE_BYTES = TC_PIX * 16;                       // 12544
-constexpr int TC_A_PLANES = 11;                                   // 5 hi, 5 lo, 1 zero
-constexpr int TC_A_BYTES = TC_A_PLANES * TC_PLANE_BYTES;          // 137984
-constexpr int TC_BTAP_FLOATS = 2 * 3 * 2 * 64 * 4;                // [hi/lo][k step][chunk][64 n][4] = 3072
-constexpr int TC_BTAP_BYTES = TC_BTAP_FLOATS * 4;                 // 12288
-constexpr int TC_BSLOTS = 4;
-constexpr int TC_SMEM_BYTES = TC_A_BYTES + TC_BSLOTS * TC_BTAP_BYTES + 128;
-constexpr int TC_TMEM_COLS = 512;                                 // 6 x 64 used; power of two
+constexpr int TC_PIX = P1 * P1;  // 784 pixels per plane
 
 // ---------------------------------------------------------------------------------------------
 // conv1 (3->20, 5x5) + bias + maxpool 2x2 on the tensor cores: the same zero-copy implicit GEMM as
@@ -179,15 +167,30 @@ constexpr int TC_TMEM_COLS = 512;                                 // 6 x 64 used
 // of 7 tiles (y0 = 0, 16, 32, 40; 224 of 256 allocated tensor-memory columns), so two CTAs fit an
 // SM and one CTA's epilogue overlaps the other's MMAs.  728 MMAs per image.
 // ---------------------------------------------------------------------------------------------
+// fp16 operand planes shared by k_conv1_tc's epilogue (writer) and k_conv2_h (reader): per image
+// [hi, lo][plane p = channels 8p .. 8p+7][784 pixels][8 halfs]
+constexpr int H_PLANE_BYTES = TC_PIX * 16;               // 12544
+constexpr int H_IMG_PLANES = 6;
+constexpr int H_IMG_BYTES = H_IMG_PLANES * H_PLANE_BYTES;  // 75264
+constexpr int H_KSTEPS = 38;                             // 25 x (one tap, planes 0 + 1) + 13 x (two taps, plane 2)
+constexpr int H_STEP_BYTES = 2 * 64 * 16;                // [chunk][64 out channels][8 halfs] = 2048
+constexpr int H_ITEM_STEPS = 4;
+constexpr int H_ITEMS = 10;                              // 9 x 4 + 2 K steps
+constexpr int H_ITEM_BYTES = 2 * H_ITEM_STEPS * H_STEP_BYTES;  // [hi: 4 steps][lo: 4 steps] = 16384
+constexpr int H_SLOTS = 4;
+constexpr int H_SMEM_BYTES = 2 * H_IMG_BYTES + H_SLOTS * H_ITEM_BYTES + 256;  // 216320
+
 constexpr int C1_PIX = 60 * 60 + 4;                       // one pixel past the end is read by the zero-weight tap
 constexpr int C1_A_BYTES = C1_PIX * 16;                   // 57664
 constexpr int C1_B_FLOATS = 13 * 2 * 2 * 32 * 4;          // [k step][lo/hi... see lenet_upload] = 6656
 constexpr int C1_B_BYTES = C1_B_FLOATS * 4;               // 26624
 constexpr int C1_SMEM_BYTES = C1_A_BYTES + C1_B_BYTES + 64;
 
+template <bool HALF_OUT>
 __global__ void __launch_bounds__(256, 2)
 k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* [13][hi, lo][2 chunks][32][4] */,
-           const float* __restrict__ bias, float4* __restrict__ out /* [n][5][784] float4 */) {
+           const float* __restrict__ bias, float4* __restrict__ out /* [n][5][784] float4, or the fp16 planes of k_conv2_h */,
+           float a_scale /* HALF_OUT: power of two that brings the activations into fp16's range */) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
   float4* A = reinterpret_cast<float4*>(tc_smem);
   uint8_t* B = tc_smem + C1_A_BYTES;
@@ -236,7 +239,7 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
         const uint32_t a_base = tc::smem_u32(A) >> 4, b_base = tc::smem_u32(B) >> 4;
         const uint64_t b_hi64 = tc::smem_desc(0, 512, 128);
 #pragma unroll 1
-        for (int prec = 1; prec >= 0; prec--) {  // w_lo (small terms) first, w_hi last: see k_conv2_tc
+        for (int prec = 1; prec >= 0; prec--) {  // w_lo (small terms) first, w_hi last: see k_conv2_h
 #pragma unroll 1
           for (int s = 0; s < 13; s++) {
             const int t0 = 2 * s;  // taps t0 and t0 + 1
@@ -270,9 +273,29 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
           float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
           v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) + __ldg(&bias[ch]);
         }
+        if (!HALF_OUT) {
 #pragma unroll
-        for (int cq = 0; cq < 5; cq++)
-          if ((cq & 3) == q) o[cq * (P1 * P1) + py * P1 + px] = make_float4(v[4 * cq], v[4 * cq + 1], v[4 * cq + 2], v[4 * cq + 3]);
+          for (int cq = 0; cq < 5; cq++)
+            if ((cq & 3) == q) o[cq * (P1 * P1) + py * P1 + px] = make_float4(v[4 * cq], v[4 * cq + 1], v[4 * cq + 2], v[4 * cq + 3]);
+        } else {
+          // lane p of the pooling quad writes plane p (channels 8p .. 8p+7; 20 .. 23 are zero) as its fp16 hi and lo parts
+          uint4* oh = reinterpret_cast<uint4*>(out) + (size_t)blockIdx.x * H_IMG_PLANES * TC_PIX + py * P1 + px;
+#pragma unroll
+          for (int pl = 0; pl < 3; pl++)
+            if (q == pl) {
+              uint32_t hw[4], lw[4];
+#pragma unroll
+              for (int e = 0; e < 4; e++) {
+                uint16_t h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+                if (8 * pl + 2 * e < C1_OUT) tc::split_f16(v[8 * pl + 2 * e] * a_scale, h0, l0);
+                if (8 * pl + 2 * e + 1 < C1_OUT) tc::split_f16(v[8 * pl + 2 * e + 1] * a_scale, h1, l1);
+                hw[e] = (uint32_t)h0 | ((uint32_t)h1 << 16);
+                lw[e] = (uint32_t)l0 | ((uint32_t)l1 << 16);
+              }
+              oh[pl * TC_PIX] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+              oh[(3 + pl) * TC_PIX] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            }
+        }
       }
     }
     tc::fence_before_sync();
@@ -286,163 +309,252 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
 // 936 steps of 8, in chunks of 4 channels
 constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
 
+// ---------------------------------------------------------------------------------------------
+// conv2 on fp16 operands (kind::f16, K = 16 per MMA): the zero-copy implicit GEMM described above
+// with half the MMAs per image of a tf32 version, as a persistent, warp-specialised kernel.
+//
+// Operands.  Activations and weights are scaled by powers of two into fp16's range (exact) and split
+// into hi + lo fp16 terms (tc::split_f16: 22 significant bits, as the tf32 split); the product is
+//   a*b ~= a_lo*b_hi + a_hi*b_lo (first, into a tiny accumulator) + a_hi*b_hi, fp32 in tensor memory,
+// and the epilogue multiplies by the inverse scale (a power of two).  k_conv1_tc writes the planes
+// (HALF_OUT), so staging an image is six bulk copies and no thread touches the A operand.
+// One 16-byte chunk = 8 channels of one pixel; the 20 input channels are planes 0, 1 and half of
+// plane 2.  One K step = two chunks, LBO apart: (tap t: plane 0, plane 1) for the 25 taps, then
+// (tap 2j, tap 2j+1) of plane 2 -- the second chunk is the same plane one tap further -- for 13
+// more: 38 K steps instead of 75, each the same 6 KB of shared-memory operand reads per MMA.
+//
+// Schedule.  grid = min(images, SMs); a CTA walks its images.  Warp 0 issues the MMAs, warp 1 the
+// bulk copies (weights through a 4-slot ring of 4-K-step items, streamed once per tile group and
+// pass; the next image's planes into the other A buffer), warps 2..5 run the epilogue, one per
+// tensor-memory lane quarter.  The six M tiles form two groups (y0 = 0 and y0 = 8, 192 columns each)
+// that are accumulated one after the other: while group 1 accumulates, group 0 is pooled and
+// stored, and group 1 drains under the next image's group 0.  Nothing but the first image's load
+// and the last group's epilogue is exposed.
+// ---------------------------------------------------------------------------------------------
+// K step k of k_conv2_h: start of its first chunk (in pixels = 16-byte units from the hi planes' base) and the
+// distance to its second chunk (the descriptor's LBO)
+struct HStepTable {
+  uint2 v[H_KSTEPS];
+};
+constexpr HStepTable make_hsteps() {
+  HStepTable t{};
+  for (int k = 0; k < H_KSTEPS; k++) {
+    if (k < 25) {
+      t.v[k].x = (unsigned)((k / 5) * P1 + k % 5);
+      t.v[k].y = (unsigned)TC_PIX;  // plane 0 -> plane 1
+    } else {
+      const int j = k - 25, t0 = j < 12 ? 2 * j : 23, t1 = t0 + 1;  // the last step repeats tap 23 with zero weights
+      t.v[k].x = (unsigned)(2 * TC_PIX + (t0 / 5) * P1 + t0 % 5);
+      t.v[k].y = (unsigned)(((t1 / 5) * P1 + t1 % 5) - ((t0 / 5) * P1 + t0 % 5));
+    }
+  }
+  return t;
+}
+__constant__ HStepTable c_hsteps = make_hsteps();
+
 template <bool TILED_OUT>
-__global__ void __launch_bounds__(256, 1)
-k_conv2_tc(const float4* __restrict__ in /* [n][5][784] float4, see k_conv1_pool */,
-           const float* __restrict__ wtc /* [25][TC_BTAP_FLOATS] */, const float* __restrict__ bias,
-           float* __restrict__ out /* plain [n][50][12][12], or tiled for k_ip1_tc */) {
+__global__ void __launch_bounds__(192, 1)
+k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const uint16_t* __restrict__ wh /* [10 items][16 KB] */,
+          const float* __restrict__ bias, float inv_scale, float* __restrict__ out, int n) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
-  float4* A = reinterpret_cast<float4*>(tc_smem);
-  uint8_t* Bring = tc_smem + TC_A_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + TC_A_BYTES + TC_BSLOTS * TC_BTAP_BYTES);
-  uint64_t* empty = full + TC_BSLOTS;
-  uint64_t* done = empty + TC_BSLOTS;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  uint8_t* A = tc_smem;
+  uint8_t* Bring = tc_smem + 2 * H_IMG_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + 2 * H_IMG_BYTES + H_SLOTS * H_ITEM_BYTES);
+  uint64_t* empty = full + H_SLOTS;
+  uint64_t* a_full = empty + H_SLOTS;
+  uint64_t* a_empty = a_full + 2;
+  uint64_t* t_full = a_empty + 2;
+  uint64_t* t_empty = t_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
-    for (int i = 0; i < TC_BSLOTS; i++) tc::mbar_init(&full[i], 1), tc::mbar_init(&empty[i], 1);
-    tc::mbar_init(done, 1);
+    for (int i = 0; i < H_SLOTS; i++) tc::mbar_init(&full[i], 1), tc::mbar_init(&empty[i], 1);
+    for (int i = 0; i < 2; i++) {
+      tc::mbar_init(&a_full[i], 1), tc::mbar_init(&a_empty[i], 1);
+      tc::mbar_init(&t_full[i], 1), tc::mbar_init(&t_empty[i], 4);
+    }
     tc::mbar_init_fence();
   }
-  if (warp == 1) tc::tmem_alloc<TC_TMEM_COLS>(tmem_slot);
-  // stage the image: split every value into its two tf32 terms
-  const float4* src = in + (size_t)blockIdx.x * 5 * TC_PIX;
-  {
-    constexpr int kPer = (5 * TC_PIX + 255) / 256;  // 16 float4 per thread, all loads in flight at once
-    float4 v[kPer];
-#pragma unroll
-    for (int u = 0; u < kPer; u++) {
-      const int i = tid + u * 256;
-      v[u] = i < 5 * TC_PIX ? __ldg(&src[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int u = 0; u < kPer; u++) {
-      const int i = tid + u * 256;
-      float4 h, l;
-      tc::split_tf32(v[u].x, h.x, l.x);
-      tc::split_tf32(v[u].y, h.y, l.y);
-      tc::split_tf32(v[u].z, h.z, l.z);
-      tc::split_tf32(v[u].w, h.w, l.w);
-      if (i < 5 * TC_PIX) {
-        A[i] = h;
-        A[5 * TC_PIX + i] = l;
-      }
-    }
-  }
-  for (int i = tid; i < TC_PIX; i += 256) A[10 * TC_PIX + i] = make_float4(0.f, 0.f, 0.f, 0.f);
-  tc::fence_async_smem();
+  if (warp == 1) tc::tmem_alloc<512>(tmem_slot);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
+  const int first = blockIdx.x, stride = gridDim.x;
 
   if (warp == 0) {
-    // the whole warp walks the ring (converged); one elected lane issues copies, MMAs and commits
+    // ---- MMA issue ----
     const bool leader = tc::elect_one();
-    const uint32_t idesc = tc::idesc_tf32(128, 64);
-    const uint32_t a_base = tc::smem_u32(A), b_base = tc::smem_u32(Bring);
-    // 50 ring items: the 25 taps twice.  First the two cross terms (a_lo*b_hi, a_hi*b_lo; needs
-    // both weight halves), then the main term a_hi*b_hi (hi half only).  The tensor core
-    // truncates when it adds into the fp32 accumulator; with the small terms first the 150
-    // cross MMAs round against a tiny accumulator and only the 75 main MMAs contribute bias.
-    auto load = [&](int i) {
-      const int slot = i % TC_BSLOTS, t = i % 25;
-      const uint32_t bytes = i < 25 ? TC_BTAP_BYTES : TC_BTAP_BYTES / 2;
-      if (leader) {
-        tc::mbar_expect_tx(&full[slot], bytes);
-        tc::bulk_g2s(Bring + slot * TC_BTAP_BYTES, wtc + (size_t)t * TC_BTAP_FLOATS, bytes, &full[slot]);
-      }
-    };
-    // descriptor halves that do not change: high word (SBO, version) and the LBO field
+    const uint32_t idesc = tc::idesc_f16(128, 64);
     const uint64_t a_hi64 = tc::smem_desc(0, 0, P1 * 16), b_hi64 = tc::smem_desc(0, 1024, 128);
-    for (int i = 0; i < TC_BSLOTS - 1; i++) load(i);
-    for (int i = 0; i < 50; i++) {
-      const int slot = i % TC_BSLOTS, t = i % 25;
-      const bool cross = i < 25;
-      tc::mbar_wait(&full[slot], (i / TC_BSLOTS) & 1);
+    uint32_t ring_i = 0;
+    for (int it = 0, img = first; img < n; img += stride, it++) {
+      const int buf = it & 1;
+      tc::mbar_wait(&a_full[buf], (it >> 1) & 1);
       tc::fence_after_sync();
-      const uint32_t tap_off = (uint32_t)((t / 5) * P1 + t % 5);  // in 16-byte units (one pixel)
-      const uint32_t b_slot = (b_base + slot * TC_BTAP_BYTES) >> 4;
-      for (int s = 0; s < 3; s++) {
-        // chunk 0 = quad 2s, chunk 1 = quad 2s+1 (the zero plane, index 10, for s == 2)
-        const uint32_t a_hi = ((a_base + (2 * s) * TC_PLANE_BYTES) >> 4) + tap_off;
-        const uint32_t a_lo = ((a_base + (5 + 2 * s) * TC_PLANE_BYTES) >> 4) + tap_off;
-        const uint32_t lbo_hi = ((s < 2 ? 1 : 6) * TC_PLANE_BYTES) >> 4, lbo_lo = TC_PLANE_BYTES >> 4;
-        for (int combo = cross ? 1 : 0; combo < (cross ? 3 : 1); combo++) {
-          const uint64_t a_desc0 = a_hi64 | (uint64_t)(combo == 1 ? a_lo : a_hi) |
-                                   ((uint64_t)(combo == 1 ? lbo_lo : lbo_hi) << 16);
-          const uint64_t b_desc = b_hi64 | (uint64_t)(b_slot + ((combo == 2 ? 3 : 0) + s) * 128);
-          const uint32_t acc = (i | s | (combo - 1)) != 0;
-          if (leader) {
+      const uint32_t a_base16 = tc::smem_u32(A + buf * H_IMG_BYTES) >> 4;
+      for (int g = 0; g < 2; g++) {
+        tc::mbar_wait(&t_empty[g], (it & 1) ^ 1);  // the previous image's group g has been read
+        tc::fence_after_sync();
+        const uint32_t a_g16 = a_base16 + (uint32_t)(g * 8 * P1);
+        for (int pass = 0; pass < 2; pass++) {  // 0: the two cross terms, 1: the main term
+          for (int item = 0; item < H_ITEMS; item++, ring_i++) {
+            const int slot = ring_i % H_SLOTS;
+            tc::mbar_wait(&full[slot], (ring_i / H_SLOTS) & 1);
+            tc::fence_after_sync();
+            if (leader) {
+              // lean issue path: the descriptors of a step differ from a per-step constant by small additions only
+              const uint64_t b_desc0 = b_hi64 | (uint64_t)(tc::smem_u32(Bring + slot * H_ITEM_BYTES) >> 4);
+              const int nsteps = item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS;
+              const uint32_t d0 = tmem + g * 192;
 #pragma unroll
-            for (int tile = 0; tile < 6; tile++)  // the start address field never carries (addresses < 256 KB)
-              tc::mma_tf32(tmem + tile * 64, a_desc0 + (uint64_t)((tile / 3) * 8 * P1 + (tile % 3) * 8), b_desc, idesc,
-                           acc);
+              for (int s = 0; s < H_ITEM_STEPS; s++) {
+                if (s < nsteps) {
+                  const uint2 st = c_hsteps.v[item * H_ITEM_STEPS + s];
+                  const uint64_t a_desc = a_hi64 | ((uint64_t)st.y << 16) | (uint64_t)(a_g16 + st.x);
+                  const uint64_t b_desc = b_desc0 + (uint64_t)(s * (H_STEP_BYTES >> 4));
+                  if (pass == 0) {
+                    const uint32_t acc = (item | s) != 0;
+                    const uint64_t a_lo = a_desc + (uint64_t)(3 * TC_PIX), b_lo = b_desc + (uint64_t)((H_ITEM_BYTES / 2) >> 4);
+                    tc::mma_f16(d0, a_lo, b_desc, idesc, acc);  // a_lo * b_hi
+                    tc::mma_f16(d0 + 64, a_lo + 8, b_desc, idesc, acc);
+                    tc::mma_f16(d0 + 128, a_lo + 16, b_desc, idesc, acc);
+                    tc::mma_f16(d0, a_desc, b_lo, idesc, 1);  // a_hi * b_lo
+                    tc::mma_f16(d0 + 64, a_desc + 8, b_lo, idesc, 1);
+                    tc::mma_f16(d0 + 128, a_desc + 16, b_lo, idesc, 1);
+                  } else {
+                    tc::mma_f16(d0, a_desc, b_desc, idesc, 1);  // a_hi * b_hi
+                    tc::mma_f16(d0 + 64, a_desc + 8, b_desc, idesc, 1);
+                    tc::mma_f16(d0 + 128, a_desc + 16, b_desc, idesc, 1);
+                  }
+                }
+              }
+              tc::mma_commit(&empty[slot]);
+            }
+            __syncwarp();
           }
         }
+        if (leader) tc::mma_commit(&t_full[g]);
+        __syncwarp();
       }
-      if (leader) tc::mma_commit(&empty[slot]);
-      // refill the slot of item i-1 with item i+3 once its MMAs have drained
-      const int ni = i + TC_BSLOTS - 1;
-      if (ni < 50) {
-        if (i >= 1) tc::mbar_wait(&empty[ni % TC_BSLOTS], ((i - 1) / TC_BSLOTS) & 1);
-        load(ni);
+      if (leader) tc::mma_commit(&a_empty[buf]);
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ---- bulk copies: operand planes of the next image, weight items ----
+    const bool leader = tc::elect_one();
+    auto load_a = [&](int it, int img) {
+      const int buf = it & 1;
+      tc::mbar_wait(&a_empty[buf], ((it >> 1) & 1) ^ 1);
+      if (leader) {
+        tc::mbar_expect_tx(&a_full[buf], H_IMG_BYTES);
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(in) + (size_t)img * H_IMG_BYTES;
+        for (int pl = 0; pl < H_IMG_PLANES; pl++)
+          tc::bulk_g2s(A + buf * H_IMG_BYTES + pl * H_PLANE_BYTES, src + pl * H_PLANE_BYTES, H_PLANE_BYTES, &a_full[buf]);
       }
-    }
-    if (leader) tc::mma_commit(done);
-    __syncwarp();
-  }
-  tc::mbar_wait(done, 0);
-  tc::fence_after_sync();
-
-  // epilogue: warp w reads TMEM lanes 32*(w%4)..+31 = image rows y0+4*(w%4)..+3, 8 x positions each;
-  // the 2x2 pooling partners are lanes ^1 (x) and ^8 (y).  After the two shuffles the four lanes
-  // of a pooling quad hold the same 50 values; lane q of the quad stores every fourth channel
-  // (plain layout) or every fourth 4-channel chunk (tiled layout for k_ip1_tc).
-  const int wq = warp & 3;
-  const int img = blockIdx.x;
-  for (int tile = warp >> 2; tile < 6; tile += 2) {
-    const int xr = tile % 3, yr = tile / 3;
-    if (yr == 1 && wq < 2) continue;  // rows 8..15 were produced by the y0 = 0 tile
-    float v[64];
-    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + tile * 64;
-    tc::tmem_ld32(taddr, v);
-    tc::tmem_ld32(taddr + 32, v + 32);
-    tc::tmem_ld_wait();
-    const int py = (yr * 8 + wq * 4 + (lane >> 3)) >> 1, px = (xr * 8 + (lane & 7)) >> 1;
-    const int q = (lane & 1) | ((lane >> 2) & 2);
-#pragma unroll
-    for (int ch = 0; ch < C2_OUT; ch++) {
-      float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
-      v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) + __ldg(&bias[ch]);
-    }
-    if (!TILED_OUT) {
-      float* o = out + (size_t)img * C2_OUT * P2 * P2;
-#pragma unroll
-      for (int ch = 0; ch < C2_OUT; ch++)
-        if ((ch & 3) == q) o[(ch * P2 + py) * P2 + px] = v[ch];
-    } else {
-      // [image tile of 128][chunk = pos*13 + ch/4][hi, lo][image row][4 channels]; channels 50, 51 are zero
-      v[50] = v[51] = 0.f;
-      float4* o = reinterpret_cast<float4*>(out) +
-                  ((size_t)(img >> 7) * I1_CHUNKS + (size_t)(py * P2 + px) * 13) * 256 + (img & 127);
-#pragma unroll
-      for (int cq = 0; cq < 13; cq++)
-        if ((cq & 3) == q) {
-          float4 h, l;
-          tc::split_tf32(v[4 * cq], h.x, l.x);
-          tc::split_tf32(v[4 * cq + 1], h.y, l.y);
-          tc::split_tf32(v[4 * cq + 2], h.z, l.z);
-          tc::split_tf32(v[4 * cq + 3], h.w, l.w);
-          o[cq * 256] = h;
-          o[cq * 256 + 128] = l;
+      __syncwarp();
+    };
+    uint32_t ring_i = 0;
+    if (first < n) load_a(0, first);
+    for (int it = 0, img = first; img < n; img += stride, it++) {
+      for (int q = 0; q < 4 * H_ITEMS; q++, ring_i++) {  // (group, pass, item)
+        const int pass = (q / H_ITEMS) & 1, item = q % H_ITEMS;
+        const int slot = ring_i % H_SLOTS;
+        tc::mbar_wait(&empty[slot], ((ring_i / H_SLOTS) & 1) ^ 1);
+        if (leader) {
+          const uint32_t half = (uint32_t)(item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS) * H_STEP_BYTES;
+          const uint8_t* src = reinterpret_cast<const uint8_t*>(wh) + (size_t)item * H_ITEM_BYTES;
+          uint8_t* dst = Bring + slot * H_ITEM_BYTES;
+          tc::mbar_expect_tx(&full[slot], pass ? half : 2 * half);
+          tc::bulk_g2s(dst, src, half, &full[slot]);
+          if (!pass) tc::bulk_g2s(dst + H_ITEM_BYTES / 2, src + H_ITEM_BYTES / 2, half, &full[slot]);
         }
+        __syncwarp();
+        // by now the MMAs of the previous image have drained (this image's first item has): its A buffer is free
+        if (q == H_SLOTS && img + stride < n) load_a(it + 1, img + stride);
+      }
+    }
+  } else {
+    // ---- epilogue: warp w reads tensor-memory lanes 32*(w%4)..+31 = image rows y0 + 4*(w%4)..+3, 8 x positions each;
+    // the 2x2 pooling partners are lanes ^1 (x) and ^8 (y); lane q of a pooling quad stores every fourth chunk ----
+    const int wq = warp & 3;
+    for (int it = 0, img = first; img < n; img += stride, it++) {
+      for (int g = 0; g < 2; g++) {
+        tc::mbar_wait(&t_full[g], it & 1);
+        tc::fence_after_sync();
+        if (!(g == 1 && wq < 2)) {  // rows 8..15 were produced by group 0
+#pragma unroll 1
+          for (int xr = 0; xr < 3; xr++) {
+            float v[64];
+            const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (g * 3 + xr) * 64;
+            tc::tmem_ld32(taddr, v);
+            tc::tmem_ld32(taddr + 32, v + 32);
+            tc::tmem_ld_wait();
+            const int py = (g * 8 + wq * 4 + (lane >> 3)) >> 1, px = (xr * 8 + (lane & 7)) >> 1;
+            const int q = (lane & 1) | ((lane >> 2) & 2);
+#pragma unroll
+            for (int ch = 0; ch < C2_OUT; ch++) {
+              float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
+              v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) * inv_scale + __ldg(&bias[ch]);
+            }
+            if (!TILED_OUT) {
+              float* o = out + (size_t)img * C2_OUT * P2 * P2;
+#pragma unroll
+              for (int ch = 0; ch < C2_OUT; ch++)
+                if ((ch & 3) == q) o[(ch * P2 + py) * P2 + px] = v[ch];
+            } else {
+              // [image tile of 128][chunk = pos*13 + ch/4][hi, lo][image row][4 channels]; channels 50, 51 are zero
+              v[50] = v[51] = 0.f;
+              float4* o = reinterpret_cast<float4*>(out) +
+                          ((size_t)(img >> 7) * I1_CHUNKS + (size_t)(py * P2 + px) * 13) * 256 + (img & 127);
+#pragma unroll
+              for (int cq = 0; cq < 13; cq++)
+                if ((cq & 3) == q) {
+                  float4 h, l;
+                  tc::split_tf32(v[4 * cq], h.x, l.x);
+                  tc::split_tf32(v[4 * cq + 1], h.y, l.y);
+                  tc::split_tf32(v[4 * cq + 2], h.z, l.z);
+                  tc::split_tf32(v[4 * cq + 3], h.w, l.w);
+                  o[cq * 256] = h;
+                  o[cq * 256 + 128] = l;
+                }
+            }
+          }
+        }
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&t_empty[g]);
+      }
     }
   }
   tc::fence_before_sync();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc<TC_TMEM_COLS>(tmem);
+  if (warp == 1) tc::tmem_dealloc<512>(tmem);
+}
+
+// fp32 pooled conv1 planes ([n][5][784] float4, k_conv1_pool) -> the fp16 planes k_conv2_h reads
+// (only the CUDA-core cross-check path needs it: k_conv1_tc writes the planes itself)
+__global__ void k_split_a1(const float4* __restrict__ a1, uint4* __restrict__ a1h, float a_scale, size_t n_pix /* images x 784 */) {
+  const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (t >= n_pix * 3) return;
+  const size_t img = t / (3 * TC_PIX);
+  const int pl = (int)((t / TC_PIX) % 3), pos = (int)(t % TC_PIX);
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 qa = a1[(img * 5 + 2 * pl) * TC_PIX + pos];
+  const float4 qb = 2 * pl + 1 < 5 ? a1[(img * 5 + 2 * pl + 1) * TC_PIX + pos] : z;
+  const float x[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+  uint32_t hw[4], lw[4];
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    uint16_t h0, l0, h1, l1;
+    tc::split_f16(x[2 * e] * a_scale, h0, l0);
+    tc::split_f16(x[2 * e + 1] * a_scale, h1, l1);
+    hw[e] = (uint32_t)h0 | ((uint32_t)h1 << 16);
+    lw[e] = (uint32_t)l0 | ((uint32_t)l1 << 16);
+  }
+  a1h[(img * H_IMG_PLANES + pl) * TC_PIX + pos] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+  a1h[(img * H_IMG_PLANES + 3 + pl) * TC_PIX + pos] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -451,7 +563,7 @@ k_conv2_tc(const float4* __restrict__ in /* [n][5][784] float4, see k_conv1_pool
 //   D[out][image] (4 M tiles of 128 x N = 128, the whole 512-column tensor memory)
 // A = the weights, B = the pooled conv2 activations, both already split into tf32 hi / lo
 // terms and stored in the canonical no-swizzle K-major tiles (weights by lenet_upload,
-// activations by k_conv2_tc's epilogue), so one K step is two plain bulk copies (32 KB + 8 KB)
+// activations by k_conv2_h's epilogue), so one K step is two plain bulk copies (32 KB + 8 KB)
 // and 12 MMAs (4 M tiles x the three-term split); no thread touches the operands.  A 5-stage
 // ring keeps 4 steps of copies in flight.  Partials go to part[z][image][500] and are summed
 // in a fixed order by k_ip2 (deterministic).
@@ -463,7 +575,7 @@ constexpr int I1_STAGES = 5;
 constexpr int I1_SMEM_BYTES = I1_STAGES * I1_STAGE_BYTES + 128;
 
 __global__ void __launch_bounds__(256, 1)
-k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_tc */, const float* __restrict__ wtc /* [936][8192] */,
+k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_h */, const float* __restrict__ wtc /* [936][8192] */,
          float* __restrict__ part, int n, int steps) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(tc_smem + I1_STAGES * I1_STAGE_BYTES);
@@ -508,7 +620,7 @@ k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_tc */, const float*
       const uint32_t sa = (s_base + slot * I1_STAGE_BYTES) >> 4, sb = sa + (I1_A_BYTES >> 4);
       if (leader) {
 #pragma unroll
-        for (int combo = 1; combo < 4; combo++) {  // cross terms first, main term last (see k_conv2_tc)
+        for (int combo = 1; combo < 4; combo++) {  // cross terms first, main term last (see k_conv2_h)
           const int pa = combo == 1, pb = combo == 2;
           const uint64_t b_desc = b_hi64 | (uint64_t)(sb + pb * 128);
 #pragma unroll
@@ -649,23 +761,48 @@ int lenet_upload(ag2_ctx* c) {
     AG2_CUDA(c, cudaMemcpyAsync(bufs[i]->p, L.host[i].data(), sizes[i] * sizeof(float), cudaMemcpyHostToDevice,
                                 c->stream));
   }
-  // conv2 weights for k_conv2_tc: per tap [hi/lo][k step s][chunk][64 out channels][4 in channels],
-  // in channel = 8s + 4*chunk + e; rows >= 50 and channels >= 20 are zero
-  std::vector<float> wtc((size_t)25 * TC_BTAP_FLOATS, 0.f);
-  for (int t = 0; t < 25; t++)
-    for (int s = 0; s < 3; s++)
+  // conv2 weights for k_conv2_h.  Scales: the pooled conv1 activations are bounded by 255 * sum|w| + |b| per output
+  // channel (u8 inputs); a power of two brings that bound, and the largest conv2 weight, to at most 2^15.
+  {
+    double bound = 1e-30, wmax = 1e-30;
+    for (int oc = 0; oc < C1_OUT; oc++) {
+      double sa = fabs((double)L.host[1][oc]);
+      for (int k = 0; k < 75; k++) sa += 255.0 * fabs((double)L.host[0][(size_t)oc * 75 + k]);
+      bound = std::max(bound, sa);
+    }
+    for (float w : L.host[2]) wmax = std::max(wmax, fabs((double)w));
+    if (!std::isfinite(bound) || !std::isfinite(wmax)) return AG2_E_INVALID;
+    auto pow2_to = [](double x) { return std::min(40, std::max(-40, (int)floor(log2(32768.0 / x)))); };
+    const int ea = pow2_to(bound), ew = pow2_to(wmax);
+    L.a1_scale = ldexpf(1.f, ea);
+    L.c2_inv_scale = ldexpf(1.f, -(ea + ew));
+    const float w_scale = ldexpf(1.f, ew);
+    std::vector<uint16_t> wh((size_t)H_ITEMS * H_ITEM_BYTES / 2, 0);
+    for (int k = 0; k < H_KSTEPS; k++)
       for (int ck = 0; ck < 2; ck++)
-        for (int n = 0; n < C2_OUT; n++)
-          for (int e = 0; e < 4; e++) {
-            const int ch = 8 * s + 4 * ck + e;
-            if (ch >= 20) continue;
-            float hi, lo;
-            tc::split_tf32(L.host[2][((size_t)n * 20 + ch) * 25 + t], hi, lo);
-            wtc[(size_t)t * TC_BTAP_FLOATS + (((0 * 3 + s) * 2 + ck) * 64 + n) * 4 + e] = hi;
-            wtc[(size_t)t * TC_BTAP_FLOATS + (((1 * 3 + s) * 2 + ck) * 64 + n) * 4 + e] = lo;
+        for (int e = 0; e < 8; e++) {
+          int tap, ch;
+          if (k < 25) {
+            tap = k, ch = 8 * ck + e;
+          } else {
+            const int j = k - 25;
+            tap = (j < 12 ? 2 * j : 23) + ck, ch = 16 + e;
+            if (j == 12 && ck == 0) continue;  // tap 23 belongs to step 36; here it only fills the pair
           }
-  AG2_CUDA(c, L.c2w_tc.reserve(wtc.size()));
-  AG2_CUDA(c, cudaMemcpyAsync(L.c2w_tc.p, wtc.data(), wtc.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+          if (ch >= 20) continue;
+          const int item = k / H_ITEM_STEPS, s = k % H_ITEM_STEPS;
+          for (int n = 0; n < C2_OUT; n++) {
+            uint16_t hi, lo;
+            tc::split_f16(L.host[2][((size_t)n * 20 + ch) * 25 + tap] * w_scale, hi, lo);
+            const size_t at = (size_t)item * (H_ITEM_BYTES / 2) + ((size_t)(s * 2 + ck) * 64 + n) * 8 + e;
+            wh[at] = hi;
+            wh[at + H_ITEM_BYTES / 4] = lo;
+          }
+        }
+    AG2_CUDA(c, L.c2w_h.reserve(wh.size()));
+    AG2_CUDA(c, cudaMemcpyAsync(L.c2w_h.p, wh.data(), wh.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
+    AG2_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   // conv1 weights for k_conv1_tc: [k step s][hi, lo][chunk = tap 2s, 2s+1][32 out channels][c0, c1, c2, 0]
   {
     std::vector<float> w0((size_t)C1_B_FLOATS, 0.f);
@@ -712,6 +849,15 @@ int lenet_upload(ag2_ctx* c) {
   return AG2_OK;
 }
 
+// dynamic shared-memory limits of the tensor-core kernels (per device; cheap enough to repeat per call)
+static int lenet_attributes(ag2_ctx* c) {
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_h<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, H_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_h<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, H_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
+  AG2_CUDA(c, cudaFuncSetAttribute(k_conv1_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM_BYTES));
+  return AG2_OK;
+}
+
 int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits) {
   if (!c->net.loaded) return AG2_E_NO_WEIGHTS;
   if (n == 0) return AG2_OK;
@@ -747,32 +893,35 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
     steps_per_split = I1_KSTEPS / splits;
     a2_floats = (size_t)itiles * I1_CHUNKS * 1024;
   }
-  AG2_CUDA(c, c->act.reserve(chunk * 20 * P1 * P1 + a2_floats + (size_t)splits * chunk * IP1_OUT));
+  const size_t a1_floats = chunk * (simt ? (size_t)(20 * P1 * P1 + (simt == 2 ? H_IMG_BYTES / 4 : 0)) : (size_t)(H_IMG_BYTES / 4));
+  AG2_CUDA(c, c->act.reserve(a1_floats + a2_floats + (size_t)splits * chunk * IP1_OUT));
   const size_t smem2 = (size_t)(20 * 28 * 29 + 10 * 500) * sizeof(float);
-  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_pool, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
-  AG2_CUDA(c, cudaFuncSetAttribute(k_conv1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM_BYTES));
+  AG2_TRY(lenet_attributes(c));
+  if (simt) AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_pool, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
   for (size_t off = 0; off < n; off += chunk_max) {
     const size_t m = std::min(chunk_max, n - off);
     float* a1 = c->act.p;
-    float* a2 = a1 + chunk * 20 * P1 * P1;
+    float* a2 = a1 + a1_floats;
     float* part = a2 + a2_floats;
-    const float4* a1q = reinterpret_cast<const float4*>(a1);
+    uint4* a1h = reinterpret_cast<uint4*>(simt == 2 ? a1 + chunk * 20 * P1 * P1 : a1);
+    const unsigned g2 = (unsigned)std::min<size_t>(m, (size_t)c->sm_count);
     if (simt)
       k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
                                                 reinterpret_cast<float4*>(a1));
     else
-      k_conv1_tc<<<(unsigned)m, 256, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
-                                                          reinterpret_cast<float4*>(a1));
+      k_conv1_tc<true><<<(unsigned)m, 256, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
+                                                                reinterpret_cast<float4*>(a1), L.a1_scale);
     AG2_LAUNCH_CHECK(c);
-    if (simt == 1)
+    if (simt == 1) {
       k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
-    else if (simt)
-      k_conv2_tc<false><<<(unsigned)m, 256, TC_SMEM_BYTES, st>>>(a1q, L.c2w_tc.p, L.c2b.p, a2);
-    else
-      k_conv2_tc<true><<<(unsigned)m, 256, TC_SMEM_BYTES, st>>>(a1q, L.c2w_tc.p, L.c2b.p, a2);
+    } else if (simt) {
+      k_split_a1<<<(unsigned)((m * 3 * TC_PIX + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(a1), a1h, L.a1_scale,
+                                                                          m * TC_PIX);
+      AG2_LAUNCH_CHECK(c);
+      k_conv2_h<false><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, a2, (int)m);
+    } else {
+      k_conv2_h<true><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, a2, (int)m);
+    }
     AG2_LAUNCH_CHECK(c);
     if (simt) {
       dim3 g1((unsigned)((m + 63) / 64), (IP1_OUT + 63) / 64, splits);
@@ -805,11 +954,11 @@ int classify_compute(ag2_ctx* c) {
 // planes, tiled conv2 output, split-K partials of ip1) live in ONE file-scope device array of fixed
 // size instead of the ctx's growing buffer; images and logits are the caller's device buffers.
 // The kernels, their launch shapes and the split-K choice are those of lenet_forward, so the logits
-// are the same bits.  Every GPU that loads libag2.so holds the array (about 26.7 MB) until exit.
+// are the same bits.  Every GPU that loads libag2.so holds the array (about 27.5 MB) until exit.
 // ---------------------------------------------------------------------------------------------
 }  // namespace ag2
 
-#define AG2_STATIC_A1_FLOATS ((size_t)AG2_CLASSIFY_STATIC_MAX_IMAGES * 20 * 28 * 28) /* pooled conv1 planes */
+#define AG2_STATIC_A1_FLOATS ((size_t)AG2_CLASSIFY_STATIC_MAX_IMAGES * 6 * 784 * 4) /* pooled conv1 planes, fp16 hi + lo */
 #define AG2_STATIC_A2_FLOATS ((size_t)2 * 936 * 1024)                                /* one tile of 128 images, tiled for ip1 */
 #define AG2_STATIC_PART_FLOATS ((size_t)117 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)  /* at most 117 K splits */
 #define AG2_STATIC_FLOATS (AG2_STATIC_A1_FLOATS + AG2_STATIC_A2_FLOATS + AG2_STATIC_PART_FLOATS)
@@ -838,9 +987,7 @@ int static_scratch_setup(ag2_ctx* c, float** out) {
       c->err = "ag2_classify_images_static: the scratch array did not resolve to memory of the ctx's device";
       return AG2_E_CUDA;
     }
-    AG2_CUDA(c, cudaFuncSetAttribute(k_conv2_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-    AG2_CUDA(c, cudaFuncSetAttribute(k_ip1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, I1_SMEM_BYTES));
-    AG2_CUDA(c, cudaFuncSetAttribute(k_conv1_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, C1_SMEM_BYTES));
+    AG2_TRY(lenet_attributes(c));
     g_static_ptr[c->device] = p;
     g_static_ready[c->device] = true;
   }
@@ -882,12 +1029,13 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
   float* a2 = a1 + AG2_STATIC_A1_FLOATS;
   float* part = a2 + AG2_STATIC_A2_FLOATS;
   // Nothing has to start at zero: every word a valid image's logits depend on is written earlier in this call
-  // (k_conv2_tc writes the two zero channels of each chunk itself); rows of the image tile beyond n keep the last
+  // (k_conv2_h writes the two zero channels of each chunk itself); rows of the image tile beyond n keep the last
   // call's values and only feed accumulator columns that are never stored.
   const unsigned m = (unsigned)n;
-  k_conv1_tc<<<m, 256, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1));
+  k_conv1_tc<true><<<m, 256, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1), L.a1_scale);
   AG2_LAUNCH_CHECK(c);
-  k_conv2_tc<true><<<m, 256, TC_SMEM_BYTES, st>>>(reinterpret_cast<const float4*>(a1), L.c2w_tc.p, L.c2b.p, a2);
+  k_conv2_h<true><<<std::min(m, (unsigned)c->sm_count), 192, H_SMEM_BYTES, st>>>(reinterpret_cast<const uint4*>(a1), L.c2w_h.p, L.c2b.p,
+                                                                               L.c2_inv_scale, a2, (int)m);
   AG2_LAUNCH_CHECK(c);
   k_ip1_tc<<<dim3(1, splits), 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
   AG2_LAUNCH_CHECK(c);

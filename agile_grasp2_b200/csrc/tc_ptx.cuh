@@ -10,6 +10,7 @@
 #ifndef AG2_TC_PTX_CUH_
 #define AG2_TC_PTX_CUH_
 
+#include <cuda_fp16.h>
 #include <stdint.h>
 
 namespace ag2 {
@@ -57,6 +58,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 // ---- 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier ------------
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -97,6 +102,11 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int m, int n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
+// instruction descriptor: D fp32, A and B fp16 (kind::f16, K = 16 per instruction = 2 chunks of 8 values), K-major
+__host__ __device__ constexpr uint32_t idesc_f16(int m, int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
 // ---- MMA ------------------------------------------------------------------------------------
 // D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
 __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
@@ -105,6 +115,15 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                        uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
@@ -148,6 +167,23 @@ __host__ __device__ __forceinline__ void split_tf32(float x, float& hi, float& l
   b.f = x - hi;
   b.u &= 0xFFFFE000u;
   lo = b.f;
+#endif
+}
+
+// fp16 split of x (already scaled into fp16's range): hi = the nearest fp16, lo = the nearest fp16 of the exact
+// residual; hi + lo carries 22 significant bits while the residual is above fp16's subnormal spacing (2^-24).
+// Returned as raw bit patterns (the same code runs on the host at upload and on the device).
+__host__ __device__ __forceinline__ void split_f16(float x, uint16_t& hi, uint16_t& lo) {
+#ifdef __CUDA_ARCH__
+  const __half h = __float2half_rn(x);
+  const __half l = __float2half_rn(x - __half2float(h));
+  hi = __half_as_ushort(h);
+  lo = __half_as_ushort(l);
+#else
+  const __half h = __float2half_rn(x);
+  const __half l = __float2half_rn(x - __half2float(h));
+  hi = static_cast<__half_raw>(h).x;
+  lo = static_cast<__half_raw>(l).x;
 #endif
 }
 
