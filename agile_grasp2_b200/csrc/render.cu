@@ -41,6 +41,7 @@ struct RenderArgs {
   uint32_t cap;                // capacity (multiple of 8) >= largest m of this launch
   uint32_t m_lo, m_hi;         // size class of this launch: images with m outside [m_lo, m_hi] are skipped
   uint32_t n;                  // images
+  uint32_t* claim;             // nullptr: CTA b takes images b, b + grid, ...; else CTAs claim images from this counter
   uint8_t* scratch;            // nullptr: sort arrays in shared memory; else gridDim.x regions of cap*16 bytes
                                // in global memory (closing regions too large for shared memory)
   uint8_t* out;                // n * 10800
@@ -101,8 +102,18 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
   __shared__ uint32_t warp_tot[kRenderThreads / 32];
   __shared__ long long miny_s;
   __shared__ double FR[3][3];
+  __shared__ uint32_t claim_s;
   const int tid = threadIdx.x;
-  for (uint32_t image = blockIdx.x; image < A.n; image += gridDim.x) {
+  // next image of this CTA: a fixed stride, or (second size class: few images, very different sizes) the next
+  // unclaimed one, so that no CTA is left with several of the large closing regions
+  auto next_image = [&](uint32_t cur) -> uint32_t {
+    if (!A.claim) return cur + gridDim.x;
+    __syncthreads();
+    if (tid == 0) claim_s = atomicAdd(A.claim, 1u);
+    __syncthreads();
+    return claim_s;
+  };
+  for (uint32_t image = A.claim ? next_image(0) : blockIdx.x; image < A.n; image = next_image(image)) {
   const uint32_t slot = EXPLICIT ? 0u : A.list[image];
   const ag2_hypothesis& hyp = A.slots[slot];
   BoxRef br;
@@ -312,7 +323,7 @@ static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) 
   if (const char* e = getenv("AG2_RENDER_SMALL_CAP")) small_cap = (std::max(atoi(e), 8) + 7) & ~7;
   A.g = grid_dev(c);
   A.n = (uint32_t)n;
-  auto launch = [&](uint32_t cap, uint32_t m_lo, uint32_t m_hi, bool one_cta_per_image) -> int {
+  auto launch = [&](cudaStream_t st, uint32_t cap, uint32_t m_lo, uint32_t m_hi, bool one_cta_per_image) -> int {
     auto kernel = k_render<EXPLICIT>;
     // Closing regions of more than ~12 000 points (fused multi-view clouds, c4) do not fit shared
     // memory: the sort arrays then live in global memory (L2 resident).
@@ -324,17 +335,29 @@ static int launch_render(ag2_ctx* c, RenderArgs A, size_t n, size_t max_points) 
     AG2_CUDA(c, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     A.cap = cap, A.m_lo = m_lo, A.m_hi = m_hi;
     A.scratch = spill ? c->render_scratch.p : nullptr;
-    kernel<<<grid, kRenderThreads, smem, c->stream>>>(A, c->hc);
+    A.claim = nullptr;
+    if (!one_cta_per_image) {
+      A.claim = c->scalars.p + 62;
+      AG2_CUDA(c, cudaMemsetAsync(A.claim, 0, 4, st));
+    }
+    kernel<<<grid, kRenderThreads, smem, st>>>(A, c->hc);
     AG2_LAUNCH_CHECK(c);
     return AG2_OK;
   };
   // Shared memory per CTA is sized by the LARGEST image of a launch, so one dense closing region
-  // would cost every image its occupancy: images up to kSmallCap points go first (one CTA each,
-  // two CTAs = 32 warps per SM), the larger ones in a second launch whose CTAs walk the list and skip
-  // the rest.  Boundary measured on c3: 2048 -> 1.41 ms, 3072 -> 1.28, 4096 -> 1.06, 5400 -> 1.07.
-  if (cap_max <= small_cap) return launch(cap_max, 0u, 0xFFFFFFFFu, true);
-  AG2_TRY(launch(small_cap, 0u, small_cap, true));
-  return launch(cap_max, small_cap + 1u, 0xFFFFFFFFu, false);
+  // would cost every image its occupancy: images up to kSmallCap points run one CTA each (two CTAs =
+  // 32 warps per SM), the larger ones in a second launch whose CTAs claim images from a counter and
+  // skip the rest.  Boundary measured on c3: 2048 -> 1.41 ms, 3072 -> 1.28, 4096 -> 1.06, 5400 -> 1.07.
+  // The second class is few, long images: it starts first, on an auxiliary stream, and the first
+  // class fills the shared memory and issue slots it leaves free.
+  if (cap_max <= small_cap) return launch(c->stream, cap_max, 0u, 0xFFFFFFFFu, true);
+  AG2_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+  AG2_CUDA(c, cudaStreamWaitEvent(c->aux[0], c->ev_fork, 0));
+  AG2_TRY(launch(c->aux[0], cap_max, small_cap + 1u, 0xFFFFFFFFu, false));
+  AG2_CUDA(c, cudaEventRecord(c->ev_join[0], c->aux[0]));
+  AG2_TRY(launch(c->stream, small_cap, 0u, small_cap, true));
+  AG2_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join[0], 0));
+  return AG2_OK;
 }
 
 // Renders the hypotheses in slots d_list[0..n) into d_out (n * 10800 bytes).
