@@ -159,13 +159,16 @@ constexpr int TC_PIX = P1 * P1;  // 784 pixels per plane
 // conv1 (3->20, 5x5) + bias + maxpool 2x2 on the tensor cores: the same zero-copy implicit GEMM as
 // conv2 (below), on the 60 x 60 input image.  The u8 image is expanded in shared memory to one
 // 16-byte K chunk per pixel, (c0, c1, c2, 0) as fp32 - exact in tf32, so only the weights are
-// split (2 MMAs per K step: w_lo first, then w_hi).  Image rows are 60 pixels = 960 bytes (SBO)
-// apart; an M = 128 tile is 8 (x) by 16 (y) of the 56 x 56 outputs; tap (ky, kx) moves the start
-// address by ky*60 + kx pixels.  One K step of 8 = TWO taps: the second chunk is simply the same
-// tile one tap further, i.e. LBO = 16 bytes inside a kernel row and (60-4)*16 bytes across rows;
-// 25 taps = 13 steps (the 26th tap has zero weights).  N = 32 columns (20 channels).  Four passes
-// of 7 tiles (y0 = 0, 16, 32, 40; 224 of 256 allocated tensor-memory columns), so two CTAs fit an
-// SM and one CTA's epilogue overlaps the other's MMAs.  728 MMAs per image.
+// split, and both weight terms ride in ONE MMA as extra columns: B has N = 48 rows, w_hi of the 20
+// channels in rows 0..19 and w_lo in rows 24..43, so a tile's accumulator holds the two partial
+// products side by side (each rounded against its own small accumulator) and the epilogue adds
+// them.  Image rows are 60 pixels = 960 bytes (SBO) apart; an M = 128 tile is 8 (x) by 16 (y) of
+// the 56 x 56 outputs; tap (ky, kx) moves the start address by ky*60 + kx pixels.  One K step of
+// 8 = TWO taps: the second chunk is simply the same tile one tap further, i.e. LBO = 16 bytes
+// inside a kernel row and (60-4)*16 bytes across rows; 25 taps = 13 steps (the 26th tap has zero
+// weights).  28 tiles (7 in x by y0 = 0, 16, 32, 40) in six passes of five (240 of 256 allocated
+// tensor-memory columns), so two CTAs fit an SM and one CTA's epilogue overlaps the other's MMAs.
+// 364 MMAs per image.
 // ---------------------------------------------------------------------------------------------
 // fp16 operand planes shared by k_conv1_tc's epilogue (writer) and k_conv2_h (reader): per image
 // [hi, lo][plane p = channels 8p .. 8p+7][784 pixels][8 halfs]
@@ -182,13 +185,16 @@ constexpr int H_SMEM_BYTES = 2 * H_IMG_BYTES + H_SLOTS * H_ITEM_BYTES + 256;  //
 
 constexpr int C1_PIX = 60 * 60 + 4;                       // one pixel past the end is read by the zero-weight tap
 constexpr int C1_A_BYTES = C1_PIX * 16;                   // 57664
-constexpr int C1_B_FLOATS = 13 * 2 * 2 * 32 * 4;          // [k step][lo/hi... see lenet_upload] = 6656
-constexpr int C1_B_BYTES = C1_B_FLOATS * 4;               // 26624
+constexpr int C1_N = 48;                                  // B rows: 0..19 w_hi, 24..43 w_lo of the 20 channels
+constexpr int C1_B_FLOATS = 13 * 2 * C1_N * 4;            // [k step][chunk][48 rows][4] = 4992
+constexpr int C1_B_BYTES = C1_B_FLOATS * 4;               // 19968
+constexpr int kC1Threads = 384;                           // three epilogue warps per tensor-memory lane quarter
+constexpr int C1_TILES = 28, C1_PASS_TILES = 5;           // 7 (x) by 4 (y0 = 0, 16, 32, 40) tiles, 5 x 48 columns per pass
 constexpr int C1_SMEM_BYTES = C1_A_BYTES + C1_B_BYTES + 64;
 
 template <bool HALF_OUT>
-__global__ void __launch_bounds__(256, 2)
-k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* [13][hi, lo][2 chunks][32][4] */,
+__global__ void __launch_bounds__(kC1Threads, 2)
+k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* [13][2 chunks][48][4] */,
            const float* __restrict__ bias, float4* __restrict__ out /* [n][5][784] float4, or the fp16 planes of k_conv2_h */,
            float a_scale /* HALF_OUT: power of two that brings the activations into fp16's range */) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
@@ -212,7 +218,7 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
   }
   // expand the image: 4 pixels = 12 bytes = 3 aligned words per step (cv::split + convertTo(CV_32F) are exact)
   const uint32_t* src = reinterpret_cast<const uint32_t*>(images + (size_t)blockIdx.x * AG2_IMAGE_BYTES);
-  for (int g4 = tid; g4 < 900; g4 += 256) {
+  for (int g4 = tid; g4 < 900; g4 += kC1Threads) {
     const uint32_t w0 = __ldg(&src[3 * g4]), w1 = __ldg(&src[3 * g4 + 1]), w2 = __ldg(&src[3 * g4 + 2]);
     A[4 * g4 + 0] = make_float4((float)(w0 & 255u), (float)((w0 >> 8) & 255u), (float)((w0 >> 16) & 255u), 0.f);
     A[4 * g4 + 1] = make_float4((float)(w0 >> 24), (float)(w1 & 255u), (float)((w1 >> 8) & 255u), 0.f);
@@ -228,31 +234,35 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
   const int wq = warp & 3;
   float4* o = out + (size_t)blockIdx.x * 5 * (P1 * P1);
 
-  for (int pass = 0; pass < 4; pass++) {
-    const int y0 = pass < 3 ? 16 * pass : 40;
+  constexpr int kPasses = (C1_TILES + C1_PASS_TILES - 1) / C1_PASS_TILES;
+  for (int pass = 0; pass < kPasses; pass++) {
+    const int t_first = pass * C1_PASS_TILES, ntiles = min(C1_PASS_TILES, C1_TILES - t_first);
     if (warp == 0) {
       const bool leader = tc::elect_one();
       if (pass == 0) tc::mbar_wait(wbar, 0);
       tc::fence_after_sync();
       if (leader) {
-        const uint32_t idesc = tc::idesc_tf32(128, 32);
+        const uint32_t idesc = tc::idesc_tf32(128, C1_N);
         const uint32_t a_base = tc::smem_u32(A) >> 4, b_base = tc::smem_u32(B) >> 4;
-        const uint64_t b_hi64 = tc::smem_desc(0, 512, 128);
-#pragma unroll 1
-        for (int prec = 1; prec >= 0; prec--) {  // w_lo (small terms) first, w_hi last: see k_conv2_h
-#pragma unroll 1
-          for (int s = 0; s < 13; s++) {
-            const int t0 = 2 * s;  // taps t0 and t0 + 1
-            const uint32_t off = (uint32_t)((t0 / 5) * 60 + t0 % 5);
-            // second chunk = the next tap of the kernel, in 16-byte units (the 26th tap, zero weights, stays inside the image)
-            const uint32_t lbo = (t0 % 5 == 4 && s < 12) ? (60 - 4) : 1;
-            const uint64_t a_desc0 = ((uint64_t)(960 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)lbo << 16) |
-                                     (uint64_t)(a_base + (uint32_t)(y0 * 60) + off);
-            const uint64_t b_desc = b_hi64 | (uint64_t)(b_base + ((s * 2 + prec) * 2) * 32);
-            const uint32_t acc = !(prec == 1 && s == 0);
+        const uint64_t a_hi64 = ((uint64_t)(960 >> 4) << 32) | ((uint64_t)1 << 46);
+        const uint64_t b_desc0 = tc::smem_desc(0, C1_N * 16, 128) | (uint64_t)b_base;
+        uint32_t tile_a[C1_PASS_TILES];  // start of each tile of this pass, in pixels
 #pragma unroll
-            for (int tile = 0; tile < 7; tile++) tc::mma_tf32(tmem + tile * 32, a_desc0 + (uint64_t)(tile * 8), b_desc, idesc, acc);
-          }
+        for (int ti = 0; ti < C1_PASS_TILES; ti++) {
+          const int t = min(t_first + ti, C1_TILES - 1), yb = t / 7, xt = t % 7;
+          tile_a[ti] = a_base + (uint32_t)((yb < 3 ? 16 * yb : 40) * 60 + xt * 8);
+        }
+#pragma unroll 1
+        for (int s = 0; s < 13; s++) {
+          const int t0 = 2 * s;  // taps t0 and t0 + 1
+          const uint32_t off = (uint32_t)((t0 / 5) * 60 + t0 % 5);
+          // second chunk = the next tap of the kernel, in 16-byte units (the 26th tap, zero weights, stays inside the image)
+          const uint32_t lbo = (t0 % 5 == 4 && s < 12) ? (60 - 4) : 1;
+          const uint64_t a_desc = a_hi64 | ((uint64_t)lbo << 16);
+          const uint64_t b_desc = b_desc0 + (uint64_t)(s * 2 * C1_N);
+#pragma unroll
+          for (int ti = 0; ti < C1_PASS_TILES; ti++)
+            if (ti < ntiles) tc::mma_tf32(tmem + ti * C1_N, a_desc | (uint64_t)(tile_a[ti] + off), b_desc, idesc, s != 0);
         }
         tc::mma_commit(done);
       }
@@ -261,12 +271,19 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
     tc::mbar_wait(done, pass & 1);
     tc::fence_after_sync();
     // epilogue: lane = 8 x positions of image row y0 + 4*wq + lane/8; pool partners are lanes ^1 and ^8
-    if (!(pass == 3 && wq < 2)) {  // rows 40..47 of the last pass repeat the previous one
-      for (int tile = warp >> 2; tile < 7; tile += 2) {
-        float v[32];
-        tc::tmem_ld32(tmem + ((uint32_t)(wq * 32) << 16) + tile * 32, v);
+    for (int ti = warp >> 2; ti < ntiles; ti += kC1Threads / 128) {
+      const int t = t_first + ti, yb = t / 7, xt = t % 7;
+      if (yb == 3 && wq < 2) continue;  // rows 40..47 of the y0 = 40 tiles repeat the y0 = 32 ones
+      const int y0 = yb < 3 ? 16 * yb : 40;
+      {
+        float v[C1_N];
+        const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + ti * C1_N;
+        tc::tmem_ld32(taddr, v);
+        tc::tmem_ld16(taddr + 32, v + 32);
         tc::tmem_ld_wait();
-        const int py = (y0 + wq * 4 + (lane >> 3)) >> 1, px = (tile * 8 + (lane & 7)) >> 1;
+#pragma unroll
+        for (int ch = 0; ch < C1_OUT; ch++) v[ch] += v[24 + ch];  // a * w_hi + a * w_lo
+        const int py = (y0 + wq * 4 + (lane >> 3)) >> 1, px = (xt * 8 + (lane & 7)) >> 1;
         const int q = (lane & 1) | ((lane >> 2) & 2);
 #pragma unroll
         for (int ch = 0; ch < C1_OUT; ch++) {
@@ -803,7 +820,7 @@ int lenet_upload(ag2_ctx* c) {
     AG2_CUDA(c, cudaMemcpyAsync(L.c2w_h.p, wh.data(), wh.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
     AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   }
-  // conv1 weights for k_conv1_tc: [k step s][hi, lo][chunk = tap 2s, 2s+1][32 out channels][c0, c1, c2, 0]
+  // conv1 weights for k_conv1_tc: [k step s][chunk = tap 2s, 2s+1][48 rows: w_hi of channel n in row n, w_lo in row 24 + n][c0, c1, c2, 0]
   {
     std::vector<float> w0((size_t)C1_B_FLOATS, 0.f);
     for (int s2 = 0; s2 < 13; s2++)
@@ -814,8 +831,8 @@ int lenet_upload(ag2_ctx* c) {
           for (int ic = 0; ic < 3; ic++) {
             float hi, lo;
             tc::split_tf32(L.host[0][((size_t)n * 3 + ic) * 25 + t], hi, lo);
-            w0[(((size_t)(s2 * 2 + 0) * 2 + ck) * 32 + n) * 4 + ic] = hi;
-            w0[(((size_t)(s2 * 2 + 1) * 2 + ck) * 32 + n) * 4 + ic] = lo;
+            w0[(((size_t)s2 * 2 + ck) * C1_N + n) * 4 + ic] = hi;
+            w0[(((size_t)s2 * 2 + ck) * C1_N + 24 + n) * 4 + ic] = lo;
           }
       }
     AG2_CUDA(c, L.c1w_tc.reserve(w0.size()));
@@ -909,7 +926,7 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
       k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
                                                 reinterpret_cast<float4*>(a1));
     else
-      k_conv1_tc<true><<<(unsigned)m, 256, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
+      k_conv1_tc<true><<<(unsigned)m, kC1Threads, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
                                                                 reinterpret_cast<float4*>(a1), L.a1_scale);
     AG2_LAUNCH_CHECK(c);
     if (simt == 1) {
@@ -1032,7 +1049,7 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
   // (k_conv2_h writes the two zero channels of each chunk itself); rows of the image tile beyond n keep the last
   // call's values and only feed accumulator columns that are never stored.
   const unsigned m = (unsigned)n;
-  k_conv1_tc<true><<<m, 256, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1), L.a1_scale);
+  k_conv1_tc<true><<<m, kC1Threads, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1), L.a1_scale);
   AG2_LAUNCH_CHECK(c);
   k_conv2_h<true><<<std::min(m, (unsigned)c->sm_count), 192, H_SMEM_BYTES, st>>>(reinterpret_cast<const uint4*>(a1), L.c2w_h.p, L.c2b.p,
                                                                                L.c2_inv_scale, a2, (int)m);
