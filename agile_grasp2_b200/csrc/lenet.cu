@@ -176,10 +176,10 @@ constexpr int H_PLANE_BYTES = TC_PIX * 16;               // 12544
 constexpr int H_IMG_PLANES = 6;
 constexpr int H_IMG_BYTES = H_IMG_PLANES * H_PLANE_BYTES;  // 75264
 constexpr int H_KSTEPS = 38;                             // 25 x (one tap, planes 0 + 1) + 13 x (two taps, plane 2)
-constexpr int H_STEP_BYTES = 2 * 64 * 16;                // [chunk][64 out channels][8 halfs] = 2048
+constexpr int H_STEP_BYTES = 2 * 128 * 16;               // [chunk][128 rows: 64 x w_hi, 64 x w_lo][8 halfs] = 4096
 constexpr int H_ITEM_STEPS = 4;
 constexpr int H_ITEMS = 10;                              // 9 x 4 + 2 K steps
-constexpr int H_ITEM_BYTES = 2 * H_ITEM_STEPS * H_STEP_BYTES;  // [hi: 4 steps][lo: 4 steps] = 16384
+constexpr int H_ITEM_BYTES = H_ITEM_STEPS * H_STEP_BYTES;  // 16384
 constexpr int H_SLOTS = 4;
 constexpr int H_SMEM_BYTES = 2 * H_IMG_BYTES + H_SLOTS * H_ITEM_BYTES + 256;  // 216320
 
@@ -332,7 +332,7 @@ constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
 //
 // Operands.  Activations and weights are scaled by powers of two into fp16's range (exact) and split
 // into hi + lo fp16 terms (tc::split_f16: 22 significant bits, as the tf32 split); the product is
-//   a*b ~= a_lo*b_hi + a_hi*b_lo (first, into a tiny accumulator) + a_hi*b_hi, fp32 in tensor memory,
+//   a*b ~= (a_lo*b_hi + a_hi*b_lo) + a_hi*b_hi, fp32 in tensor memory (two accumulators, see below),
 // and the epilogue multiplies by the inverse scale (a power of two).  k_conv1_tc writes the planes
 // (HALF_OUT), so staging an image is six bulk copies and no thread touches the A operand.
 // One 16-byte chunk = 8 channels of one pixel; the 20 input channels are planes 0, 1 and half of
@@ -341,12 +341,15 @@ constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
 // more: 38 K steps instead of 75, each the same 6 KB of shared-memory operand reads per MMA.
 //
 // Schedule.  grid = min(images, SMs); a CTA walks its images.  Warp 0 issues the MMAs, warp 1 the
-// bulk copies (weights through a 4-slot ring of 4-K-step items, streamed once per tile group and
-// pass; the next image's planes into the other A buffer), warps 2..5 run the epilogue, one per
-// tensor-memory lane quarter.  The six M tiles form two groups (y0 = 0 and y0 = 8, 192 columns each)
-// that are accumulated one after the other: while group 1 accumulates, group 0 is pooled and
-// stored, and group 1 drains under the next image's group 0.  Nothing but the first image's load
-// and the last group's epilogue is exposed.
+// bulk copies (weights through a 4-slot ring of 4-K-step items, streamed once per tile group; the
+// next image's planes into the other A buffer), warps 2..5 run the epilogue, one per tensor-memory
+// lane quarter.  Both weight terms ride in one B tile of N = 128 rows (w_hi in rows 0..63, w_lo in
+// rows 64..127): per K step and tile, a_hi * [b_hi | b_lo] fills columns 0..63 (main term) and
+// 64..127, and a_lo * b_hi (N = 64) adds into columns 64..127, so the small terms round against a
+// small accumulator and the epilogue adds the halves: two MMAs instead of three.  The six M tiles
+// form three groups (x0 = 0, 8, 16; two tiles of 128 columns each) that alternate between the
+// halves of tensor memory: while one group accumulates, the previous one is pooled and stored.
+// Nothing but the first image's load and the last group's epilogue is exposed.  456 MMAs per image.
 // ---------------------------------------------------------------------------------------------
 // K step k of k_conv2_h: start of its first chunk (in pixels = 16-byte units from the hi planes' base) and the
 // distance to its second chunk (the descriptor's LBO)
@@ -403,56 +406,48 @@ k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const
   if (warp == 0) {
     // ---- MMA issue ----
     const bool leader = tc::elect_one();
-    const uint32_t idesc = tc::idesc_f16(128, 64);
-    const uint64_t a_hi64 = tc::smem_desc(0, 0, P1 * 16), b_hi64 = tc::smem_desc(0, 1024, 128);
-    uint32_t ring_i = 0;
+    const uint32_t idesc128 = tc::idesc_f16(128, 128), idesc64 = tc::idesc_f16(128, 64);
+    const uint64_t a_hi64 = tc::smem_desc(0, 0, P1 * 16), b_hi64 = tc::smem_desc(0, 2048, 128);
+    uint32_t ring_i = 0, gi = 0;
     for (int it = 0, img = first; img < n; img += stride, it++) {
       const int buf = it & 1;
       tc::mbar_wait(&a_full[buf], (it >> 1) & 1);
       tc::fence_after_sync();
       const uint32_t a_base16 = tc::smem_u32(A + buf * H_IMG_BYTES) >> 4;
-      for (int g = 0; g < 2; g++) {
-        tc::mbar_wait(&t_empty[g], (it & 1) ^ 1);  // the previous image's group g has been read
+      for (int g = 0; g < 3; g++, gi++) {  // tile group g: x0 = 8g, y0 = 0 and 8
+        const int tb = gi & 1;
+        tc::mbar_wait(&t_empty[tb], ((gi >> 1) & 1) ^ 1);  // the group that used this half of tensor memory has been read
         tc::fence_after_sync();
-        const uint32_t a_g16 = a_base16 + (uint32_t)(g * 8 * P1);
-        for (int pass = 0; pass < 2; pass++) {  // 0: the two cross terms, 1: the main term
-          for (int item = 0; item < H_ITEMS; item++, ring_i++) {
-            const int slot = ring_i % H_SLOTS;
-            tc::mbar_wait(&full[slot], (ring_i / H_SLOTS) & 1);
-            tc::fence_after_sync();
-            if (leader) {
-              // lean issue path: the descriptors of a step differ from a per-step constant by small additions only
-              const uint64_t b_desc0 = b_hi64 | (uint64_t)(tc::smem_u32(Bring + slot * H_ITEM_BYTES) >> 4);
-              const int nsteps = item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS;
-              const uint32_t d0 = tmem + g * 192;
+        const uint32_t a_g16 = a_base16 + (uint32_t)(g * 8);
+        const uint32_t d0 = tmem + tb * 256;
+        for (int item = 0; item < H_ITEMS; item++, ring_i++) {
+          const int slot = ring_i % H_SLOTS;
+          tc::mbar_wait(&full[slot], (ring_i / H_SLOTS) & 1);
+          tc::fence_after_sync();
+          if (leader) {
+            // lean issue path: the descriptors of a step differ from a per-step constant by small additions only
+            const uint64_t b_desc0 = b_hi64 | (uint64_t)(tc::smem_u32(Bring + slot * H_ITEM_BYTES) >> 4);
+            const int nsteps = item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS;
 #pragma unroll
-              for (int s = 0; s < H_ITEM_STEPS; s++) {
-                if (s < nsteps) {
-                  const uint2 st = c_hsteps.v[item * H_ITEM_STEPS + s];
-                  const uint64_t a_desc = a_hi64 | ((uint64_t)st.y << 16) | (uint64_t)(a_g16 + st.x);
-                  const uint64_t b_desc = b_desc0 + (uint64_t)(s * (H_STEP_BYTES >> 4));
-                  if (pass == 0) {
-                    const uint32_t acc = (item | s) != 0;
-                    const uint64_t a_lo = a_desc + (uint64_t)(3 * TC_PIX), b_lo = b_desc + (uint64_t)((H_ITEM_BYTES / 2) >> 4);
-                    tc::mma_f16(d0, a_lo, b_desc, idesc, acc);  // a_lo * b_hi
-                    tc::mma_f16(d0 + 64, a_lo + 8, b_desc, idesc, acc);
-                    tc::mma_f16(d0 + 128, a_lo + 16, b_desc, idesc, acc);
-                    tc::mma_f16(d0, a_desc, b_lo, idesc, 1);  // a_hi * b_lo
-                    tc::mma_f16(d0 + 64, a_desc + 8, b_lo, idesc, 1);
-                    tc::mma_f16(d0 + 128, a_desc + 16, b_lo, idesc, 1);
-                  } else {
-                    tc::mma_f16(d0, a_desc, b_desc, idesc, 1);  // a_hi * b_hi
-                    tc::mma_f16(d0 + 64, a_desc + 8, b_desc, idesc, 1);
-                    tc::mma_f16(d0 + 128, a_desc + 16, b_desc, idesc, 1);
-                  }
-                }
+            for (int s = 0; s < H_ITEM_STEPS; s++) {
+              if (s < nsteps) {
+                const uint2 st = c_hsteps.v[item * H_ITEM_STEPS + s];
+                const uint64_t a_desc = a_hi64 | ((uint64_t)st.y << 16) | (uint64_t)(a_g16 + st.x);
+                const uint64_t a_lo = a_desc + (uint64_t)(3 * TC_PIX);
+                const uint64_t b_desc = b_desc0 + (uint64_t)(s * (H_STEP_BYTES >> 4));
+                const uint32_t acc = (item | s) != 0;
+                // a_hi * [b_hi | b_lo] -> columns 0..63 (main term) and 64..127; a_lo * b_hi -> columns 64..127 as well
+                tc::mma_f16(d0, a_desc, b_desc, idesc128, acc);
+                tc::mma_f16(d0 + 128, a_desc + (uint64_t)(8 * P1), b_desc, idesc128, acc);
+                tc::mma_f16(d0 + 64, a_lo, b_desc, idesc64, 1);
+                tc::mma_f16(d0 + 192, a_lo + (uint64_t)(8 * P1), b_desc, idesc64, 1);
               }
-              tc::mma_commit(&empty[slot]);
             }
-            __syncwarp();
+            tc::mma_commit(&empty[slot]);
           }
+          __syncwarp();
         }
-        if (leader) tc::mma_commit(&t_full[g]);
+        if (leader) tc::mma_commit(&t_full[tb]);
         __syncwarp();
       }
       if (leader) tc::mma_commit(&a_empty[buf]);
@@ -475,17 +470,14 @@ k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const
     uint32_t ring_i = 0;
     if (first < n) load_a(0, first);
     for (int it = 0, img = first; img < n; img += stride, it++) {
-      for (int q = 0; q < 4 * H_ITEMS; q++, ring_i++) {  // (group, pass, item)
-        const int pass = (q / H_ITEMS) & 1, item = q % H_ITEMS;
+      for (int q = 0; q < 3 * H_ITEMS; q++, ring_i++) {  // (group, item)
+        const int item = q % H_ITEMS;
         const int slot = ring_i % H_SLOTS;
         tc::mbar_wait(&empty[slot], ((ring_i / H_SLOTS) & 1) ^ 1);
         if (leader) {
-          const uint32_t half = (uint32_t)(item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS) * H_STEP_BYTES;
-          const uint8_t* src = reinterpret_cast<const uint8_t*>(wh) + (size_t)item * H_ITEM_BYTES;
-          uint8_t* dst = Bring + slot * H_ITEM_BYTES;
-          tc::mbar_expect_tx(&full[slot], pass ? half : 2 * half);
-          tc::bulk_g2s(dst, src, half, &full[slot]);
-          if (!pass) tc::bulk_g2s(dst + H_ITEM_BYTES / 2, src + H_ITEM_BYTES / 2, half, &full[slot]);
+          const uint32_t bytes = (uint32_t)(item < H_ITEMS - 1 ? H_ITEM_STEPS : H_KSTEPS - (H_ITEMS - 1) * H_ITEM_STEPS) * H_STEP_BYTES;
+          tc::mbar_expect_tx(&full[slot], bytes);
+          tc::bulk_g2s(Bring + slot * H_ITEM_BYTES, reinterpret_cast<const uint8_t*>(wh) + (size_t)item * H_ITEM_BYTES, bytes, &full[slot]);
         }
         __syncwarp();
         // by now the MMAs of the previous image have drained (this image's first item has): its A buffer is free
@@ -496,19 +488,32 @@ k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const
     // ---- epilogue: warp w reads tensor-memory lanes 32*(w%4)..+31 = image rows y0 + 4*(w%4)..+3, 8 x positions each;
     // the 2x2 pooling partners are lanes ^1 (x) and ^8 (y); lane q of a pooling quad stores every fourth chunk ----
     const int wq = warp & 3;
+    uint32_t gi = 0;
     for (int it = 0, img = first; img < n; img += stride, it++) {
-      for (int g = 0; g < 2; g++) {
-        tc::mbar_wait(&t_full[g], it & 1);
+      for (int g = 0; g < 3; g++, gi++) {
+        const int tb = gi & 1;
+        tc::mbar_wait(&t_full[tb], (gi >> 1) & 1);
         tc::fence_after_sync();
-        if (!(g == 1 && wq < 2)) {  // rows 8..15 were produced by group 0
 #pragma unroll 1
-          for (int xr = 0; xr < 3; xr++) {
+        for (int ty = 0; ty < 2; ty++) {
+          if (ty == 1 && wq < 2) continue;  // rows 8..15 were produced by the y0 = 0 tile
+          {
             float v[64];
-            const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (g * 3 + xr) * 64;
+            const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + tb * 256 + ty * 128;
             tc::tmem_ld32(taddr, v);
             tc::tmem_ld32(taddr + 32, v + 32);
-            tc::tmem_ld_wait();
-            const int py = (g * 8 + wq * 4 + (lane >> 3)) >> 1, px = (xr * 8 + (lane & 7)) >> 1;
+            {
+              float w[32];
+              tc::tmem_ld32(taddr + 64, w);
+              tc::tmem_ld_wait();
+#pragma unroll
+              for (int ch = 0; ch < 32; ch++) v[ch] += w[ch];  // main term + cross terms
+              tc::tmem_ld32(taddr + 96, w);
+              tc::tmem_ld_wait();
+#pragma unroll
+              for (int ch = 32; ch < C2_OUT; ch++) v[ch] += w[ch - 32];
+            }
+            const int py = (ty * 8 + wq * 4 + (lane >> 3)) >> 1, px = (g * 8 + (lane & 7)) >> 1;
             const int q = (lane & 1) | ((lane >> 2) & 2);
 #pragma unroll
             for (int ch = 0; ch < C2_OUT; ch++) {
@@ -541,7 +546,7 @@ k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const
         }
         tc::fence_before_sync();
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&t_empty[g]);
+        if (lane == 0) tc::mbar_arrive(&t_empty[tb]);
       }
     }
   }
@@ -811,9 +816,9 @@ int lenet_upload(ag2_ctx* c) {
           for (int n = 0; n < C2_OUT; n++) {
             uint16_t hi, lo;
             tc::split_f16(L.host[2][((size_t)n * 20 + ch) * 25 + tap] * w_scale, hi, lo);
-            const size_t at = (size_t)item * (H_ITEM_BYTES / 2) + ((size_t)(s * 2 + ck) * 64 + n) * 8 + e;
-            wh[at] = hi;
-            wh[at + H_ITEM_BYTES / 4] = lo;
+            const size_t at = (size_t)item * (H_ITEM_BYTES / 2) + ((size_t)(s * 2 + ck) * 128 + n) * 8 + e;
+            wh[at] = hi;           // rows 0..63: w_hi
+            wh[at + 64 * 8] = lo;  // rows 64..127: w_lo
           }
         }
     AG2_CUDA(c, L.c2w_h.reserve(wh.size()));
