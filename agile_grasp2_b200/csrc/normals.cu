@@ -736,32 +736,45 @@ __constant__ uint32_t c_tier_cap[kAllTiers] = {48,  64,  80,  96,   112,  128,  
 // tier_cnt layout: [0..15] tier sizes, [16..31] batch counters of the tier launches, [32] points over the last capacity
 constexpr int kTierCntWords = 48;
 
-// thread per point: neighbour count, NaN normal below three neighbours, tier membership lists
-// (one warp-aggregated atomic per tier present in the warp, so consecutive cell-sorted points stay
-// consecutive in their list and keep their cache locality).
+// FOUR lanes per point (they share out its cell rows; a rank's share of a cloud is too few points to hide a
+// thread-per-point walk's chain of dependent loads): neighbour count, NaN normal below three neighbours, tier
+// membership lists (one warp-aggregated atomic per tier present in the warp, so consecutive cell-sorted points
+// stay consecutive in their list and keep their cache locality).
+template <int LANES>  // lanes per point: 4, or 1 when the launch has points enough to fill the machine by itself
 __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float rq, uint32_t* __restrict__ kn,
                                                      uint32_t* __restrict__ max_out,
                                                      unsigned long long* __restrict__ sum_out,
                                                      uint32_t* __restrict__ tier_count, uint32_t* __restrict__ tier_list,
                                                      uint32_t stride, float4* __restrict__ nrm_out,
                                                      uint32_t shard_rank, uint32_t shard_world) {
-  // thread t of the launch = the t-th point this rank owns (whole warps of work at any world size)
-  const uint32_t i = shard_point(blockIdx.x * blockDim.x + threadIdx.x, shard_rank, shard_world);
-  const uint32_t lane = threadIdx.x & 31;
-  const bool owned = i < (uint32_t)g.n;
-  uint32_t cnt = 0;
-  if (owned) {
+  // group t of the launch = the t-th point this rank owns (whole warps of work at any world size)
+  const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = shard_point(LANES == 4 ? gtid >> 2 : gtid, shard_rank, shard_world);
+  const uint32_t lane = threadIdx.x & 31, sub = LANES == 4 ? lane & 3u : 0u;
+  const bool in_range = i < (uint32_t)g.n, owned = in_range && sub == 0;
+  uint32_t cnt = 0, cand = 0;
+  if (in_range) {
     const float4 q = g.pts[i];
     const QueryWindow w = make_window(g, q.x, q.y, q.z, rq);
     const int rows = w.rows();
-    for (int row = 0; row < rows; row++) {
+    for (int row = (int)sub; row < rows; row += LANES) {
       uint32_t b, e;
       row_span_trim(g, w, row, q.x, q.y, q.z, r2 * 1.002f, b, e);
+      cand += e - b;
       for (uint32_t j = b; j < e; j++) {
         const float4 p = g.pts[j];
         cnt += (dist2_f(q.x - p.x, q.y - p.y, q.z - p.z) < r2);
       }
     }
+  }
+  if (LANES == 4) {
+    cnt += __shfl_xor_sync(AG2_FULL, cnt, 1);
+    cnt += __shfl_xor_sync(AG2_FULL, cnt, 2);
+    cand += __shfl_xor_sync(AG2_FULL, cand, 1);
+    cand += __shfl_xor_sync(AG2_FULL, cand, 2);
+  }
+  if (!owned) cnt = 0;  // one lane per point reports
+  if (owned) {
     kn[i] = cnt;
     if (cnt < 3) {  // computePointNormal: fewer than 3 neighbours -> NaN
       const float nanv = __int_as_float(0x7fc00000);
@@ -783,7 +796,15 @@ __global__ void __launch_bounds__(128) k_count_tiers(GridDev g, float r2, float 
     if (cnt > c_tier_cap[kAllTiers - 1]) {
       atomicAdd(&tier_count[32], 1u);  // no launch can hold this neighbourhood: reported as AG2_E_CAPACITY
     } else {
+      // A tier fixes the capacity of its launch AND how many lanes walk a point's candidates (4, 32, 128).  A sparse
+      // point beside a dense region has few neighbours but thousands of candidates: on four lanes it would outlast
+      // its whole launch.  Such a point is filed by its walk (a sixth of the candidates, the usual hit rate being
+      // one in five) -- any tier at or above the point's own is a valid home, the normal does not depend on it.
+      // Tier 11 (one CTA per point) is as far as the walk alone moves a point: the launches above it are sized
+      // by the previous cloud's largest neighbourhood.
+      const uint32_t eff = max(cnt, cand / 6u);
       tier = 0;
+      while (tier < 11 && eff > c_tier_cap[tier]) tier++;
       while (cnt > c_tier_cap[tier]) tier++;
     }
   }
@@ -1206,10 +1227,19 @@ static int normals_moments_tiered(ag2_ctx* c) {
   AG2_CUDA(c, c->nrm_mom.reserve((size_t)kMomWords * std::max(n, 1u)));
   AG2_CUDA(c, cudaMemsetAsync(c->scalars.p + 8, 0, 16, st));  // [8] max, [10..11] sum
   AG2_CUDA(c, cudaMemsetAsync(c->tier_cnt.p, 0, kTierCntWords * 4, st));
-  k_count_tiers<<<std::max(1u, (((owned + 31) & ~31u) + 127) / 128), 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p, c->scalars.p + 8,
-                                                 (unsigned long long*)(c->scalars.p + 10), c->tier_cnt.p,
-                                                 c->tier_list.p, owned, c->nrm.p, (uint32_t)c->nrm_rank,
-                                                 (uint32_t)c->nrm_world);
+  {
+    const uint32_t owned32 = (owned + 31) & ~31u;
+    unsigned long long* sum = (unsigned long long*)(c->scalars.p + 10);
+    if (owned32 >= 200000u)
+      k_count_tiers<1><<<std::max(1u, (owned32 + 127) / 128), 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p,
+                                                                           c->scalars.p + 8, sum, c->tier_cnt.p, c->tier_list.p,
+                                                                           owned, c->nrm.p, (uint32_t)c->nrm_rank,
+                                                                           (uint32_t)c->nrm_world);
+    else
+      k_count_tiers<4><<<std::max(1u, owned32 / 32), 128, 0, st>>>(g, c->hc.r2_normals, c->hc.rq_normals, c->kn.p,
+                                                                  c->scalars.p + 8, sum, c->tier_cnt.p, c->tier_list.p, owned,
+                                                                  c->nrm.p, (uint32_t)c->nrm_rank, (uint32_t)c->nrm_world);
+  }
   AG2_LAUNCH_CHECK(c);
   // statistics and the capacity check travel to pinned memory behind the count pass; nobody waits for them here
   AG2_CUDA(c, cudaMemcpyAsync(c->h_pin, c->scalars.p + 8, 16, cudaMemcpyDeviceToHost, st));

@@ -120,7 +120,7 @@ __device__ __forceinline__ bool kv_greater(uint64_t ka, uint32_t va, uint64_t kb
 constexpr int kSortTile = 4096;  // (8 + 4) B * 4096 = 48 KB of shared memory
 
 // Sorts one tile of (key, pos) pairs in shared memory and writes its first `keep` pairs.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_sort_tile(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ pos_in, uint32_t n, uint32_t keep,
             uint64_t* __restrict__ keys_out, uint32_t* __restrict__ pos_out) {
   __shared__ uint64_t k_s[kSortTile];
@@ -533,7 +533,7 @@ int select_top(ag2_ctx* c) {
       for (;;) {
         const unsigned tiles = (unsigned)((m + kSortTile - 1) / kSortTile);
         const uint32_t keep = tiles == 1 ? (uint32_t)std::min(m, k) : (uint32_t)k;
-        k_sort_tile<<<tiles, 256, 0, st>>>(c->sort_keys[cur].p, pos_in, (uint32_t)m, keep, c->sort_keys[cur ^ 1].p,
+        k_sort_tile<<<tiles, 1024, 0, st>>>(c->sort_keys[cur].p, pos_in, (uint32_t)m, keep, c->sort_keys[cur ^ 1].p,
                                            c->sort_pos[cur ^ 1].p);
         AG2_LAUNCH_CHECK(c);
         cur ^= 1;
