@@ -190,8 +190,9 @@ struct ag2_ctx {
   ag2::DevBuf<uint32_t> tier_list;      // normals: points grouped by neighbourhood-size tier, [tier][owned points]
   ag2::DevBuf<uint32_t> tier_cnt;       // normals: per-tier counts + per-launch batch counters
   ag2::DevBuf<float> nrm_mom;           // normals: raw moment sums per point (12 floats), input of k_eigen
-  cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};  // independent normals launches run side by side
-  cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+  static constexpr int kAux = 12;
+  cudaStream_t aux[kAux] = {};  // independent launches (normals tiers, render size classes) run side by side
+  cudaEvent_t ev_fork = nullptr, ev_join[kAux] = {};
   ag2::DevBuf<uint32_t> scalars;        // small device scratch (counters, maxima, flags)
 
   // samples

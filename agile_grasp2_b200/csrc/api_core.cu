@@ -224,7 +224,7 @@ int ag2_create(const ag2_params* p, int device, ag2_ctx** out) {
   }
   for (int i = 0; i < 18; i++) cudaEventCreate(&c->ev[i]);
   cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming);
-  for (int i = 0; i < 4; i++) {
+  for (int i = 0; i < ag2_ctx::kAux; i++) {
     if (cudaStreamCreateWithFlags(&c->aux[i], cudaStreamNonBlocking) != cudaSuccess) {
       ag2_destroy(c);
       return AG2_E_CUDA;
@@ -253,7 +253,7 @@ int ag2_destroy(ag2_ctx* c) {
     cudaStreamDestroy(c->stream);
   }
   for (int i = 0; i < 18; i++) cudaEventDestroy(c->ev[i]);
-  for (int i = 0; i < 4; i++) {
+  for (int i = 0; i < ag2_ctx::kAux; i++) {
     if (c->aux[i]) {
       cudaStreamSynchronize(c->aux[i]);
       cudaStreamDestroy(c->aux[i]);

@@ -128,3 +128,9 @@ extern "C" int ag2_find_clusters(ag2_ctx* c, int which_src) {
   AG2_TRY(gather_list_records(c, which_src));
   return clusters_compute(c, c->list_rec[which_src].p, c->list_n[which_src]);
 }
+
+extern "C" int ag2_set_min_inliers(ag2_ctx* c, int min_inliers) {
+  if (!c || min_inliers < 0) return AG2_E_INVALID;
+  c->p.min_inliers = min_inliers;
+  return AG2_OK;
+}

@@ -1253,7 +1253,10 @@ static int normals_moments_tiered(ag2_ctx* c) {
     c->normals_attr_set = true;
   }
   AG2_CUDA(c, cudaEventRecord(c->ev_fork, st));
-  for (int i = 0; i < 4; i++) AG2_CUDA(c, cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
+  // AG2_NORMALS_STREAMS (1..12): how many launches may run side by side; every launch of a stream waits for the one before
+  int n_aux = 4;
+  if (const char* e = getenv("AG2_NORMALS_STREAMS")) n_aux = std::min((int)ag2_ctx::kAux, std::max(1, atoi(e)));
+  for (int i = 0; i < n_aux; i++) AG2_CUDA(c, cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
   int used = 0;
   // dense tiers first: their launches run longest
   for (int k = 0; k < kAllTiers; k++) {
@@ -1266,16 +1269,16 @@ static int normals_moments_tiered(ag2_ctx* c) {
     const uint32_t cap = kTierCapHost[tier];
     if (tier >= cta_from || tier >= 12) {  // above 1024 neighbours only the CTA kernel has the shared memory
       const bool unlikely = tier >= 12 && kTierCapHost[tier - 1] >= 2u * std::max(c->max_kn_hint, 512u);
-      AG2_TRY(launch_normals_cta(c, c->aux[used++ & 3], owned, n_dev, cap, list, c->tier_cnt.p + 16 + tier, unlikely));
+      AG2_TRY(launch_normals_cta(c, c->aux[used++ % n_aux], owned, n_dev, cap, list, c->tier_cnt.p + 16 + tier, unlikely));
       continue;
     }
     const bool quad = tier < (int)quad_tiers;
-    if (quad) AG2_TRY(launch_normals_quad(c, c->aux[used++ & 3], owned, n_dev, quad_min, cap, list));
+    if (quad) AG2_TRY(launch_normals_quad(c, c->aux[used++ % n_aux], owned, n_dev, quad_min, cap, list));
     // the warp-per-point launch of a quad tier only runs when the tier is too short for k_normals_quad
-    AG2_TRY(launch_normals(c, c->aux[used++ & 3], owned, n_dev, quad ? quad_min : 0u, cap, list, nullptr, nullptr, 0,
+    AG2_TRY(launch_normals(c, c->aux[used++ % n_aux], owned, n_dev, quad ? quad_min : 0u, cap, list, nullptr, nullptr, 0,
                            c->tier_cnt.p + 16 + tier));
   }
-  for (int i = 0; i < std::min(used, 4); i++) {
+  for (int i = 0; i < std::min(used, n_aux); i++) {
     AG2_CUDA(c, cudaEventRecord(c->ev_join[i], c->aux[i]));
     AG2_CUDA(c, cudaStreamWaitEvent(st, c->ev_join[i], 0));
   }

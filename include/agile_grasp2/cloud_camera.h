@@ -34,7 +34,7 @@ class CloudCamera {
   explicit CloudCamera(const std::string& filename) {
     processed_ = loadPointCloudFromFile(filename, &normals_);
     original_ = processed_;
-    camera_source_ = ag2shim::MatrixXi(1, (int)processed_.size());
+    camera_source_ = ag2shim::zeros_i(1, (int)processed_.size());
     for (int i = 0; i < camera_source_.cols(); i++) camera_source_(0, i) = 1;
   }
 
@@ -93,10 +93,10 @@ class CloudCamera {
 
   void initCameraSource(int n, int size_left_cloud) {
     if (size_left_cloud == n) {  // one camera: the reference leaves the row at zero here (:44-46)
-      camera_source_ = ag2shim::MatrixXi(1, n);
+      camera_source_ = ag2shim::zeros_i(1, n);
       for (int i = 0; i < n; i++) camera_source_(0, i) = 1;  // intent: the single camera sees every point
     } else {
-      camera_source_ = ag2shim::MatrixXi(2, n);
+      camera_source_ = ag2shim::zeros_i(2, n);
       for (int i = 0; i < size_left_cloud; i++) camera_source_(0, i) = 1;
       for (int i = size_left_cloud; i < n; i++) camera_source_(1, i) = 1;
     }
@@ -106,8 +106,7 @@ class CloudCamera {
     std::vector<uint8_t> mask = cameraMask();
     std::vector<float> nrm;
     if (normals_.cols() == (int)processed_.size() && normals_.cols() > 0) {
-      nrm.resize(normals_.d.size());
-      for (size_t i = 0; i < nrm.size(); i++) nrm[i] = (float)normals_.d[i];
+      nrm = ag2shim::to_floats(normals_);
     }
     check(ag2_preprocess_cloud(ctx, processed_.xyz.data(), 12, processed_.size(), mask.data(), camera_source_.rows(),
                                nrm.empty() ? nullptr : nrm.data(), filter_ws, voxelize, cell_size),
@@ -118,7 +117,7 @@ class CloudCamera {
     processed_.rgba.clear();
     mask.resize(n);
     if (n) check(ag2_get_cloud(ctx, processed_.xyz.data(), mask.data(), n, &n), "ag2_get_cloud");
-    ag2shim::MatrixXi cs(camera_source_.rows(), (int)n);
+    ag2shim::MatrixXi cs = ag2shim::zeros_i((int)camera_source_.rows(), (int)n);
     for (size_t j = 0; j < n; j++)
       for (int i = 0; i < cs.rows(); i++) cs(i, (int)j) = (mask[j] >> i) & 1;
     camera_source_ = cs;

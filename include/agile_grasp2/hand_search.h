@@ -27,8 +27,7 @@ inline void upload(ag2_ctx* ctx, const CloudCamera& cc, bool use_samples) {
   std::vector<uint8_t> mask = cc.cameraMask();
   std::vector<float> nrm;
   if (cc.getNormals().cols() == (int)cloud.size() && cloud.size() > 0) {
-    nrm.resize((size_t)3 * cloud.size());
-    for (size_t i = 0; i < nrm.size(); i++) nrm[i] = (float)cc.getNormals().d[i];
+    nrm = ag2shim::to_floats(cc.getNormals());
   }
   check(ag2_set_cloud(ctx, cloud.xyz.data(), 12, cloud.size(), mask.data(), cc.getCameraSource().rows(),
                       nrm.empty() ? nullptr : nrm.data()),
@@ -60,7 +59,7 @@ class HandSearch {
   struct Parameters {  // hand_search.h:72-91
     double nn_radius_taubin_, nn_radius_hands_;
     int num_orientations_, num_threads_, num_samples_;
-    ag2shim::Matrix4d cam_tf_left_, cam_tf_right_;
+    ag2shim::Matrix4d cam_tf_left_ = ag2shim::identity4(), cam_tf_right_ = ag2shim::identity4();
     double finger_width_, hand_outer_diameter_, hand_depth_, hand_height_, init_bite_;
   };
 
@@ -85,10 +84,8 @@ class HandSearch {
     p_.hand_depth = params.hand_depth_;
     p_.hand_height = params.hand_height_;
     p_.init_bite = params.init_bite_;
-    for (int i = 0; i < 16; i++) {
-      p_.cam_tf_left[i] = params.cam_tf_left_.m[i];
-      p_.cam_tf_right[i] = params.cam_tf_right_.m[i];
-    }
+    ag2shim::row_major16(params.cam_tf_left_, p_.cam_tf_left);
+    ag2shim::row_major16(params.cam_tf_right_, p_.cam_tf_right);
     apply();
   }
   // seed of the counter-based replacement of rand() (hand_search.cpp:130); the reference calls
@@ -98,11 +95,11 @@ class HandSearch {
     apply();
   }
   void setCamTfLeft(const ag2shim::Matrix4d& t) {
-    for (int i = 0; i < 16; i++) p_.cam_tf_left[i] = t.m[i];
+    ag2shim::row_major16(t, p_.cam_tf_left);
     apply();
   }
   void setCamTfRight(const ag2shim::Matrix4d& t) {
-    for (int i = 0; i < 16; i++) p_.cam_tf_right[i] = t.m[i];
+    ag2shim::row_major16(t, p_.cam_tf_right);
     apply();
   }
 

@@ -7,19 +7,21 @@
 
 class HandleSearch {
  public:
-  HandleSearch() : min_inliers_(0) {}
-  void setMinInliers(int m) { min_inliers_ = m; }
+  HandleSearch() : min_inliers_(-1) {}
+  void setMinInliers(int m) { min_inliers_ = m; }  // handle_search.h:83-86
   int getMinInliers() const { return min_inliers_; }
 
-  // Clusters list `which_src` (AG2_LIST_*) held by the detector's context.
+  // Clusters list `which_src` (AG2_LIST_*) held by the detector's context, with this object's min_inliers when
+  // setMinInliers was called (else the detector's own parameter).
   std::vector<GraspHypothesis> findClusters(GraspDetector& det, int which_src) {
-    ag2_ctx* ctx = det.context();  // min_inliers comes from the detector's parameters
+    ag2_ctx* ctx = det.context();
+    if (min_inliers_ >= 0) ag2shim::check(ag2_set_min_inliers(ctx, min_inliers_), "ag2_set_min_inliers", ctx);
     ag2shim::check(ag2_find_clusters(ctx, which_src), "ag2_find_clusters", ctx);
     return ag2shim::fetch(ctx, AG2_LIST_CLUSTERS);
   }
 
  private:
-  int min_inliers_;
+  int min_inliers_;  // -1: not set here
 };
 
 #endif

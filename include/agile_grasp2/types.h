@@ -1,6 +1,8 @@
-// Minimal Eigen-free value types used by the header-only shims in this directory.  Where Eigen is
-// available they map 1:1 (Eigen::Map<const Eigen::Vector3d>(v.data()) etc.); here they keep the
-// shims compilable with nothing but a C++17 compiler and libag2.so.
+// Value types of the header-only shims in this directory.  Where <Eigen/Dense> can be included (the reference's own
+// build) Vector3d / Matrix3Xd / Matrix4d / MatrixXi ARE Eigen's types, so reference code passes its matrices
+// unchanged; otherwise minimal Eigen-free stand-ins with the same members keep the shims compilable with nothing
+// but a C++17 compiler and libag2.so (define AG2SHIM_NO_EIGEN to force them).  The shims touch the matrices only
+// through operator()(r, c), rows(), cols(), resize(r, c), data() and the helpers at the end of this file.
 #ifndef AGILE_GRASP2_SHIM_TYPES_H_
 #define AGILE_GRASP2_SHIM_TYPES_H_
 
@@ -8,7 +10,23 @@
 #include <cstdint>
 #include <vector>
 
+#if defined(__has_include) && !defined(AG2SHIM_NO_EIGEN)
+#if __has_include(<Eigen/Dense>)
+#include <Eigen/Dense>
+#define AG2SHIM_HAVE_EIGEN 1
+#endif
+#endif
+
 namespace ag2shim {
+
+#ifdef AG2SHIM_HAVE_EIGEN
+using Vector3d = Eigen::Vector3d;
+using Matrix3Xd = Eigen::Matrix3Xd;  // column-major 3 x N
+using Matrix4d = Eigen::Matrix4d;
+using MatrixXi = Eigen::MatrixXi;
+inline Matrix4d identity4() { return Matrix4d::Identity(); }
+inline MatrixXi zeros_i(int rows, int cols) { return MatrixXi::Zero(rows, cols); }
+#else
 
 struct Vector3d {
   std::array<double, 3> v{{0, 0, 0}};
@@ -52,6 +70,23 @@ struct MatrixXi {
   int& operator()(int i, int j) { return d[(size_t)j * r + i]; }
   int operator()(int i, int j) const { return d[(size_t)j * r + i]; }
 };
+
+inline Matrix4d identity4() { return Matrix4d(); }
+inline MatrixXi zeros_i(int rows, int cols) { return MatrixXi(rows, cols); }
+#endif  // AG2SHIM_HAVE_EIGEN
+
+// row-major copy of a 4 x 4 transform (the layout of ag2_params::cam_tf_*), whatever the storage order of the type
+inline void row_major16(const Matrix4d& t, double* out) {
+  for (int r = 0; r < 4; r++)
+    for (int c = 0; c < 4; c++) out[4 * r + c] = t(r, c);
+}
+// 3 x N column-major doubles -> floats (xyz xyz ...)
+inline std::vector<float> to_floats(const Matrix3Xd& m) {
+  std::vector<float> out((size_t)3 * (size_t)m.cols());
+  const double* d = m.data();
+  for (size_t i = 0; i < out.size(); i++) out[i] = (float)d[i];
+  return out;
+}
 
 // 60 x 60 x 3 u8 image with the cv::Mat (HWC) layout
 struct Image {

@@ -25,6 +25,21 @@ def test_shim_headers_compile_standalone(tmp_path):
         assert r.returncode == 0, (h, r.stderr[-2000:])
 
 
+def test_shims_compile_against_the_eigen_interface():
+    """types.h aliases its value types to Eigen's where <Eigen/Dense> is found.  Eigen is not in this image: a mock with
+    Eigen's signatures and defaults (tests/cpp/mock_eigen) stands in for a compile-only check of that branch."""
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    for src in ("test_shim.cpp", "test_group.cpp"):
+        r = subprocess.run([gxx, "-std=c++17", "-Wall", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"),
+                            "-I" + os.path.join(ROOT, "tests", "cpp", "mock_eigen"), os.path.join(ROOT, "tests", "cpp", src)],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, (src, r.stderr[-2000:])
+    probe = subprocess.run([gxx, "-std=c++17", "-E", "-dM", "-I" + os.path.join(ROOT, "include"),
+                            "-I" + os.path.join(ROOT, "tests", "cpp", "mock_eigen"), "-x", "c++",
+                            os.path.join(ROOT, "include", "agile_grasp2", "types.h")], capture_output=True, text=True)
+    assert "AG2SHIM_HAVE_EIGEN" in probe.stdout
+
+
 @pytest.mark.gpu
 def test_cpp_shim_flow_matches_oracle(tiny_scene, tmp_path):
     assert os.path.exists(BIN), "build tests/cpp first (__graft_entry__.build())"
