@@ -58,8 +58,8 @@ namespace ag2 {
 namespace {
 
 constexpr int kMaxRanks = 8;
-enum { F_IN = 0, F_GRID = 1, F_NRM = 2, F_RES = 3 };
-// flag window (uint32 words): [kind * 8 + source rank] epochs; [32] wait timeouts seen here; [33] bad sample indices
+enum { F_IN = 0, F_GRID = 1, F_NRM = 2, F_RES = 3, F_IN2 = 5 };
+// flag window (uint32 words): [kind * 8 + source rank] epochs (kinds 0..3 and 5); [32] wait timeouts seen here; [33] bad sample indices
 constexpr size_t kFlagBytes = 256;
 constexpr int kErrTimeout = 32, kErrSample = 33;
 constexpr size_t kResHeader = 16;  // uint32 count, uint32 status of the sending rank, 8 bytes unused
@@ -141,6 +141,30 @@ __global__ void __launch_bounds__(256) k_copy2(const unsigned char* __restrict__
     if (a16 * 16 + tid < a_bytes) a_dst[a16 * 16 + tid] = a_src[a16 * 16 + tid];
     if (b16 * 16 + tid < b_bytes) b_dst[b16 * 16 + tid] = b_src[b16 * 16 + tid];
   }
+}
+
+// Second stage of the input distribution: byte range [0, bytes) of region `off` lives in slices of `slice` bytes,
+// slice k in the window of rank k (rank 0's window holds all of them); 16 bytes per load, everything 16-byte aligned
+// but the tail of the range.
+__device__ __forceinline__ void gather_region(const PeerPtrs& w, int rank, size_t off, size_t bytes, size_t slice,
+                                              unsigned char* __restrict__ dst, size_t tid, size_t nth) {
+  const size_t n16 = bytes / 16;
+  for (size_t i = tid; i < n16; i += nth) {
+    const size_t k = (i * 16) / slice;
+    const unsigned char* src = w.base[rank == 0 ? 0 : k] + off;
+    reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[i];
+  }
+  if (tid < 16 && n16 * 16 + tid < bytes) {
+    const size_t b = n16 * 16 + tid;
+    dst[b] = (w.base[rank == 0 ? 0 : b / slice] + off)[b];
+  }
+}
+__global__ void __launch_bounds__(256) k_gather_slices(PeerPtrs w, int rank, size_t off_a, size_t a_bytes, size_t a_slice,
+                                                       unsigned char* __restrict__ a_dst, size_t off_b, size_t b_bytes,
+                                                       size_t b_slice, unsigned char* __restrict__ b_dst) {
+  const size_t tid = blockIdx.x * (size_t)blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+  gather_region(w, rank, off_a, a_bytes, a_slice, a_dst, tid, nth);
+  gather_region(w, rank, off_b, b_bytes, b_slice, b_dst, tid, nth);
 }
 
 // Strided shard rank, rank + world, ... of the sample list (range-checked against the cloud).
@@ -449,10 +473,28 @@ struct Rank {
       if (!on_device) io_h2d += 12 * n + (cam ? n : 0) + 4 * s;
     }
     const unsigned char* src = base;  // where the inputs are read from
+    // Three ranks and more: seven ranks pulling the whole cloud from rank 0 at once are bounded by ONE GPU's NVLink
+    // egress.  Two stages instead: rank r copies slice r of cloud and mask from rank 0's window into its own, then
+    // every rank collects the slices from the windows of their holders -- every link carries 1/world of the data.
+    const bool two_stage = world > 2 && use_peer;
+    size_t xyz_slice = 0, cam_slice = 0;
     if (world > 1 && use_peer) {
       if (rank == 0) G_TRY(post(F_IN));
       G_TRY(wait(F_IN, 1u));
       src = peers.base[0];
+      if (two_stage) {
+        xyz_slice = align_up((12 * n + world - 1) / world, 16);
+        cam_slice = align_up((n + world - 1) / world, 16);
+        if (rank != 0) {
+          const size_t xb = std::min(12 * n, (size_t)rank * xyz_slice), xe = std::min(12 * n, (size_t)(rank + 1) * xyz_slice);
+          const size_t cb = std::min(n, (size_t)rank * cam_slice), ce = std::min(n, (size_t)(rank + 1) * cam_slice);
+          k_copy2<<<c->sm_count, 256, 0, st>>>(src + off_xyz + xb, base + off_xyz + xb, xe - xb, src + off_cam + cb,
+                                               base + off_cam + cb, ce - cb);
+          G_LAUNCH();
+        }
+        G_TRY(post(F_IN2));
+        if (hb || rank != 0) G_TRY(wait(F_IN2, all_mask()));  // rank 0 reads its own window only
+      }
     } else if (world > 1) {
       G_NCCL(ncclGroupStart());
       G_NCCL(ncclBroadcast(base + off_xyz, base + off_xyz, 12 * n, ncclChar, 0, comm, st));
@@ -464,8 +506,13 @@ struct Rank {
     c->normals_given = false;
     G_CUDA(c->xyz_in.reserve(3 * n));
     G_CUDA(c->cam_in.reserve(n));
-    k_copy2<<<c->sm_count * 4, 256, 0, st>>>(src + off_xyz, reinterpret_cast<unsigned char*>(c->xyz_in.p), 12 * n,
-                                             src + off_cam, c->cam_in.p, n);
+    if (two_stage)
+      k_gather_slices<<<c->sm_count * 4, 256, 0, st>>>(peers, rank, off_xyz, 12 * n, xyz_slice,
+                                                       reinterpret_cast<unsigned char*>(c->xyz_in.p), off_cam, n, cam_slice,
+                                                       c->cam_in.p);
+    else
+      k_copy2<<<c->sm_count * 4, 256, 0, st>>>(src + off_xyz, reinterpret_cast<unsigned char*>(c->xyz_in.p), 12 * n,
+                                               src + off_cam, c->cam_in.p, n);
     G_LAUNCH();
     mark(1);
     G_TRY(grid_build(c));
