@@ -20,6 +20,8 @@ constexpr int kFrameThreads = 128;
 // all sizes without the host knowing the largest one: every sample at capacity 1024, and two short persistent
 // launches over the (usually empty) lists of denser ones at 4096 and 16384.
 constexpr uint32_t kFrameCap0 = 1024, kFrameCap1 = 4096, kFrameCap2 = 16384;
+constexpr int kOrdBuckets = 256;                       // d2 buckets of the first class's ordering (multiple of 32)
+constexpr size_t kFrameSmem0 = (size_t)kFrameCap0 * 18;  // keys 8 + positions 4 + ordered positions 4 + grouping 2 bytes
 
 __device__ __forceinline__ void sample_query(const float* __restrict__ xyz_in, const int32_t* __restrict__ sidx,
                                              const double* __restrict__ sxyz, uint32_t s, float q[3]) {
@@ -159,6 +161,7 @@ __device__ void frame_of_sample(const FrameArgs& P, const uint32_t s, unsigned c
   __shared__ double M[9];
   __shared__ int num_source[8];
   __shared__ uint32_t filled;
+  __shared__ uint32_t bstart[kOrdBuckets + 1], bcursor[kOrdBuckets];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kFrameThreads / 32;
   float q[3];
   sample_query(xyz_in, sidx, sxyz, s, q);
@@ -205,17 +208,67 @@ __device__ void frame_of_sample(const FrameArgs& P, const uint32_t s, unsigned c
     }
   }
   __syncthreads();
-  const uint32_t n_pad = next_pow2(count);
-  for (uint32_t t = count + tid; t < n_pad; t += kFrameThreads) {
-    keys[t] = ~0ull;
-    vals[t] = 0;
+  const uint32_t* ordered;  // cell-sorted positions of the neighbours in ascending (d2, input index) order
+  if (cap == kFrameCap0) {
+    // First capacity class (every sample but the few dense ones): the order comes from kOrdBuckets monotone d2
+    // buckets and, inside a bucket, rank = number of smaller keys among its handful of members -- five barriers
+    // instead of the 55 of a 1024-element bitonic network, which was most of this kernel's dependent chain.
+    uint32_t* svals = vals + cap;
+    uint16_t* grouped = (uint16_t*)(svals + cap);
+    const float bscale = (float)kOrdBuckets / r2;
+    auto bucket_of = [&](uint64_t key) -> int {
+      return min(kOrdBuckets - 1, (int)(__uint_as_float((uint32_t)(key >> 32)) * bscale));  // monotone in d2
+    };
+    for (int b = tid; b <= kOrdBuckets; b += kFrameThreads) bstart[b] = 0;
+    __syncthreads();
+    for (uint32_t t = tid; t < count; t += kFrameThreads) atomicAdd(&bstart[bucket_of(keys[t]) + 1], 1u);
+    __syncthreads();
+    if (warp == 0) {  // inclusive prefix over the bucket counts, 32 lanes x kOrdBuckets / 32 consecutive buckets
+      constexpr int per = kOrdBuckets / 32;
+      uint32_t loc[per], run = 0;
+#pragma unroll
+      for (int k = 0; k < per; k++) run += bstart[1 + lane * per + k], loc[k] = run;
+      uint32_t incl = run;
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t up = __shfl_up_sync(AG2_FULL, incl, o);
+        if (lane >= o) incl += up;
+      }
+      const uint32_t before = incl - run;
+#pragma unroll
+      for (int k = 0; k < per; k++) {
+        bstart[1 + lane * per + k] = before + loc[k];
+        bcursor[lane * per + k] = before + (k ? loc[k - 1] : 0u);
+      }
+    }
+    __syncthreads();
+    for (uint32_t t = tid; t < count; t += kFrameThreads)
+      grouped[atomicAdd(&bcursor[bucket_of(keys[t])], 1u)] = (uint16_t)t;
+    __syncthreads();
+    for (uint32_t p = tid; p < count; p += kFrameThreads) {
+      const uint32_t t = grouped[p];
+      const uint64_t key = keys[t];
+      const int b = bucket_of(key);
+      const uint32_t lo = bstart[b], hi = bstart[b + 1];
+      uint32_t rank = lo;
+      for (uint32_t u = lo; u < hi; u++) rank += keys[grouped[u]] < key;  // keys are distinct: (d2, input index)
+      svals[rank] = vals[t];
+    }
+    __syncthreads();
+    ordered = svals;
+  } else {
+    const uint32_t n_pad = next_pow2(count);
+    for (uint32_t t = count + tid; t < n_pad; t += kFrameThreads) {
+      keys[t] = ~0ull;
+      vals[t] = 0;
+    }
+    __syncthreads();
+    bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kFrameThreads, BlockSync());
+    ordered = vals;
   }
-  __syncthreads();
-  bitonic_sort_kv(keys, vals, n_pad, (uint32_t)tid, (uint32_t)kFrameThreads, BlockSync());
   const int n = (int)min(50u, count);
   if (tid < n) {
     uint32_t r = draw_index(seed, id_offset + id_stride * (int64_t)s, tid, count);
-    uint32_t pos = vals[r];
+    uint32_t pos = ordered[r];
     float4 nv = g.nrm[pos];
     double nx = (double)nv.x, ny = (double)nv.y, nz = (double)nv.z;
     uint32_t mask = __float_as_uint(nv.w);
@@ -343,7 +396,7 @@ int frames_compute(ag2_ctx* c) {
   P.cam1x = h.cam_origin[1][0], P.cam1y = h.cam_origin[1][1], P.cam1z = h.cam_origin[1][2];
   P.out = c->frames.p, P.num_valid = c->scalars.p + 13;
   P.cap = kFrameCap0, P.lo = 0, P.list = nullptr, P.list_n = nullptr;
-  k_frames<<<S, kFrameThreads, (size_t)kFrameCap0 * 12, st>>>(P);
+  k_frames<<<S, kFrameThreads, kFrameSmem0, st>>>(P);
   AG2_LAUNCH_CHECK(c);
   P.cap = kFrameCap1, P.lo = kFrameCap0, P.list = big_list, P.list_n = big_n;
   k_frames<<<std::min<uint32_t>(S, (uint32_t)c->sm_count * 4), kFrameThreads, (size_t)kFrameCap1 * 12, st>>>(P);
