@@ -256,18 +256,27 @@ k_render(RenderArgs A, const __grid_constant__ HandConst hc) {
     const uint32_t a = cellc[cell] & 0xFFFFu, b = cellc[cell + 1] & 0xFFFFu;
     if (a == b) continue;
     double ax = 0.0, ay = 0.0, az = 0.0;
-    for (uint32_t u = a; u < b; u++) {
-      const uint32_t pos = run_pos[ord[u]];
-      if (EXPLICIT) {
-        const double* nv = A.xnrm + 3 * (size_t)pos;
+    if (EXPLICIT) {
+      for (uint32_t u = a; u < b; u++) {
+        const double* nv = A.xnrm + 3 * (size_t)run_pos[ord[u]];
         ax += nv[0], ay += nv[1], az += nv[2];
-      } else {
-        float4 nv = A.g.nrm[pos];
-        double n0 = (double)nv.x, n1 = (double)nv.y, n2 = (double)nv.z;
-        // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
-        ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
-        ay += (FR[0][1] * n0 + FR[1][1] * n1) + FR[2][1] * n2;
-        az += (FR[0][2] * n0 + FR[1][2] * n1) + FR[2][2] * n2;
+      }
+    } else {
+      // the sums are sequential (their order is the reference's), the gathers need not be: four normals in flight
+      for (uint32_t u0 = a; u0 < b; u0 += 4) {
+        float4 nv[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) nv[k] = A.g.nrm[run_pos[ord[min(u0 + k, b - 1)]]];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          if (u0 + k < b) {
+            const double n0 = (double)nv[k].x, n1 = (double)nv[k].y, n2 = (double)nv[k].z;
+            // normals_rot = frame_rot^T * normal (hand_search.cpp:360)
+            ax += (FR[0][0] * n0 + FR[1][0] * n1) + FR[2][0] * n2;
+            ay += (FR[0][1] * n0 + FR[1][1] * n1) + FR[2][1] * n2;
+            az += (FR[0][2] * n0 + FR[1][2] * n1) + FR[2][2] * n2;
+          }
+        }
       }
     }
     double s = 1.0 / sqrt(ax * ax + (ay * ay + az * az));
