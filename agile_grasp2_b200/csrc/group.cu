@@ -476,7 +476,8 @@ struct Rank {
     // Three ranks and more: seven ranks pulling the whole cloud from rank 0 at once are bounded by ONE GPU's NVLink
     // egress.  Two stages instead: rank r copies slice r of cloud and mask from rank 0's window into its own, then
     // every rank collects the slices from the windows of their holders -- every link carries 1/world of the data.
-    const bool two_stage = world > 2 && use_peer;
+    static const bool force_two_stage = getenv("AG2_GROUP_TWO_STAGE") && atoi(getenv("AG2_GROUP_TWO_STAGE")) != 0;  // test hook
+    const bool two_stage = (world > 2 || (force_two_stage && world > 1)) && use_peer;
     size_t xyz_slice = 0, cam_slice = 0;
     if (world > 1 && use_peer) {
       if (rank == 0) G_TRY(post(F_IN));

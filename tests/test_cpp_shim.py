@@ -130,3 +130,7 @@ def test_cpp_group_two_gpus_equals_one(tiny_scene, tmp_path):
     capi.pcd_write(pcd, tiny_scene["xyz"], binary=True)
     r = subprocess.run([binp, pcd, "120", "2"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "TEST_GROUP OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    # the two-stage input distribution of three ranks and more (slices from their holders), forced on two
+    r = subprocess.run([binp, pcd, "120", "2"], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, AG2_GROUP_TWO_STAGE="1"))
+    assert r.returncode == 0 and "TEST_GROUP OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

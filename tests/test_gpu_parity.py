@@ -142,6 +142,27 @@ def test_classify_images_direct(tiny_scene):
     assert np.all(np.abs(gl - ol) <= tol), np.abs(gl - ol).max()
 
 
+@pytest.mark.parametrize("s1,s2", [(64.0, 1.0 / 64.0), (1.0 / 512.0, 512.0), (4096.0, 1.0 / 4096.0), (3.0e-5, 1.0 / 3.0e-5)])
+def test_classify_images_with_rescaled_layers(s1, s2):
+    """conv2 runs on fp16 split operands behind power-of-two scales derived from the weights (lenet.cu): layers whose
+    weights are orders of magnitude away from Xavier's must come out within the same tolerance.  conv1 is scaled by s1
+    and conv2 by s2 (biases with their layer's output), so the activations between them move over eight decades while the logits stay put."""
+    w = {k: v.copy() for k, v in ob.xavier_weights(13, bias_scale=0.2).items()}
+    w["conv1_w"] *= np.float32(s1); w["conv1_b"] *= np.float32(s1)
+    w["conv2_w"] *= np.float32(s2); w["conv2_b"] *= np.float32(s1 * s2)
+    p = make_params(capi.MODE_PREDICTION)
+    g = capi.Context(p); o = ob.context(p)
+    g.set_lenet_weights(w); o.set_lenet_weights(w)
+    rng = np.random.default_rng(29)
+    imgs = rng.integers(0, 256, size=(33, 60, 60, 3), dtype=np.uint8)
+    imgs[rng.random(imgs.shape) < 0.6] = 0
+    imgs[0] = 255
+    gl, ol = g.classify_images(imgs), o.classify_images(imgs)
+    assert np.all(np.isfinite(gl))
+    tol = np.maximum(1e-3, 1e-5 * np.abs(ol))  # s1 * s2 = 1: the logits keep the magnitude of the unscaled network
+    assert np.all(np.abs(gl - ol) <= tol), np.abs(gl - ol).max()
+
+
 @pytest.mark.parametrize("n", [1, 129, 4500])
 def test_classify_images_batch_sizes(n):
     """Image-tile / split-K / chunk boundaries of the tensor-core LeNet: one image, one image past a
