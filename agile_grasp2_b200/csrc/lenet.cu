@@ -166,9 +166,11 @@ constexpr int TC_PIX = P1 * P1;  // 784 pixels per plane
 // the 56 x 56 outputs; tap (ky, kx) moves the start address by ky*60 + kx pixels.  One K step of
 // 8 = TWO taps: the second chunk is simply the same tile one tap further, i.e. LBO = 16 bytes
 // inside a kernel row and (60-4)*16 bytes across rows; 25 taps = 13 steps (the 26th tap has zero
-// weights).  28 tiles (7 in x by y0 = 0, 16, 32, 40) in six passes of five (240 of 256 allocated
-// tensor-memory columns), so two CTAs fit an SM and one CTA's epilogue overlaps the other's MMAs.
-// 364 MMAs per image.
+// weights).  28 tiles (7 in x by y0 = 0, 16, 32, 40) in six passes of five (240 tensor-memory columns); passes
+// alternate between the halves of tensor memory.  Persistent and warp-specialised like k_conv2_h: grid =
+// min(images, SMs); warp 0 issues the MMAs (the weights are loaded once per CTA), twenty worker warps (five per
+// lane quarter, one per tile of a pass) expand the NEXT image into the other A buffer while the first pass of this
+// one accumulates, then pool and store each pass while the next one accumulates.  364 MMAs per image.
 // ---------------------------------------------------------------------------------------------
 // fp16 operand planes shared by k_conv1_tc's epilogue (writer) and k_conv2_h (reader): per image
 // [hi, lo][plane p = channels 8p .. 8p+7][784 pixels][8 halfs]
@@ -188,138 +190,181 @@ constexpr int C1_A_BYTES = C1_PIX * 16;                   // 57664
 constexpr int C1_N = 48;                                  // B rows: 0..19 w_hi, 24..43 w_lo of the 20 channels
 constexpr int C1_B_FLOATS = 13 * 2 * C1_N * 4;            // [k step][chunk][48 rows][4] = 4992
 constexpr int C1_B_BYTES = C1_B_FLOATS * 4;               // 19968
-constexpr int kC1Threads = 384;                           // three epilogue warps per tensor-memory lane quarter
+constexpr int kC1Threads = 704;                           // MMA warp, spare warp, five worker warps per tensor-memory lane quarter (one per tile of a pass)
 constexpr int C1_TILES = 28, C1_PASS_TILES = 5;           // 7 (x) by 4 (y0 = 0, 16, 32, 40) tiles, 5 x 48 columns per pass
-constexpr int C1_SMEM_BYTES = C1_A_BYTES + C1_B_BYTES + 64;
+constexpr int C1_SMEM_BYTES = 2 * C1_A_BYTES + C1_B_BYTES + 128;  // two image buffers
 
 template <bool HALF_OUT>
-__global__ void __launch_bounds__(kC1Threads, 2)
+__global__ void __launch_bounds__(kC1Threads, 1)
 k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* [13][2 chunks][48][4] */,
            const float* __restrict__ bias, float4* __restrict__ out /* [n][5][784] float4, or the fp16 planes of k_conv2_h */,
-           float a_scale /* HALF_OUT: power of two that brings the activations into fp16's range */) {
+           float a_scale /* HALF_OUT: power of two that brings the activations into fp16's range */, int n) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
-  float4* A = reinterpret_cast<float4*>(tc_smem);
-  uint8_t* B = tc_smem + C1_A_BYTES;
-  uint64_t* wbar = reinterpret_cast<uint64_t*>(tc_smem + C1_A_BYTES + C1_B_BYTES);
-  uint64_t* done = wbar + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  uint8_t* B = tc_smem + 2 * C1_A_BYTES;
+  uint64_t* wbar = reinterpret_cast<uint64_t*>(tc_smem + 2 * C1_A_BYTES + C1_B_BYTES);
+  uint64_t* a_full = wbar + 1;   // [2] image buffer staged
+  uint64_t* t_full = a_full + 2;  // [2] a pass's accumulators complete
+  uint64_t* t_empty = t_full + 2;  // [2] ... and read by the epilogue
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  constexpr int kPasses = (C1_TILES + C1_PASS_TILES - 1) / C1_PASS_TILES;
+  constexpr int kWorkers = kC1Threads - 64;  // warps 2..: image staging + epilogue
 
   if (tid == 0) {
     tc::mbar_init(wbar, 1);
-    tc::mbar_init(done, 1);
+    for (int i = 0; i < 2; i++) tc::mbar_init(&a_full[i], 1), tc::mbar_init(&t_full[i], 1), tc::mbar_init(&t_empty[i], kWorkers / 32);
     tc::mbar_init_fence();
   }
-  if (warp == 1) tc::tmem_alloc<256>(tmem_slot);
-  __syncthreads();
-  if (tid == 0) {  // the weights: one bulk copy
-    tc::mbar_expect_tx(wbar, C1_B_BYTES);
-    tc::bulk_g2s(B, wtc, C1_B_BYTES, wbar);
-  }
-  // expand the image: 4 pixels = 12 bytes = 3 aligned words per step (cv::split + convertTo(CV_32F) are exact)
-  const uint32_t* src = reinterpret_cast<const uint32_t*>(images + (size_t)blockIdx.x * AG2_IMAGE_BYTES);
-  for (int g4 = tid; g4 < 900; g4 += kC1Threads) {
-    const uint32_t w0 = __ldg(&src[3 * g4]), w1 = __ldg(&src[3 * g4 + 1]), w2 = __ldg(&src[3 * g4 + 2]);
-    A[4 * g4 + 0] = make_float4((float)(w0 & 255u), (float)((w0 >> 8) & 255u), (float)((w0 >> 16) & 255u), 0.f);
-    A[4 * g4 + 1] = make_float4((float)(w0 >> 24), (float)(w1 & 255u), (float)((w1 >> 8) & 255u), 0.f);
-    A[4 * g4 + 2] = make_float4((float)((w1 >> 16) & 255u), (float)(w1 >> 24), (float)(w2 & 255u), 0.f);
-    A[4 * g4 + 3] = make_float4((float)((w2 >> 8) & 255u), (float)((w2 >> 16) & 255u), (float)(w2 >> 24), 0.f);
-  }
-  if (tid < 4) A[3600 + tid] = make_float4(0.f, 0.f, 0.f, 0.f);
-  tc::fence_async_smem();
+  if (warp == 1) tc::tmem_alloc<512>(tmem_slot);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
-  const int wq = warp & 3;
-  float4* o = out + (size_t)blockIdx.x * 5 * (P1 * P1);
+  const int first = blockIdx.x, stride = gridDim.x;
 
-  constexpr int kPasses = (C1_TILES + C1_PASS_TILES - 1) / C1_PASS_TILES;
-  for (int pass = 0; pass < kPasses; pass++) {
-    const int t_first = pass * C1_PASS_TILES, ntiles = min(C1_PASS_TILES, C1_TILES - t_first);
-    if (warp == 0) {
-      const bool leader = tc::elect_one();
-      if (pass == 0) tc::mbar_wait(wbar, 0);
-      tc::fence_after_sync();
-      if (leader) {
-        const uint32_t idesc = tc::idesc_tf32(128, C1_N);
-        const uint32_t a_base = tc::smem_u32(A) >> 4, b_base = tc::smem_u32(B) >> 4;
-        const uint64_t a_hi64 = ((uint64_t)(960 >> 4) << 32) | ((uint64_t)1 << 46);
-        const uint64_t b_desc0 = tc::smem_desc(0, C1_N * 16, 128) | (uint64_t)b_base;
-        uint32_t tile_a[C1_PASS_TILES];  // start of each tile of this pass, in pixels
-#pragma unroll
-        for (int ti = 0; ti < C1_PASS_TILES; ti++) {
-          const int t = min(t_first + ti, C1_TILES - 1), yb = t / 7, xt = t % 7;
-          tile_a[ti] = a_base + (uint32_t)((yb < 3 ? 16 * yb : 40) * 60 + xt * 8);
-        }
-#pragma unroll 1
-        for (int s = 0; s < 13; s++) {
-          const int t0 = 2 * s;  // taps t0 and t0 + 1
-          const uint32_t off = (uint32_t)((t0 / 5) * 60 + t0 % 5);
-          // second chunk = the next tap of the kernel, in 16-byte units (the 26th tap, zero weights, stays inside the image)
-          const uint32_t lbo = (t0 % 5 == 4 && s < 12) ? (60 - 4) : 1;
-          const uint64_t a_desc = a_hi64 | ((uint64_t)lbo << 16);
-          const uint64_t b_desc = b_desc0 + (uint64_t)(s * 2 * C1_N);
-#pragma unroll
-          for (int ti = 0; ti < C1_PASS_TILES; ti++)
-            if (ti < ntiles) tc::mma_tf32(tmem + ti * C1_N, a_desc | (uint64_t)(tile_a[ti] + off), b_desc, idesc, s != 0);
-        }
-        tc::mma_commit(done);
-      }
-      __syncwarp();
+  if (warp == 0) {
+    // ---- MMA issue: six passes of up to five tiles per image, passes alternate between the halves of tensor memory
+    const bool leader = tc::elect_one();
+    if (leader) {
+      tc::mbar_expect_tx(wbar, C1_B_BYTES);
+      tc::bulk_g2s(B, wtc, C1_B_BYTES, wbar);  // the weights stay for all images of this CTA
     }
-    tc::mbar_wait(done, pass & 1);
-    tc::fence_after_sync();
-    // epilogue: lane = 8 x positions of image row y0 + 4*wq + lane/8; pool partners are lanes ^1 and ^8
-    for (int ti = warp >> 2; ti < ntiles; ti += kC1Threads / 128) {
-      const int t = t_first + ti, yb = t / 7, xt = t % 7;
-      if (yb == 3 && wq < 2) continue;  // rows 40..47 of the y0 = 40 tiles repeat the y0 = 32 ones
-      const int y0 = yb < 3 ? 16 * yb : 40;
-      {
-        float v[C1_N];
-        const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + ti * C1_N;
-        tc::tmem_ld32(taddr, v);
-        tc::tmem_ld16(taddr + 32, v + 32);
-        tc::tmem_ld_wait();
+    __syncwarp();
+    tc::mbar_wait(wbar, 0);
+    const uint32_t idesc = tc::idesc_tf32(128, C1_N);
+    const uint32_t b_base = tc::smem_u32(B) >> 4;
+    const uint64_t a_hi64 = ((uint64_t)(960 >> 4) << 32) | ((uint64_t)1 << 46);
+    const uint64_t b_desc0 = tc::smem_desc(0, C1_N * 16, 128) | (uint64_t)b_base;
+    uint32_t gp = 0;  // pass counter over all images
+    for (int it = 0, img = first; img < n; img += stride, it++) {
+      const int buf = it & 1;
+      tc::mbar_wait(&a_full[buf], (it >> 1) & 1);
+      tc::fence_after_sync();
+      const uint32_t a_base = tc::smem_u32(tc_smem + buf * C1_A_BYTES) >> 4;
+      for (int pass = 0; pass < kPasses; pass++, gp++) {
+        const int tb = gp & 1;
+        tc::mbar_wait(&t_empty[tb], ((gp >> 1) & 1) ^ 1);
+        tc::fence_after_sync();
+        if (leader) {
+          const int t_first = pass * C1_PASS_TILES, ntiles = min(C1_PASS_TILES, C1_TILES - t_first);
+          uint32_t tile_a[C1_PASS_TILES];  // start of each tile of this pass, in pixels
 #pragma unroll
-        for (int ch = 0; ch < C1_OUT; ch++) v[ch] += v[24 + ch];  // a * w_hi + a * w_lo
-        const int py = (y0 + wq * 4 + (lane >> 3)) >> 1, px = (xt * 8 + (lane & 7)) >> 1;
-        const int q = (lane & 1) | ((lane >> 2) & 2);
+          for (int ti = 0; ti < C1_PASS_TILES; ti++) {
+            const int t = min(t_first + ti, C1_TILES - 1), yb = t / 7, xt = t % 7;
+            tile_a[ti] = a_base + (uint32_t)((yb < 3 ? 16 * yb : 40) * 60 + xt * 8);
+          }
+          const uint32_t d0 = tmem + tb * 256;
+#pragma unroll 1
+          for (int s = 0; s < 13; s++) {
+            const int t0 = 2 * s;  // taps t0 and t0 + 1
+            const uint32_t off = (uint32_t)((t0 / 5) * 60 + t0 % 5);
+            // second chunk = the next tap of the kernel, in 16-byte units (the 26th tap, zero weights, stays inside the image)
+            const uint32_t lbo = (t0 % 5 == 4 && s < 12) ? (60 - 4) : 1;
+            const uint64_t a_desc = a_hi64 | ((uint64_t)lbo << 16);
+            const uint64_t b_desc = b_desc0 + (uint64_t)(s * 2 * C1_N);
 #pragma unroll
-        for (int ch = 0; ch < C1_OUT; ch++) {
-          float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
-          v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8)) + __ldg(&bias[ch]);
+            for (int ti = 0; ti < C1_PASS_TILES; ti++)
+              if (ti < ntiles) tc::mma_tf32(d0 + ti * C1_N, a_desc | (uint64_t)(tile_a[ti] + off), b_desc, idesc, s != 0);
+          }
+          tc::mma_commit(&t_full[tb]);
         }
-        if (!HALF_OUT) {
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 2) {
+    // ---- workers: stage the NEXT image (u8 -> one 16-byte chunk per pixel) while this one's first pass accumulates,
+    // then pool and store each pass as it completes
+    const int wtid = tid - 64, wq = warp & 3, wk = (warp - 2) >> 2;  // lane quarter, and which of its three warps
+    auto stage = [&](int it, int img) {
+      float4* A = reinterpret_cast<float4*>(tc_smem + (it & 1) * C1_A_BYTES);
+      // 4 pixels = 12 bytes = 3 aligned words per step (cv::split + convertTo(CV_32F) are exact)
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(images + (size_t)img * AG2_IMAGE_BYTES);
+      for (int g4 = wtid; g4 < 900; g4 += kWorkers) {
+        const uint32_t w0 = __ldg(&src[3 * g4]), w1 = __ldg(&src[3 * g4 + 1]), w2 = __ldg(&src[3 * g4 + 2]);
+        A[4 * g4 + 0] = make_float4((float)(w0 & 255u), (float)((w0 >> 8) & 255u), (float)((w0 >> 16) & 255u), 0.f);
+        A[4 * g4 + 1] = make_float4((float)(w0 >> 24), (float)(w1 & 255u), (float)((w1 >> 8) & 255u), 0.f);
+        A[4 * g4 + 2] = make_float4((float)((w1 >> 16) & 255u), (float)(w1 >> 24), (float)(w2 & 255u), 0.f);
+        A[4 * g4 + 3] = make_float4((float)((w2 >> 8) & 255u), (float)((w2 >> 16) & 255u), (float)(w2 >> 24), 0.f);
+      }
+      if (wtid < 4) A[3600 + wtid] = make_float4(0.f, 0.f, 0.f, 0.f);
+      tc::fence_async_smem();
+      asm volatile("bar.sync 1, %0;" ::"n"(kWorkers) : "memory");  // the workers only
+      if (wtid == 0) tc::mbar_arrive(&a_full[it & 1]);
+    };
+    uint32_t gp = 0;
+    if (first < n) stage(0, first);
+    for (int it = 0, img = first; img < n; img += stride, it++) {
+      // the other buffer was last read by the MMAs of the image before this one: every worker has seen them complete
+      if (img + stride < n) stage(it + 1, img + stride);
+      float4* o = out + (size_t)img * 5 * (P1 * P1);
+      for (int pass = 0; pass < kPasses; pass++, gp++) {
+        const int tb = gp & 1;
+        const int t_first = pass * C1_PASS_TILES, ntiles = min(C1_PASS_TILES, C1_TILES - t_first);
+        tc::mbar_wait(&t_full[tb], (gp >> 1) & 1);
+        tc::fence_after_sync();
+        // lane = 8 x positions of image row y0 + 4*wq + lane/8; pool partners are lanes ^1 and ^8
+        for (int ti = wk; ti < ntiles; ti += kWorkers / 128) {
+          const int t = t_first + ti, yb = t / 7, xt = t % 7;
+          if (yb == 3 && wq < 2) continue;  // rows 40..47 of the y0 = 40 tiles repeat the y0 = 32 ones
+          const int y0 = yb < 3 ? 16 * yb : 40;
+          float v[C1_N];
+          const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + tb * 256 + ti * C1_N;
+          tc::tmem_ld32(taddr, v);
+          tc::tmem_ld16(taddr + 32, v + 32);
+          tc::tmem_ld_wait();
 #pragma unroll
-          for (int cq = 0; cq < 5; cq++)
-            if ((cq & 3) == q) o[cq * (P1 * P1) + py * P1 + px] = make_float4(v[4 * cq], v[4 * cq + 1], v[4 * cq + 2], v[4 * cq + 3]);
-        } else {
-          // lane p of the pooling quad writes plane p (channels 8p .. 8p+7; 20 .. 23 are zero) as its fp16 hi and lo parts
-          uint4* oh = reinterpret_cast<uint4*>(out) + (size_t)blockIdx.x * H_IMG_PLANES * TC_PIX + py * P1 + px;
+          for (int ch = 0; ch < C1_OUT; ch++) v[ch] += v[24 + ch];  // a * w_hi + a * w_lo
+          const int py = (y0 + wq * 4 + (lane >> 3)) >> 1, px = (xt * 8 + (lane & 7)) >> 1;
+          const int q = (lane & 1) | ((lane >> 2) & 2);
 #pragma unroll
-          for (int pl = 0; pl < 3; pl++)
-            if (q == pl) {
-              uint32_t hw[4], lw[4];
+          for (int ch = 0; ch < C1_OUT; ch++) {
+            const float m = fmaxf(v[ch], __shfl_xor_sync(AG2_FULL, v[ch], 1));
+            v[ch] = fmaxf(m, __shfl_xor_sync(AG2_FULL, m, 8));
+          }
+          if (!HALF_OUT) {
 #pragma unroll
-              for (int e = 0; e < 4; e++) {
-                uint16_t h0 = 0, l0 = 0, h1 = 0, l1 = 0;
-                if (8 * pl + 2 * e < C1_OUT) tc::split_f16(v[8 * pl + 2 * e] * a_scale, h0, l0);
-                if (8 * pl + 2 * e + 1 < C1_OUT) tc::split_f16(v[8 * pl + 2 * e + 1] * a_scale, h1, l1);
-                hw[e] = (uint32_t)h0 | ((uint32_t)h1 << 16);
-                lw[e] = (uint32_t)l0 | ((uint32_t)l1 << 16);
-              }
+            for (int cq = 0; cq < 5; cq++)
+              if ((cq & 3) == q)
+                o[cq * (P1 * P1) + py * P1 + px] = make_float4(v[4 * cq] + __ldg(&bias[4 * cq]), v[4 * cq + 1] + __ldg(&bias[4 * cq + 1]),
+                                                               v[4 * cq + 2] + __ldg(&bias[4 * cq + 2]), v[4 * cq + 3] + __ldg(&bias[4 * cq + 3]));
+          } else {
+            // The four lanes of a pooling quad hold the same 20 values; lane p < 3 writes plane p (channels 8p .. 8p+7;
+            // 20 .. 23 are zero) as its fp16 hi and lo parts.  Selects, not branches: the quad's lanes stay converged.
+            const int pl = min(q, 2);
+            float mine[8];
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+              const float c2 = 16 + e < C1_OUT ? v[(16 + e) % C1_N] : 0.f;
+              mine[e] = pl == 0 ? v[e] : (pl == 1 ? v[8 + e] : c2);
+            }
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias) + 2 * pl);  // bias[8 pl .. 8 pl + 3]
+            const float4 b1 = pl < 2 ? __ldg(reinterpret_cast<const float4*>(bias) + 2 * pl + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+            uint32_t hw[4], lw[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+              uint16_t h0, l0, h1, l1;
+              tc::split_f16((mine[2 * e] + bb[2 * e]) * a_scale, h0, l0);
+              tc::split_f16((mine[2 * e + 1] + bb[2 * e + 1]) * a_scale, h1, l1);
+              hw[e] = (uint32_t)h0 | ((uint32_t)h1 << 16);
+              lw[e] = (uint32_t)l0 | ((uint32_t)l1 << 16);
+            }
+            if (q < 3) {
+              uint4* oh = reinterpret_cast<uint4*>(out) + (size_t)img * H_IMG_PLANES * TC_PIX + py * P1 + px;
               oh[pl * TC_PIX] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
               oh[(3 + pl) * TC_PIX] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
             }
+          }
         }
+        tc::fence_before_sync();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&t_empty[tb]);
       }
     }
-    tc::fence_before_sync();
-    __syncthreads();  // the accumulators are overwritten by the next pass
-    tc::fence_after_sync();
   }
-  if (warp == 1) tc::tmem_dealloc<256>(tmem);
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc<512>(tmem);
 }
 
 // ip1 on the tensor cores (k_ip1_tc) reduces over K' = 144 positions x 52 channels (50 + 2 zero) =
@@ -931,8 +976,8 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
       k_conv1_pool<<<(unsigned)m, 256, 0, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w.p, L.c1b.p,
                                                 reinterpret_cast<float4*>(a1));
     else
-      k_conv1_tc<true><<<(unsigned)m, kC1Threads, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
-                                                                reinterpret_cast<float4*>(a1), L.a1_scale);
+      k_conv1_tc<true><<<g2, kC1Threads, C1_SMEM_BYTES, st>>>(d_images + off * AG2_IMAGE_BYTES, L.c1w_tc.p, L.c1b.p,
+                                                              reinterpret_cast<float4*>(a1), L.a1_scale, (int)m);
     AG2_LAUNCH_CHECK(c);
     if (simt == 1) {
       k_conv2_pool<<<(unsigned)m, 288, smem2, st>>>(a1, L.c2w.p, L.c2b.p, a2);
@@ -1054,7 +1099,8 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
   // (k_conv2_h writes the two zero channels of each chunk itself); rows of the image tile beyond n keep the last
   // call's values and only feed accumulator columns that are never stored.
   const unsigned m = (unsigned)n;
-  k_conv1_tc<true><<<m, kC1Threads, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p, reinterpret_cast<float4*>(a1), L.a1_scale);
+  k_conv1_tc<true><<<std::min(m, (unsigned)c->sm_count), kC1Threads, C1_SMEM_BYTES, st>>>(d_images, L.c1w_tc.p, L.c1b.p,
+                                                                                        reinterpret_cast<float4*>(a1), L.a1_scale, (int)m);
   AG2_LAUNCH_CHECK(c);
   k_conv2_h<true><<<std::min(m, (unsigned)c->sm_count), 192, H_SMEM_BYTES, st>>>(reinterpret_cast<const uint4*>(a1), L.c2w_h.p, L.c2b.p,
                                                                                L.c2_inv_scale, a2, (int)m);
