@@ -42,6 +42,8 @@ namespace {
 constexpr int kHandThreads = 384;
 constexpr int kMaxRows = 1024;
 constexpr int kCand = 4;  // consecutive candidates per thread per fill batch
+constexpr uint32_t kFillBatch = 32u * kCand;  // candidates per warp and fill batch
+constexpr int kBatchRows = 1024;  // batches whose first cell row is tabulated (neighbourhoods up to 131 072 candidates)
 constexpr int kMaxDepths = AG2_MAX_DEEPEN_STEPS + 2;
 
 struct HandsArgs {
@@ -106,6 +108,7 @@ struct Fixed {
   double bottom[kMaxDepths];
   uint32_t row_prefix[kMaxRows + 1];
   uint32_t row_begin[kMaxRows];
+  uint16_t batch_row[kBatchRows];  // cell row that holds the first candidate of fill batch b
   uint32_t nkept, total_cand, cursor, pool_ok, nrows, next_batch;
   unsigned long long sumK, sumKc;
 };

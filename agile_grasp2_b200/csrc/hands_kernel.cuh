@@ -60,6 +60,21 @@ __device__ void setup_rows(Fixed& sh, const GridDev& g, const float q[3], float 
     if (tid == 31) sh.total_cand = run;
   }
   __syncthreads();
+  // first cell row of every fill batch: one search per BATCH here instead of one per thread and batch in fill_chunk
+  {
+    const uint32_t T = sh.total_cand;
+    const uint32_t nb = min((uint32_t)kBatchRows, (T + kFillBatch - 1) / kFillBatch);
+    for (uint32_t b = tid; b < nb; b += kHandThreads) {
+      const uint32_t tb = b * kFillBatch;
+      int lo = 0, hi = (int)sh.nrows;  // prefix[lo] <= tb < prefix[hi]
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (sh.row_prefix[mid] <= tb) lo = mid; else hi = mid;
+      }
+      sh.batch_row[b] = (uint16_t)lo;
+    }
+  }
+  __syncthreads();
 }
 
 // Stages the next chunk of cropped neighbours, starting at candidate sh.cursor (a multiple of the batch size, or
@@ -68,11 +83,12 @@ __device__ void setup_rows(Fixed& sh, const GridDev& g, const float q[3], float 
 // adding) fits the staging buffer: the LAST batch ever taken saw nkept + kInFlight <= cap, and what was not yet
 // counted in that nkept is at most one batch per warp, so the buffer cannot overflow; a refused warp stops, and
 // since nkept only grows every later request is refused too: the batches taken are a prefix of the sequence.
-// Each thread takes kCand CONSECUTIVE candidates: one binary search over the row prefix, then sequential row advance.
+// Each thread takes kCand CONSECUTIVE candidates: its batch's first row from the table of setup_rows, a short walk to
+// its own row, then sequential row advance.
 __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const HandConst& hc,
                            const float q[3], bool count_stats, int tid) {
   const int lane = tid & 31;
-  constexpr uint32_t kBatch = 32u * kCand;
+  constexpr uint32_t kBatch = kFillBatch;
   constexpr uint32_t kInFlight = (kHandThreads / 32) * kBatch;
   const uint32_t T = sh.total_cand;
   if (tid == 0) {
@@ -95,10 +111,17 @@ __device__ void fill_chunk(Fixed& sh, float4* cache, const HandsArgs& A, const H
     int row = 0;
     uint32_t row_end = 0, pos = 0;
     if (tb < T) {
-      int lo = 0, hi = (int)sh.nrows;  // prefix[lo] <= tb < prefix[hi]
-      while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (sh.row_prefix[mid] <= tb) lo = mid; else hi = mid;
+      int lo;
+      if (batch < (uint32_t)kBatchRows) {  // the batch's first row is tabulated: a lane walks the few rows to its own
+        lo = sh.batch_row[batch];
+        while (sh.row_prefix[lo + 1] <= tb) lo++;
+      } else {
+        int hi = (int)sh.nrows;  // prefix[lo] <= tb < prefix[hi]
+        lo = 0;
+        while (hi - lo > 1) {
+          int mid = (lo + hi) >> 1;
+          if (sh.row_prefix[mid] <= tb) lo = mid; else hi = mid;
+        }
       }
       row = lo;
       row_end = sh.row_prefix[row + 1];
