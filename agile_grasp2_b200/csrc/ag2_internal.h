@@ -126,10 +126,12 @@ struct LeNetDev {
   bool loaded = false;
   DevBuf<float> c1w, c1b, c2w, c2b, i1w, i1b, i2w, i2b;
   DevBuf<float> c1w_tc;  // conv1 weights split into tf32 terms, two taps per K step
-  DevBuf<float> i1w_tc;  // ip1 weights, same treatment, per K step and 128-output tile
+  DevBuf<float> i1w_tc;  // ip1 weights scaled, split into fp16 terms, per K step and 128-output tile (raw bytes)
   DevBuf<uint16_t> c2w_h;  // conv2 weights scaled, split into fp16 terms and tiled per K step (k_conv2_h)
   float a1_scale = 1.f;      // power of two applied to the pooled conv1 activations before their fp16 split
   float c2_inv_scale = 1.f;  // 1 / (a1_scale * conv2 weight scale)
+  float a2_scale = 1.f;      // power of two applied to the pooled conv2 activations before their fp16 split (ip1's operand)
+  float i1_inv_scale = 1.f;  // 1 / (a2_scale * ip1 weight scale)
   std::vector<float> host[8];
 };
 

@@ -5,7 +5,7 @@
 //   conv1 20@5x5 -> maxpool 2/2 -> conv2 50@5x5 -> maxpool 2/2 -> ip1 500 -> ReLU -> ip2 2
 // and returns the raw ip2 logits (caffe_classifier.cpp:121-126).
 // conv1, conv2 and ip1 run on the tensor cores (k_conv1_tc, k_conv2_h, k_ip1_tc: tcgen05 MMA,
-// tf32 (conv1, ip1) or fp16 (conv2) operands split into hi + lo terms for fp32 accuracy, accumulators in tensor memory; PTX
+// tf32 (conv1) or fp16 (conv2, ip1) operands split into hi + lo terms for fp32 accuracy, accumulators in tensor memory; PTX
 // wrappers in tc_ptx.cuh), pooling / bias fused into the epilogues; k_ip2 finishes the split-K
 // sum, bias, ReLU and the 500 -> 2 product.  The fp32 CUDA-core kernels of the first version
 // (k_conv1_pool, k_conv2_pool, k_ip1_partial) are kept as an independent cross-check
@@ -367,9 +367,9 @@ k_conv1_tc(const uint8_t* __restrict__ images, const float* __restrict__ wtc /* 
   if (warp == 1) tc::tmem_dealloc<512>(tmem);
 }
 
-// ip1 on the tensor cores (k_ip1_tc) reduces over K' = 144 positions x 52 channels (50 + 2 zero) =
-// 936 steps of 8, in chunks of 4 channels
-constexpr int I1_KSTEPS = 936, I1_CHUNKS = 2 * I1_KSTEPS;
+// ip1 on the tensor cores (k_ip1_tc, fp16 split operands) reduces over K' = 144 positions x 56 channels (50 + 6 zero) =
+// 504 steps of 16, in chunks of 8 channels
+constexpr int I1_KSTEPS = 504, I1_CHUNKS = 2 * I1_KSTEPS;
 
 // ---------------------------------------------------------------------------------------------
 // conv2 on fp16 operands (kind::f16, K = 16 per MMA): the zero-copy implicit GEMM described above
@@ -420,7 +420,8 @@ __constant__ HStepTable c_hsteps = make_hsteps();
 template <bool TILED_OUT>
 __global__ void __launch_bounds__(192, 1)
 k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const uint16_t* __restrict__ wh /* [10 items][16 KB] */,
-          const float* __restrict__ bias, float inv_scale, float* __restrict__ out, int n) {
+          const float* __restrict__ bias, float inv_scale, float out_scale /* TILED_OUT: fp16 scale of the ip1 operand */,
+          float* __restrict__ out, int n) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
   uint8_t* A = tc_smem;
   uint8_t* Bring = tc_smem + 2 * H_IMG_BYTES;
@@ -571,20 +572,23 @@ k_conv2_h(const uint4* __restrict__ in /* [n][6 planes][784] x 8 halfs */, const
               for (int ch = 0; ch < C2_OUT; ch++)
                 if ((ch & 3) == q) o[(ch * P2 + py) * P2 + px] = v[ch];
             } else {
-              // [image tile of 128][chunk = pos*13 + ch/4][hi, lo][image row][4 channels]; channels 50, 51 are zero
-              v[50] = v[51] = 0.f;
-              float4* o = reinterpret_cast<float4*>(out) +
-                          ((size_t)(img >> 7) * I1_CHUNKS + (size_t)(py * P2 + px) * 13) * 256 + (img & 127);
+              // [image tile of 128][chunk = pos*7 + ch/8][hi, lo][image row][8 channels as fp16]; channels 50..55 are zero
+              uint4* o = reinterpret_cast<uint4*>(out) +
+                         ((size_t)(img >> 7) * I1_CHUNKS + (size_t)(py * P2 + px) * 7) * 256 + (img & 127);
 #pragma unroll
-              for (int cq = 0; cq < 13; cq++)
+              for (int cq = 0; cq < 7; cq++)
                 if ((cq & 3) == q) {
-                  float4 h, l;
-                  tc::split_tf32(v[4 * cq], h.x, l.x);
-                  tc::split_tf32(v[4 * cq + 1], h.y, l.y);
-                  tc::split_tf32(v[4 * cq + 2], h.z, l.z);
-                  tc::split_tf32(v[4 * cq + 3], h.w, l.w);
-                  o[cq * 256] = h;
-                  o[cq * 256 + 128] = l;
+                  uint32_t hw[4], lw[4];
+#pragma unroll
+                  for (int e = 0; e < 4; e++) {
+                    uint16_t h0 = 0, l0 = 0, h1 = 0, l1 = 0;
+                    if (8 * cq + 2 * e < C2_OUT) tc::split_f16(v[(8 * cq + 2 * e) % 64] * out_scale, h0, l0);
+                    if (8 * cq + 2 * e + 1 < C2_OUT) tc::split_f16(v[(8 * cq + 2 * e + 1) % 64] * out_scale, h1, l1);
+                    hw[e] = (uint32_t)h0 | ((uint32_t)h1 << 16);
+                    lw[e] = (uint32_t)l0 | ((uint32_t)l1 << 16);
+                  }
+                  o[cq * 256] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                  o[cq * 256 + 128] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
                 }
             }
           }
@@ -625,15 +629,15 @@ __global__ void k_split_a1(const float4* __restrict__ a1, uint4* __restrict__ a1
 }
 
 // ---------------------------------------------------------------------------------------------
-// ip1 (7200 -> 500) on the tensor cores, split-K.  CTA (it, z) computes, for the 128 images of
-// tile `it` and the K' steps [z*steps, (z+1)*steps), the partial products of ALL 500 outputs:
+// ip1 (7200 -> 500) on the tensor cores (kind::f16, fp16 split operands like conv2), split-K.  CTA (it, z) computes,
+// for the 128 images of tile `it` and the K' steps [z*steps, (z+1)*steps), the partial products of ALL 500 outputs:
 //   D[out][image] (4 M tiles of 128 x N = 128, the whole 512-column tensor memory)
-// A = the weights, B = the pooled conv2 activations, both already split into tf32 hi / lo
+// A = the weights, B = the pooled conv2 activations, both scaled by a power of two, split into fp16 hi / lo
 // terms and stored in the canonical no-swizzle K-major tiles (weights by lenet_upload,
-// activations by k_conv2_h's epilogue), so one K step is two plain bulk copies (32 KB + 8 KB)
+// activations by k_conv2_h's epilogue), so one K step of 16 is two plain bulk copies (32 KB + 8 KB)
 // and 12 MMAs (4 M tiles x the three-term split); no thread touches the operands.  A 5-stage
 // ring keeps 4 steps of copies in flight.  Partials go to part[z][image][500] and are summed
-// in a fixed order by k_ip2 (deterministic).
+// in a fixed order, multiplied by the inverse scale, by k_ip2 (deterministic).
 // ---------------------------------------------------------------------------------------------
 constexpr int I1_A_BYTES = 2 * 4 * 2 * 128 * 16;  // [hi/lo][M tile][chunk][128 rows][16 B] = 32768
 constexpr int I1_B_BYTES = 2 * 2 * 128 * 16;      // [chunk][hi/lo][128 images][16 B] = 8192
@@ -665,7 +669,7 @@ k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_h */, const float* 
 
   if (warp == 0) {
     const bool leader = tc::elect_one();
-    const uint32_t idesc = tc::idesc_tf32(128, 128);
+    const uint32_t idesc = tc::idesc_f16(128, 128);
     const uint32_t s_base = tc::smem_u32(tc_smem);
     const float* srcA = wtc + (size_t)z * steps * (I1_A_BYTES / 4);
     const float* srcB = act + ((size_t)it * I1_CHUNKS + (size_t)2 * z * steps) * 1024;
@@ -692,7 +696,7 @@ k_ip1_tc(const float* __restrict__ act /* tiled, see k_conv2_h */, const float* 
           const uint64_t b_desc = b_hi64 | (uint64_t)(sb + pb * 128);
 #pragma unroll
           for (int mt = 0; mt < 4; mt++)
-            tc::mma_tf32(tmem + mt * 128, a_hi64 | (uint64_t)(sa + ((pa * 4 + mt) * 2) * 128), b_desc, idesc,
+            tc::mma_f16(tmem + mt * 128, a_hi64 | (uint64_t)(sa + ((pa * 4 + mt) * 2) * 128), b_desc, idesc,
                          (i | (combo - 1)) != 0);
         }
         tc::mma_commit(&empty[slot]);
@@ -793,8 +797,8 @@ k_ip1_partial(const float* __restrict__ X, const float* __restrict__ W, float* _
 // split-K reduction + ip1 bias + ReLU + ip2: logits[n][2]; one CTA of 128 threads per image, the
 // partials of one output are summed in split order, the 500 products in a fixed tree (deterministic)
 __global__ void __launch_bounds__(128)
-k_ip2(const float* __restrict__ part, int splits, const float* __restrict__ b1, const float* __restrict__ W,
-      const float* __restrict__ b, float* __restrict__ logits, int n) {
+k_ip2(const float* __restrict__ part, int splits, float part_scale /* 1, or the inverse of ip1's fp16 operand scales */,
+      const float* __restrict__ b1, const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ logits, int n) {
   __shared__ float red[2][4];
   const int img = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   float a0 = 0.f, a1 = 0.f;
@@ -803,7 +807,7 @@ k_ip2(const float* __restrict__ part, int splits, const float* __restrict__ b1, 
     float h = 0.f;
 #pragma unroll 13
     for (int z = 0; z < splits; z++) h += p[(size_t)z * n * IP1_OUT];
-    h = fmaxf(h + b1[k], 0.f);
+    h = fmaxf(h * part_scale + b1[k], 0.f);
     a0 += W[k] * h;
     a1 += W[IP1_OUT + k] * h;
   }
@@ -889,31 +893,59 @@ int lenet_upload(ag2_ctx* c) {
     AG2_CUDA(c, cudaMemcpyAsync(L.c1w_tc.p, w0.data(), w0.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   }
-  // ip1 weights for k_ip1_tc: [k step][hi/lo][M tile][chunk][128 outputs][4]; K' index
-  // k' = 8*step + 4*chunk + e = position*52 + channel (channels 50, 51 and outputs >= 500 are zero)
+  // ip1 for k_ip1_tc.  Its activations (pooled conv2 outputs) are bounded by sum|w2| * (conv1 bound) + |b2|; as for
+  // conv2 a power of two brings that bound, and the largest ip1 weight, to at most 2^15 before the fp16 split.
+  // Weights: [k step][hi/lo][M tile][chunk][128 outputs][8 halfs]; K' index k' = 16*step + 8*chunk + e = position*56 +
+  // channel (channels 50..55 and outputs >= 500 are zero)
   {
-    std::vector<float> w1((size_t)I1_KSTEPS * (I1_A_BYTES / 4), 0.f);
+    double bound1 = 1e-30, bound2 = 1e-30, wmax = 1e-30;
+    for (int oc = 0; oc < C1_OUT; oc++) {
+      double sa = fabs((double)L.host[1][oc]);
+      for (int k = 0; k < 75; k++) sa += 255.0 * fabs((double)L.host[0][(size_t)oc * 75 + k]);
+      bound1 = std::max(bound1, sa);
+    }
+    for (int oc = 0; oc < C2_OUT; oc++) {
+      double sa = 0.0;
+      for (int k = 0; k < 500; k++) sa += fabs((double)L.host[2][(size_t)oc * 500 + k]);
+      bound2 = std::max(bound2, sa * bound1 + fabs((double)L.host[3][oc]));
+    }
     const std::vector<float>& W = L.host[4];
+    for (float w : W) wmax = std::max(wmax, fabs((double)w));
+    if (!std::isfinite(bound2) || !std::isfinite(wmax)) return AG2_E_INVALID;
+    auto pow2_to = [](double x) { return std::min(60, std::max(-60, (int)floor(log2(32768.0 / x)))); };
+    const int ea = pow2_to(bound2), ew = pow2_to(wmax);
+    L.a2_scale = ldexpf(1.f, ea);
+    L.i1_inv_scale = ldexpf(1.f, -(ea + ew));
+    const float w_scale = ldexpf(1.f, ew);
+    std::vector<uint16_t> w1((size_t)I1_KSTEPS * (I1_A_BYTES / 2), 0);
     for (int ks = 0; ks < I1_KSTEPS; ks++)
       for (int ck = 0; ck < 2; ck++)
-        for (int e = 0; e < 4; e++) {
-          const int kk = 8 * ks + 4 * ck + e, pos = kk / 52, ch = kk % 52;
+        for (int e = 0; e < 8; e++) {
+          const int kk = 16 * ks + 8 * ck + e, pos = kk / 56, ch = kk % 56;
           if (ch >= C2_OUT) continue;
           for (int o = 0; o < IP1_OUT; o++) {
-            float hi, lo;
-            tc::split_tf32(W[(size_t)o * 7200 + ch * 144 + pos], hi, lo);
-            const size_t base = (size_t)ks * (I1_A_BYTES / 4) + ((size_t)((o >> 7) * 2 + ck) * 128 + (o & 127)) * 4 + e;
+            uint16_t hi, lo;
+            tc::split_f16(W[(size_t)o * 7200 + ch * 144 + pos] * w_scale, hi, lo);
+            const size_t base = (size_t)ks * (I1_A_BYTES / 2) + ((size_t)((o >> 7) * 2 + ck) * 128 + (o & 127)) * 8 + e;
             w1[base] = hi;
-            w1[base + 4 * 2 * 128 * 4] = lo;
+            w1[base + 4 * 2 * 128 * 8] = lo;
           }
         }
-    AG2_CUDA(c, L.i1w_tc.reserve(w1.size()));
-    AG2_CUDA(c, cudaMemcpyAsync(L.i1w_tc.p, w1.data(), w1.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    AG2_CUDA(c, L.i1w_tc.reserve(w1.size() / 2));
+    AG2_CUDA(c, cudaMemcpyAsync(L.i1w_tc.p, w1.data(), w1.size() * sizeof(uint16_t), cudaMemcpyHostToDevice, c->stream));
     AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   }
   AG2_CUDA(c, cudaStreamSynchronize(c->stream));
   L.loaded = true;
   return AG2_OK;
+}
+
+// K splits of ip1: the largest divisor of its 504 K' steps that keeps tiles x splits within one wave of CTAs
+static int ip1_splits(int itiles, int sm_count) {
+  static const int divs[] = {126, 84, 72, 63, 56, 42, 36, 28, 24, 21};
+  for (int d : divs)
+    if ((long)d * itiles <= sm_count) return d;
+  return 21;
 }
 
 // dynamic shared-memory limits of the tensor-core kernels (per device; cheap enough to repeat per call)
@@ -946,17 +978,11 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
     splits = (450 + steps_per_split - 1) / steps_per_split;
     a2_floats = chunk * 50 * P2 * P2;
   } else {
-    // A divisor of the 936 K' steps: as many splits as fit one wave of CTAs, but never fewer than
-    // 39 (<= 24 steps = 72 MMAs per accumulator).  The tensor core truncates when it adds into
+    // A divisor of the 504 K' steps: as many splits as fit one wave of CTAs, but never fewer than
+    // 21 (<= 24 steps = 72 MMAs per accumulator).  The tensor core truncates when it adds into
     // the fp32 accumulator, a bias of ~4e-8 relative per MMA that grows linearly with the chain;
     // across splits the partials are summed with round-to-nearest by k_ip2.
-    static const int divs[] = {117, 104, 78, 72, 52, 39};
-    splits = 39;
-    for (int d : divs)
-      if ((long)d * itiles <= c->sm_count) {
-        splits = d;
-        break;
-      }
+    splits = ip1_splits(itiles, c->sm_count);
     steps_per_split = I1_KSTEPS / splits;
     a2_floats = (size_t)itiles * I1_CHUNKS * 1024;
   }
@@ -985,9 +1011,9 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
       k_split_a1<<<(unsigned)((m * 3 * TC_PIX + 255) / 256), 256, 0, st>>>(reinterpret_cast<const float4*>(a1), a1h, L.a1_scale,
                                                                           m * TC_PIX);
       AG2_LAUNCH_CHECK(c);
-      k_conv2_h<false><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, a2, (int)m);
+      k_conv2_h<false><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, 1.f, a2, (int)m);
     } else {
-      k_conv2_h<true><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, a2, (int)m);
+      k_conv2_h<true><<<g2, 192, H_SMEM_BYTES, st>>>(a1h, L.c2w_h.p, L.c2b.p, L.c2_inv_scale, L.a2_scale, a2, (int)m);
     }
     AG2_LAUNCH_CHECK(c);
     if (simt) {
@@ -998,8 +1024,8 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
       k_ip1_tc<<<g1, 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
     }
     AG2_LAUNCH_CHECK(c);
-    k_ip2<<<(unsigned)m, 128, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p,
-                                                            d_logits + 2 * off, (int)m);
+    k_ip2<<<(unsigned)m, 128, 0, st>>>(part, splits, simt ? 1.f : L.i1_inv_scale, L.i1b.p, L.i2w.p, L.i2b.p, d_logits + 2 * off,
+                                       (int)m);
     AG2_LAUNCH_CHECK(c);
   }
   return AG2_OK;
@@ -1021,13 +1047,13 @@ int classify_compute(ag2_ctx* c) {
 // planes, tiled conv2 output, split-K partials of ip1) live in ONE file-scope device array of fixed
 // size instead of the ctx's growing buffer; images and logits are the caller's device buffers.
 // The kernels, their launch shapes and the split-K choice are those of lenet_forward, so the logits
-// are the same bits.  Every GPU that loads libag2.so holds the array (about 27.5 MB) until exit.
+// are the same bits.  Every GPU that loads libag2.so holds the array (about 25.1 MB) until exit.
 // ---------------------------------------------------------------------------------------------
 }  // namespace ag2
 
 #define AG2_STATIC_A1_FLOATS ((size_t)AG2_CLASSIFY_STATIC_MAX_IMAGES * 6 * 784 * 4) /* pooled conv1 planes, fp16 hi + lo */
-#define AG2_STATIC_A2_FLOATS ((size_t)2 * 936 * 1024)                                /* one tile of 128 images, tiled for ip1 */
-#define AG2_STATIC_PART_FLOATS ((size_t)117 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)  /* at most 117 K splits */
+#define AG2_STATIC_A2_FLOATS ((size_t)2 * 504 * 1024)                                /* one tile of 128 images, tiled for ip1 */
+#define AG2_STATIC_PART_FLOATS ((size_t)126 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)  /* at most 126 K splits */
 #define AG2_STATIC_FLOATS (AG2_STATIC_A1_FLOATS + AG2_STATIC_A2_FLOATS + AG2_STATIC_PART_FLOATS)
 
 static __device__ __align__(256) float g_classify_static_scratch[AG2_STATIC_FLOATS];
@@ -1083,14 +1109,7 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
   AG2_TRY(static_scratch_setup(c, &scratch));
   const LeNetDev& L = c->net;
   cudaStream_t st = c->stream;
-  // lenet_forward's split choice for one tile of images: the largest divisor of the 936 K' steps that fits one wave
-  static const int divs[] = {117, 104, 78, 72, 52, 39};
-  int splits = 39;
-  for (int d : divs)
-    if (d <= c->sm_count) {
-      splits = d;
-      break;
-    }
+  const int splits = ip1_splits(1, c->sm_count);  // lenet_forward's choice for one tile of images
   const int steps_per_split = I1_KSTEPS / splits;
   float* a1 = scratch;
   float* a2 = a1 + AG2_STATIC_A1_FLOATS;
@@ -1103,11 +1122,11 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
                                                                                         reinterpret_cast<float4*>(a1), L.a1_scale, (int)m);
   AG2_LAUNCH_CHECK(c);
   k_conv2_h<true><<<std::min(m, (unsigned)c->sm_count), 192, H_SMEM_BYTES, st>>>(reinterpret_cast<const uint4*>(a1), L.c2w_h.p, L.c2b.p,
-                                                                               L.c2_inv_scale, a2, (int)m);
+                                                                               L.c2_inv_scale, L.a2_scale, a2, (int)m);
   AG2_LAUNCH_CHECK(c);
   k_ip1_tc<<<dim3(1, splits), 256, I1_SMEM_BYTES, st>>>(a2, L.i1w_tc.p, part, (int)m, steps_per_split);
   AG2_LAUNCH_CHECK(c);
-  k_ip2<<<m, 128, 0, st>>>(part, splits, L.i1b.p, L.i2w.p, L.i2b.p, d_logits, (int)m);
+  k_ip2<<<m, 128, 0, st>>>(part, splits, L.i1_inv_scale, L.i1b.p, L.i2w.p, L.i2b.p, d_logits, (int)m);
   AG2_LAUNCH_CHECK(c);
   return AG2_OK;
 }
