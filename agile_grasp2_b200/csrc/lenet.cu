@@ -940,13 +940,12 @@ int lenet_upload(ag2_ctx* c) {
   return AG2_OK;
 }
 
-// K splits of ip1: the largest divisor of its 504 K' steps that keeps tiles x splits within one wave of CTAs
-static int ip1_splits(int itiles, int sm_count) {
-  static const int divs[] = {126, 84, 72, 63, 56, 42, 36, 28, 24, 21};
-  for (int d : divs)
-    if ((long)d * itiles <= sm_count) return d;
-  return 21;
-}
+// K splits of ip1: 21 x 24 steps, whatever the batch.  The split fixes the order of the fp32 sums, so it must not
+// depend on how many images a call holds: a hand's score is then the same bits on one GPU and on a rank's share of
+// the samples (bench.py's sharded_equals_single).  24 steps = 72 MMAs per accumulator bounds the truncation bias of
+// the tensor core's accumulate; even one tile of images still gives 21 CTAs of ~10 us.
+constexpr int kIp1Splits = 21;
+static_assert(I1_KSTEPS % kIp1Splits == 0, "whole K steps per split");
 
 // dynamic shared-memory limits of the tensor-core kernels (per device; cheap enough to repeat per call)
 static int lenet_attributes(ag2_ctx* c) {
@@ -978,11 +977,7 @@ int lenet_forward(ag2_ctx* c, const uint8_t* d_images, size_t n, float* d_logits
     splits = (450 + steps_per_split - 1) / steps_per_split;
     a2_floats = chunk * 50 * P2 * P2;
   } else {
-    // A divisor of the 504 K' steps: as many splits as fit one wave of CTAs, but never fewer than
-    // 21 (<= 24 steps = 72 MMAs per accumulator).  The tensor core truncates when it adds into
-    // the fp32 accumulator, a bias of ~4e-8 relative per MMA that grows linearly with the chain;
-    // across splits the partials are summed with round-to-nearest by k_ip2.
-    splits = ip1_splits(itiles, c->sm_count);
+    splits = kIp1Splits;
     steps_per_split = I1_KSTEPS / splits;
     a2_floats = (size_t)itiles * I1_CHUNKS * 1024;
   }
@@ -1047,13 +1042,13 @@ int classify_compute(ag2_ctx* c) {
 // planes, tiled conv2 output, split-K partials of ip1) live in ONE file-scope device array of fixed
 // size instead of the ctx's growing buffer; images and logits are the caller's device buffers.
 // The kernels, their launch shapes and the split-K choice are those of lenet_forward, so the logits
-// are the same bits.  Every GPU that loads libag2.so holds the array (about 25.1 MB) until exit.
+// are the same bits.  Every GPU that loads libag2.so holds the array (about 11.6 MB) until exit.
 // ---------------------------------------------------------------------------------------------
 }  // namespace ag2
 
 #define AG2_STATIC_A1_FLOATS ((size_t)AG2_CLASSIFY_STATIC_MAX_IMAGES * 6 * 784 * 4) /* pooled conv1 planes, fp16 hi + lo */
 #define AG2_STATIC_A2_FLOATS ((size_t)2 * 504 * 1024)                                /* one tile of 128 images, tiled for ip1 */
-#define AG2_STATIC_PART_FLOATS ((size_t)126 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)  /* at most 126 K splits */
+#define AG2_STATIC_PART_FLOATS ((size_t)21 * AG2_CLASSIFY_STATIC_MAX_IMAGES * 500)   /* kIp1Splits partials */
 #define AG2_STATIC_FLOATS (AG2_STATIC_A1_FLOATS + AG2_STATIC_A2_FLOATS + AG2_STATIC_PART_FLOATS)
 
 static __device__ __align__(256) float g_classify_static_scratch[AG2_STATIC_FLOATS];
@@ -1109,7 +1104,7 @@ extern "C" int ag2_classify_images_static(ag2_ctx* c, const uint8_t* d_images, s
   AG2_TRY(static_scratch_setup(c, &scratch));
   const LeNetDev& L = c->net;
   cudaStream_t st = c->stream;
-  const int splits = ip1_splits(1, c->sm_count);  // lenet_forward's choice for one tile of images
+  const int splits = kIp1Splits;
   const int steps_per_split = I1_KSTEPS / splits;
   float* a1 = scratch;
   float* a2 = a1 + AG2_STATIC_A1_FLOATS;

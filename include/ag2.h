@@ -367,7 +367,7 @@ int ag2_classify_images(ag2_ctx* ctx, const uint8_t* images, size_t n, float* lo
  * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
  * d_images (n x 10800 bytes, HWC u8) and d_logits (2 floats per image) are
  * DEVICE buffers of the ctx's GPU, owned by the caller; the activations live in a fixed array inside
- * libag2.so (about 25.1 MB, held by every GPU that loads the library until exit), so the call makes
+ * libag2.so (about 11.6 MB, held by every GPU that loads the library until exit), so the call makes
  * no cudaMalloc / cudaFree and at most AG2_CLASSIFY_STATIC_MAX_IMAGES images go in one call
  * (more: AG2_E_CAPACITY, nothing launched).  The kernels are enqueued on the ctx stream and the call
  * returns without waiting: the logits are ready after ag2_synchronize, or for work ordered behind

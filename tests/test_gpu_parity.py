@@ -183,6 +183,9 @@ def test_classify_images_batch_sizes(n):
     for r in range(43, n, 43):
         m = min(43, n - r)
         assert np.array_equal(gl[r:r + m], gl[:m]), r
+    # ... and whatever the batch they arrive in (a rank's share of the samples holds other images than the whole list)
+    alone = g.classify_images(base[:min(n, 7)])
+    assert np.array_equal(alone.view(np.uint32), gl[:len(alone)].view(np.uint32))
 
 
 def test_sample_points_and_precomputed_normals(tiny_scene):
