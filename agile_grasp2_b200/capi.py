@@ -488,6 +488,10 @@ class Context:
                    C.c_int(1 if aligns else 0), _fptr(out))
         return out[:n]
 
+    def set_min_inliers(self, min_inliers: int):
+        """HandleSearch::setMinInliers: the cluster threshold alone, without invalidating the lists."""
+        self._call("set_min_inliers", C.c_int(min_inliers))
+
     def find_clusters(self, which_src: int):
         """HandleSearch::findClusters on list `which_src`; result in LIST_CLUSTERS."""
         self._call("find_clusters", C.c_int(which_src))

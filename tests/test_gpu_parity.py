@@ -406,6 +406,28 @@ def test_find_clusters(dense_scene):
         assert np.allclose(gc[f], oc[f], rtol=0, atol=1e-9), f
 
 
+def test_set_min_inliers_changes_the_threshold_of_the_next_clustering(dense_scene):
+    """HandleSearch::setMinInliers (handle_search.h:83-86) through ag2_set_min_inliers: the lists of the last call stay,
+    the next findClusters uses the new threshold -- the same clusters as a context created with that threshold."""
+    a = capi.Context(make_params(capi.MODE_NONE, min_inliers=1))
+    b = capi.Context(make_params(capi.MODE_NONE, min_inliers=3))
+    for c in (a, b):
+        c.set_cloud(dense_scene["xyz"], dense_scene["cam_mask"], dense_scene["num_cams"])
+        c.set_sample_indices(dense_scene["samples"])
+        c.detect()
+    a.find_clusters(capi.LIST_HYPOTHESES)
+    loose = a.hypotheses(capi.LIST_CLUSTERS)
+    a.set_min_inliers(3)
+    assert a.num(capi.LIST_HYPOTHESES) == b.num(capi.LIST_HYPOTHESES) > 0  # nothing was invalidated
+    a.find_clusters(capi.LIST_HYPOTHESES)
+    b.find_clusters(capi.LIST_HYPOTHESES)
+    ga, gb = a.hypotheses(capi.LIST_CLUSTERS), b.hypotheses(capi.LIST_CLUSTERS)
+    assert len(ga) == len(gb) and ga.tobytes() == gb.tobytes()
+    assert len(ga) < len(loose)
+    with pytest.raises(capi.Ag2Error):
+        a.set_min_inliers(-1)
+
+
 def test_detect_with_clustering(dense_scene):
     """grasp_detector.cpp:229-252: clusters of the accepted hands, then top-k over the clusters."""
     w = ob.xavier_weights(3, bias_scale=0.5)
