@@ -1785,6 +1785,15 @@ int ag2o_classify_images(ag2o_ctx* c, const uint8_t* images, size_t n, float* lo
   return AG2_OK;
 }
 
+// test hooks: the exactly reproducible log / cos / normal draw of include/ag2_detmath.h (deviation D5), n values each
+int ag2o_detmath(const double* u1, const double* u2, size_t n, double* log_u1, double* cos2pi_u2, double* normal) {
+  for (size_t i = 0; i < n; i++) {
+    log_u1[i] = ag2_det_log(u1[i]);
+    cos2pi_u2[i] = ag2_det_cos2pi(u2[i]);
+    normal[i] = ag2_det_normal(u1[i], u2[i]);
+  }
+  return AG2_OK;
+}
 int ag2o_eigen33(const float* cov9, float* eigenvalue, float* ev3) {
   eigen33(cov9, *eigenvalue, ev3);
   return AG2_OK;

@@ -88,6 +88,16 @@ def point_normals(ctx: capi.Context, idx) -> np.ndarray:
     return out
 
 
+def detmath(u1: np.ndarray, u2: np.ndarray):
+    """(log(u1), cos(2 pi u2), Box-Muller normal) from include/ag2_detmath.h as compiled into the oracle."""
+    u1 = np.ascontiguousarray(u1, dtype=np.float64)
+    u2 = np.ascontiguousarray(u2, dtype=np.float64)
+    out = [np.zeros(len(u1)) for _ in range(3)]
+    load().lib.ag2o_detmath(u1.ctypes.data_as(C.c_void_p), u2.ctypes.data_as(C.c_void_p), C.c_size_t(len(u1)),
+                            *[o.ctypes.data_as(C.c_void_p) for o in out])
+    return out
+
+
 def eigen33(cov: np.ndarray):
     cov = np.ascontiguousarray(cov, dtype=np.float32).reshape(9)
     val = C.c_float()

@@ -415,3 +415,25 @@ def test_eigen33_vs_numpy_at_the_normals_tolerance():
         assert abs(val - w[0]) <= 1e-6 * w[2]
         assert ang <= 1e-3, (ang, sep)
     assert 1e-5 < worst  # the closed form is NOT exact: documents why the bound is not 1e-4
+
+
+def test_reproducible_log_and_cos_of_the_sampler_vs_numpy():
+    """include/ag2_detmath.h (deviation D5): log and cos(2 pi u) as fixed sequences of correctly rounded double
+    operations, compiled into the oracle and into the device sampler.  Pinned here against numpy's libm: a few ulp,
+    which is all Box-Muller needs; the bit-equality of GPU and oracle draws is tested on the GPU."""
+    rng = np.random.default_rng(5)
+    u1 = np.concatenate([rng.random(200000), 2.0 ** -rng.integers(1, 53, 2000), [1.0 - 2.0 ** -53, 0.5, 2.0 ** -53]])
+    u1 = u1[u1 > 0]
+    u2 = np.concatenate([rng.random(len(u1) - 9), [0.0, 0.125, 0.25, 0.375, 0.5, 0.625, 0.75, 0.875, 1.0 - 2.0 ** -53]])
+    lg, cs, nrm = ob.detmath(u1, u2)
+    ref_log = np.log(u1)
+    assert np.max(np.abs(lg - ref_log) / np.maximum(np.abs(ref_log), 1e-300)) < 2e-15
+    # cos(2 pi u) with the argument reduced exactly, as the header does (numpy's cos of a rounded 2 pi u is the worse one)
+    k = np.floor(4 * u2 + 0.5)
+    r = u2 - 0.25 * k
+    z = 2 * np.pi * r
+    ref_cos = np.where(k % 4 == 0, np.cos(z), np.where(k % 4 == 1, -np.sin(z), np.where(k % 4 == 2, -np.cos(z), np.sin(z))))
+    assert np.max(np.abs(cs - ref_cos)) < 2e-15
+    ref_n = np.sqrt(-2.0 * ref_log) * ref_cos
+    assert np.max(np.abs(nrm - ref_n)) < 1e-13
+    assert cs[len(u1) - 9] == 1.0 and abs(cs[len(u1) - 7]) < 1e-15 and cs[len(u1) - 5] == -1.0  # u = 0, 1/4, 1/2
