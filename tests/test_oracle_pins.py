@@ -437,3 +437,115 @@ def test_reproducible_log_and_cos_of_the_sampler_vs_numpy():
     ref_n = np.sqrt(-2.0 * ref_log) * ref_cos
     assert np.max(np.abs(nrm - ref_n)) < 1e-13
     assert cs[len(u1) - 9] == 1.0 and abs(cs[len(u1) - 7]) < 1e-15 and cs[len(u1) - 5] == -1.0  # u = 0, 1/4, 1/2
+
+
+def test_find_clusters_vs_numpy_restatement():
+    """HandleSearch::findClusters (handle_search.cpp:4-80, remove_inliers = false) restated in numpy from the reference
+    text, independently of the oracle's loops: same hands kept, same moved positions and mean scores."""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=700)
+    min_inliers = 2
+    o = ob.context(make_params(capi.MODE_NONE, min_inliers=min_inliers))
+    load_scene(o, sc)
+    o.detect()
+    hands = o.hypotheses(capi.LIST_HYPOTHESES)
+    assert len(hands) > 50
+    o.find_clusters(capi.LIST_HYPOTHESES)
+    got = o.hypotheses(capi.LIST_CLUSTERS)
+    axis, bottom, score = hands["axis"], hands["bottom"], hands["score"]
+    n = len(hands)
+    keep, moved, mean = [], [], []
+    cos_thresh = np.cos(15.0 * np.pi / 180.0)
+    for i in range(n):
+        aligned = np.abs(axis @ axis[i]) > cos_thresh
+        delta = bottom[i] - bottom                       # delta_pos = pos_i - pos_j
+        near = np.linalg.norm(delta, axis=1) <= 0.05
+        proj = delta - np.outer(delta @ axis[i], axis[i])  # (I - a a^T) delta
+        on_axis = np.linalg.norm(proj, axis=1) <= 0.005
+        inl = aligned & near & on_axis
+        inl[i] = False
+        k = int(inl.sum())
+        if k >= min_inliers:
+            keep.append(i)
+            moved.append(bottom[inl].sum(0) / k - bottom[i])
+            mean.append(score[inl].sum() / k)
+    assert 0 < len(keep) < n
+    assert len(got) == len(keep)
+    assert np.array_equal(got["sample_id"], hands["sample_id"][keep])
+    assert np.array_equal(got["orientation_id"], hands["orientation_id"][keep])
+    moved = np.array(moved)
+    for f in ("bottom", "surface", "top"):
+        assert np.allclose(got[f], hands[f][keep] + moved, rtol=0, atol=1e-12), f
+    assert np.allclose(got["score"], np.array(mean), rtol=0, atol=1e-12)
+    assert np.array_equal(got["axis"], hands["axis"][keep])
+
+
+def test_prune_vs_numpy_restatement():
+    """GraspDetector::pruneGraspsOnHandParameters (grasp_detector.cpp:363-395, called at :150-156 with the workspace as
+    FLOAT arguments and the cloud's minimum z) restated in numpy from the reference text."""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=700)
+    xyz = sc["xyz"]
+    lo, hi = xyz.min(0), xyz.max(0)
+    mid = 0.5 * (lo + hi)
+    p = make_params(capi.MODE_NONE)
+    ws = [float(lo[0] - 1.0), float(mid[0] + 0.02), float(mid[1] - 0.06), float(hi[1] + 1.0), -10.0, 10.0]  # cuts in x and y
+    for k in range(6):
+        p.workspace[k] = ws[k]
+    for filt in (1, 0):
+        p.filter_half_grasps = filt
+        o = ob.context(p)
+        load_scene(o, sc)
+        o.detect()
+        hands, got = o.hypotheses(capi.LIST_HYPOTHESES), o.hypotheses(capi.LIST_PRUNED)
+        half_width = 0.5 * p.hand_outer_diameter
+        corners = np.stack([hands["bottom"] + half_width * hands["binormal"], hands["bottom"] - half_width * hands["binormal"],
+                            hands["top"] + half_width * hands["binormal"], hands["top"] - half_width * hands["binormal"],
+                            hands["bottom"] - 0.10 * hands["approach"]], axis=1)  # hands x 5 x 3
+        mn, mx = corners.min(1), corners.max(1)
+        f32 = lambda v: float(np.float32(v))  # noqa: E731  (float parameters of the reference function)
+        min_z = float(xyz[:, 2].min())        # pcl::getMinMax3D of the processed cloud
+        keep = ((hands["width"] >= p.min_aperture) & (hands["width"] <= p.max_aperture) & (mn[:, 2] >= min_z) &
+                (mn[:, 1] >= f32(ws[2])) & (mx[:, 1] <= f32(ws[3])) & (mn[:, 0] >= f32(ws[0])) & (mx[:, 0] <= f32(ws[1])))
+        if filt:
+            keep &= hands["half_antipodal"] != 0
+        assert 0 < keep.sum() < len(hands), (filt, keep.sum(), len(hands))
+        assert len(got) == keep.sum()
+        assert np.array_equal(got["sample_id"], hands["sample_id"][keep])
+        assert np.array_equal(got["orientation_id"], hands["orientation_id"][keep])
+
+
+def test_antipodal_flags_vs_numpy_restatement():
+    """Antipodal::evaluateGrasp (antipodal.cpp:8-84) on the closing region of every hypothesis of a scene, restated in
+    numpy from the reference text on the oracle's own in-box sets and normals: extremal points within 0.003 of the
+    scaled x range (x is scaled by 1 / 0.1, hand_search.cpp:399-409), normals within the 30 degree friction cone of the
+    closing direction, HALF if one side has such points, FULL if both sides do and their y and z ranges overlap."""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=300)
+    o = ob.context(make_params(capi.MODE_NONE))
+    load_scene(o, sc)
+    o.detect()
+    hands = o.hypotheses(capi.LIST_HYPOTHESES)
+    normals = o.normals().astype(np.float64)
+    xyz = sc["xyz"]
+    cos_f = np.cos(30.0 * np.pi / 180.0)
+    n_half = n_full = 0
+    for h, hy in enumerate(hands):
+        ids = o.in_box(capi.LIST_HYPOTHESES, h)
+        assert len(ids) == hy["num_in_box"] > 0
+        sample = xyz[sc["samples"][hy["sample_id"]]]
+        d = (xyz[ids] - sample).astype(np.float64)        # centred in float, then double (hand_search.cpp:209)
+        x, y, z = d @ hy["binormal"], d @ hy["approach"], d @ hy["axis"]
+        nx = normals[ids] @ hy["binormal"]
+        xs = x * 10.0                                       # only x needs its scale: the threshold is absolute
+        left = (xs < xs.min() + 0.003) & (-nx > cos_f)
+        right = (xs > xs.max() - 0.003) & (nx > cos_f)
+        half = bool(left.any() or right.any())
+        full = False
+        if left.any() and right.any():
+            full = bool(min(y[left].max(), y[right].max()) > max(y[left].min(), y[right].min()) and
+                        min(z[left].max(), z[right].max()) > max(z[left].min(), z[right].min()))
+        assert half == bool(hy["half_antipodal"]) and full == bool(hy["full_antipodal"]), (h, half, full)
+        n_half += half
+        n_full += full
+    assert len(hands) > 100 and 0 < n_full < n_half < len(hands)
