@@ -549,3 +549,54 @@ def test_antipodal_flags_vs_numpy_restatement():
         n_half += half
         n_full += full
     assert len(hands) > 100 and 0 < n_full < n_half < len(hands)
+
+
+def test_grasp_images_vs_numpy_restatement():
+    """Learning::createGraspImages -> createInstance -> convertToImageRGB (learning.cpp:4-33, 221-249, 143-209) with the
+    unit-box scaling of hand_search.cpp:399-409, restated in numpy from the reference text on the oracle's in-box sets
+    and normals: cell of every point, per-cell double sums in list order, normalise, abs, float image, 3x3 dilation,
+    BGR2RGB, x255 with round-half-even.  (The OpenCV tail alone is pinned against cv2 in test_image_tail_vs_opencv.)"""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=200)
+    p = make_params(capi.MODE_NONE)
+    o = ob.context(p)
+    load_scene(o, sc)
+    o.detect()
+    hands = o.hypotheses(capi.LIST_PRUNED)
+    imgs = o.render_images()
+    assert len(hands) == len(imgs) > 30
+    normals = o.normals().astype(np.float64)
+    xyz = sc["xyz"]
+    fs = ob.finger_spacing(p.finger_width, p.hand_outer_diameter)
+    cellsize = 1.0 / 60.0
+    differing = total = 0
+    for h, hy in enumerate(hands):
+        ids = o.in_box(capi.LIST_PRUNED, h)
+        sample = xyz[sc["samples"][hy["sample_id"]]]
+        d = (xyz[ids] - sample).astype(np.float64)
+        frame = np.stack([hy["binormal"], hy["approach"], hy["axis"]], axis=1)  # frame_rot columns
+        pts, nrm = d @ frame, normals[ids] @ frame
+        e = int(hy["finger_slot"])
+        left, right = fs[e] + p.finger_width, fs[10 + e]
+        left_const = left - 0.5 * (0.1 - (right - left))
+        xs = (1.0 / 0.1) * (pts[:, 0] - left_const)
+        ys = (1.0 / (hy["hand_top"] - hy["hand_bottom"])) * (pts[:, 1] - hy["hand_bottom"])
+        ys = ys - ys.min()  # aligns = true (default argument)
+        cell = np.floor(xs / cellsize).astype(np.int64) + np.floor(ys / cellsize).astype(np.int64) * 60
+        ok = (cell >= 0) & (cell < 3600)
+        acc = np.zeros((3600, 3))
+        np.add.at(acc, cell[ok], nrm[ok])  # unbuffered: the points of a cell are added in list order
+        cnt = np.bincount(cell[ok], minlength=3600)
+        img = np.zeros((60, 60, 3), np.float32)
+        occ = np.nonzero(cnt)[0]
+        v = np.abs(acc[occ] * (1.0 / np.linalg.norm(acc[occ], axis=1))[:, None])
+        img[59 - occ // 60, occ % 60] = v.astype(np.float32)
+        pad = np.zeros((62, 62, 3), np.float32)
+        pad[1:61, 1:61] = img
+        dil = np.max([pad[a:a + 60, b:b + 60] for a in range(3) for b in range(3)], axis=0)
+        rgb = dil[:, :, ::-1]
+        u8 = np.clip(np.rint(rgb * np.float32(255.0)), 0, 255).astype(np.uint8)  # rint = round half to even
+        differing += int(np.count_nonzero(u8 != imgs[h]))
+        total += u8.size
+        assert np.max(np.abs(u8.astype(int) - imgs[h].astype(int))) <= 1, h
+    assert differing <= 1e-5 * total, (differing, total)
