@@ -600,3 +600,69 @@ def test_grasp_images_vs_numpy_restatement():
         total += u8.size
         assert np.max(np.abs(u8.astype(int) - imgs[h].astype(int))) <= 1, h
     assert differing <= 1e-5 * total, (differing, total)
+
+
+def test_finger_sweep_vs_numpy_restatement():
+    """HandSearch::calculateHand (hand_search.cpp:319-426) with FingerHand::evaluateFingers / evaluateHand / deepenHand /
+    computePointsInClosingRegion (finger_hand.cpp:17-180, 313-325), restated in numpy from the reference text for every
+    (sample, orientation) of a scene: crop at the hand height, rotate, finger placements free of points below the bite,
+    hands = matching finger pairs, middle hand, deepen in 5 mm steps while both of its fingers stay free, closing region.
+    The oracle's sweep records (finger mask, hand mask, chosen slot, deepen steps, in-box count, emitted) must equal it."""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=150)
+    p = make_params(capi.MODE_NONE)
+    o = ob.context(p)
+    load_scene(o, sc)
+    o.detect()
+    frames, sweeps = o.frames(), o.sweep_records()
+    xyz = sc["xyz"]
+    fw, od, hd, hh, bite0 = p.finger_width, p.hand_outer_diameter, p.hand_depth, p.hand_height, p.init_bite
+    fs = ob.finger_spacing(fw, od)
+    angles = ob.orientation_angles(p.num_orientations)
+    depths = ob.deepen_depths(bite0, hd)  # init_bite + 0.005, ... while <= hand_depth (accumulated in double)
+
+    def fingers_at(pts, bite, only=None):
+        out = np.zeros(20, bool)
+        crop = pts[pts[:, 1] < bite]
+        if len(crop) == 0 or np.any(crop[:, 1] < bite - hd):  # nothing between the fingers / the hand base would collide
+            return out
+        for i in (range(20) if only is None else (only, 10 + only)):
+            out[i] = not np.any((crop[:, 0] > fs[i]) & (crop[:, 0] < fs[i] + fw))
+        return out
+
+    checked = emitted = 0
+    for s, fr in enumerate(frames):
+        if not fr["valid"]:
+            continue
+        q = xyz[sc["samples"][s]]
+        ids, _ = o.radius_search(q, p.nn_radius_hands)
+        pts = (xyz[ids] - q).astype(np.float64)  # centred in float, then double (hand_search.cpp:209)
+        frame = np.stack([fr["normal"], fr["binormal"], fr["curvature_axis"]], axis=1)
+        z = pts @ frame[:, 2]
+        cropped = pts[(z > -hh) & (z < hh)]
+        for r, ang in enumerate(angles):
+            rot = np.array([[np.cos(ang), -np.sin(ang), 0.0], [np.sin(ang), np.cos(ang), 0.0], [0.0, 0.0, 1.0]])
+            prot = cropped @ (frame @ rot)  # points_rot = frame_rot^T * points, one row per point
+            rec = sweeps[s, r]
+            f = fingers_at(prot, bite0)
+            assert int(rec["fingers"]) == int(sum(1 << i for i in range(20) if f[i])), (s, r)
+            hand = f[:10] & f[10:] if f.sum() > 2 else np.zeros(10, bool)
+            assert int(rec["hand"]) == int(sum(1 << i for i in range(10) if hand[i])), (s, r)
+            checked += 1
+            if not hand.any():
+                assert rec["slot"] == -1 and rec["emitted"] == 0
+                continue
+            idx = np.nonzero(hand)[0]
+            e = int(idx[int(np.ceil(len(idx) / 2.0)) - 1])  # the middle hand
+            top, steps = bite0, 0
+            for dpt in depths:
+                if fingers_at(prot, dpt, only=e).sum() < 2:
+                    break
+                top, steps = dpt, steps + 1
+            left, right = fs[e] + fw, fs[10 + e]
+            inbox = (prot[:, 1] < top) & (prot[:, 0] > left) & (prot[:, 0] < right)
+            assert rec["slot"] == e and rec["depth_step"] == steps, (s, r, e, steps)
+            assert rec["num_in_box"] == inbox.sum(), (s, r)
+            assert rec["emitted"] == (1 if inbox.any() else 0)
+            emitted += int(inbox.any())
+    assert checked > 900 and emitted > 60
