@@ -666,3 +666,88 @@ def test_finger_sweep_vs_numpy_restatement():
             assert rec["emitted"] == (1 if inbox.any() else 0)
             emitted += int(inbox.any())
     assert checked > 900 and emitted > 60
+
+
+def test_grasp_poses_vs_numpy_restatement():
+    """FingerHand::calculateGraspParameters (finger_hand.cpp:183-214) and the grasp width (hand_search.cpp:397) from the
+    oracle's own frames, sweep records and in-box sets: surface / bottom / top = frame_rot * (center, y, 0) + sample with
+    center = (left + right) / 2, y = min y of the rotated points / bite - hand_depth / bite; axes = columns of frame_rot."""
+    from common import load_scene
+    sc = scenes.make_scene("tiny", num_samples=150)
+    p = make_params(capi.MODE_NONE)
+    o = ob.context(p)
+    load_scene(o, sc)
+    o.detect()
+    frames, hands = o.frames(), o.hypotheses(capi.LIST_HYPOTHESES)
+    xyz = sc["xyz"]
+    fs = ob.finger_spacing(p.finger_width, p.hand_outer_diameter)
+    angles = ob.orientation_angles(p.num_orientations)
+    depths = np.concatenate([[p.init_bite], ob.deepen_depths(p.init_bite, p.hand_depth)])
+    assert len(hands) > 60
+    for h, hy in enumerate(hands):
+        fr = frames[hy["sample_id"]]
+        ang = angles[hy["orientation_id"]]
+        frame = np.stack([fr["normal"], fr["binormal"], fr["curvature_axis"]], axis=1)
+        rot = np.array([[np.cos(ang), -np.sin(ang), 0.0], [np.sin(ang), np.cos(ang), 0.0], [0.0, 0.0, 1.0]])
+        frame_rot = frame @ rot
+        for k, name in enumerate(("binormal", "approach", "axis")):
+            assert np.allclose(hy[name], frame_rot[:, k], rtol=0, atol=1e-12), (h, name)
+        q = xyz[sc["samples"][hy["sample_id"]]]
+        ids, _ = o.radius_search(q, p.nn_radius_hands)
+        pts = (xyz[ids] - q).astype(np.float64)
+        z = pts @ frame[:, 2]
+        prot = pts[(z > -p.hand_height) & (z < p.hand_height)] @ frame_rot
+        e = int(hy["finger_slot"])
+        left, right = fs[e] + p.finger_width, fs[10 + e]
+        top = depths[hy["depth_step"]]
+        assert abs(hy["hand_top"] - top) < 1e-15 and abs(hy["hand_bottom"] - (top - p.hand_depth)) < 1e-15
+        center, surface = 0.5 * (left + right), prot[:, 1].min()
+        sample = fr["sample"]
+        for name, y in (("surface", surface), ("bottom", top - p.hand_depth), ("top", top)):
+            assert np.allclose(hy[name], frame_rot @ np.array([center, y, 0.0]) + sample, rtol=0, atol=1e-12), (h, name)
+        inbox = prot[(prot[:, 1] < top) & (prot[:, 0] > left) & (prot[:, 0] < right)]
+        assert abs(hy["width"] - (inbox[:, 0].max() - inbox[:, 0].min())) < 1e-12
+
+
+def test_normals_vs_numpy_restatement_of_pcl():
+    """pcl::NormalEstimation::computePointNormal as the path uses it (hand_search.cpp:83-94, r = 0.01): neighbours in
+    radiusSearch order, computeMeanAndCovarianceMatrix's single pass over nine FLOAT sums without centring, covariance =
+    second moments - centroid products, normal = eigenvector of the smallest eigenvalue, flipped towards the viewpoint
+    (0, 0, 0); fewer than three neighbours -> NaN.  The moments are restated in float32 in that order.  Fed to the
+    oracle's eigen33 (itself pinned against numpy) they must give the oracle's normal BIT FOR BIT -- the order of the
+    sums is part of the semantics; numpy's double-precision eigenvector of the same matrix agrees to 3e-3 rad where the
+    two smallest eigenvalues are well separated (the float closed form is that far off on thin neighbourhoods)."""
+    sc = scenes.make_scene("tiny")
+    o = ob.context(make_params(capi.MODE_NONE))
+    o.set_cloud(sc["xyz"], sc["cam_mask"], sc["num_cams"])
+    o.compute_normals()
+    got = o.normals()
+    xyz = sc["xyz"]
+    rng = np.random.default_rng(9)
+    checked = 0
+    for i in rng.choice(len(xyz), 400, replace=False):
+        ids, d2 = o.radius_search(xyz[i], 0.01)
+        if len(ids) < 3:
+            assert np.all(np.isnan(got[i]))
+            continue
+        order = np.lexsort((ids, d2))  # ascending (d2, index), FLANN's order
+        pts = xyz[ids[order]]
+        acc = np.zeros(9, np.float32)
+        for x, y, z in pts:  # sequential float32 sums, as PCL's loop
+            acc += np.array([x * x, x * y, x * z, y * y, y * z, z * z, x, y, z], np.float32)
+        acc = acc * (np.float32(1.0) / np.float32(len(pts)))  # Eigen 3.2's operator/=(scalar) multiplies by the reciprocal
+        c = acc[6:9]
+        cov = np.array([[acc[0] - c[0] * c[0], acc[1] - c[0] * c[1], acc[2] - c[0] * c[2]],
+                        [acc[1] - c[0] * c[1], acc[3] - c[1] * c[1], acc[4] - c[1] * c[2]],
+                        [acc[2] - c[0] * c[2], acc[4] - c[1] * c[2], acc[5] - c[2] * c[2]]], np.float32)
+        _, ev = ob.eigen33(cov)
+        flip = np.float32(-1.0) if np.dot(-xyz[i], ev) < 0 else np.float32(1.0)  # flipNormalTowardsViewpoint, viewpoint (0, 0, 0)
+        mine = (ev * flip).astype(np.float32)
+        assert np.array_equal(np.abs(mine).view(np.uint32), np.abs(got[i]).view(np.uint32)), (i, mine, got[i])
+        assert np.dot(mine.astype(np.float64), got[i].astype(np.float64)) > 0, i
+        checked += 1
+        w, v = np.linalg.eigh(cov.astype(np.float64))
+        if w[1] - w[0] > 0.2 * max(abs(w[2]), 1e-30):
+            cosang = abs(np.dot(v[:, 0], got[i].astype(np.float64))) / np.linalg.norm(got[i])
+            assert np.arccos(np.clip(cosang, -1, 1)) < 3e-3, (i, w)
+    assert checked > 150
