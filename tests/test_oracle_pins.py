@@ -926,3 +926,96 @@ def test_pcl_eigen33_numpy_float32_restatement_and_size_of_deviation_d2(tiny_sce
     assert n > 1000
     assert worst < 1e-6, (differ, n, worst)
     print(f"D2: {differ} of {n} normals differ from libm float trigonometry, worst {worst:.2e} rad")
+
+
+def test_local_frames_vs_numpy_restatement(tiny_scene):
+    """HandSearch::calculateLocalFrames (hand_search.cpp:97-170) + LocalFrame (local_frame.cpp:4-15, 26-59) restated in
+    numpy: radiusSearch(sample, nn_radius_taubin); no neighbour -> no frame (:122); min(50, n) normals drawn WITH
+    replacement from the neighbour list (:126-137; rand() % n replaced by deviation D1's counter-based draw
+    splitmix64(seed ^ splitmix64(sample_id << 8 ^ j)) % n); the camera counts of the DRAWN points, first maximum wins
+    (:139-147, Eigen's maxCoeff); columns normalised (:149-150); curvature axis = eigenvector of the smallest eigenvalue
+    of N N^T (:29-38, numpy.linalg.eigh here); normal = the drawn normal with the largest column sum of (N^T N)^6
+    projected off the axis (:41-44); binormal = axis x normal; both turned against (sample - camera origin of the majority
+    camera) (:50-54); axis = normal x binormal (:57).  Counts and camera exact, axes to 1e-9."""
+    p = make_params(capi.MODE_NONE)
+    o = ob.context(p)
+    o.set_cloud(tiny_scene["xyz"], tiny_scene["cam_mask"], tiny_scene["num_cams"])
+    samples = np.asarray(tiny_scene["samples"], np.int64)
+    o.set_sample_indices(samples)
+    o.compute_normals()
+    o.generate_hypotheses()
+    fr = o.frames()
+    nrm = o.normals().astype(np.float64)
+    xyz, cam = tiny_scene["xyz"], tiny_scene["cam_mask"]
+    tfs = [np.array(p.cam_tf_left).reshape(4, 4), np.array(p.cam_tf_right).reshape(4, 4)]
+    m64 = (1 << 64) - 1
+    checked = 0
+    for s, i in enumerate(samples):
+        ids, d2 = o.radius_search(xyz[i], p.nn_radius_taubin)
+        assert fr[s]["num_neighbors"] == len(ids)
+        if len(ids) == 0:
+            assert fr[s]["valid"] == 0
+            continue
+        ids = ids[np.lexsort((ids, d2))]
+        m = min(50, len(ids))
+        drawn = [ids[_splitmix64(int(p.rng_seed) ^ _splitmix64(((s << 8) ^ j) & m64)) % len(ids)] for j in range(m)]
+        N = nrm[drawn].T  # 3 x m
+        if not np.all(np.isfinite(N)):
+            continue
+        counts = [sum((cam[d] >> c) & 1 for d in drawn) for c in range(tiny_scene["num_cams"])]
+        majority = int(np.argmax(counts))
+        N = N / np.sqrt((N * N).sum(axis=0))
+        w, v = np.linalg.eigh(N @ N.T)
+        if min(w[1] - w[0], w[2] - w[1]) < 1e-6 * w[2]:
+            continue
+        axis = v[:, 0]
+        k = int(np.argmax(((N.T @ N) ** 6).sum(axis=0)))
+        npart = (np.eye(3) - np.outer(axis, axis)) @ N[:, k]
+        normal = npart / np.linalg.norm(npart)
+        binormal = np.cross(axis, normal)
+        src = xyz[i].astype(np.float64) - tfs[majority][:3, 3]
+        if normal @ src > 0:
+            normal = -normal
+        if binormal @ src > 0:
+            binormal = -binormal
+        axis = np.cross(normal, binormal)
+        assert fr[s]["valid"] == 1 and fr[s]["majority_cam"] == majority, s
+        assert np.array_equal(fr[s]["sample"], xyz[i].astype(np.float64))
+        for name, want in (("normal", normal), ("binormal", binormal), ("curvature_axis", axis)):
+            assert np.abs(fr[s][name] - want).max() < 1e-9, (s, name, fr[s][name], want)
+        checked += 1
+    assert checked >= 0.8 * len(samples)
+
+
+@pytest.mark.parametrize("num_selected,min_score_diff", [(7, -1e30), (50, 0.0), (0, -10.0), (3, 5.0)])
+def test_score_and_select_vs_numpy_restatement(tiny_scene, num_selected, min_score_diff):
+    """GraspDetector::detectGraspPoses, PREDICTION branch and selection (grasp_detector.cpp:186-221, 238-252), in numpy:
+    score = logits[1] - logits[0] as a FLOAT difference widened to double (:203); a hand is kept iff score >=
+    min_score_diff (:205), marked full antipodal with that score (:208-209), in list order; then the num_selected best
+    by score, best first (isScoreGreater), all of them when there are no more than num_selected (:241-252).  Equal
+    scores keep list order (deviation D4: std::partial_sort leaves it unspecified)."""
+    p = make_params(capi.MODE_PREDICTION, num_selected=num_selected, min_score_diff=min_score_diff)
+    o = ob.context(p)
+    o.set_lenet_weights(ob.xavier_weights(5))
+    o.set_cloud(tiny_scene["xyz"], tiny_scene["cam_mask"], tiny_scene["num_cams"])
+    o.set_sample_indices(tiny_scene["samples"])
+    o.detect()
+    pruned = o.hypotheses(capi.LIST_PRUNED)
+    logits = o.logits()
+    assert logits.dtype == np.float32 and logits.shape == (len(pruned), 2) and len(pruned) > 15
+    score = (logits[:, 1] - logits[:, 0]).astype(np.float64)
+    keep = np.flatnonzero(score >= min_score_diff)
+    anti = o.hypotheses(capi.LIST_ANTIPODAL)
+    assert len(anti) == len(keep) and (0 < len(keep) < len(pruned) or min_score_diff < -1e29)
+    for name in ("sample_id", "orientation_id"):
+        assert np.array_equal(anti[name], pruned[name][keep])
+    assert np.array_equal(anti["score"], score[keep]) and np.all(anti["full_antipodal"] == 1)
+    order = keep[np.argsort(-score[keep], kind="stable")]
+    if 0 < num_selected < len(order):
+        order = order[:num_selected]
+    sel = o.hypotheses(capi.LIST_SELECTED)
+    assert len(sel) == len(order)
+    for name in ("sample_id", "orientation_id"):
+        assert np.array_equal(sel[name], pruned[name][order]), name
+    assert np.array_equal(sel["score"], score[order])
+    assert np.array_equal(sel["surface"], pruned["surface"][order])
