@@ -172,11 +172,15 @@ int ag2_default_params(ag2_params* p);
 /* Replaces: GraspDetector ctor + HandSearch::setParameters (grasp_detector.cpp:15-81,
  * hand_search.cpp:64-80).  device = CUDA ordinal. */
 int ag2_create(const ag2_params* p, int device, ag2_ctx** out);
+/* ~GraspDetector (grasp_detector.h:76-80): frees the device memory, streams and events of the ctx. */
 int ag2_destroy(ag2_ctx* ctx);
 /* HandSearch::setParameters / setCamTfLeft / setCamTfRight (hand_search.h:121-133). */
 int ag2_set_params(ag2_ctx* ctx, const ag2_params* p);
+/* Error reporting of the C ABI (no reference counterpart: the reference prints and returns an empty list, e.g.
+ * grasp_detector.cpp:86-91): every entry point returns an AG2_E_* code; text for the code and for the last failure. */
 const char* ag2_strerror(int code);
 const char* ag2_last_error(const ag2_ctx* ctx);
+/* AG2_ABI_VERSION the library was built with (no reference counterpart). */
 int ag2_abi_version(void);
 
 /* ---- classifier weights ------------------------------------------------- */
@@ -184,13 +188,15 @@ int ag2_abi_version(void);
 /* Replaces Classifier ctor's net_->CopyTrainedLayersFrom (caffe_classifier.cpp:13-14):
  * parses the caffemodel protobuf wire format (V1 "layers" and V2 "layer"). */
 int ag2_load_lenet_caffemodel(ag2_ctx* ctx, const char* path);
-/* Caffe blob layouts: conv [out,in,kh,kw], ip [out,in]; fp32. */
+/* The same blobs from memory (what net_->CopyTrainedLayersFrom leaves in the four layers of
+ * caffe/sigmoid_lenet.prototxt:10-90).  Caffe blob layouts: conv [out,in,kh,kw], ip [out,in]; fp32. */
 int ag2_set_lenet_weights(ag2_ctx* ctx, const float* conv1_w, const float* conv1_b,
                           const float* conv2_w, const float* conv2_b, const float* ip1_w,
                           const float* ip1_b, const float* ip2_w, const float* ip2_b);
 /* Xavier fillers named in caffe/sigmoid_lenet.prototxt:17-19,41-43,64-66,82-84
  * (the trained blob is absent from the reference checkout). */
 int ag2_init_lenet_xavier(ag2_ctx* ctx, uint64_t seed);
+/* Reads the blobs back in the same layouts (tests; no reference counterpart). */
 int ag2_get_lenet_weights(ag2_ctx* ctx, float* conv1_w, float* conv1_b, float* conv2_w,
                           float* conv2_b, float* ip1_w, float* ip1_b, float* ip2_w,
                           float* ip2_b);
@@ -208,23 +214,24 @@ int ag2_get_lenet_weights(ag2_ctx* ctx, float* conv1_w, float* conv1_b, float* c
  * (they were validated against the old cloud; ag2_detect then returns AG2_E_NO_SAMPLES). */
 int ag2_set_cloud(ag2_ctx* ctx, const float* xyz, size_t stride_bytes, size_t n,
                   const uint8_t* cam_mask, int num_cams, const float* normals_or_null);
-/* Same with DEVICE pointers (packed xyz; used after an NCCL broadcast). */
+/* Same contract (cloud_camera.h:102-139) with DEVICE pointers (packed xyz; used after an NCCL broadcast). */
 int ag2_set_cloud_device(ag2_ctx* ctx, const float* d_xyz, size_t n, const uint8_t* d_cam_mask,
                          int num_cams, const float* d_normals_or_null);
-/* CloudCamera::setSampleIndices (cloud_camera.h:131) -> calculateLocalFrames(indices),
+/* CloudCamera::setSampleIndices (cloud_camera.h:132-135) -> calculateLocalFrames(indices),
  * hand_search.cpp:97-170. */
 int ag2_set_sample_indices(ag2_ctx* ctx, const int32_t* idx, size_t n);
-/* Same with a DEVICE pointer (the sample list after an NCCL broadcast); indices are range-checked
- * on the device. */
+/* CloudCamera::setSampleIndices (cloud_camera.h:132-135) with a DEVICE pointer (the sample list after an NCCL
+ * broadcast); indices are range-checked on the device. */
 int ag2_set_sample_indices_device(ag2_ctx* ctx, const int32_t* d_idx, size_t n);
 /* CloudCamera::setSamples (cloud_camera.cpp:254-257) -> calculateLocalFrames(samples),
  * hand_search.cpp:238-317.  xyz: 3 doubles per sample. */
 int ag2_set_sample_points(ag2_ctx* ctx, const double* xyz, size_t n);
-/* Offset added to the sample position when deriving the rand() replacement
- * stream, so that a shard of a larger sample list draws like the whole list. */
+/* Offset added to the sample position when deriving the stream that replaces rand() in
+ * hand_search.cpp:130, so that a shard of a larger sample list draws like the whole list
+ * (no reference counterpart: its rand() is shared by the OpenMP threads). */
 int ag2_set_sample_id_offset(ag2_ctx* ctx, int64_t first_sample_id);
-/* General form: sample s of this context is sample first + stride*s of the whole list (a strided
- * shard; stride >= 1).  ag2_set_sample_id_offset(first) == ag2_set_sample_id_map(first, 1). */
+/* General form (no reference counterpart either): sample s of this context is sample first + stride*s of the
+ * whole list (a strided shard; stride >= 1).  ag2_set_sample_id_offset(first) == ag2_set_sample_id_map(first, 1). */
 int ag2_set_sample_id_map(ag2_ctx* ctx, int64_t first_sample_id, int64_t stride);
 
 /* ---- multi-GPU: the normals (calculateNormalsOMP, hand_search.cpp:83-94) sharded by point ------
@@ -248,11 +255,13 @@ int ag2_set_normals_shards(ag2_ctx* ctx, const float* d_all, size_t cap_points, 
 int ag2_preprocess_cloud(ag2_ctx* ctx, const float* xyz, size_t stride_bytes, size_t n,
                          const uint8_t* cam_mask, int num_cams, const float* normals_or_null,
                          int filter_workspace, int voxelize, double voxel_size);
-/* The ctx's (processed) cloud: packed xyz and camera masks.  CloudCamera::getCloudProcessed. */
+/* The ctx's (processed) cloud: packed xyz and camera masks.  CloudCamera::getCloudProcessed /
+ * getCameraSource (cloud_camera.h:102-110). */
 int ag2_get_cloud(ag2_ctx* ctx, float* xyz, uint8_t* cam_mask, size_t cap, size_t* n);
 /* CloudCamera::subsampleUniformly (cloud_camera.cpp:171-178): num_samples distinct ascending
  * indices into the processed cloud become the sample indices. */
 int ag2_subsample_uniformly(ag2_ctx* ctx, int num_samples, uint64_t seed);
+/* CloudCamera::getSampleIndices (cloud_camera.h:117-120). */
 int ag2_get_sample_indices(ag2_ctx* ctx, int32_t* idx, size_t cap, size_t* n);
 
 /* ---- stages -------------------------------------------------------------- */
@@ -266,7 +275,7 @@ int ag2_prune(ag2_ctx* ctx);
 /* Learning::createGraspImages (learning.cpp:4-33) on the pruned list.
  * out_or_null: host buffer of num_pruned * AG2_IMAGE_BYTES (HWC u8, the cv::Mat layout). */
 int ag2_render_images(ag2_ctx* ctx, uint8_t* out_or_null);
-/* Same for caller-chosen hypotheses of the last ag2_generate_hypotheses call, addressed by
+/* Learning::createGraspImages (learning.cpp:4-33) for caller-chosen hypotheses of the last ag2_generate_hypotheses call, addressed by
  * (sample_id, orientation_id) as found in their records; out: n * AG2_IMAGE_BYTES (host). */
 int ag2_render_hypotheses(ag2_ctx* ctx, const int32_t* sample_ids, const int32_t* orientation_ids,
                           size_t n, uint8_t* out);
@@ -304,6 +313,7 @@ typedef struct ag2_is_params {
   double radius;              /* 0.02: sigma of the Gaussians */
   uint64_t seed;              /* counter-based replacement of rand() / boost::mt19937(time) */
 } ag2_is_params;
+/* The constants of importance_sampling.cpp:9-15. */
 int ag2_default_is_params(ag2_is_params* p);
 /* ImportanceSampling::detectGraspPoses (importance_sampling.cpp:30-112) without the final
  * clustering: detect on the samples currently set, then num_iterations rounds of
@@ -320,8 +330,10 @@ int ag2_draw_importance_samples(ag2_ctx* ctx, const ag2_is_params* p, int round,
                                 size_t n_hands, double* xyz_out);
 /* Samples drawn in round `round` (0-based), 3 doubles each, for the parity tests. */
 int ag2_get_importance_samples(ag2_ctx* ctx, int round, double* xyz, size_t cap, size_t* n);
+/* Waits for everything enqueued on the ctx stream (no reference counterpart: the reference is synchronous). */
 int ag2_synchronize(ag2_ctx* ctx);
-/* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing. */
+/* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing (no reference
+ * counterpart). */
 int ag2_get_stream(ag2_ctx* ctx, void** stream);
 
 /* Measurement aid (no reference counterpart): FMA throughput of this ctx's GPU right now, in TFLOP/s --
@@ -339,29 +351,38 @@ enum {
   AG2_LIST_IMPORTANCE = 4, /* result of ag2_detect_importance */
   AG2_LIST_CLUSTERS = 5    /* result of ag2_find_clusters */
 };
+/* The std::vector<GraspHypothesis> each step of GraspDetector::detectGraspPoses holds (grasp_detector.cpp:
+ * 141 hands, :149-160 hands_filtered, :170-221 antipodal_hands, :239-252 hands_selected), as ag2_hypothesis
+ * records (grasp_hypothesis.h:62-313) in the reference's list order. */
 int ag2_num_hypotheses(ag2_ctx* ctx, int which, size_t* n);
 int ag2_get_hypotheses(ag2_ctx* ctx, int which, ag2_hypothesis* out, size_t cap, size_t* n);
-/* Device pointer of a list (records are contiguous); valid until the next stage call. */
+/* Device pointer of a list (records are contiguous); valid until the next stage call (no reference counterpart). */
 int ag2_get_hypotheses_device(ag2_ctx* ctx, int which, const ag2_hypothesis** d_ptr, size_t* n);
 /* Copies a list into caller-owned DEVICE memory of `cap` records and zero-fills the rest (a valid
  * record never has an all-zero approach vector); the buffer is complete when the call returns.
- * This is the send buffer of the multi-GPU all-gather (grasp lists of all ranks). */
+ * This is the send buffer of the multi-GPU all-gather (grasp lists of all ranks; no reference counterpart). */
 int ag2_copy_hypotheses_device(ag2_ctx* ctx, int which, ag2_hypothesis* d_dst, size_t cap, size_t* n);
+/* Counts and per-phase device times of the last call: what the reference prints with omp_get_wtime
+ * (grasp_detector.cpp:93,174,185,210,254; hand_search.cpp:7,19,30,58,166,230). */
 int ag2_get_stats(ag2_ctx* ctx, ag2_stats* out);
 
-/* ---- introspection used by the parity tests ------------------------------ */
+/* ---- introspection used by the parity tests (intermediate values the reference keeps in members / locals) -- */
+/* HandSearch::cloud_normals_ (hand_search.cpp:93), as floats. */
 int ag2_get_normals(ag2_ctx* ctx, float* out /* 3*n, input point order */);
+/* The LocalFrame of every sample (local_frame.h:53-146; hand_search.cpp:150-152), invalid ones included. */
 int ag2_get_frames(ag2_ctx* ctx, ag2_frame* out, size_t cap);
+/* FingerHand's state after calculateHand for every (sample, orientation) (finger_hand.h:201-222; hand_search.cpp:322,363-376). */
 int ag2_get_sweep_records(ag2_ctx* ctx, ag2_sweep_record* out, size_t cap /* samples*R */);
-/* Fixed-radius query (KdTreeFLANN::radiusSearch semantics): ids in
+/* Fixed-radius query (KdTreeFLANN::radiusSearch as called in hand_search.cpp:122,201,268): ids in
  * input point order sorted by (d2, id).  Host pointers. */
 int ag2_radius_search(ag2_ctx* ctx, const float* q /*3*/, double radius, int32_t* idx, float* d2,
                       size_t cap, size_t* n);
-/* In-box point ids (input order, reference list order) of hypothesis h of list `which`. */
+/* In-box point ids (input order, reference list order) of hypothesis h of list `which`:
+ * FingerHand::computePointsInClosingRegion (finger_hand.cpp:137-180) -> GraspHypothesis::indices_points_for_learning_. */
 int ag2_get_in_box(ag2_ctx* ctx, int which, size_t h, int32_t* idx, size_t cap, size_t* n);
-/* ip2 logits of the pruned list after ag2_classify: 2 floats per image. */
+/* ip2 logits of the pruned list after ag2_classify: 2 floats per image (the `predictions` of grasp_detector.cpp:196). */
 int ag2_get_logits(ag2_ctx* ctx, float* out, size_t cap_images);
-/* Classifier::ClassifyBatch on caller images (HWC u8, 60x60x3): 2 floats per image. */
+/* Classifier::ClassifyBatch (caffe_classifier.cpp:70-127) on caller images (HWC u8, 60x60x3): 2 floats per image. */
 int ag2_classify_images(ag2_ctx* ctx, const uint8_t* images, size_t n, float* logits_out);
 /* The same classifier pass for callers that may not allocate (CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference: added
@@ -384,6 +405,8 @@ int ag2_classify_images_static(ag2_ctx* ctx, const uint8_t* d_images, size_t n, 
 int ag2_pcd_info(const char* path, size_t* n, int* has_normals, int* has_color);
 int ag2_pcd_read(const char* path, float* xyz /*3*cap*/, float* normals_or_null, uint32_t* rgba_or_null,
                  size_t cap, size_t* n);
+/* pcl::io::savePCDFile's format for the tests and tools (no reference counterpart: it only reads,
+ * cloud_camera.cpp:231-240). */
 int ag2_pcd_write(const char* path, const float* xyz, const float* normals_or_null,
                   const uint32_t* rgba_or_null, size_t n, int binary);
 /* ROS 1 wire format of agile_grasp2/GraspListMsg (msg/GraspListMsg.msg, msg/GraspMsg.msg;
@@ -415,30 +438,34 @@ int ag2_merge_selected(const ag2_hypothesis* blocks, int world, size_t cap, int 
 typedef struct ag2_group ag2_group;
 typedef struct ag2_group_id { unsigned char bytes[128]; } ag2_group_id;  /* an ncclUniqueId */
 
-/* One process, n_gpus ranks on devices 0..n_gpus-1, one host thread per GPU inside the library.
- * This is what the C++ shim's GraspDetector uses when Params::num_gpus > 1. */
+/* One process, n_gpus ranks on devices 0..n_gpus-1, one host thread per GPU inside the library: the place of
+ * the GraspDetector the node constructs once (grasp_detection_node.cpp:98-107).  This is what the C++ shim's
+ * GraspDetector uses when Params::num_gpus > 1. */
 int ag2_group_create(const ag2_params* p, int n_gpus, ag2_group** out);
-/* One process per rank (torchrun, mpirun): rank 0 calls ag2_group_unique_id and hands the id to the
- * others by any channel; then every rank calls ag2_group_create_rank (collective). */
+/* One process per rank (torchrun, mpirun; no reference counterpart): rank 0 calls ag2_group_unique_id and hands
+ * the id to the others by any channel; then every rank calls ag2_group_create_rank (collective). */
 int ag2_group_unique_id(ag2_group_id* out);
 int ag2_group_create_rank(const ag2_params* p, const ag2_group_id* id, int rank, int world, int device,
                           ag2_group** out);
+/* Lifetime and shape of the group (no reference counterpart). */
 int ag2_group_destroy(ag2_group* g);
 int ag2_group_size(const ag2_group* g, int* world, int* n_local);
-/* ctx of the i-th LOCAL rank: weights (ag2_set_lenet_weights ...), ag2_get_stats, ag2_get_stream. */
+/* ctx of the i-th LOCAL rank: weights (ag2_set_lenet_weights ...), ag2_get_stats, ag2_get_stream
+ * (no reference counterpart). */
 int ag2_group_local_ctx(ag2_group* g, int i, ag2_ctx** ctx);
 const char* ag2_group_last_error(const ag2_group* g);
 /* 1 when the exchanges run on peer memory (NVLink loads / stores), 0 on the NCCL fallback; valid after
- * the first detect call. */
+ * the first detect call (measurement aid, no reference counterpart). */
 int ag2_group_transport(const ag2_group* g, int* peer_stores);
 /* Bytes the FIRST local rank moved between host and device in the last call (cloud + samples in, result
- * window out); every other rank of a multi-process group reports h2d = 0. */
+ * window out); every other rank of a multi-process group reports h2d = 0 (measurement aid, no reference
+ * counterpart). */
 int ag2_group_io_bytes(const ag2_group* g, size_t* h2d, size_t* d2h);
 /* Per-segment account of the FIRST local rank's last ag2_group_detect call, ms[10]: device time (CUDA events on
  * the ctx stream) of [0] inputs staged and pulled, [1] cell index, [2] own normal moments, [3] wait for all cell
  * indexes + own normals stored to all ranks, [4] wait for all normals + sample shard, [5] local detect (frames ..
  * select), [6] results stored to all ranks + wait; host clock of [7] result exchange incl. D2H and merge, [8] the
- * whole call; [9] device time start .. results in. */
+ * whole call; [9] device time start .. results in (measurement aid, no reference counterpart). */
 int ag2_group_last_timing(const ag2_group* g, double* ms);
 /* GraspDetector::detectGraspPoses (grasp_detector.cpp:84-282) over the group.  Collective when ranks are
  * processes: every rank calls it with the same n, num_cams, n_samples; xyz (packed, 3 floats per point),

@@ -91,3 +91,32 @@ def test_native_merge_of_per_rank_selections_equals_the_python_rule():
         want = sharded.merge_selected(parts, k)
         got = capi.merge_selected_blocks(blocks, k)
         assert got.tobytes() == want.tobytes(), (world, cap, k)
+
+
+def test_headers_are_plain_c(tmp_path):
+    """The boundary is a C ABI: include/ag2.h (and the sampler arithmetic shared with the oracle, ag2_detmath.h) must
+    compile as C99 with no C++ or CUDA construct, which is what a cgo / JNI / ctypes binding needs."""
+    import subprocess
+
+    src = tmp_path / "t.c"
+    src.write_text('#include "ag2.h"\n#include "ag2_detmath.h"\n'
+                   "int main(void) { ag2_params p; ag2_is_params q; (void)p; (void)q; return ag2_det_normal(0.3, 0.4) > 9.0; }\n")
+    r = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"),
+                        "-fsyntax-only", str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+
+
+def test_every_declaration_block_cites_the_reference_or_says_it_has_no_counterpart():
+    """include/ag2.h: each paragraph that declares entry points names the reference interface it replaces
+    (file.ext:line) or says that the reference has no counterpart."""
+    src = open(os.path.join(ROOT, "include", "ag2.h")).read()
+    cite = re.compile(r"\b\w+\.(cpp|h|prototxt|msg|launch):\d+|msg/\w+\.msg|[Nn]o (reference )?counterpart")
+    decl = re.compile(r"^\s*(?:int|const char\*)\s+(ag2_\w+)\s*\(", re.M)
+    bare = [names for block in re.split(r"\n\s*\n", src) if (names := decl.findall(block)) and not cite.search(block)]
+    assert not bare, bare
+    # and, one level finer, at least three quarters of the entry points carry a citation in their OWN comment
+    own = 0
+    decls = list(re.finditer(r"((?:/\*(?:(?!\*/).)*\*/\s*)?)^\s*(?:int|const char\*)\s+(ag2_\w+)\s*\(", src, re.M | re.S))
+    for m in decls:
+        own += bool(cite.search(re.sub(r"\s*\n\s*\*\s*", " ", m.group(1))))
+    assert len(decls) >= 70 and own >= 0.75 * len(decls), (own, len(decls))
