@@ -11,6 +11,7 @@
 #include <string>
 #include <vector>
 
+#include "sample_selection.h"
 #include "types.h"
 
 class CloudCamera {
@@ -75,6 +76,20 @@ class CloudCamera {
     sample_indices_.resize((size_t)num_samples);
     check(ag2_get_sample_indices(ctx, sample_indices_.data(), sample_indices_.size(), &n), "ag2_get_sample_indices");
     sample_indices_.resize(n);
+  }
+
+  // subsampleSamples, cloud_camera.cpp:181-206: at most num_samples of the incoming sample points become the xyz
+  // samples.  `Msg` is agile_grasp2::SamplesMsg or anything with samples[i].x / .y / .z; std::random_shuffle is replaced
+  // by the counter-based shuffle of sample_selection.h.
+  template <class Msg>
+  void subsampleSamples(const Msg& msg, int num_samples, uint64_t seed = 0) {
+    const std::vector<int> pos = ag2shim::subsampledPositions(msg.samples.size(), num_samples, seed);
+    samples_.resize(3, (int)pos.size());
+    for (int i = 0; i < (int)pos.size(); i++) {
+      samples_(0, i) = msg.samples[(size_t)pos[(size_t)i]].x;
+      samples_(1, i) = msg.samples[(size_t)pos[(size_t)i]].y;
+      samples_(2, i) = msg.samples[(size_t)pos[(size_t)i]].z;
+    }
   }
 
   const ag2shim::Matrix3Xd& getNormals() const { return normals_; }

@@ -86,11 +86,52 @@ class GraspDetector {
   GraspDetector(const GraspDetector&) = delete;
   GraspDetector& operator=(const GraspDetector&) = delete;
 
+  // Stand-ins for the two ROS messages the reference keeps sample requests in (msg/SamplesMsg.msg: geometry_msgs/Point[]
+  // samples; msg/CloudIndexed.msg: std_msgs/Int64[] indices).  The setters below are templates, so the real message
+  // types work as well.
+  struct Point {
+    double x, y, z;
+  };
+  struct SamplesMsg {
+    std::vector<Point> samples;
+  };
+
+  // grasp_detector.h:111 / grasp_detector.cpp:353-360: cloud indices to sample at (CloudIndexed); they switch the
+  // workspace filter, the voxelisation and the pruning off (:287, :150-160)
+  template <class Msg>
+  void setIndicesFromMsg(const Msg& msg) {
+    indices_.resize(msg.indices.size());
+    for (size_t i = 0; i < indices_.size(); i++) indices_[i] = (int)msg.indices[i].data;
+  }
+  void setIndices(const std::vector<int>& indices) { indices_ = indices; }
+  // grasp_detector.h:113-116: sample points from an external source, used when use_incoming_samples is set
+  template <class Msg>
+  void setSamplesMsg(const Msg& msg) {
+    samples_msg_.samples.resize(msg.samples.size());
+    for (size_t i = 0; i < msg.samples.size(); i++)
+      samples_msg_.samples[i] = Point{(double)msg.samples[i].x, (double)msg.samples[i].y, (double)msg.samples[i].z};
+    have_samples_msg_ = true;
+  }
+
   // grasp_detector.cpp:285-350: workspace filter, voxelisation (voxel_size_ = 0.003), sample selection
   void preprocessPointCloud(CloudCamera& cloud_cam) {
+    if (!indices_.empty()) {  // :334-347: the cloud is used as it came
+      cloud_cam.setSampleIndices(
+          ag2shim::drawFromIndices(indices_, prm_.num_samples, cloud_cam.getCloudOriginal().size(), prm_.rng_seed));
+      return;
+    }
     cloud_cam.filterWorkspaceAndVoxelize(ctx_, prm_.voxelize, 0.003);
     const int n = (int)cloud_cam.getCloudProcessed().size();
-    if (use_incoming_samples_) return;  // xyz samples were set by the caller (setSamples)
+    if (use_incoming_samples_) {
+      if (!have_samples_msg_) return;  // xyz samples were set on the CloudCamera by the caller (setSamples)
+      std::vector<ag2shim::SamplePoint> all;
+      for (const Point& q : samples_msg_.samples) all.push_back(ag2shim::SamplePoint{{q.x, q.y, q.z}});
+      SamplesMsg inside;  // :305-313: samples outside the workspace are removed
+      for (const ag2shim::SamplePoint& q : ag2shim::samplesInWorkspace(all, p_.workspace))
+        inside.samples.push_back(Point{q[0], q[1], q[2]});
+      cloud_cam.subsampleSamples(inside, prm_.num_samples, prm_.rng_seed);  // :317
+      return;
+    }
     if (prm_.num_samples > n) {
       std::vector<int> all((size_t)n);
       for (int i = 0; i < n; i++) all[(size_t)i] = i;
@@ -106,7 +147,8 @@ class GraspDetector {
       return std::vector<GraspHypothesis>();  // :86-91
     ag2_params p = p_;
     if (!clusters_grasps) p.min_inliers = 0;
-    if (group_ && !use_incoming_samples_ && p.min_inliers == 0 && cloud_cam.getNormals().cols() == 0)
+    if (!indices_.empty()) p.prune = 0;  // :150-160: no pruning on caller-supplied indices
+    if (group_ && !use_incoming_samples_ && indices_.empty() && p.min_inliers == 0 && cloud_cam.getNormals().cols() == 0)
       return detectOnGroup(cloud_cam, nullptr);
     ag2shim::check(ag2_set_params(ctx_, &p), "ag2_set_params", ctx_);
     ag2shim::upload(ctx_, cloud_cam, use_incoming_samples_);
@@ -163,6 +205,9 @@ class GraspDetector {
   ag2_ctx* ctx_;
   ag2_group* group_;
   bool use_incoming_samples_;
+  bool have_samples_msg_ = false;
+  SamplesMsg samples_msg_;
+  std::vector<int> indices_;
 };
 
 class ImportanceSampling : public GraspDetector {

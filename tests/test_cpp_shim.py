@@ -29,7 +29,7 @@ def test_shims_compile_against_the_eigen_interface():
     """types.h aliases its value types to Eigen's where <Eigen/Dense> is found.  Eigen is not in this image: a mock with
     Eigen's signatures and defaults (tests/cpp/mock_eigen) stands in for a compile-only check of that branch."""
     gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
-    for src in ("test_shim.cpp", "test_group.cpp"):
+    for src in ("test_shim.cpp", "test_group.cpp", "test_selection.cpp"):
         r = subprocess.run([gxx, "-std=c++17", "-Wall", "-fsyntax-only", "-I" + os.path.join(ROOT, "include"),
                             "-I" + os.path.join(ROOT, "tests", "cpp", "mock_eigen"), os.path.join(ROOT, "tests", "cpp", src)],
                            capture_output=True, text=True)
@@ -38,6 +38,57 @@ def test_shims_compile_against_the_eigen_interface():
                             "-I" + os.path.join(ROOT, "tests", "cpp", "mock_eigen"), "-x", "c++",
                             os.path.join(ROOT, "include", "agile_grasp2", "types.h")], capture_output=True, text=True)
     assert "AG2SHIM_HAVE_EIGEN" in probe.stdout
+
+
+def _splitmix64(x):
+    m = (1 << 64) - 1
+    x = (x + 0x9E3779B97F4A7C15) & m
+    x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & m
+    x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & m
+    return x ^ (x >> 31)
+
+
+def _selection_draw(seed, what, k):
+    m = (1 << 64) - 1
+    return _splitmix64((_splitmix64(seed ^ ((0xA5A5F00DBAADC0DE + what) & m)) + k) & m)
+
+
+@pytest.mark.parametrize("n,k,seed,cloud", [(10, 4, 5, 100), (40, 40, 1, 100), (40, 60, 1, 100), (200, 17, 99, 5000),
+                                            (30, 12, 7, 10), (1, 1, 0, 1), (0, 5, 3, 10)])
+def test_sample_selection_of_the_shims_vs_numpy_restatement(tmp_path, n, k, seed, cloud):
+    """include/agile_grasp2/sample_selection.h + CloudCamera::subsampleSamples on the CPU (tests/cpp/test_selection.cpp,
+    no ctx): CloudCamera::subsampleSamples (cloud_camera.cpp:181-206: all incoming samples when there are no more than
+    num_samples, else the first num_samples of a shuffled sequence), the strict workspace filter on sample points
+    (grasp_detector.cpp:305-313) and the draw with replacement from caller-supplied indices (grasp_detector.cpp:334-347),
+    against the same rules written in Python with the documented counter-based stream."""
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    exe = tmp_path / "test_selection"
+    r = subprocess.run([gxx, "-O1", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", str(exe),
+                        os.path.join(ROOT, "tests", "cpp", "test_selection.cpp")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = subprocess.run([str(exe), str(n), str(k), str(seed), str(cloud)], capture_output=True, text=True, check=True).stdout
+    lines = {ln.split()[0]: ln.split()[1:] for ln in out.strip().splitlines()}
+
+    def positions(count):
+        seq = list(range(count))
+        if k >= count:
+            return seq
+        for i in range(count - 1, 0, -1):
+            j = _selection_draw(seed, 1, i) % (i + 1)
+            seq[i], seq[j] = seq[j], seq[i]
+        return seq[:k]
+
+    assert [int(v) for v in lines["positions"]] == positions(n)
+    if n > k:
+        assert len(set(lines["positions"])) == k  # a subset without repetition
+    idx = [7 * i + 3 for i in range(n)]
+    want = [idx[_selection_draw(seed, 2, i) % n] for i in range(k)] if (n and k != n and k < cloud) else idx
+    assert [int(v) for v in lines["indices"]] == want
+    pts = np.array([[0.25 * (i % 7) - 0.25, 0.5 * (i % 6) - 0.5, -0.25 * (i % 5)] for i in range(n)]).reshape(-1, 3)
+    inside = pts[(pts[:, 0] > 0) & (pts[:, 0] < 1) & (pts[:, 1] > 0) & (pts[:, 1] < 2) & (pts[:, 2] > -1) & (pts[:, 2] < 0)]
+    assert int(lines["inside"][0]) == len(inside)
+    got = np.array([float(v) for v in lines["samples"]]).reshape(-1, 3)
+    assert np.array_equal(got, inside[positions(len(inside))].reshape(-1, 3))
 
 
 @pytest.mark.gpu
