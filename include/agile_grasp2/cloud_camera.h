@@ -7,8 +7,10 @@
 
 #include <ag2.h>
 
+#include <cstdio>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "sample_selection.h"
@@ -100,6 +102,25 @@ class CloudCamera {
   const ag2shim::Matrix3Xd& getSamples() const { return samples_; }
   void setSampleIndices(const std::vector<int>& sample_indices) { sample_indices_ = sample_indices; }
   void setSamples(const ag2shim::Matrix3Xd& samples) { samples_ = samples; }
+  // setSamples(const agile_grasp2::SamplesMsg&), cloud_camera.cpp:243-251: any message type with samples[i].x / .y / .z
+  template <class Msg, class = decltype(std::declval<const Msg&>().samples)>
+  void setSamples(const Msg& msg) {
+    samples_.resize(3, (int)msg.samples.size());
+    for (int i = 0; i < (int)msg.samples.size(); i++) {
+      samples_(0, i) = msg.samples[(size_t)i].x;
+      samples_(1, i) = msg.samples[(size_t)i].y;
+      samples_(2, i) = msg.samples[(size_t)i].z;
+    }
+  }
+
+  // writeNormalsToFile, cloud_camera.cpp:209-220: one "nx,ny,nz" line per column, 17 significant digits as
+  // boost::lexical_cast<std::string>(double) prints them
+  static void writeNormalsToFile(const std::string& filename, const ag2shim::Matrix3Xd& normals) {
+    std::FILE* f = std::fopen(filename.c_str(), "w");
+    if (!f) throw std::runtime_error("writeNormalsToFile: cannot open " + filename);
+    for (int i = 0; i < normals.cols(); i++) std::fprintf(f, "%.17g,%.17g,%.17g\n", normals(0, i), normals(1, i), normals(2, i));
+    std::fclose(f);
+  }
 
  private:
   static void check(int rc, const char* what) {

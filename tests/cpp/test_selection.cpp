@@ -42,5 +42,9 @@ int main(int argc, char** argv) {
   for (int c = 0; c < cc.getSamples().cols(); c++)
     std::printf(" %.17g %.17g %.17g", cc.getSamples()(0, c), cc.getSamples()(1, c), cc.getSamples()(2, c));
   std::printf("\n");
+  // setSamples(msg) keeps every sample in order; writeNormalsToFile prints one "x,y,z" line per column
+  cc.setSamples(msg);
+  std::printf("all %d\n", cc.getSamples().cols());
+  if (argc > 5) CloudCamera::writeNormalsToFile(argv[5], cc.getSamples());
   return 0;
 }

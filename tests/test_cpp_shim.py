@@ -66,7 +66,9 @@ def test_sample_selection_of_the_shims_vs_numpy_restatement(tmp_path, n, k, seed
     r = subprocess.run([gxx, "-O1", "-std=c++17", "-Wall", "-I" + os.path.join(ROOT, "include"), "-o", str(exe),
                         os.path.join(ROOT, "tests", "cpp", "test_selection.cpp")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
-    out = subprocess.run([str(exe), str(n), str(k), str(seed), str(cloud)], capture_output=True, text=True, check=True).stdout
+    nfile = tmp_path / "normals.csv"
+    out = subprocess.run([str(exe), str(n), str(k), str(seed), str(cloud), str(nfile)], capture_output=True, text=True,
+                         check=True).stdout
     lines = {ln.split()[0]: ln.split()[1:] for ln in out.strip().splitlines()}
 
     def positions(count):
@@ -89,6 +91,13 @@ def test_sample_selection_of_the_shims_vs_numpy_restatement(tmp_path, n, k, seed
     assert int(lines["inside"][0]) == len(inside)
     got = np.array([float(v) for v in lines["samples"]]).reshape(-1, 3)
     assert np.array_equal(got, inside[positions(len(inside))].reshape(-1, 3))
+    # CloudCamera::setSamples(msg) (cloud_camera.cpp:243-251) and writeNormalsToFile (:209-220)
+    assert int(lines["all"][0]) == len(inside)
+    text = nfile.read_text()
+    rows = np.array([[float(v) for v in ln.split(",")] for ln in text.splitlines()]).reshape(-1, 3)
+    assert np.array_equal(rows, inside)
+    if len(inside):
+        assert text.splitlines()[0] == ",".join("%.17g" % v for v in inside[0])
 
 
 @pytest.mark.gpu
