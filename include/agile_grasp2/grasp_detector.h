@@ -159,6 +159,12 @@ class GraspDetector {
   }
 
   void setUseIncomingSamples(bool b) { use_incoming_samples_ = b; }
+  // grasp_detector.h:86-125
+  static bool isScoreGreater(const GraspHypothesis& a, const GraspHypothesis& b) { return a.getScore() > b.getScore(); }
+  bool getUseIncomingSamples() const { return use_incoming_samples_; }
+  std::vector<double> getWorkspace() const { return std::vector<double>(p_.workspace, p_.workspace + 6); }
+  int getNumSamples() const { return prm_.num_samples; }
+  void setNumSamples(int num_samples) { prm_.num_samples = p_.num_samples = num_samples; }
   ag2_ctx* context() { return ctx_; }
   ag2_stats stats() {
     ag2_stats s;

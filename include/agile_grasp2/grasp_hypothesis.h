@@ -45,6 +45,46 @@ class GraspHypothesis {
                 rec_.top[1], rec_.top[2]);
   }
 
+  // agile_grasp2/GraspMsg (msg/GraspMsg.msg:5-16) as a plain struct: points and vectors in double, width and score
+  // narrowed to float32 as std_msgs/Float32 does
+  struct GraspMsg {
+    struct Xyz {
+      double x, y, z;
+    };
+    struct Float32 {
+      float data;
+    };
+    Xyz surface, bottom, top, axis, approach, binormal;
+    Float32 width, score;
+  };
+  // convertToGraspMsg, grasp_hypothesis.cpp:37-50
+  GraspMsg convertToGraspMsg() const {
+    GraspMsg m;
+    m.surface = GraspMsg::Xyz{rec_.surface[0], rec_.surface[1], rec_.surface[2]};
+    m.bottom = GraspMsg::Xyz{rec_.bottom[0], rec_.bottom[1], rec_.bottom[2]};
+    m.top = GraspMsg::Xyz{rec_.top[0], rec_.top[1], rec_.top[2]};
+    m.axis = GraspMsg::Xyz{rec_.axis[0], rec_.axis[1], rec_.axis[2]};
+    m.approach = GraspMsg::Xyz{rec_.approach[0], rec_.approach[1], rec_.approach[2]};
+    m.binormal = GraspMsg::Xyz{rec_.binormal[0], rec_.binormal[1], rec_.binormal[2]};
+    m.width.data = (float)rec_.width;
+    m.score.data = (float)rec_.score;
+    return m;
+  }
+
+  // writeHandsToFile, grasp_hypothesis.cpp:4-23 (without its console echo): per hand one line of bottom, surface, axis,
+  // approach, binormal -- each component followed by a comma, 17 significant digits as
+  // boost::lexical_cast<std::string>(double) prints -- then the width as an ostream prints a double (%g)
+  static void writeHandsToFile(const std::string& filename, const std::vector<GraspHypothesis>& hands) {
+    std::FILE* f = std::fopen(filename.c_str(), "w");
+    if (!f) return;  // the reference's ofstream fails silently too
+    for (const GraspHypothesis& h : hands) {
+      const double* v[5] = {h.rec_.bottom, h.rec_.surface, h.rec_.axis, h.rec_.approach, h.rec_.binormal};
+      for (int k = 0; k < 5; k++) std::fprintf(f, "%.17g,%.17g,%.17g,", v[k][0], v[k][1], v[k][2]);
+      std::fprintf(f, "%g\n", h.rec_.width);
+    }
+    std::fclose(f);
+  }
+
   // convertToGraspMsg / createGraspListMsg (grasp_hypothesis.cpp:37-50, grasp_detection_node.cpp:306-313):
   // the ROS wire bytes of an agile_grasp2/GraspListMsg
   static std::vector<uint8_t> toGraspListMsg(const std::vector<GraspHypothesis>& hands, const std::string& frame_id,

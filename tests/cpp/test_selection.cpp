@@ -1,6 +1,7 @@
 // Host-only check of include/agile_grasp2/sample_selection.h and CloudCamera::subsampleSamples: prints the choices
 // for the cases tests/test_cpp_shim.py restates in numpy.  Needs no GPU (no ag2_ctx is created).
 #include <agile_grasp2/cloud_camera.h>
+#include <agile_grasp2/grasp_hypothesis.h>
 #include <agile_grasp2/sample_selection.h>
 
 #include <cstdio>
@@ -46,5 +47,26 @@ int main(int argc, char** argv) {
   cc.setSamples(msg);
   std::printf("all %d\n", cc.getSamples().cols());
   if (argc > 5) CloudCamera::writeNormalsToFile(argv[5], cc.getSamples());
+  // GraspHypothesis: convertToGraspMsg narrows width and score to float32; writeHandsToFile's line format
+  if (argc > 6) {
+    std::vector<GraspHypothesis> hands;
+    for (int h = 0; h < 3; h++) {
+      ag2_hypothesis r = ag2_hypothesis();
+      for (int a = 0; a < 3; a++) {
+        r.bottom[a] = 0.1 * (h + 1) + a / 3.0;
+        r.surface[a] = -0.2 * (h + 1) + a / 7.0;
+        r.top[a] = 0.3 + a;
+        r.axis[a] = a == 0;
+        r.approach[a] = a == 1;
+        r.binormal[a] = a == 2;
+      }
+      r.width = 0.05 + h / 300.0;
+      r.score = 1.0 / 3.0 + h;
+      hands.push_back(GraspHypothesis(r, nullptr));
+    }
+    GraspHypothesis::writeHandsToFile(argv[6], hands);
+    GraspHypothesis::GraspMsg m = hands[1].convertToGraspMsg();
+    std::printf("msg %.17g %.17g %.9g %.9g\n", m.bottom.x, m.surface.z, (double)m.width.data, (double)m.score.data);
+  }
   return 0;
 }

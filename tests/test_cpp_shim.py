@@ -67,7 +67,8 @@ def test_sample_selection_of_the_shims_vs_numpy_restatement(tmp_path, n, k, seed
                         os.path.join(ROOT, "tests", "cpp", "test_selection.cpp")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
     nfile = tmp_path / "normals.csv"
-    out = subprocess.run([str(exe), str(n), str(k), str(seed), str(cloud), str(nfile)], capture_output=True, text=True,
+    hfile = tmp_path / "hands.csv"
+    out = subprocess.run([str(exe), str(n), str(k), str(seed), str(cloud), str(nfile), str(hfile)], capture_output=True, text=True,
                          check=True).stdout
     lines = {ln.split()[0]: ln.split()[1:] for ln in out.strip().splitlines()}
 
@@ -98,6 +99,18 @@ def test_sample_selection_of_the_shims_vs_numpy_restatement(tmp_path, n, k, seed
     assert np.array_equal(rows, inside)
     if len(inside):
         assert text.splitlines()[0] == ",".join("%.17g" % v for v in inside[0])
+    # GraspHypothesis::writeHandsToFile (grasp_hypothesis.cpp:4-23) and convertToGraspMsg (:37-50)
+    hl = hfile.read_text().splitlines()
+    assert len(hl) == 3
+    for h, ln in enumerate(hl):
+        bottom = [0.1 * (h + 1) + a / 3.0 for a in range(3)]
+        surface = [-0.2 * (h + 1) + a / 7.0 for a in range(3)]
+        want = "".join("%.17g," % v for v in bottom + surface + [1, 0, 0, 0, 1, 0, 0, 0, 1]) + "%g" % (0.05 + h / 300.0)
+        assert ln == want
+    m = [float(v) for v in lines["msg"]]
+    assert m[0] == 0.1 * 2 and m[1] == -0.2 * 2 + 2 / 7.0
+    assert np.float32(m[2]) == np.float32(0.05 + 1 / 300.0) and np.float32(m[3]) == np.float32(1.0 / 3.0 + 1)
+    assert m[2] != 0.05 + 1 / 300.0  # narrowed, not the double
 
 
 @pytest.mark.gpu
