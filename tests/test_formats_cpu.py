@@ -116,3 +116,36 @@ def test_grasp_list_wire_format():
         assert np.array_equal(np.array(v[:18]), exp)
         assert v[18] == np.float32(h["width"][i]) and v[19] == np.float32(h["score"][i])
         off += 152
+
+
+def test_pcd_header_variants(tmp_path):
+    """Headers real .pcd files carry and pcl::io::loadPCDFile accepts (cloud_camera.cpp:231-240): double-typed
+    coordinates, organised clouds (WIDTH x HEIGHT), fields with COUNT > 1 and extra fields around x y z, a v0.6 header
+    without COUNT, no VIEWPOINT line, CRLF line ends, PCL's "_" padding field, ascii data."""
+    rng = np.random.default_rng(1)
+    n = 12
+    xyz = rng.normal(0, 1, (n, 3))
+    f32 = xyz.astype(np.float32)
+    tail = "WIDTH %d\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %d\nDATA binary\n" % (n, n)
+    cases = {
+        "double": ("VERSION 0.7\nFIELDS x y z\nSIZE 8 8 8\nTYPE F F F\nCOUNT 1 1 1\n" + tail, xyz.astype("<f8").tobytes()),
+        "organised": ("VERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\nWIDTH 4\nHEIGHT 3\n"
+                      "VIEWPOINT 0 0 0 1 0 0 0\nPOINTS 12\nDATA binary\n", f32.tobytes()),
+        "count5": ("VERSION 0.7\nFIELDS fpfh x y z intensity\nSIZE 4 4 4 4 2\nTYPE F F F F U\nCOUNT 5 1 1 1 1\n" + tail,
+                   b"".join(struct.pack("<5f3fH", 0, 1, 2, 3, 4, *f32[i], 7) for i in range(n))),
+        "ascii_no_viewpoint": ("# comment\nVERSION .7\nFIELDS x y z rgb\nSIZE 4 4 4 4\nTYPE F F F F\nCOUNT 1 1 1 1\n"
+                               "WIDTH 12\nHEIGHT 1\nPOINTS 12\nDATA ascii\n",
+                               ("\n".join("%r %r %r 4.2e-38" % tuple(float(v) for v in f32[i]) for i in range(n)) + "\n").encode()),
+        "v06_no_count": ("VERSION 0.6\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nWIDTH 12\nHEIGHT 1\nPOINTS 12\nDATA binary\n",
+                         f32.tobytes()),
+        "crlf": (("VERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\n" + tail).replace("\n", "\r\n"), f32.tobytes()),
+        "padding": ("VERSION 0.7\nFIELDS x y z _ rgba\nSIZE 4 4 4 1 4\nTYPE F F F U U\nCOUNT 1 1 1 4 1\n" + tail,
+                    b"".join(struct.pack("<3f4BI", *f32[i], 0, 0, 0, 0, 0xFF112233) for i in range(n))),
+    }
+    for name, (hdr, body) in cases.items():
+        path = tmp_path / (name + ".pcd")
+        path.write_bytes(hdr.encode() + body)
+        got = capi.pcd_read(str(path))
+        got_xyz = got[0] if isinstance(got, tuple) else got["xyz"]
+        assert got_xyz.shape == (n, 3), name
+        assert np.array_equal(got_xyz, f32), name
