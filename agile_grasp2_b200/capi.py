@@ -242,6 +242,17 @@ def default_params() -> Params:
     return p
 
 
+def read_lenet_caffemodel(path: str) -> dict:
+    """ag2_read_lenet_caffemodel: the eight blobs of a .caffemodel as float32 arrays (host parser, no ctx)."""
+    lib = load().lib
+    out = {k: np.zeros(shp, np.float32) for k, shp in LENET_SHAPES}
+    lib.ag2_read_lenet_caffemodel.restype = C.c_int
+    rc = lib.ag2_read_lenet_caffemodel(path.encode(), *[_fptr(out[k]) for k, _ in LENET_SHAPES])
+    if rc:
+        raise Ag2Error(rc, "ag2_read_lenet_caffemodel", path)
+    return out
+
+
 def pcd_read(path: str):
     """ag2_pcd_read: returns (xyz [N,3] f32, normals [N,3] f32 or None, rgba [N] u32 or None)."""
     lib = load().lib

@@ -165,6 +165,24 @@ int load_caffemodel(const char* path, std::vector<float> out[8], std::string& er
   return AG2_OK;
 }
 
+}  // namespace ag2
+
+// The same parser without a context: the blobs of a .caffemodel into host arrays (NULL = not wanted).
+extern "C" int ag2_read_lenet_caffemodel(const char* path, float* conv1_w, float* conv1_b, float* conv2_w,
+                                         float* conv2_b, float* ip1_w, float* ip1_b, float* ip2_w, float* ip2_b) {
+  if (!path) return AG2_E_INVALID;
+  std::vector<float> w[8];
+  std::string err;
+  int rc = ag2::load_caffemodel(path, w, err);
+  if (rc) return rc;
+  float* dst[8] = {conv1_w, conv1_b, conv2_w, conv2_b, ip1_w, ip1_b, ip2_w, ip2_b};
+  for (int i = 0; i < 8; i++)
+    if (dst[i]) memcpy(dst[i], w[i].data(), w[i].size() * sizeof(float));
+  return AG2_OK;
+}
+
+namespace ag2 {
+
 // Caffe XavierFiller: uniform(-s, s), s = sqrt(3 / fan_in), fan_in = count / num_output;
 // bias filler defaults to constant 0.  Deterministic splitmix64 stream.
 void xavier_fill(uint64_t seed, std::vector<float> out[8]) {

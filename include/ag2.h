@@ -188,6 +188,13 @@ int ag2_abi_version(void);
 /* Replaces Classifier ctor's net_->CopyTrainedLayersFrom (caffe_classifier.cpp:13-14):
  * parses the caffemodel protobuf wire format (V1 "layers" and V2 "layer"). */
 int ag2_load_lenet_caffemodel(ag2_ctx* ctx, const char* path);
+/* The parser behind it on its own (host code, no ctx, no GPU): the eight blobs of a .caffemodel into caller
+ * arrays in the layouts of ag2_set_lenet_weights (conv1 20x1500/20 ... see below; NULL = not wanted).  Layers are
+ * matched by the names of caffe/sigmoid_lenet.prototxt:10,34,58,76 (conv1, conv2, ip1, ip2); a layer without a
+ * bias blob gets zeros; AG2_E_IO for an unreadable or malformed file, a missing layer or blob sizes that are not
+ * the prototxt's. */
+int ag2_read_lenet_caffemodel(const char* path, float* conv1_w, float* conv1_b, float* conv2_w, float* conv2_b,
+                              float* ip1_w, float* ip1_b, float* ip2_w, float* ip2_b);
 /* The same blobs from memory (what net_->CopyTrainedLayersFrom leaves in the four layers of
  * caffe/sigmoid_lenet.prototxt:10-90).  Caffe blob layouts: conv [out,in,kh,kw], ip [out,in]; fp32. */
 int ag2_set_lenet_weights(ag2_ctx* ctx, const float* conv1_w, const float* conv1_b,

@@ -149,3 +149,98 @@ def test_pcd_header_variants(tmp_path):
         got_xyz = got[0] if isinstance(got, tuple) else got["xyz"]
         assert got_xyz.shape == (n, 3), name
         assert np.array_equal(got_xyz, f32), name
+
+
+# ---- .caffemodel (protobuf wire format of caffe.NetParameter), written here by hand -------------------------------
+
+def _varint(v: int) -> bytes:
+    out = bytearray()
+    while True:
+        b = v & 0x7F
+        v >>= 7
+        out.append(b | (0x80 if v else 0))
+        if not v:
+            return bytes(out)
+
+
+def _field(num: int, wire: int, payload: bytes) -> bytes:
+    return _varint((num << 3) | wire) + (_varint(len(payload)) + payload if wire == 2 else payload)
+
+
+def _blob(a: np.ndarray, packed: bool, legacy_dims: bool) -> bytes:
+    a = np.ascontiguousarray(a, "<f4")
+    out = b""
+    if legacy_dims:  # BlobProto.num / channels / height / width = 1..4
+        dims = (list(a.shape) + [1, 1, 1, 1])[:4]
+        out += b"".join(_field(i + 1, 0, _varint(d)) for i, d in enumerate(dims))
+    else:  # BlobProto.shape = 7 { dim = 1, packed }
+        out += _field(7, 2, _field(1, 2, b"".join(_varint(d) for d in a.shape)))
+    if packed:
+        out += _field(5, 2, a.tobytes())
+    else:
+        out += b"".join(_field(5, 5, a.reshape(-1)[i:i + 1].tobytes()) for i in range(a.size))
+    return out
+
+
+def _caffemodel(w: dict, v1: bool, packed: bool = True, skip_bias_of=(), order=("conv1", "conv2", "ip1", "ip2")) -> bytes:
+    """NetParameter: name = 1; V2 layer = 100 {name = 1, type = 2 (string), bottom = 3, top = 4, blobs = 7};
+    V1 layers = 2 {bottom = 2, top = 3, name = 4, type = 5 (enum), blobs = 6}; plus layers without blobs."""
+    name_f, blobs_f, layer_f = (4, 6, 2) if v1 else (1, 7, 100)
+    out = _field(1, 2, b"LeNet")
+    pool = _field(name_f, 2, b"pool1") + (_field(5, 0, _varint(17)) if v1 else _field(2, 2, b"Pooling"))
+    out += _field(layer_f, 2, pool)
+    for name in order:
+        body = _field(name_f, 2, name.encode())
+        body += _field(5, 0, _varint(4)) if v1 else _field(2, 2, b"Convolution")
+        body += _field(2 if v1 else 3, 2, b"data") + _field(3 if v1 else 4, 2, name.encode())
+        # conv / ip weights are unpacked only for the small layers (an unpacked ip1 would be 18 MB of 5-byte fields)
+        body += _field(blobs_f, 2, _blob(w[name + "_w"], packed or name == "ip1", v1))
+        if name not in skip_bias_of:
+            body += _field(blobs_f, 2, _blob(w[name + "_b"], packed, v1))
+        out += _field(layer_f, 2, body)
+    return out
+
+
+def _weights(seed=3):
+    rng = np.random.default_rng(seed)
+    return {k: rng.normal(0, 0.1, shp).astype(np.float32) for k, shp in capi.LENET_SHAPES}
+
+
+def test_caffemodel_v2_v1_packed_and_repeated(tmp_path):
+    """Net::CopyTrainedLayersFrom's input (caffe_classifier.cpp:13-14): current `layer` and legacy V1 `layers` messages,
+    packed and one-float-per-field blob data, blobs with shape or with num/channels/height/width, layers in any order,
+    layers without blobs in between -- all give back the blobs bit for bit."""
+    w = _weights()
+    for v1, packed, order in ((False, True, ("conv1", "conv2", "ip1", "ip2")), (True, True, ("ip2", "conv2", "ip1", "conv1")),
+                              (False, False, ("conv1", "conv2", "ip1", "ip2")), (True, False, ("conv1", "conv2", "ip1", "ip2"))):
+        path = tmp_path / ("lenet_%d_%d.caffemodel" % (v1, packed))
+        path.write_bytes(_caffemodel(w, v1, packed, order=order))
+        got = capi.read_lenet_caffemodel(str(path))
+        for k, _ in capi.LENET_SHAPES:
+            assert np.array_equal(got[k], w[k]), (v1, packed, k)
+
+
+def test_caffemodel_missing_bias_and_errors(tmp_path):
+    import pytest
+
+    w = _weights(4)
+    path = tmp_path / "nobias.caffemodel"
+    path.write_bytes(_caffemodel(w, False, skip_bias_of=("conv2",)))
+    got = capi.read_lenet_caffemodel(str(path))
+    assert np.array_equal(got["conv2_w"], w["conv2_w"]) and not got["conv2_b"].any()  # bias_term: false -> zeros
+    good = _caffemodel(w, False)
+    bad = dict(w)
+    bad["conv1_w"] = np.zeros((20, 1, 5, 5), np.float32)  # a grey-scale LeNet: not the prototxt's shapes
+    cases = {
+        "truncated": good[: len(good) // 2],
+        "wrong_shape": _caffemodel(bad, False),
+        "missing_layer": _caffemodel(w, False, order=("conv1", "conv2", "ip1")),
+        "garbage": bytes(range(256)) * 7,
+    }
+    for name, data in cases.items():
+        p = tmp_path / (name + ".caffemodel")
+        p.write_bytes(data)
+        with pytest.raises(capi.Ag2Error):
+            capi.read_lenet_caffemodel(str(p))
+    with pytest.raises(capi.Ag2Error):
+        capi.read_lenet_caffemodel(str(tmp_path / "does_not_exist.caffemodel"))
