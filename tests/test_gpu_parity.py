@@ -670,3 +670,26 @@ def test_image_cells_on_a_sixtieth_boundary_gpu_equals_oracle(aligns):
         got = g.render_point_sets(pts, nrm, [0, len(pts)], aligns=aligns)[0]
     want = ob.context(p).render_point_sets(pts, nrm, [0, len(pts)], aligns=aligns)[0]
     assert np.array_equal(got, want), int(np.sum(got != want))
+
+
+def test_caffemodel_file_loads_like_set_lenet_weights(tmp_path):
+    """Classifier ctor -> net_->CopyTrainedLayersFrom(trained_file) (caffe_classifier.cpp:13-14): a .caffemodel written by
+    the hand-made protobuf writer of test_formats_cpu.py (legacy V1 layers, bias of ip2 absent) gives the ctx the same
+    blobs, and the same logits bit for bit, as ag2_set_lenet_weights with the arrays."""
+    from test_formats_cpu import _caffemodel
+
+    w = {k: v.copy() for k, v in ob.xavier_weights(11, bias_scale=0.2).items()}
+    path = tmp_path / "lenet.caffemodel"
+    path.write_bytes(_caffemodel(w, True, skip_bias_of=("ip2",)))
+    w["ip2_b"] = np.zeros_like(w["ip2_b"])
+    imgs = np.random.default_rng(2).integers(0, 256, (9, 60, 60, 3), dtype=np.uint8)
+    p = make_params(capi.MODE_PREDICTION)
+    with capi.Context(p) as a, capi.Context(p) as b:
+        a.load_lenet_caffemodel(str(path))
+        b.set_lenet_weights(w)
+        got = a.get_lenet_weights()
+        for k, _ in capi.LENET_SHAPES:
+            assert np.array_equal(np.asarray(got[k]).reshape(w[k].shape), w[k]), k
+        assert np.array_equal(a.classify_images(imgs), b.classify_images(imgs))
+        with pytest.raises(capi.Ag2Error):
+            a.load_lenet_caffemodel(str(tmp_path / "missing.caffemodel"))
