@@ -120,3 +120,45 @@ def test_every_declaration_block_cites_the_reference_or_says_it_has_no_counterpa
     for m in decls:
         own += bool(cite.search(re.sub(r"\s*\n\s*\*\s*", " ", m.group(1))))
     assert len(decls) >= 70 and own >= 0.75 * len(decls), (own, len(decls))
+
+
+def test_reference_citations_point_into_existing_files():
+    """Every `file.ext:line[-line]` citation of a reference file in the headers, the sources, the oracle, the tests and
+    the design documents names a file of the reference checkout and lines inside it.  Skipped where the checkout is
+    absent (the GPU box)."""
+    import subprocess
+
+    ref = "/root/reference"
+    if not os.path.isdir(ref):
+        pytest.skip("reference checkout not present")
+    lengths = {}
+    for root, _, files in os.walk(ref):
+        if ".git" in root:
+            continue
+        for f in files:
+            try:
+                n = sum(1 for _ in open(os.path.join(root, f), errors="ignore"))
+            except OSError:
+                continue
+            lengths[f] = max(lengths.get(f, 0), n)
+    tracked = subprocess.run(["git", "ls-files"], cwd=ROOT, capture_output=True, text=True).stdout.split()
+    if not tracked:
+        pytest.skip("not a git checkout")
+    ours = [p for p in tracked if p.endswith((".md", ".h", ".py", ".cu", ".cuh", ".cpp"))
+            and not p.startswith(("SURVEY", "VERDICT", "ADVICE", "PAPERS", "SNIPPETS"))]
+    own_names = {os.path.basename(p) for p in tracked}
+    pat = re.compile(r"\b([A-Za-z_0-9]+\.(?:cpp|h|prototxt|launch|msg)):(\d+)(?:-(\d+))?((?:,\s?:?\d+(?:-\d+)?)*)")
+    bad, checked = [], 0
+    for p in ours:
+        text = open(os.path.join(ROOT, p), errors="ignore").read()
+        for m in pat.finditer(text):
+            name = m.group(1)
+            if name not in lengths:
+                if name not in own_names:
+                    bad.append((p, m.group(0), "no such reference file"))
+                continue
+            nums = [int(v) for v in re.findall(r"\d+", m.group(0)[len(name):])]
+            checked += 1
+            if max(nums) > lengths[name] or min(nums) < 1:
+                bad.append((p, m.group(0), "file has %d lines" % lengths[name]))
+    assert checked > 300 and not bad, bad[:10]
