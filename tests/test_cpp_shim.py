@@ -193,6 +193,35 @@ def _fill_unit_box(h, dens, start):
 
 
 @pytest.mark.gpu
+def test_detect_grasps_file_example_equals_the_c_abi_steps(tiny_scene, tmp_path):
+    """examples/detect_grasps_file (the headless stand-in for src/nodes/detect_grasps_file.cpp +
+    grasp_detection_node.cpp:98-120) on a .pcd of the tiny scene: its grasp file holds what the same steps give
+    through the C ABI (preprocess, subsample, detect), and its GraspListMsg bytes have the wire size."""
+    exe = os.path.join(ROOT, "examples", "detect_grasps_file")
+    assert os.path.exists(exe), "build examples first (__graft_entry__.build())"
+    pcd, hands_file, msg_file = str(tmp_path / "scene.pcd"), str(tmp_path / "hands.csv"), str(tmp_path / "grasps.bin")
+    capi.pcd_write(pcd, tiny_scene["xyz"], binary=True)
+    r = subprocess.run([exe, "cloud_file_name:=" + pcd, "num_samples:=64", "antipodal_mode:=2", "min_inliers:=0",
+                        "rng_seed:=5", "_num_selected:=30", "hands_file:=" + hands_file, "msg_file:=" + msg_file],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    p = make_params(capi.MODE_GEOMETRIC, num_selected=30, num_samples=64, rng_seed=5, min_inliers=0, num_threads=4,
+                    filter_half_grasps=0, min_aperture=0.03, max_aperture=0.08, min_score_diff=300.0)
+    with capi.Context(p) as g:
+        g.preprocess_cloud(tiny_scene["xyz"], None, 1, voxelize=True, voxel_size=0.003)
+        g.subsample_uniformly(64, seed=5)
+        g.detect()
+        want = g.hypotheses(capi.LIST_SELECTED)
+    assert ("# grasps: %d;" % len(want)) in r.stdout and len(want) > 0
+    rows = np.array([[float(v) for v in ln.split(",")] for ln in open(hands_file).read().splitlines()]).reshape(-1, 16)
+    assert len(rows) == len(want)
+    for k, name in enumerate(("bottom", "surface", "axis", "approach", "binormal")):
+        assert np.array_equal(rows[:, 3 * k:3 * k + 3], want[name]), name
+    assert np.allclose(rows[:, 15], want["width"], rtol=1e-5)
+    assert os.path.getsize(msg_file) == 16 + 4 + 4 + len(want) * 152
+
+
+@pytest.mark.gpu
 @pytest.mark.skipif("__import__('torch').cuda.device_count() < 2")
 def test_cpp_group_two_gpus_equals_one(tiny_scene, tmp_path):
     """tests/cpp/test_group.cpp: GraspDetector / ImportanceSampling with Params::num_gpus = 2 (ag2_group_create:
