@@ -201,13 +201,14 @@ def test_detect_grasps_file_example_equals_the_c_abi_steps(tiny_scene, tmp_path)
     assert os.path.exists(exe), "build examples first (__graft_entry__.build())"
     pcd, hands_file, msg_file = str(tmp_path / "scene.pcd"), str(tmp_path / "hands.csv"), str(tmp_path / "grasps.bin")
     capi.pcd_write(pcd, tiny_scene["xyz"], binary=True)
-    r = subprocess.run([exe, "cloud_file_name:=" + pcd, "num_samples:=64", "antipodal_mode:=2", "min_inliers:=0",
-                        "rng_seed:=5", "_num_selected:=30", "hands_file:=" + hands_file, "msg_file:=" + msg_file],
+    r = subprocess.run([exe, "cloud_file_name:=" + pcd, "num_samples:=64", "antipodal_mode:=1", "min_inliers:=0",
+                        "min_score_diff:=-1e9", "rng_seed:=5", "_num_selected:=30", "hands_file:=" + hands_file, "msg_file:=" + msg_file],
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    p = make_params(capi.MODE_GEOMETRIC, num_selected=30, num_samples=64, rng_seed=5, min_inliers=0, num_threads=4,
-                    filter_half_grasps=0, min_aperture=0.03, max_aperture=0.08, min_score_diff=300.0)
+    p = make_params(capi.MODE_PREDICTION, num_selected=30, num_samples=64, rng_seed=5, min_inliers=0, num_threads=4,
+                    filter_half_grasps=0, min_aperture=0.03, max_aperture=0.08, min_score_diff=-1e9)
     with capi.Context(p) as g:
+        g.init_lenet_xavier(1)  # the shim's weights when trained_file is empty
         g.preprocess_cloud(tiny_scene["xyz"], None, 1, voxelize=True, voxel_size=0.003)
         g.subsample_uniformly(64, seed=5)
         g.detect()
