@@ -69,6 +69,21 @@ class HandSearch {
     p_.prune = 0;
   }
   explicit HandSearch(const Parameters& params) : HandSearch() { setParameters(params); }
+  // hand_search.h:114-118: hand geometry only; nn_radius_taubin_ = 0.03 and nn_radius_hands_ = 0.08 as there (the
+  // reference leaves num_orientations_ uninitialised in this constructor; the default of 8 is kept)
+  HandSearch(double finger_width, double hand_outer_diameter, double hand_depth, double hand_height, double init_bite,
+             int num_threads, int num_samples)
+      : HandSearch() {
+    p_.finger_width = finger_width;
+    p_.hand_outer_diameter = hand_outer_diameter;
+    p_.hand_depth = hand_depth;
+    p_.hand_height = hand_height;
+    p_.init_bite = init_bite;
+    p_.num_threads = num_threads;
+    p_.num_samples = num_samples;
+    p_.nn_radius_taubin = 0.03;
+    p_.nn_radius_hands = 0.08;
+  }
   ~HandSearch() { ag2_destroy(ctx_); }
   HandSearch(const HandSearch&) = delete;
   HandSearch& operator=(const HandSearch&) = delete;
