@@ -602,15 +602,23 @@ def test_grasp_images_vs_numpy_restatement():
     assert differing <= 1e-5 * total, (differing, total)
 
 
-def test_finger_sweep_vs_numpy_restatement():
+@pytest.mark.parametrize("geom", [
+    {},  # the launch files' hand (finger 1 cm, aperture 9 cm, depth 6 cm, height 2 cm, bite 1 cm), 8 orientations
+    {"num_orientations": 16, "nn_radius_hands": 0.06},  # c5's corner: more orientations, smaller neighbourhood
+    {"num_orientations": 5, "finger_width": 0.015, "hand_outer_diameter": 0.12, "hand_depth": 0.08, "hand_height": 0.03,
+     "init_bite": 0.015, "nn_radius_hands": 0.12},  # a larger hand
+    {"num_orientations": 3, "finger_width": 0.005, "hand_outer_diameter": 0.06, "hand_depth": 0.03, "hand_height": 0.01,
+     "init_bite": 0.0},  # a small hand that starts at the surface
+], ids=["default", "r16_small_radius", "large_hand", "small_hand"])
+def test_finger_sweep_vs_numpy_restatement(geom):
     """HandSearch::calculateHand (hand_search.cpp:319-426) with FingerHand::evaluateFingers / evaluateHand / deepenHand /
     computePointsInClosingRegion (finger_hand.cpp:17-180, 313-325), restated in numpy from the reference text for every
     (sample, orientation) of a scene: crop at the hand height, rotate, finger placements free of points below the bite,
     hands = matching finger pairs, middle hand, deepen in 5 mm steps while both of its fingers stay free, closing region.
     The oracle's sweep records (finger mask, hand mask, chosen slot, deepen steps, in-box count, emitted) must equal it."""
     from common import load_scene
-    sc = scenes.make_scene("tiny", num_samples=150)
-    p = make_params(capi.MODE_NONE)
+    sc = scenes.make_scene("tiny", num_samples=150 if not geom else 60)
+    p = make_params(capi.MODE_NONE, **geom)
     o = ob.context(p)
     load_scene(o, sc)
     o.detect()
@@ -665,7 +673,8 @@ def test_finger_sweep_vs_numpy_restatement():
             assert rec["num_in_box"] == inbox.sum(), (s, r)
             assert rec["emitted"] == (1 if inbox.any() else 0)
             emitted += int(inbox.any())
-    assert checked > 900 and emitted > 60
+    print("finger sweep pin:", geom, "pairs", checked, "emitted", emitted)
+    assert checked > (900 if not geom else 100) and emitted > (60 if not geom else 10)
 
 
 def test_grasp_poses_vs_numpy_restatement():
