@@ -4,6 +4,7 @@ import os
 import sys
 
 import numpy as np
+import pytest
 import torch.multiprocessing as mp
 
 from agile_grasp2_b200 import capi, scenes, sharded
@@ -38,11 +39,13 @@ def _worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-def test_two_rank_result_equals_single_process(tmp_path):
-    world, port = 2, 29541 + (os.getpid() % 200)
+@pytest.mark.parametrize("world", [2, 3])  # 40 samples over three ranks: shards of 14, 13, 13
+def test_two_rank_result_equals_single_process(tmp_path, world):
+    port = 29541 + (os.getpid() % 200) + 211 * world
     mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
-    a, b = np.load(tmp_path / "sel0.npy"), np.load(tmp_path / "sel1.npy")
-    assert a.tobytes() == b.tobytes()  # every rank holds the same merged selection
+    a = np.load(tmp_path / "sel0.npy")
+    for r in range(1, world):
+        assert a.tobytes() == np.load(tmp_path / ("sel%d.npy" % r)).tobytes()  # every rank holds the same merged selection
     p = make_params(capi.MODE_GEOMETRIC, num_selected=10, num_threads=2)
     sc = scenes.make_scene("tiny", num_samples=40)
     o = ob.context(p)
